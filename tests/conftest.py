@@ -1,0 +1,24 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def kd_lw():
+    from rte_rrtmgp_cpp_b200.kdist import synthetic_kdist
+    return synthetic_kdist("lw")
+
+
+@pytest.fixture(scope="session")
+def kd_sw():
+    from rte_rrtmgp_cpp_b200.kdist import synthetic_kdist
+    return synthetic_kdist("sw")
