@@ -1,0 +1,261 @@
+/*
+ * rrtmgp_b200.h — C ABI of the B200-native (sm_100a) column radiation hot path.
+ *
+ * This is the drop-in boundary.  The reference has no FFI: callers link its
+ * static libs and call the L3 C++ classes.  Each entry point below names the reference
+ * interface it replaces (paths relative to the reference root).  The thin C++ class layer
+ * in include/rrtmgp_b200/ (same class and method names as the reference) and the Python mirror
+ * in rte_rrtmgp_cpp_b200/api.py call only these symbols.
+ *
+ * Conventions
+ *  - every pointer named d_* is a DEVICE pointer; arrays are column-major (first index
+ *    fastest) in exactly the reference's shapes; integer tables hold 1-based Fortran indices;
+ *  - `Real` is float for a plan created with RRTMGP_B200_F32, double for RRTMGP_B200_F64
+ *    (the reference's compile-time `Float`, include/types.h:19-25); Bool is signed char
+ *    (RTE_USE_CBOOL, include/types.h:13-17);
+ *  - every call returns 0 on success or an RRTMGP_B200_E* code; the message is available from
+ *    rrtmgp_b200_last_error() (thread-local).  The C++ class layer maps codes back to the
+ *    reference's exception types (E_RANGE -> std::range_error, others -> std::runtime_error);
+ *  - every call takes the CUDA stream to launch on (as void*, a cudaStream_t); no call
+ *    synchronises the device unless documented; no global state besides the error string;
+ *  - there is NO CPU fallback: without a CUDA device every compute call fails with E_CUDA.
+ */
+#ifndef RRTMGP_B200_H
+#define RRTMGP_B200_H
+
+#include <stddef.h>
+#include "rrtmgp_b200_tables.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { RRTMGP_B200_F32 = 0, RRTMGP_B200_F64 = 1,
+       /* OR-ed into dtype at gas_optics_create: build the host tables only (no device upload), so
+        * the constructor logic can be checked on a machine without a GPU.  Compute calls on such a
+        * handle fail with E_CUDA. */
+       RRTMGP_B200_HOST_ONLY = 0x100 };
+
+enum {
+    RRTMGP_B200_OK = 0,
+    RRTMGP_B200_E_ARG = 1,      /* bad dimensions / null pointer / unsupported combination  */
+    RRTMGP_B200_E_RANGE = 2,    /* input outside the k-distribution's validity range        */
+    RRTMGP_B200_E_MISSING = 3,  /* required gas missing (std::runtime_error in the reference) */
+    RRTMGP_B200_E_CUDA = 4      /* CUDA runtime failure (reference: printf + throw 1)        */
+};
+
+typedef struct rrtmgp_b200_gas_optics rrtmgp_b200_gas_optics;     /* Gas_optics_rrtmgp_gpu  */
+typedef struct rrtmgp_b200_cloud_optics rrtmgp_b200_cloud_optics; /* Cloud_optics_gpu       */
+
+const char* rrtmgp_b200_last_error(void);
+int rrtmgp_b200_version(void);
+
+/* ---- Gas_optics_rrtmgp_gpu constructor / destructor / getters -------------------------------
+ * replaces Gas_optics_rrtmgp_gpu::Gas_optics_rrtmgp_gpu (include/Gas_optics_rrtmgp.h:293-364,
+ * src_cuda/Gas_optics_rrtmgp.cu:427-803; CPU twin src/Gas_optics_rrtmgp.cpp:391-742) fed with
+ * the file variables read at src_test/Radiation_solver.cpp:78-243.  `gas_names_avail` is the
+ * blank-padded [n_avail][string_len] list of gases present in the caller's Gas_concs. */
+int rrtmgp_b200_gas_optics_create(const rrtmgp_b200_kdist_file* kd, int n_avail,
+                                  const char* gas_names_avail, int string_len,
+                                  int dtype, rrtmgp_b200_gas_optics** out);
+void rrtmgp_b200_gas_optics_destroy(rrtmgp_b200_gas_optics* go);
+
+/* include/Optical_props.h:191-200 and include/Gas_optics_rrtmgp.h:371-386 getters */
+typedef struct rrtmgp_b200_gas_optics_info
+{
+    int dtype, is_longwave, ngpt, nbnd, nflav, ngas, ntemp, npres, neta, n_minor_lower,
+        n_minor_upper, idx_h2o, gpt_width; /* gpt_width: padded g-points per band on device */
+    double press_ref_min, press_ref_max, temp_ref_min, temp_ref_max, tsi;
+} rrtmgp_b200_gas_optics_info;
+int rrtmgp_b200_gas_optics_get_info(const rrtmgp_b200_gas_optics* go, rrtmgp_b200_gas_optics_info* info);
+/* host copies; band_lims_gpt(2,nbnd) 1-based; band_lims_wvn(2,nbnd); gpoint_bands(ngpt) 1-based;
+ * flavor(2,nflav); gpoint_flavor(2,ngpt); gas_names [ngas][string_len]; solar_source(ngpt) */
+int rrtmgp_b200_gas_optics_get_tables(const rrtmgp_b200_gas_optics* go, int* band_lims_gpt,
+                                      double* band_lims_wvn, int* gpoint_bands, int* flavor,
+                                      int* gpoint_flavor, char* gas_names, int string_len,
+                                      double* solar_source);
+
+/* reduced minor-contributor descriptors of side 0 (lower) / 1 (upper): arrays of n_minor_* ints;
+ * idx_minor / idx_minor_scaling as create_idx_minor[_scaling] (src/Gas_optics_rrtmgp.cpp:164-196),
+ * kminor_start and limits(2,n) as reduce_minor_arrays (:54-162).  Any pointer may be NULL. */
+int rrtmgp_b200_gas_optics_get_minor(const rrtmgp_b200_gas_optics* go, int side, int* idx_minor,
+                                     int* idx_minor_scaling, int* kminor_start, int* limits_gpt,
+                                     int* scales_with_density, int* scale_by_complement);
+
+/* Gas concentrations handed to gas_optics: replaces Gas_concs_gpu (include/Gas_concs.h:73-91).
+ * For gas i of the plan (order of get_tables' gas_names) d_vmr[i] points at a device array that
+ * is a scalar (ncol_i=1,nlay_i=1), a profile (1,nlay) or a field (ncol,nlay).
+ * The three arrays themselves are HOST arrays of length ngas. */
+typedef struct rrtmgp_b200_gas_concs
+{
+    int ngas;
+    const void* const* d_vmr;
+    const int* vmr_ncol;
+    const int* vmr_nlay;
+} rrtmgp_b200_gas_concs;
+
+/* Gas_optics_rrtmgp_gpu::get_col_dry (include/Gas_optics_rrtmgp.h:366, src_cuda/…cu:806-903) */
+int rrtmgp_b200_get_col_dry(int dtype, int ncol, int nlay, const void* d_vmr_h2o /*(ncol,nlay)*/,
+                            const void* d_plev /*(ncol,nlay+1)*/, void* d_col_dry, void* stream);
+
+/* rrtmgp_interpolation + the vmr fill of compute_gas_taus (include/rrtmgp_kernels.h:34-58,
+ * src/Gas_optics_rrtmgp.cpp:1103-1194; CUDA src_kernels_cuda/gas_optics_rrtmgp_kernels.cu:317-395).
+ * Outputs in reference layouts; any output pointer may be NULL.  Index outputs are bit-exact
+ * with the fp64 CPU path for the same input values in both precisions (index math is fp64). */
+int rrtmgp_b200_interpolation(const rrtmgp_b200_gas_optics* go, int ncol, int nlay,
+                              const void* d_play, const void* d_tlay, const void* d_col_dry,
+                              const rrtmgp_b200_gas_concs* concs,
+                              int* d_jtemp, int* d_jpress, signed char* d_tropo, int* d_jeta,
+                              void* d_col_mix, void* d_fminor, void* d_fmajor, void* d_col_gas,
+                              void* stream);
+
+/* Gas_optics_rrtmgp_gpu::gas_optics, longwave (include/Gas_optics_rrtmgp.h:389-398,
+ * src_cuda/Gas_optics_rrtmgp.cu:907-977 -> compute_gas_taus :980 + source :1167).
+ * tau,lay_src (ncol,nlay,ngpt); lev_src (ncol,nlay+1,ngpt); sfc_src,sfc_src_jac (ncol,ngpt). */
+int rrtmgp_b200_gas_optics_lw(const rrtmgp_b200_gas_optics* go, int ncol, int nlay,
+                              const void* d_play, const void* d_plev, const void* d_tlay,
+                              const void* d_tsfc, const void* d_tlev, const void* d_col_dry,
+                              const rrtmgp_b200_gas_concs* concs,
+                              void* d_tau, void* d_lay_src, void* d_lev_src, void* d_sfc_src,
+                              void* d_sfc_src_jac, void* stream);
+
+/* Gas_optics_rrtmgp_gpu::gas_optics, shortwave (include/Gas_optics_rrtmgp.h:401-408):
+ * tau,ssa,g (ncol,nlay,ngpt) incl. Rayleigh + combine (src/Gas_optics_rrtmgp.cpp:365-385);
+ * toa_src (ncol,ngpt) = solar_source (src/Gas_optics_rrtmgp.cpp:895-897). */
+int rrtmgp_b200_gas_optics_sw(const rrtmgp_b200_gas_optics* go, int ncol, int nlay,
+                              const void* d_play, const void* d_plev, const void* d_tlay,
+                              const void* d_col_dry, const rrtmgp_b200_gas_concs* concs,
+                              void* d_tau, void* d_ssa, void* d_g, void* d_toa_src, void* stream);
+
+/* range validation of src/Gas_optics_rrtmgp.cpp:812-827 (the CPU path throws std::range_error;
+ * the reference GPU path skips it).  Synchronises `stream`.  Returns E_RANGE with the reference's
+ * message ("<name> is out of range") when any value is outside [lo, hi]. */
+int rrtmgp_b200_check_range(int dtype, size_t n, const void* d_x, double lo, double hi,
+                            const char* name, void* stream);
+
+/* ---- Cloud_optics_gpu (include/Cloud_optics.h, src_cuda/Cloud_optics.cu:31-329; CPU
+ * src/Cloud_optics.cpp:29-232).  Outputs are by band: (ncol,nlay,nband). */
+int rrtmgp_b200_cloud_optics_create(const rrtmgp_b200_cloud_file* lut, int dtype,
+                                    rrtmgp_b200_cloud_optics** out);
+void rrtmgp_b200_cloud_optics_destroy(rrtmgp_b200_cloud_optics* co);
+int rrtmgp_b200_cloud_optics_nband(const rrtmgp_b200_cloud_optics* co);
+int rrtmgp_b200_cloud_optics_2str(const rrtmgp_b200_cloud_optics* co, int ncol, int nlay,
+                                  const void* d_lwp, const void* d_iwp, const void* d_rel,
+                                  const void* d_dei, void* d_tau, void* d_ssa, void* d_g, void* stream);
+int rrtmgp_b200_cloud_optics_1scl(const rrtmgp_b200_cloud_optics* co, int ncol, int nlay,
+                                  const void* d_lwp, const void* d_iwp, const void* d_rel,
+                                  const void* d_dei, void* d_tau, void* stream);
+
+/* ---- Optical_props: delta_scale / add_to (include/Optical_props.h:165-176,214-293;
+ * kernels rte_delta_scale_2str_k, rte_increment_*, rte_inc_*_bybnd, include/rrtmgp_kernels.h:
+ * 137-205; CUDA src_kernels_cuda/optical_props_kernels.cu:30-161).  In-place on op1. */
+int rrtmgp_b200_delta_scale_2str(int dtype, int ncol, int nlay, int ngpt,
+                                 void* d_tau, void* d_ssa, void* d_g, void* stream);
+int rrtmgp_b200_increment_1scl(int dtype, int ncol, int nlay, int ngpt, void* d_tau1,
+                               const void* d_tau2, void* stream);
+int rrtmgp_b200_increment_2str(int dtype, int ncol, int nlay, int ngpt, void* d_tau1, void* d_ssa1,
+                               void* d_g1, const void* d_tau2, const void* d_ssa2,
+                               const void* d_g2, void* stream);
+/* band_lims_gpt: HOST (2,nbnd) 1-based */
+int rrtmgp_b200_increment_1scl_bybnd(int dtype, int ncol, int nlay, int ngpt, void* d_tau1,
+                                     const void* d_tau2, int nbnd, const int* band_lims_gpt,
+                                     void* stream);
+int rrtmgp_b200_increment_2str_bybnd(int dtype, int ncol, int nlay, int ngpt, void* d_tau1,
+                                     void* d_ssa1, void* d_g1, const void* d_tau2,
+                                     const void* d_ssa2, const void* d_g2, int nbnd,
+                                     const int* band_lims_gpt, void* stream);
+
+/* ---- Rte_lw_gpu::rte_lw / Rte_sw_gpu::rte_sw (include/Rte_lw.h:62-77, include/Rte_sw.h:62-80).
+ * expand_and_transpose (src/Rte_lw.cpp:204-217): (nbnd,ncol) -> (ncol,ngpt). */
+int rrtmgp_b200_expand_and_transpose(int dtype, int ncol, int nbnd, int ngpt,
+                                     const int* band_lims_gpt /*HOST (2,nbnd)*/,
+                                     const void* d_in, void* d_out, void* stream);
+/* rte_lw_solver_noscat (include/rrtmgp_kernels.h:207-232; Fortran mo_rte_solver_kernels.F90:
+ * 248-367; CUDA src_kernels_cuda/rte_solver_kernels_launchers.cu:61-286).  n_gauss_angles 1..4
+ * with the Gauss-Jacobi-5 secants/weights of src/Rte_lw.cpp:139-151 applied internally.
+ * sfc_emis_gpt,sfc_src,inc_flux (ncol,ngpt) [inc_flux may be NULL = 0].
+ * do_broadband=0: flux_up/dn are (ncol,nlay+1,ngpt); =1: (ncol,nlay+1) sums over g-points.
+ * d_sfc_src_jac/d_flux_up_jac may be NULL (no Jacobian). */
+int rrtmgp_b200_lw_solver_noscat(int dtype, int ncol, int nlay, int ngpt, int top_at_1,
+                                 int n_gauss_angles, const void* d_tau, const void* d_lay_src,
+                                 const void* d_lev_src, const void* d_sfc_emis_gpt,
+                                 const void* d_sfc_src, const void* d_inc_flux,
+                                 void* d_flux_up, void* d_flux_dn, int do_broadband,
+                                 const void* d_sfc_src_jac, void* d_flux_up_jac, void* stream);
+/* rte_sw_solver_2stream (include/rrtmgp_kernels.h:234-264; Fortran :503-609,985-1245).
+ * mu0 (ncol); albedos, inc_flux_dir (ncol,ngpt); inc_flux_dif may be NULL. flux_dn includes
+ * the direct beam on return, as in the reference. */
+int rrtmgp_b200_sw_solver_2stream(int dtype, int ncol, int nlay, int ngpt, int top_at_1,
+                                  const void* d_tau, const void* d_ssa, const void* d_g,
+                                  const void* d_mu0, const void* d_sfc_alb_dir_gpt,
+                                  const void* d_sfc_alb_dif_gpt, const void* d_inc_flux_dir,
+                                  const void* d_inc_flux_dif, void* d_flux_up, void* d_flux_dn,
+                                  void* d_flux_dir, int do_broadband, void* stream);
+
+/* ---- Fluxes_broadband_gpu / Fluxes_byband_gpu ::reduce (include/Fluxes.h:127-210; kernels
+ * rte_sum_broadband, rte_net_broadband_precalc, sum_byband, net_byband_precalc,
+ * include/rrtmgp_kernels.h:266-288; CUDA src_kernels_cuda/fluxes_kernels.cu:26-114). */
+int rrtmgp_b200_sum_broadband(int dtype, int ncol, int nlev, int ngpt, const void* d_gpt_flux,
+                              void* d_flux, void* stream);
+int rrtmgp_b200_sum_byband(int dtype, int ncol, int nlev, int ngpt, int nbnd,
+                           const int* band_lims_gpt /*HOST*/, const void* d_gpt_flux,
+                           void* d_bnd_flux, void* stream);
+int rrtmgp_b200_net_flux(int dtype, size_t n, const void* d_dn, const void* d_up, void* d_net,
+                         void* stream);
+/* heating rate (not in the C++ reference; rte-rrtmgp/extensions/mo_heating_rates.F90:44-73) */
+int rrtmgp_b200_heating_rate(int dtype, int ncol, int nlay, const void* d_flux_up,
+                             const void* d_flux_dn, const void* d_plev, void* d_hr, void* stream);
+
+/* ---- Fused column solvers: one call = Radiation_solver_{longwave,shortwave}::solve_gpu for a
+ * set of columns (src_test/Radiation_solver.cu:419-657, 690-950), i.e. gas_optics ->
+ * [cloud_optics -> delta_scale -> add_to] -> rte_lw / rte_sw -> Fluxes::reduce, with the
+ * per-g-point arrays kept on chip.  All inputs as the class API takes them. */
+typedef struct rrtmgp_b200_columns
+{
+    int ncol, nlay;
+    int top_at_1;                  /* -1: derive from play like Radiation_solver.cu:442 (syncs) */
+    const void* d_play;            /* (ncol,nlay)   */
+    const void* d_plev;            /* (ncol,nlay+1) */
+    const void* d_tlay;            /* (ncol,nlay)   */
+    const void* d_tlev;            /* (ncol,nlay+1) longwave only */
+    const void* d_tsfc;            /* (ncol)        longwave only */
+    const void* d_col_dry;         /* (ncol,nlay) or NULL -> get_col_dry from h2o */
+    rrtmgp_b200_gas_concs concs;
+    const void* d_sfc_emis;        /* LW: (nbnd,ncol) */
+    const void* d_sfc_alb_dir;     /* SW: (nbnd,ncol) */
+    const void* d_sfc_alb_dif;     /* SW: (nbnd,ncol) */
+    const void* d_mu0;             /* SW: (ncol) */
+    const void* d_tsi_scaling;     /* SW: (ncol) or NULL (=1) ; Radiation_solver.cu:744-746 */
+    /* clouds (NULL cloud handle = clear sky) */
+    const rrtmgp_b200_cloud_optics* cloud;
+    int delta_cloud;               /* --delta-cloud, default on in the reference (SW only) */
+    const void* d_lwp; const void* d_iwp; const void* d_rel; const void* d_dei; /* (ncol,nlay) */
+    int n_gauss_angles;            /* LW, 1..4 (0 -> 1) */
+} rrtmgp_b200_columns;
+
+typedef struct rrtmgp_b200_fluxes
+{
+    void* d_flux_up;       /* (ncol,nlay+1) */
+    void* d_flux_dn;       /* (ncol,nlay+1) */
+    void* d_flux_net;      /* (ncol,nlay+1) or NULL */
+    void* d_flux_dn_dir;   /* SW (ncol,nlay+1) or NULL */
+    void* d_bnd_flux_up;   /* (ncol,nlay+1,nbnd) or NULL */
+    void* d_bnd_flux_dn;
+    void* d_bnd_flux_net;
+    void* d_bnd_flux_dn_dir;
+    void* d_heating_rate;  /* (ncol,nlay) or NULL */
+} rrtmgp_b200_fluxes;
+
+int rrtmgp_b200_lw_fluxes(rrtmgp_b200_gas_optics* go, const rrtmgp_b200_columns* cols,
+                          const rrtmgp_b200_fluxes* out, void* stream);
+int rrtmgp_b200_sw_fluxes(rrtmgp_b200_gas_optics* go, const rrtmgp_b200_columns* cols,
+                          const rrtmgp_b200_fluxes* out, void* stream);
+/* tuning / introspection of the fused path: columns per tile (0 = default), and the number of
+ * kernels the last fused call launched (for bench.py's gpu_launches). */
+int rrtmgp_b200_set_tile_columns(rrtmgp_b200_gas_optics* go, int ncol_tile);
+long long rrtmgp_b200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

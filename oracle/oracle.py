@@ -329,7 +329,7 @@ class GasOptics(SpectralDisc):
         return st
 
     def get_tsi(self) -> float:                                             # :1347-1356
-        return float(np.sum(self.solar_source))
+        return float(np.cumsum(self.solar_source)[-1])   # sequential igpt = 1..ngpt, like the reference loop
 
 
 # ------------------------------------------------------------------------------------------

@@ -1,0 +1,783 @@
+// cabi.cu — the extern "C" boundary (include/rrtmgp_b200.h): handles, table upload, argument
+// checks, tile loop of the fused path.  No compute happens on the host and there is no CPU
+// fallback: every entry that needs the device fails with RRTMGP_B200_E_CUDA when CUDA is absent.
+#include <atomic>
+#include <cstdio>
+#include <memory>
+#include <string>
+#include <vector>
+#include "../../include/rrtmgp_b200.h"
+#include "plan.hpp"
+#include "launch.hpp"
+#include "stages.hpp"
+
+namespace rb200 {
+
+static thread_local std::string g_err;
+static std::atomic<long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+struct CudaError : std::runtime_error { using std::runtime_error::runtime_error; };
+struct RangeError : std::runtime_error { using std::runtime_error::runtime_error; };
+
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+    throw CudaError(std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+
+template<typename F> static int guarded(F&& f, bool check_cuda = true)
+{
+    try { f(); cudaError_t e = check_cuda ? cudaPeekAtLastError() : cudaSuccess; if (e != cudaSuccess) { cudaGetLastError(); return fail(RRTMGP_B200_E_CUDA, std::string("kernel launch: ") + cudaGetErrorString(e)); } return 0; }
+    catch (const ArgError& e) { return fail(RRTMGP_B200_E_ARG, e.what()); }
+    catch (const MissingError& e) { return fail(RRTMGP_B200_E_MISSING, e.what()); }
+    catch (const RangeError& e) { return fail(RRTMGP_B200_E_RANGE, e.what()); }
+    catch (const CudaError& e) { return fail(RRTMGP_B200_E_CUDA, e.what()); }
+    catch (const std::exception& e) { return fail(RRTMGP_B200_E_ARG, e.what()); }
+}
+
+// device buffer that converts host doubles to Real
+struct DevBuf
+{
+    void* p = nullptr; size_t bytes = 0;
+    ~DevBuf() { if (p) cudaFree(p); }
+    DevBuf() = default; DevBuf(const DevBuf&) = delete; DevBuf& operator=(const DevBuf&) = delete;
+    void alloc(size_t n) { if (p) { cudaFree(p); p = nullptr; } bytes = n; if (n) CK(cudaMalloc(&p, n)); }
+    template<typename T> void upload(const std::vector<T>& v)
+    {
+        alloc(v.size() * sizeof(T));
+        if (!v.empty()) CK(cudaMemcpy(p, v.data(), bytes, cudaMemcpyHostToDevice));
+    }
+    template<typename Real> void upload_as(const std::vector<double>& v)
+    {
+        std::vector<Real> t(v.begin(), v.end());
+        upload(t);
+    }
+};
+
+// grow-only workspace carved into aligned pieces per call
+struct Arena
+{
+    char* base = nullptr; size_t cap = 0, off = 0;
+    ~Arena() { if (base) cudaFree(base); }
+    void reserve(size_t n, cudaStream_t s)
+    {
+        if (n > cap)
+        {
+            if (base) { CK(cudaStreamSynchronize(s)); cudaFree(base); base = nullptr; }
+            CK(cudaMalloc((void**)&base, n)); cap = n;
+        }
+        off = 0;
+    }
+    template<typename T> T* take(size_t count)
+    {
+        off = (off + 255) & ~(size_t)255;
+        T* r = reinterpret_cast<T*>(base + off);
+        off += count * sizeof(T);
+        if (off > cap) throw ArgError("internal: workspace overflow");
+        return r;
+    }
+};
+static size_t pad256(size_t n) { return (n + 255) & ~(size_t)255; }
+
+}  // namespace rb200
+
+using namespace rb200;
+
+struct rrtmgp_b200_gas_optics
+{
+    int dtype = 0, device = 0;
+    bool host_only = false;
+    HostPlan h;
+    DevBuf kmajor, pfrac, krayl, kminor[2], totplnk, solar, temp_ref, vmr_ref, flavor, band_flavor, band_lims;
+    DevPlan<float> pf{};
+    DevPlan<double> pd{};
+    std::vector<BandArgs> bands;
+    BandLims lims{};
+    Arena ws;
+    int tile_cols = 0;
+};
+
+struct rrtmgp_b200_cloud_optics
+{
+    int dtype = 0;
+    DevBuf t[6];
+    CloudDev<float> cf{};
+    CloudDev<double> cd{};
+};
+
+template<typename Real> static const DevPlan<Real>& dplan(const rrtmgp_b200_gas_optics* g);
+template<> const DevPlan<float>& dplan<float>(const rrtmgp_b200_gas_optics* g) { return g->pf; }
+template<> const DevPlan<double>& dplan<double>(const rrtmgp_b200_gas_optics* g) { return g->pd; }
+template<typename Real> static const CloudDev<Real>& dcloud(const rrtmgp_b200_cloud_optics* c);
+template<> const CloudDev<float>& dcloud<float>(const rrtmgp_b200_cloud_optics* c) { return c->cf; }
+template<> const CloudDev<double>& dcloud<double>(const rrtmgp_b200_cloud_optics* c) { return c->cd; }
+
+template<typename Real>
+static void fill_devplan(rrtmgp_b200_gas_optics* g, DevPlan<Real>& P)
+{
+    const HostPlan& h = g->h;
+    g->kmajor.upload_as<Real>(h.kmajor);
+    if (h.is_lw) { g->pfrac.upload_as<Real>(h.pfrac); g->totplnk.upload_as<Real>(h.totplnk); }
+    else { g->solar.upload_as<Real>(h.solar_source); if (!h.krayl.empty()) g->krayl.upload_as<Real>(h.krayl); }
+    for (int s = 0; s < 2; ++s) g->kminor[s].upload_as<Real>(h.minor[s].table);
+    g->temp_ref.upload(h.temp_ref); g->vmr_ref.upload(h.vmr_ref);
+    g->flavor.upload(h.flavor); g->band_flavor.upload(h.band_flavor); g->band_lims.upload(h.band_lims_gpt);
+    P.is_lw = h.is_lw; P.ntemp = h.ntemp; P.npres = h.npres; P.neta = h.neta; P.nbnd = h.nbnd; P.ngpt = h.ngpt;
+    P.nflav = h.nflav; P.ngas = h.ngas; P.gw = h.gw; P.nplanck = h.nplanck; P.idx_h2o = h.idx_h2o;
+    P.kmajor = (const Real*)g->kmajor.p; P.pfrac = (const Real*)g->pfrac.p; P.krayl = (const Real*)g->krayl.p;
+    P.kminor[0] = (const Real*)g->kminor[0].p; P.kminor[1] = (const Real*)g->kminor[1].p;
+    P.totplnk = (const Real*)g->totplnk.p; P.solar_source = (const Real*)g->solar.p;
+    P.temp_ref = (const double*)g->temp_ref.p; P.vmr_ref = (const double*)g->vmr_ref.p;
+    P.flavor = (const int*)g->flavor.p; P.band_flavor = (const int*)g->band_flavor.p; P.band_lims = (const int*)g->band_lims.p;
+    P.press_ref_log0 = h.press_ref_log[0]; P.press_ref_log_delta = h.press_ref_log_delta;
+    P.press_ref_trop_log = h.press_ref_trop_log; P.temp_ref_min = h.temp_ref_min; P.temp_ref_delta = h.temp_ref_delta;
+    P.planck_tmin = (Real)h.temp_ref_min; P.planck_delta = (Real)h.totplnk_delta;
+}
+
+extern "C" {
+
+const char* rrtmgp_b200_last_error(void) { return g_err.c_str(); }
+int rrtmgp_b200_version(void) { return 100; }
+long long rrtmgp_b200_launch_count(void) { return g_launches.load(); }
+
+int rrtmgp_b200_gas_optics_create(const rrtmgp_b200_kdist_file* kd, int n_avail, const char* names,
+                                  int string_len, int dtype, rrtmgp_b200_gas_optics** out)
+{
+    if (!kd || !out || !names || n_avail <= 0) return fail(RRTMGP_B200_E_ARG, "gas_optics_create: null argument");
+    const bool host_only = (dtype & RRTMGP_B200_HOST_ONLY) != 0;
+    dtype &= ~RRTMGP_B200_HOST_ONLY;
+    if (dtype != RRTMGP_B200_F32 && dtype != RRTMGP_B200_F64) return fail(RRTMGP_B200_E_ARG, "gas_optics_create: bad dtype");
+    *out = nullptr;
+    std::unique_ptr<rrtmgp_b200_gas_optics> g(new rrtmgp_b200_gas_optics);
+    const int rc = guarded([&] {
+        g->dtype = dtype;
+        g->h = build_host_plan(*kd, n_avail, names, string_len);
+        if (g->h.ngas > MAX_GAS) throw ArgError("too many gases");
+        if (g->h.nbnd > MAX_BANDS) throw ArgError("too many bands");
+        g->host_only = host_only;
+        if (!host_only)
+        {
+            CK(cudaGetDevice(&g->device));
+            if (dtype == RRTMGP_B200_F32) fill_devplan(g.get(), g->pf); else fill_devplan(g.get(), g->pd);
+        }
+        const HostPlan& h = g->h;
+        g->lims.nbnd = h.nbnd;
+        for (int i = 0; i < 2 * h.nbnd; ++i) g->lims.lims[i] = h.band_lims_gpt[i];
+        g->bands.resize(h.nbnd);
+        for (int b = 0; b < h.nbnd; ++b)
+        {
+            BandArgs& B = g->bands[b];
+            B.band = b; B.gpt0 = h.band_lims_gpt[2 * b] - 1; B.ngb = h.band_lims_gpt[2 * b + 1] - B.gpt0;
+            for (int s = 0; s < 2; ++s)
+            {
+                const auto& lst = h.minor[s].by_band[b];
+                B.nminor[s] = (int)lst.size();
+                for (size_t m = 0; m < lst.size(); ++m)
+                {
+                    const MinorDesc& d = h.minor[s].desc[lst[m]];
+                    if (d.idx_minor < 0) throw ArgError("internal: minor gas index");
+                    B.minor[s][m] = MinorDev{d.idx_minor, d.idx_scaling, (d.scales_with_density ? 1 : 0) | (d.scale_by_complement ? 2 : 0), d.contributor};
+                }
+            }
+        }
+    }, !host_only);
+    if (rc) return rc;
+    *out = g.release();
+    return 0;
+}
+
+void rrtmgp_b200_gas_optics_destroy(rrtmgp_b200_gas_optics* g) { if (g) { if (!g->host_only) cudaDeviceSynchronize(); delete g; } }
+
+int rrtmgp_b200_gas_optics_get_minor(const rrtmgp_b200_gas_optics* g, int side, int* idx_minor, int* idx_scaling,
+                                     int* kstart, int* limits, int* dens, int* comp)
+{
+    if (!g || side < 0 || side > 1) return fail(RRTMGP_B200_E_ARG, "get_minor: bad argument");
+    const MinorSide& m = g->h.minor[side];
+    for (int i = 0; i < m.n; ++i)
+    {
+        if (idx_minor) idx_minor[i] = m.desc[i].idx_minor;
+        if (idx_scaling) idx_scaling[i] = m.desc[i].idx_scaling;
+        if (kstart) kstart[i] = m.kstart[i];
+        if (limits) { limits[2 * i] = m.limits[2 * i]; limits[2 * i + 1] = m.limits[2 * i + 1]; }
+        if (dens) dens[i] = m.desc[i].scales_with_density;
+        if (comp) comp[i] = m.desc[i].scale_by_complement;
+    }
+    return 0;
+}
+
+int rrtmgp_b200_gas_optics_get_info(const rrtmgp_b200_gas_optics* g, rrtmgp_b200_gas_optics_info* i)
+{
+    if (!g || !i) return fail(RRTMGP_B200_E_ARG, "get_info: null argument");
+    const HostPlan& h = g->h;
+    i->dtype = g->dtype; i->is_longwave = h.is_lw; i->ngpt = h.ngpt; i->nbnd = h.nbnd; i->nflav = h.nflav;
+    i->ngas = h.ngas; i->ntemp = h.ntemp; i->npres = h.npres; i->neta = h.neta;
+    i->n_minor_lower = h.minor[0].n; i->n_minor_upper = h.minor[1].n; i->idx_h2o = h.idx_h2o; i->gpt_width = h.gw;
+    i->press_ref_min = h.press_ref_min; i->press_ref_max = h.press_ref_max;
+    i->temp_ref_min = h.temp_ref_min; i->temp_ref_max = h.temp_ref_max; i->tsi = h.tsi;
+    return 0;
+}
+
+int rrtmgp_b200_gas_optics_get_tables(const rrtmgp_b200_gas_optics* g, int* band_lims_gpt, double* band_lims_wvn,
+                                      int* gpoint_bands, int* flavor, int* gpoint_flavor, char* gas_names,
+                                      int string_len, double* solar_source)
+{
+    if (!g) return fail(RRTMGP_B200_E_ARG, "get_tables: null handle");
+    const HostPlan& h = g->h;
+    if (band_lims_gpt) std::copy(h.band_lims_gpt.begin(), h.band_lims_gpt.end(), band_lims_gpt);
+    if (band_lims_wvn) std::copy(h.band_lims_wvn.begin(), h.band_lims_wvn.end(), band_lims_wvn);
+    if (gpoint_bands) std::copy(h.gpoint_bands.begin(), h.gpoint_bands.end(), gpoint_bands);
+    if (flavor) std::copy(h.flavor.begin(), h.flavor.end(), flavor);
+    if (gpoint_flavor) std::copy(h.gpoint_flavor.begin(), h.gpoint_flavor.end(), gpoint_flavor);
+    if (gas_names)
+        for (int i = 0; i < h.ngas; ++i)
+        {
+            std::memset(gas_names + (size_t)i * string_len, ' ', string_len);
+            std::memcpy(gas_names + (size_t)i * string_len, h.gas_names[i].data(), std::min<size_t>(string_len, h.gas_names[i].size()));
+        }
+    if (solar_source && !h.solar_source.empty()) std::copy(h.solar_source.begin(), h.solar_source.end(), solar_source);
+    return 0;
+}
+
+int rrtmgp_b200_set_tile_columns(rrtmgp_b200_gas_optics* g, int n)
+{
+    if (!g || n < 0) return fail(RRTMGP_B200_E_ARG, "set_tile_columns: bad argument");
+    g->tile_cols = n; return 0;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+VmrArgs make_vmr(const rrtmgp_b200_gas_optics* g, const rrtmgp_b200_gas_concs* c, int ncol, int nlay)
+{
+    if (g->host_only) throw CudaError("this handle was created HOST_ONLY: no device tables, and there is no CPU fallback");
+    if (!c || c->ngas != g->h.ngas || !c->d_vmr || !c->vmr_ncol || !c->vmr_nlay)
+        throw ArgError("gas concentrations: need one entry per gas of the k-distribution object");
+    VmrArgs v{};
+    for (int i = 0; i < c->ngas; ++i)
+    {
+        if (!c->d_vmr[i]) throw MissingError("Gas_concs: gas " + g->h.gas_names[i] + " not set");
+        const int nc = c->vmr_ncol[i], nl = c->vmr_nlay[i];
+        if (!((nc == 1 && nl == 1) || (nc == 1 && nl == nlay) || (nc == ncol && nl == nlay)))
+            throw ArgError("Gas_concs: vmr of " + g->h.gas_names[i] + " must be (1,1), (1,nlay) or (ncol,nlay)");
+        v.p[i] = c->d_vmr[i]; v.ncol[i] = (nc == 1 && ncol > 1) ? 1 : nc; v.nlay[i] = nl;
+        if (ncol == 1 && nc == 1 && nl == nlay) { v.ncol[i] = 1; }
+    }
+    return v;
+}
+
+template<typename Real>
+TileState<Real> carve_state(Arena& ws, const HostPlan& h, int nc, int nlay)
+{
+    TileState<Real> st{};
+    const size_t tcl = (size_t)nc * nlay;
+    st.nc = nc; st.nlay = nlay;
+    st.cell = ws.take<V4<Real>>(tcl);
+    st.flvA = ws.take<V4<Real>>(tcl * h.nflav);
+    st.flvB = ws.take<V4<Real>>(tcl * h.nflav);
+    st.col_gas = ws.take<Real>(tcl * (h.ngas + 1));
+    return st;
+}
+template<typename Real> size_t state_bytes(const HostPlan& h, int nc, int nlay)
+{
+    const size_t tcl = (size_t)nc * nlay;
+    return pad256(tcl * sizeof(V4<Real>)) + 2 * pad256(tcl * h.nflav * sizeof(V4<Real>))
+         + pad256(tcl * (h.ngas + 1) * sizeof(Real)) + 1024;
+}
+
+void check_dims(int ncol, int nlay)
+{
+    if (ncol < 1 || nlay < 1) throw ArgError("ncol and nlay must be positive");
+}
+
+template<typename Real>
+void gas_optics_materialised(rrtmgp_b200_gas_optics* g, int ncol, int nlay, const void* play, const void* plev,
+                             const void* tlay, const void* tsfc, const void* tlev, const void* col_dry,
+                             const rrtmgp_b200_gas_concs* concs, GasOut<Real> o, cudaStream_t s)
+{
+    check_dims(ncol, nlay);
+    const HostPlan& h = g->h;
+    if (!play || !tlay || !o.tau) throw ArgError("gas_optics: null array");
+    const VmrArgs vmr = make_vmr(g, concs, ncol, nlay);
+    const size_t tcl = (size_t)ncol * nlay;
+    g->ws.reserve(state_bytes<Real>(h, ncol, nlay) + pad256(tcl * sizeof(Real)) + 2 * sizeof(Real) + 512, s);
+    TileState<Real> st = carve_state<Real>(g->ws, h, ncol, nlay);
+    const void* cd = col_dry;
+    if (!cd)
+    {
+        if (!plev) throw ArgError("gas_optics: plev is needed to compute col_dry");
+        Real* t = g->ws.take<Real>(tcl);
+        const int ih = h.idx_h2o - 1;
+        if (!(concs->vmr_ncol[ih] == ncol && concs->vmr_nlay[ih] == nlay))
+            throw ArgError("gas_optics: computing col_dry needs an (ncol,nlay) h2o field");
+        launch_col_dry<Real>(ncol, nlay, concs->d_vmr[ih], plev, t, s);
+        cd = t;
+    }
+    launch_interp<Real>(dplan<Real>(g), vmr, ncol, 0, ncol, nlay, play, tlay, cd, st,
+                        nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, s);
+    if (h.is_lw)
+    {
+        // sfc_lay from play(1,1) > play(1,nlay) (src/Gas_optics_rrtmgp.cpp:1333); one blocking read
+        Real p2[2];
+        CK(cudaMemcpyAsync(&p2[0], play, sizeof(Real), cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(&p2[1], (const Real*)play + (size_t)ncol * (nlay - 1), sizeof(Real), cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        o.sfc_lay = p2[0] > p2[1] ? 0 : nlay - 1;
+    }
+    o.tlay = (const Real*)tlay; o.tlev = (const Real*)tlev; o.tsfc = (const Real*)tsfc;
+    for (int b = 0; b < h.nbnd; ++b) launch_gas_band<Real>(dplan<Real>(g), g->bands[b], st, ncol, nlay, o, s);
+}
+
+BandLims make_lims(int nbnd, const int* lims, int ngpt)
+{
+    if (nbnd < 1 || nbnd > MAX_BANDS || !lims) throw ArgError("band limits: bad argument");
+    BandLims bl{}; bl.nbnd = nbnd;
+    for (int i = 0; i < 2 * nbnd; ++i) bl.lims[i] = lims[i];
+    for (int b = 0; b < nbnd; ++b)
+        if (lims[2 * b] < 1 || lims[2 * b + 1] > ngpt || lims[2 * b + 1] < lims[2 * b]) throw ArgError("band limits out of range");
+    return bl;
+}
+
+}  // namespace
+
+#define DISPATCH(dtype, CALL_F32, CALL_F64) \
+    if ((dtype) == RRTMGP_B200_F32) { CALL_F32; } else if ((dtype) == RRTMGP_B200_F64) { CALL_F64; } \
+    else throw ArgError("bad dtype")
+
+extern "C" {
+
+int rrtmgp_b200_get_col_dry(int dtype, int ncol, int nlay, const void* vmr_h2o, const void* plev, void* col_dry, void* stream)
+{
+    return guarded([&] {
+        check_dims(ncol, nlay);
+        if (!vmr_h2o || !plev || !col_dry) throw ArgError("get_col_dry: null array");
+        DISPATCH(dtype, launch_col_dry<float>(ncol, nlay, vmr_h2o, plev, col_dry, (cudaStream_t)stream),
+                        launch_col_dry<double>(ncol, nlay, vmr_h2o, plev, col_dry, (cudaStream_t)stream));
+    });
+}
+
+int rrtmgp_b200_interpolation(const rrtmgp_b200_gas_optics* g, int ncol, int nlay, const void* play, const void* tlay,
+                              const void* col_dry, const rrtmgp_b200_gas_concs* concs, int* jtemp, int* jpress,
+                              signed char* tropo, int* jeta, void* col_mix, void* fminor, void* fmajor,
+                              void* col_gas, void* stream)
+{
+    return guarded([&] {
+        if (!g) throw ArgError("interpolation: null handle");
+        check_dims(ncol, nlay);
+        if (!play || !tlay || !col_dry) throw ArgError("interpolation: null array");
+        const VmrArgs vmr = make_vmr(g, concs, ncol, nlay);
+        DISPATCH(g->dtype,
+            launch_interp<float>(g->pf, vmr, ncol, 0, ncol, nlay, play, tlay, col_dry, TileState<float>{}, jtemp, jpress, tropo, jeta, col_mix, fminor, fmajor, col_gas, (cudaStream_t)stream),
+            launch_interp<double>(g->pd, vmr, ncol, 0, ncol, nlay, play, tlay, col_dry, TileState<double>{}, jtemp, jpress, tropo, jeta, col_mix, fminor, fmajor, col_gas, (cudaStream_t)stream));
+    });
+}
+
+int rrtmgp_b200_gas_optics_lw(const rrtmgp_b200_gas_optics* g_, int ncol, int nlay, const void* play, const void* plev,
+                              const void* tlay, const void* tsfc, const void* tlev, const void* col_dry,
+                              const rrtmgp_b200_gas_concs* concs, void* tau, void* lay_src, void* lev_src,
+                              void* sfc_src, void* sfc_src_jac, void* stream)
+{
+    return guarded([&] {
+        auto* g = const_cast<rrtmgp_b200_gas_optics*>(g_);
+        if (!g || !g->h.is_lw) throw ArgError("gas_optics_lw: needs a longwave k-distribution");
+        if (!tsfc || !tlev || !lay_src || !lev_src || !sfc_src || !sfc_src_jac) throw ArgError("gas_optics_lw: null array");
+        if (g->dtype == RRTMGP_B200_F32)
+        {
+            GasOut<float> o{}; o.tau = (float*)tau; o.lay_src = (float*)lay_src; o.lev_src = (float*)lev_src;
+            o.sfc_src = (float*)sfc_src; o.sfc_src_jac = (float*)sfc_src_jac;
+            gas_optics_materialised<float>(g, ncol, nlay, play, plev, tlay, tsfc, tlev, col_dry, concs, o, (cudaStream_t)stream);
+        }
+        else
+        {
+            GasOut<double> o{}; o.tau = (double*)tau; o.lay_src = (double*)lay_src; o.lev_src = (double*)lev_src;
+            o.sfc_src = (double*)sfc_src; o.sfc_src_jac = (double*)sfc_src_jac;
+            gas_optics_materialised<double>(g, ncol, nlay, play, plev, tlay, tsfc, tlev, col_dry, concs, o, (cudaStream_t)stream);
+        }
+    });
+}
+
+int rrtmgp_b200_gas_optics_sw(const rrtmgp_b200_gas_optics* g_, int ncol, int nlay, const void* play, const void* plev,
+                              const void* tlay, const void* col_dry, const rrtmgp_b200_gas_concs* concs,
+                              void* tau, void* ssa, void* gg, void* toa_src, void* stream)
+{
+    return guarded([&] {
+        auto* g = const_cast<rrtmgp_b200_gas_optics*>(g_);
+        if (!g || g->h.is_lw) throw ArgError("gas_optics_sw: needs a shortwave k-distribution");
+        if ((ssa == nullptr) != (gg == nullptr)) throw ArgError("gas_optics_sw: ssa and g go together");
+        if (g->dtype == RRTMGP_B200_F32)
+        {
+            GasOut<float> o{}; o.tau = (float*)tau; o.ssa = (float*)ssa; o.g = (float*)gg; o.toa_src = (float*)toa_src;
+            gas_optics_materialised<float>(g, ncol, nlay, play, plev, tlay, nullptr, nullptr, col_dry, concs, o, (cudaStream_t)stream);
+        }
+        else
+        {
+            GasOut<double> o{}; o.tau = (double*)tau; o.ssa = (double*)ssa; o.g = (double*)gg; o.toa_src = (double*)toa_src;
+            gas_optics_materialised<double>(g, ncol, nlay, play, plev, tlay, nullptr, nullptr, col_dry, concs, o, (cudaStream_t)stream);
+        }
+    });
+}
+
+int rrtmgp_b200_check_range(int dtype, size_t n, const void* x, double lo, double hi, const char* name, void* stream)
+{
+    return guarded([&] {
+        if (!x || !name) throw ArgError("check_range: null argument");
+        cudaStream_t s = (cudaStream_t)stream;
+        int* d_flag = nullptr; int flag = 0;
+        CK(cudaMallocAsync((void**)&d_flag, sizeof(int), s));
+        CK(cudaMemsetAsync(d_flag, 0, sizeof(int), s));
+        DISPATCH(dtype, launch_range_flag<float>(n, x, lo, hi, d_flag, s), launch_range_flag<double>(n, x, lo, hi, d_flag, s));
+        CK(cudaMemcpyAsync(&flag, d_flag, sizeof(int), cudaMemcpyDeviceToHost, s));
+        CK(cudaFreeAsync(d_flag, s));
+        CK(cudaStreamSynchronize(s));
+        if (flag) throw RangeError(std::string(name) + " is out of range");
+    });
+}
+
+// ---- cloud optics
+int rrtmgp_b200_cloud_optics_create(const rrtmgp_b200_cloud_file* lut, int dtype, rrtmgp_b200_cloud_optics** out)
+{
+    if (!lut || !out) return fail(RRTMGP_B200_E_ARG, "cloud_optics_create: null argument");
+    *out = nullptr;
+    std::unique_ptr<rrtmgp_b200_cloud_optics> c(new rrtmgp_b200_cloud_optics);
+    const int rc = guarded([&] {
+        if (dtype != RRTMGP_B200_F32 && dtype != RRTMGP_B200_F64) throw ArgError("bad dtype");
+        if (lut->n_rghice < 2 || lut->n_size_liq < 2 || lut->n_size_ice < 2 || lut->n_band < 1) throw ArgError("cloud LUT: bad dimensions");
+        c->dtype = dtype;
+        const int nb = lut->n_band, nl = lut->n_size_liq, ni = lut->n_size_ice;
+        const int icergh = 2;                                       // src/Cloud_optics.cpp:59
+        const double* src[6] = {lut->lut_extliq, lut->lut_ssaliq, lut->lut_asyliq,
+                                lut->lut_extice + (size_t)(icergh - 1) * nb * ni,
+                                lut->lut_ssaice + (size_t)(icergh - 1) * nb * ni,
+                                lut->lut_asyice + (size_t)(icergh - 1) * nb * ni};
+        for (int k = 0; k < 6; ++k)
+        {
+            std::vector<double> v(src[k], src[k] + (size_t)nb * (k < 3 ? nl : ni));
+            if (dtype == RRTMGP_B200_F32) c->t[k].upload_as<float>(v); else c->t[k].upload_as<double>(v);
+        }
+        const double liq_step = (lut->radliq_upr - lut->radliq_lwr) / (nl - 1.0);
+        const double ice_step = (lut->diamice_upr - lut->diamice_lwr) / (ni - 1.0);
+        c->cf = CloudDev<float>{nb, nl, ni, (float)liq_step, (float)ice_step, (float)lut->radliq_lwr, (float)lut->diamice_lwr,
+                                (const float*)c->t[0].p, (const float*)c->t[1].p, (const float*)c->t[2].p,
+                                (const float*)c->t[3].p, (const float*)c->t[4].p, (const float*)c->t[5].p};
+        c->cd = CloudDev<double>{nb, nl, ni, liq_step, ice_step, lut->radliq_lwr, lut->diamice_lwr,
+                                 (const double*)c->t[0].p, (const double*)c->t[1].p, (const double*)c->t[2].p,
+                                 (const double*)c->t[3].p, (const double*)c->t[4].p, (const double*)c->t[5].p};
+    });
+    if (rc) return rc;
+    *out = c.release();
+    return 0;
+}
+void rrtmgp_b200_cloud_optics_destroy(rrtmgp_b200_cloud_optics* c) { if (c) { cudaDeviceSynchronize(); delete c; } }
+int rrtmgp_b200_cloud_optics_nband(const rrtmgp_b200_cloud_optics* c) { return c ? c->cf.nbnd : -1; }
+
+int rrtmgp_b200_cloud_optics_2str(const rrtmgp_b200_cloud_optics* c, int ncol, int nlay, const void* lwp, const void* iwp,
+                                  const void* rel, const void* dei, void* tau, void* ssa, void* g, void* stream)
+{
+    return guarded([&] {
+        if (!c || !lwp || !iwp || !rel || !dei || !tau || !ssa || !g) throw ArgError("cloud_optics: null argument");
+        check_dims(ncol, nlay);
+        DISPATCH(c->dtype,
+            launch_cloud_optics<float>(c->cf, true, ncol, 0, ncol, nlay, lwp, iwp, rel, dei, ncol, 0, 0, tau, ssa, g, (cudaStream_t)stream),
+            launch_cloud_optics<double>(c->cd, true, ncol, 0, ncol, nlay, lwp, iwp, rel, dei, ncol, 0, 0, tau, ssa, g, (cudaStream_t)stream));
+    });
+}
+int rrtmgp_b200_cloud_optics_1scl(const rrtmgp_b200_cloud_optics* c, int ncol, int nlay, const void* lwp, const void* iwp,
+                                  const void* rel, const void* dei, void* tau, void* stream)
+{
+    return guarded([&] {
+        if (!c || !lwp || !iwp || !rel || !dei || !tau) throw ArgError("cloud_optics: null argument");
+        check_dims(ncol, nlay);
+        DISPATCH(c->dtype,
+            launch_cloud_optics<float>(c->cf, false, ncol, 0, ncol, nlay, lwp, iwp, rel, dei, ncol, 0, 0, tau, nullptr, nullptr, (cudaStream_t)stream),
+            launch_cloud_optics<double>(c->cd, false, ncol, 0, ncol, nlay, lwp, iwp, rel, dei, ncol, 0, 0, tau, nullptr, nullptr, (cudaStream_t)stream));
+    });
+}
+
+}  // extern "C"
+
+extern "C" {
+
+int rrtmgp_b200_delta_scale_2str(int dtype, int ncol, int nlay, int ngpt, void* tau, void* ssa, void* g, void* stream)
+{
+    return guarded([&] {
+        check_dims(ncol, nlay);
+        if (ngpt < 1 || !tau || !ssa || !g) throw ArgError("delta_scale: bad argument");
+        const size_t n = (size_t)ncol * nlay * ngpt;
+        DISPATCH(dtype, launch_delta_scale<float>(n, tau, ssa, g, (cudaStream_t)stream),
+                        launch_delta_scale<double>(n, tau, ssa, g, (cudaStream_t)stream));
+    });
+}
+
+static int increment_impl(int dtype, bool twostr, int ncol, int nlay, int ngpt, void* tau1, void* ssa1, void* g1,
+                          const void* tau2, const void* ssa2, const void* g2, int nbnd, const int* lims, void* stream)
+{
+    return guarded([&] {
+        check_dims(ncol, nlay);
+        if (ngpt < 1 || !tau1 || !tau2 || (twostr && (!ssa1 || !g1 || !ssa2 || !g2))) throw ArgError("increment: bad argument");
+        BandLims bl{};
+        if (nbnd > 0) bl = make_lims(nbnd, lims, ngpt);
+        const size_t ncl = (size_t)ncol * nlay;
+        DISPATCH(dtype, launch_increment<float>(twostr, ncl, ngpt, bl, tau1, ssa1, g1, tau2, ssa2, g2, (cudaStream_t)stream),
+                        launch_increment<double>(twostr, ncl, ngpt, bl, tau1, ssa1, g1, tau2, ssa2, g2, (cudaStream_t)stream));
+    });
+}
+int rrtmgp_b200_increment_1scl(int dtype, int ncol, int nlay, int ngpt, void* tau1, const void* tau2, void* stream)
+{ return increment_impl(dtype, false, ncol, nlay, ngpt, tau1, nullptr, nullptr, tau2, nullptr, nullptr, 0, nullptr, stream); }
+int rrtmgp_b200_increment_2str(int dtype, int ncol, int nlay, int ngpt, void* tau1, void* ssa1, void* g1,
+                               const void* tau2, const void* ssa2, const void* g2, void* stream)
+{ return increment_impl(dtype, true, ncol, nlay, ngpt, tau1, ssa1, g1, tau2, ssa2, g2, 0, nullptr, stream); }
+int rrtmgp_b200_increment_1scl_bybnd(int dtype, int ncol, int nlay, int ngpt, void* tau1, const void* tau2,
+                                     int nbnd, const int* lims, void* stream)
+{
+    if (nbnd < 1) return fail(RRTMGP_B200_E_ARG, "increment_bybnd: nbnd must be positive");
+    return increment_impl(dtype, false, ncol, nlay, ngpt, tau1, nullptr, nullptr, tau2, nullptr, nullptr, nbnd, lims, stream);
+}
+int rrtmgp_b200_increment_2str_bybnd(int dtype, int ncol, int nlay, int ngpt, void* tau1, void* ssa1, void* g1,
+                                     const void* tau2, const void* ssa2, const void* g2, int nbnd, const int* lims, void* stream)
+{
+    if (nbnd < 1) return fail(RRTMGP_B200_E_ARG, "increment_bybnd: nbnd must be positive");
+    return increment_impl(dtype, true, ncol, nlay, ngpt, tau1, ssa1, g1, tau2, ssa2, g2, nbnd, lims, stream);
+}
+
+int rrtmgp_b200_expand_and_transpose(int dtype, int ncol, int nbnd, int ngpt, const int* lims, const void* in, void* out, void* stream)
+{
+    return guarded([&] {
+        if (ncol < 1 || !in || !out) throw ArgError("expand_and_transpose: bad argument");
+        const BandLims bl = make_lims(nbnd, lims, ngpt);
+        DISPATCH(dtype, launch_expand<float>(ncol, bl, in, out, (cudaStream_t)stream),
+                        launch_expand<double>(ncol, bl, in, out, (cudaStream_t)stream));
+    });
+}
+
+int rrtmgp_b200_lw_solver_noscat(int dtype, int ncol, int nlay, int ngpt, int top_at_1, int nmus, const void* tau,
+                                 const void* lay_src, const void* lev_src, const void* sfc_emis, const void* sfc_src,
+                                 const void* inc_flux, void* flux_up, void* flux_dn, int do_broadband,
+                                 const void* sfc_src_jac, void* flux_up_jac, void* stream)
+{
+    return guarded([&] {
+        check_dims(ncol, nlay);
+        if (ngpt < 1 || !tau || !lay_src || !lev_src || !sfc_emis || !sfc_src || !flux_up || !flux_dn) throw ArgError("lw_solver: null array");
+        if (nmus < 1 || nmus > 4) throw ArgError("lw_solver: n_gauss_angles must be 1..4");   // src/Rte_lw.cpp:139-151
+        if ((sfc_src_jac == nullptr) != (flux_up_jac == nullptr)) throw ArgError("lw_solver: Jacobian input and output go together");
+        cudaStream_t s = (cudaStream_t)stream;
+        const size_t esz = dtype == RRTMGP_B200_F32 ? 4 : 8;
+        const size_t ncv = (size_t)ncol * (nlay + 1);
+        void *up = flux_up, *dn = flux_dn;
+        char* tmp = nullptr;
+        if (do_broadband)
+        {
+            CK(cudaMallocAsync((void**)&tmp, 2 * ncv * ngpt * esz, s));
+            up = tmp; dn = tmp + ncv * ngpt * esz;
+        }
+        if (flux_up_jac) CK(cudaMemsetAsync(flux_up_jac, 0, ncv * esz, s));
+        DISPATCH(dtype,
+            launch_lw_solver<float>(ncol, nlay, ngpt, top_at_1, nmus, tau, lay_src, lev_src, sfc_emis, sfc_src, inc_flux, up, dn, sfc_src_jac, flux_up_jac, s),
+            launch_lw_solver<double>(ncol, nlay, ngpt, top_at_1, nmus, tau, lay_src, lev_src, sfc_emis, sfc_src, inc_flux, up, dn, sfc_src_jac, flux_up_jac, s));
+        if (do_broadband)
+        {
+            DISPATCH(dtype, (launch_sum_broadband<float>(ncol, nlay + 1, ngpt, up, flux_up, s), launch_sum_broadband<float>(ncol, nlay + 1, ngpt, dn, flux_dn, s)),
+                            (launch_sum_broadband<double>(ncol, nlay + 1, ngpt, up, flux_up, s), launch_sum_broadband<double>(ncol, nlay + 1, ngpt, dn, flux_dn, s)));
+            CK(cudaFreeAsync(tmp, s));
+        }
+    });
+}
+
+int rrtmgp_b200_sw_solver_2stream(int dtype, int ncol, int nlay, int ngpt, int top_at_1, const void* tau, const void* ssa,
+                                  const void* g, const void* mu0, const void* alb_dir, const void* alb_dif,
+                                  const void* inc_dir, const void* inc_dif, void* flux_up, void* flux_dn, void* flux_dir,
+                                  int do_broadband, void* stream)
+{
+    return guarded([&] {
+        check_dims(ncol, nlay);
+        if (ngpt < 1 || !tau || !ssa || !g || !mu0 || !alb_dir || !alb_dif || !inc_dir || !flux_up || !flux_dn || !flux_dir)
+            throw ArgError("sw_solver: null array");
+        cudaStream_t s = (cudaStream_t)stream;
+        const size_t esz = dtype == RRTMGP_B200_F32 ? 4 : 8;
+        const size_t ncv = (size_t)ncol * (nlay + 1), ncl = (size_t)ncol * nlay;
+        char* tmp = nullptr;
+        const size_t wbytes = 4 * ncl * ngpt * esz, fbytes = ncv * ngpt * esz;
+        CK(cudaMallocAsync((void**)&tmp, wbytes + (do_broadband ? 3 * fbytes : 0), s));
+        void *up = flux_up, *dn = flux_dn, *dr = flux_dir;
+        if (do_broadband) { up = tmp + wbytes; dn = tmp + wbytes + fbytes; dr = tmp + wbytes + 2 * fbytes; }
+        DISPATCH(dtype,
+            launch_sw_solver<float>(ncol, nlay, ngpt, top_at_1, tau, ssa, g, mu0, alb_dir, alb_dif, inc_dir, inc_dif, up, dn, dr, tmp, s),
+            launch_sw_solver<double>(ncol, nlay, ngpt, top_at_1, tau, ssa, g, mu0, alb_dir, alb_dif, inc_dir, inc_dif, up, dn, dr, tmp, s));
+        if (do_broadband)
+        {
+            void* src[3] = {up, dn, dr}; void* dst[3] = {flux_up, flux_dn, flux_dir};
+            for (int k = 0; k < 3; ++k)
+            { DISPATCH(dtype, launch_sum_broadband<float>(ncol, nlay + 1, ngpt, src[k], dst[k], s), launch_sum_broadband<double>(ncol, nlay + 1, ngpt, src[k], dst[k], s)); }
+        }
+        CK(cudaFreeAsync(tmp, s));
+    });
+}
+
+int rrtmgp_b200_sum_broadband(int dtype, int ncol, int nlev, int ngpt, const void* gpt_flux, void* flux, void* stream)
+{
+    return guarded([&] {
+        if (ncol < 1 || nlev < 1 || ngpt < 1 || !gpt_flux || !flux) throw ArgError("sum_broadband: bad argument");
+        DISPATCH(dtype, launch_sum_broadband<float>(ncol, nlev, ngpt, gpt_flux, flux, (cudaStream_t)stream),
+                        launch_sum_broadband<double>(ncol, nlev, ngpt, gpt_flux, flux, (cudaStream_t)stream));
+    });
+}
+int rrtmgp_b200_sum_byband(int dtype, int ncol, int nlev, int ngpt, int nbnd, const int* lims, const void* gpt_flux,
+                           void* bnd_flux, void* stream)
+{
+    return guarded([&] {
+        if (ncol < 1 || nlev < 1 || !gpt_flux || !bnd_flux) throw ArgError("sum_byband: bad argument");
+        const BandLims bl = make_lims(nbnd, lims, ngpt);
+        DISPATCH(dtype, launch_sum_byband<float>(ncol, nlev, bl, gpt_flux, bnd_flux, (cudaStream_t)stream),
+                        launch_sum_byband<double>(ncol, nlev, bl, gpt_flux, bnd_flux, (cudaStream_t)stream));
+    });
+}
+int rrtmgp_b200_net_flux(int dtype, size_t n, const void* dn, const void* up, void* net, void* stream)
+{
+    return guarded([&] {
+        if (!dn || !up || !net) throw ArgError("net_flux: null array");
+        DISPATCH(dtype, launch_net<float>(n, dn, up, net, (cudaStream_t)stream), launch_net<double>(n, dn, up, net, (cudaStream_t)stream));
+    });
+}
+int rrtmgp_b200_heating_rate(int dtype, int ncol, int nlay, const void* up, const void* dn, const void* plev, void* hr, void* stream)
+{
+    return guarded([&] {
+        check_dims(ncol, nlay);
+        if (!up || !dn || !plev || !hr) throw ArgError("heating_rate: null array");
+        DISPATCH(dtype, launch_heating_rate<float>(ncol, nlay, up, dn, plev, hr, (cudaStream_t)stream),
+                        launch_heating_rate<double>(ncol, nlay, up, dn, plev, hr, (cudaStream_t)stream));
+    });
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// Fused column solvers
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+template<typename Real>
+void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, const rrtmgp_b200_fluxes* out,
+                  cudaStream_t s, bool sw)
+{
+    if (!g || !cols || !out) throw ArgError("fused fluxes: null argument");
+    const HostPlan& h = g->h;
+    if (h.is_lw == sw) throw ArgError(sw ? "sw_fluxes needs a shortwave k-distribution" : "lw_fluxes needs a longwave k-distribution");
+    const int ncol = cols->ncol, nlay = cols->nlay, nlev = nlay + 1;
+    check_dims(ncol, nlay);
+    if (!cols->d_play || !cols->d_plev || !cols->d_tlay || !out->d_flux_up || !out->d_flux_dn) throw ArgError("fused fluxes: null array");
+    if (!sw && (!cols->d_tlev || !cols->d_tsfc || !cols->d_sfc_emis)) throw ArgError("lw_fluxes: tlev, tsfc and sfc_emis are required");
+    if (sw && (!cols->d_mu0 || !cols->d_sfc_alb_dir || !cols->d_sfc_alb_dif)) throw ArgError("sw_fluxes: mu0 and surface albedos are required");
+    if (!sw && cols->n_gauss_angles > 1) throw ArgError("lw_fluxes: the fused path supports one Gauss angle; use lw_solver_noscat for 2..4");
+    const bool cloud = cols->cloud != nullptr;
+    if (cloud)
+    {
+        if (cols->cloud->dtype != g->dtype) throw ArgError("cloud optics object has a different precision");
+        if (cols->cloud->cf.nbnd != h.nbnd) throw ArgError("Cannot add optical properties with incompatible band - gpoint combination");
+        if (!cols->d_lwp || !cols->d_iwp || !cols->d_rel || !cols->d_dei) throw ArgError("cloud inputs missing");
+    }
+    const bool bnd = out->d_bnd_flux_up != nullptr;
+    if (bnd && !out->d_bnd_flux_dn) throw ArgError("by-band output needs both bnd_flux_up and bnd_flux_dn");
+    const VmrArgs vmr = make_vmr(g, &cols->concs, ncol, nlay);
+
+    int top_at_1 = cols->top_at_1;
+    if (top_at_1 < 0)
+    {
+        Real p2[2];
+        CK(cudaMemcpyAsync(&p2[0], cols->d_play, sizeof(Real), cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(&p2[1], (const Real*)cols->d_play + (size_t)ncol * (nlay - 1), sizeof(Real), cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        top_at_1 = p2[0] < p2[1];
+    }
+
+    const int cpb = FUSED_THREADS / (h.gw / 4);
+    int tile = g->tile_cols;
+    if (tile <= 0)
+    {
+        const int blocks = sw ? sw_blocks_per_wave<Real>(h.gw) : lw_blocks_per_wave<Real>(h.gw);
+        tile = std::max(blocks, 1) * cpb;
+    }
+    tile = std::min(tile, ncol);
+    const size_t tcl = (size_t)tile * nlay, ncl = (size_t)ncol * nlay, ncv = (size_t)ncol * nlev;
+    size_t need = state_bytes<Real>(h, tile, nlay) + pad256(fused_scratch_bytes<Real>(tile, nlay, h.gw, sw)) + 4096;
+    if (!cols->d_col_dry) need += pad256(ncl * sizeof(Real));
+    if (cloud) need += 3 * pad256(tcl * h.nbnd * sizeof(Real));
+    if (sw && !out->d_flux_dn_dir) need += pad256(ncv * sizeof(Real));
+    if (sw && bnd && !out->d_bnd_flux_dn_dir) need += pad256(ncv * h.nbnd * sizeof(Real));
+    g->ws.reserve(need, s);
+    TileState<Real> st = carve_state<Real>(g->ws, h, tile, nlay);
+
+    FusedArgs<Real> a{};
+    a.ncol = ncol; a.nlay = nlay; a.top_at_1 = top_at_1;
+    a.tlay = (const Real*)cols->d_tlay; a.tlev = (const Real*)cols->d_tlev; a.tsfc = (const Real*)cols->d_tsfc;
+    a.sfc_emis = (const Real*)cols->d_sfc_emis; a.mu0 = (const Real*)cols->d_mu0;
+    a.alb_dir = (const Real*)cols->d_sfc_alb_dir; a.alb_dif = (const Real*)cols->d_sfc_alb_dif;
+    a.tsi_scaling = (const Real*)cols->d_tsi_scaling;
+    a.scratch = (V4<Real>*)g->ws.take<char>(fused_scratch_bytes<Real>(tile, nlay, h.gw, sw));
+    a.flux_up = (Real*)out->d_flux_up; a.flux_dn = (Real*)out->d_flux_dn;
+    a.flux_dir = (Real*)out->d_flux_dn_dir;
+    a.bnd_up = (Real*)out->d_bnd_flux_up; a.bnd_dn = (Real*)out->d_bnd_flux_dn; a.bnd_dir = (Real*)out->d_bnd_flux_dn_dir;
+    a.secant = (Real)(1. / 0.6096748751); a.weight = (Real)1;      // src/Rte_lw.cpp:139-151, n = 1
+    const Real* col_dry = (const Real*)cols->d_col_dry;
+    if (!col_dry)
+    {
+        const int ih = h.idx_h2o - 1;
+        if (!(cols->concs.vmr_ncol[ih] == ncol && cols->concs.vmr_nlay[ih] == nlay))
+            throw ArgError("fused fluxes: computing col_dry needs an (ncol,nlay) h2o field");
+        Real* t = g->ws.take<Real>(ncl);
+        launch_col_dry<Real>(ncol, nlay, cols->concs.d_vmr[ih], cols->d_plev, t, s);
+        col_dry = t;
+    }
+    Real *ctau = nullptr, *cssa = nullptr, *cg = nullptr;
+    if (cloud) { ctau = g->ws.take<Real>(tcl * h.nbnd); cssa = g->ws.take<Real>(tcl * h.nbnd); cg = g->ws.take<Real>(tcl * h.nbnd); }
+    if (sw && !a.flux_dir) a.flux_dir = g->ws.take<Real>(ncv);
+    if (sw && bnd && !a.bnd_dir) a.bnd_dir = g->ws.take<Real>(ncv * h.nbnd);
+
+    CK(cudaMemsetAsync(a.flux_up, 0, ncv * sizeof(Real), s));
+    CK(cudaMemsetAsync(a.flux_dn, 0, ncv * sizeof(Real), s));
+    if (sw) CK(cudaMemsetAsync(a.flux_dir, 0, ncv * sizeof(Real), s));
+
+    for (int c0 = 0; c0 < ncol; c0 += tile)
+    {
+        const int nc = std::min(tile, ncol - c0);
+        st.nc = nc; a.c0 = c0; a.nc = nc;
+        launch_interp<Real>(dplan<Real>(g), vmr, ncol, c0, nc, nlay, cols->d_play, cols->d_tlay, col_dry, st,
+                            nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, s);
+        if (cloud)
+        {
+            launch_cloud_optics<Real>(dcloud<Real>(cols->cloud), sw, ncol, c0, nc, nlay, cols->d_lwp, cols->d_iwp,
+                                      cols->d_rel, cols->d_dei, nc, 0, sw && cols->delta_cloud, ctau, cssa, cg, s);
+            a.cld_tau = ctau; a.cld_ssa = cssa; a.cld_g = cg;
+        }
+        for (int b = 0; b < h.nbnd; ++b)
+        {
+            if (sw) launch_sw_band<Real>(dplan<Real>(g), g->bands[b], st, a, s);
+            else launch_lw_band<Real>(dplan<Real>(g), g->bands[b], st, a, s);
+        }
+    }
+    if (out->d_flux_net) launch_net<Real>(ncv, a.flux_dn, a.flux_up, out->d_flux_net, s);
+    if (bnd && out->d_bnd_flux_net) launch_net<Real>(ncv * h.nbnd, a.bnd_dn, a.bnd_up, out->d_bnd_flux_net, s);
+    if (out->d_heating_rate) launch_heating_rate<Real>(ncol, nlay, a.flux_up, a.flux_dn, cols->d_plev, out->d_heating_rate, s);
+}
+
+}  // namespace
+
+extern "C" {
+
+int rrtmgp_b200_lw_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, const rrtmgp_b200_fluxes* out, void* stream)
+{
+    return guarded([&] {
+        if (!g) throw ArgError("lw_fluxes: null handle");
+        if (g->dtype == RRTMGP_B200_F32) fused_fluxes<float>(g, cols, out, (cudaStream_t)stream, false);
+        else fused_fluxes<double>(g, cols, out, (cudaStream_t)stream, false);
+    });
+}
+int rrtmgp_b200_sw_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, const rrtmgp_b200_fluxes* out, void* stream)
+{
+    return guarded([&] {
+        if (!g) throw ArgError("sw_fluxes: null handle");
+        if (g->dtype == RRTMGP_B200_F32) fused_fluxes<float>(g, cols, out, (cudaStream_t)stream, true);
+        else fused_fluxes<double>(g, cols, out, (cudaStream_t)stream, true);
+    });
+}
+
+}  // extern "C"

@@ -1,0 +1,113 @@
+// common.cuh — shared device-side types of the B200 column radiation kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <cfloat>
+#include <cstdint>
+
+namespace rb200 {
+
+constexpr int MAX_GAS = 32;
+constexpr int MAX_MINOR_DEV = 16;
+
+// ---- 4-wide vectors: one 16-byte (fp32) or 32-byte (fp64) aligned access -------------------
+template<typename Real> struct V4;
+template<> struct alignas(16) V4<float>  { float x, y, z, w; };
+template<> struct alignas(32) V4<double> { double x, y, z, w; };
+
+template<typename Real> __device__ __forceinline__ V4<Real> ldg4(const Real* p)
+{
+    return *reinterpret_cast<const V4<Real>*>(p);
+}
+template<> __device__ __forceinline__ V4<float> ldg4<float>(const float* p)
+{
+    const float4 v = __ldg(reinterpret_cast<const float4*>(p));
+    return V4<float>{v.x, v.y, v.z, v.w};
+}
+template<> __device__ __forceinline__ V4<double> ldg4<double>(const double* p)
+{
+    const double2 a = __ldg(reinterpret_cast<const double2*>(p));
+    const double2 b = __ldg(reinterpret_cast<const double2*>(p) + 1);
+    return V4<double>{a.x, a.y, b.x, b.y};
+}
+
+// ---- per-precision math: fp32 uses the fast SFU paths, fp64 the accurate library ------------
+template<typename Real> struct M;
+template<> struct M<float>
+{
+    static constexpr float eps = FLT_EPSILON;
+    static constexpr float tiny = FLT_MIN;
+    static __device__ __forceinline__ float exp(float x) { return __expf(x); }
+    static __device__ __forceinline__ float sqrt(float x) { return sqrtf(x); }
+    static __device__ __forceinline__ float div(float a, float b) { return __fdividef(a, b); }
+    static __device__ __forceinline__ float rcp(float a) { return __frcp_rn(a); }
+    static __device__ __forceinline__ float fabs(float a) { return fabsf(a); }
+    static __device__ __forceinline__ float max(float a, float b) { return fmaxf(a, b); }
+    static __device__ __forceinline__ float min(float a, float b) { return fminf(a, b); }
+    static __device__ __forceinline__ int as_int(float a) { return __float_as_int(a); }
+    static __device__ __forceinline__ float from_int(int a) { return __int_as_float(a); }
+};
+template<> struct M<double>
+{
+    static constexpr double eps = DBL_EPSILON;
+    static constexpr double tiny = DBL_MIN;
+    static __device__ __forceinline__ double exp(double x) { return ::exp(x); }
+    static __device__ __forceinline__ double sqrt(double x) { return ::sqrt(x); }
+    static __device__ __forceinline__ double div(double a, double b) { return a / b; }
+    static __device__ __forceinline__ double rcp(double a) { return 1.0 / a; }
+    static __device__ __forceinline__ double fabs(double a) { return ::fabs(a); }
+    static __device__ __forceinline__ double max(double a, double b) { return ::fmax(a, b); }
+    static __device__ __forceinline__ double min(double a, double b) { return ::fmin(a, b); }
+    static __device__ __forceinline__ int as_int(double a) { return (int)__double_as_longlong(a); }
+    static __device__ __forceinline__ double from_int(int a) { return __longlong_as_double((long long)a); }
+};
+
+// ---- device view of the k-distribution (tables in Real, index grids in double) -------------
+template<typename Real> struct DevPlan
+{
+    int is_lw, ntemp, npres, neta, nbnd, ngpt, nflav, ngas, gw, nplanck, idx_h2o;
+    const Real* kmajor;        // [b][it][ip][ie][gw]
+    const Real* pfrac;         // idem (LW)
+    const Real* krayl;         // [side][b][it][ie][gw] (SW) or null
+    const Real* kminor[2];     // [m][it][ie][gw]
+    const Real* totplnk;       // [b][nplanck] (LW)
+    const Real* solar_source;  // [ngpt] (SW)
+    const double* temp_ref;    // [ntemp]
+    const double* vmr_ref;     // (2, ngas+1, ntemp)
+    const int* flavor;         // (2, nflav) 1-based gas index, 0 = dry air
+    const int* band_flavor;    // (2, nbnd) 0-based flavor
+    const int* band_lims;      // (2, nbnd) 1-based
+    double press_ref_log0, press_ref_log_delta, press_ref_trop_log;
+    double temp_ref_min, temp_ref_delta;
+    Real planck_tmin, planck_delta;
+};
+
+// vmr inputs of one call: scalar / profile / field per gas (Gas_concs semantics)
+struct VmrArgs
+{
+    const void* p[MAX_GAS];
+    int ncol[MAX_GAS];
+    int nlay[MAX_GAS];
+};
+
+// ---- per-tile interpolation state produced by the prologue kernel, g-point independent ------
+// All arrays are column-fastest over the tile: index (c + nc*l) [+ nc*nlay*f].
+template<typename Real> struct TileState
+{
+    int nc, nlay;            // columns in this tile, layers
+    V4<Real>* cell;          // {fpress, dens = 0.01 p/T, vd = vmr_fact*dry_fact, bits}
+                             //   bits = jtemp | jpress<<8 | tropo<<16
+    V4<Real>* flvA;          // [f]: {col_mix0, col_mix1, fminor(1,1), fminor(2,1)}
+    V4<Real>* flvB;          // [f]: {fminor(1,2), fminor(2,2), bits(jeta0 | jeta1<<8), 0}
+    Real* col_gas;           // [g = 0..ngas]
+};
+
+struct MinorDev { int idx_minor, idx_scaling, flags, contributor; };   // flags: 1 density, 2 complement
+
+struct BandArgs
+{
+    int band, gpt0, ngb;     // 0-based band, first g-point (0-based), g-points in band
+    int nminor[2];
+    MinorDev minor[2][MAX_MINOR_DEV];
+};
+
+}  // namespace rb200

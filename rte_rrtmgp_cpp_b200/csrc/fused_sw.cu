@@ -1,0 +1,215 @@
+// fused_sw.cu — shortwave: gas optics (+Rayleigh, +cloud increment) + two-stream coefficients +
+// direct beam + adding + g-point reduction in one kernel per (column tile, band).
+//
+// Restates (fp order aside) the chain the oracle pins:
+//   compute_tau_absorption / compute_tau_rayleigh  mo_gas_optics_rrtmgp_kernels.F90:178-564
+//   combine_abs_and_rayleigh                       src/Gas_optics_rrtmgp.cpp:365-385
+//   inc_2stream_by_2stream_bybnd (clouds)          mo_optical_props_kernels.F90:451-482
+//   sw_solver_2stream = sw_dif_and_source + adding mo_rte_solver_kernels.F90:503-609,985-1245
+//   sum_broadband / sum_byband
+// Same thread mapping as fused_lw.cu.  Three vertical passes per (column, g-point):
+//   1 top->bottom : optics, two-stream, direct beam; parks {Rdif,Tdif,src_up,src_dn}
+//   2 bottom->top : adding recurrences for albedo/src; re-parks {a,b,albedo,src} with
+//                   flux_dn(l+1) = a*flux_dn(l) + b,  flux_up(l+1) = flux_dn(l+1)*albedo + src
+//   3 top->bottom : two FMAs per level + reduction
+#include "physics.cuh"
+#include "launch.hpp"
+
+namespace rb200 {
+
+template<typename Real, int LPC, bool CLOUD>
+__global__ void __launch_bounds__(FUSED_THREADS)
+sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const TileState<Real> st,
+               const FusedArgs<Real> a)
+{
+    constexpr int CPB = FUSED_THREADS / LPC;
+    const int tid = threadIdx.x;
+    const int q = tid % LPC, cl = tid / LPC;
+    const int craw = blockIdx.x * CPB + cl;
+    const bool active = craw < a.nc;
+    const int c = active ? craw : a.nc - 1;
+    const int nlay = a.nlay, nc = a.nc;
+    const size_t tcl = (size_t)nc * nlay;
+    const size_t cg = (size_t)a.c0 + c;
+    const int q4 = q * 4;
+    const int band = B.band;
+    const size_t band_elems = (size_t)P.ntemp * (P.npres + 1) * P.neta * P.gw;
+    const size_t ray_elems = (size_t)P.ntemp * P.neta * P.gw;
+    const Real* kmaj = P.kmajor + band_elems * band;
+    const int flav[2] = {P.band_flavor[2 * band], P.band_flavor[2 * band + 1]};
+    V4<Real>* scr = a.scratch + (size_t)blockIdx.x * nlay * 4 * FUSED_THREADS + tid;
+    const bool lead = active && q == 0;
+    const size_t nlev_stride = (size_t)a.ncol * (nlay + 1);
+    auto level = [&](int j) { return a.top_at_1 ? j : nlay - j; };
+
+    const Real mu0 = a.mu0[cg];
+    const Real mu0s = M<Real>::max(M<Real>::sqrt(M<Real>::eps), mu0);
+    const bool sun = mu0 > (Real)0;
+    const Real tsi = a.tsi_scaling ? a.tsi_scaling[cg] : (Real)1;
+
+    // top-of-domain boundary condition (F90:575-583): direct = toa_src * mu0, diffuse = 0
+    Real dir[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+    {
+        const int gl = q4 + j;
+        dir[j] = gl < B.ngb ? P.solar_source[B.gpt0 + gl] * tsi * mu0 : (Real)0;
+    }
+    {
+        const Real s = quad_sum<Real, LPC>(dir);
+        if (lead)
+        {
+            const size_t o = cg + (size_t)a.ncol * level(0);
+            a.flux_dir[o] += s; a.flux_dn[o] += s;
+            if (a.bnd_dir) a.bnd_dir[o + nlev_stride * band] = s;
+        }
+    }
+
+    // ---- pass 1
+    for (int k = 0; k < nlay; ++k)
+    {
+        const int l = a.top_at_1 ? k : nlay - 1 - k;
+        const size_t icl = (size_t)c + (size_t)nc * l;
+        const V4<Real> cell = st.cell[icl];
+        const int f = flav[cell_side(cell)];
+        Cell<Real> ce;
+        decode_cell(P, cell, st.flvA[icl + tcl * f], st.flvB[icl + tcl * f], ce);
+        Real tau[4], s0[4], s1[4];
+        gas_tau(P, B, ce, kmaj, q4, st.col_gas, icl, tcl, tau, s0, s1);
+        Real ray[4] = {0, 0, 0, 0};
+        if (P.krayl)
+        {
+            interp_minor(P.krayl + ray_elems * ((size_t)ce.side * P.nbnd + band) + q4, P, ce, ray);
+            const Real wet = st.col_gas[icl + tcl * P.idx_h2o] + st.col_gas[icl];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) ray[j] *= wet;
+        }
+        Real ct = 0, cs = 0, cgg = 0;
+        if (CLOUD) { ct = a.cld_tau[icl + tcl * band]; cs = a.cld_ssa[icl + tcl * band]; cgg = a.cld_g[icl + tcl * band]; }
+        V4<Real> v0, v1, v2, v3;
+        Real* p0 = &v0.x; Real* p1 = &v1.x; Real* p2 = &v2.x; Real* p3 = &v3.x;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+        {
+            Real t, w0, g = 0;
+            combine_rayleigh(tau[j], ray[j], t, w0);
+            if (CLOUD) increment_2str(t, w0, g, ct, cs, cgg);
+            Real Rdif, Tdif, Rdir, Tdir, Tnoscat;
+            two_stream(t, w0, g, mu0s, Rdif, Tdif, Rdir, Tdir, Tnoscat);
+            p0[j] = Rdif; p1[j] = Tdif;
+            p2[j] = sun ? Rdir * dir[j] : (Real)0;     // source_up
+            p3[j] = sun ? Tdir * dir[j] : (Real)0;     // source_dn
+            dir[j] = Tnoscat * dir[j];
+        }
+        scr[(size_t)(k * 4 + 0) * FUSED_THREADS] = v0;
+        scr[(size_t)(k * 4 + 1) * FUSED_THREADS] = v1;
+        scr[(size_t)(k * 4 + 2) * FUSED_THREADS] = v2;
+        scr[(size_t)(k * 4 + 3) * FUSED_THREADS] = v3;
+        const Real s = quad_sum<Real, LPC>(dir);
+        if (lead)
+        {
+            const size_t o = cg + (size_t)a.ncol * level(k + 1);
+            a.flux_dir[o] += s; a.flux_dn[o] += s;
+            if (a.bnd_dir) a.bnd_dir[o + nlev_stride * band] = s;
+        }
+    }
+
+    // ---- pass 2: adding, surface -> top (F90:1135-1245)
+    Real alb[4], src[4];
+    {
+        const Real adir = a.alb_dir[band + (size_t)P.nbnd * cg];
+        const Real adif = a.alb_dif[band + (size_t)P.nbnd * cg];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { alb[j] = adif; src[j] = sun ? dir[j] * adir : (Real)0; }
+    }
+    for (int k = nlay - 1; k >= 0; --k)
+    {
+        const V4<Real> v0 = scr[(size_t)(k * 4 + 0) * FUSED_THREADS], v1 = scr[(size_t)(k * 4 + 1) * FUSED_THREADS];
+        const V4<Real> v2 = scr[(size_t)(k * 4 + 2) * FUSED_THREADS], v3 = scr[(size_t)(k * 4 + 3) * FUSED_THREADS];
+        const Real* rdif = &v0.x; const Real* tdif = &v1.x; const Real* sup = &v2.x; const Real* sdn = &v3.x;
+        V4<Real> oa, ob, oc, od;
+        Real* pa = &oa.x; Real* pb = &ob.x; Real* pc = &oc.x; Real* pd = &od.x;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+        {
+            const Real denom = M<Real>::rcp((Real)1 - rdif[j] * alb[j]);
+            pa[j] = tdif[j] * denom;
+            pb[j] = (rdif[j] * src[j] + sdn[j]) * denom;
+            pc[j] = alb[j]; pd[j] = src[j];
+            const Real nsrc = sup[j] + tdif[j] * denom * (src[j] + alb[j] * sdn[j]);
+            alb[j] = rdif[j] + tdif[j] * tdif[j] * alb[j] * denom;
+            src[j] = nsrc;
+        }
+        scr[(size_t)(k * 4 + 0) * FUSED_THREADS] = oa;
+        scr[(size_t)(k * 4 + 1) * FUSED_THREADS] = ob;
+        scr[(size_t)(k * 4 + 2) * FUSED_THREADS] = oc;
+        scr[(size_t)(k * 4 + 3) * FUSED_THREADS] = od;
+    }
+
+    // ---- pass 3: fluxes, top -> surface; diffuse flux_dn(top) = 0 (no inc_flux_dif)
+    Real fdn[4] = {0, 0, 0, 0}, fup[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) fup[j] = fdn[j] * alb[j] + src[j];
+    {
+        const Real su = quad_sum<Real, LPC>(fup);
+        if (lead)
+        {
+            const size_t o = cg + (size_t)a.ncol * level(0);
+            a.flux_up[o] += su;
+            if (a.bnd_up) { a.bnd_up[o + nlev_stride * band] = su; a.bnd_dn[o + nlev_stride * band] = a.bnd_dir[o + nlev_stride * band]; }
+        }
+    }
+    for (int k = 0; k < nlay; ++k)
+    {
+        const V4<Real> va = scr[(size_t)(k * 4 + 0) * FUSED_THREADS], vb = scr[(size_t)(k * 4 + 1) * FUSED_THREADS];
+        const V4<Real> vc = scr[(size_t)(k * 4 + 2) * FUSED_THREADS], vd = scr[(size_t)(k * 4 + 3) * FUSED_THREADS];
+        fdn[0] = fma(va.x, fdn[0], vb.x); fdn[1] = fma(va.y, fdn[1], vb.y);
+        fdn[2] = fma(va.z, fdn[2], vb.z); fdn[3] = fma(va.w, fdn[3], vb.w);
+        fup[0] = fma(fdn[0], vc.x, vd.x); fup[1] = fma(fdn[1], vc.y, vd.y);
+        fup[2] = fma(fdn[2], vc.z, vd.z); fup[3] = fma(fdn[3], vc.w, vd.w);
+        const Real su = quad_sum<Real, LPC>(fup), sd = quad_sum<Real, LPC>(fdn);
+        if (lead)
+        {
+            const size_t o = cg + (size_t)a.ncol * level(k + 1);
+            a.flux_up[o] += su; a.flux_dn[o] += sd;
+            if (a.bnd_up) { a.bnd_up[o + nlev_stride * band] = su; a.bnd_dn[o + nlev_stride * band] = sd + a.bnd_dir[o + nlev_stride * band]; }
+        }
+    }
+}
+
+template<typename Real>
+void launch_sw_band(const DevPlan<Real>& P, const BandArgs& B, const TileState<Real>& st,
+                    const FusedArgs<Real>& a, cudaStream_t s)
+{
+    const int lpc = P.gw / 4, cpb = FUSED_THREADS / lpc;
+    const unsigned grid = (unsigned)((a.nc + cpb - 1) / cpb);
+    const bool cloud = a.cld_tau != nullptr;
+    if (lpc == 4)
+    {
+        if (cloud) sw_band_kernel<Real, 4, true><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, a);
+        else sw_band_kernel<Real, 4, false><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, a);
+    }
+    else
+    {
+        if (cloud) sw_band_kernel<Real, 2, true><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, a);
+        else sw_band_kernel<Real, 2, false><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, a);
+    }
+    count_launch();
+}
+
+template void launch_sw_band<float>(const DevPlan<float>&, const BandArgs&, const TileState<float>&, const FusedArgs<float>&, cudaStream_t);
+template void launch_sw_band<double>(const DevPlan<double>&, const BandArgs&, const TileState<double>&, const FusedArgs<double>&, cudaStream_t);
+
+template<typename Real> int sw_blocks_per_wave(int gw)
+{
+    int dev = 0, sms = 0, occ = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (gw == 16) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sw_band_kernel<Real, 4, false>, FUSED_THREADS, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sw_band_kernel<Real, 2, false>, FUSED_THREADS, 0);
+    return sms * occ;
+}
+template int sw_blocks_per_wave<float>(int);
+template int sw_blocks_per_wave<double>(int);
+
+}  // namespace rb200

@@ -1,0 +1,219 @@
+// physics.cuh — per-cell device functions shared by the fused and the materialised kernels.
+// A thread owns one column and NG=4 consecutive g-points of one band ("quad"); the tables are
+// band-blocked with the g-point fastest (plan.hpp), so every interpolation corner is one
+// aligned 4-wide vector load.
+#pragma once
+#include "common.cuh"
+
+namespace rb200 {
+
+// decoded (column, layer, band) interpolation state
+template<typename Real> struct Cell
+{
+    Real w[8];        // fmajor: [it*4 + ip*2 + ie]
+    Real fm[4];       // fminor: [it*2 + ie]
+    Real cm0, cm1;    // col_mix
+    Real dens, vd;    // 0.01 p/T ; vmr_fact*dry_fact
+    int maj0, maj1;   // element offsets of the (it, ip=0, ie=0) rows in a band's major block
+    int min0, min1;   // element offsets of the (it, ie=0) rows in a contributor / Rayleigh block
+    int side;         // 0 lower (tropo), 1 upper
+};
+
+template<typename Real>
+__device__ __forceinline__ int cell_side(const V4<Real>& cell) { return ((M<Real>::as_int(cell.w) >> 16) & 1) ? 0 : 1; }
+
+template<typename Real>
+__device__ __forceinline__ void decode_cell(const DevPlan<Real>& P, const V4<Real>& cell,
+                                            const V4<Real>& fa, const V4<Real>& fb, Cell<Real>& o)
+{
+    const int bits = M<Real>::as_int(cell.w);
+    const int jt = bits & 0xff, jp = (bits >> 8) & 0xff;
+    o.side = ((bits >> 16) & 1) ? 0 : 1;
+    const int jb = M<Real>::as_int(fb.z);
+    const int je0 = jb & 0xff, je1 = (jb >> 8) & 0xff;
+    const Real fpress = cell.x, omf = (Real)1 - fpress;
+    o.dens = cell.y; o.vd = cell.z;
+    o.cm0 = fa.x; o.cm1 = fa.y;
+    o.fm[0] = fa.z; o.fm[1] = fa.w; o.fm[2] = fb.x; o.fm[3] = fb.y;
+    o.w[0] = omf * o.fm[0]; o.w[1] = omf * o.fm[1]; o.w[2] = fpress * o.fm[0]; o.w[3] = fpress * o.fm[1];
+    o.w[4] = omf * o.fm[2]; o.w[5] = omf * o.fm[3]; o.w[6] = fpress * o.fm[2]; o.w[7] = fpress * o.fm[3];
+    const int ip0 = jp + o.side - 1;   // 0-based lower pressure row (Fortran jpress+itropo-1)
+    o.maj0 = (((jt - 1) * (P.npres + 1) + ip0) * P.neta + (je0 - 1)) * P.gw;
+    o.maj1 = (((jt) * (P.npres + 1) + ip0) * P.neta + (je1 - 1)) * P.gw;
+    o.min0 = ((jt - 1) * P.neta + (je0 - 1)) * P.gw;
+    o.min1 = ((jt) * P.neta + (je1 - 1)) * P.gw;
+}
+
+#define RB_FMA4(acc, s, v) { acc[0] = fma(s, v.x, acc[0]); acc[1] = fma(s, v.y, acc[1]); acc[2] = fma(s, v.z, acc[2]); acc[3] = fma(s, v.w, acc[3]); }
+
+// interpolate3D_byflav (mo_gas_optics_rrtmgp_kernels.F90:760-789): partial sums per temperature
+template<typename Real>
+__device__ __forceinline__ void interp_major(const Real* __restrict__ tab, const DevPlan<Real>& P,
+                                             const Cell<Real>& c, Real (&s0)[4], Real (&s1)[4])
+{
+    const int de = P.gw, dp = P.neta * P.gw;
+    const V4<Real> a0 = ldg4(tab + c.maj0), a1 = ldg4(tab + c.maj0 + de);
+    const V4<Real> a2 = ldg4(tab + c.maj0 + dp), a3 = ldg4(tab + c.maj0 + dp + de);
+    const V4<Real> b0 = ldg4(tab + c.maj1), b1 = ldg4(tab + c.maj1 + de);
+    const V4<Real> b2 = ldg4(tab + c.maj1 + dp), b3 = ldg4(tab + c.maj1 + dp + de);
+    s0[0] = c.w[0] * a0.x; s0[1] = c.w[0] * a0.y; s0[2] = c.w[0] * a0.z; s0[3] = c.w[0] * a0.w;
+    RB_FMA4(s0, c.w[1], a1) RB_FMA4(s0, c.w[2], a2) RB_FMA4(s0, c.w[3], a3)
+    s1[0] = c.w[4] * b0.x; s1[1] = c.w[4] * b0.y; s1[2] = c.w[4] * b0.z; s1[3] = c.w[4] * b0.w;
+    RB_FMA4(s1, c.w[5], b1) RB_FMA4(s1, c.w[6], b2) RB_FMA4(s1, c.w[7], b3)
+}
+
+// interpolate2D_byflav (F90:738-758)
+template<typename Real>
+__device__ __forceinline__ void interp_minor(const Real* __restrict__ tab, const DevPlan<Real>& P,
+                                             const Cell<Real>& c, Real (&s)[4])
+{
+    const V4<Real> a0 = ldg4(tab + c.min0), a1 = ldg4(tab + c.min0 + P.gw);
+    const V4<Real> b0 = ldg4(tab + c.min1), b1 = ldg4(tab + c.min1 + P.gw);
+    s[0] = c.fm[0] * a0.x; s[1] = c.fm[0] * a0.y; s[2] = c.fm[0] * a0.z; s[3] = c.fm[0] * a0.w;
+    RB_FMA4(s, c.fm[1], a1) RB_FMA4(s, c.fm[2], b0) RB_FMA4(s, c.fm[3], b1)
+}
+
+// gas absorption optical depth of 4 g-points: major + minor contributors of the layer's side
+// (compute_tau_absorption, F90:178-502).  q4 = first g-point of the quad within the band.
+template<typename Real>
+__device__ __forceinline__ void gas_tau(const DevPlan<Real>& P, const BandArgs& B, const Cell<Real>& c,
+                                        const Real* __restrict__ kmaj_band, int q4,
+                                        const Real* __restrict__ col_gas, size_t icl, size_t tcl,
+                                        Real (&tau)[4], Real (&s0)[4], Real (&s1)[4])
+{
+    interp_major(kmaj_band + q4, P, c, s0, s1);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) tau[j] = c.cm0 * s0[j] + c.cm1 * s1[j];
+    const int side = c.side;
+    const int nm = B.nminor[side];
+    const size_t mstride = (size_t)P.ntemp * P.neta * P.gw;
+    for (int m = 0; m < nm; ++m)
+    {
+        const MinorDev d = B.minor[side][m];
+        Real scaling = col_gas[icl + tcl * d.idx_minor];
+        if (d.flags & 1)
+        {
+            scaling *= c.dens;
+            if (d.idx_scaling > 0)
+            {
+                const Real x = col_gas[icl + tcl * d.idx_scaling] * c.vd;
+                scaling *= (d.flags & 2) ? ((Real)1 - x) : x;
+            }
+        }
+        Real s[4];
+        interp_minor(P.kminor[side] + mstride * d.contributor + q4, P, c, s);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) tau[j] = fma(scaling, s[j], tau[j]);
+    }
+}
+
+// interpolate1D (F90:715-734) for one band
+template<typename Real>
+__device__ __forceinline__ Real planck_band(const Real* __restrict__ tab, int n, Real tmin, Real delta, Real T)
+{
+    const Real val0 = M<Real>::div(T - tmin, delta);
+    const int iv = (int)val0;
+    const Real frac = val0 - (Real)iv;
+    const int index = min(n - 1, max(1, iv + 1));
+    const Real t0 = tab[index - 1], t1 = tab[index];
+    return t0 + frac * (t1 - t0);
+}
+
+// sum of a quad's 4 values across the LPC lanes of a column; result valid in every lane
+template<typename Real, int LPC>
+__device__ __forceinline__ Real quad_sum(const Real (&v)[4])
+{
+    Real s = (v[0] + v[1]) + (v[2] + v[3]);
+    if (LPC >= 2) s += __shfl_xor_sync(0xffffffffu, s, 1);
+    if (LPC >= 4) s += __shfl_xor_sync(0xffffffffu, s, 2);
+    return s;
+}
+
+// lw_source_noscat + one transport step (mo_rte_solver_kernels.F90:620-708) for one g-point
+template<typename Real>
+__device__ __forceinline__ void lw_layer(Real tau_loc, Real lay_src, Real lev_above, Real lev_below,
+                                         Real& trans, Real& src_up, Real& src_dn)
+{
+    // tau_thresh = sqrt(sqrt(epsilon))
+    const Real tau_thresh = sizeof(Real) == 4 ? (Real)1.857e-2 : (Real)1.220703125e-4;
+    trans = M<Real>::exp(-tau_loc);
+    Real fact;
+    if (tau_loc > tau_thresh) fact = M<Real>::div((Real)1 - trans, tau_loc) - trans;
+    else fact = tau_loc * ((Real)0.5 + tau_loc * ((Real)(-1.0 / 3.0) + tau_loc * (Real)0.125));
+    const Real omt = (Real)1 - trans;
+    src_dn = omt * lev_below + (Real)2 * fact * (lay_src - lev_below);
+    src_up = omt * lev_above + (Real)2 * fact * (lay_src - lev_above);
+}
+
+}  // namespace rb200
+
+namespace rb200 {
+
+// combine_abs_and_rayleigh (src/Gas_optics_rrtmgp.cpp:365-385): ssa threshold 2*epsilon
+template<typename Real>
+__device__ __forceinline__ void combine_rayleigh(Real tau_abs, Real tau_ray, Real& tau, Real& ssa)
+{
+    tau = tau_abs + tau_ray;
+    ssa = (tau > (Real)2 * M<Real>::eps) ? M<Real>::div(tau_ray, tau) : (Real)0;
+}
+
+// inc_2stream_by_2stream_bybnd for one cell (mo_optical_props_kernels.F90:451-482), eps = 3*tiny
+template<typename Real>
+__device__ __forceinline__ void increment_2str(Real& tau, Real& ssa, Real& g, Real t2, Real s2, Real g2)
+{
+    const Real eps3 = (Real)3 * M<Real>::tiny;
+    const Real tau12 = tau + t2;
+    const Real ts1 = tau * ssa, ts2 = t2 * s2;
+    const Real tauscat12 = ts1 + ts2;
+    g = M<Real>::div(ts1 * g + ts2 * g2, M<Real>::max(eps3, tauscat12));
+    ssa = M<Real>::div(tauscat12, M<Real>::max(eps3, tau12));
+    tau = tau12;
+}
+
+// delta_scale_2str_k for one cell (mo_optical_props_kernels.F90:76-98)
+template<typename Real>
+__device__ __forceinline__ void delta_scale_cell(Real& tau, Real& ssa, Real& g)
+{
+    const Real eps3 = (Real)3 * M<Real>::tiny;
+    const Real f = g * g, wf = ssa * f;
+    tau = ((Real)1 - wf) * tau;
+    ssa = M<Real>::div(ssa - wf, M<Real>::max(eps3, (Real)1 - wf));
+    g = M<Real>::div(g - f, M<Real>::max(eps3, (Real)1 - f));
+}
+
+// sw_dif_and_source for one cell (mo_rte_solver_kernels.F90:985-1127): two-stream coefficients
+// (Zdunkowski PIFM; Meador & Weaver eqs. 14, 15, 25, 26) — mu0s is max(min_mu0, mu0).
+template<typename Real>
+__device__ __forceinline__ void two_stream(Real tau, Real w0, Real g, Real mu0s,
+                                           Real& Rdif, Real& Tdif, Real& Rdir, Real& Tdir, Real& Tnoscat)
+{
+    const Real min_k = (Real)1.e4 * M<Real>::eps;
+    const Real gamma1 = ((Real)8 - w0 * ((Real)5 + (Real)3 * g)) * (Real).25;
+    const Real gamma2 = (Real)3 * (w0 * ((Real)1 - g)) * (Real).25;
+    const Real k = M<Real>::sqrt(M<Real>::max((gamma1 - gamma2) * (gamma1 + gamma2), min_k));
+    const Real exp_minusktau = M<Real>::exp(-tau * k);
+    const Real exp_minus2ktau = exp_minusktau * exp_minusktau;
+    Real RT_term = M<Real>::rcp(k * ((Real)1 + exp_minus2ktau) + gamma1 * ((Real)1 - exp_minus2ktau));
+    Rdif = RT_term * gamma2 * ((Real)1 - exp_minus2ktau);
+    Tdif = RT_term * (Real)2 * k * exp_minusktau;
+
+    const Real k_mu = k * mu0s;
+    const Real d = (Real)1 - k_mu * k_mu;
+    RT_term = M<Real>::div(w0 * RT_term, (M<Real>::fabs(d) >= M<Real>::eps) ? d : M<Real>::eps);
+    const Real gamma3 = ((Real)2 - (Real)3 * mu0s * g) * (Real).25;
+    const Real gamma4 = (Real)1 - gamma3;
+    const Real alpha1 = gamma1 * gamma4 + gamma2 * gamma3;
+    const Real alpha2 = gamma1 * gamma3 + gamma2 * gamma4;
+    const Real k_gamma3 = k * gamma3, k_gamma4 = k * gamma4;
+    Tnoscat = M<Real>::exp(-M<Real>::div(tau, mu0s));
+    Rdir = RT_term * (((Real)1 - k_mu) * (alpha2 + k_gamma3)
+                      - ((Real)1 + k_mu) * (alpha2 - k_gamma3) * exp_minus2ktau
+                      - (Real)2 * (k_gamma3 - alpha2 * k_mu) * exp_minusktau * Tnoscat);
+    Tdir = -RT_term * (((Real)1 + k_mu) * (alpha1 + k_gamma4) * Tnoscat
+                       - ((Real)1 - k_mu) * (alpha1 - k_gamma4) * exp_minus2ktau * Tnoscat
+                       - (Real)2 * (k_gamma4 + alpha1 * k_mu) * exp_minusktau);
+    Rdir = M<Real>::max((Real)0, M<Real>::min(Rdir, (Real)1 - Tnoscat));
+    Tdir = M<Real>::max((Real)0, M<Real>::min(Tdir, (Real)1 - Tnoscat - Rdir));
+}
+
+}  // namespace rb200

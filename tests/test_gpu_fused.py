@@ -1,0 +1,116 @@
+"""GPU parity of the fused LW / SW column solvers (C ABI rrtmgp_b200_{lw,sw}_fluxes) against the
+CPU oracle on identical seeded inputs.  Tolerances are BASELINE.json's: fluxes within 1e-5 W/m2
+in the fp64 build, within 0.05 W/m2 in the fp32 build (vs the fp64 oracle)."""
+import numpy as np
+import pytest
+import torch
+
+from rte_rrtmgp_cpp_b200 import api
+from rte_rrtmgp_cpp_b200.atmos import rce_atmosphere, allsky_atmosphere
+from rte_rrtmgp_cpp_b200.kdist import synthetic_kdist, synthetic_cloud_lut, REDUCED_LW_128, REDUCED_SW_112
+from helpers import oracle_lw, oracle_sw
+
+pytestmark = pytest.mark.gpu
+TOL = {torch.float64: 1e-5, torch.float32: 0.05}
+
+
+def _cmp(out, ref, keys, tol):
+    for k in keys:
+        d = np.max(np.abs(out[k].numpy() - ref[k]))
+        assert d <= tol, f"{k}: max abs diff {d} > {tol}"
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("top_at_1", [False, True])
+def test_lw_fused_clear(dtype, top_at_1):
+    kd = synthetic_kdist("lw")
+    atm = rce_atmosphere(70, 48, top_at_1=top_at_1)
+    ref = oracle_lw(kd, atm)
+    sol = api.Radiation_solver_longwave(kd, atm.vmr.keys(), dtype=dtype)
+    out = sol.solve_gpu(api.DeviceColumns(atm, dtype), switch_output_bnd_fluxes=True, heating=True)
+    _cmp(out, ref, ("flux_up", "flux_dn", "flux_net", "bnd_flux_up", "bnd_flux_dn", "bnd_flux_net"), TOL[dtype])
+    hr_tol = 1e-9 if dtype == torch.float64 else 2e-3   # K/s; thin top layers amplify flux noise in fp32
+    assert np.max(np.abs(out["heating_rate"].numpy() - ref["heating_rate"])) <= hr_tol
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("top_at_1", [False, True])
+def test_sw_fused_clear(dtype, top_at_1):
+    kd = synthetic_kdist("sw")
+    atm = rce_atmosphere(70, 48, top_at_1=top_at_1, night_fraction=0.2)
+    atm.tsi_scaling[:] = np.linspace(0.9, 1.1, atm.ncol)
+    ref = oracle_sw(kd, atm)
+    sol = api.Radiation_solver_shortwave(kd, atm.vmr.keys(), dtype=dtype)
+    out = sol.solve_gpu(api.DeviceColumns(atm, dtype), switch_output_bnd_fluxes=True)
+    _cmp(out, ref, ("flux_up", "flux_dn", "flux_net", "flux_dn_dir", "bnd_flux_up", "bnd_flux_dn",
+                    "bnd_flux_net", "bnd_flux_dn_dir"), TOL[dtype])
+    night = atm.mu0 <= 0
+    assert night.any() and np.all(out["flux_dn"].numpy()[night] == 0.0)
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("delta", [True, False])
+def test_allsky_fused(dtype, delta):
+    atm = allsky_atmosphere(24, 72)       # the reference's all-sky case: 2 of 3 columns cloudy
+    for kind in ("lw", "sw"):
+        kd, lut = synthetic_kdist(kind), synthetic_cloud_lut(kind)
+        if kind == "lw":
+            ref = oracle_lw(kd, atm, lut)
+            sol = api.Radiation_solver_longwave(kd, atm.vmr.keys(), lut, dtype)
+            keys = ("flux_up", "flux_dn", "flux_net")
+        else:
+            ref = oracle_sw(kd, atm, lut, delta)
+            sol = api.Radiation_solver_shortwave(kd, atm.vmr.keys(), lut, dtype)
+            keys = ("flux_up", "flux_dn", "flux_net", "flux_dn_dir")
+        out = sol.solve_gpu(api.DeviceColumns(atm, dtype), switch_cloud_optics=True, switch_delta_cloud=delta)
+        _cmp(out, ref, keys, TOL[dtype])
+
+
+@pytest.mark.parametrize("kind,sizes", [("lw", REDUCED_LW_128), ("sw", REDUCED_SW_112)])
+def test_reduced_gpoint_sets(kind, sizes):
+    kd = synthetic_kdist(kind, sizes)
+    atm = rce_atmosphere(33, 30, cloudy=True)
+    lut = synthetic_cloud_lut(kind)
+    if kind == "lw":
+        ref, sol = oracle_lw(kd, atm, lut), api.Radiation_solver_longwave(kd, atm.vmr.keys(), lut)
+    else:
+        ref, sol = oracle_sw(kd, atm, lut), api.Radiation_solver_shortwave(kd, atm.vmr.keys(), lut)
+    out = sol.solve_gpu(api.DeviceColumns(atm), switch_cloud_optics=True, switch_output_bnd_fluxes=True)
+    _cmp(out, ref, ("flux_up", "flux_dn", "bnd_flux_up", "bnd_flux_dn"), 1e-5)
+
+
+def test_tiling_and_column_sharding_are_bit_identical():
+    """T5: a column's result does not depend on the tile or shard it is computed in."""
+    kd = synthetic_kdist("lw")
+    atm = rce_atmosphere(200, 32)
+    sol = api.Radiation_solver_longwave(kd, atm.vmr.keys())
+    full = sol.solve_gpu(api.DeviceColumns(atm))["flux_up"].numpy().copy()
+    sol.set_tile_columns(64)
+    tiled = sol.solve_gpu(api.DeviceColumns(atm))["flux_up"].numpy().copy()
+    assert np.array_equal(full, tiled)
+    sol.set_tile_columns(0)
+    parts = [sol.solve_gpu(api.DeviceColumns(atm.subset(a, b)))["flux_up"].numpy().copy()
+             for a, b in ((0, 77), (77, 200))]
+    assert np.array_equal(full, np.concatenate(parts, axis=0))
+
+
+def test_vertical_flip_invariance():
+    kd = synthetic_kdist("sw")
+    atm = rce_atmosphere(40, 36)
+    sol = api.Radiation_solver_shortwave(kd, atm.vmr.keys())
+    a = sol.solve_gpu(api.DeviceColumns(atm))["flux_net"].numpy().copy()
+    b = sol.solve_gpu(api.DeviceColumns(atm.flipped()))["flux_net"].numpy().copy()
+    assert np.max(np.abs(a - b[:, ::-1])) < 1e-9
+
+
+def test_errors_are_loud():
+    kd = synthetic_kdist("lw")
+    atm = rce_atmosphere(4, 8)
+    with pytest.raises(RuntimeError, match="required gas"):
+        api.Gas_optics_rrtmgp_gpu(kd, [g for g in atm.vmr if g != "co2"])
+    sol = api.Radiation_solver_shortwave(synthetic_kdist("sw"), atm.vmr.keys())
+    lw = api.Radiation_solver_longwave(kd, atm.vmr.keys())
+    cols = api.DeviceColumns(atm)
+    cols.gas_concs.gas_concs_map.pop("o3")
+    with pytest.raises(RuntimeError, match="o3"):
+        lw.solve_gpu(cols)
