@@ -254,6 +254,11 @@ int rrtmgp_b200_sw_fluxes(rrtmgp_b200_gas_optics* go, const rrtmgp_b200_columns*
  * kernels the last fused call launched (for bench.py's gpu_launches). */
 int rrtmgp_b200_set_tile_columns(rrtmgp_b200_gas_optics* go, int ncol_tile);
 long long rrtmgp_b200_launch_count(void);
+/* Device-side timing of the fused band kernels: each call first returns (and resets) the time
+ * and launch count accumulated since the previous call — CUDA events recorded on the launching
+ * stream around every tile's band-kernel loop — then switches recording on/off.  Synchronises. */
+int rrtmgp_b200_profile(int enable, double* lw_ms, long long* lw_launches, double* sw_ms,
+                        long long* sw_launches);
 
 #ifdef __cplusplus
 }

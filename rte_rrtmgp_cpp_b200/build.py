@@ -8,8 +8,9 @@ from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB = os.path.join(HERE, "librrtmgp_b200.so")
-OBJ = os.path.join(HERE, "csrc", "_obj")
+LIB = os.environ.get("RB200_LIB", os.path.join(HERE, "librrtmgp_b200.so"))
+OBJ = os.path.join(HERE, "csrc", "_obj" + os.environ.get("RB200_TAG", ""))
+EXTRA = os.environ.get("RB200_DEFS", "").split()
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 # k1_interp.cu carries the index arithmetic: no FMA contraction there (bit-exact indices)
@@ -32,7 +33,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     def cc(item):
         src, extra = item
         obj = os.path.join(OBJ, src.replace(".cu", ".o"))
-        cmd = ["nvcc", *ARCH, *COMMON, *extra, "-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = ["nvcc", *ARCH, *COMMON, *EXTRA, *extra, "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         r = subprocess.run(cmd, capture_output=True, text=True)

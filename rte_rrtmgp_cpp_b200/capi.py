@@ -8,7 +8,7 @@ import os
 from .ctables import KDistFileC, CloudFileC
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librrtmgp_b200.so")
+LIB_PATH = os.environ.get("RB200_LIB", os.path.join(_HERE, "librrtmgp_b200.so"))
 F32, F64, HOST_ONLY = 0, 1, 0x100
 E_ARG, E_RANGE, E_MISSING, E_CUDA = 1, 2, 3, 4
 
@@ -76,6 +76,7 @@ SYMBOLS = {
     "rrtmgp_b200_sw_fluxes": (i, [vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp]),
     "rrtmgp_b200_set_tile_columns": (i, [vp, i]),
     "rrtmgp_b200_launch_count": (C.c_longlong, []),
+    "rrtmgp_b200_profile": (i, [i, C.POINTER(d), C.POINTER(C.c_longlong), C.POINTER(d), C.POINTER(C.c_longlong)]),
 }
 
 _lib = None

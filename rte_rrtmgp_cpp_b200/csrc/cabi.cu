@@ -17,6 +17,10 @@ static thread_local std::string g_err;
 static std::atomic<long long> g_launches{0};
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
+// optional device-side timing of the fused band kernels (bench.py's roofline leg)
+struct Profile { bool on = false; std::vector<cudaEvent_t> ev[2]; double ms[2] = {0, 0}; long long launches[2] = {0, 0}; };
+static Profile g_prof;
+
 struct CudaError : std::runtime_error { using std::runtime_error::runtime_error; };
 struct RangeError : std::runtime_error { using std::runtime_error::runtime_error; };
 
@@ -235,6 +239,28 @@ int rrtmgp_b200_gas_optics_get_tables(const rrtmgp_b200_gas_optics* g, int* band
             std::memcpy(gas_names + (size_t)i * string_len, h.gas_names[i].data(), std::min<size_t>(string_len, h.gas_names[i].size()));
         }
     if (solar_source && !h.solar_source.empty()) std::copy(h.solar_source.begin(), h.solar_source.end(), solar_source);
+    return 0;
+}
+
+int rrtmgp_b200_profile(int enable, double* lw_ms, long long* lw_launches, double* sw_ms, long long* sw_launches)
+{
+    // collect: synchronises the device, folds the recorded event pairs into milliseconds
+    cudaDeviceSynchronize();
+    for (int k = 0; k < 2; ++k)
+    {
+        for (size_t i = 0; i + 1 < g_prof.ev[k].size(); i += 2)
+        {
+            float ms = 0; cudaEventElapsedTime(&ms, g_prof.ev[k][i], g_prof.ev[k][i + 1]); g_prof.ms[k] += ms;
+        }
+        for (cudaEvent_t e : g_prof.ev[k]) cudaEventDestroy(e);
+        g_prof.ev[k].clear();
+    }
+    if (lw_ms) *lw_ms = g_prof.ms[0];
+    if (lw_launches) *lw_launches = g_prof.launches[0];
+    if (sw_ms) *sw_ms = g_prof.ms[1];
+    if (sw_launches) *sw_launches = g_prof.launches[1];
+    g_prof.ms[0] = g_prof.ms[1] = 0; g_prof.launches[0] = g_prof.launches[1] = 0;
+    g_prof.on = enable != 0;
     return 0;
 }
 
@@ -748,10 +774,16 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
                                       cols->d_rel, cols->d_dei, nc, 0, sw && cols->delta_cloud, ctau, cssa, cg, s);
             a.cld_tau = ctau; a.cld_ssa = cssa; a.cld_g = cg;
         }
+        if (g_prof.on) { cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, s)); g_prof.ev[sw].push_back(e); }
         for (int b = 0; b < h.nbnd; ++b)
         {
             if (sw) launch_sw_band<Real>(dplan<Real>(g), g->bands[b], st, a, s);
             else launch_lw_band<Real>(dplan<Real>(g), g->bands[b], st, a, s);
+        }
+        if (g_prof.on)
+        {
+            cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, s)); g_prof.ev[sw].push_back(e);
+            g_prof.launches[sw] += h.nbnd;
         }
     }
     if (out->d_flux_net) launch_net<Real>(ncv, a.flux_dn, a.flux_up, out->d_flux_net, s);

@@ -36,9 +36,15 @@ template<> struct M<float>
 {
     static constexpr float eps = FLT_EPSILON;
     static constexpr float tiny = FLT_MIN;
+#ifdef RB_F32_PRECISE
+    static __device__ __forceinline__ float exp(float x) { return expf(x); }
+    static __device__ __forceinline__ float sqrt(float x) { return sqrtf(x); }
+    static __device__ __forceinline__ float div(float a, float b) { return a / b; }
+#else
     static __device__ __forceinline__ float exp(float x) { return __expf(x); }
     static __device__ __forceinline__ float sqrt(float x) { return sqrtf(x); }
     static __device__ __forceinline__ float div(float a, float b) { return __fdividef(a, b); }
+#endif
     static __device__ __forceinline__ float rcp(float a) { return __frcp_rn(a); }
     static __device__ __forceinline__ float fabs(float a) { return fabsf(a); }
     static __device__ __forceinline__ float max(float a, float b) { return fmaxf(a, b); }

@@ -154,7 +154,11 @@ template<typename Real>
 __device__ __forceinline__ void combine_rayleigh(Real tau_abs, Real tau_ray, Real& tau, Real& ssa)
 {
     tau = tau_abs + tau_ray;
-    ssa = (tau > (Real)2 * M<Real>::eps) ? M<Real>::div(tau_ray, tau) : (Real)0;
+    // CPU reference: 2*epsilon (fp64).  In the fp32 build 2*epsilon(float) would zero the
+    // single-scattering albedo of every cell thinner than 2.4e-7; use the reference CUDA path's
+    // 2*tiny there (src_kernels_cuda/gas_optics_rrtmgp_kernels.cu:721-746).
+    const Real thr = sizeof(Real) == 4 ? (Real)2 * M<Real>::tiny : (Real)2 * M<Real>::eps;
+    ssa = (tau > thr) ? M<Real>::div(tau_ray, tau) : (Real)0;
 }
 
 // inc_2stream_by_2stream_bybnd for one cell (mo_optical_props_kernels.F90:451-482), eps = 3*tiny
@@ -184,7 +188,7 @@ __device__ __forceinline__ void delta_scale_cell(Real& tau, Real& ssa, Real& g)
 // sw_dif_and_source for one cell (mo_rte_solver_kernels.F90:985-1127): two-stream coefficients
 // (Zdunkowski PIFM; Meador & Weaver eqs. 14, 15, 25, 26) — mu0s is max(min_mu0, mu0).
 template<typename Real>
-__device__ __forceinline__ void two_stream(Real tau, Real w0, Real g, Real mu0s,
+__device__ __forceinline__ void two_stream_ref(Real tau, Real w0, Real g, Real mu0s,
                                            Real& Rdif, Real& Tdif, Real& Rdir, Real& Tdir, Real& Tnoscat)
 {
     const Real min_k = (Real)1.e4 * M<Real>::eps;
@@ -215,5 +219,84 @@ __device__ __forceinline__ void two_stream(Real tau, Real w0, Real g, Real mu0s,
     Rdir = M<Real>::max((Real)0, M<Real>::min(Rdir, (Real)1 - Tnoscat));
     Tdir = M<Real>::max((Real)0, M<Real>::min(Tdir, (Real)1 - Tnoscat - Rdir));
 }
+
+// (1 - exp(-x)) / x for x >= 0 given e = exp(-x): series below 0.03 (no cancellation)
+__device__ __forceinline__ float omexp_over_x(float x, float e)
+{
+    return x < 0.03f ? 1.f - 0.5f * x * (1.f - (1.f / 3.f) * x * (1.f - 0.25f * x)) : __fdividef(1.f - e, x);
+}
+
+// fp32 two-stream: the same Meador-Weaver / PIFM expressions as two_stream_ref, algebraically
+// rearranged so nothing is divided by k and no O(1) terms cancel to O(tau) or O(k):
+//   P = (1-e2)/k = tau*g(a)*(1+e1),  g(a) = (1-e^-a)/a,  a = k*tau
+//   D = (1+e2) + gamma1*P            (RT_term = 1/(k*D))
+//   Rdif = gamma2*P/D, Tdif = 2*e1/D
+//   Rdir =  w0*[alpha2*P + (gamma3 - mu*alpha2)*Q  - k^2*mu*gamma3*P   ] / (D*(1-k^2 mu^2))
+//   Tdir = -w0*[T0*alpha1*P + (gamma4 + mu*alpha1)*Q' + k^2*mu*gamma4*P*T0] / (D*(1-k^2 mu^2))
+//   Q = (1-e1)^2 + 2*e1*(1-T0),  Q' = T0*(1-e1)^2 - 2*e1*(1-T0)
+// so k may go to zero (conservative scattering) without the reference's min_k = 1e4*eps floor,
+// which in fp32 (k >= 0.035) biases thick near-conservative clouds by O(0.3 W/m2).  Within
+// |1 - k^2 mu^2| < 1e-3 of the removable singularity mu is nudged to the edge of that band for the
+// scattering terms only (the direct-beam transmission keeps the true mu).
+__device__ __forceinline__ void two_stream_f32(float tau, float w0, float g, float mu0s,
+                                               float& Rdif, float& Tdif, float& Rdir, float& Tdir, float& Tnoscat)
+{
+    const float gamma1 = (8.f - w0 * (5.f + 3.f * g)) * .25f;
+    const float gamma2 = 3.f * (w0 * (1.f - g)) * .25f;
+    const float k2 = fmaxf(2.f * (1.f - w0) * (2.f - 0.5f * w0 * (1.f + 3.f * g)), 0.f);   // (g1-g2)(g1+g2)
+    const float k = sqrtf(k2);
+    const float a = k * tau;
+    const float e1 = __expf(-a), e2 = e1 * e1;
+    const float ga = omexp_over_x(a, e1);
+    const float om1 = a * ga;
+    const float P = tau * ga * (1.f + e1);
+    const float rD = __frcp_rn((1.f + e2) + gamma1 * P);
+    Rdif = gamma2 * P * rD;
+    Tdif = 2.f * e1 * rD;
+
+    const float x = __fdividef(tau, mu0s);
+    Tnoscat = __expf(-x);
+    const float omT_true = x * omexp_over_x(x, Tnoscat);
+    float mu = mu0s, T0 = Tnoscat, omT = omT_true;
+    float kmu = k * mu, d = 1.f - kmu * kmu;
+    const float band = 1.e-3f;
+    if (fabsf(d) < band)
+    {
+        d = d >= 0.f ? band : -band;
+        mu = __fdividef(sqrtf(1.f - d), k);
+        const float xe = __fdividef(tau, mu);
+        T0 = __expf(-xe);
+        omT = xe * omexp_over_x(xe, T0);
+    }
+    const float gamma3 = (2.f - 3.f * mu * g) * .25f;
+    const float gamma4 = 1.f - gamma3;
+    const float alpha1 = gamma1 * gamma4 + gamma2 * gamma3;
+    const float alpha2 = gamma1 * gamma3 + gamma2 * gamma4;
+    const float Q = om1 * om1 + 2.f * e1 * omT;
+    const float Qp = T0 * om1 * om1 - 2.f * e1 * omT;
+    const float k2mu = k2 * mu;
+    const float NR = alpha2 * P + (gamma3 - mu * alpha2) * Q - k2mu * gamma3 * P;
+    const float NT = T0 * (alpha1 * P + k2mu * gamma4 * P) + (gamma4 + mu * alpha1) * Qp;
+    const float f = __fdividef(w0 * rD, d);
+    Rdir = f * NR;
+    Tdir = -f * NT;
+    Rdir = fmaxf(0.f, fminf(Rdir, omT_true));
+    Tdir = fmaxf(0.f, fminf(Tdir, omT_true - Rdir));
+}
+
+template<typename Real>
+__device__ __forceinline__ void two_stream(Real tau, Real w0, Real g, Real mu0s,
+                                           Real& Rdif, Real& Tdif, Real& Rdir, Real& Tdir, Real& Tnoscat)
+{
+    two_stream_ref<Real>(tau, w0, g, mu0s, Rdif, Tdif, Rdir, Tdir, Tnoscat);
+}
+#ifndef RB_F32_REFERENCE_TWOSTREAM
+template<>
+__device__ __forceinline__ void two_stream<float>(float tau, float w0, float g, float mu0s,
+                                                  float& Rdif, float& Tdif, float& Rdir, float& Tdir, float& Tnoscat)
+{
+    two_stream_f32(tau, w0, g, mu0s, Rdif, Tdif, Rdir, Tdir, Tnoscat);
+}
+#endif
 
 }  // namespace rb200
