@@ -121,14 +121,15 @@ static void fill_devplan(rrtmgp_b200_gas_optics* g, DevPlan<Real>& P)
 {
     const HostPlan& h = g->h;
     g->kmajor.upload_as<Real>(h.kmajor);
-    if (h.is_lw) { g->pfrac.upload_as<Real>(h.pfrac); g->totplnk.upload_as<Real>(h.totplnk); }
+    if (h.is_lw) g->totplnk.upload_as<Real>(h.totplnk);
     else { g->solar.upload_as<Real>(h.solar_source); if (!h.krayl.empty()) g->krayl.upload_as<Real>(h.krayl); }
     for (int s = 0; s < 2; ++s) g->kminor[s].upload_as<Real>(h.minor[s].table);
     g->temp_ref.upload(h.temp_ref); g->vmr_ref.upload(h.vmr_ref);
     g->flavor.upload(h.flavor); g->band_flavor.upload(h.band_flavor); g->band_lims.upload(h.band_lims_gpt);
     P.is_lw = h.is_lw; P.ntemp = h.ntemp; P.npres = h.npres; P.neta = h.neta; P.nbnd = h.nbnd; P.ngpt = h.ngpt;
     P.nflav = h.nflav; P.ngas = h.ngas; P.gw = h.gw; P.nplanck = h.nplanck; P.idx_h2o = h.idx_h2o;
-    P.kmajor = (const Real*)g->kmajor.p; P.pfrac = (const Real*)g->pfrac.p; P.krayl = (const Real*)g->krayl.p;
+    P.kmajor = (const Real*)g->kmajor.p; P.pfrac = h.is_lw ? (const Real*)g->kmajor.p + h.gw : nullptr; P.krayl = (const Real*)g->krayl.p;
+    P.row_stride = h.row_stride;
     P.kminor[0] = (const Real*)g->kminor[0].p; P.kminor[1] = (const Real*)g->kminor[1].p;
     P.totplnk = (const Real*)g->totplnk.p; P.solar_source = (const Real*)g->solar.p;
     P.temp_ref = (const double*)g->temp_ref.p; P.vmr_ref = (const double*)g->vmr_ref.p;
@@ -176,6 +177,7 @@ int rrtmgp_b200_gas_optics_create(const rrtmgp_b200_kdist_file* kd, int n_avail,
             {
                 const auto& lst = h.minor[s].by_band[b];
                 B.nminor[s] = (int)lst.size();
+                B.first_minor[s] = lst.empty() ? 0 : h.minor[s].desc[lst[0]].contributor;
                 for (size_t m = 0; m < lst.size(); ++m)
                 {
                     const MinorDesc& d = h.minor[s].desc[lst[m]];
@@ -303,13 +305,17 @@ TileState<Real> carve_state(Arena& ws, const HostPlan& h, int nc, int nlay)
     st.flvA = ws.take<V4<Real>>(tcl * h.nflav);
     st.flvB = ws.take<V4<Real>>(tcl * h.nflav);
     st.col_gas = ws.take<Real>(tcl * (h.ngas + 1));
+    st.pl_lay = nullptr; st.pl_lev = nullptr;
+    if (h.is_lw) { st.pl_lay = ws.take<V2<Real>>(tcl); st.pl_lev = ws.take<V2<Real>>(tcl + nc); }
+    st.tmask = ws.take<unsigned>((size_t)nc * TMASK_WORDS);
     return st;
 }
 template<typename Real> size_t state_bytes(const HostPlan& h, int nc, int nlay)
 {
     const size_t tcl = (size_t)nc * nlay;
     return pad256(tcl * sizeof(V4<Real>)) + 2 * pad256(tcl * h.nflav * sizeof(V4<Real>))
-         + pad256(tcl * (h.ngas + 1) * sizeof(Real)) + 1024;
+         + pad256(tcl * (h.ngas + 1) * sizeof(Real)) + pad256((size_t)nc * TMASK_WORDS * sizeof(unsigned))
+         + 2 * pad256((tcl + nc) * sizeof(V2<Real>)) + 1024;
 }
 
 void check_dims(int ncol, int nlay)
@@ -329,6 +335,7 @@ void gas_optics_materialised(rrtmgp_b200_gas_optics* g, int ncol, int nlay, cons
     const size_t tcl = (size_t)ncol * nlay;
     g->ws.reserve(state_bytes<Real>(h, ncol, nlay) + pad256(tcl * sizeof(Real)) + 2 * sizeof(Real) + 512, s);
     TileState<Real> st = carve_state<Real>(g->ws, h, ncol, nlay);
+    st.tmask = nullptr;
     const void* cd = col_dry;
     if (!cd)
     {
@@ -340,7 +347,7 @@ void gas_optics_materialised(rrtmgp_b200_gas_optics* g, int ncol, int nlay, cons
         launch_col_dry<Real>(ncol, nlay, concs->d_vmr[ih], plev, t, s);
         cd = t;
     }
-    launch_interp<Real>(dplan<Real>(g), vmr, ncol, 0, ncol, nlay, play, tlay, cd, st,
+    launch_interp<Real>(dplan<Real>(g), vmr, ncol, 0, ncol, nlay, play, tlay, cd, tlev, st,
                         nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, s);
     if (h.is_lw)
     {
@@ -394,8 +401,8 @@ int rrtmgp_b200_interpolation(const rrtmgp_b200_gas_optics* g, int ncol, int nla
         if (!play || !tlay || !col_dry) throw ArgError("interpolation: null array");
         const VmrArgs vmr = make_vmr(g, concs, ncol, nlay);
         DISPATCH(g->dtype,
-            launch_interp<float>(g->pf, vmr, ncol, 0, ncol, nlay, play, tlay, col_dry, TileState<float>{}, jtemp, jpress, tropo, jeta, col_mix, fminor, fmajor, col_gas, (cudaStream_t)stream),
-            launch_interp<double>(g->pd, vmr, ncol, 0, ncol, nlay, play, tlay, col_dry, TileState<double>{}, jtemp, jpress, tropo, jeta, col_mix, fminor, fmajor, col_gas, (cudaStream_t)stream));
+            launch_interp<float>(g->pf, vmr, ncol, 0, ncol, nlay, play, tlay, col_dry, nullptr, TileState<float>{}, jtemp, jpress, tropo, jeta, col_mix, fminor, fmajor, col_gas, (cudaStream_t)stream),
+            launch_interp<double>(g->pd, vmr, ncol, 0, ncol, nlay, play, tlay, col_dry, nullptr, TileState<double>{}, jtemp, jpress, tropo, jeta, col_mix, fminor, fmajor, col_gas, (cudaStream_t)stream));
     });
 }
 
@@ -693,6 +700,7 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
     if (!cols->d_play || !cols->d_plev || !cols->d_tlay || !out->d_flux_up || !out->d_flux_dn) throw ArgError("fused fluxes: null array");
     if (!sw && (!cols->d_tlev || !cols->d_tsfc || !cols->d_sfc_emis)) throw ArgError("lw_fluxes: tlev, tsfc and sfc_emis are required");
     if (sw && (!cols->d_mu0 || !cols->d_sfc_alb_dir || !cols->d_sfc_alb_dif)) throw ArgError("sw_fluxes: mu0 and surface albedos are required");
+    if (nlay > 32 * TMASK_WORDS) throw ArgError("fused fluxes: at most 256 layers (use the stage calls for taller columns)");
     if (!sw && cols->n_gauss_angles > 1) throw ArgError("lw_fluxes: the fused path supports one Gauss angle; use lw_solver_noscat for 2..4");
     const bool cloud = cols->cloud != nullptr;
     if (cloud)
@@ -766,7 +774,8 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
     {
         const int nc = std::min(tile, ncol - c0);
         st.nc = nc; a.c0 = c0; a.nc = nc;
-        launch_interp<Real>(dplan<Real>(g), vmr, ncol, c0, nc, nlay, cols->d_play, cols->d_tlay, col_dry, st,
+        CK(cudaMemsetAsync(st.tmask, 0, (size_t)nc * TMASK_WORDS * sizeof(unsigned), s));
+        launch_interp<Real>(dplan<Real>(g), vmr, ncol, c0, nc, nlay, cols->d_play, cols->d_tlay, col_dry, cols->d_tlev, st,
                             nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, s);
         if (cloud)
         {

@@ -42,10 +42,10 @@ template<> struct M<float>
     static __device__ __forceinline__ float div(float a, float b) { return a / b; }
 #else
     static __device__ __forceinline__ float exp(float x) { return __expf(x); }
-    static __device__ __forceinline__ float sqrt(float x) { return sqrtf(x); }
+    static __device__ __forceinline__ float sqrt(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
     static __device__ __forceinline__ float div(float a, float b) { return __fdividef(a, b); }
 #endif
-    static __device__ __forceinline__ float rcp(float a) { return __frcp_rn(a); }
+    static __device__ __forceinline__ float rcp(float a) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
     static __device__ __forceinline__ float fabs(float a) { return fabsf(a); }
     static __device__ __forceinline__ float max(float a, float b) { return fmaxf(a, b); }
     static __device__ __forceinline__ float min(float a, float b) { return fminf(a, b); }
@@ -70,9 +70,9 @@ template<> struct M<double>
 // ---- device view of the k-distribution (tables in Real, index grids in double) -------------
 template<typename Real> struct DevPlan
 {
-    int is_lw, ntemp, npres, neta, nbnd, ngpt, nflav, ngas, gw, nplanck, idx_h2o;
-    const Real* kmajor;        // [b][it][ip][ie][gw]
-    const Real* pfrac;         // idem (LW)
+    int is_lw, ntemp, npres, neta, nbnd, ngpt, nflav, ngas, gw, nplanck, idx_h2o, row_stride;
+    const Real* kmajor;        // [b][it][ip][ie][slot][gw], row_stride = (LW ? 2 : 1) * gw
+    const Real* pfrac;         // LW: kmajor + gw (slot 1 of the same rows)
     const Real* krayl;         // [side][b][it][ie][gw] (SW) or null
     const Real* kminor[2];     // [m][it][ie][gw]
     const Real* totplnk;       // [b][nplanck] (LW)
@@ -97,15 +97,24 @@ struct VmrArgs
 
 // ---- per-tile interpolation state produced by the prologue kernel, g-point independent ------
 // All arrays are column-fastest over the tile: index (c + nc*l) [+ nc*nlay*f].
+template<typename Real> struct V2;
+template<> struct alignas(8) V2<float> { float x, y; };
+template<> struct alignas(16) V2<double> { double x, y; };
+
 template<typename Real> struct TileState
 {
     int nc, nlay;            // columns in this tile, layers
     V4<Real>* cell;          // {fpress, dens = 0.01 p/T, vd = vmr_fact*dry_fact, bits}
                              //   bits = jtemp | jpress<<8 | tropo<<16
     V4<Real>* flvA;          // [f]: {col_mix0, col_mix1, fminor(1,1), fminor(2,1)}
-    V4<Real>* flvB;          // [f]: {fminor(1,2), fminor(2,2), bits(jeta0 | jeta1<<8), 0}
+    V4<Real>* flvB;          // [f]: {fminor(1,2), fminor(2,2), rows(itemp 1), rows(itemp 2)}
+                             //   rows = major row | minor row << 20 (row = offset / row stride)
+    V2<Real>* pl_lay;        // LW: Planck table position of tlay {frac, lower index}  (nc, nlay)
+    V2<Real>* pl_lev;        // LW: idem for tlev                                      (nc, nlay+1)
     Real* col_gas;           // [g = 0..ngas]
+    unsigned* tmask;         // [c][TMASK_WORDS]: bit l of a column = tropo(c, l)  (fused path only)
 };
+constexpr int TMASK_WORDS = 8;   // the fused path handles up to 256 layers
 
 struct MinorDev { int idx_minor, idx_scaling, flags, contributor; };   // flags: 1 density, 2 complement
 
@@ -113,6 +122,7 @@ struct BandArgs
 {
     int band, gpt0, ngb;     // 0-based band, first g-point (0-based), g-points in band
     int nminor[2];
+    int first_minor[2];      // device block index of the band's first contributor (blocks are consecutive)
     MinorDev minor[2][MAX_MINOR_DEV];
 };
 

@@ -20,12 +20,14 @@
 
 namespace rb200 {
 
-template<typename Real, int LPC, bool CLOUD>
+template<typename Real, int LPC, bool CLOUD, int NE>
 __global__ void __launch_bounds__(FUSED_THREADS)
 lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const TileState<Real> st,
                const FusedArgs<Real> a)
 {
+    using G = Geo<4 * LPC, NE, true>;
     constexpr int CPB = FUSED_THREADS / LPC;
+    constexpr int T = FUSED_THREADS;
     const int tid = threadIdx.x;
     const int q = tid % LPC, cl = tid / LPC;
     const int craw = blockIdx.x * CPB + cl;
@@ -36,51 +38,66 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     const size_t cg = (size_t)a.c0 + c;                 // column in the caller's arrays
     const int q4 = q * 4;
     const int band = B.band;
-    const size_t band_elems = (size_t)P.ntemp * (P.npres + 1) * P.neta * P.gw;
-    const Real* kmaj = P.kmajor + band_elems * band;
-    const Real* pfr = P.pfrac + band_elems * band + q4;
+    const size_t band_elems = (size_t)P.ntemp * (P.npres + 1) * G::neta(P) * G::RS;
+    const Real* kmaj = P.kmajor + band_elems * band + q4;
     const Real* plk = P.totplnk + (size_t)P.nplanck * band;
-    const int flav[2] = {P.band_flavor[2 * band], P.band_flavor[2 * band + 1]};
-    V4<Real>* scr = a.scratch + (size_t)blockIdx.x * nlay * 2 * FUSED_THREADS + tid;
+    const int flav0 = P.band_flavor[2 * band], flav1 = P.band_flavor[2 * band + 1];
+    const unsigned* tm = st.tmask + (size_t)c * TMASK_WORDS;
+    V4<Real>* const scr = a.scratch + (size_t)blockIdx.x * nlay * 2 * T + tid;
     const Real piw = (Real)3.14159265358979323846 * a.weight;
     const bool lead = active && q == 0;
     const size_t nlev_stride = (size_t)a.ncol * (nlay + 1);
+    const int top = a.top_at_1;
+    const long lstep = top ? (long)a.ncol : -(long)a.ncol;
+    const int tstep = top ? nc : -nc;                                          // same, tile arrays
+    const size_t o_top = cg + (top ? (size_t)0 : (size_t)a.ncol * nlay);       // level index * ncol
 
     Real radn[4] = {0, 0, 0, 0};        // incident diffuse flux = 0 (Radiation_solver.cu passes zeros)
     Real pf_prev[4] = {0, 0, 0, 0}, tau_prev[4] = {0, 0, 0, 0}, lev_top[4] = {0, 0, 0, 0};
     Real blay_prev = 0;
 
-    auto level = [&](int j) { return a.top_at_1 ? j : nlay - j; };
-
     // ---- down-sweep, top of atmosphere -> surface; layer k-1 is finalised at iteration k because
-    // its lower level source needs the Planck fraction of layer k (F90:681-708).
+    // its lower level source needs the Planck fraction of layer k (F90:681-708).  State and
+    // Planck-table positions of the next layer are fetched one iteration ahead.
+    int l = top ? 0 : nlay - 1;                         // current layer, array order
+    const V2<Real>* plev_p = st.pl_lev + (size_t)c + (size_t)nc * (top ? 0 : nlay);
+    RawState<Real> nxt = load_state(st, tm, flav0, flav1, c, l, tcl);
+    V2<Real> play_n = st.pl_lay[(size_t)c + (size_t)nc * l], plev_n = *plev_p;
+    size_t o = o_top;
     for (int k = 0; k <= nlay; ++k)
     {
         Real pf[4] = {0, 0, 0, 0}, tau[4] = {0, 0, 0, 0};
         Real blay = 0;
+        const V2<Real> play_c = play_n, plev_c = plev_n;
+        const RawState<Real> cur = nxt;
         if (k < nlay)
         {
-            const int l = a.top_at_1 ? k : nlay - 1 - k;
+            plev_p += tstep;
+            plev_n = *plev_p;
             const size_t icl = (size_t)c + (size_t)nc * l;
-            const V4<Real> cell = st.cell[icl];
-            const int f = flav[cell_side(cell)];
+            if (k + 1 < nlay)
+            {
+                const int ln = top ? l + 1 : l - 1;
+                nxt = load_state(st, tm, flav0, flav1, c, ln, tcl);
+                play_n = st.pl_lay[(size_t)c + (size_t)nc * ln];
+            }
             Cell<Real> ce;
-            decode_cell(P, cell, st.flvA[icl + tcl * f], st.flvB[icl + tcl * f], ce);
-            Real s0[4], s1[4];
-            gas_tau(P, B, ce, kmaj, q4, st.col_gas, icl, tcl, tau, s0, s1);
+            decode_cell(cur.cell, cur.fa, cur.fb, ce);
+            Real s0[4], s1[4], p0[4], p1[4];
+            interp_major_pair<G>(kmaj, P, ce, s0, s1, p0, p1);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { tau[j] = ce.cm0 * s0[j] + ce.cm1 * s1[j]; pf[j] = p0[j] + p1[j]; }
+            add_minor_tau<G>(P, B, ce, q4, st.col_gas + icl, tcl, tau);
             if (CLOUD)
             {
                 const Real ct = a.cld_tau[icl + tcl * band];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) tau[j] += ct;
             }
-            interp_major(pfr, P, ce, s0, s1);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) pf[j] = s0[j] + s1[j];
-            blay = planck_band(plk, P.nplanck, P.planck_tmin, P.planck_delta, a.tlay[cg + (size_t)a.ncol * l]);
+            blay = planck_at(plk, play_c);
+            l += top ? 1 : -1;
         }
-        const Real blev = planck_band(plk, P.nplanck, P.planck_tmin, P.planck_delta,
-                                      a.tlev[cg + (size_t)a.ncol * level(k)]);
+        const Real blev = planck_at(plk, plev_c);
         if (k == 0)
         {
 #pragma unroll
@@ -100,13 +117,12 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
                 trp[j] = t; sup[j] = s_up;
                 lev_top[j] = lev_bot;
             }
-            scr[(size_t)((k - 1) * 2 + 0) * FUSED_THREADS] = tr;
-            scr[(size_t)((k - 1) * 2 + 1) * FUSED_THREADS] = su;
+            V4<Real>* w = scr + (size_t)(k - 1) * 2 * T;
+            w[0] = tr; w[T] = su;
             const Real s = quad_sum<Real, LPC>(radn) * piw;
             if (lead)
             {
-                const size_t o = cg + (size_t)a.ncol * level(k);
-                a.flux_dn[o] += s;
+                atomicAdd(a.flux_dn + o, s);
                 if (a.bnd_dn) a.bnd_dn[o + nlev_stride * band] = s;
             }
         }
@@ -115,6 +131,7 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
 #pragma unroll
             for (int j = 0; j < 4; ++j) { pf_prev[j] = pf[j]; tau_prev[j] = tau[j]; }
             blay_prev = blay;
+            o += lstep;
         }
     }
 
@@ -127,24 +144,35 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
         const Real s = quad_sum<Real, LPC>(radn) * piw;
         if (lead)
         {
-            const size_t o = cg + (size_t)a.ncol * level(nlay);
-            a.flux_up[o] += s;
+            atomicAdd(a.flux_up + o, s);
             if (a.bnd_up) a.bnd_up[o + nlev_stride * band] = s;
         }
     }
-    // ---- up-sweep, surface -> top (F90:710-745), state read back LIFO
-    for (int k = nlay - 1; k >= 0; --k)
+    // ---- up-sweep, surface -> top (F90:710-745): the parked {trans, source_up} come back LIFO in
+    // chunks of 4 layers (8 independent vector loads in flight per thread)
+    for (int k0 = nlay - 1; k0 >= 0; k0 -= 4)
     {
-        const V4<Real> tr = scr[(size_t)(k * 2 + 0) * FUSED_THREADS];
-        const V4<Real> su = scr[(size_t)(k * 2 + 1) * FUSED_THREADS];
-        radn[0] = fma(tr.x, radn[0], su.x); radn[1] = fma(tr.y, radn[1], su.y);
-        radn[2] = fma(tr.z, radn[2], su.z); radn[3] = fma(tr.w, radn[3], su.w);
-        const Real s = quad_sum<Real, LPC>(radn) * piw;
-        if (lead)
+        V4<Real> tr[4], su[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
         {
-            const size_t o = cg + (size_t)a.ncol * level(k);
-            a.flux_up[o] += s;
-            if (a.bnd_up) a.bnd_up[o + nlev_stride * band] = s;
+            const int k = max(k0 - u, 0);
+            const V4<Real>* w = scr + (size_t)k * 2 * T;
+            tr[u] = w[0]; su[u] = w[T];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+        {
+            if (k0 - u < 0) break;
+            radn[0] = fma(tr[u].x, radn[0], su[u].x); radn[1] = fma(tr[u].y, radn[1], su[u].y);
+            radn[2] = fma(tr[u].z, radn[2], su[u].z); radn[3] = fma(tr[u].w, radn[3], su[u].w);
+            const Real s = quad_sum<Real, LPC>(radn) * piw;
+            o -= lstep;
+            if (lead)
+            {
+                atomicAdd(a.flux_up + o, s);
+                if (a.bnd_up) a.bnd_up[o + nlev_stride * band] = s;
+            }
         }
     }
 }
@@ -163,16 +191,12 @@ void launch_lw_band(const DevPlan<Real>& P, const BandArgs& B, const TileState<R
     const int lpc = P.gw / 4, cpb = FUSED_THREADS / lpc;
     const unsigned grid = (unsigned)((a.nc + cpb - 1) / cpb);
     const bool cloud = a.cld_tau != nullptr;
-    if (lpc == 4)
-    {
-        if (cloud) lw_band_kernel<Real, 4, true><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, a);
-        else lw_band_kernel<Real, 4, false><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, a);
-    }
-    else
-    {
-        if (cloud) lw_band_kernel<Real, 2, true><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, a);
-        else lw_band_kernel<Real, 2, false><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, a);
-    }
+#define RB_LAUNCH(LPC_, CL_, NE_) lw_band_kernel<Real, LPC_, CL_, NE_><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, a)
+#define RB_NE(LPC_, CL_) { if (P.neta == 9) RB_LAUNCH(LPC_, CL_, 9); else RB_LAUNCH(LPC_, CL_, 0); }
+    if (lpc == 4) { if (cloud) RB_NE(4, true) else RB_NE(4, false) }
+    else { if (cloud) RB_NE(2, true) else RB_NE(2, false) }
+#undef RB_NE
+#undef RB_LAUNCH
     count_launch();
 }
 
@@ -186,8 +210,8 @@ template<typename Real> int lw_blocks_per_wave(int gw)
     int dev = 0, sms = 0, occ = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (gw == 16) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, lw_band_kernel<Real, 4, false>, FUSED_THREADS, 0);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, lw_band_kernel<Real, 2, false>, FUSED_THREADS, 0);
+    if (gw == 16) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, lw_band_kernel<Real, 4, false, 9>, FUSED_THREADS, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, lw_band_kernel<Real, 2, false, 9>, FUSED_THREADS, 0);
     return sms * occ;
 }
 template int lw_blocks_per_wave<float>(int);

@@ -17,12 +17,14 @@
 
 namespace rb200 {
 
-template<typename Real, int LPC, bool CLOUD>
+template<typename Real, int LPC, bool CLOUD, int NE>
 __global__ void __launch_bounds__(FUSED_THREADS)
 sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const TileState<Real> st,
                const FusedArgs<Real> a)
 {
+    using G = Geo<4 * LPC, NE, false>;
     constexpr int CPB = FUSED_THREADS / LPC;
+    constexpr int T = FUSED_THREADS;
     const int tid = threadIdx.x;
     const int q = tid % LPC, cl = tid / LPC;
     const int craw = blockIdx.x * CPB + cl;
@@ -33,14 +35,20 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     const size_t cg = (size_t)a.c0 + c;
     const int q4 = q * 4;
     const int band = B.band;
-    const size_t band_elems = (size_t)P.ntemp * (P.npres + 1) * P.neta * P.gw;
-    const size_t ray_elems = (size_t)P.ntemp * P.neta * P.gw;
-    const Real* kmaj = P.kmajor + band_elems * band;
-    const int flav[2] = {P.band_flavor[2 * band], P.band_flavor[2 * band + 1]};
-    V4<Real>* scr = a.scratch + (size_t)blockIdx.x * nlay * 4 * FUSED_THREADS + tid;
+    const size_t band_elems = (size_t)P.ntemp * (P.npres + 1) * G::neta(P) * G::RS;
+    const size_t ray_elems = (size_t)P.ntemp * G::neta(P) * G::GW;
+    const Real* kmaj = P.kmajor + band_elems * band + q4;
+    const Real* kray = P.krayl ? P.krayl + ray_elems * band + q4 : nullptr;
+    const size_t ray_side = ray_elems * P.nbnd;
+    const int flav0 = P.band_flavor[2 * band], flav1 = P.band_flavor[2 * band + 1];
+    const unsigned* tm = st.tmask + (size_t)c * TMASK_WORDS;
+    V4<Real>* const scr = a.scratch + (size_t)blockIdx.x * nlay * 4 * T + tid;
     const bool lead = active && q == 0;
     const size_t nlev_stride = (size_t)a.ncol * (nlay + 1);
-    auto level = [&](int j) { return a.top_at_1 ? j : nlay - j; };
+    const int top = a.top_at_1;
+    // level j / layer k counted from the top of the atmosphere -> array index, times ncol
+    const long lstep = top ? (long)a.ncol : -(long)a.ncol;
+    const size_t o_top = cg + (top ? (size_t)0 : (size_t)a.ncol * nlay);
 
     const Real mu0 = a.mu0[cg];
     const Real mu0s = M<Real>::max(M<Real>::sqrt(M<Real>::eps), mu0);
@@ -59,27 +67,30 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
         const Real s = quad_sum<Real, LPC>(dir);
         if (lead)
         {
-            const size_t o = cg + (size_t)a.ncol * level(0);
-            a.flux_dir[o] += s; a.flux_dn[o] += s;
-            if (a.bnd_dir) a.bnd_dir[o + nlev_stride * band] = s;
+            atomicAdd(a.flux_dir + o_top, s); atomicAdd(a.flux_dn + o_top, s);
+            if (a.bnd_dir) a.bnd_dir[o_top + nlev_stride * band] = s;
         }
     }
 
-    // ---- pass 1
+    // ---- pass 1: optics + two-stream + direct beam, top -> surface.  The next layer's state is
+    // fetched one iteration ahead (its address does not depend on loaded data: the flavor comes
+    // from the column's tropopause bit mask).
+    RawState<Real> nxt = load_state(st, tm, flav0, flav1, c, top ? 0 : nlay - 1, tcl);
+    size_t o = o_top;
     for (int k = 0; k < nlay; ++k)
     {
-        const int l = a.top_at_1 ? k : nlay - 1 - k;
+        const int l = top ? k : nlay - 1 - k;
         const size_t icl = (size_t)c + (size_t)nc * l;
-        const V4<Real> cell = st.cell[icl];
-        const int f = flav[cell_side(cell)];
+        const RawState<Real> cur = nxt;
+        if (k + 1 < nlay) nxt = load_state(st, tm, flav0, flav1, c, top ? k + 1 : nlay - 2 - k, tcl);
         Cell<Real> ce;
-        decode_cell(P, cell, st.flvA[icl + tcl * f], st.flvB[icl + tcl * f], ce);
-        Real tau[4], s0[4], s1[4];
-        gas_tau(P, B, ce, kmaj, q4, st.col_gas, icl, tcl, tau, s0, s1);
+        decode_cell(cur.cell, cur.fa, cur.fb, ce);
+        Real tau[4];
+        gas_tau<G>(P, B, ce, kmaj, q4, st.col_gas + icl, tcl, tau);
         Real ray[4] = {0, 0, 0, 0};
-        if (P.krayl)
+        if (kray)
         {
-            interp_minor(P.krayl + ray_elems * ((size_t)ce.side * P.nbnd + band) + q4, P, ce, ray);
+            interp_minor<G>(kray + (ce.side ? ray_side : 0), ce, ray);
             const Real wet = st.col_gas[icl + tcl * P.idx_h2o] + st.col_gas[icl];
 #pragma unroll
             for (int j = 0; j < 4; ++j) ray[j] *= wet;
@@ -101,20 +112,18 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
             p3[j] = sun ? Tdir * dir[j] : (Real)0;     // source_dn
             dir[j] = Tnoscat * dir[j];
         }
-        scr[(size_t)(k * 4 + 0) * FUSED_THREADS] = v0;
-        scr[(size_t)(k * 4 + 1) * FUSED_THREADS] = v1;
-        scr[(size_t)(k * 4 + 2) * FUSED_THREADS] = v2;
-        scr[(size_t)(k * 4 + 3) * FUSED_THREADS] = v3;
+        V4<Real>* w = scr + (size_t)k * 4 * T;
+        w[0] = v0; w[T] = v1; w[2 * T] = v2; w[3 * T] = v3;
         const Real s = quad_sum<Real, LPC>(dir);
+        o += lstep;
         if (lead)
         {
-            const size_t o = cg + (size_t)a.ncol * level(k + 1);
-            a.flux_dir[o] += s; a.flux_dn[o] += s;
+            atomicAdd(a.flux_dir + o, s); atomicAdd(a.flux_dn + o, s);
             if (a.bnd_dir) a.bnd_dir[o + nlev_stride * band] = s;
         }
     }
 
-    // ---- pass 2: adding, surface -> top (F90:1135-1245)
+    // ---- pass 2: adding, surface -> top (F90:1135-1245); scratch read one layer ahead
     Real alb[4], src[4];
     {
         const Real adir = a.alb_dir[band + (size_t)P.nbnd * cg];
@@ -122,57 +131,77 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
 #pragma unroll
         for (int j = 0; j < 4; ++j) { alb[j] = adif; src[j] = sun ? dir[j] * adir : (Real)0; }
     }
-    for (int k = nlay - 1; k >= 0; --k)
+    for (int k0 = nlay - 1; k0 >= 0; k0 -= 2)
     {
-        const V4<Real> v0 = scr[(size_t)(k * 4 + 0) * FUSED_THREADS], v1 = scr[(size_t)(k * 4 + 1) * FUSED_THREADS];
-        const V4<Real> v2 = scr[(size_t)(k * 4 + 2) * FUSED_THREADS], v3 = scr[(size_t)(k * 4 + 3) * FUSED_THREADS];
-        const Real* rdif = &v0.x; const Real* tdif = &v1.x; const Real* sup = &v2.x; const Real* sdn = &v3.x;
-        V4<Real> oa, ob, oc, od;
-        Real* pa = &oa.x; Real* pb = &ob.x; Real* pc = &oc.x; Real* pd = &od.x;
+        V4<Real> in[2][4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
+        for (int u = 0; u < 2; ++u)
         {
-            const Real denom = M<Real>::rcp((Real)1 - rdif[j] * alb[j]);
-            pa[j] = tdif[j] * denom;
-            pb[j] = (rdif[j] * src[j] + sdn[j]) * denom;
-            pc[j] = alb[j]; pd[j] = src[j];
-            const Real nsrc = sup[j] + tdif[j] * denom * (src[j] + alb[j] * sdn[j]);
-            alb[j] = rdif[j] + tdif[j] * tdif[j] * alb[j] * denom;
-            src[j] = nsrc;
+            const V4<Real>* w = scr + (size_t)max(k0 - u, 0) * 4 * T;
+            in[u][0] = w[0]; in[u][1] = w[T]; in[u][2] = w[2 * T]; in[u][3] = w[3 * T];
         }
-        scr[(size_t)(k * 4 + 0) * FUSED_THREADS] = oa;
-        scr[(size_t)(k * 4 + 1) * FUSED_THREADS] = ob;
-        scr[(size_t)(k * 4 + 2) * FUSED_THREADS] = oc;
-        scr[(size_t)(k * 4 + 3) * FUSED_THREADS] = od;
+#pragma unroll
+        for (int u = 0; u < 2; ++u)
+        {
+            if (k0 - u < 0) break;
+            const Real* rdif = &in[u][0].x; const Real* tdif = &in[u][1].x; const Real* sup = &in[u][2].x; const Real* sdn = &in[u][3].x;
+            V4<Real> oa, ob, oc, od;
+            Real* pa = &oa.x; Real* pb = &ob.x; Real* pc = &oc.x; Real* pd = &od.x;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+            {
+                const Real denom = M<Real>::rcp((Real)1 - rdif[j] * alb[j]);
+                const Real td = tdif[j] * denom;
+                pa[j] = td;
+                pb[j] = (rdif[j] * src[j] + sdn[j]) * denom;
+                pc[j] = alb[j]; pd[j] = src[j];
+                const Real nsrc = sup[j] + td * (src[j] + alb[j] * sdn[j]);
+                alb[j] = rdif[j] + tdif[j] * td * alb[j];
+                src[j] = nsrc;
+            }
+            V4<Real>* wc = scr + (size_t)(k0 - u) * 4 * T;
+            wc[0] = oa; wc[T] = ob; wc[2 * T] = oc; wc[3 * T] = od;
+        }
     }
 
     // ---- pass 3: fluxes, top -> surface; diffuse flux_dn(top) = 0 (no inc_flux_dif)
     Real fdn[4] = {0, 0, 0, 0}, fup[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) fup[j] = fdn[j] * alb[j] + src[j];
+    o = o_top;
     {
         const Real su = quad_sum<Real, LPC>(fup);
         if (lead)
         {
-            const size_t o = cg + (size_t)a.ncol * level(0);
-            a.flux_up[o] += su;
+            atomicAdd(a.flux_up + o, su);
             if (a.bnd_up) { a.bnd_up[o + nlev_stride * band] = su; a.bnd_dn[o + nlev_stride * band] = a.bnd_dir[o + nlev_stride * band]; }
         }
     }
-    for (int k = 0; k < nlay; ++k)
+    for (int k0 = 0; k0 < nlay; k0 += 4)
     {
-        const V4<Real> va = scr[(size_t)(k * 4 + 0) * FUSED_THREADS], vb = scr[(size_t)(k * 4 + 1) * FUSED_THREADS];
-        const V4<Real> vc = scr[(size_t)(k * 4 + 2) * FUSED_THREADS], vd = scr[(size_t)(k * 4 + 3) * FUSED_THREADS];
-        fdn[0] = fma(va.x, fdn[0], vb.x); fdn[1] = fma(va.y, fdn[1], vb.y);
-        fdn[2] = fma(va.z, fdn[2], vb.z); fdn[3] = fma(va.w, fdn[3], vb.w);
-        fup[0] = fma(fdn[0], vc.x, vd.x); fup[1] = fma(fdn[1], vc.y, vd.y);
-        fup[2] = fma(fdn[2], vc.z, vd.z); fup[3] = fma(fdn[3], vc.w, vd.w);
-        const Real su = quad_sum<Real, LPC>(fup), sd = quad_sum<Real, LPC>(fdn);
-        if (lead)
+        V4<Real> in[4][4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
         {
-            const size_t o = cg + (size_t)a.ncol * level(k + 1);
-            a.flux_up[o] += su; a.flux_dn[o] += sd;
-            if (a.bnd_up) { a.bnd_up[o + nlev_stride * band] = su; a.bnd_dn[o + nlev_stride * band] = sd + a.bnd_dir[o + nlev_stride * band]; }
+            const V4<Real>* w = scr + (size_t)min(k0 + u, nlay - 1) * 4 * T;
+            in[u][0] = w[0]; in[u][1] = w[T]; in[u][2] = w[2 * T]; in[u][3] = w[3 * T];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+        {
+            if (k0 + u >= nlay) break;
+            const V4<Real> va = in[u][0], vb = in[u][1], vc = in[u][2], vd = in[u][3];
+            fdn[0] = fma(va.x, fdn[0], vb.x); fdn[1] = fma(va.y, fdn[1], vb.y);
+            fdn[2] = fma(va.z, fdn[2], vb.z); fdn[3] = fma(va.w, fdn[3], vb.w);
+            fup[0] = fma(fdn[0], vc.x, vd.x); fup[1] = fma(fdn[1], vc.y, vd.y);
+            fup[2] = fma(fdn[2], vc.z, vd.z); fup[3] = fma(fdn[3], vc.w, vd.w);
+            const Real su = quad_sum<Real, LPC>(fup), sd = quad_sum<Real, LPC>(fdn);
+            o += lstep;
+            if (lead)
+            {
+                atomicAdd(a.flux_up + o, su); atomicAdd(a.flux_dn + o, sd);
+                if (a.bnd_up) { a.bnd_up[o + nlev_stride * band] = su; a.bnd_dn[o + nlev_stride * band] = sd + a.bnd_dir[o + nlev_stride * band]; }
+            }
         }
     }
 }
@@ -184,16 +213,12 @@ void launch_sw_band(const DevPlan<Real>& P, const BandArgs& B, const TileState<R
     const int lpc = P.gw / 4, cpb = FUSED_THREADS / lpc;
     const unsigned grid = (unsigned)((a.nc + cpb - 1) / cpb);
     const bool cloud = a.cld_tau != nullptr;
-    if (lpc == 4)
-    {
-        if (cloud) sw_band_kernel<Real, 4, true><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, a);
-        else sw_band_kernel<Real, 4, false><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, a);
-    }
-    else
-    {
-        if (cloud) sw_band_kernel<Real, 2, true><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, a);
-        else sw_band_kernel<Real, 2, false><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, a);
-    }
+#define RB_LAUNCH(LPC_, CL_, NE_) sw_band_kernel<Real, LPC_, CL_, NE_><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, a)
+#define RB_NE(LPC_, CL_) { if (P.neta == 9) RB_LAUNCH(LPC_, CL_, 9); else RB_LAUNCH(LPC_, CL_, 0); }
+    if (lpc == 4) { if (cloud) RB_NE(4, true) else RB_NE(4, false) }
+    else { if (cloud) RB_NE(2, true) else RB_NE(2, false) }
+#undef RB_NE
+#undef RB_LAUNCH
     count_launch();
 }
 
@@ -205,8 +230,8 @@ template<typename Real> int sw_blocks_per_wave(int gw)
     int dev = 0, sms = 0, occ = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (gw == 16) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sw_band_kernel<Real, 4, false>, FUSED_THREADS, 0);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sw_band_kernel<Real, 2, false>, FUSED_THREADS, 0);
+    if (gw == 16) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sw_band_kernel<Real, 4, false, 9>, FUSED_THREADS, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sw_band_kernel<Real, 2, false, 9>, FUSED_THREADS, 0);
     return sms * occ;
 }
 template int sw_blocks_per_wave<float>(int);

@@ -9,11 +9,12 @@
 
 namespace rb200 {
 
-template<typename Real, int LPC>
+template<typename Real, int LPC, bool LW>
 __global__ void __launch_bounds__(FUSED_THREADS)
 gas_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const TileState<Real> st,
                 int ncol, int nlay, const GasOut<Real> o)
 {
+    using G = Geo<4 * LPC, 0, LW>;
     constexpr int CPB = FUSED_THREADS / LPC;
     const int tid = threadIdx.x;
     const int q = tid % LPC, cl = tid / LPC;
@@ -22,11 +23,11 @@ gas_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const
     const size_t ncl = (size_t)ncol * nlay, ncv = (size_t)ncol * (nlay + 1);
     const int q4 = q * 4;
     const int band = B.band;
-    const size_t band_elems = (size_t)P.ntemp * (P.npres + 1) * P.neta * P.gw;
-    const size_t ray_elems = (size_t)P.ntemp * P.neta * P.gw;
-    const Real* kmaj = P.kmajor + band_elems * band;
+    const size_t band_elems = (size_t)P.ntemp * (P.npres + 1) * P.neta * G::RS;
+    const size_t ray_elems = (size_t)P.ntemp * P.neta * G::GW;
+    const Real* kmaj = P.kmajor + band_elems * band + q4;
     const int flav[2] = {P.band_flavor[2 * band], P.band_flavor[2 * band + 1]};
-    const bool lw = o.lay_src != nullptr;
+    constexpr bool lw = LW;
     const Real* plk = lw ? P.totplnk + (size_t)P.nplanck * band : nullptr;
     int nvalid = B.ngb - q4; nvalid = nvalid < 0 ? 0 : (nvalid > 4 ? 4 : nvalid);
     const int g0 = B.gpt0 + q4;
@@ -38,13 +39,13 @@ gas_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const
         const V4<Real> cell = st.cell[icl];
         const int f = flav[cell_side(cell)];
         Cell<Real> ce;
-        decode_cell(P, cell, st.flvA[icl + ncl * f], st.flvB[icl + ncl * f], ce);
+        decode_cell(cell, st.flvA[icl + ncl * f], st.flvB[icl + ncl * f], ce);
         Real tau[4], s0[4], s1[4];
-        gas_tau(P, B, ce, kmaj, q4, st.col_gas, icl, ncl, tau, s0, s1);
+        gas_tau<G>(P, B, ce, kmaj, q4, st.col_gas + icl, ncl, tau);
         if (lw)
         {
             Real pf[4];
-            interp_major(P.pfrac + band_elems * band + q4, P, ce, s0, s1);
+            interp_major<G>(P.pfrac + band_elems * band + q4, P, ce, s0, s1);
             const Real blay = planck_band(plk, P.nplanck, P.planck_tmin, P.planck_delta, o.tlay[icl]);
             const Real blev = planck_band(plk, P.nplanck, P.planck_tmin, P.planck_delta, o.tlev[icl]);
             for (int j = 0; j < nvalid; ++j)
@@ -74,7 +75,7 @@ gas_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const
             Real ray[4] = {0, 0, 0, 0};
             if (P.krayl)
             {
-                interp_minor(P.krayl + ray_elems * ((size_t)ce.side * P.nbnd + band) + q4, P, ce, ray);
+                interp_minor<G>(P.krayl + ray_elems * ((size_t)ce.side * P.nbnd + band) + q4, ce, ray);
                 const Real wet = st.col_gas[icl + ncl * P.idx_h2o] + st.col_gas[icl];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) ray[j] *= wet;
@@ -101,8 +102,11 @@ void launch_gas_band(const DevPlan<Real>& P, const BandArgs& B, const TileState<
 {
     const int lpc = P.gw / 4, cpb = FUSED_THREADS / lpc;
     const unsigned grid = (unsigned)((ncol + cpb - 1) / cpb);
-    if (lpc == 4) gas_band_kernel<Real, 4><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, ncol, nlay, o);
-    else gas_band_kernel<Real, 2><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, ncol, nlay, o);
+    const bool lw = o.lay_src != nullptr;
+    if (lpc == 4) { if (lw) gas_band_kernel<Real, 4, true><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, ncol, nlay, o);
+                    else gas_band_kernel<Real, 4, false><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, ncol, nlay, o); }
+    else { if (lw) gas_band_kernel<Real, 2, true><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, ncol, nlay, o);
+           else gas_band_kernel<Real, 2, false><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, ncol, nlay, o); }
     count_launch();
 }
 

@@ -47,7 +47,8 @@ template<typename Real>
 __global__ void __launch_bounds__(128)
 interp_kernel(const DevPlan<Real> P, const VmrArgs vmr, int ncol, int c0, int nc, int nlay,
               const Real* __restrict__ play, const Real* __restrict__ tlay,
-              const Real* __restrict__ col_dry, TileState<Real> st, RefInterpOut<Real> ro)
+              const Real* __restrict__ col_dry, const Real* __restrict__ tlev,
+              TileState<Real> st, RefInterpOut<Real> ro)
 {
     const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (size_t)nc * nlay) return;
@@ -91,6 +92,20 @@ interp_kernel(const DevPlan<Real> P, const VmrArgs vmr, int ncol, int c0, int nc
         rec.z = (Real)(vmr_fact * dry_fact);
         rec.w = M<Real>::from_int(jt | (jp << 8) | (tropo << 16));
         st.cell[it] = rec;
+        if (st.pl_lay && tlev)
+        {
+            // interpolate1D position in totplnk (F90:715-734), band independent
+            auto pos = [&](Real T) {
+                const Real val0 = (T - P.planck_tmin) / P.planck_delta;
+                const int iv = (int)val0;
+                const int index = min(P.nplanck - 1, max(1, iv + 1));
+                return V2<Real>{val0 - (Real)iv, M<Real>::from_int(index - 1)};
+            };
+            st.pl_lay[it] = pos(tlay[i]);
+            st.pl_lev[it] = pos(tlev[i]);
+            if (l == nlay - 1) st.pl_lev[it + nc] = pos(tlev[i + ncol]);
+        }
+        if (st.tmask && tropo) atomicOr(&st.tmask[(size_t)c * TMASK_WORDS + (l >> 5)], 1u << (l & 31));
     }
 
     // F90:127-169
@@ -136,7 +151,12 @@ interp_kernel(const DevPlan<Real> P, const VmrArgs vmr, int ncol, int c0, int nc
         {
             const size_t k = it + tcl * f;
             st.flvA[k] = V4<Real>{(Real)cm[0], (Real)cm[1], (Real)fm[0][0], (Real)fm[0][1]};
-            st.flvB[k] = V4<Real>{(Real)fm[1][0], (Real)fm[1][1], M<Real>::from_int(je[0] | (je[1] << 8)), (Real)0};
+            const int ip0 = jp + side - 1;     // 0-based lower pressure row (Fortran jpress+itropo-1)
+            const int maj0 = ((jt - 1) * (P.npres + 1) + ip0) * P.neta + (je[0] - 1);
+            const int maj1 = (jt * (P.npres + 1) + ip0) * P.neta + (je[1] - 1);
+            const int min0 = (jt - 1) * P.neta + (je[0] - 1), min1 = jt * P.neta + (je[1] - 1);
+            st.flvB[k] = V4<Real>{(Real)fm[1][0], (Real)fm[1][1], M<Real>::from_int(maj0 | (min0 << 20)),
+                                  M<Real>::from_int(maj1 | (min1 << 20))};
         }
     }
 }
@@ -152,21 +172,22 @@ void launch_col_dry(int ncol, int nlay, const void* vmr_h2o, const void* plev, v
 
 template<typename Real>
 void launch_interp(const DevPlan<Real>& P, const VmrArgs& vmr, int ncol, int c0, int nc, int nlay,
-                   const void* play, const void* tlay, const void* col_dry, const TileState<Real>& st,
-                   int* jtemp, int* jpress, signed char* tropo, int* jeta, void* col_mix,
+                   const void* play, const void* tlay, const void* col_dry, const void* tlev,
+                   const TileState<Real>& st, int* jtemp, int* jpress, signed char* tropo, int* jeta, void* col_mix,
                    void* fminor, void* fmajor, void* col_gas, cudaStream_t s)
 {
     RefInterpOut<Real> ro{jtemp, jpress, tropo, jeta, (Real*)col_mix, (Real*)fminor, (Real*)fmajor, (Real*)col_gas};
     const size_t n = (size_t)nc * nlay;
     interp_kernel<Real><<<(unsigned)((n + 127) / 128), 128, 0, s>>>(
-            P, vmr, ncol, c0, nc, nlay, (const Real*)play, (const Real*)tlay, (const Real*)col_dry, st, ro);
+            P, vmr, ncol, c0, nc, nlay, (const Real*)play, (const Real*)tlay, (const Real*)col_dry,
+            (const Real*)tlev, st, ro);
     count_launch();
 }
 
 #define INST(Real) \
     template void launch_col_dry<Real>(int, int, const void*, const void*, void*, cudaStream_t); \
     template void launch_interp<Real>(const DevPlan<Real>&, const VmrArgs&, int, int, int, int, const void*, \
-        const void*, const void*, const TileState<Real>&, int*, int*, signed char*, int*, void*, void*, void*, void*, cudaStream_t);
+        const void*, const void*, const void*, const TileState<Real>&, int*, int*, signed char*, int*, void*, void*, void*, void*, cudaStream_t);
 INST(float)
 INST(double)
 #undef INST

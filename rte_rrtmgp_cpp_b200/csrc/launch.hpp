@@ -12,8 +12,8 @@ template<typename Real>
 void launch_col_dry(int ncol, int nlay, const void* vmr_h2o, const void* plev, void* col_dry, cudaStream_t s);
 template<typename Real>
 void launch_interp(const DevPlan<Real>& P, const VmrArgs& vmr, int ncol, int c0, int nc, int nlay,
-                   const void* play, const void* tlay, const void* col_dry, const TileState<Real>& st,
-                   int* jtemp, int* jpress, signed char* tropo, int* jeta, void* col_mix,
+                   const void* play, const void* tlay, const void* col_dry, const void* tlev,
+                   const TileState<Real>& st, int* jtemp, int* jpress, signed char* tropo, int* jeta, void* col_mix,
                    void* fminor, void* fmajor, void* col_gas, cudaStream_t s);
 
 // ---- fused_lw.cu / fused_sw.cu : one launch = one band of one column tile

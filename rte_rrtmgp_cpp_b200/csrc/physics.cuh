@@ -7,6 +7,15 @@
 
 namespace rb200 {
 
+// Compile-time table geometry of a kernel instantiation: GW padded g-points per band,
+// NE mixing-fraction points (0 = take it from the plan at run time), RS row stride in elements
+// (2*GW when planck_frac rows are interleaved with kmajor rows, GW otherwise).
+template<int GW_, int NE_, bool LW_> struct Geo
+{
+    static constexpr int GW = GW_, NE = NE_, RS = LW_ ? 2 * GW_ : GW_;
+    template<typename Real> static __device__ __forceinline__ int neta(const DevPlan<Real>& P) { return NE_ > 0 ? NE_ : P.neta; }
+};
+
 // decoded (column, layer, band) interpolation state
 template<typename Real> struct Cell
 {
@@ -14,8 +23,8 @@ template<typename Real> struct Cell
     Real fm[4];       // fminor: [it*2 + ie]
     Real cm0, cm1;    // col_mix
     Real dens, vd;    // 0.01 p/T ; vmr_fact*dry_fact
-    int maj0, maj1;   // element offsets of the (it, ip=0, ie=0) rows in a band's major block
-    int min0, min1;   // element offsets of the (it, ie=0) rows in a contributor / Rayleigh block
+    int maj0, maj1;   // row numbers of the (it, ip=0, ie=0) corners in a band's major block
+    int min0, min1;   // row numbers of the (it, ie=0) corners in a contributor / Rayleigh block
     int side;         // 0 lower (tropo), 1 upper
 };
 
@@ -23,88 +32,134 @@ template<typename Real>
 __device__ __forceinline__ int cell_side(const V4<Real>& cell) { return ((M<Real>::as_int(cell.w) >> 16) & 1) ? 0 : 1; }
 
 template<typename Real>
-__device__ __forceinline__ void decode_cell(const DevPlan<Real>& P, const V4<Real>& cell,
-                                            const V4<Real>& fa, const V4<Real>& fb, Cell<Real>& o)
+__device__ __forceinline__ void decode_cell(const V4<Real>& cell, const V4<Real>& fa, const V4<Real>& fb, Cell<Real>& o)
 {
-    const int bits = M<Real>::as_int(cell.w);
-    const int jt = bits & 0xff, jp = (bits >> 8) & 0xff;
-    o.side = ((bits >> 16) & 1) ? 0 : 1;
-    const int jb = M<Real>::as_int(fb.z);
-    const int je0 = jb & 0xff, je1 = (jb >> 8) & 0xff;
+    o.side = cell_side(cell);
+    const int r0 = M<Real>::as_int(fb.z), r1 = M<Real>::as_int(fb.w);
+    o.maj0 = r0 & 0xfffff; o.min0 = (r0 >> 20) & 0xfff;
+    o.maj1 = r1 & 0xfffff; o.min1 = (r1 >> 20) & 0xfff;
     const Real fpress = cell.x, omf = (Real)1 - fpress;
     o.dens = cell.y; o.vd = cell.z;
     o.cm0 = fa.x; o.cm1 = fa.y;
     o.fm[0] = fa.z; o.fm[1] = fa.w; o.fm[2] = fb.x; o.fm[3] = fb.y;
     o.w[0] = omf * o.fm[0]; o.w[1] = omf * o.fm[1]; o.w[2] = fpress * o.fm[0]; o.w[3] = fpress * o.fm[1];
     o.w[4] = omf * o.fm[2]; o.w[5] = omf * o.fm[3]; o.w[6] = fpress * o.fm[2]; o.w[7] = fpress * o.fm[3];
-    const int ip0 = jp + o.side - 1;   // 0-based lower pressure row (Fortran jpress+itropo-1)
-    o.maj0 = (((jt - 1) * (P.npres + 1) + ip0) * P.neta + (je0 - 1)) * P.gw;
-    o.maj1 = (((jt) * (P.npres + 1) + ip0) * P.neta + (je1 - 1)) * P.gw;
-    o.min0 = ((jt - 1) * P.neta + (je0 - 1)) * P.gw;
-    o.min1 = ((jt) * P.neta + (je1 - 1)) * P.gw;
+}
+
+// raw per-(column, layer) state of one band: what the prologue kernel left in HBM
+template<typename Real> struct RawState { V4<Real> cell, fa, fb; };
+
+// flavor of layer l from the column's tropopause bit mask (no dependent load on `cell`)
+__device__ __forceinline__ int layer_side(const unsigned* __restrict__ tm, int l)
+{
+    return ((__ldg(tm + (l >> 5)) >> (l & 31)) & 1u) ? 0 : 1;
+}
+
+template<typename Real>
+__device__ __forceinline__ RawState<Real> load_state(const TileState<Real>& st, const unsigned* tm, int flav0, int flav1,
+                                                    int c, int l, size_t tcl)
+{
+    const size_t icl = (size_t)c + (size_t)st.nc * l;
+    const int f = layer_side(tm, l) == 0 ? flav0 : flav1;
+    RawState<Real> r;
+    r.cell = st.cell[icl];
+    r.fa = st.flvA[icl + tcl * f];
+    r.fb = st.flvB[icl + tcl * f];
+    return r;
 }
 
 #define RB_FMA4(acc, s, v) { acc[0] = fma(s, v.x, acc[0]); acc[1] = fma(s, v.y, acc[1]); acc[2] = fma(s, v.z, acc[2]); acc[3] = fma(s, v.w, acc[3]); }
+#define RB_MUL4(acc, s, v) { acc[0] = s * v.x; acc[1] = s * v.y; acc[2] = s * v.z; acc[3] = s * v.w; }
 
-// interpolate3D_byflav (mo_gas_optics_rrtmgp_kernels.F90:760-789): partial sums per temperature
-template<typename Real>
+// interpolate3D_byflav (mo_gas_optics_rrtmgp_kernels.F90:760-789): partial sums per temperature.
+// `tab` points at the band block (+ slot and quad offset); with G::NE > 0 the 4 corners of a
+// temperature are at compile-time byte offsets from one computed address.
+template<typename G, typename Real>
 __device__ __forceinline__ void interp_major(const Real* __restrict__ tab, const DevPlan<Real>& P,
                                              const Cell<Real>& c, Real (&s0)[4], Real (&s1)[4])
 {
-    const int de = P.gw, dp = P.neta * P.gw;
-    const V4<Real> a0 = ldg4(tab + c.maj0), a1 = ldg4(tab + c.maj0 + de);
-    const V4<Real> a2 = ldg4(tab + c.maj0 + dp), a3 = ldg4(tab + c.maj0 + dp + de);
-    const V4<Real> b0 = ldg4(tab + c.maj1), b1 = ldg4(tab + c.maj1 + de);
-    const V4<Real> b2 = ldg4(tab + c.maj1 + dp), b3 = ldg4(tab + c.maj1 + dp + de);
-    s0[0] = c.w[0] * a0.x; s0[1] = c.w[0] * a0.y; s0[2] = c.w[0] * a0.z; s0[3] = c.w[0] * a0.w;
-    RB_FMA4(s0, c.w[1], a1) RB_FMA4(s0, c.w[2], a2) RB_FMA4(s0, c.w[3], a3)
-    s1[0] = c.w[4] * b0.x; s1[1] = c.w[4] * b0.y; s1[2] = c.w[4] * b0.z; s1[3] = c.w[4] * b0.w;
-    RB_FMA4(s1, c.w[5], b1) RB_FMA4(s1, c.w[6], b2) RB_FMA4(s1, c.w[7], b3)
+    const int de = G::RS, dp = G::neta(P) * G::RS;
+    const Real* t0 = tab + (unsigned)(c.maj0 * G::RS);
+    const Real* t1 = tab + (unsigned)(c.maj1 * G::RS);
+    const V4<Real> a0 = ldg4(t0), a1 = ldg4(t0 + de), a2 = ldg4(t0 + dp), a3 = ldg4(t0 + dp + de);
+    const V4<Real> b0 = ldg4(t1), b1 = ldg4(t1 + de), b2 = ldg4(t1 + dp), b3 = ldg4(t1 + dp + de);
+    RB_MUL4(s0, c.w[0], a0) RB_FMA4(s0, c.w[1], a1) RB_FMA4(s0, c.w[2], a2) RB_FMA4(s0, c.w[3], a3)
+    RB_MUL4(s1, c.w[4], b0) RB_FMA4(s1, c.w[5], b1) RB_FMA4(s1, c.w[6], b2) RB_FMA4(s1, c.w[7], b3)
 }
 
-// interpolate2D_byflav (F90:738-758)
-template<typename Real>
-__device__ __forceinline__ void interp_minor(const Real* __restrict__ tab, const DevPlan<Real>& P,
-                                             const Cell<Real>& c, Real (&s)[4])
+// kmajor and planck_frac of the same 8 corners (interleaved rows, longwave)
+template<typename G, typename Real>
+__device__ __forceinline__ void interp_major_pair(const Real* __restrict__ tab, const DevPlan<Real>& P, const Cell<Real>& c,
+                                                  Real (&s0)[4], Real (&s1)[4], Real (&p0)[4], Real (&p1)[4])
 {
-    const V4<Real> a0 = ldg4(tab + c.min0), a1 = ldg4(tab + c.min0 + P.gw);
-    const V4<Real> b0 = ldg4(tab + c.min1), b1 = ldg4(tab + c.min1 + P.gw);
-    s[0] = c.fm[0] * a0.x; s[1] = c.fm[0] * a0.y; s[2] = c.fm[0] * a0.z; s[3] = c.fm[0] * a0.w;
-    RB_FMA4(s, c.fm[1], a1) RB_FMA4(s, c.fm[2], b0) RB_FMA4(s, c.fm[3], b1)
+    const int de = G::RS, dp = G::neta(P) * G::RS, pf = G::GW;
+    const Real* t0 = tab + (unsigned)(c.maj0 * G::RS);
+    const Real* t1 = tab + (unsigned)(c.maj1 * G::RS);
+    {
+        const V4<Real> a0 = ldg4(t0), a1 = ldg4(t0 + de), a2 = ldg4(t0 + dp), a3 = ldg4(t0 + dp + de);
+        const V4<Real> f0 = ldg4(t0 + pf), f1 = ldg4(t0 + de + pf), f2 = ldg4(t0 + dp + pf), f3 = ldg4(t0 + dp + de + pf);
+        RB_MUL4(s0, c.w[0], a0) RB_FMA4(s0, c.w[1], a1) RB_FMA4(s0, c.w[2], a2) RB_FMA4(s0, c.w[3], a3)
+        RB_MUL4(p0, c.w[0], f0) RB_FMA4(p0, c.w[1], f1) RB_FMA4(p0, c.w[2], f2) RB_FMA4(p0, c.w[3], f3)
+    }
+    {
+        const V4<Real> b0 = ldg4(t1), b1 = ldg4(t1 + de), b2 = ldg4(t1 + dp), b3 = ldg4(t1 + dp + de);
+        const V4<Real> f0 = ldg4(t1 + pf), f1 = ldg4(t1 + de + pf), f2 = ldg4(t1 + dp + pf), f3 = ldg4(t1 + dp + de + pf);
+        RB_MUL4(s1, c.w[4], b0) RB_FMA4(s1, c.w[5], b1) RB_FMA4(s1, c.w[6], b2) RB_FMA4(s1, c.w[7], b3)
+        RB_MUL4(p1, c.w[4], f0) RB_FMA4(p1, c.w[5], f1) RB_FMA4(p1, c.w[6], f2) RB_FMA4(p1, c.w[7], f3)
+    }
 }
 
-// gas absorption optical depth of 4 g-points: major + minor contributors of the layer's side
-// (compute_tau_absorption, F90:178-502).  q4 = first g-point of the quad within the band.
-template<typename Real>
-__device__ __forceinline__ void gas_tau(const DevPlan<Real>& P, const BandArgs& B, const Cell<Real>& c,
-                                        const Real* __restrict__ kmaj_band, int q4,
-                                        const Real* __restrict__ col_gas, size_t icl, size_t tcl,
-                                        Real (&tau)[4], Real (&s0)[4], Real (&s1)[4])
+// interpolate2D_byflav (F90:738-758); minor / Rayleigh blocks have row stride GW
+template<typename G, typename Real>
+__device__ __forceinline__ void interp_minor(const Real* __restrict__ tab, const Cell<Real>& c, Real (&s)[4])
 {
-    interp_major(kmaj_band + q4, P, c, s0, s1);
-#pragma unroll
-    for (int j = 0; j < 4; ++j) tau[j] = c.cm0 * s0[j] + c.cm1 * s1[j];
+    const Real* t0 = tab + c.min0 * G::GW;
+    const Real* t1 = tab + c.min1 * G::GW;
+    const V4<Real> a0 = ldg4(t0), a1 = ldg4(t0 + G::GW), b0 = ldg4(t1), b1 = ldg4(t1 + G::GW);
+    RB_MUL4(s, c.fm[0], a0) RB_FMA4(s, c.fm[1], a1) RB_FMA4(s, c.fm[2], b0) RB_FMA4(s, c.fm[3], b1)
+}
+
+// minor-gas part of compute_tau_absorption (F90:404-502) for the layer's side, added onto tau.
+// The band's contributors are consecutive blocks of P.kminor[side].
+template<typename G, typename Real>
+__device__ __forceinline__ void add_minor_tau(const DevPlan<Real>& P, const BandArgs& B, const Cell<Real>& c, int q4,
+                                              const Real* __restrict__ cgp, size_t tcl, Real (&tau)[4])
+{
     const int side = c.side;
     const int nm = B.nminor[side];
-    const size_t mstride = (size_t)P.ntemp * P.neta * P.gw;
-    for (int m = 0; m < nm; ++m)
+    const size_t mstride = (size_t)P.ntemp * G::neta(P) * G::GW;
+    const Real* km = P.kminor[side] + mstride * B.first_minor[side] + q4;
+    for (int m = 0; m < nm; ++m, km += mstride)
     {
         const MinorDev d = B.minor[side][m];
-        Real scaling = col_gas[icl + tcl * d.idx_minor];
+        Real scaling = cgp[tcl * d.idx_minor];
         if (d.flags & 1)
         {
             scaling *= c.dens;
             if (d.idx_scaling > 0)
             {
-                const Real x = col_gas[icl + tcl * d.idx_scaling] * c.vd;
+                const Real x = cgp[tcl * d.idx_scaling] * c.vd;
                 scaling *= (d.flags & 2) ? ((Real)1 - x) : x;
             }
         }
         Real s[4];
-        interp_minor(P.kminor[side] + mstride * d.contributor + q4, P, c, s);
+        interp_minor<G>(km, c, s);
 #pragma unroll
         for (int j = 0; j < 4; ++j) tau[j] = fma(scaling, s[j], tau[j]);
     }
+}
+
+// gas absorption optical depth of 4 g-points: major + minor (compute_tau_absorption, F90:178-502)
+template<typename G, typename Real>
+__device__ __forceinline__ void gas_tau(const DevPlan<Real>& P, const BandArgs& B, const Cell<Real>& c,
+                                        const Real* __restrict__ kmaj_quad, int q4,
+                                        const Real* __restrict__ cgp, size_t tcl, Real (&tau)[4])
+{
+    Real s0[4], s1[4];
+    interp_major<G>(kmaj_quad, P, c, s0, s1);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) tau[j] = c.cm0 * s0[j] + c.cm1 * s1[j];
+    add_minor_tau<G>(P, B, c, q4, cgp, tcl, tau);
 }
 
 // interpolate1D (F90:715-734) for one band
@@ -117,6 +172,14 @@ __device__ __forceinline__ Real planck_band(const Real* __restrict__ tab, int n,
     const int index = min(n - 1, max(1, iv + 1));
     const Real t0 = tab[index - 1], t1 = tab[index];
     return t0 + frac * (t1 - t0);
+}
+// the same from a position {frac, lower index} precomputed by the prologue kernel
+template<typename Real>
+__device__ __forceinline__ Real planck_at(const Real* __restrict__ tab, const V2<Real>& pos)
+{
+    const int i = M<Real>::as_int(pos.y);
+    const Real t0 = tab[i], t1 = tab[i + 1];
+    return t0 + pos.x * (t1 - t0);
 }
 
 // sum of a quad's 4 values across the LPC lanes of a column; result valid in every lane
@@ -137,10 +200,10 @@ __device__ __forceinline__ void lw_layer(Real tau_loc, Real lay_src, Real lev_ab
     // tau_thresh = sqrt(sqrt(epsilon))
     const Real tau_thresh = sizeof(Real) == 4 ? (Real)1.857e-2 : (Real)1.220703125e-4;
     trans = M<Real>::exp(-tau_loc);
-    Real fact;
-    if (tau_loc > tau_thresh) fact = M<Real>::div((Real)1 - trans, tau_loc) - trans;
-    else fact = tau_loc * ((Real)0.5 + tau_loc * ((Real)(-1.0 / 3.0) + tau_loc * (Real)0.125));
     const Real omt = (Real)1 - trans;
+    const Real f_big = M<Real>::div(omt, M<Real>::max(tau_loc, tau_thresh)) - trans;
+    const Real f_small = tau_loc * ((Real)0.5 + tau_loc * ((Real)(-1.0 / 3.0) + tau_loc * (Real)0.125));
+    const Real fact = tau_loc > tau_thresh ? f_big : f_small;
     src_dn = omt * lev_below + (Real)2 * fact * (lay_src - lev_below);
     src_up = omt * lev_above + (Real)2 * fact * (lay_src - lev_above);
 }
@@ -223,7 +286,9 @@ __device__ __forceinline__ void two_stream_ref(Real tau, Real w0, Real g, Real m
 // (1 - exp(-x)) / x for x >= 0 given e = exp(-x): series below 0.03 (no cancellation)
 __device__ __forceinline__ float omexp_over_x(float x, float e)
 {
-    return x < 0.03f ? 1.f - 0.5f * x * (1.f - (1.f / 3.f) * x * (1.f - 0.25f * x)) : __fdividef(1.f - e, x);
+    const float ser = fmaf(-0.5f * x, fmaf(-(1.f / 3.f) * x, fmaf(-0.25f, x, 1.f), 1.f), 1.f);
+    const float dir = __fdividef(1.f - e, fmaxf(x, 1e-30f));
+    return x < 0.03f ? ser : dir;
 }
 
 // fp32 two-stream: the same Meador-Weaver / PIFM expressions as two_stream_ref, algebraically
@@ -244,13 +309,13 @@ __device__ __forceinline__ void two_stream_f32(float tau, float w0, float g, flo
     const float gamma1 = (8.f - w0 * (5.f + 3.f * g)) * .25f;
     const float gamma2 = 3.f * (w0 * (1.f - g)) * .25f;
     const float k2 = fmaxf(2.f * (1.f - w0) * (2.f - 0.5f * w0 * (1.f + 3.f * g)), 0.f);   // (g1-g2)(g1+g2)
-    const float k = sqrtf(k2);
+    const float k = M<float>::sqrt(k2);
     const float a = k * tau;
     const float e1 = __expf(-a), e2 = e1 * e1;
     const float ga = omexp_over_x(a, e1);
     const float om1 = a * ga;
     const float P = tau * ga * (1.f + e1);
-    const float rD = __frcp_rn((1.f + e2) + gamma1 * P);
+    const float rD = M<float>::rcp((1.f + e2) + gamma1 * P);
     Rdif = gamma2 * P * rD;
     Tdif = 2.f * e1 * rD;
 
@@ -263,7 +328,7 @@ __device__ __forceinline__ void two_stream_f32(float tau, float w0, float g, flo
     if (fabsf(d) < band)
     {
         d = d >= 0.f ? band : -band;
-        mu = __fdividef(sqrtf(1.f - d), k);
+        mu = __fdividef(M<float>::sqrt(1.f - d), k);
         const float xe = __fdividef(tau, mu);
         T0 = __expf(-xe);
         omT = xe * omexp_over_x(xe, T0);

@@ -57,7 +57,7 @@ struct HostPlan
 {
     bool is_lw = false;
     int ntemp = 0, npres = 0, neta = 0, nbnd = 0, ngpt = 0, nflav = 0, ngas = 0, gw = 0;
-    int nplanck = 0, idx_h2o = 0;
+    int nplanck = 0, idx_h2o = 0, row_stride = 0;
     std::vector<std::string> gas_names;          // reduced list, slot i+1 of col_gas
     std::vector<int> band_lims_gpt;              // (2,nbnd) 1-based
     std::vector<double> band_lims_wvn;           // (2,nbnd)
@@ -69,7 +69,7 @@ struct HostPlan
     std::vector<double> press_ref, press_ref_log, temp_ref;
     double press_ref_log_delta = 0, temp_ref_min = 0, temp_ref_max = 0, temp_ref_delta = 0;
     double press_ref_min = 0, press_ref_max = 0, press_ref_trop_log = 0, totplnk_delta = 0;
-    std::vector<double> kmajor, pfrac;           // device layout [b][it][ip][ie][gw]
+    std::vector<double> kmajor;                  // device layout [b][it][ip][ie][slot][gw]; slot 1 = planck_frac (LW)
     std::vector<double> krayl;                   // device layout [side][b][it][ie][gw]
     std::vector<double> totplnk;                 // [b][nplanck]
     std::vector<double> solar_source;            // (ngpt)
@@ -198,8 +198,14 @@ inline HostPlan build_host_plan(const rrtmgp_b200_kdist_file& kd, int n_avail,
 
     // Big tables.  File kmajor(temperature, pressure_interp, mixing_fraction, gpt) (C order);
     // reference member kmajor(ntemp, neta, npres+1, ngpt) (:657-663).  Device: [b][it][ip][ie][gw].
-    auto block4 = [&](const double* src) {
-        std::vector<double> out((size_t)nbnd * ntemp * (npres + 1) * neta * gw, 0.0);
+    // Longwave: kmajor and planck_frac rows are interleaved ([...][ie][2][gw]) so the two tables'
+    // corners of a cell share one 128-byte line (fp32) and one address computation.
+    const int rs = p.is_lw ? 2 * gw : gw;          // row stride in elements
+    p.row_stride = rs;
+    if ((long long)ntemp * (npres + 1) * neta >= (1 << 20) || ntemp * neta >= (1 << 12))
+        throw ArgError("k-distribution: table too large for the packed row indices");
+    auto block4 = [&](const double* src, int slot, std::vector<double>& out) {
+        out.resize((size_t)nbnd * ntemp * (npres + 1) * neta * rs, 0.0);
         for (int b = 0; b < nbnd; ++b)
         {
             const int g1 = p.band_lims_gpt[2 * b] - 1, n = p.band_lims_gpt[2 * b + 1] - g1;
@@ -208,17 +214,16 @@ inline HostPlan build_host_plan(const rrtmgp_b200_kdist_file& kd, int n_avail,
                     for (int ie = 0; ie < neta; ++ie)
                     {
                         const double* s = src + (((size_t)it * (npres + 1) + ip) * neta + ie) * ngpt + g1;
-                        double* d = &out[((((size_t)b * ntemp + it) * (npres + 1) + ip) * neta + ie) * gw];
+                        double* d = &out[((((size_t)b * ntemp + it) * (npres + 1) + ip) * neta + ie) * rs + (size_t)slot * gw];
                         for (int g = 0; g < n; ++g) d[g] = s[g];
                     }
         }
-        return out;
     };
-    p.kmajor = block4(kd.kmajor);
+    block4(kd.kmajor, 0, p.kmajor);
     if (p.is_lw)
     {
         if (!kd.plank_fraction || kd.n_planck_temps < 2) throw ArgError("longwave k-distribution without Planck tables");
-        p.pfrac = block4(kd.plank_fraction);
+        block4(kd.plank_fraction, 1, p.kmajor);
         p.nplanck = kd.n_planck_temps;
         p.totplnk.assign(kd.totplnk, kd.totplnk + (size_t)nbnd * p.nplanck);   // file (bnd, temperature_Planck)
         p.totplnk_delta = (p.temp_ref_max - p.temp_ref_min) / (p.nplanck - 1);  // :458
@@ -309,6 +314,12 @@ inline HostPlan build_host_plan(const rrtmgp_b200_kdist_file& kd, int n_avail,
         for (int m = 0; m < ms.n; ++m) ms.nk += ms.limits[2 * m + 1] - ms.limits[2 * m] + 1;
         ms.kminor_ref.assign((size_t)ntemp * neta * std::max(ms.nk, 1), 0.0);
         ms.table.assign((size_t)std::max(ms.n, 1) * ntemp * neta * gw, 0.0);
+        // device blocks in band order, so a band's contributors are consecutive blocks
+        {
+            int pos = 0;
+            for (int b = 0; b < nbnd; ++b)
+                for (int m : ms.by_band[b]) ms.desc[m].contributor = pos++;
+        }
         for (int m = 0; m < ms.n; ++m)
         {
             const int ng = ms.limits[2 * m + 1] - ms.limits[2 * m] + 1;
@@ -318,7 +329,7 @@ inline HostPlan build_host_plan(const rrtmgp_b200_kdist_file& kd, int n_avail,
                     {
                         const double v = kmin[((size_t)it * neta + ie) * nkfile + src_start[m] + g];
                         ms.kminor_ref[it + (size_t)ntemp * (ie + (size_t)neta * (ms.kstart[m] - 1 + g))] = v;
-                        ms.table[(((size_t)m * ntemp + it) * neta + ie) * gw + g] = v;
+                        ms.table[(((size_t)ms.desc[m].contributor * ntemp + it) * neta + ie) * gw + g] = v;
                     }
         }
     }
