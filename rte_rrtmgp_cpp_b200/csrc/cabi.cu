@@ -92,7 +92,7 @@ struct rrtmgp_b200_gas_optics
     int dtype = 0, device = 0;
     bool host_only = false;
     HostPlan h;
-    DevBuf kmajor, pfrac, krayl, kminor[2], totplnk, solar, temp_ref, vmr_ref, flavor, band_flavor, band_lims;
+    DevBuf kmajor, pfrac, krayl, kminor[2], totplnk, solar, temp_ref, vmr_ref, flavor, band_flavor, band_lims, minor_slots[2];
     DevPlan<float> pf{};
     DevPlan<double> pd{};
     std::vector<BandArgs> bands;
@@ -134,6 +134,24 @@ static void fill_devplan(rrtmgp_b200_gas_optics* g, DevPlan<Real>& P)
     P.totplnk = (const Real*)g->totplnk.p; P.solar_source = (const Real*)g->solar.p;
     P.temp_ref = (const double*)g->temp_ref.p; P.vmr_ref = (const double*)g->vmr_ref.p;
     P.flavor = (const int*)g->flavor.p; P.band_flavor = (const int*)g->band_flavor.p; P.band_lims = (const int*)g->band_lims.p;
+    for (int sd = 0; sd < 2; ++sd)
+    {
+        std::vector<int> slots((size_t)4 * h.nscal, 0);
+        for (int k = 0; k < h.nscal; ++k)
+        {
+            const int m = k < (int)h.minor[sd].slot_desc.size() ? h.minor[sd].slot_desc[k] : -1;
+            slots[4 * k] = -1;
+            if (m >= 0)
+            {
+                const MinorDesc& dd = h.minor[sd].desc[m];
+                slots[4 * k] = dd.idx_minor; slots[4 * k + 1] = dd.idx_scaling;
+                slots[4 * k + 2] = (dd.scales_with_density ? 1 : 0) | (dd.scale_by_complement ? 2 : 0);
+            }
+        }
+        g->minor_slots[sd].upload(slots);
+        P.minor_slots[sd] = (const int4*)g->minor_slots[sd].p;
+    }
+    P.nscal = h.nscal;
     P.press_ref_log0 = h.press_ref_log[0]; P.press_ref_log_delta = h.press_ref_log_delta;
     P.press_ref_trop_log = h.press_ref_trop_log; P.temp_ref_min = h.temp_ref_min; P.temp_ref_delta = h.temp_ref_delta;
     P.planck_tmin = (Real)h.temp_ref_min; P.planck_delta = (Real)h.totplnk_delta;
@@ -178,12 +196,9 @@ int rrtmgp_b200_gas_optics_create(const rrtmgp_b200_kdist_file* kd, int n_avail,
                 const auto& lst = h.minor[s].by_band[b];
                 B.nminor[s] = (int)lst.size();
                 B.first_minor[s] = lst.empty() ? 0 : h.minor[s].desc[lst[0]].contributor;
+                B.scal_off[s] = h.minor[s].scal_off[b] / 4;
                 for (size_t m = 0; m < lst.size(); ++m)
-                {
-                    const MinorDesc& d = h.minor[s].desc[lst[m]];
-                    if (d.idx_minor < 0) throw ArgError("internal: minor gas index");
-                    B.minor[s][m] = MinorDev{d.idx_minor, d.idx_scaling, (d.scales_with_density ? 1 : 0) | (d.scale_by_complement ? 2 : 0), d.contributor};
-                }
+                    if (h.minor[s].desc[lst[m]].idx_minor < 0) throw ArgError("internal: minor gas index");
             }
         }
     }, !host_only);
@@ -304,7 +319,7 @@ TileState<Real> carve_state(Arena& ws, const HostPlan& h, int nc, int nlay)
     st.cell = ws.take<V4<Real>>(tcl);
     st.flvA = ws.take<V4<Real>>(tcl * h.nflav);
     st.flvB = ws.take<V4<Real>>(tcl * h.nflav);
-    st.col_gas = ws.take<Real>(tcl * (h.ngas + 1));
+    st.scal = ws.take<V4<Real>>(tcl * (h.nscal / 4));
     st.pl_lay = nullptr; st.pl_lev = nullptr;
     if (h.is_lw) { st.pl_lay = ws.take<V2<Real>>(tcl); st.pl_lev = ws.take<V2<Real>>(tcl + nc); }
     st.tmask = ws.take<unsigned>((size_t)nc * TMASK_WORDS);
@@ -314,7 +329,7 @@ template<typename Real> size_t state_bytes(const HostPlan& h, int nc, int nlay)
 {
     const size_t tcl = (size_t)nc * nlay;
     return pad256(tcl * sizeof(V4<Real>)) + 2 * pad256(tcl * h.nflav * sizeof(V4<Real>))
-         + pad256(tcl * (h.ngas + 1) * sizeof(Real)) + pad256((size_t)nc * TMASK_WORDS * sizeof(unsigned))
+         + pad256(tcl * h.nscal * sizeof(Real)) + pad256((size_t)nc * TMASK_WORDS * sizeof(unsigned))
          + 2 * pad256((tcl + nc) * sizeof(V2<Real>)) + 1024;
 }
 
@@ -724,15 +739,15 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
     }
 
     const int cpb = FUSED_THREADS / (h.gw / 4);
+    // A tile is several waves of CTAs: CTAs retire and start continuously, so the compute-heavy
+    // and the memory-heavy passes of different CTAs overlap.  Scratch strips are per resident CTA.
+    const int wave = std::max(sw ? sw_blocks_per_wave<Real>(h.gw) : lw_blocks_per_wave<Real>(h.gw), 1);
+    const int nslots = 2 * wave;
     int tile = g->tile_cols;
-    if (tile <= 0)
-    {
-        const int blocks = sw ? sw_blocks_per_wave<Real>(h.gw) : lw_blocks_per_wave<Real>(h.gw);
-        tile = std::max(blocks, 1) * cpb;
-    }
+    if (tile <= 0) tile = 8 * wave * cpb;
     tile = std::min(tile, ncol);
     const size_t tcl = (size_t)tile * nlay, ncl = (size_t)ncol * nlay, ncv = (size_t)ncol * nlev;
-    size_t need = state_bytes<Real>(h, tile, nlay) + pad256(fused_scratch_bytes<Real>(tile, nlay, h.gw, sw)) + 4096;
+    size_t need = state_bytes<Real>(h, tile, nlay) + pad256(fused_scratch_bytes<Real>(nslots, nlay, sw)) + pad256(nslots * sizeof(int)) + 4096;
     if (!cols->d_col_dry) need += pad256(ncl * sizeof(Real));
     if (cloud) need += 3 * pad256(tcl * h.nbnd * sizeof(Real));
     if (sw && !out->d_flux_dn_dir) need += pad256(ncv * sizeof(Real));
@@ -746,7 +761,9 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
     a.sfc_emis = (const Real*)cols->d_sfc_emis; a.mu0 = (const Real*)cols->d_mu0;
     a.alb_dir = (const Real*)cols->d_sfc_alb_dir; a.alb_dif = (const Real*)cols->d_sfc_alb_dif;
     a.tsi_scaling = (const Real*)cols->d_tsi_scaling;
-    a.scratch = (V4<Real>*)g->ws.take<char>(fused_scratch_bytes<Real>(tile, nlay, h.gw, sw));
+    a.scratch = (V4<Real>*)g->ws.take<char>(fused_scratch_bytes<Real>(nslots, nlay, sw));
+    a.slot_busy = g->ws.take<int>(nslots); a.nslots = nslots;
+    CK(cudaMemsetAsync(a.slot_busy, 0, nslots * sizeof(int), s));
     a.flux_up = (Real*)out->d_flux_up; a.flux_dn = (Real*)out->d_flux_dn;
     a.flux_dir = (Real*)out->d_flux_dn_dir;
     a.bnd_up = (Real*)out->d_bnd_flux_up; a.bnd_dn = (Real*)out->d_bnd_flux_dn; a.bnd_dir = (Real*)out->d_bnd_flux_dn_dir;

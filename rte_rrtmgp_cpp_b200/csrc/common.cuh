@@ -82,6 +82,8 @@ template<typename Real> struct DevPlan
     const int* flavor;         // (2, nflav) 1-based gas index, 0 = dry air
     const int* band_flavor;    // (2, nbnd) 0-based flavor
     const int* band_lims;      // (2, nbnd) 1-based
+    const int4* minor_slots[2]; // per side, nscal entries {idx_minor (-1 = padding), idx_scaling, flags, 0}
+    int nscal;                 // slots of the per-(column, layer) minor scaling vector (multiple of 4)
     double press_ref_log0, press_ref_log_delta, press_ref_trop_log;
     double temp_ref_min, temp_ref_delta;
     Real planck_tmin, planck_delta;
@@ -104,14 +106,15 @@ template<> struct alignas(16) V2<double> { double x, y; };
 template<typename Real> struct TileState
 {
     int nc, nlay;            // columns in this tile, layers
-    V4<Real>* cell;          // {fpress, dens = 0.01 p/T, vd = vmr_fact*dry_fact, bits}
+    V4<Real>* cell;          // {fpress, col_gas(h2o) + col_dry, 0, bits}
                              //   bits = jtemp | jpress<<8 | tropo<<16
+    V4<Real>* scal;          // [nscal/4] per (c,l): minor-gas scaling of every contributor of the layer's
+                             //   side (col_gas * density * scaling-gas factor, F90:453-475), band-blocked
     V4<Real>* flvA;          // [f]: {col_mix0, col_mix1, fminor(1,1), fminor(2,1)}
     V4<Real>* flvB;          // [f]: {fminor(1,2), fminor(2,2), rows(itemp 1), rows(itemp 2)}
                              //   rows = major row | minor row << 20 (row = offset / row stride)
     V2<Real>* pl_lay;        // LW: Planck table position of tlay {frac, lower index}  (nc, nlay)
     V2<Real>* pl_lev;        // LW: idem for tlev                                      (nc, nlay+1)
-    Real* col_gas;           // [g = 0..ngas]
     unsigned* tmask;         // [c][TMASK_WORDS]: bit l of a column = tropo(c, l)  (fused path only)
 };
 constexpr int TMASK_WORDS = 8;   // the fused path handles up to 256 layers
@@ -123,7 +126,7 @@ struct BandArgs
     int band, gpt0, ngb;     // 0-based band, first g-point (0-based), g-points in band
     int nminor[2];
     int first_minor[2];      // device block index of the band's first contributor (blocks are consecutive)
-    MinorDev minor[2][MAX_MINOR_DEV];
+    int scal_off[2];         // first V4 of the band's contributors in TileState::scal
 };
 
 }  // namespace rb200

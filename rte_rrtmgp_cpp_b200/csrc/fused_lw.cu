@@ -20,8 +20,14 @@
 
 namespace rb200 {
 
+#ifndef RB_LW_MINB
+#define RB_LW_MINB 5
+#endif
+// resident CTAs per SM requested from ptxas for the fp32 instantiations (fp64 needs the registers)
+template<typename Real> struct LWMinBlocks { static constexpr int v = sizeof(Real) == 4 ? RB_LW_MINB : 1; };
+
 template<typename Real, int LPC, bool CLOUD, int NE>
-__global__ void __launch_bounds__(FUSED_THREADS)
+__global__ void __launch_bounds__(FUSED_THREADS, LWMinBlocks<Real>::v)
 lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const TileState<Real> st,
                const FusedArgs<Real> a)
 {
@@ -43,7 +49,8 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     const Real* plk = P.totplnk + (size_t)P.nplanck * band;
     const int flav0 = P.band_flavor[2 * band], flav1 = P.band_flavor[2 * band + 1];
     const unsigned* tm = st.tmask + (size_t)c * TMASK_WORDS;
-    V4<Real>* const scr = a.scratch + (size_t)blockIdx.x * nlay * 2 * T + tid;
+    const int slot = claim_slot(a.slot_busy, a.nslots);
+    V4<Real>* const scr = a.scratch + (size_t)slot * nlay * 2 * T + tid;
     const Real piw = (Real)3.14159265358979323846 * a.weight;
     const bool lead = active && q == 0;
     const size_t nlev_stride = (size_t)a.ncol * (nlay + 1);
@@ -61,7 +68,7 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     // Planck-table positions of the next layer are fetched one iteration ahead.
     int l = top ? 0 : nlay - 1;                         // current layer, array order
     const V2<Real>* plev_p = st.pl_lev + (size_t)c + (size_t)nc * (top ? 0 : nlay);
-    RawState<Real> nxt = load_state(st, tm, flav0, flav1, c, l, tcl);
+    RawState<Real> nxt = load_state(st, P, B, tm, flav0, flav1, c, l, tcl);
     V2<Real> play_n = st.pl_lay[(size_t)c + (size_t)nc * l], plev_n = *plev_p;
     size_t o = o_top;
     for (int k = 0; k <= nlay; ++k)
@@ -78,7 +85,7 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
             if (k + 1 < nlay)
             {
                 const int ln = top ? l + 1 : l - 1;
-                nxt = load_state(st, tm, flav0, flav1, c, ln, tcl);
+                nxt = load_state(st, P, B, tm, flav0, flav1, c, ln, tcl);
                 play_n = st.pl_lay[(size_t)c + (size_t)nc * ln];
             }
             Cell<Real> ce;
@@ -87,7 +94,7 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
             interp_major_pair<G>(kmaj, P, ce, s0, s1, p0, p1);
 #pragma unroll
             for (int j = 0; j < 4; ++j) { tau[j] = ce.cm0 * s0[j] + ce.cm1 * s1[j]; pf[j] = p0[j] + p1[j]; }
-            add_minor_tau<G>(P, B, ce, q4, st.col_gas + icl, tcl, tau);
+            add_minor_tau<G>(P, B, ce, q4, cur.sc0, cur.sc1, st.scal + icl * (size_t)(P.nscal >> 2), tau);
             if (CLOUD)
             {
                 const Real ct = a.cld_tau[icl + tcl * band];
@@ -175,13 +182,12 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
             }
         }
     }
+    release_slot(a.slot_busy, slot);
 }
 
-template<typename Real> size_t fused_scratch_bytes(int nc, int nlay, int gw, bool sw)
+template<typename Real> size_t fused_scratch_bytes(int nslots, int nlay, bool sw)
 {
-    const int cpb = FUSED_THREADS / (gw / 4);
-    const size_t nblk = (size_t)(nc + cpb - 1) / cpb;
-    return nblk * nlay * (sw ? 4 : 2) * FUSED_THREADS * sizeof(V4<Real>);
+    return (size_t)nslots * nlay * (sw ? 4 : 2) * FUSED_THREADS * sizeof(V4<Real>);
 }
 
 template<typename Real>
@@ -200,8 +206,8 @@ void launch_lw_band(const DevPlan<Real>& P, const BandArgs& B, const TileState<R
     count_launch();
 }
 
-template size_t fused_scratch_bytes<float>(int, int, int, bool);
-template size_t fused_scratch_bytes<double>(int, int, int, bool);
+template size_t fused_scratch_bytes<float>(int, int, bool);
+template size_t fused_scratch_bytes<double>(int, int, bool);
 template void launch_lw_band<float>(const DevPlan<float>&, const BandArgs&, const TileState<float>&, const FusedArgs<float>&, cudaStream_t);
 template void launch_lw_band<double>(const DevPlan<double>&, const BandArgs&, const TileState<double>&, const FusedArgs<double>&, cudaStream_t);
 

@@ -17,8 +17,14 @@
 
 namespace rb200 {
 
+#ifndef RB_SW_MINB
+#define RB_SW_MINB 5
+#endif
+// resident CTAs per SM requested from ptxas for the fp32 instantiations (fp64 needs the registers)
+template<typename Real> struct SWMinBlocks { static constexpr int v = sizeof(Real) == 4 ? RB_SW_MINB : 1; };
+
 template<typename Real, int LPC, bool CLOUD, int NE>
-__global__ void __launch_bounds__(FUSED_THREADS)
+__global__ void __launch_bounds__(FUSED_THREADS, SWMinBlocks<Real>::v)
 sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const TileState<Real> st,
                const FusedArgs<Real> a)
 {
@@ -42,7 +48,8 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     const size_t ray_side = ray_elems * P.nbnd;
     const int flav0 = P.band_flavor[2 * band], flav1 = P.band_flavor[2 * band + 1];
     const unsigned* tm = st.tmask + (size_t)c * TMASK_WORDS;
-    V4<Real>* const scr = a.scratch + (size_t)blockIdx.x * nlay * 4 * T + tid;
+    const int slot = claim_slot(a.slot_busy, a.nslots);
+    V4<Real>* const scr = a.scratch + (size_t)slot * nlay * 4 * T + tid;
     const bool lead = active && q == 0;
     const size_t nlev_stride = (size_t)a.ncol * (nlay + 1);
     const int top = a.top_at_1;
@@ -75,25 +82,24 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     // ---- pass 1: optics + two-stream + direct beam, top -> surface.  The next layer's state is
     // fetched one iteration ahead (its address does not depend on loaded data: the flavor comes
     // from the column's tropopause bit mask).
-    RawState<Real> nxt = load_state(st, tm, flav0, flav1, c, top ? 0 : nlay - 1, tcl);
+    RawState<Real> nxt = load_state(st, P, B, tm, flav0, flav1, c, top ? 0 : nlay - 1, tcl);
     size_t o = o_top;
     for (int k = 0; k < nlay; ++k)
     {
         const int l = top ? k : nlay - 1 - k;
         const size_t icl = (size_t)c + (size_t)nc * l;
         const RawState<Real> cur = nxt;
-        if (k + 1 < nlay) nxt = load_state(st, tm, flav0, flav1, c, top ? k + 1 : nlay - 2 - k, tcl);
+        if (k + 1 < nlay) nxt = load_state(st, P, B, tm, flav0, flav1, c, top ? k + 1 : nlay - 2 - k, tcl);
         Cell<Real> ce;
         decode_cell(cur.cell, cur.fa, cur.fb, ce);
         Real tau[4];
-        gas_tau<G>(P, B, ce, kmaj, q4, st.col_gas + icl, tcl, tau);
+        gas_tau<G>(P, B, ce, kmaj, q4, cur.sc0, cur.sc1, st.scal + icl * (size_t)(P.nscal >> 2), tau);
         Real ray[4] = {0, 0, 0, 0};
         if (kray)
         {
             interp_minor<G>(kray + (ce.side ? ray_side : 0), ce, ray);
-            const Real wet = st.col_gas[icl + tcl * P.idx_h2o] + st.col_gas[icl];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) ray[j] *= wet;
+            for (int j = 0; j < 4; ++j) ray[j] *= ce.wet;
         }
         Real ct = 0, cs = 0, cgg = 0;
         if (CLOUD) { ct = a.cld_tau[icl + tcl * band]; cs = a.cld_ssa[icl + tcl * band]; cgg = a.cld_g[icl + tcl * band]; }
@@ -204,6 +210,7 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
             }
         }
     }
+    release_slot(a.slot_busy, slot);
 }
 
 template<typename Real>

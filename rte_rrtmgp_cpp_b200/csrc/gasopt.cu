@@ -41,7 +41,10 @@ gas_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const
         Cell<Real> ce;
         decode_cell(cell, st.flvA[icl + ncl * f], st.flvB[icl + ncl * f], ce);
         Real tau[4], s0[4], s1[4];
-        gas_tau<G>(P, B, ce, kmaj, q4, st.col_gas + icl, ncl, tau);
+        const V4<Real>* sc = st.scal + icl * (size_t)(P.nscal >> 2);
+        const V4<Real> sc0 = sc[B.scal_off[ce.side]];
+        const V4<Real> sc1 = B.nminor[ce.side] > 4 ? sc[B.scal_off[ce.side] + 1] : sc0;
+        gas_tau<G>(P, B, ce, kmaj, q4, sc0, sc1, sc, tau);
         if (lw)
         {
             Real pf[4];
@@ -76,9 +79,8 @@ gas_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const
             if (P.krayl)
             {
                 interp_minor<G>(P.krayl + ray_elems * ((size_t)ce.side * P.nbnd + band) + q4, ce, ray);
-                const Real wet = st.col_gas[icl + ncl * P.idx_h2o] + st.col_gas[icl];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) ray[j] *= wet;
+                for (int j = 0; j < 4; ++j) ray[j] *= ce.wet;
             }
             for (int j = 0; j < nvalid; ++j)
             {

@@ -75,23 +75,47 @@ interp_kernel(const DevPlan<Real> P, const VmrArgs vmr, int ncol, int c0, int nc
     if (ro.jtemp) ro.jtemp[i] = jt;
     if (ro.jpress) ro.jpress[i] = jp;
     if (ro.tropo) ro.tropo[i] = (signed char)tropo;
-    if (ro.col_gas || st.col_gas)
-        for (int ig = 0; ig <= P.ngas; ++ig)
-        {
-            const double v = cgas(ig);
-            if (ro.col_gas) ro.col_gas[i + ncl * ig] = (Real)v;
-            if (st.col_gas) st.col_gas[it + tcl * ig] = (Real)v;
-        }
+    if (ro.col_gas)
+        for (int ig = 0; ig <= P.ngas; ++ig) ro.col_gas[i + ncl * ig] = (Real)cgas(ig);
     if (st.cell)
     {
-        const double vmr_fact = 1.0 / cd;
-        const double dry_fact = 1.0 / (1.0 + cgas(P.idx_h2o) * vmr_fact);
         V4<Real> rec;
         rec.x = (Real)fpress;
-        rec.y = (Real)(0.01 * pr / t);
-        rec.z = (Real)(vmr_fact * dry_fact);
+        rec.y = (Real)(cgas(P.idx_h2o) + cd);
+        rec.z = (Real)0;
         rec.w = M<Real>::from_int(jt | (jp << 8) | (tropo << 16));
         st.cell[it] = rec;
+        // minor-gas scaling of every contributor of this layer's side (F90:453-475)
+        const double vmr_fact = 1.0 / cd;
+        const double dry_fact = 1.0 / (1.0 + cgas(P.idx_h2o) * vmr_fact);
+        const double dens = 0.01 * pr / t;
+        const int4* slots = P.minor_slots[side];
+        Real* out = reinterpret_cast<Real*>(st.scal) + it * (size_t)P.nscal;
+        for (int p4 = 0; p4 < P.nscal; p4 += 4)
+        {
+            Real v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+            {
+                const int4 dsc = slots[p4 + u];
+                double scaling = 0.0;
+                if (dsc.x >= 0)
+                {
+                    scaling = cgas(dsc.x);
+                    if (dsc.z & 1)
+                    {
+                        scaling = scaling * dens;
+                        if (dsc.y > 0)
+                        {
+                            const double x = cgas(dsc.y) * vmr_fact * dry_fact;
+                            scaling = scaling * ((dsc.z & 2) ? (1.0 - x) : x);
+                        }
+                    }
+                }
+                v[u] = (Real)scaling;
+            }
+            *reinterpret_cast<V4<Real>*>(out + p4) = V4<Real>{v[0], v[1], v[2], v[3]};
+        }
         if (st.pl_lay && tlev)
         {
             // interpolate1D position in totplnk (F90:715-734), band independent

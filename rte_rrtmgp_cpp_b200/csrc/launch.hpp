@@ -25,7 +25,8 @@ template<typename Real> struct FusedArgs
     const Real* mu0; const Real* alb_dir; const Real* alb_dif;     // SW (ncol), (nbnd, ncol)
     const Real* tsi_scaling;                                        // SW (ncol) or null
     const Real* cld_tau; const Real* cld_ssa; const Real* cld_g;   // tile-local (nc,nlay,nbnd) or null
-    V4<Real>* scratch;                                              // per-CTA recurrence state
+    V4<Real>* scratch;                                              // recurrence state, one strip per slot
+    int* slot_busy; int nslots;                                     // strips are claimed by resident CTAs
     Real* flux_up; Real* flux_dn; Real* flux_dir;                   // (ncol, nlay+1), accumulated
     Real* bnd_up; Real* bnd_dn; Real* bnd_dir;                      // (ncol, nlay+1, nbnd) or null
     Real secant, weight;                                            // LW quadrature
@@ -33,7 +34,7 @@ template<typename Real> struct FusedArgs
 constexpr int FUSED_THREADS = 128;
 template<typename Real> int lw_blocks_per_wave(int gw);
 template<typename Real> int sw_blocks_per_wave(int gw);
-template<typename Real> size_t fused_scratch_bytes(int nc, int nlay, int gw, bool sw);
+template<typename Real> size_t fused_scratch_bytes(int nslots, int nlay, bool sw);
 template<typename Real> void launch_lw_band(const DevPlan<Real>& P, const BandArgs& B, const TileState<Real>& st,
                                             const FusedArgs<Real>& a, cudaStream_t s);
 template<typename Real> void launch_sw_band(const DevPlan<Real>& P, const BandArgs& B, const TileState<Real>& st,

@@ -22,7 +22,7 @@ template<typename Real> struct Cell
     Real w[8];        // fmajor: [it*4 + ip*2 + ie]
     Real fm[4];       // fminor: [it*2 + ie]
     Real cm0, cm1;    // col_mix
-    Real dens, vd;    // 0.01 p/T ; vmr_fact*dry_fact
+    Real wet;         // col_gas(h2o) + col_dry (Rayleigh)
     int maj0, maj1;   // row numbers of the (it, ip=0, ie=0) corners in a band's major block
     int min0, min1;   // row numbers of the (it, ie=0) corners in a contributor / Rayleigh block
     int side;         // 0 lower (tropo), 1 upper
@@ -39,7 +39,7 @@ __device__ __forceinline__ void decode_cell(const V4<Real>& cell, const V4<Real>
     o.maj0 = r0 & 0xfffff; o.min0 = (r0 >> 20) & 0xfff;
     o.maj1 = r1 & 0xfffff; o.min1 = (r1 >> 20) & 0xfff;
     const Real fpress = cell.x, omf = (Real)1 - fpress;
-    o.dens = cell.y; o.vd = cell.z;
+    o.wet = cell.y;
     o.cm0 = fa.x; o.cm1 = fa.y;
     o.fm[0] = fa.z; o.fm[1] = fa.w; o.fm[2] = fb.x; o.fm[3] = fb.y;
     o.w[0] = omf * o.fm[0]; o.w[1] = omf * o.fm[1]; o.w[2] = fpress * o.fm[0]; o.w[3] = fpress * o.fm[1];
@@ -47,7 +47,7 @@ __device__ __forceinline__ void decode_cell(const V4<Real>& cell, const V4<Real>
 }
 
 // raw per-(column, layer) state of one band: what the prologue kernel left in HBM
-template<typename Real> struct RawState { V4<Real> cell, fa, fb; };
+template<typename Real> struct RawState { V4<Real> cell, fa, fb, sc0, sc1; };
 
 // flavor of layer l from the column's tropopause bit mask (no dependent load on `cell`)
 __device__ __forceinline__ int layer_side(const unsigned* __restrict__ tm, int l)
@@ -56,12 +56,16 @@ __device__ __forceinline__ int layer_side(const unsigned* __restrict__ tm, int l
 }
 
 template<typename Real>
-__device__ __forceinline__ RawState<Real> load_state(const TileState<Real>& st, const unsigned* tm, int flav0, int flav1,
-                                                    int c, int l, size_t tcl)
+__device__ __forceinline__ RawState<Real> load_state(const TileState<Real>& st, const DevPlan<Real>& P, const BandArgs& B,
+                                                    const unsigned* tm, int flav0, int flav1, int c, int l, size_t tcl)
 {
     const size_t icl = (size_t)c + (size_t)st.nc * l;
-    const int f = layer_side(tm, l) == 0 ? flav0 : flav1;
+    const int side = layer_side(tm, l);
+    const int f = side == 0 ? flav0 : flav1;
     RawState<Real> r;
+    const V4<Real>* sc = st.scal + icl * (size_t)(P.nscal >> 2) + B.scal_off[side];
+    r.sc0 = sc[0];
+    r.sc1 = B.nminor[side] > 4 ? sc[1] : r.sc0;
     r.cell = st.cell[icl];
     r.fa = st.flvA[icl + tcl * f];
     r.fb = st.flvB[icl + tcl * f];
@@ -120,32 +124,33 @@ __device__ __forceinline__ void interp_minor(const Real* __restrict__ tab, const
 }
 
 // minor-gas part of compute_tau_absorption (F90:404-502) for the layer's side, added onto tau.
-// The band's contributors are consecutive blocks of P.kminor[side].
+// The band's contributors are consecutive table blocks and consecutive entries of the scaling
+// vector the prologue kernel prepared; `pre0/pre1` hold its first 8 entries (fetched a layer ahead).
 template<typename G, typename Real>
 __device__ __forceinline__ void add_minor_tau(const DevPlan<Real>& P, const BandArgs& B, const Cell<Real>& c, int q4,
-                                              const Real* __restrict__ cgp, size_t tcl, Real (&tau)[4])
+                                              const V4<Real>& pre0, const V4<Real>& pre1,
+                                              const V4<Real>* __restrict__ scal_cl, Real (&tau)[4])
 {
     const int side = c.side;
     const int nm = B.nminor[side];
     const size_t mstride = (size_t)P.ntemp * G::neta(P) * G::GW;
     const Real* km = P.kminor[side] + mstride * B.first_minor[side] + q4;
-    for (int m = 0; m < nm; ++m, km += mstride)
+    for (int m0 = 0; m0 < nm; m0 += 4)
     {
-        const MinorDev d = B.minor[side][m];
-        Real scaling = cgp[tcl * d.idx_minor];
-        if (d.flags & 1)
+        V4<Real> sc = m0 == 0 ? pre0 : (m0 == 4 ? pre1 : scal_cl[B.scal_off[side] + (m0 >> 2)]);
+        const Real* scp = &sc.x;
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
         {
-            scaling *= c.dens;
-            if (d.idx_scaling > 0)
+            if (m0 + u < nm)
             {
-                const Real x = cgp[tcl * d.idx_scaling] * c.vd;
-                scaling *= (d.flags & 2) ? ((Real)1 - x) : x;
+                Real s[4];
+                interp_minor<G>(km, c, s);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) tau[j] = fma(scp[u], s[j], tau[j]);
+                km += mstride;
             }
         }
-        Real s[4];
-        interp_minor<G>(km, c, s);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) tau[j] = fma(scaling, s[j], tau[j]);
     }
 }
 
@@ -153,13 +158,14 @@ __device__ __forceinline__ void add_minor_tau(const DevPlan<Real>& P, const Band
 template<typename G, typename Real>
 __device__ __forceinline__ void gas_tau(const DevPlan<Real>& P, const BandArgs& B, const Cell<Real>& c,
                                         const Real* __restrict__ kmaj_quad, int q4,
-                                        const Real* __restrict__ cgp, size_t tcl, Real (&tau)[4])
+                                        const V4<Real>& pre0, const V4<Real>& pre1,
+                                        const V4<Real>* __restrict__ scal_cl, Real (&tau)[4])
 {
     Real s0[4], s1[4];
     interp_major<G>(kmaj_quad, P, c, s0, s1);
 #pragma unroll
     for (int j = 0; j < 4; ++j) tau[j] = c.cm0 * s0[j] + c.cm1 * s1[j];
-    add_minor_tau<G>(P, B, c, q4, cgp, tcl, tau);
+    add_minor_tau<G>(P, B, c, q4, pre0, pre1, scal_cl, tau);
 }
 
 // interpolate1D (F90:715-734) for one band
@@ -180,6 +186,26 @@ __device__ __forceinline__ Real planck_at(const Real* __restrict__ tab, const V2
     const int i = M<Real>::as_int(pos.y);
     const Real t0 = tab[i], t1 = tab[i + 1];
     return t0 + pos.x * (t1 - t0);
+}
+
+// A resident CTA claims one scratch strip for its lifetime (grids are larger than one wave, so
+// strips are recycled as CTAs retire; which strip a CTA gets does not affect any result).
+__device__ __forceinline__ int claim_slot(int* busy, int nslots)
+{
+    __shared__ int s_slot;
+    if (threadIdx.x == 0)
+    {
+        int s = (int)((blockIdx.x * 2654435761u) % (unsigned)nslots);
+        while (atomicCAS(&busy[s], 0, 1) != 0) s = (s + 1 == nslots) ? 0 : s + 1;
+        s_slot = s;
+    }
+    __syncthreads();
+    return s_slot;
+}
+__device__ __forceinline__ void release_slot(int* busy, int slot)
+{
+    __syncthreads();
+    if (threadIdx.x == 0) atomicExch(&busy[slot], 0);
 }
 
 // sum of a quad's 4 values across the LPC lanes of a column; result valid in every lane

@@ -51,6 +51,8 @@ struct MinorSide
     std::vector<double> kminor_ref;          // reduced, reference layout (ntemp, neta, nk)
     int nk = 0;
     std::vector<double> table;               // device layout [m][it][ie][gw]
+    std::vector<int> scal_off;               // per band: first slot in the per-(column,layer) scaling vector
+    std::vector<int> slot_desc;              // per slot: index into desc, -1 = padding (slots per band padded to 4)
 };
 
 struct HostPlan
@@ -75,6 +77,7 @@ struct HostPlan
     std::vector<double> solar_source;            // (ngpt)
     double tsi = 0;
     MinorSide minor[2];                          // 0 = lower (tropo true), 1 = upper
+    int nscal = 0;                               // length of the scaling vector (max over sides, multiple of 4)
 };
 
 inline HostPlan build_host_plan(const rrtmgp_b200_kdist_file& kd, int n_avail,
@@ -320,6 +323,14 @@ inline HostPlan build_host_plan(const rrtmgp_b200_kdist_file& kd, int n_avail,
             for (int b = 0; b < nbnd; ++b)
                 for (int m : ms.by_band[b]) ms.desc[m].contributor = pos++;
         }
+        ms.scal_off.assign(nbnd, 0);
+        for (int b = 0; b < nbnd; ++b)
+        {
+            ms.scal_off[b] = (int)ms.slot_desc.size();
+            for (int m : ms.by_band[b]) ms.slot_desc.push_back(m);
+            while (ms.slot_desc.size() % 4) ms.slot_desc.push_back(-1);
+        }
+        p.nscal = std::max<int>(p.nscal, std::max<int>((int)ms.slot_desc.size(), 4));
         for (int m = 0; m < ms.n; ++m)
         {
             const int ng = ms.limits[2 * m + 1] - ms.limits[2 * m] + 1;
