@@ -219,7 +219,8 @@ def run_b200(args):
     esz = 4 if args.dtype == "f32" else 8
 
     # column shard of this rank: contiguous [c0, c1) of the x-fastest flattened domain
-    c0 = rank * args.ncol // world; c1 = (rank + 1) * args.ncol // world
+    from rte_rrtmgp_cpp_b200 import shard
+    c0, c1 = shard.shard_bounds(args.ncol, world, rank)
     ncol = c1 - c0
     nlay, nlev = args.nlay, args.nlay + 1
     base = rce_atmosphere(min(NBASE, ncol), nlay, cloudy=args.cloudy)
@@ -245,10 +246,8 @@ def run_b200(args):
         if world > 1:
             # final flux gather to rank 0 over NCCL: (rank, field, level, column-in-shard)
             nonlocal gather_buf
-            packed = torch.stack([(out_lw if w == "lw" else out_sw)[k].t for w, k in flux_names])
-            if rank == 0 and gather_buf is None:
-                gather_buf = [torch.empty_like(packed) for _ in range(world)]
-            dist.gather(packed, gather_buf if rank == 0 else None, dst=0)
+            packed = shard.pack_fields([(out_lw if w == "lw" else out_sw)[k].t for w, k in flux_names])
+            gather_buf = shard.gather_fields(packed, args.ncol, nlev, dst=0, recv=gather_buf)
 
     def barrier():
         if world > 1:

@@ -1,0 +1,67 @@
+"""Column sharding of a radiation call over the GPUs of one box.
+
+Columns are independent in every stage of the path, so a domain of `ncol` columns is cut into
+`world` contiguous shards of the x-fastest flattened domain (reference flattening:
+src_test/test_rte_rrtmgp.cpp:217); tables are replicated; there is no collective inside the
+computation.  The only exchange is the final gather of the broadband flux slabs to one rank
+(NCCL on GPUs; any torch.distributed backend works, the CPU tests use gloo).
+
+A flux field is a column-major (ncol_shard, nlev) array, i.e. a C-contiguous (nlev, ncol_shard)
+tensor.  `gather_fields` moves all fields of a rank in ONE collective; `assemble` lays the
+shards out as the reference's (ncol, nlev) column-major arrays.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def shard_bounds(ncol: int, world: int, rank: int) -> Tuple[int, int]:
+    """Contiguous shard [c0, c1) of rank `rank`; sizes differ by at most one column."""
+    if not (0 <= rank < world) or ncol < 0:
+        raise ValueError("shard_bounds: bad rank/world/ncol")
+    return rank * ncol // world, (rank + 1) * ncol // world
+
+
+def pack_fields(fields: Sequence[torch.Tensor]) -> torch.Tensor:
+    """Stack equal-sized flat flux fields into one (nfield, nlev*ncol_shard) buffer."""
+    return torch.stack([f.reshape(-1) for f in fields])
+
+
+def gather_fields(packed: torch.Tensor, ncol: int, nlev: int, dst: int = 0,
+                  recv: Optional[List[torch.Tensor]] = None) -> Optional[List[torch.Tensor]]:
+    """Gather every rank's packed fields on `dst`.  Shards may be ragged (ncol % world != 0):
+    buffers are padded to the largest shard.  Returns the per-rank buffers on dst, else None."""
+    world, rank = dist.get_world_size(), dist.get_rank()
+    nfield = packed.shape[0]
+    maxc = max(shard_bounds(ncol, world, r)[1] - shard_bounds(ncol, world, r)[0] for r in range(world))
+    c0, c1 = shard_bounds(ncol, world, rank)
+    if (c1 - c0) != maxc:
+        pad = torch.zeros((nfield, nlev * maxc), dtype=packed.dtype, device=packed.device)
+        pad.view(nfield, nlev, maxc)[:, :, :c1 - c0] = packed.view(nfield, nlev, c1 - c0)
+        packed = pad
+    if rank == dst and recv is None:
+        recv = [torch.empty_like(packed) for _ in range(world)]
+    dist.gather(packed, recv if rank == dst else None, dst=dst)
+    return recv if rank == dst else None
+
+
+def assemble(recv: Sequence[torch.Tensor], ncol: int, nlev: int) -> torch.Tensor:
+    """Per-rank (nfield, nlev*maxc) buffers -> (nfield, nlev, ncol): every field as the
+    reference's column-major (ncol, nlev) array."""
+    world = len(recv)
+    nfield = recv[0].shape[0]
+    maxc = recv[0].shape[1] // nlev
+    out = torch.empty((nfield, nlev, ncol), dtype=recv[0].dtype, device=recv[0].device)
+    for r in range(world):
+        c0, c1 = shard_bounds(ncol, world, r)
+        out[:, :, c0:c1] = recv[r].view(nfield, nlev, maxc)[:, :, :c1 - c0]
+    return out
+
+
+def domain_mean(profile_sum: torch.Tensor, ncol: int) -> torch.Tensor:
+    """All-reduce of per-rank column sums (nlev,) -> domain-mean profile on every rank."""
+    dist.all_reduce(profile_sum, op=dist.ReduceOp.SUM)
+    return profile_sum / ncol

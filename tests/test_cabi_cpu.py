@@ -1,0 +1,91 @@
+"""CPU-side checks of the C-ABI library: it loads, exports every symbol include/rrtmgp_b200.h
+declares, its host-side table preparation (RRTMGP_B200_HOST_ONLY) reproduces the reference
+constructor logic as restated by the oracle, argument errors are reported without a device, and
+device entry points fail loudly (no CPU fallback) when there is no GPU."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+from rte_rrtmgp_cpp_b200 import api, capi
+from rte_rrtmgp_cpp_b200.kdist import synthetic_kdist, synthetic_cloud_lut, REDUCED_LW_128, REDUCED_SW_112
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GASES = ["h2o", "co2", "o3", "n2o", "ch4", "n2", "o2"]
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "rrtmgp_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(rrtmgp_b200_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 30
+    L = C.CDLL(capi.LIB_PATH)
+    for name in sorted(declared):
+        assert hasattr(L, name), f"{name} declared in include/rrtmgp_b200.h but not exported"
+    assert declared == set(capi.SYMBOLS), declared ^ set(capi.SYMBOLS)
+    assert capi.lib().rrtmgp_b200_version() >= 100
+
+
+@pytest.mark.parametrize("kind,sizes", [("lw", 16), ("sw", 16), ("lw", REDUCED_LW_128), ("sw", REDUCED_SW_112)])
+@pytest.mark.parametrize("gases", [GASES, GASES + ["co", "cfc11", "cfc12", "no2"]])
+def test_host_tables_match_reference_constructor(kind, sizes, gases):
+    kd = synthetic_kdist(kind, sizes)
+    go = api.Gas_optics_rrtmgp_gpu(kd, gases, host_only=True)
+    og = O.GasOptics(kd, gases)
+    assert go.gas_names == og.gas_names
+    assert (go.get_ngpt(), go.get_nband(), go.get_nflav()) == (og.ngpt, og.nbnd, og.nflav)
+    assert np.array_equal(go.flavor, og.flavor)
+    assert np.array_equal(go.gpoint_flavor, og.gpoint_flavor)
+    assert np.array_equal(go.get_band_lims_gpoint(), og.band2gpt)
+    assert np.array_equal(go.get_gpoint_bands(), og.gpt2band)
+    assert np.array_equal(go.get_band_lims_wavenumber(), og.band_lims_wvn)
+    for side, o in ((0, og.lower), (1, og.upper)):
+        m = go.get_minor(side)
+        for k in ("idx_minor", "idx_scal", "kstart", "limits", "dens", "comp"):
+            assert np.array_equal(m[k], o[k]), (side, k)
+    assert go.get_press_ref_min() == og.press_ref_min and go.get_press_ref_max() == og.press_ref_max
+    assert go.get_temp_min() == og.temp_ref_min and go.get_temp_max() == og.temp_ref_max
+    if kind == "sw":
+        assert np.array_equal(go.solar_source, og.solar_source) and go.get_tsi() == og.get_tsi()
+        assert go.source_is_external() and not go.source_is_internal()
+    else:
+        assert go.source_is_internal()
+
+
+def test_constructor_errors_match_reference():
+    kd = synthetic_kdist("lw")
+    with pytest.raises(RuntimeError, match="required gas co2 is missing"):
+        api.Gas_optics_rrtmgp_gpu(kd, [g for g in GASES if g != "co2"], host_only=True)
+    with pytest.raises(RuntimeError):
+        O.GasOptics(kd, [g for g in GASES if g != "co2"])
+
+
+def test_argument_errors_need_no_device():
+    L = capi.lib()
+    rc = L.rrtmgp_b200_delta_scale_2str(capi.F32, 0, 4, 4, None, None, None, None)
+    assert rc == capi.E_ARG and b"ncol" in L.rrtmgp_b200_last_error()
+    rc = L.rrtmgp_b200_lw_solver_noscat(capi.F64, 4, 4, 4, 1, 7, *([None] * 8), 0, None, None, None)
+    assert rc == capi.E_ARG
+    lims = (C.c_int * 4)(1, 2, 4, 3)
+    rc = L.rrtmgp_b200_sum_byband(capi.F64, 4, 4, 4, 2, lims, C.c_void_p(8), C.c_void_p(8), None)
+    assert rc == capi.E_ARG and b"band limits" in L.rrtmgp_b200_last_error()
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU behaviour")
+def test_no_cpu_fallback_without_a_device():
+    kd = synthetic_kdist("lw")
+    with pytest.raises(RuntimeError, match="(?i)cuda"):
+        api.Gas_optics_rrtmgp_gpu(kd, GASES)                     # device tables need a GPU
+    go = api.Gas_optics_rrtmgp_gpu(kd, GASES, host_only=True)
+    concs = (C.c_void_p * go.info.ngas)(*([8] * go.info.ngas))
+    one = (C.c_int * go.info.ngas)(*([1] * go.info.ngas))
+    gc = capi.GasConcsC(go.info.ngas, concs, one, one)
+    rc = capi.lib().rrtmgp_b200_interpolation(go.h, 1, 1, C.c_void_p(8), C.c_void_p(8), C.c_void_p(8), C.byref(gc),
+                                              *([None] * 8), None)
+    assert rc == capi.E_CUDA and b"no CPU fallback" in capi.lib().rrtmgp_b200_last_error()
+    with pytest.raises(RuntimeError, match="(?i)cuda"):
+        api.Cloud_optics_gpu(synthetic_cloud_lut("lw"))
