@@ -202,6 +202,9 @@ int rrtmgp_b200_sum_byband(int dtype, int ncol, int nlev, int ngpt, int nbnd,
                            void* d_bnd_flux, void* stream);
 int rrtmgp_b200_net_flux(int dtype, size_t n, const void* d_dn, const void* d_up, void* d_net,
                          void* stream);
+/* x(icol, j) *= scale(icol), j < n2: the TSI scaling of the top-of-atmosphere source
+ * (scaling_to_subset, src_test/Radiation_solver.cu:42-70). */
+int rrtmgp_b200_scale_columns(int dtype, int ncol, int n2, void* d_x, const void* d_scale, void* stream);
 /* heating rate (not in the C++ reference; rte-rrtmgp/extensions/mo_heating_rates.F90:44-73) */
 int rrtmgp_b200_heating_rate(int dtype, int ncol, int nlay, const void* d_flux_up,
                              const void* d_flux_dn, const void* d_plev, void* d_hr, void* stream);

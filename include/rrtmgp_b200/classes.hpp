@@ -1,0 +1,704 @@
+// classes.hpp — header-only C++ mirror of the reference's L3 `_gpu` class API over the C ABI
+// (include/rrtmgp_b200.h).  Same class and method names, argument order and error behaviour as
+// the reference (paths relative to the reference root):
+//   Array_gpu<T,N>            include/Array.h:355-650          (1-based dims, owning or view)
+//   Gas_concs_gpu             include/Gas_concs.h:73-91
+//   Optical_props[_1scl|_2str]_gpu, add_to   include/Optical_props.h:165-293
+//   Source_func_lw_gpu        include/Source_functions.h:70-93
+//   Gas_optics_rrtmgp_gpu     include/Gas_optics_rrtmgp.h:293-408
+//   Cloud_optics_gpu          include/Cloud_optics.h
+//   Rte_lw_gpu / Rte_sw_gpu   include/Rte_lw.h:62-77, include/Rte_sw.h:62-80
+//   Fluxes_broadband_gpu / Fluxes_byband_gpu   include/Fluxes.h:127-210
+// Precision follows the reference switch: -DRTE_USE_SP -> Float = float (include/types.h:19-25).
+// All work is enqueued on `rrtmgp_b200::stream()` (default: the legacy default stream, like the
+// reference); nothing here computes on the host.  Link: -lrrtmgp_b200 -lcudart.
+#pragma once
+#include <cuda_runtime.h>
+#include <array>
+#include <map>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+#include "../rrtmgp_b200.h"
+
+#ifdef RTE_USE_SP
+using Float = float;
+#else
+using Float = double;
+#endif
+using Bool = signed char;
+
+namespace rrtmgp_b200 {
+inline cudaStream_t& stream() { static cudaStream_t s = nullptr; return s; }
+constexpr int dtype = sizeof(Float) == 4 ? RRTMGP_B200_F32 : RRTMGP_B200_F64;
+inline void check(int rc)
+{
+    if (rc == RRTMGP_B200_OK) return;
+    const std::string msg = rrtmgp_b200_last_error();
+    if (rc == RRTMGP_B200_E_RANGE) throw std::range_error(msg);      // src/Gas_optics_rrtmgp.cpp:812-827
+    throw std::runtime_error(msg);
+}
+inline void cuda_check(cudaError_t e) { if (e != cudaSuccess) throw std::runtime_error(cudaGetErrorString(e)); }
+}  // namespace rrtmgp_b200
+
+template<typename T, int N>
+class Array_gpu
+{
+    public:
+        Array_gpu() = default;
+        explicit Array_gpu(const std::array<int, N>& dims) { set_dims(dims); }
+        Array_gpu(T* ptr, const std::array<int, N>& dims) : dims_(dims), n_(count(dims)), p_(ptr), own_(false) {}   // view
+        Array_gpu(const std::vector<T>& host, const std::array<int, N>& dims) { set_dims(dims); copy_from(host); }
+        Array_gpu(const Array_gpu& o) { *this = o; }
+        Array_gpu(Array_gpu&& o) noexcept { *this = std::move(o); }
+        ~Array_gpu() { release(); }
+        Array_gpu& operator=(const Array_gpu& o)
+        {
+            if (this == &o) return *this;
+            set_dims(o.dims_);
+            if (n_) rrtmgp_b200::cuda_check(cudaMemcpyAsync(p_, o.p_, n_ * sizeof(T), cudaMemcpyDeviceToDevice, rrtmgp_b200::stream()));
+            return *this;
+        }
+        Array_gpu& operator=(Array_gpu&& o) noexcept
+        {
+            if (this == &o) return *this;
+            release();
+            dims_ = o.dims_; n_ = o.n_; p_ = o.p_; own_ = o.own_;
+            o.p_ = nullptr; o.n_ = 0; o.own_ = false;
+            return *this;
+        }
+        void set_dims(const std::array<int, N>& dims)
+        {
+            release();
+            dims_ = dims; n_ = count(dims); own_ = true;
+            if (n_) rrtmgp_b200::cuda_check(cudaMalloc((void**)&p_, n_ * sizeof(T)));
+        }
+        void fill(const T v)
+        {
+            std::vector<T> h(n_, v);
+            copy_from(h);
+        }
+        void copy_from(const std::vector<T>& h)
+        {
+            if (h.size() != n_) throw std::runtime_error("Array_gpu: size mismatch");
+            if (n_) rrtmgp_b200::cuda_check(cudaMemcpy(p_, h.data(), n_ * sizeof(T), cudaMemcpyHostToDevice));
+        }
+        std::vector<T> to_host() const
+        {
+            std::vector<T> h(n_);
+            rrtmgp_b200::cuda_check(cudaStreamSynchronize(rrtmgp_b200::stream()));
+            if (n_) rrtmgp_b200::cuda_check(cudaMemcpy(h.data(), p_, n_ * sizeof(T), cudaMemcpyDeviceToHost));
+            return h;
+        }
+        T* ptr() { return p_; }
+        const T* ptr() const { return p_; }
+        int dim(const int i) const { return dims_[i - 1]; }      // 1-based like the reference
+        size_t size() const { return n_; }
+        const std::array<int, N>& get_dims() const { return dims_; }
+    private:
+        static size_t count(const std::array<int, N>& d) { size_t n = 1; for (int v : d) n *= (size_t)v; return n; }
+        void release() { if (own_ && p_) cudaFree(p_); p_ = nullptr; n_ = 0; }
+        std::array<int, N> dims_{};
+        size_t n_ = 0;
+        T* p_ = nullptr;
+        bool own_ = false;
+};
+
+class Gas_concs_gpu
+{
+    public:
+        void set_vmr(const std::string& name, const Float data)
+        {
+            if (data < Float(0.) || data > Float(1.)) throw std::range_error("Gas concentration values should be between 0 and 1");
+            gas_concs_map[name] = Array_gpu<Float,2>(std::vector<Float>{data}, {1, 1});
+        }
+        void set_vmr(const std::string& name, const std::vector<Float>& data, const int ncol, const int nlay)
+        {
+            for (const Float v : data)
+                if (v < Float(0.) || v > Float(1.)) throw std::range_error("Gas concentration values should be between 0 and 1");
+            gas_concs_map[name] = Array_gpu<Float,2>(data, {ncol, nlay});
+        }
+        void set_vmr(const std::string& name, const Array_gpu<Float,2>& data) { gas_concs_map[name] = data; }   // caller validated
+        const Array_gpu<Float,2>& get_vmr(const std::string& name) const
+        {
+            auto it = gas_concs_map.find(name);
+            if (it == gas_concs_map.end()) throw std::runtime_error("Gas_concs: gas " + name + " not set");
+            return it->second;
+        }
+        bool exists(const std::string& name) const { return gas_concs_map.count(name) != 0; }
+        std::vector<std::string> names() const { std::vector<std::string> n; for (auto& kv : gas_concs_map) n.push_back(kv.first); return n; }
+    private:
+        std::map<std::string, Array_gpu<Float,2>> gas_concs_map;
+};
+
+// band <-> g-point bookkeeping (src/Optical_props.cpp:31-72); limits are (2, nbnd), 1-based
+class Optical_props_gpu
+{
+    public:
+        Optical_props_gpu() = default;
+        Optical_props_gpu(const std::vector<Float>& band_lims_wvn, const std::vector<int>& band_lims_gpt)
+            : band_lims_wvn(band_lims_wvn), band2gpt(band_lims_gpt) { init(); }
+        explicit Optical_props_gpu(const std::vector<Float>& band_lims_wvn) : band_lims_wvn(band_lims_wvn)
+        {
+            for (int b = 1; b <= (int)band_lims_wvn.size() / 2; ++b) { band2gpt.push_back(b); band2gpt.push_back(b); }
+            init();
+        }
+        virtual ~Optical_props_gpu() = default;
+        int get_nband() const { return (int)band2gpt.size() / 2; }
+        int get_ngpt() const { return ngpt; }
+        const std::vector<int>& get_band_lims_gpoint() const { return band2gpt; }
+        const std::vector<Float>& get_band_lims_wavenumber() const { return band_lims_wvn; }
+        const std::vector<int>& get_gpoint_bands() const { return gpt2band; }
+    protected:
+        void init()
+        {
+            ngpt = 0;
+            for (size_t i = 1; i < band2gpt.size(); i += 2) ngpt = std::max(ngpt, band2gpt[i]);
+            gpt2band.assign(ngpt, 0);
+            for (int b = 0; b < get_nband(); ++b)
+                for (int g = band2gpt[2 * b]; g <= band2gpt[2 * b + 1]; ++g) gpt2band[g - 1] = b + 1;
+        }
+        std::vector<Float> band_lims_wvn;
+        std::vector<int> band2gpt, gpt2band;
+        int ngpt = 0;
+};
+
+class Optical_props_arry_gpu : public Optical_props_gpu
+{
+    public:
+        Optical_props_arry_gpu(const Optical_props_gpu& o) : Optical_props_gpu(o) {}
+        virtual Array_gpu<Float,3>& get_tau() = 0;
+        virtual Array_gpu<Float,3>& get_ssa() = 0;
+        virtual Array_gpu<Float,3>& get_g() = 0;
+        virtual const Array_gpu<Float,3>& get_tau() const = 0;
+        virtual const Array_gpu<Float,3>& get_ssa() const = 0;
+        virtual const Array_gpu<Float,3>& get_g() const = 0;
+        virtual void delta_scale(const Array_gpu<Float,3>& forward_frac = Array_gpu<Float,3>()) = 0;
+        virtual int get_ncol() const = 0;
+        virtual int get_nlay() const = 0;
+};
+
+class Optical_props_1scl_gpu : public Optical_props_arry_gpu
+{
+    public:
+        Optical_props_1scl_gpu(const int ncol, const int nlay, const Optical_props_gpu& o)
+            : Optical_props_arry_gpu(o), tau({ncol, nlay, o.get_ngpt()}) {}
+        Array_gpu<Float,3>& get_tau() override { return tau; }
+        const Array_gpu<Float,3>& get_tau() const override { return tau; }
+        Array_gpu<Float,3>& get_ssa() override { throw std::runtime_error("ssa is not available in this class"); }
+        Array_gpu<Float,3>& get_g() override { throw std::runtime_error("g is not available in this class"); }
+        const Array_gpu<Float,3>& get_ssa() const override { throw std::runtime_error("ssa is not available in this class"); }
+        const Array_gpu<Float,3>& get_g() const override { throw std::runtime_error("g is not available in this class"); }
+        void delta_scale(const Array_gpu<Float,3>& = Array_gpu<Float,3>()) override {}
+        int get_ncol() const override { return tau.dim(1); }
+        int get_nlay() const override { return tau.dim(2); }
+    private:
+        Array_gpu<Float,3> tau;
+};
+
+class Optical_props_2str_gpu : public Optical_props_arry_gpu
+{
+    public:
+        Optical_props_2str_gpu(const int ncol, const int nlay, const Optical_props_gpu& o)
+            : Optical_props_arry_gpu(o), tau({ncol, nlay, o.get_ngpt()}), ssa({ncol, nlay, o.get_ngpt()}), g({ncol, nlay, o.get_ngpt()}) {}
+        Array_gpu<Float,3>& get_tau() override { return tau; }
+        Array_gpu<Float,3>& get_ssa() override { return ssa; }
+        Array_gpu<Float,3>& get_g() override { return g; }
+        const Array_gpu<Float,3>& get_tau() const override { return tau; }
+        const Array_gpu<Float,3>& get_ssa() const override { return ssa; }
+        const Array_gpu<Float,3>& get_g() const override { return g; }
+        void delta_scale(const Array_gpu<Float,3>& = Array_gpu<Float,3>()) override     // src/Optical_props.cpp:207-216
+        {
+            rrtmgp_b200::check(rrtmgp_b200_delta_scale_2str(rrtmgp_b200::dtype, tau.dim(1), tau.dim(2), tau.dim(3),
+                                                            tau.ptr(), ssa.ptr(), g.ptr(), rrtmgp_b200::stream()));
+        }
+        int get_ncol() const override { return tau.dim(1); }
+        int get_nlay() const override { return tau.dim(2); }
+    private:
+        Array_gpu<Float,3> tau, ssa, g;
+};
+
+// Optical_props increment (src/Optical_props.cpp:219-268)
+inline void add_to(Optical_props_1scl_gpu& op_inout, const Optical_props_1scl_gpu& op_in)
+{
+    const int ncol = op_inout.get_ncol(), nlay = op_inout.get_nlay(), ngpt = op_inout.get_ngpt();
+    if (ngpt == op_in.get_ngpt())
+        rrtmgp_b200::check(rrtmgp_b200_increment_1scl(rrtmgp_b200::dtype, ncol, nlay, ngpt, op_inout.get_tau().ptr(),
+                                                      op_in.get_tau().ptr(), rrtmgp_b200::stream()));
+    else
+    {
+        if (op_in.get_ngpt() != op_inout.get_nband())
+            throw std::runtime_error("Cannot add optical properties with incompatible band - gpoint combination");
+        rrtmgp_b200::check(rrtmgp_b200_increment_1scl_bybnd(rrtmgp_b200::dtype, ncol, nlay, ngpt, op_inout.get_tau().ptr(),
+                op_in.get_tau().ptr(), op_inout.get_nband(), op_inout.get_band_lims_gpoint().data(), rrtmgp_b200::stream()));
+    }
+}
+inline void add_to(Optical_props_2str_gpu& op_inout, const Optical_props_2str_gpu& op_in)
+{
+    const int ncol = op_inout.get_ncol(), nlay = op_inout.get_nlay(), ngpt = op_inout.get_ngpt();
+    if (ngpt == op_in.get_ngpt())
+        rrtmgp_b200::check(rrtmgp_b200_increment_2str(rrtmgp_b200::dtype, ncol, nlay, ngpt, op_inout.get_tau().ptr(),
+                op_inout.get_ssa().ptr(), op_inout.get_g().ptr(), op_in.get_tau().ptr(), op_in.get_ssa().ptr(),
+                op_in.get_g().ptr(), rrtmgp_b200::stream()));
+    else
+    {
+        if (op_in.get_ngpt() != op_inout.get_nband())
+            throw std::runtime_error("Cannot add optical properties with incompatible band - gpoint combination");
+        rrtmgp_b200::check(rrtmgp_b200_increment_2str_bybnd(rrtmgp_b200::dtype, ncol, nlay, ngpt, op_inout.get_tau().ptr(),
+                op_inout.get_ssa().ptr(), op_inout.get_g().ptr(), op_in.get_tau().ptr(), op_in.get_ssa().ptr(),
+                op_in.get_g().ptr(), op_inout.get_nband(), op_inout.get_band_lims_gpoint().data(), rrtmgp_b200::stream()));
+    }
+}
+
+class Source_func_lw_gpu : public Optical_props_gpu
+{
+    public:
+        Source_func_lw_gpu(const int n_col, const int n_lay, const Optical_props_gpu& o)
+            : Optical_props_gpu(o), sfc_source({n_col, o.get_ngpt()}), sfc_source_jac({n_col, o.get_ngpt()}),
+              lay_source({n_col, n_lay, o.get_ngpt()}), lev_source({n_col, n_lay + 1, o.get_ngpt()}) {}
+        Array_gpu<Float,2>& get_sfc_source() { return sfc_source; }
+        Array_gpu<Float,2>& get_sfc_source_jac() { return sfc_source_jac; }
+        Array_gpu<Float,3>& get_lay_source() { return lay_source; }
+        Array_gpu<Float,3>& get_lev_source() { return lev_source; }
+        const Array_gpu<Float,2>& get_sfc_source() const { return sfc_source; }
+        const Array_gpu<Float,2>& get_sfc_source_jac() const { return sfc_source_jac; }
+        const Array_gpu<Float,3>& get_lay_source() const { return lay_source; }
+        const Array_gpu<Float,3>& get_lev_source() const { return lev_source; }
+    private:
+        Array_gpu<Float,2> sfc_source, sfc_source_jac;
+        Array_gpu<Float,3> lay_source, lev_source;
+};
+
+namespace rrtmgp_b200 {
+// Gas_concs -> the C struct, in the order of the k-distribution object's gas list
+struct Concs_view
+{
+    std::vector<const void*> p; std::vector<int> nc, nl; rrtmgp_b200_gas_concs c{};
+    Concs_view(const Gas_concs_gpu& g, const std::vector<std::string>& names)
+    {
+        for (auto& n : names) { const auto& a = g.get_vmr(n); p.push_back(a.ptr()); nc.push_back(a.dim(1)); nl.push_back(a.dim(2)); }
+        c.ngas = (int)names.size(); c.d_vmr = p.data(); c.vmr_ncol = nc.data(); c.vmr_nlay = nl.data();
+    }
+};
+inline std::string pad_names(const std::vector<std::string>& names, int len)
+{
+    std::string s;
+    for (auto n : names) { n.resize(len, ' '); s += n; }
+    return s;
+}
+}  // namespace rrtmgp_b200
+
+class Gas_optics_rrtmgp_gpu : public Optical_props_gpu
+{
+    public:
+        // The reference constructor takes the ~32 file variables as Array objects
+        // (include/Gas_optics_rrtmgp.h:293-364); here they arrive in one struct with the same
+        // names and file dimension orders (include/rrtmgp_b200_tables.h).
+        Gas_optics_rrtmgp_gpu(const Gas_concs_gpu& available_gases, const rrtmgp_b200_kdist_file& kdist)
+        {
+            const auto names = available_gases.names();
+            const std::string blk = rrtmgp_b200::pad_names(names, 32);
+            rrtmgp_b200::check(rrtmgp_b200_gas_optics_create(&kdist, (int)names.size(), blk.c_str(), 32, rrtmgp_b200::dtype, &h));
+            rrtmgp_b200::check(rrtmgp_b200_gas_optics_get_info(h, &info));
+            band2gpt.resize(2 * info.nbnd); gpt2band.resize(info.ngpt);
+            std::vector<double> wvn(2 * info.nbnd), sol(info.ngpt);
+            std::vector<char> gn((size_t)info.ngas * 32);
+            rrtmgp_b200::check(rrtmgp_b200_gas_optics_get_tables(h, band2gpt.data(), wvn.data(), gpt2band.data(), nullptr,
+                                                                 nullptr, gn.data(), 32, sol.data()));
+            band_lims_wvn.assign(wvn.begin(), wvn.end());
+            init();
+            for (int i = 0; i < info.ngas; ++i)
+            {
+                std::string s(gn.data() + (size_t)i * 32, 32);
+                gas_names.push_back(s.substr(0, s.find_last_not_of(' ') + 1));
+            }
+        }
+        ~Gas_optics_rrtmgp_gpu() { rrtmgp_b200_gas_optics_destroy(h); }
+        Gas_optics_rrtmgp_gpu(const Gas_optics_rrtmgp_gpu&) = delete;
+        Gas_optics_rrtmgp_gpu& operator=(const Gas_optics_rrtmgp_gpu&) = delete;
+
+        static void get_col_dry(Array_gpu<Float,2>& col_dry, const Array_gpu<Float,2>& vmr_h2o, const Array_gpu<Float,2>& plev)
+        {
+            rrtmgp_b200::check(rrtmgp_b200_get_col_dry(rrtmgp_b200::dtype, vmr_h2o.dim(1), vmr_h2o.dim(2), vmr_h2o.ptr(),
+                                                       plev.ptr(), col_dry.ptr(), rrtmgp_b200::stream()));
+        }
+        bool source_is_internal() const { return info.is_longwave != 0; }
+        bool source_is_external() const { return info.is_longwave == 0; }
+        Float get_press_ref_min() const { return (Float)info.press_ref_min; }
+        Float get_press_ref_max() const { return (Float)info.press_ref_max; }
+        Float get_temp_min() const { return (Float)info.temp_ref_min; }
+        Float get_temp_max() const { return (Float)info.temp_ref_max; }
+        Float get_tsi() const { return (Float)info.tsi; }
+        rrtmgp_b200_gas_optics* handle() const { return h; }
+        const std::vector<std::string>& get_gas_names() const { return gas_names; }
+
+        // Longwave (include/Gas_optics_rrtmgp.h:389-398).  Range checks as the CPU path throws them.
+        void gas_optics(const Array_gpu<Float,2>& play, const Array_gpu<Float,2>& plev, const Array_gpu<Float,2>& tlay,
+                        const Array_gpu<Float,1>& tsfc, const Gas_concs_gpu& gas_desc,
+                        std::unique_ptr<Optical_props_arry_gpu>& optical_props, Source_func_lw_gpu& sources,
+                        const Array_gpu<Float,2>& col_dry, const Array_gpu<Float,2>& tlev)
+        {
+            validate(play, "play", true); validate(plev, "plev", true); validate(tlay, "tlay", false);
+            validate(tlev, "tlev", false); validate(tsfc, "tsfc", false);
+            rrtmgp_b200::Concs_view cv(gas_desc, gas_names);
+            rrtmgp_b200::check(rrtmgp_b200_gas_optics_lw(h, play.dim(1), play.dim(2), play.ptr(), plev.ptr(), tlay.ptr(),
+                    tsfc.ptr(), tlev.ptr(), col_dry.size() ? col_dry.ptr() : nullptr, &cv.c, optical_props->get_tau().ptr(),
+                    sources.get_lay_source().ptr(), sources.get_lev_source().ptr(), sources.get_sfc_source().ptr(),
+                    sources.get_sfc_source_jac().ptr(), rrtmgp_b200::stream()));
+        }
+        // Shortwave (include/Gas_optics_rrtmgp.h:401-408)
+        void gas_optics(const Array_gpu<Float,2>& play, const Array_gpu<Float,2>& plev, const Array_gpu<Float,2>& tlay,
+                        const Gas_concs_gpu& gas_desc, std::unique_ptr<Optical_props_arry_gpu>& optical_props,
+                        Array_gpu<Float,2>& toa_src, const Array_gpu<Float,2>& col_dry)
+        {
+            validate(play, "play", true); validate(plev, "plev", true); validate(tlay, "tlay", false);
+            rrtmgp_b200::Concs_view cv(gas_desc, gas_names);
+            const bool two = dynamic_cast<Optical_props_2str_gpu*>(optical_props.get()) != nullptr;
+            rrtmgp_b200::check(rrtmgp_b200_gas_optics_sw(h, play.dim(1), play.dim(2), play.ptr(), plev.ptr(), tlay.ptr(),
+                    col_dry.size() ? col_dry.ptr() : nullptr, &cv.c, optical_props->get_tau().ptr(),
+                    two ? optical_props->get_ssa().ptr() : nullptr, two ? optical_props->get_g().ptr() : nullptr,
+                    toa_src.ptr(), rrtmgp_b200::stream()));
+        }
+    private:
+        template<int N> void validate(const Array_gpu<Float,N>& a, const char* name, bool pressure) const
+        {
+            const double lo = pressure ? info.press_ref_min : info.temp_ref_min, hi = pressure ? info.press_ref_max : info.temp_ref_max;
+            rrtmgp_b200::check(rrtmgp_b200_check_range(rrtmgp_b200::dtype, a.size(), a.ptr(), lo, hi, name, rrtmgp_b200::stream()));
+        }
+        rrtmgp_b200_gas_optics* h = nullptr;
+        rrtmgp_b200_gas_optics_info info{};
+        std::vector<std::string> gas_names;
+};
+
+class Cloud_optics_gpu : public Optical_props_gpu
+{
+    public:
+        explicit Cloud_optics_gpu(const rrtmgp_b200_cloud_file& lut)
+            : Optical_props_gpu(std::vector<Float>(lut.bnd_limits_wavenumber, lut.bnd_limits_wavenumber + 2 * lut.n_band))
+        { rrtmgp_b200::check(rrtmgp_b200_cloud_optics_create(&lut, rrtmgp_b200::dtype, &h)); }
+        ~Cloud_optics_gpu() { rrtmgp_b200_cloud_optics_destroy(h); }
+        Cloud_optics_gpu(const Cloud_optics_gpu&) = delete;
+        void cloud_optics(const Array_gpu<Float,2>& clwp, const Array_gpu<Float,2>& ciwp, const Array_gpu<Float,2>& reliq,
+                          const Array_gpu<Float,2>& deice, Optical_props_2str_gpu& optical_props)
+        {
+            rrtmgp_b200::check(rrtmgp_b200_cloud_optics_2str(h, clwp.dim(1), clwp.dim(2), clwp.ptr(), ciwp.ptr(), reliq.ptr(),
+                    deice.ptr(), optical_props.get_tau().ptr(), optical_props.get_ssa().ptr(), optical_props.get_g().ptr(),
+                    rrtmgp_b200::stream()));
+        }
+        void cloud_optics(const Array_gpu<Float,2>& clwp, const Array_gpu<Float,2>& ciwp, const Array_gpu<Float,2>& reliq,
+                          const Array_gpu<Float,2>& deice, Optical_props_1scl_gpu& optical_props)
+        {
+            rrtmgp_b200::check(rrtmgp_b200_cloud_optics_1scl(h, clwp.dim(1), clwp.dim(2), clwp.ptr(), ciwp.ptr(), reliq.ptr(),
+                    deice.ptr(), optical_props.get_tau().ptr(), rrtmgp_b200::stream()));
+        }
+        rrtmgp_b200_cloud_optics* handle() const { return h; }
+    private:
+        rrtmgp_b200_cloud_optics* h = nullptr;
+};
+
+class Rte_lw_gpu
+{
+    public:
+        static void expand_and_transpose(const std::unique_ptr<Optical_props_arry_gpu>& ops, const Array_gpu<Float,2>& arr_in,
+                                         Array_gpu<Float,2>& arr_out)
+        {
+            rrtmgp_b200::check(rrtmgp_b200_expand_and_transpose(rrtmgp_b200::dtype, arr_in.dim(2), arr_in.dim(1), ops->get_ngpt(),
+                    ops->get_band_lims_gpoint().data(), arr_in.ptr(), arr_out.ptr(), rrtmgp_b200::stream()));
+        }
+        // include/Rte_lw.h:62-77; broadband iff gpt_flux_up.dim(3) == 1 (src/Rte_lw.cpp:170)
+        static void rte_lw(const std::unique_ptr<Optical_props_arry_gpu>& optical_props, const Bool top_at_1,
+                           const Source_func_lw_gpu& sources, const Array_gpu<Float,2>& sfc_emis,
+                           const Array_gpu<Float,2>& inc_flux, Array_gpu<Float,3>& gpt_flux_up, Array_gpu<Float,3>& gpt_flux_dn,
+                           const int n_gauss_angles)
+        {
+            const int ncol = optical_props->get_ncol(), nlay = optical_props->get_nlay(), ngpt = optical_props->get_ngpt();
+            Array_gpu<Float,2> emis_gpt({ncol, ngpt});
+            expand_and_transpose(optical_props, sfc_emis, emis_gpt);
+            rrtmgp_b200::check(rrtmgp_b200_lw_solver_noscat(rrtmgp_b200::dtype, ncol, nlay, ngpt, top_at_1, n_gauss_angles,
+                    optical_props->get_tau().ptr(), sources.get_lay_source().ptr(), sources.get_lev_source().ptr(),
+                    emis_gpt.ptr(), sources.get_sfc_source().ptr(), inc_flux.size() ? inc_flux.ptr() : nullptr,
+                    gpt_flux_up.ptr(), gpt_flux_dn.ptr(), gpt_flux_up.dim(3) == 1, nullptr, nullptr, rrtmgp_b200::stream()));
+        }
+};
+
+class Rte_sw_gpu
+{
+    public:
+        // include/Rte_sw.h:62-80; has_dif_bc iff inc_flux_dif.size() > 0
+        static void rte_sw(const std::unique_ptr<Optical_props_arry_gpu>& optical_props, const Bool top_at_1,
+                           const Array_gpu<Float,1>& mu0, const Array_gpu<Float,2>& inc_flux_dir,
+                           const Array_gpu<Float,2>& sfc_alb_dir, const Array_gpu<Float,2>& sfc_alb_dif,
+                           const Array_gpu<Float,2>& inc_flux_dif, Array_gpu<Float,3>& gpt_flux_up,
+                           Array_gpu<Float,3>& gpt_flux_dn, Array_gpu<Float,3>& gpt_flux_dir)
+        {
+            const int ncol = optical_props->get_ncol(), nlay = optical_props->get_nlay(), ngpt = optical_props->get_ngpt();
+            Array_gpu<Float,2> a_dir({ncol, ngpt}), a_dif({ncol, ngpt});
+            Rte_lw_gpu::expand_and_transpose(optical_props, sfc_alb_dir, a_dir);
+            Rte_lw_gpu::expand_and_transpose(optical_props, sfc_alb_dif, a_dif);
+            rrtmgp_b200::check(rrtmgp_b200_sw_solver_2stream(rrtmgp_b200::dtype, ncol, nlay, ngpt, top_at_1,
+                    optical_props->get_tau().ptr(), optical_props->get_ssa().ptr(), optical_props->get_g().ptr(), mu0.ptr(),
+                    a_dir.ptr(), a_dif.ptr(), inc_flux_dir.ptr(), inc_flux_dif.size() ? inc_flux_dif.ptr() : nullptr,
+                    gpt_flux_up.ptr(), gpt_flux_dn.ptr(), gpt_flux_dir.ptr(), gpt_flux_up.dim(3) == 1, rrtmgp_b200::stream()));
+        }
+};
+
+class Fluxes_broadband_gpu
+{
+    public:
+        Fluxes_broadband_gpu(const int ncol, const int nlev)
+            : flux_up({ncol, nlev}), flux_dn({ncol, nlev}), flux_dn_dir({ncol, nlev}), flux_net({ncol, nlev}) {}
+        virtual ~Fluxes_broadband_gpu() = default;
+        virtual void reduce(const Array_gpu<Float,3>& gpt_flux_up, const Array_gpu<Float,3>& gpt_flux_dn,
+                            const std::unique_ptr<Optical_props_arry_gpu>& spectral_disc, const Bool top_at_1)
+        {
+            sum(gpt_flux_up, flux_up); sum(gpt_flux_dn, flux_dn); net_flux();
+        }
+        virtual void reduce(const Array_gpu<Float,3>& gpt_flux_up, const Array_gpu<Float,3>& gpt_flux_dn,
+                            const Array_gpu<Float,3>& gpt_flux_dn_dir,
+                            const std::unique_ptr<Optical_props_arry_gpu>& spectral_disc, const Bool top_at_1)
+        {
+            reduce(gpt_flux_up, gpt_flux_dn, spectral_disc, top_at_1);
+            sum(gpt_flux_dn_dir, flux_dn_dir);
+        }
+        void net_flux()
+        {
+            rrtmgp_b200::check(rrtmgp_b200_net_flux(rrtmgp_b200::dtype, flux_up.size(), flux_dn.ptr(), flux_up.ptr(),
+                                                    flux_net.ptr(), rrtmgp_b200::stream()));
+        }
+        Array_gpu<Float,2>& get_flux_up() { return flux_up; }
+        Array_gpu<Float,2>& get_flux_dn() { return flux_dn; }
+        Array_gpu<Float,2>& get_flux_dn_dir() { return flux_dn_dir; }
+        Array_gpu<Float,2>& get_flux_net() { return flux_net; }
+    protected:
+        static void sum(const Array_gpu<Float,3>& g, Array_gpu<Float,2>& f)
+        {
+            rrtmgp_b200::check(rrtmgp_b200_sum_broadband(rrtmgp_b200::dtype, g.dim(1), g.dim(2), g.dim(3), g.ptr(), f.ptr(),
+                                                         rrtmgp_b200::stream()));
+        }
+        Array_gpu<Float,2> flux_up, flux_dn, flux_dn_dir, flux_net;
+};
+
+class Fluxes_byband_gpu : public Fluxes_broadband_gpu
+{
+    public:
+        Fluxes_byband_gpu(const int ncol, const int nlev, const int nbnd)
+            : Fluxes_broadband_gpu(ncol, nlev), bnd_flux_up({ncol, nlev, nbnd}), bnd_flux_dn({ncol, nlev, nbnd}),
+              bnd_flux_dn_dir({ncol, nlev, nbnd}), bnd_flux_net({ncol, nlev, nbnd}) {}
+        void reduce(const Array_gpu<Float,3>& gpt_flux_up, const Array_gpu<Float,3>& gpt_flux_dn,
+                    const std::unique_ptr<Optical_props_arry_gpu>& spectral_disc, const Bool top_at_1) override
+        {
+            Fluxes_broadband_gpu::reduce(gpt_flux_up, gpt_flux_dn, spectral_disc, top_at_1);
+            sumb(gpt_flux_up, bnd_flux_up, spectral_disc); sumb(gpt_flux_dn, bnd_flux_dn, spectral_disc);
+            rrtmgp_b200::check(rrtmgp_b200_net_flux(rrtmgp_b200::dtype, bnd_flux_up.size(), bnd_flux_dn.ptr(), bnd_flux_up.ptr(),
+                                                    bnd_flux_net.ptr(), rrtmgp_b200::stream()));
+        }
+        void reduce(const Array_gpu<Float,3>& gpt_flux_up, const Array_gpu<Float,3>& gpt_flux_dn,
+                    const Array_gpu<Float,3>& gpt_flux_dn_dir,
+                    const std::unique_ptr<Optical_props_arry_gpu>& spectral_disc, const Bool top_at_1) override
+        {
+            reduce(gpt_flux_up, gpt_flux_dn, spectral_disc, top_at_1);
+            sum(gpt_flux_dn_dir, flux_dn_dir); sumb(gpt_flux_dn_dir, bnd_flux_dn_dir, spectral_disc);
+        }
+        Array_gpu<Float,3>& get_bnd_flux_up() { return bnd_flux_up; }
+        Array_gpu<Float,3>& get_bnd_flux_dn() { return bnd_flux_dn; }
+        Array_gpu<Float,3>& get_bnd_flux_dn_dir() { return bnd_flux_dn_dir; }
+        Array_gpu<Float,3>& get_bnd_flux_net() { return bnd_flux_net; }
+    private:
+        static void sumb(const Array_gpu<Float,3>& g, Array_gpu<Float,3>& f, const std::unique_ptr<Optical_props_arry_gpu>& d)
+        {
+            rrtmgp_b200::check(rrtmgp_b200_sum_byband(rrtmgp_b200::dtype, g.dim(1), g.dim(2), g.dim(3), d->get_nband(),
+                    d->get_band_lims_gpoint().data(), g.ptr(), f.ptr(), rrtmgp_b200::stream()));
+        }
+        Array_gpu<Float,3> bnd_flux_up, bnd_flux_dn, bnd_flux_dn_dir, bnd_flux_net;
+};
+
+// ---- Radiation_solver_{longwave,shortwave}::solve_gpu (include_test/Radiation_solver.h:73-88,176-199;
+// src_test/Radiation_solver.cu:419-657,690-950).  Same switches and argument order (aerosols are out of
+// scope).  With switch_output_optical=false the whole chain runs in the fused band
+// kernels (one C-ABI call); with it true the stage-by-stage class path runs so tau/sources are returned.
+class Radiation_solver_longwave
+{
+    public:
+        Radiation_solver_longwave(const Gas_concs_gpu& gas_concs, const rrtmgp_b200_kdist_file& kdist,
+                                  const rrtmgp_b200_cloud_file* cloud = nullptr)
+            : kdist_gpu(std::make_unique<Gas_optics_rrtmgp_gpu>(gas_concs, kdist))
+        { if (cloud) cloud_optics_gpu = std::make_unique<Cloud_optics_gpu>(*cloud); }
+
+        int get_n_gpt_gpu() const { return kdist_gpu->get_ngpt(); }
+        int get_n_bnd_gpu() const { return kdist_gpu->get_nband(); }
+        const std::vector<int>& get_band_lims_gpoint_gpu() const { return kdist_gpu->get_band_lims_gpoint(); }
+        const std::vector<Float>& get_band_lims_wavenumber_gpu() const { return kdist_gpu->get_band_lims_wavenumber(); }
+        Gas_optics_rrtmgp_gpu& get_kdist_gpu() { return *kdist_gpu; }
+        void set_n_gauss_angles(const int n) { n_gauss_angles = n; }
+
+        void solve_gpu(const bool switch_fluxes, const bool switch_cloud_optics, const bool switch_output_optical,
+                       const bool switch_output_bnd_fluxes, const Gas_concs_gpu& gas_concs,
+                       const Array_gpu<Float,2>& p_lay, const Array_gpu<Float,2>& p_lev,
+                       const Array_gpu<Float,2>& t_lay, const Array_gpu<Float,2>& t_lev,
+                       const Array_gpu<Float,2>& col_dry, const Array_gpu<Float,1>& t_sfc, const Array_gpu<Float,2>& emis_sfc,
+                       const Array_gpu<Float,2>& lwp, const Array_gpu<Float,2>& iwp,
+                       const Array_gpu<Float,2>& rel, const Array_gpu<Float,2>& dei,
+                       Array_gpu<Float,3>& tau, Array_gpu<Float,3>& lay_source, Array_gpu<Float,3>& lev_source,
+                       Array_gpu<Float,2>& sfc_source,
+                       Array_gpu<Float,2>& lw_flux_up, Array_gpu<Float,2>& lw_flux_dn, Array_gpu<Float,2>& lw_flux_net,
+                       Array_gpu<Float,3>& lw_bnd_flux_up, Array_gpu<Float,3>& lw_bnd_flux_dn, Array_gpu<Float,3>& lw_bnd_flux_net)
+        {
+            const int n_col = p_lay.dim(1), n_lay = p_lay.dim(2), n_lev = p_lev.dim(2);
+            if (switch_cloud_optics && !cloud_optics_gpu) throw std::runtime_error("cloud optics requested without cloud tables");
+            if (!switch_output_optical)
+            {
+                if (!switch_fluxes) return;
+                rrtmgp_b200::Concs_view cv(gas_concs, kdist_gpu->get_gas_names());
+                rrtmgp_b200_columns c{};
+                c.ncol = n_col; c.nlay = n_lay; c.top_at_1 = -1;
+                c.d_play = p_lay.ptr(); c.d_plev = p_lev.ptr(); c.d_tlay = t_lay.ptr(); c.d_tlev = t_lev.ptr();
+                c.d_tsfc = t_sfc.ptr(); c.d_col_dry = col_dry.size() ? col_dry.ptr() : nullptr; c.concs = cv.c;
+                c.d_sfc_emis = emis_sfc.ptr(); c.n_gauss_angles = n_gauss_angles;
+                if (switch_cloud_optics)
+                { c.cloud = cloud_optics_gpu->handle(); c.d_lwp = lwp.ptr(); c.d_iwp = iwp.ptr(); c.d_rel = rel.ptr(); c.d_dei = dei.ptr(); }
+                rrtmgp_b200_fluxes f{};
+                f.d_flux_up = lw_flux_up.ptr(); f.d_flux_dn = lw_flux_dn.ptr(); f.d_flux_net = lw_flux_net.ptr();
+                if (switch_output_bnd_fluxes)
+                { f.d_bnd_flux_up = lw_bnd_flux_up.ptr(); f.d_bnd_flux_dn = lw_bnd_flux_dn.ptr(); f.d_bnd_flux_net = lw_bnd_flux_net.ptr(); }
+                rrtmgp_b200::check(rrtmgp_b200_lw_fluxes(kdist_gpu->handle(), &c, &f, rrtmgp_b200::stream()));
+                return;
+            }
+            // staged path: gas_optics -> [cloud_optics -> add_to] -> rte_lw -> reduce
+            std::unique_ptr<Optical_props_arry_gpu> optical_props = std::make_unique<Optical_props_1scl_gpu>(n_col, n_lay, *kdist_gpu);
+            Source_func_lw_gpu sources(n_col, n_lay, *kdist_gpu);
+            kdist_gpu->gas_optics(p_lay, p_lev, t_lay, t_sfc, gas_concs, optical_props, sources, col_dry, t_lev);
+            if (switch_cloud_optics)
+            {
+                Optical_props_1scl_gpu clouds(n_col, n_lay, *cloud_optics_gpu);
+                cloud_optics_gpu->cloud_optics(lwp, iwp, rel, dei, clouds);
+                add_to(dynamic_cast<Optical_props_1scl_gpu&>(*optical_props), clouds);
+            }
+            tau = optical_props->get_tau(); lay_source = sources.get_lay_source();
+            lev_source = sources.get_lev_source(); sfc_source = sources.get_sfc_source();
+            if (!switch_fluxes) return;
+            const std::vector<Float> pl = top_probe(p_lay);
+            const Bool top_at_1 = pl[0] < pl[1];
+            Array_gpu<Float,3> gpt_flux_up({n_col, n_lev, get_n_gpt_gpu()}), gpt_flux_dn({n_col, n_lev, get_n_gpt_gpu()});
+            Rte_lw_gpu::rte_lw(optical_props, top_at_1, sources, emis_sfc, Array_gpu<Float,2>(), gpt_flux_up, gpt_flux_dn, n_gauss_angles);
+            std::unique_ptr<Fluxes_broadband_gpu> fl;
+            if (switch_output_bnd_fluxes) fl = std::make_unique<Fluxes_byband_gpu>(n_col, n_lev, get_n_bnd_gpu());
+            else fl = std::make_unique<Fluxes_broadband_gpu>(n_col, n_lev);
+            fl->reduce(gpt_flux_up, gpt_flux_dn, optical_props, top_at_1);
+            lw_flux_up = fl->get_flux_up(); lw_flux_dn = fl->get_flux_dn(); lw_flux_net = fl->get_flux_net();
+            if (switch_output_bnd_fluxes)
+            {
+                auto& fb = dynamic_cast<Fluxes_byband_gpu&>(*fl);
+                lw_bnd_flux_up = fb.get_bnd_flux_up(); lw_bnd_flux_dn = fb.get_bnd_flux_dn(); lw_bnd_flux_net = fb.get_bnd_flux_net();
+            }
+        }
+        // p_lay(1,1) and p_lay(1,n_lay), as src_test/Radiation_solver.cu:442 reads them
+        static std::vector<Float> top_probe(const Array_gpu<Float,2>& p_lay)
+        {
+            std::vector<Float> v(2);
+            rrtmgp_b200::cuda_check(cudaStreamSynchronize(rrtmgp_b200::stream()));
+            rrtmgp_b200::cuda_check(cudaMemcpy(&v[0], p_lay.ptr(), sizeof(Float), cudaMemcpyDeviceToHost));
+            rrtmgp_b200::cuda_check(cudaMemcpy(&v[1], p_lay.ptr() + (size_t)(p_lay.dim(2) - 1) * p_lay.dim(1), sizeof(Float), cudaMemcpyDeviceToHost));
+            return v;
+        }
+    private:
+        std::unique_ptr<Gas_optics_rrtmgp_gpu> kdist_gpu;
+        std::unique_ptr<Cloud_optics_gpu> cloud_optics_gpu;
+        int n_gauss_angles = 1;
+};
+
+class Radiation_solver_shortwave
+{
+    public:
+        Radiation_solver_shortwave(const Gas_concs_gpu& gas_concs, const rrtmgp_b200_kdist_file& kdist,
+                                   const rrtmgp_b200_cloud_file* cloud = nullptr)
+            : kdist_gpu(std::make_unique<Gas_optics_rrtmgp_gpu>(gas_concs, kdist))
+        { if (cloud) cloud_optics_gpu = std::make_unique<Cloud_optics_gpu>(*cloud); }
+
+        int get_n_gpt_gpu() const { return kdist_gpu->get_ngpt(); }
+        int get_n_bnd_gpu() const { return kdist_gpu->get_nband(); }
+        Float get_tsi_gpu() const { return kdist_gpu->get_tsi(); }
+        const std::vector<int>& get_band_lims_gpoint_gpu() const { return kdist_gpu->get_band_lims_gpoint(); }
+        const std::vector<Float>& get_band_lims_wavenumber_gpu() const { return kdist_gpu->get_band_lims_wavenumber(); }
+        Gas_optics_rrtmgp_gpu& get_kdist_gpu() { return *kdist_gpu; }
+
+        void solve_gpu(const bool switch_fluxes, const bool switch_cloud_optics, const bool switch_output_optical,
+                       const bool switch_output_bnd_fluxes, const bool switch_delta_cloud, const Gas_concs_gpu& gas_concs,
+                       const Array_gpu<Float,2>& p_lay, const Array_gpu<Float,2>& p_lev,
+                       const Array_gpu<Float,2>& t_lay, const Array_gpu<Float,2>& t_lev, const Array_gpu<Float,2>& col_dry,
+                       const Array_gpu<Float,2>& sfc_alb_dir, const Array_gpu<Float,2>& sfc_alb_dif,
+                       const Array_gpu<Float,1>& tsi_scaling, const Array_gpu<Float,1>& mu0,
+                       const Array_gpu<Float,2>& lwp, const Array_gpu<Float,2>& iwp,
+                       const Array_gpu<Float,2>& rel, const Array_gpu<Float,2>& dei,
+                       Array_gpu<Float,3>& tau, Array_gpu<Float,3>& ssa, Array_gpu<Float,3>& g, Array_gpu<Float,2>& toa_src,
+                       Array_gpu<Float,2>& sw_flux_up, Array_gpu<Float,2>& sw_flux_dn,
+                       Array_gpu<Float,2>& sw_flux_dn_dir, Array_gpu<Float,2>& sw_flux_net,
+                       Array_gpu<Float,3>& sw_bnd_flux_up, Array_gpu<Float,3>& sw_bnd_flux_dn,
+                       Array_gpu<Float,3>& sw_bnd_flux_dn_dir, Array_gpu<Float,3>& sw_bnd_flux_net)
+        {
+            const int n_col = p_lay.dim(1), n_lay = p_lay.dim(2), n_lev = p_lev.dim(2);
+            (void)t_lev;
+            if (switch_cloud_optics && !cloud_optics_gpu) throw std::runtime_error("cloud optics requested without cloud tables");
+            if (!switch_output_optical)
+            {
+                if (!switch_fluxes) return;
+                rrtmgp_b200::Concs_view cv(gas_concs, kdist_gpu->get_gas_names());
+                rrtmgp_b200_columns c{};
+                c.ncol = n_col; c.nlay = n_lay; c.top_at_1 = -1;
+                c.d_play = p_lay.ptr(); c.d_plev = p_lev.ptr(); c.d_tlay = t_lay.ptr();
+                c.d_col_dry = col_dry.size() ? col_dry.ptr() : nullptr; c.concs = cv.c;
+                c.d_sfc_alb_dir = sfc_alb_dir.ptr(); c.d_sfc_alb_dif = sfc_alb_dif.ptr(); c.d_mu0 = mu0.ptr();
+                c.d_tsi_scaling = tsi_scaling.size() ? tsi_scaling.ptr() : nullptr;
+                if (switch_cloud_optics)
+                {
+                    c.cloud = cloud_optics_gpu->handle(); c.delta_cloud = switch_delta_cloud;
+                    c.d_lwp = lwp.ptr(); c.d_iwp = iwp.ptr(); c.d_rel = rel.ptr(); c.d_dei = dei.ptr();
+                }
+                rrtmgp_b200_fluxes f{};
+                f.d_flux_up = sw_flux_up.ptr(); f.d_flux_dn = sw_flux_dn.ptr(); f.d_flux_net = sw_flux_net.ptr();
+                f.d_flux_dn_dir = sw_flux_dn_dir.ptr();
+                if (switch_output_bnd_fluxes)
+                {
+                    f.d_bnd_flux_up = sw_bnd_flux_up.ptr(); f.d_bnd_flux_dn = sw_bnd_flux_dn.ptr();
+                    f.d_bnd_flux_net = sw_bnd_flux_net.ptr(); f.d_bnd_flux_dn_dir = sw_bnd_flux_dn_dir.ptr();
+                }
+                rrtmgp_b200::check(rrtmgp_b200_sw_fluxes(kdist_gpu->handle(), &c, &f, rrtmgp_b200::stream()));
+                return;
+            }
+            std::unique_ptr<Optical_props_arry_gpu> optical_props = std::make_unique<Optical_props_2str_gpu>(n_col, n_lay, *kdist_gpu);
+            Array_gpu<Float,2> toa({n_col, get_n_gpt_gpu()});
+            kdist_gpu->gas_optics(p_lay, p_lev, t_lay, gas_concs, optical_props, toa, col_dry);
+            if (tsi_scaling.size())      // scaling_to_subset, src_test/Radiation_solver.cu:42-70,772
+                rrtmgp_b200::check(rrtmgp_b200_scale_columns(rrtmgp_b200::dtype, n_col, get_n_gpt_gpu(), toa.ptr(), tsi_scaling.ptr(),
+                                                             rrtmgp_b200::stream()));
+            if (switch_cloud_optics)
+            {
+                Optical_props_2str_gpu clouds(n_col, n_lay, *cloud_optics_gpu);
+                cloud_optics_gpu->cloud_optics(lwp, iwp, rel, dei, clouds);
+                if (switch_delta_cloud) clouds.delta_scale();
+                add_to(dynamic_cast<Optical_props_2str_gpu&>(*optical_props), clouds);
+            }
+            tau = optical_props->get_tau(); ssa = optical_props->get_ssa(); g = optical_props->get_g(); toa_src = toa;
+            if (!switch_fluxes) return;
+            const std::vector<Float> pl = Radiation_solver_longwave::top_probe(p_lay);
+            const Bool top_at_1 = pl[0] < pl[1];
+            const int ngpt = get_n_gpt_gpu();
+            Array_gpu<Float,3> gpt_flux_up({n_col, n_lev, ngpt}), gpt_flux_dn({n_col, n_lev, ngpt}), gpt_flux_dn_dir({n_col, n_lev, ngpt});
+            Rte_sw_gpu::rte_sw(optical_props, top_at_1, mu0, toa, sfc_alb_dir, sfc_alb_dif, Array_gpu<Float,2>(),
+                               gpt_flux_up, gpt_flux_dn, gpt_flux_dn_dir);
+            std::unique_ptr<Fluxes_broadband_gpu> fl;
+            if (switch_output_bnd_fluxes) fl = std::make_unique<Fluxes_byband_gpu>(n_col, n_lev, get_n_bnd_gpu());
+            else fl = std::make_unique<Fluxes_broadband_gpu>(n_col, n_lev);
+            fl->reduce(gpt_flux_up, gpt_flux_dn, gpt_flux_dn_dir, optical_props, top_at_1);
+            sw_flux_up = fl->get_flux_up(); sw_flux_dn = fl->get_flux_dn(); sw_flux_dn_dir = fl->get_flux_dn_dir(); sw_flux_net = fl->get_flux_net();
+            if (switch_output_bnd_fluxes)
+            {
+                auto& fb = dynamic_cast<Fluxes_byband_gpu&>(*fl);
+                sw_bnd_flux_up = fb.get_bnd_flux_up(); sw_bnd_flux_dn = fb.get_bnd_flux_dn();
+                sw_bnd_flux_dn_dir = fb.get_bnd_flux_dn_dir(); sw_bnd_flux_net = fb.get_bnd_flux_net();
+            }
+        }
+    private:
+        std::unique_ptr<Gas_optics_rrtmgp_gpu> kdist_gpu;
+        std::unique_ptr<Cloud_optics_gpu> cloud_optics_gpu;
+};

@@ -71,6 +71,7 @@ SYMBOLS = {
     "rrtmgp_b200_sum_broadband": (i, [i, i, i, i, vp, vp, vp]),
     "rrtmgp_b200_sum_byband": (i, [i, i, i, i, i, ip, vp, vp, vp]),
     "rrtmgp_b200_net_flux": (i, [i, sz, vp, vp, vp, vp]),
+    "rrtmgp_b200_scale_columns": (i, [i, i, i, vp, vp, vp]),
     "rrtmgp_b200_heating_rate": (i, [i, i, i, vp, vp, vp, vp, vp]),
     "rrtmgp_b200_lw_fluxes": (i, [vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp]),
     "rrtmgp_b200_sw_fluxes": (i, [vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp]),

@@ -686,6 +686,14 @@ int rrtmgp_b200_net_flux(int dtype, size_t n, const void* dn, const void* up, vo
         DISPATCH(dtype, launch_net<float>(n, dn, up, net, (cudaStream_t)stream), launch_net<double>(n, dn, up, net, (cudaStream_t)stream));
     });
 }
+int rrtmgp_b200_scale_columns(int dtype, int ncol, int n2, void* x, const void* scale, void* stream)
+{
+    return guarded([&] {
+        if (ncol < 1 || n2 < 1 || !x || !scale) throw ArgError("scale_columns: bad argument");
+        DISPATCH(dtype, launch_scale_columns<float>(ncol, n2, x, scale, (cudaStream_t)stream),
+                        launch_scale_columns<double>(ncol, n2, x, scale, (cudaStream_t)stream));
+    });
+}
 int rrtmgp_b200_heating_rate(int dtype, int ncol, int nlay, const void* up, const void* dn, const void* plev, void* hr, void* stream)
 {
     return guarded([&] {

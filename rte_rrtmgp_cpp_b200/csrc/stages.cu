@@ -396,6 +396,18 @@ template<typename Real> void launch_net(size_t n, const void* dn, const void* up
     net_kernel<Real><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(n, (const Real*)dn, (const Real*)up, (Real*)net);
     count_launch();
 }
+// toa_src(icol,igpt) *= tsi_scaling(icol)  (src_test/Radiation_solver.cu:42-70)
+template<typename Real> __global__ void scale_columns_kernel(size_t n, int ncol, Real* x, const Real* __restrict__ scale)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) x[i] *= scale[i % ncol];
+}
+template<typename Real> void launch_scale_columns(int ncol, int n2, void* x, const void* scale, cudaStream_t s)
+{
+    const size_t n = (size_t)ncol * n2;
+    scale_columns_kernel<Real><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(n, ncol, (Real*)x, (const Real*)scale);
+    count_launch();
+}
 template<typename Real>
 void launch_heating_rate(int ncol, int nlay, const void* up, const void* dn, const void* plev, void* hr, cudaStream_t s)
 {
@@ -422,6 +434,7 @@ void launch_range_flag(size_t n, const void* x, double lo, double hi, int* d_fla
     template void launch_sum_broadband<Real>(int, int, int, const void*, void*, cudaStream_t); \
     template void launch_sum_byband<Real>(int, int, const BandLims&, const void*, void*, cudaStream_t); \
     template void launch_net<Real>(size_t, const void*, const void*, void*, cudaStream_t); \
+    template void launch_scale_columns<Real>(int, int, void*, const void*, cudaStream_t); \
     template void launch_heating_rate<Real>(int, int, const void*, const void*, const void*, void*, cudaStream_t); \
     template void launch_range_flag<Real>(size_t, const void*, double, double, int*, cudaStream_t);
 INST(float)

@@ -38,6 +38,7 @@ void launch_sum_broadband(int ncol, int nlev, int ngpt, const void* gpt_flux, vo
 template<typename Real>
 void launch_sum_byband(int ncol, int nlev, const BandLims& bl, const void* gpt_flux, void* bnd_flux, cudaStream_t s);
 template<typename Real> void launch_net(size_t n, const void* dn, const void* up, void* net, cudaStream_t s);
+template<typename Real> void launch_scale_columns(int ncol, int n2, void* x, const void* scale, cudaStream_t s);
 template<typename Real>
 void launch_heating_rate(int ncol, int nlay, const void* up, const void* dn, const void* plev, void* hr, cudaStream_t s);
 template<typename Real>

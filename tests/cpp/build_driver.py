@@ -1,0 +1,34 @@
+"""Build the C++ class-layer test drivers (tests/cpp/classes_driver.cpp) against the in-tree
+librrtmgp_b200.so: one with Float=double, one with -DRTE_USE_SP.  g++ only (the header has no
+device code); links cudart for the Array_gpu allocations."""
+import os
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+PKG = os.path.join(ROOT, "rte_rrtmgp_cpp_b200")
+CUDA = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+
+
+def path(tag: str) -> str:
+    return os.path.join(HERE, f"libclasses_driver_{tag}.so")
+
+
+def build(force: bool = False) -> None:
+    src = os.path.join(HERE, "classes_driver.cpp")
+    hdrs = [os.path.join(ROOT, "include", "rrtmgp_b200", "classes.hpp"), os.path.join(ROOT, "include", "rrtmgp_b200.h"), src]
+    newest = max(os.path.getmtime(h) for h in hdrs)
+    for tag, defs in (("f64", []), ("f32", ["-DRTE_USE_SP"])):
+        out = path(tag)
+        if not force and os.path.exists(out) and os.path.getmtime(out) >= newest:
+            continue
+        cmd = ["g++", "-std=c++17", "-O1", "-fPIC", "-shared", "-Wall", *defs, "-I" + os.path.join(ROOT, "include"),
+               "-I" + os.path.join(CUDA, "include"), src, "-o", out, "-L" + PKG, "-lrrtmgp_b200",
+               "-L" + os.path.join(CUDA, "lib64"), "-lcudart", "-Wl,-rpath,$ORIGIN/../../rte_rrtmgp_cpp_b200"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("g++ failed for the class-layer driver:\n" + r.stdout + r.stderr)
+
+
+if __name__ == "__main__":
+    build(force=True)
