@@ -253,6 +253,16 @@ int rrtmgp_b200_lw_fluxes(rrtmgp_b200_gas_optics* go, const rrtmgp_b200_columns*
                           const rrtmgp_b200_fluxes* out, void* stream);
 int rrtmgp_b200_sw_fluxes(rrtmgp_b200_gas_optics* go, const rrtmgp_b200_columns* cols,
                           const rrtmgp_b200_fluxes* out, void* stream);
+/* Host-buffer form of the two calls above: every array pointer inside cols_* and out_* is a HOST
+ * pointer here (same shapes and layouts; pinned memory gives full PCIe speed, pageable works).
+ * The columns are processed in chunks (chunk_cols, 0 = one default tile); chunk i+1 is uploaded
+ * and chunk i-1 downloaded while chunk i computes, so the copies hide behind the kernels.  Arrays
+ * that LW and SW share (same host address: play, plev, tlay, vmr, col_dry) are uploaded once.
+ * Either solver may be NULL.  Returns when the host outputs are complete (synchronises). */
+int rrtmgp_b200_fluxes_host(rrtmgp_b200_gas_optics* go_lw, const rrtmgp_b200_columns* cols_lw,
+                            const rrtmgp_b200_fluxes* out_lw, rrtmgp_b200_gas_optics* go_sw,
+                            const rrtmgp_b200_columns* cols_sw, const rrtmgp_b200_fluxes* out_sw,
+                            int chunk_cols, void* stream);
 /* tuning / introspection of the fused path: columns per tile (0 = default), and the number of
  * kernels the last fused call launched (for bench.py's gpu_launches). */
 int rrtmgp_b200_set_tile_columns(rrtmgp_b200_gas_optics* go, int ncol_tile);

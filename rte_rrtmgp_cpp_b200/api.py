@@ -518,16 +518,16 @@ class _Radiation_solver:
     def set_tile_columns(self, n: int) -> None:
         check(lib().rrtmgp_b200_set_tile_columns(self.kdist.h, int(n)))
 
-    def solve_gpu(self, cols: DeviceColumns, switch_cloud_optics: bool = False, switch_delta_cloud: bool = True,
-                  switch_output_bnd_fluxes: bool = False, heating: bool = False, out: Optional[dict] = None) -> dict:
+    def _pack(self, cols, out, switch_cloud_optics, switch_delta_cloud, switch_output_bnd_fluxes, heating, device):
+        """ColumnsC / FluxesC for `cols` (device or pinned-host resident), allocating outputs in `out`."""
         k = self.kdist
         ncol, nlay, nlev, nb = cols.ncol, cols.nlay, cols.nlay + 1, k.get_nband()
         dt = self.dtype
-        if out is None:
-            out = {}
         def arr(name, dims):
             if name not in out or out[name].dims != tuple(dims):
-                out[name] = Array_gpu(dims, dt)
+                n = int(np.prod(dims))
+                data = torch.zeros(n, dtype=dt, pin_memory=True) if device == "cpu" else None
+                out[name] = Array_gpu(dims, dt, device, data)
             return out[name]
         f = capi.FluxesC()
         f.d_flux_up, f.d_flux_dn, f.d_flux_net = arr("flux_up", (ncol, nlev)).ptr, arr("flux_dn", (ncol, nlev)).ptr, arr("flux_net", (ncol, nlev)).ptr
@@ -558,8 +558,16 @@ class _Radiation_solver:
             c.delta_cloud = int(switch_delta_cloud)
             c.d_lwp, c.d_iwp, c.d_rel, c.d_dei = cols.lwp.ptr, cols.iwp.ptr, cols.rel.ptr, cols.dei.ptr
         c.n_gauss_angles = 1
+        c._keep = concs
+        return c, f
+
+    def solve_gpu(self, cols: DeviceColumns, switch_cloud_optics: bool = False, switch_delta_cloud: bool = True,
+                  switch_output_bnd_fluxes: bool = False, heating: bool = False, out: Optional[dict] = None) -> dict:
+        if out is None:
+            out = {}
+        c, f = self._pack(cols, out, switch_cloud_optics, switch_delta_cloud, switch_output_bnd_fluxes, heating, "cuda")
         fn = lib().rrtmgp_b200_sw_fluxes if self.sw else lib().rrtmgp_b200_lw_fluxes
-        check(fn(k.h, C.byref(c), C.byref(f), _stream()))
+        check(fn(self.kdist.h, C.byref(c), C.byref(f), _stream()))
         return out
 
 
@@ -569,3 +577,34 @@ class Radiation_solver_longwave(_Radiation_solver):
 
 class Radiation_solver_shortwave(_Radiation_solver):
     sw = True
+
+
+class HostColumns(DeviceColumns):
+    """The same inputs resident in pinned HOST memory: what a host model (MicroHH's CPU fields, a
+    NetCDF reader) holds before a radiation call.  Consumed by solve_host()."""
+
+    def __init__(self, atm, dtype=torch.float64):
+        super().__init__(atm, dtype, device="cpu")
+        for obj in (vars(self), self.gas_concs.gas_concs_map):
+            for v in obj.values():
+                if isinstance(v, Array_gpu):
+                    v.t = v.t.pin_memory()
+
+
+def solve_host(lw: Optional[Radiation_solver_longwave], sw: Optional[Radiation_solver_shortwave], cols: HostColumns,
+               switch_cloud_optics: bool = False, switch_delta_cloud: bool = True, switch_output_bnd_fluxes: bool = False,
+               heating: bool = False, out_lw: Optional[dict] = None, out_sw: Optional[dict] = None, chunk_columns: int = 0):
+    """Host buffers in, host buffers out (rrtmgp_b200_fluxes_host): column chunks stream through
+    H2D -> fused LW and SW -> D2H with the copies hidden behind the kernels.  Returns
+    (out_lw, out_sw): dicts of pinned host Array_gpu objects.  Blocks until the outputs are ready."""
+    out_lw = {} if out_lw is None else out_lw
+    out_sw = {} if out_sw is None else out_sw
+    cl = fl = cs = fs = None
+    if lw is not None:
+        cl, fl = lw._pack(cols, out_lw, switch_cloud_optics, switch_delta_cloud, switch_output_bnd_fluxes, heating, "cpu")
+    if sw is not None:
+        cs, fs = sw._pack(cols, out_sw, switch_cloud_optics, switch_delta_cloud, switch_output_bnd_fluxes, heating, "cpu")
+    check(lib().rrtmgp_b200_fluxes_host(lw.kdist.h if lw else None, C.byref(cl) if cl else None, C.byref(fl) if fl else None,
+                                        sw.kdist.h if sw else None, C.byref(cs) if cs else None, C.byref(fs) if fs else None,
+                                        int(chunk_columns), _stream()))
+    return out_lw, out_sw

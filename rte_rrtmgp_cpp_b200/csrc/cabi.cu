@@ -3,6 +3,7 @@
 // fallback: every entry that needs the device fails with RRTMGP_B200_E_CUDA when CUDA is absent.
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <memory>
 #include <string>
 #include <vector>
@@ -20,6 +21,8 @@ void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 // optional device-side timing of the fused band kernels (bench.py's roofline leg)
 struct Profile { bool on = false; std::vector<cudaEvent_t> ev[2]; double ms[2] = {0, 0}; long long launches[2] = {0, 0}; };
 static Profile g_prof;
+// host-buffer entry: run the LW and the SW band kernels of a chunk on two streams (RB200_HOST_CONCURRENT=0 disables)
+static const bool g_host_concurrent = [] { const char* e = getenv("RB200_HOST_CONCURRENT"); return !(e && e[0] == '0'); }();
 
 struct CudaError : std::runtime_error { using std::runtime_error::runtime_error; };
 struct RangeError : std::runtime_error { using std::runtime_error::runtime_error; };
@@ -99,6 +102,7 @@ struct rrtmgp_b200_gas_optics
     BandLims lims{};
     Arena ws;
     int tile_cols = 0;
+    std::shared_ptr<void> pipe;     // HostPipe of the host-buffer entry, created on first use
 };
 
 struct rrtmgp_b200_cloud_optics
@@ -825,6 +829,194 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
     if (out->d_heating_rate) launch_heating_rate<Real>(ncol, nlay, a.flux_up, a.flux_dn, cols->d_plev, out->d_heating_rate, s);
 }
 
+
+// ---- host-buffer entry: chunks of columns stream H2D -> fused LW/SW -> D2H, double-buffered on
+// three streams so the PCIe copies hide behind the band kernels of the neighbouring chunks.
+struct HostPipe
+{
+    Arena in[2], out[2];
+    cudaStream_t h2d = nullptr, d2h = nullptr, side = nullptr;
+    cudaEvent_t e_h2d[2]{}, e_comp[2]{}, e_d2h[2]{}, e_side[2]{};
+    HostPipe()
+    {
+        CK(cudaStreamCreateWithFlags(&h2d, cudaStreamNonBlocking)); CK(cudaStreamCreateWithFlags(&d2h, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i)
+        {
+            CK(cudaEventCreateWithFlags(&e_h2d[i], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&e_comp[i], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&e_d2h[i], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&e_side[i], cudaEventDisableTiming));
+        }
+    }
+    ~HostPipe()
+    {
+        for (int i = 0; i < 2; ++i) { cudaEventDestroy(e_h2d[i]); cudaEventDestroy(e_comp[i]); cudaEventDestroy(e_d2h[i]); cudaEventDestroy(e_side[i]); }
+        cudaStreamDestroy(h2d); cudaStreamDestroy(d2h); cudaStreamDestroy(side);
+    }
+};
+HostPipe& host_pipe(rrtmgp_b200_gas_optics* g)
+{
+    if (!g->pipe) g->pipe = std::make_shared<HostPipe>();
+    return *static_cast<HostPipe*>(g->pipe.get());
+}
+
+// one host array of the column set. kind 0: (ncol, n2) column-major, chunked by rows of the first index;
+// kind 1: (n2, ncol) band-major, a chunk is contiguous; kind 2: not column-dependent, uploaded whole
+struct HostItem { const void* h; int kind; size_t n2; void* d[2]; };
+
+template<typename Real>
+void fluxes_host(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, const rrtmgp_b200_fluxes* olw,
+                 rrtmgp_b200_gas_optics* gsw, const rrtmgp_b200_columns* csw, const rrtmgp_b200_fluxes* osw,
+                 int chunk_cols, cudaStream_t s)
+{
+    rrtmgp_b200_gas_optics* g0 = glw ? glw : gsw;
+    const rrtmgp_b200_columns* c0p = glw ? clw : csw;
+    if (!g0 || !c0p) throw ArgError("fluxes_host: need a longwave and/or a shortwave solver with its columns");
+    if (glw && (!clw || !olw)) throw ArgError("fluxes_host: longwave columns/outputs missing");
+    if (gsw && (!csw || !osw)) throw ArgError("fluxes_host: shortwave columns/outputs missing");
+    if (glw && gsw && (clw->ncol != csw->ncol || clw->nlay != csw->nlay)) throw ArgError("fluxes_host: LW and SW column sets differ in shape");
+    if (g0->host_only || (gsw && gsw->host_only)) throw CudaError("this handle was created HOST_ONLY: no device tables, and there is no CPU fallback");
+    const int ncol = c0p->ncol, nlay = c0p->nlay, nlev = nlay + 1;
+    check_dims(ncol, nlay);
+    if (!c0p->d_play) throw ArgError("fluxes_host: play missing");
+    HostPipe& P = host_pipe(g0);
+    int top_at_1 = c0p->top_at_1;
+    if (top_at_1 < 0) { const Real* pl = (const Real*)c0p->d_play; top_at_1 = pl[0] < pl[(size_t)ncol * (nlay - 1)]; }
+
+    // chunk = one default tile of the wider solver, so every chunk fills whole waves
+    int chunk = chunk_cols;
+    if (chunk <= 0)
+        for (auto* g : {glw, gsw})
+            if (g)
+            {
+                const int cpb = FUSED_THREADS / (g->h.gw / 4);
+                const int wave = std::max(g->h.is_lw ? lw_blocks_per_wave<Real>(g->h.gw) : sw_blocks_per_wave<Real>(g->h.gw), 1);
+                chunk = std::max(chunk, g->tile_cols > 0 ? g->tile_cols : 8 * wave * cpb);
+            }
+    chunk = std::min(chunk, ncol);
+
+    // inputs, de-duplicated by host address (LW and SW normally share play/plev/tlay/vmr/col_dry)
+    std::vector<HostItem> items;
+    auto item = [&](const void* h, int kind, size_t n2) -> int {
+        if (!h) return -1;
+        for (size_t i = 0; i < items.size(); ++i) if (items[i].h == h) return (int)i;
+        items.push_back({h, kind, n2, {nullptr, nullptr}});
+        return (int)items.size() - 1;
+    };
+    struct Side
+    {
+        rrtmgp_b200_gas_optics* g; const rrtmgp_b200_columns* c; const rrtmgp_b200_fluxes* o; bool sw;
+        int play, plev, tlay, tlev, tsfc, coldry, emis, adir, adif, mu0, tsi, lwp, iwp, rel, dei; std::vector<int> vmr;
+        std::vector<const void*> dv; std::vector<int> vnc, vnl;
+    };
+    std::vector<Side> sides;
+    for (int k = 0; k < 2; ++k)
+    {
+        rrtmgp_b200_gas_optics* g = k ? gsw : glw; const rrtmgp_b200_columns* c = k ? csw : clw;
+        if (!g) continue;
+        if (g->dtype != g0->dtype) throw ArgError("fluxes_host: LW and SW solvers differ in precision");
+        if (g->h.is_lw == (k == 1)) throw ArgError("fluxes_host: solver passed on the wrong side (LW first, SW second)");
+        Side sd{}; sd.g = g; sd.c = c; sd.o = k ? osw : olw; sd.sw = k == 1;
+        sd.play = item(c->d_play, 0, nlay); sd.plev = item(c->d_plev, 0, nlev); sd.tlay = item(c->d_tlay, 0, nlay);
+        sd.tlev = k ? -1 : item(c->d_tlev, 0, nlev); sd.tsfc = k ? -1 : item(c->d_tsfc, 0, 1);
+        sd.coldry = item(c->d_col_dry, 0, nlay);
+        sd.emis = k ? -1 : item(c->d_sfc_emis, 1, g->h.nbnd);
+        sd.adir = k ? item(c->d_sfc_alb_dir, 1, g->h.nbnd) : -1; sd.adif = k ? item(c->d_sfc_alb_dif, 1, g->h.nbnd) : -1;
+        sd.mu0 = k ? item(c->d_mu0, 0, 1) : -1; sd.tsi = k ? item(c->d_tsi_scaling, 0, 1) : -1;
+        const bool cl = c->cloud != nullptr;
+        sd.lwp = cl ? item(c->d_lwp, 0, nlay) : -1; sd.iwp = cl ? item(c->d_iwp, 0, nlay) : -1;
+        sd.rel = cl ? item(c->d_rel, 0, nlay) : -1; sd.dei = cl ? item(c->d_dei, 0, nlay) : -1;
+        const rrtmgp_b200_gas_concs& gc = c->concs;
+        if (gc.ngas != g->h.ngas || !gc.d_vmr || !gc.vmr_ncol || !gc.vmr_nlay)
+            throw ArgError("gas concentrations: need one entry per gas of the k-distribution object");
+        for (int i = 0; i < gc.ngas; ++i)
+        {
+            if (!gc.d_vmr[i]) throw MissingError("Gas_concs: gas " + g->h.gas_names[i] + " not set");
+            const bool field = gc.vmr_ncol[i] == ncol && ncol > 1;
+            sd.vmr.push_back(item(gc.d_vmr[i], field ? 0 : 2, field ? (size_t)gc.vmr_nlay[i] : (size_t)gc.vmr_ncol[i] * gc.vmr_nlay[i]));
+        }
+        sd.dv.resize(gc.ngas); sd.vnc.assign(gc.vmr_ncol, gc.vmr_ncol + gc.ngas); sd.vnl.assign(gc.vmr_nlay, gc.vmr_nlay + gc.ngas);
+        sides.push_back(std::move(sd));
+    }
+    // outputs: (ncol, rows) host arrays; device chunk arrays (chunk, rows)
+    struct OutItem { void* h; size_t rows; void* d[2]; };
+    std::vector<OutItem> outs;
+    auto oitem = [&](void* h, size_t rows) -> int { if (!h) return -1; outs.push_back({h, rows, {nullptr, nullptr}}); return (int)outs.size() - 1; };
+    struct SideOut { int up, dn, net, dir, bup, bdn, bnet, bdir, hr; };
+    std::vector<SideOut> so;
+    for (auto& sd : sides)
+    {
+        const rrtmgp_b200_fluxes* o = sd.o; const size_t nb = sd.g->h.nbnd;
+        if (!o->d_flux_up || !o->d_flux_dn) throw ArgError("fluxes_host: flux_up and flux_dn are required");
+        so.push_back({oitem(o->d_flux_up, nlev), oitem(o->d_flux_dn, nlev), oitem(o->d_flux_net, nlev), sd.sw ? oitem(o->d_flux_dn_dir, nlev) : -1,
+                      oitem(o->d_bnd_flux_up, nlev * nb), oitem(o->d_bnd_flux_dn, nlev * nb), oitem(o->d_bnd_flux_net, nlev * nb),
+                      sd.sw ? oitem(o->d_bnd_flux_dn_dir, nlev * nb) : -1, oitem(o->d_heating_rate, nlay)});
+    }
+    size_t in_bytes = 4096, out_bytes = 4096;
+    for (auto& it : items) in_bytes += pad256((it.kind == 2 ? it.n2 : (size_t)chunk * it.n2) * sizeof(Real)) + 256;
+    for (auto& ot : outs) out_bytes += pad256((size_t)chunk * ot.rows * sizeof(Real)) + 256;
+    for (int b = 0; b < 2; ++b)
+    {
+        P.in[b].reserve(in_bytes, s); P.out[b].reserve(out_bytes, s);
+        for (auto& it : items) it.d[b] = P.in[b].take<Real>(it.kind == 2 ? it.n2 : (size_t)chunk * it.n2);
+        for (auto& ot : outs) ot.d[b] = P.out[b].take<Real>((size_t)chunk * ot.rows);
+    }
+    for (auto& it : items)          // column-independent inputs once, into both buffers
+        if (it.kind == 2)
+            for (int b = 0; b < 2; ++b) CK(cudaMemcpyAsync(it.d[b], it.h, it.n2 * sizeof(Real), cudaMemcpyHostToDevice, P.h2d));
+
+    const bool concurrent = sides.size() == 2 && g_host_concurrent;
+    int i = 0;
+    for (int c0 = 0; c0 < ncol; c0 += chunk, ++i)
+    {
+        const int nc = std::min(chunk, ncol - c0), b = i & 1;
+        // H2D of chunk i once the kernels of chunk i-2 have drained this buffer
+        if (i >= 2) CK(cudaStreamWaitEvent(P.h2d, P.e_comp[b], 0));
+        for (auto& it : items)
+        {
+            if (it.kind == 0)
+                CK(cudaMemcpy2DAsync(it.d[b], (size_t)nc * sizeof(Real), (const Real*)it.h + c0, (size_t)ncol * sizeof(Real),
+                                     (size_t)nc * sizeof(Real), it.n2, cudaMemcpyHostToDevice, P.h2d));
+            else if (it.kind == 1)
+                CK(cudaMemcpyAsync(it.d[b], (const Real*)it.h + (size_t)c0 * it.n2, (size_t)nc * it.n2 * sizeof(Real), cudaMemcpyHostToDevice, P.h2d));
+        }
+        CK(cudaEventRecord(P.e_h2d[b], P.h2d));
+        CK(cudaStreamWaitEvent(s, P.e_h2d[b], 0));
+        if (i >= 2) CK(cudaStreamWaitEvent(s, P.e_d2h[b], 0));
+        if (concurrent) { CK(cudaEventRecord(P.e_side[0], s)); CK(cudaStreamWaitEvent(P.side, P.e_side[0], 0)); }
+        for (size_t k = 0; k < sides.size(); ++k)
+        {
+            Side& sd = sides[k];
+            auto D = [&](int idx) -> const void* { return idx < 0 ? nullptr : items[idx].d[b]; };
+            auto O = [&](int idx) -> void* { return idx < 0 ? nullptr : outs[idx].d[b]; };
+            rrtmgp_b200_columns dc = *sd.c;
+            dc.ncol = nc; dc.top_at_1 = top_at_1;
+            dc.d_play = D(sd.play); dc.d_plev = D(sd.plev); dc.d_tlay = D(sd.tlay); dc.d_tlev = D(sd.tlev); dc.d_tsfc = D(sd.tsfc);
+            dc.d_col_dry = D(sd.coldry); dc.d_sfc_emis = D(sd.emis); dc.d_sfc_alb_dir = D(sd.adir); dc.d_sfc_alb_dif = D(sd.adif);
+            dc.d_mu0 = D(sd.mu0); dc.d_tsi_scaling = D(sd.tsi);
+            dc.d_lwp = D(sd.lwp); dc.d_iwp = D(sd.iwp); dc.d_rel = D(sd.rel); dc.d_dei = D(sd.dei);
+            for (size_t gi = 0; gi < sd.vmr.size(); ++gi)
+            {
+                sd.dv[gi] = D(sd.vmr[gi]);
+                sd.vnc[gi] = items[sd.vmr[gi]].kind == 0 ? nc : sd.c->concs.vmr_ncol[gi];
+            }
+            dc.concs.d_vmr = sd.dv.data(); dc.concs.vmr_ncol = sd.vnc.data(); dc.concs.vmr_nlay = sd.vnl.data();
+            rrtmgp_b200_fluxes df{};
+            df.d_flux_up = O(so[k].up); df.d_flux_dn = O(so[k].dn); df.d_flux_net = O(so[k].net); df.d_flux_dn_dir = O(so[k].dir);
+            df.d_bnd_flux_up = O(so[k].bup); df.d_bnd_flux_dn = O(so[k].bdn); df.d_bnd_flux_net = O(so[k].bnet);
+            df.d_bnd_flux_dn_dir = O(so[k].bdir); df.d_heating_rate = O(so[k].hr);
+            fused_fluxes<Real>(sd.g, &dc, &df, (concurrent && k == 1) ? P.side : s, sd.sw);
+        }
+        if (concurrent) { CK(cudaEventRecord(P.e_side[1], P.side)); CK(cudaStreamWaitEvent(s, P.e_side[1], 0)); }
+        CK(cudaEventRecord(P.e_comp[b], s));
+        CK(cudaStreamWaitEvent(P.d2h, P.e_comp[b], 0));
+        for (auto& ot : outs)
+            CK(cudaMemcpy2DAsync((Real*)ot.h + c0, (size_t)ncol * sizeof(Real), ot.d[b], (size_t)nc * sizeof(Real),
+                                 (size_t)nc * sizeof(Real), ot.rows, cudaMemcpyDeviceToHost, P.d2h));
+        CK(cudaEventRecord(P.e_d2h[b], P.d2h));
+    }
+    CK(cudaStreamSynchronize(P.d2h));
+    CK(cudaStreamSynchronize(s));
+}
 }  // namespace
 
 extern "C" {
@@ -835,6 +1027,17 @@ int rrtmgp_b200_lw_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* 
         if (!g) throw ArgError("lw_fluxes: null handle");
         if (g->dtype == RRTMGP_B200_F32) fused_fluxes<float>(g, cols, out, (cudaStream_t)stream, false);
         else fused_fluxes<double>(g, cols, out, (cudaStream_t)stream, false);
+    });
+}
+int rrtmgp_b200_fluxes_host(rrtmgp_b200_gas_optics* go_lw, const rrtmgp_b200_columns* cols_lw, const rrtmgp_b200_fluxes* out_lw,
+                            rrtmgp_b200_gas_optics* go_sw, const rrtmgp_b200_columns* cols_sw, const rrtmgp_b200_fluxes* out_sw,
+                            int chunk_cols, void* stream)
+{
+    return guarded([&] {
+        rrtmgp_b200_gas_optics* g0 = go_lw ? go_lw : go_sw;
+        if (!g0) throw ArgError("fluxes_host: null handles");
+        if (g0->dtype == RRTMGP_B200_F32) fluxes_host<float>(go_lw, cols_lw, out_lw, go_sw, cols_sw, out_sw, chunk_cols, (cudaStream_t)stream);
+        else fluxes_host<double>(go_lw, cols_lw, out_lw, go_sw, cols_sw, out_sw, chunk_cols, (cudaStream_t)stream);
     });
 }
 int rrtmgp_b200_sw_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, const rrtmgp_b200_fluxes* out, void* stream)
