@@ -561,6 +561,10 @@ class _Radiation_solver:
         c._keep = concs
         return c, f
 
+    def set_fused_path(self, path: int) -> None:
+        """1 column-resident kernels (default), 0 per-band kernels with HBM scratch strips."""
+        check(lib().rrtmgp_b200_set_fused_path(self.kdist.h, int(path)))
+
     def solve_gpu(self, cols: DeviceColumns, switch_cloud_optics: bool = False, switch_delta_cloud: bool = True,
                   switch_output_bnd_fluxes: bool = False, heating: bool = False, out: Optional[dict] = None) -> dict:
         if out is None:

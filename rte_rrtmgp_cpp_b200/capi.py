@@ -77,6 +77,7 @@ SYMBOLS = {
     "rrtmgp_b200_sw_fluxes": (i, [vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp]),
     "rrtmgp_b200_fluxes_host": (i, [vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), i, vp]),
     "rrtmgp_b200_set_tile_columns": (i, [vp, i]),
+    "rrtmgp_b200_set_fused_path": (i, [vp, i]),
     "rrtmgp_b200_launch_count": (C.c_longlong, []),
     "rrtmgp_b200_profile": (i, [i, C.POINTER(d), C.POINTER(C.c_longlong), C.POINTER(d), C.POINTER(C.c_longlong)]),
 }

@@ -22,6 +22,8 @@ void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 struct Profile { bool on = false; std::vector<cudaEvent_t> ev[2]; double ms[2] = {0, 0}; long long launches[2] = {0, 0}; };
 static Profile g_prof;
 // host-buffer entry: run the LW and the SW band kernels of a chunk on two streams (RB200_HOST_CONCURRENT=0 disables)
+// RB200_PATH=strips selects the earlier per-band kernels with recurrence scratch strips in HBM
+static const bool g_colres = [] { const char* e = getenv("RB200_PATH"); return !(e && e[0] == 's'); }();
 static const bool g_host_concurrent = [] { const char* e = getenv("RB200_HOST_CONCURRENT"); return !(e && e[0] == '0'); }();
 
 struct CudaError : std::runtime_error { using std::runtime_error::runtime_error; };
@@ -99,9 +101,11 @@ struct rrtmgp_b200_gas_optics
     DevPlan<float> pf{};
     DevPlan<double> pd{};
     std::vector<BandArgs> bands;
+    DevBuf bands_dev;               // the same on the device (column-resident kernels loop over bands)
     BandLims lims{};
     Arena ws;
     int tile_cols = 0;
+    int colres = -1;                // fused path: 1 column-resident, 0 strips, -1 default (RB200_PATH)
     std::shared_ptr<void> pipe;     // HostPipe of the host-buffer entry, created on first use
 };
 
@@ -165,6 +169,13 @@ extern "C" {
 
 const char* rrtmgp_b200_last_error(void) { return g_err.c_str(); }
 int rrtmgp_b200_version(void) { return 100; }
+int rrtmgp_b200_set_fused_path(rrtmgp_b200_gas_optics* g, int path)
+{
+    return guarded([&] {
+        if (!g || path < -1 || path > 1) throw ArgError("set_fused_path: handle and path in {-1, 0, 1}");
+        g->colres = path;
+    }, false);
+}
 long long rrtmgp_b200_launch_count(void) { return g_launches.load(); }
 
 int rrtmgp_b200_gas_optics_create(const rrtmgp_b200_kdist_file* kd, int n_avail, const char* names,
@@ -205,6 +216,7 @@ int rrtmgp_b200_gas_optics_create(const rrtmgp_b200_kdist_file* kd, int n_avail,
                     if (h.minor[s].desc[lst[m]].idx_minor < 0) throw ArgError("internal: minor gas index");
             }
         }
+        if (!host_only) g->bands_dev.upload(g->bands);
     }, !host_only);
     if (rc) return rc;
     *out = g.release();
@@ -750,11 +762,15 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
         top_at_1 = p2[0] < p2[1];
     }
 
+    const bool colres = g->colres < 0 ? g_colres : g->colres != 0;
+    if (colres && colres_smem_bytes<Real>(nlay, h.gw, sw) > 227 * 1024)
+        throw ArgError("fused fluxes: column too tall for the shared-memory resident path");
     const int cpb = FUSED_THREADS / (h.gw / 4);
-    // A tile is several waves of CTAs: CTAs retire and start continuously, so the compute-heavy
-    // and the memory-heavy passes of different CTAs overlap.  Scratch strips are per resident CTA.
+    // strips path: a tile is several waves of CTAs (CTAs retire and start continuously, so compute-heavy
+    // and memory-heavy passes of different CTAs overlap); scratch strips are per resident CTA.
+    // column-resident path: a tile only bounds the interpolation state (one CTA per 16/gw columns).
     const int wave = std::max(sw ? sw_blocks_per_wave<Real>(h.gw) : lw_blocks_per_wave<Real>(h.gw), 1);
-    const int nslots = 2 * wave;
+    const int nslots = colres ? 0 : 2 * wave;
     int tile = g->tile_cols;
     if (tile <= 0) tile = 8 * wave * cpb;
     tile = std::min(tile, ncol);
@@ -775,7 +791,7 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
     a.tsi_scaling = (const Real*)cols->d_tsi_scaling;
     a.scratch = (V4<Real>*)g->ws.take<char>(fused_scratch_bytes<Real>(nslots, nlay, sw));
     a.slot_busy = g->ws.take<int>(nslots); a.nslots = nslots;
-    CK(cudaMemsetAsync(a.slot_busy, 0, nslots * sizeof(int), s));
+    if (nslots) CK(cudaMemsetAsync(a.slot_busy, 0, nslots * sizeof(int), s));
     a.flux_up = (Real*)out->d_flux_up; a.flux_dn = (Real*)out->d_flux_dn;
     a.flux_dir = (Real*)out->d_flux_dn_dir;
     a.bnd_up = (Real*)out->d_bnd_flux_up; a.bnd_dn = (Real*)out->d_bnd_flux_dn; a.bnd_dir = (Real*)out->d_bnd_flux_dn_dir;
@@ -795,9 +811,12 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
     if (sw && !a.flux_dir) a.flux_dir = g->ws.take<Real>(ncv);
     if (sw && bnd && !a.bnd_dir) a.bnd_dir = g->ws.take<Real>(ncv * h.nbnd);
 
-    CK(cudaMemsetAsync(a.flux_up, 0, ncv * sizeof(Real), s));
-    CK(cudaMemsetAsync(a.flux_dn, 0, ncv * sizeof(Real), s));
-    if (sw) CK(cudaMemsetAsync(a.flux_dir, 0, ncv * sizeof(Real), s));
+    if (!colres)        // the strips kernels accumulate band by band; the column-resident ones store once
+    {
+        CK(cudaMemsetAsync(a.flux_up, 0, ncv * sizeof(Real), s));
+        CK(cudaMemsetAsync(a.flux_dn, 0, ncv * sizeof(Real), s));
+        if (sw) CK(cudaMemsetAsync(a.flux_dir, 0, ncv * sizeof(Real), s));
+    }
 
     for (int c0 = 0; c0 < ncol; c0 += tile)
     {
@@ -813,15 +832,17 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
             a.cld_tau = ctau; a.cld_ssa = cssa; a.cld_g = cg;
         }
         if (g_prof.on) { cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, s)); g_prof.ev[sw].push_back(e); }
-        for (int b = 0; b < h.nbnd; ++b)
-        {
-            if (sw) launch_sw_band<Real>(dplan<Real>(g), g->bands[b], st, a, s);
-            else launch_lw_band<Real>(dplan<Real>(g), g->bands[b], st, a, s);
-        }
+        if (colres) launch_cols<Real>(sw, dplan<Real>(g), (const BandArgs*)g->bands_dev.p, st, a, s);
+        else
+            for (int b = 0; b < h.nbnd; ++b)
+            {
+                if (sw) launch_sw_band<Real>(dplan<Real>(g), g->bands[b], st, a, s);
+                else launch_lw_band<Real>(dplan<Real>(g), g->bands[b], st, a, s);
+            }
         if (g_prof.on)
         {
             cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, s)); g_prof.ev[sw].push_back(e);
-            g_prof.launches[sw] += h.nbnd;
+            g_prof.launches[sw] += colres ? 1 : h.nbnd;
         }
     }
     if (out->d_flux_net) launch_net<Real>(ncv, a.flux_dn, a.flux_up, out->d_flux_net, s);

@@ -1,0 +1,432 @@
+// colres.cu — column-resident fused kernels: the per-(column, g-point) vertical recurrences of the
+// RTE solvers live in shared memory, never in HBM.
+//
+// One CTA owns 16 recurrence chains = (16 / gw) columns x the gw (padded) g-points of a band and
+// loops over all bands of the k-distribution:
+//   phase 1 (all 128 threads, layer-parallel): thread = (layer group, 4 g-points).  Gas optics
+//            (+ Rayleigh / cloud increment) and the layer's transfer coefficients (two-stream
+//            R/T or exp(-tau) + Planck sources) -> shared memory rows [word][level][chain].
+//   phase 2 (16 lanes of warp 0, one chain each): the sequential sweeps (direct beam, adding,
+//            fluxes / down- and up-welling radiances) read and overwrite the rows in place.
+//   phase 3 (all threads, level-parallel): g-point sums by quad shuffle into per-CTA broadband
+//            accumulators (and the optional by-band outputs).
+// After the last band the accumulators are stored once to (ncol, nlay+1): no atomics, no memset.
+// DRAM traffic is the prologue kernel's interpolation state (~100 B per (column, layer, band))
+// and the k-tables (L2-resident); 5 CTAs x (41 KB + 1.5 KB) fit an SM's 227 KB at fp32, nlay 128.
+//
+// Restates the same reference chain as fused_lw.cu / fused_sw.cu (same per-cell arithmetic from
+// physics.cuh); see those files for the Fortran line references.
+#include "physics.cuh"
+#include "launch.hpp"
+
+namespace rb200 {
+
+constexpr int CR_T = FUSED_THREADS;      // 128
+constexpr int CR_CH = 16;                // chains per CTA = floats per shared-memory row
+constexpr int CR_NL = CR_T / 4;          // layers in flight in phase 1 (4 quads per row)
+
+template<typename Real> struct CRMinBlocks { static constexpr int v = sizeof(Real) == 4 ? 5 : 2; };
+
+template<typename Real> __device__ __forceinline__ V4<Real> lds4(const Real* p) { return *reinterpret_cast<const V4<Real>*>(p); }
+template<typename Real> __device__ __forceinline__ void sts4(Real* p, const V4<Real>& v) { *reinterpret_cast<V4<Real>*>(p) = v; }
+
+// ------------------------------------------------------------------------------------ shortwave
+template<typename Real, int LPC, bool CLOUD, int NE>
+__global__ void __launch_bounds__(CR_T, CRMinBlocks<Real>::v)
+sw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const TileState<Real> st,
+              const FusedArgs<Real> a)
+{
+    using G = Geo<4 * LPC, NE, false>;
+    constexpr int GW = 4 * LPC, NCB = CR_CH / GW;
+    extern __shared__ __align__(16) unsigned char cr_smem[];
+    __shared__ BandArgs sB;
+    const int nlay = a.nlay, nlev = nlay + 1, nc = a.nc;
+    const size_t ws = (size_t)nlev * CR_CH;
+    Real* const sR = reinterpret_cast<Real*>(cr_smem);      // rows: level 0 at row 0, layer k at row k+1
+    Real* const sT = sR + ws; Real* const sU = sT + ws; Real* const sV = sU + ws; Real* const sN = sV + ws;
+    Real* const acc = sN + ws;                               // [NCB][3][nlev] broadband up, dn, dir
+
+    const int tid = threadIdx.x;
+    const int quad = tid & 3, lsub = tid >> 2;
+    const int cb = quad / LPC, q = quad % LPC, q4 = q * 4;
+    const int craw = blockIdx.x * NCB + cb;
+    const bool active = craw < nc;
+    const int c = active ? craw : nc - 1;
+    const size_t tcl = (size_t)nc * nlay;
+    const size_t cg = (size_t)a.c0 + c;
+    const unsigned* tm = st.tmask + (size_t)c * TMASK_WORDS;
+    const int top = a.top_at_1;
+    const size_t nlev_stride = (size_t)a.ncol * nlev;
+    const Real mu0 = a.mu0[cg];
+    const Real mu0s = M<Real>::max(M<Real>::sqrt(M<Real>::eps), mu0);
+
+    // sweep lanes: chain ch = tid (< 16) -> (column cbs, g-point gs)
+    const int cbs = (tid & 15) / GW, gs = (tid & 15) % GW;
+    const int cs = min(blockIdx.x * NCB + cbs, nc - 1);
+    const size_t cgs = (size_t)a.c0 + cs;
+
+    for (int i = tid; i < NCB * 3 * nlev; i += CR_T) acc[i] = (Real)0;
+
+    for (int ib = 0; ib < P.nbnd; ++ib)
+    {
+        if (tid == 0) sB = bands[ib];
+        __syncthreads();                 // also orders the previous band's phase 3 before this phase 1
+        const BandArgs& B = sB;
+        const int band = B.band;
+        const size_t band_elems = (size_t)P.ntemp * (P.npres + 1) * G::neta(P) * G::RS;
+        const size_t ray_elems = (size_t)P.ntemp * G::neta(P) * G::GW;
+        const Real* kmaj = P.kmajor + band_elems * band + q4;
+        const Real* kray = P.krayl ? P.krayl + ray_elems * band + q4 : nullptr;
+        const size_t ray_side = ray_elems * P.nbnd;
+        const int flav0 = P.band_flavor[2 * band], flav1 = P.band_flavor[2 * band + 1];
+
+        // ---- phase 1: optics + two-stream coefficients of every layer, 32 layers at a time
+        {
+            int k = lsub;
+            RawState<Real> nxt;
+            if (k < nlay) nxt = load_state(st, P, B, tm, flav0, flav1, c, top ? k : nlay - 1 - k, tcl);
+            for (; k < nlay; k += CR_NL)
+            {
+                const int l = top ? k : nlay - 1 - k;
+                const size_t icl = (size_t)c + (size_t)nc * l;
+                const RawState<Real> cur = nxt;
+                if (k + CR_NL < nlay) nxt = load_state(st, P, B, tm, flav0, flav1, c, top ? k + CR_NL : nlay - 1 - k - CR_NL, tcl);
+                Cell<Real> ce;
+                decode_cell(cur.cell, cur.fa, cur.fb, ce);
+                Real tau[4];
+                gas_tau<G>(P, B, ce, kmaj, q4, cur.sc0, cur.sc1, st.scal + icl * (size_t)(P.nscal >> 2), tau);
+                Real ray[4] = {0, 0, 0, 0};
+                if (kray)
+                {
+                    interp_minor<G>(kray + (ce.side ? ray_side : 0), ce, ray);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) ray[j] *= ce.wet;
+                }
+                Real ct = 0, cs_ = 0, cgg = 0;
+                if (CLOUD) { ct = a.cld_tau[icl + tcl * band]; cs_ = a.cld_ssa[icl + tcl * band]; cgg = a.cld_g[icl + tcl * band]; }
+                V4<Real> v0, v1, v2, v3, v4;
+                Real* p0 = &v0.x; Real* p1 = &v1.x; Real* p2 = &v2.x; Real* p3 = &v3.x; Real* p4 = &v4.x;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                {
+                    Real t, w0, g = 0;
+                    combine_rayleigh(tau[j], ray[j], t, w0);
+                    if (CLOUD) increment_2str(t, w0, g, ct, cs_, cgg);
+                    two_stream(t, w0, g, mu0s, p0[j], p1[j], p2[j], p3[j], p4[j]);
+                }
+                const int r = (k + 1) * CR_CH + quad * 4;
+                sts4(sR + r, v0); sts4(sT + r, v1); sts4(sU + r, v2); sts4(sV + r, v3); sts4(sN + r, v4);
+            }
+        }
+        __syncthreads();
+
+        // ---- phase 2: the three sweeps of one chain per lane (mo_rte_solver_kernels.F90:575-609, 1135-1245)
+        if (tid < CR_CH)
+        {
+            const int ch = tid;
+            const Real mu0c = a.mu0[cgs];
+            const bool sun = mu0c > (Real)0;
+            const Real tsi = a.tsi_scaling ? a.tsi_scaling[cgs] : (Real)1;
+            Real dir = gs < B.ngb ? P.solar_source[B.gpt0 + gs] * tsi * mu0c : (Real)0;
+            sN[ch] = dir;
+            // direct beam, top -> surface: source_up/dn = Rdir/Tdir * incident direct flux
+#pragma unroll 4
+            for (int k = 0; k < nlay; ++k)
+            {
+                const int r = (k + 1) * CR_CH + ch;
+                const Real rdir = sU[r], tdir = sV[r], tn = sN[r];
+                sU[r] = sun ? rdir * dir : (Real)0;
+                sV[r] = sun ? tdir * dir : (Real)0;
+                dir = tn * dir;
+                sN[r] = dir;
+            }
+            // adding, surface -> top: leaves {a, b, albedo(k+1), src(k+1)} with
+            //   flux_dn(k+1) = a*flux_dn(k) + b,  flux_up(k+1) = flux_dn(k+1)*albedo(k+1) + src(k+1)
+            Real alb = a.alb_dif[band + (size_t)P.nbnd * cgs];
+            Real src = sun ? dir * a.alb_dir[band + (size_t)P.nbnd * cgs] : (Real)0;
+#pragma unroll 4
+            for (int k = nlay - 1; k >= 0; --k)
+            {
+                const int r = (k + 1) * CR_CH + ch;
+                const Real rdif = sR[r], tdif = sT[r], sup = sU[r], sdn = sV[r];
+                const Real denom = M<Real>::rcp((Real)1 - rdif * alb);
+                const Real td = tdif * denom;
+                sR[r] = td;
+                sT[r] = (rdif * src + sdn) * denom;
+                sU[r] = alb; sV[r] = src;
+                const Real nsrc = sup + td * (src + alb * sdn);
+                alb = rdif + tdif * td * alb;
+                src = nsrc;
+            }
+            // fluxes, top -> surface; diffuse flux_dn(top) = 0
+            Real fdn = 0, fup = fdn * alb + src;
+            sT[ch] = fdn; sV[ch] = fup;
+#pragma unroll 4
+            for (int k = 0; k < nlay; ++k)
+            {
+                const int r = (k + 1) * CR_CH + ch;
+                fdn = fma(sR[r], fdn, sT[r]);
+                fup = fma(fdn, sU[r], sV[r]);
+                sT[r] = fdn; sV[r] = fup;
+            }
+        }
+        __syncthreads();
+
+        // ---- phase 3: g-point sums per level -> broadband accumulators (+ by-band outputs)
+        for (int j0 = 0; j0 < nlev; j0 += CR_NL)
+        {
+            const int jr = j0 + lsub;
+            const bool valid = jr < nlev;
+            const int j = valid ? jr : nlev - 1;
+            const int r = j * CR_CH + quad * 4;
+            const V4<Real> vu = lds4(sV + r), vd = lds4(sT + r), vr = lds4(sN + r);
+            const Real au[4] = {vu.x, vu.y, vu.z, vu.w}, ad[4] = {vd.x, vd.y, vd.z, vd.w}, ar[4] = {vr.x, vr.y, vr.z, vr.w};
+            const Real su = quad_sum<Real, LPC>(au), sd = quad_sum<Real, LPC>(ad), sr = quad_sum<Real, LPC>(ar);
+            if (valid && q == 0 && active)
+            {
+                Real* ac = acc + (size_t)cb * 3 * nlev;
+                ac[j] += su;
+                ac[nlev + j] = (ac[nlev + j] + sr) + sd;
+                ac[2 * nlev + j] += sr;
+                if (a.bnd_up)
+                {
+                    const size_t o = cg + (size_t)a.ncol * (top ? j : nlay - j) + nlev_stride * band;
+                    a.bnd_up[o] = su; a.bnd_dn[o] = sd + sr;
+                    if (a.bnd_dir) a.bnd_dir[o] = sr;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < NCB * nlev; i += CR_T)
+    {
+        const int cbi = i / nlev, j = i - cbi * nlev;
+        const int cc = blockIdx.x * NCB + cbi;
+        if (cc < nc)
+        {
+            const size_t o = (size_t)a.c0 + cc + (size_t)a.ncol * (top ? j : nlay - j);
+            const Real* ac = acc + (size_t)cbi * 3 * nlev;
+            a.flux_up[o] = ac[j]; a.flux_dn[o] = ac[nlev + j];
+            if (a.flux_dir) a.flux_dir[o] = ac[2 * nlev + j];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------- longwave
+template<typename Real, int LPC, bool CLOUD, int NE>
+__global__ void __launch_bounds__(CR_T, CRMinBlocks<Real>::v)
+lw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const TileState<Real> st,
+              const FusedArgs<Real> a)
+{
+    using G = Geo<4 * LPC, NE, true>;
+    constexpr int GW = 4 * LPC, NCB = CR_CH / GW;
+    extern __shared__ __align__(16) unsigned char cr_smem[];
+    __shared__ BandArgs sB;
+    const int nlay = a.nlay, nlev = nlay + 1, nc = a.nc;
+    const size_t ws = (size_t)nlev * CR_CH;
+    Real* const sA = reinterpret_cast<Real*>(cr_smem);   // tau(k) -> source_up(k) -> radiance up at level k; row nlay: surface
+    Real* const sP = sA + ws;                            // Planck fraction of layer k
+    Real* const sC = sP + ws;                            // trans(k); row nlay: surface source
+    Real* const sD = sC + ws;                            // source_dn(k) at row k+1 -> radiance down at level k+1
+    Real* const acc = sD + ws;                           // [NCB][2][nlev] broadband up, dn
+
+    const int tid = threadIdx.x;
+    const int quad = tid & 3, lsub = tid >> 2;
+    const int cb = quad / LPC, q = quad % LPC, q4 = q * 4;
+    const int craw = blockIdx.x * NCB + cb;
+    const bool active = craw < nc;
+    const int c = active ? craw : nc - 1;
+    const size_t tcl = (size_t)nc * nlay;
+    const size_t cg = (size_t)a.c0 + c;
+    const unsigned* tm = st.tmask + (size_t)c * TMASK_WORDS;
+    const int top = a.top_at_1;
+    const size_t nlev_stride = (size_t)a.ncol * nlev;
+    const Real piw = (Real)3.14159265358979323846 * a.weight;
+    const Real tsfc = a.tsfc[cg];
+
+    const int cbs = (tid & 15) / GW;
+    const int cs = min(blockIdx.x * NCB + cbs, nc - 1);
+    const size_t cgs = (size_t)a.c0 + cs;
+
+    for (int i = tid; i < NCB * 2 * nlev; i += CR_T) acc[i] = (Real)0;
+
+    for (int ib = 0; ib < P.nbnd; ++ib)
+    {
+        if (tid == 0) sB = bands[ib];
+        __syncthreads();
+        const BandArgs& B = sB;
+        const int band = B.band;
+        const size_t band_elems = (size_t)P.ntemp * (P.npres + 1) * G::neta(P) * G::RS;
+        const Real* kmaj = P.kmajor + band_elems * band + q4;
+        const Real* plk = P.totplnk + (size_t)P.nplanck * band;
+        const int flav0 = P.band_flavor[2 * band], flav1 = P.band_flavor[2 * band + 1];
+
+        // ---- phase 1a: absorption optical depth and Planck fraction of every layer
+        {
+            int k = lsub;
+            RawState<Real> nxt;
+            if (k < nlay) nxt = load_state(st, P, B, tm, flav0, flav1, c, top ? k : nlay - 1 - k, tcl);
+            for (; k < nlay; k += CR_NL)
+            {
+                const int l = top ? k : nlay - 1 - k;
+                const size_t icl = (size_t)c + (size_t)nc * l;
+                const RawState<Real> cur = nxt;
+                if (k + CR_NL < nlay) nxt = load_state(st, P, B, tm, flav0, flav1, c, top ? k + CR_NL : nlay - 1 - k - CR_NL, tcl);
+                Cell<Real> ce;
+                decode_cell(cur.cell, cur.fa, cur.fb, ce);
+                Real s0[4], s1[4], p0[4], p1[4];
+                interp_major_pair<G>(kmaj, P, ce, s0, s1, p0, p1);
+                V4<Real> vt, vp;
+                Real* tau = &vt.x; Real* pf = &vp.x;
+                Real tl[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { tl[j] = ce.cm0 * s0[j] + ce.cm1 * s1[j]; pf[j] = p0[j] + p1[j]; }
+                add_minor_tau<G>(P, B, ce, q4, cur.sc0, cur.sc1, st.scal + icl * (size_t)(P.nscal >> 2), tl);
+                if (CLOUD)
+                {
+                    const Real ct = a.cld_tau[icl + tcl * band];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) tl[j] += ct;
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) tau[j] = tl[j];
+                const int r = k * CR_CH + quad * 4;
+                sts4(sA + r, vt); sts4(sP + r, vp);
+            }
+        }
+        __syncthreads();
+        // ---- phase 1b: level sources need the Planck fraction of both neighbours (F90:681-708);
+        // then lw_source_noscat + transmissivity per layer (F90:620-680)
+        for (int k = lsub; k < nlay; k += CR_NL)
+        {
+            const int l = top ? k : nlay - 1 - k;
+            const int r = k * CR_CH + quad * 4;
+            const V4<Real> vt = lds4(sA + r), vp = lds4(sP + r);
+            const V4<Real> vm = lds4(sP + (k > 0 ? r - CR_CH : r)), vn = lds4(sP + (k + 1 < nlay ? r + CR_CH : r));
+            const Real blay = planck_at(plk, st.pl_lay[(size_t)c + (size_t)nc * l]);
+            const Real bla = planck_at(plk, st.pl_lev[(size_t)c + (size_t)nc * (top ? k : nlay - k)]);
+            const Real blb = planck_at(plk, st.pl_lev[(size_t)c + (size_t)nc * (top ? k + 1 : nlay - k - 1)]);
+            const Real* tau = &vt.x; const Real* pf = &vp.x; const Real* pm = &vm.x; const Real* pn = &vn.x;
+            V4<Real> ot, ou, od;
+            Real* trp = &ot.x; Real* sup = &ou.x; Real* sdp = &od.x;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+            {
+                const Real lev_a = k > 0 ? M<Real>::sqrt(pm[j] * pf[j]) * bla : pf[j] * bla;
+                const Real lev_b = k + 1 < nlay ? M<Real>::sqrt(pf[j] * pn[j]) * blb : pf[j] * blb;
+                lw_layer(tau[j] * a.secant, pf[j] * blay, lev_a, lev_b, trp[j], sup[j], sdp[j]);
+            }
+            sts4(sC + r, ot); sts4(sA + r, ou); sts4(sD + r + CR_CH, od);
+            if (k == nlay - 1)
+            {
+                // sfc_src = pfrac(surface layer) * B(tsfc)  (F90:640-656)
+                const Real bsfc = planck_band(plk, P.nplanck, P.planck_tmin, P.planck_delta, tsfc);
+                V4<Real> os; os.x = pf[0] * bsfc; os.y = pf[1] * bsfc; os.z = pf[2] * bsfc; os.w = pf[3] * bsfc;
+                sts4(sC + r + CR_CH, os);
+            }
+        }
+        __syncthreads();
+
+        // ---- phase 2: down-sweep, surface, up-sweep of one chain per lane (F90:51-240, 710-745)
+        if (tid < CR_CH)
+        {
+            const int ch = tid;
+            const Real emis = a.sfc_emis[band + (size_t)P.nbnd * cgs];
+            Real rad = 0;                       // incident diffuse flux = 0
+            sD[ch] = rad;
+#pragma unroll 8
+            for (int k = 0; k < nlay; ++k)
+            {
+                const int r = k * CR_CH + ch;
+                rad = fma(sC[r], rad, sD[r + CR_CH]);
+                sD[r + CR_CH] = rad;
+            }
+            rad = rad * ((Real)1 - emis) + emis * sC[nlay * CR_CH + ch];
+            sA[nlay * CR_CH + ch] = rad;
+#pragma unroll 8
+            for (int k = nlay - 1; k >= 0; --k)
+            {
+                const int r = k * CR_CH + ch;
+                rad = fma(sC[r], rad, sA[r]);
+                sA[r] = rad;
+            }
+        }
+        __syncthreads();
+
+        // ---- phase 3: g-point sums per level
+        for (int j0 = 0; j0 < nlev; j0 += CR_NL)
+        {
+            const int jr = j0 + lsub;
+            const bool valid = jr < nlev;
+            const int j = valid ? jr : nlev - 1;
+            const int r = j * CR_CH + quad * 4;
+            const V4<Real> vu = lds4(sA + r), vd = lds4(sD + r);
+            const Real au[4] = {vu.x, vu.y, vu.z, vu.w}, ad[4] = {vd.x, vd.y, vd.z, vd.w};
+            const Real su = quad_sum<Real, LPC>(au) * piw, sd = quad_sum<Real, LPC>(ad) * piw;
+            if (valid && q == 0 && active)
+            {
+                Real* ac = acc + (size_t)cb * 2 * nlev;
+                ac[j] += su; ac[nlev + j] += sd;
+                if (a.bnd_up)
+                {
+                    const size_t o = cg + (size_t)a.ncol * (top ? j : nlay - j) + nlev_stride * band;
+                    a.bnd_up[o] = su; a.bnd_dn[o] = sd;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < NCB * nlev; i += CR_T)
+    {
+        const int cbi = i / nlev, j = i - cbi * nlev;
+        const int cc = blockIdx.x * NCB + cbi;
+        if (cc < nc)
+        {
+            const size_t o = (size_t)a.c0 + cc + (size_t)a.ncol * (top ? j : nlay - j);
+            const Real* ac = acc + (size_t)cbi * 2 * nlev;
+            a.flux_up[o] = ac[j]; a.flux_dn[o] = ac[nlev + j];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------ launchers
+template<typename Real> size_t colres_smem_bytes(int nlay, int gw, bool sw)
+{
+    const int nlev = nlay + 1, ncb = CR_CH / gw;
+    return (size_t)((sw ? 5 : 4) * nlev * CR_CH + (sw ? 3 : 2) * ncb * nlev) * sizeof(Real);
+}
+
+template<typename K> static void cr_launch(K kern, unsigned grid, size_t smem, cudaStream_t s,
+                                           const void* P, const void* bands, const void* st, const void* a)
+{
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    void* args[4] = {const_cast<void*>(P), const_cast<void*>(bands), const_cast<void*>(st), const_cast<void*>(a)};
+    cudaLaunchKernel((const void*)kern, dim3(grid), dim3(CR_T), args, smem, s);
+}
+
+template<typename Real>
+void launch_cols(bool sw, const DevPlan<Real>& P, const BandArgs* bands, const TileState<Real>& st,
+                 const FusedArgs<Real>& a, cudaStream_t s)
+{
+    const int lpc = P.gw / 4, ncb = CR_CH / P.gw;
+    const unsigned grid = (unsigned)((a.nc + ncb - 1) / ncb);
+    const size_t smem = colres_smem_bytes<Real>(a.nlay, P.gw, sw);
+    const bool cloud = a.cld_tau != nullptr;
+    const void* pb = &bands;
+#define RB_GO(K_) cr_launch(K_, grid, smem, s, &P, pb, &st, &a)
+#define RB_NE(KN_, LPC_, CL_) { if (P.neta == 9) RB_GO((KN_<Real, LPC_, CL_, 9>)); else RB_GO((KN_<Real, LPC_, CL_, 0>)); }
+#define RB_ALL(KN_) { if (lpc == 4) { if (cloud) RB_NE(KN_, 4, true) else RB_NE(KN_, 4, false) } \
+                      else { if (cloud) RB_NE(KN_, 2, true) else RB_NE(KN_, 2, false) } }
+    if (sw) RB_ALL(sw_col_kernel) else RB_ALL(lw_col_kernel)
+#undef RB_ALL
+#undef RB_NE
+#undef RB_GO
+    count_launch();
+}
+
+template size_t colres_smem_bytes<float>(int, int, bool);
+template size_t colres_smem_bytes<double>(int, int, bool);
+template void launch_cols<float>(bool, const DevPlan<float>&, const BandArgs*, const TileState<float>&, const FusedArgs<float>&, cudaStream_t);
+template void launch_cols<double>(bool, const DevPlan<double>&, const BandArgs*, const TileState<double>&, const FusedArgs<double>&, cudaStream_t);
+
+}  // namespace rb200

@@ -109,6 +109,7 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
         {
 #pragma unroll
             for (int j = 0; j < 4; ++j) lev_top[j] = pf[j] * blev;
+            if (lead && a.bnd_dn) a.bnd_dn[o_top + nlev_stride * band] = 0;      // no incident diffuse flux
         }
         else
         {

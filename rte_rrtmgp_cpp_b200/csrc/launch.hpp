@@ -40,4 +40,9 @@ template<typename Real> void launch_lw_band(const DevPlan<Real>& P, const BandAr
 template<typename Real> void launch_sw_band(const DevPlan<Real>& P, const BandArgs& B, const TileState<Real>& st,
                                             const FusedArgs<Real>& a, cudaStream_t s);
 
+// ---- colres.cu : one launch = all bands of one column tile, recurrences resident in shared memory
+template<typename Real> size_t colres_smem_bytes(int nlay, int gw, bool sw);
+template<typename Real> void launch_cols(bool sw, const DevPlan<Real>& P, const BandArgs* bands_dev, const TileState<Real>& st,
+                                         const FusedArgs<Real>& a, cudaStream_t s);
+
 }  // namespace rb200
