@@ -266,9 +266,10 @@ int rrtmgp_b200_fluxes_host(rrtmgp_b200_gas_optics* go_lw, const rrtmgp_b200_col
 /* tuning / introspection of the fused path: columns per tile (0 = default), and the number of
  * kernels the last fused call launched (for bench.py's gpu_launches). */
 int rrtmgp_b200_set_tile_columns(rrtmgp_b200_gas_optics* go, int ncol_tile);
-/* which fused kernels a handle uses: 1 = column-resident (recurrences in shared memory, one launch
- * per tile; default), 0 = per-band kernels with recurrence scratch strips in HBM, -1 = default
- * (environment RB200_PATH=strips selects 0).  Both give the same fluxes to rounding. */
+/* which fused kernels a handle uses: 0 = per-band kernels with recurrence scratch strips in HBM
+ * (default: measured faster), 1 = column-resident (recurrences in shared memory, one launch per
+ * tile, ~30x less DRAM traffic), -1 = default (environment RB200_PATH=colres selects 1).
+ * Both give the same fluxes to rounding. */
 int rrtmgp_b200_set_fused_path(rrtmgp_b200_gas_optics* go, int path);
 long long rrtmgp_b200_launch_count(void);
 /* Device-side timing of the fused band kernels: each call first returns (and resets) the time

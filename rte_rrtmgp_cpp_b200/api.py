@@ -562,7 +562,7 @@ class _Radiation_solver:
         return c, f
 
     def set_fused_path(self, path: int) -> None:
-        """1 column-resident kernels (default), 0 per-band kernels with HBM scratch strips."""
+        """0 per-band kernels with HBM scratch strips (default), 1 column-resident kernels."""
         check(lib().rrtmgp_b200_set_fused_path(self.kdist.h, int(path)))
 
     def solve_gpu(self, cols: DeviceColumns, switch_cloud_optics: bool = False, switch_delta_cloud: bool = True,

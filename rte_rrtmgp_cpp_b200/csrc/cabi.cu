@@ -22,8 +22,9 @@ void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 struct Profile { bool on = false; std::vector<cudaEvent_t> ev[2]; double ms[2] = {0, 0}; long long launches[2] = {0, 0}; };
 static Profile g_prof;
 // host-buffer entry: run the LW and the SW band kernels of a chunk on two streams (RB200_HOST_CONCURRENT=0 disables)
-// RB200_PATH=strips selects the earlier per-band kernels with recurrence scratch strips in HBM
-static const bool g_colres = [] { const char* e = getenv("RB200_PATH"); return !(e && e[0] == 's'); }();
+// RB200_PATH=colres selects the column-resident kernels (recurrences in shared memory) instead of the
+// per-band kernels with recurrence scratch strips in HBM, which measure faster (kernels)
+static const bool g_colres = [] { const char* e = getenv("RB200_PATH"); return e && e[0] == 'c'; }();
 static const bool g_host_concurrent = [] { const char* e = getenv("RB200_HOST_CONCURRENT"); return !(e && e[0] == '0'); }();
 
 struct CudaError : std::runtime_error { using std::runtime_error::runtime_error; };

@@ -188,7 +188,7 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
 
 template<typename Real> size_t fused_scratch_bytes(int nslots, int nlay, bool sw)
 {
-    return (size_t)nslots * nlay * (sw ? 4 : 2) * FUSED_THREADS * sizeof(V4<Real>);
+    return (size_t)nslots * nlay * (sw ? 6 : 2) * FUSED_THREADS * sizeof(V4<Real>);
 }
 
 template<typename Real>

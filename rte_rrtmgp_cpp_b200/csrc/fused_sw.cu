@@ -7,11 +7,17 @@
 //   inc_2stream_by_2stream_bybnd (clouds)          mo_optical_props_kernels.F90:451-482
 //   sw_solver_2stream = sw_dif_and_source + adding mo_rte_solver_kernels.F90:503-609,985-1245
 //   sum_broadband / sum_byband
-// Same thread mapping as fused_lw.cu.  Three vertical passes per (column, g-point):
-//   1 top->bottom : optics, two-stream, direct beam; parks {Rdif,Tdif,src_up,src_dn}
-//   2 bottom->top : adding recurrences for albedo/src; re-parks {a,b,albedo,src} with
-//                   flux_dn(l+1) = a*flux_dn(l) + b,  flux_up(l+1) = flux_dn(l+1)*albedo + src
-//   3 top->bottom : two FMAs per level + reduction
+// Same thread mapping as fused_lw.cu.  Two vertical passes per (column, g-point):
+//   1 top->bottom : optics, two-stream, direct beam, and the adding recurrences for the stack above
+//                   each level (reflectance Ra seen from below, emerging downward diffuse flux Sa);
+//                   parks {Rdif,Tdif,src_up,src_dn,Ra,Sa} (6 words per layer and g-point)
+//   2 bottom->top : the reference's adding recurrences for the stack below each level (albedo A,
+//                   source Sb); where the two meet the fluxes follow in closed form,
+//                   flux_dn = (Sa + Ra*Sb)/(1 - Ra*A), flux_up = A*flux_dn + Sb, + reduction.
+// The reference (and the oracle) sweeps a third time, top->bottom, for the fluxes; combining the
+// two half-stacks instead is algebraically the same adding method (same interaction principle,
+// same denominators 1 - R*A > 0) and saves re-parking 4 words per cell: 12 instead of 16 words of
+// HBM scratch traffic per (cell, g-point).
 #include "physics.cuh"
 #include "launch.hpp"
 
@@ -49,7 +55,7 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     const int flav0 = P.band_flavor[2 * band], flav1 = P.band_flavor[2 * band + 1];
     const unsigned* tm = st.tmask + (size_t)c * TMASK_WORDS;
     const int slot = claim_slot(a.slot_busy, a.nslots);
-    V4<Real>* const scr = a.scratch + (size_t)slot * nlay * 4 * T + tid;
+    V4<Real>* const scr = a.scratch + (size_t)slot * nlay * 6 * T + tid;
     const bool lead = active && q == 0;
     const size_t nlev_stride = (size_t)a.ncol * (nlay + 1);
     const int top = a.top_at_1;
@@ -79,9 +85,12 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
         }
     }
 
-    // ---- pass 1: optics + two-stream + direct beam, top -> surface.  The next layer's state is
-    // fetched one iteration ahead (its address does not depend on loaded data: the flavor comes
-    // from the column's tropopause bit mask).
+    // ---- pass 1: optics + two-stream + direct beam + adding of the stack ABOVE each level, top -> surface.
+    // Ra(j) = diffuse reflectance of everything above level j seen from below, Sa(j) = downward diffuse
+    // flux leaving that stack (driven by the direct-beam sources), Ra(0) = Sa(0) = 0.  The next layer's
+    // state is fetched one iteration ahead (its address does not depend on loaded data: the flavor
+    // comes from the column's tropopause bit mask).
+    Real Ra[4] = {0, 0, 0, 0}, Sa[4] = {0, 0, 0, 0};
     RawState<Real> nxt = load_state(st, P, B, tm, flav0, flav1, c, top ? 0 : nlay - 1, tcl);
     size_t o = o_top;
     for (int k = 0; k < nlay; ++k)
@@ -103,8 +112,8 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
         }
         Real ct = 0, cs = 0, cgg = 0;
         if (CLOUD) { ct = a.cld_tau[icl + tcl * band]; cs = a.cld_ssa[icl + tcl * band]; cgg = a.cld_g[icl + tcl * band]; }
-        V4<Real> v0, v1, v2, v3;
-        Real* p0 = &v0.x; Real* p1 = &v1.x; Real* p2 = &v2.x; Real* p3 = &v3.x;
+        V4<Real> v0, v1, v2, v3, v4, v5;
+        Real* p0 = &v0.x; Real* p1 = &v1.x; Real* p2 = &v2.x; Real* p3 = &v3.x; Real* p4 = &v4.x; Real* p5 = &v5.x;
 #pragma unroll
         for (int j = 0; j < 4; ++j)
         {
@@ -113,13 +122,17 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
             if (CLOUD) increment_2str(t, w0, g, ct, cs, cgg);
             Real Rdif, Tdif, Rdir, Tdir, Tnoscat;
             two_stream(t, w0, g, mu0s, Rdif, Tdif, Rdir, Tdir, Tnoscat);
-            p0[j] = Rdif; p1[j] = Tdif;
-            p2[j] = sun ? Rdir * dir[j] : (Real)0;     // source_up
-            p3[j] = sun ? Tdir * dir[j] : (Real)0;     // source_dn
+            const Real su = sun ? Rdir * dir[j] : (Real)0;     // source_up
+            const Real sd = sun ? Tdir * dir[j] : (Real)0;     // source_dn
             dir[j] = Tnoscat * dir[j];
+            p0[j] = Rdif; p1[j] = Tdif; p2[j] = su; p3[j] = sd; p4[j] = Ra[j]; p5[j] = Sa[j];
+            // add layer k below the stack: multiple reflections between Ra (above) and Rdif (the layer)
+            const Real td = Tdif * M<Real>::rcp((Real)1 - Ra[j] * Rdif);
+            Sa[j] = sd + td * (Sa[j] + Ra[j] * su);
+            Ra[j] = Rdif + Tdif * td * Ra[j];
         }
-        V4<Real>* w = scr + (size_t)k * 4 * T;
-        w[0] = v0; w[T] = v1; w[2 * T] = v2; w[3 * T] = v3;
+        V4<Real>* w = scr + (size_t)k * 6 * T;
+        w[0] = v0; w[T] = v1; w[2 * T] = v2; w[3 * T] = v3; w[4 * T] = v4; w[5 * T] = v5;
         const Real s = quad_sum<Real, LPC>(dir);
         o += lstep;
         if (lead)
@@ -129,80 +142,57 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
         }
     }
 
-    // ---- pass 2: adding, surface -> top (F90:1135-1245); scratch read one layer ahead
+    // ---- pass 2: adding of the stack BELOW each level, surface -> top (F90:1135-1245), and the fluxes
+    // where the two stacks meet:  dn(j) = (Sa + Ra*Sb) / (1 - Ra*A),  up(j) = A*dn(j) + Sb.
+    // `o` is at the surface level; scratch is read two layers ahead.
     Real alb[4], src[4];
     {
         const Real adir = a.alb_dir[band + (size_t)P.nbnd * cg];
         const Real adif = a.alb_dif[band + (size_t)P.nbnd * cg];
+        Real fdn[4], fup[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) { alb[j] = adif; src[j] = sun ? dir[j] * adir : (Real)0; }
+        for (int j = 0; j < 4; ++j)
+        {
+            alb[j] = adif; src[j] = sun ? dir[j] * adir : (Real)0;
+            fdn[j] = (Sa[j] + Ra[j] * src[j]) * M<Real>::rcp((Real)1 - Ra[j] * alb[j]);
+            fup[j] = alb[j] * fdn[j] + src[j];
+        }
+        const Real su = quad_sum<Real, LPC>(fup), sd = quad_sum<Real, LPC>(fdn);
+        if (lead)
+        {
+            atomicAdd(a.flux_up + o, su); atomicAdd(a.flux_dn + o, sd);
+            if (a.bnd_up) { a.bnd_up[o + nlev_stride * band] = su; a.bnd_dn[o + nlev_stride * band] = sd + a.bnd_dir[o + nlev_stride * band]; }
+        }
     }
     for (int k0 = nlay - 1; k0 >= 0; k0 -= 2)
     {
-        V4<Real> in[2][4];
+        V4<Real> in[2][6];
 #pragma unroll
         for (int u = 0; u < 2; ++u)
         {
-            const V4<Real>* w = scr + (size_t)max(k0 - u, 0) * 4 * T;
-            in[u][0] = w[0]; in[u][1] = w[T]; in[u][2] = w[2 * T]; in[u][3] = w[3 * T];
+            const V4<Real>* w = scr + (size_t)max(k0 - u, 0) * 6 * T;
+#pragma unroll
+            for (int m = 0; m < 6; ++m) in[u][m] = w[m * T];
         }
 #pragma unroll
         for (int u = 0; u < 2; ++u)
         {
             if (k0 - u < 0) break;
             const Real* rdif = &in[u][0].x; const Real* tdif = &in[u][1].x; const Real* sup = &in[u][2].x; const Real* sdn = &in[u][3].x;
-            V4<Real> oa, ob, oc, od;
-            Real* pa = &oa.x; Real* pb = &ob.x; Real* pc = &oc.x; Real* pd = &od.x;
+            const Real* ra = &in[u][4].x; const Real* sa = &in[u][5].x;
+            Real fdn[4], fup[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j)
             {
-                const Real denom = M<Real>::rcp((Real)1 - rdif[j] * alb[j]);
-                const Real td = tdif[j] * denom;
-                pa[j] = td;
-                pb[j] = (rdif[j] * src[j] + sdn[j]) * denom;
-                pc[j] = alb[j]; pd[j] = src[j];
+                const Real td = tdif[j] * M<Real>::rcp((Real)1 - rdif[j] * alb[j]);
                 const Real nsrc = sup[j] + td * (src[j] + alb[j] * sdn[j]);
                 alb[j] = rdif[j] + tdif[j] * td * alb[j];
                 src[j] = nsrc;
+                fdn[j] = (sa[j] + ra[j] * src[j]) * M<Real>::rcp((Real)1 - ra[j] * alb[j]);
+                fup[j] = alb[j] * fdn[j] + src[j];
             }
-            V4<Real>* wc = scr + (size_t)(k0 - u) * 4 * T;
-            wc[0] = oa; wc[T] = ob; wc[2 * T] = oc; wc[3 * T] = od;
-        }
-    }
-
-    // ---- pass 3: fluxes, top -> surface; diffuse flux_dn(top) = 0 (no inc_flux_dif)
-    Real fdn[4] = {0, 0, 0, 0}, fup[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) fup[j] = fdn[j] * alb[j] + src[j];
-    o = o_top;
-    {
-        const Real su = quad_sum<Real, LPC>(fup);
-        if (lead)
-        {
-            atomicAdd(a.flux_up + o, su);
-            if (a.bnd_up) { a.bnd_up[o + nlev_stride * band] = su; a.bnd_dn[o + nlev_stride * band] = a.bnd_dir[o + nlev_stride * band]; }
-        }
-    }
-    for (int k0 = 0; k0 < nlay; k0 += 4)
-    {
-        V4<Real> in[4][4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-        {
-            const V4<Real>* w = scr + (size_t)min(k0 + u, nlay - 1) * 4 * T;
-            in[u][0] = w[0]; in[u][1] = w[T]; in[u][2] = w[2 * T]; in[u][3] = w[3 * T];
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-        {
-            if (k0 + u >= nlay) break;
-            const V4<Real> va = in[u][0], vb = in[u][1], vc = in[u][2], vd = in[u][3];
-            fdn[0] = fma(va.x, fdn[0], vb.x); fdn[1] = fma(va.y, fdn[1], vb.y);
-            fdn[2] = fma(va.z, fdn[2], vb.z); fdn[3] = fma(va.w, fdn[3], vb.w);
-            fup[0] = fma(fdn[0], vc.x, vd.x); fup[1] = fma(fdn[1], vc.y, vd.y);
-            fup[2] = fma(fdn[2], vc.z, vd.z); fup[3] = fma(fdn[3], vc.w, vd.w);
             const Real su = quad_sum<Real, LPC>(fup), sd = quad_sum<Real, LPC>(fdn);
-            o += lstep;
+            o -= lstep;
             if (lead)
             {
                 atomicAdd(a.flux_up + o, su); atomicAdd(a.flux_dn + o, sd);
