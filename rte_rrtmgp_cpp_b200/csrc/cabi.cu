@@ -98,7 +98,7 @@ struct rrtmgp_b200_gas_optics
     int dtype = 0, device = 0;
     bool host_only = false;
     HostPlan h;
-    DevBuf kmajor, pfrac, krayl, kminor[2], totplnk, solar, temp_ref, vmr_ref, flavor, band_flavor, band_lims, minor_slots[2];
+    DevBuf kmajor, pfrac, krayl, kminor[2], totplnk, solar, temp_ref, vmr_ref, eta_half, flavor, band_flavor, band_lims, minor_slots[2];
     DevPlan<float> pf{};
     DevPlan<double> pd{};
     std::vector<BandArgs> bands;
@@ -134,6 +134,20 @@ static void fill_devplan(rrtmgp_b200_gas_optics* g, DevPlan<Real>& P)
     else { g->solar.upload_as<Real>(h.solar_source); if (!h.krayl.empty()) g->krayl.upload_as<Real>(h.krayl); }
     for (int s = 0; s < 2; ++s) g->kminor[s].upload_as<Real>(h.minor[s].table);
     g->temp_ref.upload(h.temp_ref); g->vmr_ref.upload(h.vmr_ref);
+    {
+        // ratio_eta_half of interpolation (F90:137-139) depends on (side, flavor, reference temperature)
+        // only: the same IEEE double division, done once here instead of per (column, layer) on the device
+        std::vector<double> eh((size_t)2 * h.nflav * h.ntemp);
+        for (int it = 0; it < h.ntemp; ++it)
+            for (int f = 0; f < h.nflav; ++f)
+                for (int sd = 0; sd < 2; ++sd)
+                {
+                    const int ig1 = h.flavor[2 * f], ig2 = h.flavor[2 * f + 1];
+                    eh[sd + 2 * (f + (size_t)h.nflav * it)] = h.vmr_ref[sd + 2 * (ig1 + (size_t)(h.ngas + 1) * it)] /
+                                                              h.vmr_ref[sd + 2 * (ig2 + (size_t)(h.ngas + 1) * it)];
+                }
+        g->eta_half.upload(eh);
+    }
     g->flavor.upload(h.flavor); g->band_flavor.upload(h.band_flavor); g->band_lims.upload(h.band_lims_gpt);
     P.is_lw = h.is_lw; P.ntemp = h.ntemp; P.npres = h.npres; P.neta = h.neta; P.nbnd = h.nbnd; P.ngpt = h.ngpt;
     P.nflav = h.nflav; P.ngas = h.ngas; P.gw = h.gw; P.nplanck = h.nplanck; P.idx_h2o = h.idx_h2o;
@@ -141,7 +155,7 @@ static void fill_devplan(rrtmgp_b200_gas_optics* g, DevPlan<Real>& P)
     P.row_stride = h.row_stride;
     P.kminor[0] = (const Real*)g->kminor[0].p; P.kminor[1] = (const Real*)g->kminor[1].p;
     P.totplnk = (const Real*)g->totplnk.p; P.solar_source = (const Real*)g->solar.p;
-    P.temp_ref = (const double*)g->temp_ref.p; P.vmr_ref = (const double*)g->vmr_ref.p;
+    P.temp_ref = (const double*)g->temp_ref.p; P.vmr_ref = (const double*)g->vmr_ref.p; P.eta_half = (const double*)g->eta_half.p;
     P.flavor = (const int*)g->flavor.p; P.band_flavor = (const int*)g->band_flavor.p; P.band_lims = (const int*)g->band_lims.p;
     for (int sd = 0; sd < 2; ++sd)
     {
@@ -773,8 +787,22 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
     const int wave = std::max(sw ? sw_blocks_per_wave<Real>(h.gw) : lw_blocks_per_wave<Real>(h.gw), 1);
     const int nslots = colres ? 0 : 2 * wave;
     int tile = g->tile_cols;
-    if (tile <= 0) tile = 8 * wave * cpb;
+    if (tile <= 0)
+    {
+        // 8 waves per tile; 16 when the interpolation state of such a tile takes under a quarter of the
+        // free device memory (longer launches: fewer tails, fewer prologue launches)
+        tile = 8 * wave * cpb;
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess &&
+            state_bytes<Real>(h, 2 * tile, nlay) < (free_b + g->ws.cap) / 4) tile *= 2;
+    }
     tile = std::min(tile, ncol);
+    {
+        // equal tiles (rounded up to whole CTAs) instead of full tiles plus a remainder
+        const int ntiles = (ncol + tile - 1) / tile;
+        tile = (((ncol + ntiles - 1) / ntiles + cpb - 1) / cpb) * cpb;
+        tile = std::min(tile, ncol);
+    }
     const size_t tcl = (size_t)tile * nlay, ncl = (size_t)ncol * nlay, ncv = (size_t)ncol * nlev;
     size_t need = state_bytes<Real>(h, tile, nlay) + pad256(fused_scratch_bytes<Real>(nslots, nlay, sw)) + pad256(nslots * sizeof(int)) + 4096;
     if (!cols->d_col_dry) need += pad256(ncl * sizeof(Real));
@@ -915,6 +943,11 @@ void fluxes_host(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, co
                 chunk = std::max(chunk, g->tile_cols > 0 ? g->tile_cols : 8 * wave * cpb);
             }
     chunk = std::min(chunk, ncol);
+    if (chunk_cols <= 0)
+    {
+        const int nchunks = (ncol + chunk - 1) / chunk;          // equal chunks, whole CTAs
+        chunk = std::min((((ncol + nchunks - 1) / nchunks + 31) / 32) * 32, ncol);
+    }
 
     // inputs, de-duplicated by host address (LW and SW normally share play/plev/tlay/vmr/col_dry)
     std::vector<HostItem> items;

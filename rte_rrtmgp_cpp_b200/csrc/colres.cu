@@ -22,15 +22,24 @@
 namespace rb200 {
 
 constexpr int CR_T = FUSED_THREADS;      // 128
-constexpr int CR_CH = 16;                // chains per CTA = floats per shared-memory row
+constexpr int CR_CH = 16;                // chains per CTA = floats per shared-memory word row
 constexpr int CR_NL = CR_T / 4;          // layers in flight in phase 1 (4 quads per row)
+constexpr int CR_RS = 80;                // floats per level row: up to 5 words x 16 chains (80 = 16 mod 32 keeps
+                                         // the phase-1 vector stores of consecutive levels on disjoint banks)
 
 template<typename Real> struct CRMinBlocks { static constexpr int v = sizeof(Real) == 4 ? 5 : 2; };
 
 template<typename Real> __device__ __forceinline__ V4<Real> lds4(const Real* p) { return *reinterpret_cast<const V4<Real>*>(p); }
 template<typename Real> __device__ __forceinline__ void sts4(Real* p, const V4<Real>& v) { *reinterpret_cast<V4<Real>*>(p) = v; }
 
+// Shared memory: row j (level j; layer k lives in row k+1 unless noted) holds the words of the 16
+// chains back to back, sm[j*CR_RS + w*16 + chain], so a sweep lane walks one pointer with
+// compile-time word offsets.  Sweeps load a group of rows into registers before touching any of
+// them (the compiler cannot move shared loads above the stores of the previous row itself).
+
 // ------------------------------------------------------------------------------------ shortwave
+// words: 0 Rdif -> a, 1 Tdif -> b -> flux_dn(diffuse), 2 Rdir -> source_up -> albedo, 3 Tdir -> source_dn -> src -> flux_up,
+//        4 Tnoscat -> direct flux
 template<typename Real, int LPC, bool CLOUD, int NE>
 __global__ void __launch_bounds__(CR_T, CRMinBlocks<Real>::v)
 sw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const TileState<Real> st,
@@ -38,13 +47,12 @@ sw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
 {
     using G = Geo<4 * LPC, NE, false>;
     constexpr int GW = 4 * LPC, NCB = CR_CH / GW;
+    constexpr int W0 = 0, W1 = 16, W2 = 32, W3 = 48, W4 = 64;
     extern __shared__ __align__(16) unsigned char cr_smem[];
     __shared__ BandArgs sB;
     const int nlay = a.nlay, nlev = nlay + 1, nc = a.nc;
-    const size_t ws = (size_t)nlev * CR_CH;
-    Real* const sR = reinterpret_cast<Real*>(cr_smem);      // rows: level 0 at row 0, layer k at row k+1
-    Real* const sT = sR + ws; Real* const sU = sT + ws; Real* const sV = sU + ws; Real* const sN = sV + ws;
-    Real* const acc = sN + ws;                               // [NCB][3][nlev] broadband up, dn, dir
+    Real* const sm = reinterpret_cast<Real*>(cr_smem);
+    Real* const acc = sm + (size_t)nlev * CR_RS;            // [NCB][3][nlev] broadband up, dn, dir
 
     const int tid = threadIdx.x;
     const int quad = tid & 3, lsub = tid >> 2;
@@ -114,8 +122,8 @@ sw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
                     if (CLOUD) increment_2str(t, w0, g, ct, cs_, cgg);
                     two_stream(t, w0, g, mu0s, p0[j], p1[j], p2[j], p3[j], p4[j]);
                 }
-                const int r = (k + 1) * CR_CH + quad * 4;
-                sts4(sR + r, v0); sts4(sT + r, v1); sts4(sU + r, v2); sts4(sV + r, v3); sts4(sN + r, v4);
+                Real* r = sm + (k + 1) * CR_RS + quad * 4;
+                sts4(r + W0, v0); sts4(r + W1, v1); sts4(r + W2, v2); sts4(r + W3, v3); sts4(r + W4, v4);
             }
         }
         __syncthreads();
@@ -123,51 +131,90 @@ sw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
         // ---- phase 2: the three sweeps of one chain per lane (mo_rte_solver_kernels.F90:575-609, 1135-1245)
         if (tid < CR_CH)
         {
-            const int ch = tid;
+            Real* const p0 = sm + tid;
             const Real mu0c = a.mu0[cgs];
             const bool sun = mu0c > (Real)0;
             const Real tsi = a.tsi_scaling ? a.tsi_scaling[cgs] : (Real)1;
             Real dir = gs < B.ngb ? P.solar_source[B.gpt0 + gs] * tsi * mu0c : (Real)0;
-            sN[ch] = dir;
+            p0[W4] = dir;
             // direct beam, top -> surface: source_up/dn = Rdir/Tdir * incident direct flux
-#pragma unroll 4
-            for (int k = 0; k < nlay; ++k)
             {
-                const int r = (k + 1) * CR_CH + ch;
-                const Real rdir = sU[r], tdir = sV[r], tn = sN[r];
-                sU[r] = sun ? rdir * dir : (Real)0;
-                sV[r] = sun ? tdir * dir : (Real)0;
-                dir = tn * dir;
-                sN[r] = dir;
+                Real* p = p0 + CR_RS;
+                int k = 0;
+                for (; k + 8 <= nlay; k += 8, p += 8 * CR_RS)
+                {
+                    Real rd[8], td[8], tn[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) { rd[u] = p[u * CR_RS + W2]; td[u] = p[u * CR_RS + W3]; tn[u] = p[u * CR_RS + W4]; }
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                    {
+                        p[u * CR_RS + W2] = sun ? rd[u] * dir : (Real)0;
+                        p[u * CR_RS + W3] = sun ? td[u] * dir : (Real)0;
+                        dir = tn[u] * dir;
+                        p[u * CR_RS + W4] = dir;
+                    }
+                }
+                for (; k < nlay; ++k, p += CR_RS)
+                {
+                    const Real rd = p[W2], td = p[W3], tn = p[W4];
+                    p[W2] = sun ? rd * dir : (Real)0; p[W3] = sun ? td * dir : (Real)0;
+                    dir = tn * dir; p[W4] = dir;
+                }
             }
             // adding, surface -> top: leaves {a, b, albedo(k+1), src(k+1)} with
             //   flux_dn(k+1) = a*flux_dn(k) + b,  flux_up(k+1) = flux_dn(k+1)*albedo(k+1) + src(k+1)
             Real alb = a.alb_dif[band + (size_t)P.nbnd * cgs];
             Real src = sun ? dir * a.alb_dir[band + (size_t)P.nbnd * cgs] : (Real)0;
-#pragma unroll 4
-            for (int k = nlay - 1; k >= 0; --k)
+            auto add_row = [&](Real* pr, Real rdif, Real tdif, Real sup, Real sdn)
             {
-                const int r = (k + 1) * CR_CH + ch;
-                const Real rdif = sR[r], tdif = sT[r], sup = sU[r], sdn = sV[r];
                 const Real denom = M<Real>::rcp((Real)1 - rdif * alb);
                 const Real td = tdif * denom;
-                sR[r] = td;
-                sT[r] = (rdif * src + sdn) * denom;
-                sU[r] = alb; sV[r] = src;
+                pr[W0] = td;
+                pr[W1] = (rdif * src + sdn) * denom;
+                pr[W2] = alb; pr[W3] = src;
                 const Real nsrc = sup + td * (src + alb * sdn);
                 alb = rdif + tdif * td * alb;
                 src = nsrc;
+            };
+            {
+                Real* p = p0 + nlay * CR_RS;           // row of layer nlay-1
+                int k = nlay - 1;
+                for (; k >= 3; k -= 4, p -= 4 * CR_RS)
+                {
+                    Real r0[4], r1[4], r2[4], r3[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) { const Real* pr = p - u * CR_RS; r0[u] = pr[W0]; r1[u] = pr[W1]; r2[u] = pr[W2]; r3[u] = pr[W3]; }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) add_row(p - u * CR_RS, r0[u], r1[u], r2[u], r3[u]);
+                }
+                for (; k >= 0; --k, p -= CR_RS) add_row(p, p[W0], p[W1], p[W2], p[W3]);
             }
             // fluxes, top -> surface; diffuse flux_dn(top) = 0
             Real fdn = 0, fup = fdn * alb + src;
-            sT[ch] = fdn; sV[ch] = fup;
-#pragma unroll 4
-            for (int k = 0; k < nlay; ++k)
+            p0[W1] = fdn; p0[W3] = fup;
             {
-                const int r = (k + 1) * CR_CH + ch;
-                fdn = fma(sR[r], fdn, sT[r]);
-                fup = fma(fdn, sU[r], sV[r]);
-                sT[r] = fdn; sV[r] = fup;
+                Real* p = p0 + CR_RS;
+                int k = 0;
+                for (; k + 8 <= nlay; k += 8, p += 8 * CR_RS)
+                {
+                    Real ca[8], cb_[8], cc[8], cd[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) { const Real* pr = p + u * CR_RS; ca[u] = pr[W0]; cb_[u] = pr[W1]; cc[u] = pr[W2]; cd[u] = pr[W3]; }
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                    {
+                        fdn = fma(ca[u], fdn, cb_[u]);
+                        fup = fma(fdn, cc[u], cd[u]);
+                        p[u * CR_RS + W1] = fdn; p[u * CR_RS + W3] = fup;
+                    }
+                }
+                for (; k < nlay; ++k, p += CR_RS)
+                {
+                    fdn = fma(p[W0], fdn, p[W1]);
+                    fup = fma(fdn, p[W2], p[W3]);
+                    p[W1] = fdn; p[W3] = fup;
+                }
             }
         }
         __syncthreads();
@@ -178,8 +225,8 @@ sw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
             const int jr = j0 + lsub;
             const bool valid = jr < nlev;
             const int j = valid ? jr : nlev - 1;
-            const int r = j * CR_CH + quad * 4;
-            const V4<Real> vu = lds4(sV + r), vd = lds4(sT + r), vr = lds4(sN + r);
+            const Real* r = sm + j * CR_RS + quad * 4;
+            const V4<Real> vu = lds4(r + W3), vd = lds4(r + W1), vr = lds4(r + W4);
             const Real au[4] = {vu.x, vu.y, vu.z, vu.w}, ad[4] = {vd.x, vd.y, vd.z, vd.w}, ar[4] = {vr.x, vr.y, vr.z, vr.w};
             const Real su = quad_sum<Real, LPC>(au), sd = quad_sum<Real, LPC>(ad), sr = quad_sum<Real, LPC>(ar);
             if (valid && q == 0 && active)
@@ -213,6 +260,11 @@ sw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
 }
 
 // ------------------------------------------------------------------------------------- longwave
+// words (rows are layers k / levels j, no shift except word 3):
+//   0 tau(k) -> source_up(k) -> radiance up at level k; row nlay: radiance up at the surface
+//   1 Planck fraction of layer k
+//   2 trans(k); row nlay: surface source
+//   3 row k+1: source_dn(k) -> radiance down at level k+1; row 0: incident (0)
 template<typename Real, int LPC, bool CLOUD, int NE>
 __global__ void __launch_bounds__(CR_T, CRMinBlocks<Real>::v)
 lw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const TileState<Real> st,
@@ -220,15 +272,12 @@ lw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
 {
     using G = Geo<4 * LPC, NE, true>;
     constexpr int GW = 4 * LPC, NCB = CR_CH / GW;
+    constexpr int W0 = 0, W1 = 16, W2 = 32, W3 = 48;
     extern __shared__ __align__(16) unsigned char cr_smem[];
     __shared__ BandArgs sB;
     const int nlay = a.nlay, nlev = nlay + 1, nc = a.nc;
-    const size_t ws = (size_t)nlev * CR_CH;
-    Real* const sA = reinterpret_cast<Real*>(cr_smem);   // tau(k) -> source_up(k) -> radiance up at level k; row nlay: surface
-    Real* const sP = sA + ws;                            // Planck fraction of layer k
-    Real* const sC = sP + ws;                            // trans(k); row nlay: surface source
-    Real* const sD = sC + ws;                            // source_dn(k) at row k+1 -> radiance down at level k+1
-    Real* const acc = sD + ws;                           // [NCB][2][nlev] broadband up, dn
+    Real* const sm = reinterpret_cast<Real*>(cr_smem);
+    Real* const acc = sm + (size_t)nlev * CR_RS;         // [NCB][2][nlev] broadband up, dn
 
     const int tid = threadIdx.x;
     const int quad = tid & 3, lsub = tid >> 2;
@@ -290,8 +339,8 @@ lw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
                 }
 #pragma unroll
                 for (int j = 0; j < 4; ++j) tau[j] = tl[j];
-                const int r = k * CR_CH + quad * 4;
-                sts4(sA + r, vt); sts4(sP + r, vp);
+                Real* r = sm + k * CR_RS + quad * 4;
+                sts4(r + W0, vt); sts4(r + W1, vp);
             }
         }
         __syncthreads();
@@ -300,9 +349,9 @@ lw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
         for (int k = lsub; k < nlay; k += CR_NL)
         {
             const int l = top ? k : nlay - 1 - k;
-            const int r = k * CR_CH + quad * 4;
-            const V4<Real> vt = lds4(sA + r), vp = lds4(sP + r);
-            const V4<Real> vm = lds4(sP + (k > 0 ? r - CR_CH : r)), vn = lds4(sP + (k + 1 < nlay ? r + CR_CH : r));
+            Real* r = sm + k * CR_RS + quad * 4;
+            const V4<Real> vt = lds4(r + W0), vp = lds4(r + W1);
+            const V4<Real> vm = lds4(r + W1 - (k > 0 ? CR_RS : 0)), vn = lds4(r + W1 + (k + 1 < nlay ? CR_RS : 0));
             const Real blay = planck_at(plk, st.pl_lay[(size_t)c + (size_t)nc * l]);
             const Real bla = planck_at(plk, st.pl_lev[(size_t)c + (size_t)nc * (top ? k : nlay - k)]);
             const Real blb = planck_at(plk, st.pl_lev[(size_t)c + (size_t)nc * (top ? k + 1 : nlay - k - 1)]);
@@ -316,13 +365,13 @@ lw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
                 const Real lev_b = k + 1 < nlay ? M<Real>::sqrt(pf[j] * pn[j]) * blb : pf[j] * blb;
                 lw_layer(tau[j] * a.secant, pf[j] * blay, lev_a, lev_b, trp[j], sup[j], sdp[j]);
             }
-            sts4(sC + r, ot); sts4(sA + r, ou); sts4(sD + r + CR_CH, od);
+            sts4(r + W2, ot); sts4(r + W0, ou); sts4(r + CR_RS + W3, od);
             if (k == nlay - 1)
             {
                 // sfc_src = pfrac(surface layer) * B(tsfc)  (F90:640-656)
                 const Real bsfc = planck_band(plk, P.nplanck, P.planck_tmin, P.planck_delta, tsfc);
                 V4<Real> os; os.x = pf[0] * bsfc; os.y = pf[1] * bsfc; os.z = pf[2] * bsfc; os.w = pf[3] * bsfc;
-                sts4(sC + r + CR_CH, os);
+                sts4(r + CR_RS + W2, os);
             }
         }
         __syncthreads();
@@ -330,25 +379,37 @@ lw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
         // ---- phase 2: down-sweep, surface, up-sweep of one chain per lane (F90:51-240, 710-745)
         if (tid < CR_CH)
         {
-            const int ch = tid;
+            Real* const p0 = sm + tid;
             const Real emis = a.sfc_emis[band + (size_t)P.nbnd * cgs];
             Real rad = 0;                       // incident diffuse flux = 0
-            sD[ch] = rad;
-#pragma unroll 8
-            for (int k = 0; k < nlay; ++k)
+            p0[W3] = rad;
             {
-                const int r = k * CR_CH + ch;
-                rad = fma(sC[r], rad, sD[r + CR_CH]);
-                sD[r + CR_CH] = rad;
+                Real* p = p0;
+                int k = 0;
+                for (; k + 8 <= nlay; k += 8, p += 8 * CR_RS)
+                {
+                    Real tr[8], sd[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) { tr[u] = p[u * CR_RS + W2]; sd[u] = p[(u + 1) * CR_RS + W3]; }
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) { rad = fma(tr[u], rad, sd[u]); p[(u + 1) * CR_RS + W3] = rad; }
+                }
+                for (; k < nlay; ++k, p += CR_RS) { rad = fma(p[W2], rad, p[CR_RS + W3]); p[CR_RS + W3] = rad; }
             }
-            rad = rad * ((Real)1 - emis) + emis * sC[nlay * CR_CH + ch];
-            sA[nlay * CR_CH + ch] = rad;
-#pragma unroll 8
-            for (int k = nlay - 1; k >= 0; --k)
+            rad = rad * ((Real)1 - emis) + emis * p0[nlay * CR_RS + W2];
+            p0[nlay * CR_RS + W0] = rad;
             {
-                const int r = k * CR_CH + ch;
-                rad = fma(sC[r], rad, sA[r]);
-                sA[r] = rad;
+                Real* p = p0 + (nlay - 1) * CR_RS;
+                int k = nlay - 1;
+                for (; k >= 7; k -= 8, p -= 8 * CR_RS)
+                {
+                    Real tr[8], su[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) { tr[u] = p[-u * CR_RS + W2]; su[u] = p[-u * CR_RS + W0]; }
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) { rad = fma(tr[u], rad, su[u]); p[-u * CR_RS + W0] = rad; }
+                }
+                for (; k >= 0; --k, p -= CR_RS) { rad = fma(p[W2], rad, p[W0]); p[W0] = rad; }
             }
         }
         __syncthreads();
@@ -359,8 +420,8 @@ lw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
             const int jr = j0 + lsub;
             const bool valid = jr < nlev;
             const int j = valid ? jr : nlev - 1;
-            const int r = j * CR_CH + quad * 4;
-            const V4<Real> vu = lds4(sA + r), vd = lds4(sD + r);
+            const Real* r = sm + j * CR_RS + quad * 4;
+            const V4<Real> vu = lds4(r + W0), vd = lds4(r + W3);
             const Real au[4] = {vu.x, vu.y, vu.z, vu.w}, ad[4] = {vd.x, vd.y, vd.z, vd.w};
             const Real su = quad_sum<Real, LPC>(au) * piw, sd = quad_sum<Real, LPC>(ad) * piw;
             if (valid && q == 0 && active)
@@ -393,7 +454,7 @@ lw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
 template<typename Real> size_t colres_smem_bytes(int nlay, int gw, bool sw)
 {
     const int nlev = nlay + 1, ncb = CR_CH / gw;
-    return (size_t)((sw ? 5 : 4) * nlev * CR_CH + (sw ? 3 : 2) * ncb * nlev) * sizeof(Real);
+    return (size_t)(nlev * CR_RS + (sw ? 3 : 2) * ncb * nlev) * sizeof(Real);
 }
 
 template<typename K> static void cr_launch(K kern, unsigned grid, size_t smem, cudaStream_t s,

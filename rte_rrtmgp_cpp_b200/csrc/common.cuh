@@ -30,6 +30,45 @@ template<> __device__ __forceinline__ V4<double> ldg4<double>(const double* p)
     return V4<double>{a.x, a.y, b.x, b.y};
 }
 
+// Streaming (evict-first) vector access for the recurrence scratch strips: they are written once and
+// read once, so they should not displace the k-tables and the interpolation state from L2.
+__device__ __forceinline__ void st_stream(V4<float>* p, const V4<float>& v)
+{
+#ifdef RB_NO_STREAM_HINT
+    *p = v;
+#else
+    __stcs(reinterpret_cast<float4*>(p), make_float4(v.x, v.y, v.z, v.w));
+#endif
+}
+__device__ __forceinline__ void st_stream(V4<double>* p, const V4<double>& v)
+{
+#ifdef RB_NO_STREAM_HINT
+    *p = v;
+#else
+    __stcs(reinterpret_cast<double2*>(p), make_double2(v.x, v.y));
+    __stcs(reinterpret_cast<double2*>(p) + 1, make_double2(v.z, v.w));
+#endif
+}
+__device__ __forceinline__ V4<float> ld_stream(const V4<float>* p)
+{
+#ifdef RB_NO_STREAM_HINT
+    return *p;
+#else
+    const float4 v = __ldcs(reinterpret_cast<const float4*>(p));
+    return V4<float>{v.x, v.y, v.z, v.w};
+#endif
+}
+__device__ __forceinline__ V4<double> ld_stream(const V4<double>* p)
+{
+#ifdef RB_NO_STREAM_HINT
+    return *p;
+#else
+    const double2 a = __ldcs(reinterpret_cast<const double2*>(p));
+    const double2 b = __ldcs(reinterpret_cast<const double2*>(p) + 1);
+    return V4<double>{a.x, a.y, b.x, b.y};
+#endif
+}
+
 // ---- per-precision math: fp32 uses the fast SFU paths, fp64 the accurate library ------------
 template<typename Real> struct M;
 template<> struct M<float>
@@ -41,9 +80,11 @@ template<> struct M<float>
     static __device__ __forceinline__ float sqrt(float x) { return sqrtf(x); }
     static __device__ __forceinline__ float div(float a, float b) { return a / b; }
 #else
-    static __device__ __forceinline__ float exp(float x) { return __expf(x); }
+    // bare SFU forms: ex2/rcp.approx.ftz without the range fix-ups of __expf / __fdividef (2 instructions
+    // instead of 5; arguments here are never denormal or beyond 2^126)
+    static __device__ __forceinline__ float exp(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x * 1.4426950408889634f)); return r; }
     static __device__ __forceinline__ float sqrt(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
-    static __device__ __forceinline__ float div(float a, float b) { return __fdividef(a, b); }
+    static __device__ __forceinline__ float div(float a, float b) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(b)); return a * r; }
 #endif
     static __device__ __forceinline__ float rcp(float a) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
     static __device__ __forceinline__ float fabs(float a) { return fabsf(a); }
@@ -79,6 +120,7 @@ template<typename Real> struct DevPlan
     const Real* solar_source;  // [ngpt] (SW)
     const double* temp_ref;    // [ntemp]
     const double* vmr_ref;     // (2, ngas+1, ntemp)
+    const double* eta_half;    // (2, nflav, ntemp): vmr_ref(key species 1) / vmr_ref(key species 2) of a flavor
     const int* flavor;         // (2, nflav) 1-based gas index, 0 = dry air
     const int* band_flavor;    // (2, nbnd) 0-based flavor
     const int* band_lims;      // (2, nbnd) 1-based

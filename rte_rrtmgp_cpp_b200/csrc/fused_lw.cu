@@ -126,7 +126,7 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
                 lev_top[j] = lev_bot;
             }
             V4<Real>* w = scr + (size_t)(k - 1) * 2 * T;
-            w[0] = tr; w[T] = su;
+            st_stream(w, tr); st_stream(w + T, su);
             const Real s = quad_sum<Real, LPC>(radn) * piw;
             if (lead)
             {
@@ -156,18 +156,20 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
             if (a.bnd_up) a.bnd_up[o + nlev_stride * band] = s;
         }
     }
-    // ---- up-sweep, surface -> top (F90:710-745): the parked {trans, source_up} come back LIFO in
-    // chunks of 4 layers (8 independent vector loads in flight per thread)
-    for (int k0 = nlay - 1; k0 >= 0; k0 -= 4)
+    // ---- up-sweep, surface -> top (F90:710-745): the parked {trans, source_up} come back LIFO through
+    // two register buffers of 4 layers; the loads of the next 4 layers are issued before the
+    // arithmetic of the current 4.
+    auto ld = [&](V4<Real> (&tr)[4], V4<Real> (&su)[4], int k0)
     {
-        V4<Real> tr[4], su[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u)
         {
-            const int k = max(k0 - u, 0);
-            const V4<Real>* w = scr + (size_t)k * 2 * T;
-            tr[u] = w[0]; su[u] = w[T];
+            const V4<Real>* w = scr + (size_t)max(k0 - u, 0) * 2 * T;
+            tr[u] = ld_stream(w); su[u] = ld_stream(w + T);
         }
+    };
+    auto sweep = [&](const V4<Real> (&tr)[4], const V4<Real> (&su)[4], int k0)
+    {
 #pragma unroll
         for (int u = 0; u < 4; ++u)
         {
@@ -181,6 +183,18 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
                 atomicAdd(a.flux_up + o, s);
                 if (a.bnd_up) a.bnd_up[o + nlev_stride * band] = s;
             }
+        }
+    };
+    {
+        V4<Real> trA[4], suA[4], trB[4], suB[4];
+        ld(trA, suA, nlay - 1);
+        for (int k0 = nlay - 1; k0 >= 0; k0 -= 8)
+        {
+            ld(trB, suB, k0 - 4);
+            sweep(trA, suA, k0);
+            if (k0 - 4 < 0) break;
+            ld(trA, suA, k0 - 8);
+            sweep(trB, suB, k0 - 4);
         }
     }
     release_slot(a.slot_busy, slot);

@@ -132,7 +132,7 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
             Ra[j] = Rdif + Tdif * td * Ra[j];
         }
         V4<Real>* w = scr + (size_t)k * 6 * T;
-        w[0] = v0; w[T] = v1; w[2 * T] = v2; w[3 * T] = v3; w[4 * T] = v4; w[5 * T] = v5;
+        st_stream(w, v0); st_stream(w + T, v1); st_stream(w + 2 * T, v2); st_stream(w + 3 * T, v3); st_stream(w + 4 * T, v4); st_stream(w + 5 * T, v5);
         const Real s = quad_sum<Real, LPC>(dir);
         o += lstep;
         if (lead)
@@ -145,6 +145,16 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     // ---- pass 2: adding of the stack BELOW each level, surface -> top (F90:1135-1245), and the fluxes
     // where the two stacks meet:  dn(j) = (Sa + Ra*Sb) / (1 - Ra*A),  up(j) = A*dn(j) + Sb.
     // `o` is at the surface level; scratch is read two layers ahead.
+    // Scratch comes back LIFO through two register buffers: the loads of layer k-1 are issued before
+    // the arithmetic of layer k, so a full layer step sits between a load and its first use.
+    auto ld6 = [&](V4<Real> (&d)[6], int k)
+    {
+        const V4<Real>* w = scr + (size_t)max(k, 0) * 6 * T;
+#pragma unroll
+        for (int m = 0; m < 6; ++m) d[m] = ld_stream(w + m * T);
+    };
+    V4<Real> bufA[6], bufB[6];
+    ld6(bufA, nlay - 1);
     Real alb[4], src[4];
     {
         const Real adir = a.alb_dir[band + (size_t)P.nbnd * cg];
@@ -164,41 +174,36 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
             if (a.bnd_up) { a.bnd_up[o + nlev_stride * band] = su; a.bnd_dn[o + nlev_stride * band] = sd + a.bnd_dir[o + nlev_stride * band]; }
         }
     }
+    auto step = [&](const V4<Real> (&in)[6])
+    {
+        const Real* rdif = &in[0].x; const Real* tdif = &in[1].x; const Real* sup = &in[2].x; const Real* sdn = &in[3].x;
+        const Real* ra = &in[4].x; const Real* sa = &in[5].x;
+        Real fdn[4], fup[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+        {
+            const Real td = tdif[j] * M<Real>::rcp((Real)1 - rdif[j] * alb[j]);
+            const Real nsrc = sup[j] + td * (src[j] + alb[j] * sdn[j]);
+            alb[j] = rdif[j] + tdif[j] * td * alb[j];
+            src[j] = nsrc;
+            fdn[j] = (sa[j] + ra[j] * src[j]) * M<Real>::rcp((Real)1 - ra[j] * alb[j]);
+            fup[j] = alb[j] * fdn[j] + src[j];
+        }
+        const Real su = quad_sum<Real, LPC>(fup), sd = quad_sum<Real, LPC>(fdn);
+        o -= lstep;
+        if (lead)
+        {
+            atomicAdd(a.flux_up + o, su); atomicAdd(a.flux_dn + o, sd);
+            if (a.bnd_up) { a.bnd_up[o + nlev_stride * band] = su; a.bnd_dn[o + nlev_stride * band] = sd + a.bnd_dir[o + nlev_stride * band]; }
+        }
+    };
     for (int k0 = nlay - 1; k0 >= 0; k0 -= 2)
     {
-        V4<Real> in[2][6];
-#pragma unroll
-        for (int u = 0; u < 2; ++u)
-        {
-            const V4<Real>* w = scr + (size_t)max(k0 - u, 0) * 6 * T;
-#pragma unroll
-            for (int m = 0; m < 6; ++m) in[u][m] = w[m * T];
-        }
-#pragma unroll
-        for (int u = 0; u < 2; ++u)
-        {
-            if (k0 - u < 0) break;
-            const Real* rdif = &in[u][0].x; const Real* tdif = &in[u][1].x; const Real* sup = &in[u][2].x; const Real* sdn = &in[u][3].x;
-            const Real* ra = &in[u][4].x; const Real* sa = &in[u][5].x;
-            Real fdn[4], fup[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-            {
-                const Real td = tdif[j] * M<Real>::rcp((Real)1 - rdif[j] * alb[j]);
-                const Real nsrc = sup[j] + td * (src[j] + alb[j] * sdn[j]);
-                alb[j] = rdif[j] + tdif[j] * td * alb[j];
-                src[j] = nsrc;
-                fdn[j] = (sa[j] + ra[j] * src[j]) * M<Real>::rcp((Real)1 - ra[j] * alb[j]);
-                fup[j] = alb[j] * fdn[j] + src[j];
-            }
-            const Real su = quad_sum<Real, LPC>(fup), sd = quad_sum<Real, LPC>(fdn);
-            o -= lstep;
-            if (lead)
-            {
-                atomicAdd(a.flux_up + o, su); atomicAdd(a.flux_dn + o, sd);
-                if (a.bnd_up) { a.bnd_up[o + nlev_stride * band] = su; a.bnd_dn[o + nlev_stride * band] = sd + a.bnd_dir[o + nlev_stride * band]; }
-            }
-        }
+        ld6(bufB, k0 - 1);
+        step(bufA);
+        if (k0 - 1 < 0) break;
+        ld6(bufA, k0 - 2);
+        step(bufB);
     }
     release_slot(a.slot_busy, slot);
 }

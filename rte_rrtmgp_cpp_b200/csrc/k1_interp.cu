@@ -142,14 +142,12 @@ interp_kernel(const DevPlan<Real> P, const VmrArgs vmr, int ncol, int c0, int nc
         for (int itemp = 0; itemp < 2; ++itemp)
         {
             const int jtt = jt + itemp;   // 1-based
-            const double v1 = P.vmr_ref[side + 2 * (ig1 + (size_t)(P.ngas + 1) * (jtt - 1))];
-            const double v2 = P.vmr_ref[side + 2 * (ig2 + (size_t)(P.ngas + 1) * (jtt - 1))];
-            const double ratio_eta_half = v1 / v2;
+            const double ratio_eta_half = P.eta_half[side + 2 * (f + (size_t)P.nflav * (jtt - 1))];
             cm[itemp] = cg1 + ratio_eta_half * cg2;
             const double eta = (cm[itemp] > 2.0 * DBL_MIN) ? cg1 / cm[itemp] : 0.5;
             const double loceta = eta * (double)(P.neta - 1);
             je[itemp] = min((int)loceta + 1, P.neta - 1);
-            const double feta = fmod(loceta, 1.0);
+            const double feta = loceta - trunc(loceta);      // == fmod(loceta, 1.0) exactly for loceta >= 0
             const double ftt = itemp == 0 ? (1.0 - ftemp) : ftemp;
             fm[itemp][0] = (1.0 - feta) * ftt;
             fm[itemp][1] = feta * ftt;

@@ -65,7 +65,7 @@ __device__ __forceinline__ RawState<Real> load_state(const TileState<Real>& st, 
     RawState<Real> r;
     const V4<Real>* sc = st.scal + icl * (size_t)(P.nscal >> 2) + B.scal_off[side];
     r.sc0 = sc[0];
-    r.sc1 = B.nminor[side] > 4 ? sc[1] : r.sc0;
+    r.sc1 = sc[B.nminor[side] > 4 ? 1 : 0];     // a second load, not a copy of sc0: a copy would wait on sc0 right here
     r.cell = st.cell[icl];
     r.fa = st.flvA[icl + tcl * f];
     r.fb = st.flvB[icl + tcl * f];
@@ -313,7 +313,7 @@ __device__ __forceinline__ void two_stream_ref(Real tau, Real w0, Real g, Real m
 __device__ __forceinline__ float omexp_over_x(float x, float e)
 {
     const float ser = fmaf(-0.5f * x, fmaf(-(1.f / 3.f) * x, fmaf(-0.25f, x, 1.f), 1.f), 1.f);
-    const float dir = __fdividef(1.f - e, fmaxf(x, 1e-30f));
+    const float dir = M<float>::div(1.f - e, fmaxf(x, 1e-30f));
     return x < 0.03f ? ser : dir;
 }
 
@@ -337,7 +337,7 @@ __device__ __forceinline__ void two_stream_f32(float tau, float w0, float g, flo
     const float k2 = fmaxf(2.f * (1.f - w0) * (2.f - 0.5f * w0 * (1.f + 3.f * g)), 0.f);   // (g1-g2)(g1+g2)
     const float k = M<float>::sqrt(k2);
     const float a = k * tau;
-    const float e1 = __expf(-a), e2 = e1 * e1;
+    const float e1 = M<float>::exp(-a), e2 = e1 * e1;
     const float ga = omexp_over_x(a, e1);
     const float om1 = a * ga;
     const float P = tau * ga * (1.f + e1);
@@ -345,8 +345,8 @@ __device__ __forceinline__ void two_stream_f32(float tau, float w0, float g, flo
     Rdif = gamma2 * P * rD;
     Tdif = 2.f * e1 * rD;
 
-    const float x = __fdividef(tau, mu0s);
-    Tnoscat = __expf(-x);
+    const float x = M<float>::div(tau, mu0s);
+    Tnoscat = M<float>::exp(-x);
     const float omT_true = x * omexp_over_x(x, Tnoscat);
     float mu = mu0s, T0 = Tnoscat, omT = omT_true;
     float kmu = k * mu, d = 1.f - kmu * kmu;
@@ -354,9 +354,9 @@ __device__ __forceinline__ void two_stream_f32(float tau, float w0, float g, flo
     if (fabsf(d) < band)
     {
         d = d >= 0.f ? band : -band;
-        mu = __fdividef(M<float>::sqrt(1.f - d), k);
-        const float xe = __fdividef(tau, mu);
-        T0 = __expf(-xe);
+        mu = M<float>::div(M<float>::sqrt(1.f - d), k);
+        const float xe = M<float>::div(tau, mu);
+        T0 = M<float>::exp(-xe);
         omT = xe * omexp_over_x(xe, T0);
     }
     const float gamma3 = (2.f - 3.f * mu * g) * .25f;
@@ -368,7 +368,7 @@ __device__ __forceinline__ void two_stream_f32(float tau, float w0, float g, flo
     const float k2mu = k2 * mu;
     const float NR = alpha2 * P + (gamma3 - mu * alpha2) * Q - k2mu * gamma3 * P;
     const float NT = T0 * (alpha1 * P + k2mu * gamma4 * P) + (gamma4 + mu * alpha1) * Qp;
-    const float f = __fdividef(w0 * rD, d);
+    const float f = M<float>::div(w0 * rD, d);
     Rdir = f * NR;
     Tdir = -f * NT;
     Rdir = fmaxf(0.f, fminf(Rdir, omT_true));
