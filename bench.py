@@ -44,6 +44,7 @@ def parse():
     ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
     ap.add_argument("--cloudy", action="store_true", help="all-sky: cloud optics LUT + delta scaling")
     ap.add_argument("--tile", type=int, default=0, help="columns per tile of the fused path (0 = auto)")
+    ap.add_argument("--chunk", type=int, default=0, help="columns per chunk of the host-buffer pipeline (0 = auto)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-cols-per-core", type=int, default=2048)
@@ -308,7 +309,7 @@ def run_b200(args):
         h_lw, h_sw = {}, {}
 
         def e2e_step():
-            api.solve_host(lw, sw, hcols, switch_cloud_optics=args.cloudy, out_lw=h_lw, out_sw=h_sw)
+            api.solve_host(lw, sw, hcols, switch_cloud_optics=args.cloudy, out_lw=h_lw, out_sw=h_sw, chunk_columns=args.chunk)
 
         e2e_step(); e2e_step(); barrier()
         d2h = sum(a.t.numel() * a.t.element_size() for o in (h_lw, h_sw) for a in o.values())

@@ -940,7 +940,7 @@ void fluxes_host(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, co
             {
                 const int cpb = FUSED_THREADS / (g->h.gw / 4);
                 const int wave = std::max(g->h.is_lw ? lw_blocks_per_wave<Real>(g->h.gw) : sw_blocks_per_wave<Real>(g->h.gw), 1);
-                chunk = std::max(chunk, g->tile_cols > 0 ? g->tile_cols : 8 * wave * cpb);
+                chunk = std::max(chunk, g->tile_cols > 0 ? g->tile_cols : 4 * wave * cpb);   // finer than a tile: shorter pipeline ramps
             }
     chunk = std::min(chunk, ncol);
     if (chunk_cols <= 0)

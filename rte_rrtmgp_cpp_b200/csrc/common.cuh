@@ -30,11 +30,12 @@ template<> __device__ __forceinline__ V4<double> ldg4<double>(const double* p)
     return V4<double>{a.x, a.y, b.x, b.y};
 }
 
-// Streaming (evict-first) vector access for the recurrence scratch strips: they are written once and
-// read once, so they should not displace the k-tables and the interpolation state from L2.
+// Vector access for the recurrence scratch strips.  -DRB_STREAM_HINT makes them streaming (evict-first):
+// measured neutral to slightly slower on B200 (the LIFO re-reads of the deepest layers do hit L2), so
+// plain accesses are the default.
 __device__ __forceinline__ void st_stream(V4<float>* p, const V4<float>& v)
 {
-#ifdef RB_NO_STREAM_HINT
+#ifndef RB_STREAM_HINT
     *p = v;
 #else
     __stcs(reinterpret_cast<float4*>(p), make_float4(v.x, v.y, v.z, v.w));
@@ -42,7 +43,7 @@ __device__ __forceinline__ void st_stream(V4<float>* p, const V4<float>& v)
 }
 __device__ __forceinline__ void st_stream(V4<double>* p, const V4<double>& v)
 {
-#ifdef RB_NO_STREAM_HINT
+#ifndef RB_STREAM_HINT
     *p = v;
 #else
     __stcs(reinterpret_cast<double2*>(p), make_double2(v.x, v.y));
@@ -51,7 +52,7 @@ __device__ __forceinline__ void st_stream(V4<double>* p, const V4<double>& v)
 }
 __device__ __forceinline__ V4<float> ld_stream(const V4<float>* p)
 {
-#ifdef RB_NO_STREAM_HINT
+#ifndef RB_STREAM_HINT
     return *p;
 #else
     const float4 v = __ldcs(reinterpret_cast<const float4*>(p));
@@ -60,7 +61,7 @@ __device__ __forceinline__ V4<float> ld_stream(const V4<float>* p)
 }
 __device__ __forceinline__ V4<double> ld_stream(const V4<double>* p)
 {
-#ifdef RB_NO_STREAM_HINT
+#ifndef RB_STREAM_HINT
     return *p;
 #else
     const double2 a = __ldcs(reinterpret_cast<const double2*>(p));
