@@ -47,6 +47,8 @@ def parse():
     ap.add_argument("--chunk", type=int, default=0, help="columns per chunk of the host-buffer pipeline (0 = auto)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-ref-cuda", action="store_true", help="skip timing the reference's own CUDA path (oracle/_ref/librefcuda_*.so)")
+    ap.add_argument("--ref-cuda-cols", type=int, default=65536)
     ap.add_argument("--cpu-cols-per-core", type=int, default=2048)
     return ap.parse_args()
 
@@ -357,6 +359,27 @@ def run_b200(args):
             traffic = json.load(f).get(f"{dom}_{args.dtype}")
     except Exception:
         pass
+    # ---- the reference's own CUDA implementation of the path on this GPU (secondary baseline):
+    # separate process (its memory pool, tuner file and any fault stay out of this one), after our timing
+    ref_cuda = None
+    if world == 1 and not args.no_ref_cuda and not args.cloudy:
+        try:
+            from oracle import refcuda
+            if refcuda.available(args.dtype):
+                torch.cuda.empty_cache()
+                r = subprocess.run([sys.executable, "-m", "oracle.refcuda", "--ncol", str(min(args.ref_cuda_cols, args.ncol)),
+                                    "--nlay", str(nlay), "--dtype", args.dtype, "--reps", "3"], cwd=ROOT,
+                                   capture_output=True, text=True, timeout=600)
+                for ln in r.stdout.splitlines():
+                    if ln.startswith("{"):
+                        ref_cuda = json.loads(ln)
+                if ref_cuda is None:
+                    ref_cuda = {"unavailable": (r.stderr or r.stdout).strip().splitlines()[-1][:200] if (r.stderr or r.stdout).strip() else "no output"}
+                else:
+                    ref_cuda["note"] = ("unmodified reference src_cuda + src_kernels_cuda built for sm_100a, driven like "
+                                        "Radiation_solver::solve_gpu; its fluxes are NOT the parity target (SURVEY 2.1 quirks)")
+        except Exception as ex:      # noqa: BLE001 - a baseline failure must not lose the measurement
+            ref_cuda = {"unavailable": str(ex)[:200]}
     whole = (ncol * (256 * b_lw + 224 * b_sw) * args.steps) / ((lw_ms.value + sw_ms.value) * 1e-3) / 1e9
     line = {
         "metric": "LW+SW column-gpts/s", "value": value, "unit": "column-gpts/s", "n_gpus": world,
@@ -378,7 +401,7 @@ def run_b200(args):
                      "lw_band_ms_total": lw_ms.value, "sw_band_ms_total": sw_ms.value,
                      "lw_plus_sw_effective_GBs": whole, "lw_plus_sw_frac": whole / peak,
                      "note": "effective bandwidth on the materialised-API byte model; the fused kernels move far fewer DRAM bytes"},
-        "cpu_baseline": cpu, "e2e": e2e,
+        "cpu_baseline": cpu, "e2e": e2e, "reference_cuda": ref_cuda,
     }
     print(json.dumps(line))
     if world > 1:
