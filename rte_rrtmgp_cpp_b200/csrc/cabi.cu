@@ -364,6 +364,44 @@ template<typename Real> size_t state_bytes(const HostPlan& h, int nc, int nlay)
          + 2 * pad256((tcl + nc) * sizeof(V2<Real>)) + 1024;
 }
 
+// Pin the k-major table (the bulk of the table bytes) in L2 for the band kernels of one fused call: an
+// access-policy window on the launching stream, persisting on hit.  The recurrence scratch streams tens
+// of GB through L2 per launch and would otherwise keep evicting table lines.  RB200_L2_PIN=0 disables.
+struct L2Pin
+{
+    cudaStream_t s; bool on = false;
+    L2Pin(cudaStream_t s_, const void* base, size_t bytes) : s(s_)
+    {
+        static const bool enabled = [] { const char* e = getenv("RB200_L2_PIN"); return !(e && e[0] == '0'); }();
+        static const size_t max_window = [] {
+            int dev = 0, persist = 0, window = 0;
+            if (cudaGetDevice(&dev) != cudaSuccess) return (size_t)0;
+            cudaDeviceGetAttribute(&persist, cudaDevAttrMaxPersistingL2CacheSize, dev);
+            cudaDeviceGetAttribute(&window, cudaDevAttrMaxAccessPolicyWindowSize, dev);
+            if (persist <= 0 || window <= 0) return (size_t)0;
+            const size_t set_aside = std::min<size_t>((size_t)persist, (size_t)32 << 20);
+            if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, set_aside) != cudaSuccess) { cudaGetLastError(); return (size_t)0; }
+            return std::min<size_t>((size_t)window, set_aside);
+        }();
+        if (!enabled || !max_window || !base || !bytes) return;
+        cudaStreamAttrValue v{};
+        v.accessPolicyWindow.base_ptr = const_cast<void*>(base);
+        v.accessPolicyWindow.num_bytes = std::min(bytes, max_window);
+        v.accessPolicyWindow.hitRatio = 1.0f;
+        v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        on = cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &v) == cudaSuccess;
+        if (!on) cudaGetLastError();
+    }
+    ~L2Pin()
+    {
+        if (!on) return;
+        cudaStreamAttrValue v{};
+        v.accessPolicyWindow.num_bytes = 0;
+        cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &v);
+    }
+};
+
 void check_dims(int ncol, int nlay)
 {
     if (ncol < 1 || nlay < 1) throw ArgError("ncol and nlay must be positive");
@@ -847,6 +885,7 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
         if (sw) CK(cudaMemsetAsync(a.flux_dir, 0, ncv * sizeof(Real), s));
     }
 
+    L2Pin pin(s, g->kmajor.p, g->kmajor.bytes);
     for (int c0 = 0; c0 < ncol; c0 += tile)
     {
         const int nc = std::min(tile, ncol - c0);

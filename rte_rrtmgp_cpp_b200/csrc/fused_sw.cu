@@ -26,8 +26,11 @@ namespace rb200 {
 #ifndef RB_SW_MINB
 #define RB_SW_MINB 5
 #endif
-// resident CTAs per SM requested from ptxas for the fp32 instantiations (fp64 needs the registers)
-template<typename Real> struct SWMinBlocks { static constexpr int v = sizeof(Real) == 4 ? RB_SW_MINB : 1; };
+#ifndef RB_SW_MINB64
+#define RB_SW_MINB64 3
+#endif
+// resident CTAs per SM requested from ptxas: 5 (96 registers) for fp32, 3 (168 registers) for fp64 — measured best
+template<typename Real> struct SWMinBlocks { static constexpr int v = sizeof(Real) == 4 ? RB_SW_MINB : RB_SW_MINB64; };
 
 template<typename Real, int LPC, bool CLOUD, int NE>
 __global__ void __launch_bounds__(FUSED_THREADS, SWMinBlocks<Real>::v)
