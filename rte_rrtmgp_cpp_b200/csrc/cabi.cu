@@ -98,7 +98,7 @@ struct rrtmgp_b200_gas_optics
     int dtype = 0, device = 0;
     bool host_only = false;
     HostPlan h;
-    DevBuf kmajor, pfrac, krayl, kminor[2], totplnk, solar, temp_ref, vmr_ref, eta_half, flavor, band_flavor, band_lims, minor_slots[2];
+    DevBuf kmajor, pfrac, krayl, kminor[2], totplnk, solar, temp_ref, vmr_ref, eta_half, flavor, band_flavor, band_lims, minor_slots[2], slot_uid[2];
     DevPlan<float> pf{};
     DevPlan<double> pd{};
     std::vector<BandArgs> bands;
@@ -159,22 +159,26 @@ static void fill_devplan(rrtmgp_b200_gas_optics* g, DevPlan<Real>& P)
     P.flavor = (const int*)g->flavor.p; P.band_flavor = (const int*)g->band_flavor.p; P.band_lims = (const int*)g->band_lims.p;
     for (int sd = 0; sd < 2; ++sd)
     {
-        std::vector<int> slots((size_t)4 * h.nscal, 0);
-        for (int k = 0; k < h.nscal; ++k)
+        std::vector<int> slots((size_t)4 * h.nuniq, 0);
+        for (int k = 0; k < h.nuniq; ++k)
         {
-            const int m = k < (int)h.minor[sd].slot_desc.size() ? h.minor[sd].slot_desc[k] : -1;
             slots[4 * k] = -1;
-            if (m >= 0)
+            if (k < (int)h.minor[sd].uniq_rep.size())
             {
-                const MinorDesc& dd = h.minor[sd].desc[m];
+                const MinorDesc& dd = h.minor[sd].desc[h.minor[sd].uniq_rep[k]];
                 slots[4 * k] = dd.idx_minor; slots[4 * k + 1] = dd.idx_scaling;
                 slots[4 * k + 2] = (dd.scales_with_density ? 1 : 0) | (dd.scale_by_complement ? 2 : 0);
             }
         }
+        std::vector<int> suid((size_t)h.nscal, h.nuniq);       // nuniq = the zero entry
+        for (size_t k = 0; k < h.minor[sd].slot_desc.size(); ++k)
+            if (h.minor[sd].slot_desc[k] >= 0) suid[k] = h.minor[sd].uid[h.minor[sd].slot_desc[k]];
+        g->slot_uid[sd].upload(suid);
+        P.slot_uid[sd] = (const int4*)g->slot_uid[sd].p;
         g->minor_slots[sd].upload(slots);
         P.minor_slots[sd] = (const int4*)g->minor_slots[sd].p;
     }
-    P.nscal = h.nscal;
+    P.nscal = h.nscal; P.nuniq = h.nuniq;
     P.press_ref_log0 = h.press_ref_log[0]; P.press_ref_log_delta = h.press_ref_log_delta;
     P.press_ref_trop_log = h.press_ref_trop_log; P.temp_ref_min = h.temp_ref_min; P.temp_ref_delta = h.temp_ref_delta;
     P.planck_tmin = (Real)h.temp_ref_min; P.planck_delta = (Real)h.totplnk_delta;

@@ -102,7 +102,7 @@ sw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
                 Cell<Real> ce;
                 decode_cell(cur.cell, cur.fa, cur.fb, ce);
                 Real tau[4];
-                gas_tau<G>(P, B, ce, kmaj, q4, cur.sc0, cur.sc1, st.scal + icl * (size_t)(P.nscal >> 2), tau);
+                gas_tau<G>(P, B, ce, kmaj, q4, cur.sc0, cur.sc1, st.scal + icl, tcl, tau);
                 Real ray[4] = {0, 0, 0, 0};
                 if (kray)
                 {
@@ -330,7 +330,7 @@ lw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
                 Real tl[4];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) { tl[j] = ce.cm0 * s0[j] + ce.cm1 * s1[j]; pf[j] = p0[j] + p1[j]; }
-                add_minor_tau<G>(P, B, ce, q4, cur.sc0, cur.sc1, st.scal + icl * (size_t)(P.nscal >> 2), tl);
+                add_minor_tau<G>(P, B, ce, q4, cur.sc0, cur.sc1, st.scal + icl, tcl, tl);
                 if (CLOUD)
                 {
                     const Real ct = a.cld_tau[icl + tcl * band];

@@ -8,6 +8,7 @@ namespace rb200 {
 
 constexpr int MAX_GAS = 32;
 constexpr int MAX_MINOR_DEV = 16;
+constexpr int MAX_UNIQ = 63;       // distinct minor-gas scalings per side the prologue kernel keeps per thread
 
 // ---- 4-wide vectors: one 16-byte (fp32) or 32-byte (fp64) aligned access -------------------
 template<typename Real> struct V4;
@@ -125,8 +126,9 @@ template<typename Real> struct DevPlan
     const int* flavor;         // (2, nflav) 1-based gas index, 0 = dry air
     const int* band_flavor;    // (2, nbnd) 0-based flavor
     const int* band_lims;      // (2, nbnd) 1-based
-    const int4* minor_slots[2]; // per side, nscal entries {idx_minor (-1 = padding), idx_scaling, flags, 0}
-    int nscal;                 // slots of the per-(column, layer) minor scaling vector (multiple of 4)
+    const int4* minor_slots[2]; // per side, nuniq entries {idx_minor (-1 = unused), idx_scaling, flags, 0}: the DISTINCT scalings
+    const int4* slot_uid[2];    // per side, nscal/4 groups: distinct-scaling number of each slot (nuniq = padding, value 0)
+    int nscal, nuniq;          // slots of the band-blocked scaling vector (multiple of 4); distinct scalings
     double press_ref_log0, press_ref_log_delta, press_ref_trop_log;
     double temp_ref_min, temp_ref_delta;
     Real planck_tmin, planck_delta;
@@ -151,8 +153,8 @@ template<typename Real> struct TileState
     int nc, nlay;            // columns in this tile, layers
     V4<Real>* cell;          // {fpress, col_gas(h2o) + col_dry, 0, bits}
                              //   bits = jtemp | jpress<<8 | tropo<<16
-    V4<Real>* scal;          // [nscal/4] per (c,l): minor-gas scaling of every contributor of the layer's
-                             //   side (col_gas * density * scaling-gas factor, F90:453-475), band-blocked
+    V4<Real>* scal;          // [nscal/4][l][c]: minor-gas scalings of the contributors of the layer's side
+                             //   (col_gas * density * scaling-gas factor, F90:453-475), band-blocked groups of 4
     V4<Real>* flvA;          // [f]: {col_mix0, col_mix1, fminor(1,1), fminor(2,1)}
     V4<Real>* flvB;          // [f]: {fminor(1,2), fminor(2,2), rows(itemp 1), rows(itemp 2)}
                              //   rows = major row | minor row << 20 (row = offset / row stride)
@@ -169,7 +171,7 @@ struct BandArgs
     int band, gpt0, ngb;     // 0-based band, first g-point (0-based), g-points in band
     int nminor[2];
     int first_minor[2];      // device block index of the band's first contributor (blocks are consecutive)
-    int scal_off[2];         // first V4 of the band's contributors in TileState::scal
+    int scal_off[2];         // first group (V4 plane) of the band's contributors in TileState::scal
 };
 
 }  // namespace rb200

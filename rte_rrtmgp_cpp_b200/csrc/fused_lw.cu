@@ -97,7 +97,7 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
             interp_major_pair<G>(kmaj, P, ce, s0, s1, p0, p1);
 #pragma unroll
             for (int j = 0; j < 4; ++j) { tau[j] = ce.cm0 * s0[j] + ce.cm1 * s1[j]; pf[j] = p0[j] + p1[j]; }
-            add_minor_tau<G>(P, B, ce, q4, cur.sc0, cur.sc1, st.scal + icl * (size_t)(P.nscal >> 2), tau);
+            add_minor_tau<G>(P, B, ce, q4, cur.sc0, cur.sc1, st.scal + icl, tcl, tau);
             if (CLOUD)
             {
                 const Real ct = a.cld_tau[icl + tcl * band];

@@ -105,7 +105,7 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
         Cell<Real> ce;
         decode_cell(cur.cell, cur.fa, cur.fb, ce);
         Real tau[4];
-        gas_tau<G>(P, B, ce, kmaj, q4, cur.sc0, cur.sc1, st.scal + icl * (size_t)(P.nscal >> 2), tau);
+        gas_tau<G>(P, B, ce, kmaj, q4, cur.sc0, cur.sc1, st.scal + icl, tcl, tau);
         Real ray[4] = {0, 0, 0, 0};
         if (kray)
         {

@@ -41,10 +41,10 @@ gas_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const
         Cell<Real> ce;
         decode_cell(cell, st.flvA[icl + ncl * f], st.flvB[icl + ncl * f], ce);
         Real tau[4], s0[4], s1[4];
-        const V4<Real>* sc = st.scal + icl * (size_t)(P.nscal >> 2);
-        const V4<Real> sc0 = sc[B.scal_off[ce.side]];
-        const V4<Real> sc1 = B.nminor[ce.side] > 4 ? sc[B.scal_off[ce.side] + 1] : sc0;
-        gas_tau<G>(P, B, ce, kmaj, q4, sc0, sc1, sc, tau);
+        V4<Real> sc0, sc1;
+        load_scal4(st.scal + icl, ncl, B, ce.side, 0, sc0);
+        load_scal4(st.scal + icl, ncl, B, ce.side, 4, sc1);
+        gas_tau<G>(P, B, ce, kmaj, q4, sc0, sc1, st.scal + icl, ncl, tau);
         if (lw)
         {
             Real pf[4];

@@ -89,32 +89,35 @@ interp_kernel(const DevPlan<Real> P, const VmrArgs vmr, int ncol, int c0, int nc
         const double vmr_fact = 1.0 / cd;
         const double dry_fact = 1.0 / (1.0 + cgas(P.idx_h2o) * vmr_fact);
         const double dens = 0.01 * pr / t;
+        // each DISTINCT scaling once (many contributors share one: same gas, scaling gas and flags) ...
         const int4* slots = P.minor_slots[side];
-        Real* out = reinterpret_cast<Real*>(st.scal) + it * (size_t)P.nscal;
-        for (int p4 = 0; p4 < P.nscal; p4 += 4)
+        Real uval[MAX_UNIQ + 1];
+        for (int u = 0; u < P.nuniq; ++u)
         {
-            Real v[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
+            const int4 dsc = slots[u];
+            double scaling = 0.0;
+            if (dsc.x >= 0)
             {
-                const int4 dsc = slots[p4 + u];
-                double scaling = 0.0;
-                if (dsc.x >= 0)
+                scaling = cgas(dsc.x);
+                if (dsc.z & 1)
                 {
-                    scaling = cgas(dsc.x);
-                    if (dsc.z & 1)
+                    scaling = scaling * dens;
+                    if (dsc.y > 0)
                     {
-                        scaling = scaling * dens;
-                        if (dsc.y > 0)
-                        {
-                            const double x = cgas(dsc.y) * vmr_fact * dry_fact;
-                            scaling = scaling * ((dsc.z & 2) ? (1.0 - x) : x);
-                        }
+                        const double x = cgas(dsc.y) * vmr_fact * dry_fact;
+                        scaling = scaling * ((dsc.z & 2) ? (1.0 - x) : x);
                     }
                 }
-                v[u] = (Real)scaling;
             }
-            *reinterpret_cast<V4<Real>*>(out + p4) = V4<Real>{v[0], v[1], v[2], v[3]};
+            uval[u] = (Real)scaling;
+        }
+        uval[P.nuniq] = (Real)0;
+        // ... then scattered to the band-blocked groups of 4 the band kernels read as one vector
+        const int4* suid = P.slot_uid[side];
+        for (int g4 = 0; g4 < (P.nscal >> 2); ++g4)
+        {
+            const int4 id = suid[g4];
+            st.scal[(size_t)g4 * tcl + it] = V4<Real>{uval[id.x], uval[id.y], uval[id.z], uval[id.w]};
         }
         if (st.pl_lay && tlev)
         {

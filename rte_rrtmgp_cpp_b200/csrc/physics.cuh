@@ -55,6 +55,14 @@ __device__ __forceinline__ int layer_side(const unsigned* __restrict__ tm, int l
     return ((__ldg(tm + (l >> 5)) >> (l & 31)) & 1u) ? 0 : 1;
 }
 
+// scalings of contributors m0..m0+3 of the band on this side: one vector from the group's plane
+// (planes are [group][l][c], so a warp's columns read one contiguous 128-byte line)
+template<typename Real>
+__device__ __forceinline__ void load_scal4(const V4<Real>* __restrict__ scal_icl, size_t tcl, const BandArgs& B, int side, int m0, V4<Real>& out)
+{
+    out = scal_icl[(size_t)(B.scal_off[side] + (m0 >> 2)) * tcl];
+}
+
 template<typename Real>
 __device__ __forceinline__ RawState<Real> load_state(const TileState<Real>& st, const DevPlan<Real>& P, const BandArgs& B,
                                                     const unsigned* tm, int flav0, int flav1, int c, int l, size_t tcl)
@@ -63,9 +71,8 @@ __device__ __forceinline__ RawState<Real> load_state(const TileState<Real>& st, 
     const int side = layer_side(tm, l);
     const int f = side == 0 ? flav0 : flav1;
     RawState<Real> r;
-    const V4<Real>* sc = st.scal + icl * (size_t)(P.nscal >> 2) + B.scal_off[side];
-    r.sc0 = sc[0];
-    r.sc1 = sc[B.nminor[side] > 4 ? 1 : 0];     // a second load, not a copy of sc0: a copy would wait on sc0 right here
+    load_scal4(st.scal + icl, tcl, B, side, 0, r.sc0);
+    load_scal4(st.scal + icl, tcl, B, side, B.nminor[side] > 4 ? 4 : 0, r.sc1);   // a second load, never a copy of sc0
     r.cell = st.cell[icl];
     r.fa = st.flvA[icl + tcl * f];
     r.fb = st.flvB[icl + tcl * f];
@@ -125,11 +132,11 @@ __device__ __forceinline__ void interp_minor(const Real* __restrict__ tab, const
 
 // minor-gas part of compute_tau_absorption (F90:404-502) for the layer's side, added onto tau.
 // The band's contributors are consecutive table blocks and consecutive entries of the scaling
-// vector the prologue kernel prepared; `pre0/pre1` hold its first 8 entries (fetched a layer ahead).
+// scalings the prologue kernel prepared; `pre0/pre1` hold those of the first 8 contributors (fetched a layer ahead).
 template<typename G, typename Real>
 __device__ __forceinline__ void add_minor_tau(const DevPlan<Real>& P, const BandArgs& B, const Cell<Real>& c, int q4,
                                               const V4<Real>& pre0, const V4<Real>& pre1,
-                                              const V4<Real>* __restrict__ scal_cl, Real (&tau)[4])
+                                              const V4<Real>* __restrict__ scal_icl, size_t tcl, Real (&tau)[4])
 {
     const int side = c.side;
     const int nm = B.nminor[side];
@@ -137,7 +144,8 @@ __device__ __forceinline__ void add_minor_tau(const DevPlan<Real>& P, const Band
     const Real* km = P.kminor[side] + mstride * B.first_minor[side] + q4;
     for (int m0 = 0; m0 < nm; m0 += 4)
     {
-        V4<Real> sc = m0 == 0 ? pre0 : (m0 == 4 ? pre1 : scal_cl[B.scal_off[side] + (m0 >> 2)]);
+        V4<Real> sc;
+        if (m0 == 0) sc = pre0; else if (m0 == 4) sc = pre1; else load_scal4(scal_icl, tcl, B, side, m0, sc);
         const Real* scp = &sc.x;
 #pragma unroll
         for (int u = 0; u < 4; ++u)
@@ -159,13 +167,13 @@ template<typename G, typename Real>
 __device__ __forceinline__ void gas_tau(const DevPlan<Real>& P, const BandArgs& B, const Cell<Real>& c,
                                         const Real* __restrict__ kmaj_quad, int q4,
                                         const V4<Real>& pre0, const V4<Real>& pre1,
-                                        const V4<Real>* __restrict__ scal_cl, Real (&tau)[4])
+                                        const V4<Real>* __restrict__ scal_icl, size_t tcl, Real (&tau)[4])
 {
     Real s0[4], s1[4];
     interp_major<G>(kmaj_quad, P, c, s0, s1);
 #pragma unroll
     for (int j = 0; j < 4; ++j) tau[j] = c.cm0 * s0[j] + c.cm1 * s1[j];
-    add_minor_tau<G>(P, B, c, q4, pre0, pre1, scal_cl, tau);
+    add_minor_tau<G>(P, B, c, q4, pre0, pre1, scal_icl, tcl, tau);
 }
 
 // interpolate1D (F90:715-734) for one band

@@ -51,8 +51,12 @@ struct MinorSide
     std::vector<double> kminor_ref;          // reduced, reference layout (ntemp, neta, nk)
     int nk = 0;
     std::vector<double> table;               // device layout [m][it][ie][gw]
-    std::vector<int> scal_off;               // per band: first slot in the per-(column,layer) scaling vector
-    std::vector<int> slot_desc;              // per slot: index into desc, -1 = padding (slots per band padded to 4)
+    // many contributors share one scaling (same gas, same scaling gas, same flags; e.g. the h2o continua of
+    // every band): the prologue kernel computes each distinct one once per (column, layer)
+    std::vector<int> uid;                    // per contributor: its distinct-scaling number
+    std::vector<int> uniq_rep;               // per distinct scaling: a contributor that has it
+    std::vector<int> scal_off;               // per band: first slot of the band's contributors (slots per band padded to 4)
+    std::vector<int> slot_desc;              // per slot: index into desc, -1 = padding
 };
 
 struct HostPlan
@@ -77,7 +81,8 @@ struct HostPlan
     std::vector<double> solar_source;            // (ngpt)
     double tsi = 0;
     MinorSide minor[2];                          // 0 = lower (tropo true), 1 = upper
-    int nscal = 0;                               // length of the scaling vector (max over sides, multiple of 4)
+    int nscal = 0;                               // slots of the band-blocked scaling vector (max over sides, multiple of 4)
+    int nuniq = 0;                               // distinct scalings per (column, layer): max over the two sides, >= 1
 };
 
 inline HostPlan build_host_plan(const rrtmgp_b200_kdist_file& kd, int n_avail,
@@ -323,6 +328,22 @@ inline HostPlan build_host_plan(const rrtmgp_b200_kdist_file& kd, int n_avail,
             for (int b = 0; b < nbnd; ++b)
                 for (int m : ms.by_band[b]) ms.desc[m].contributor = pos++;
         }
+        ms.uid.assign(ms.n, 0);
+        for (int m = 0; m < ms.n; ++m)
+        {
+            const MinorDesc& d = ms.desc[m];
+            int u = -1;
+            for (size_t k = 0; k < ms.uniq_rep.size() && u < 0; ++k)
+            {
+                const MinorDesc& e = ms.desc[ms.uniq_rep[k]];
+                if (e.idx_minor == d.idx_minor && e.idx_scaling == d.idx_scaling && e.scales_with_density == d.scales_with_density &&
+                    e.scale_by_complement == d.scale_by_complement) u = (int)k;
+            }
+            if (u < 0) { u = (int)ms.uniq_rep.size(); ms.uniq_rep.push_back(m); }
+            ms.uid[m] = u;
+        }
+        if (ms.uniq_rep.size() > 63) throw ArgError("k-distribution: more than 63 distinct minor-gas scalings on one side (unsupported)");
+        p.nuniq = std::max<int>(p.nuniq, std::max<int>((int)ms.uniq_rep.size(), 1));
         ms.scal_off.assign(nbnd, 0);
         for (int b = 0; b < nbnd; ++b)
         {
