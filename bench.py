@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--nlay", type=int, default=NLAY_DEFAULT)
     ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
     ap.add_argument("--cloudy", action="store_true", help="all-sky: cloud optics LUT + delta scaling")
+    ap.add_argument("--reduced", action="store_true", help="reduced g-point sets LW 128 / SW 112 (BASELINE config 5)")
     ap.add_argument("--tile", type=int, default=0, help="columns per tile of the fused path (0 = auto)")
     ap.add_argument("--chunk", type=int, default=0, help="columns per chunk of the host-buffer pipeline (0 = auto)")
     ap.add_argument("--no-e2e", action="store_true")
@@ -228,7 +229,12 @@ def run_b200(args):
     nlay, nlev = args.nlay, args.nlay + 1
     base = rce_atmosphere(min(NBASE, ncol), nlay, cloudy=args.cloudy)
     cols = tile_columns(api.DeviceColumns(base, dtype), ncol, shift=37 * rank)
-    kd_lw, kd_sw = synthetic_kdist("lw"), synthetic_kdist("sw")
+    if args.reduced:
+        from rte_rrtmgp_cpp_b200.kdist import REDUCED_LW_128, REDUCED_SW_112
+        kd_lw, kd_sw = synthetic_kdist("lw", REDUCED_LW_128), synthetic_kdist("sw", REDUCED_SW_112)
+    else:
+        kd_lw, kd_sw = synthetic_kdist("lw"), synthetic_kdist("sw")
+    g_lw, g_sw = kd_lw.ngpt, kd_sw.ngpt
     lw = api.Radiation_solver_longwave(kd_lw, GASES, synthetic_cloud_lut("lw") if args.cloudy else None, dtype)
     sw = api.Radiation_solver_shortwave(kd_sw, GASES, synthetic_cloud_lut("sw") if args.cloudy else None, dtype)
     if args.tile:
@@ -362,7 +368,7 @@ def run_b200(args):
     # ---- the reference's own CUDA implementation of the path on this GPU (secondary baseline):
     # separate process (its memory pool, tuner file and any fault stay out of this one), after our timing
     ref_cuda = None
-    if world == 1 and not args.no_ref_cuda and not args.cloudy:
+    if world == 1 and not args.no_ref_cuda and not args.cloudy and not args.reduced:
         try:
             from oracle import refcuda
             if refcuda.available(args.dtype):
@@ -380,17 +386,17 @@ def run_b200(args):
                                         "Radiation_solver::solve_gpu; its fluxes are NOT the parity target (SURVEY 2.1 quirks)")
         except Exception as ex:      # noqa: BLE001 - a baseline failure must not lose the measurement
             ref_cuda = {"unavailable": str(ex)[:200]}
-    whole = (ncol * (256 * b_lw + 224 * b_sw) * args.steps) / ((lw_ms.value + sw_ms.value) * 1e-3) / 1e9
+    whole = (ncol * (g_lw * b_lw + g_sw * b_sw) * args.steps) / ((lw_ms.value + sw_ms.value) * 1e-3) / 1e9
     line = {
         "metric": "LW+SW column-gpts/s", "value": value, "unit": "column-gpts/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": args.dtype,
         "data": "synthetic (seeded S-RCE columns, synthetic k-distribution tables of the g256/g224 shape: "
                 "the rrtmgp-gas-*.nc files are absent from the reference mount)",
-        "config": {"workload": f"{args.ncol} columns x {nlay} layers, LW 256 + SW 224 g-points, "
+        "config": {"workload": f"{args.ncol} columns x {nlay} layers, LW {g_lw} + SW {g_sw} g-points, "
                                f"{'all-sky (cloud LUT + delta scaling)' if args.cloudy else 'clear-sky'}, fused path, "
                                f"column-sharded over {world} GPU(s) + NCCL flux gather to rank 0",
-                   "ncol": args.ncol, "nlay": nlay, "ngpt_lw": 256, "ngpt_sw": 224,
+                   "ncol": args.ncol, "nlay": nlay, "ngpt_lw": g_lw, "ngpt_sw": g_sw,
                    "distinct_columns": min(NBASE, ncol), "l2_policy": "inputs and scratch larger than L2 (GBs per step)",
                    "tile_columns": args.tile or "auto (one resident wave)"},
         "clocks": clocks, "gpu_launches": int(launches),

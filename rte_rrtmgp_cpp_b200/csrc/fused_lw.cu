@@ -29,12 +29,12 @@ namespace rb200 {
 // resident CTAs per SM requested from ptxas: 5 (96 registers) for fp32, 3 (168 registers) for fp64 — measured best
 template<typename Real> struct LWMinBlocks { static constexpr int v = sizeof(Real) == 4 ? RB_LW_MINB : RB_LW_MINB64; };
 
-template<typename Real, int LPC, bool CLOUD, int NE>
+template<typename Real, int LPC, int GWT, bool CLOUD, int NE>
 __global__ void __launch_bounds__(FUSED_THREADS, LWMinBlocks<Real>::v)
 lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const TileState<Real> st,
                const FusedArgs<Real> a)
 {
-    using G = Geo<4 * LPC, NE, true>;
+    using G = Geo<GWT, NE, true>;      // table rows are GWT wide; LPC lanes cover this band's (<= 4*LPC) g-points
     constexpr int CPB = FUSED_THREADS / LPC;
     constexpr int T = FUSED_THREADS;
     const int tid = threadIdx.x;
@@ -212,13 +212,17 @@ template<typename Real>
 void launch_lw_band(const DevPlan<Real>& P, const BandArgs& B, const TileState<Real>& st,
                     const FusedArgs<Real>& a, cudaStream_t s)
 {
-    const int lpc = P.gw / 4, cpb = FUSED_THREADS / lpc;
+    // lanes per column follow the BAND's width (a 16-wide table layout still runs its <= 8-g-point bands on
+    // two lanes: the reduced LW set mixes 6..12 g-points per band)
+    const int lpc = (P.gw == 16 && B.ngb <= 8) ? 2 : P.gw / 4, cpb = FUSED_THREADS / lpc;
     const unsigned grid = (unsigned)((a.nc + cpb - 1) / cpb);
     const bool cloud = a.cld_tau != nullptr;
-#define RB_LAUNCH(LPC_, CL_, NE_) lw_band_kernel<Real, LPC_, CL_, NE_><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, a)
-#define RB_NE(LPC_, CL_) { if (P.neta == 9) RB_LAUNCH(LPC_, CL_, 9); else RB_LAUNCH(LPC_, CL_, 0); }
-    if (lpc == 4) { if (cloud) RB_NE(4, true) else RB_NE(4, false) }
-    else { if (cloud) RB_NE(2, true) else RB_NE(2, false) }
+#define RB_LAUNCH(LPC_, GW_, CL_, NE_) lw_band_kernel<Real, LPC_, GW_, CL_, NE_><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, a)
+#define RB_NE(LPC_, GW_, CL_) { if (P.neta == 9) RB_LAUNCH(LPC_, GW_, CL_, 9); else RB_LAUNCH(LPC_, GW_, CL_, 0); }
+#define RB_CL(LPC_, GW_) { if (cloud) RB_NE(LPC_, GW_, true) else RB_NE(LPC_, GW_, false) }
+    if (P.gw == 16) { if (lpc == 4) RB_CL(4, 16) else RB_CL(2, 16) }
+    else RB_CL(2, 8)
+#undef RB_CL
 #undef RB_NE
 #undef RB_LAUNCH
     count_launch();
@@ -234,8 +238,8 @@ template<typename Real> int lw_blocks_per_wave(int gw)
     int dev = 0, sms = 0, occ = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (gw == 16) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, lw_band_kernel<Real, 4, false, 9>, FUSED_THREADS, 0);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, lw_band_kernel<Real, 2, false, 9>, FUSED_THREADS, 0);
+    if (gw == 16) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, lw_band_kernel<Real, 4, 16, false, 9>, FUSED_THREADS, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, lw_band_kernel<Real, 2, 8, false, 9>, FUSED_THREADS, 0);
     return sms * occ;
 }
 template int lw_blocks_per_wave<float>(int);
