@@ -233,7 +233,7 @@ typedef struct rrtmgp_b200_columns
     const rrtmgp_b200_cloud_optics* cloud;
     int delta_cloud;               /* --delta-cloud, default on in the reference (SW only) */
     const void* d_lwp; const void* d_iwp; const void* d_rel; const void* d_dei; /* (ncol,nlay) */
-    int n_gauss_angles;            /* LW, 1..4 (0 -> 1) */
+    int n_gauss_angles;            /* LW, 1..4 (0 -> 1): Gauss-Jacobi-5 angles of src/Rte_lw.cpp:139-151 */
 } rrtmgp_b200_columns;
 
 typedef struct rrtmgp_b200_fluxes

@@ -557,7 +557,7 @@ class _Radiation_solver:
             c.cloud = self.cloud.h
             c.delta_cloud = int(switch_delta_cloud)
             c.d_lwp, c.d_iwp, c.d_rel, c.d_dei = cols.lwp.ptr, cols.iwp.ptr, cols.rel.ptr, cols.dei.ptr
-        c.n_gauss_angles = 1
+        c.n_gauss_angles = int(getattr(self, "n_gauss_angles", 1))
         c._keep = concs
         return c, f
 

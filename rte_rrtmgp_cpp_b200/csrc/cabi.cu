@@ -797,7 +797,8 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
     if (!sw && (!cols->d_tlev || !cols->d_tsfc || !cols->d_sfc_emis)) throw ArgError("lw_fluxes: tlev, tsfc and sfc_emis are required");
     if (sw && (!cols->d_mu0 || !cols->d_sfc_alb_dir || !cols->d_sfc_alb_dif)) throw ArgError("sw_fluxes: mu0 and surface albedos are required");
     if (nlay > 32 * TMASK_WORDS) throw ArgError("fused fluxes: at most 256 layers (use the stage calls for taller columns)");
-    if (!sw && cols->n_gauss_angles > 1) throw ArgError("lw_fluxes: the fused path supports one Gauss angle; use lw_solver_noscat for 2..4");
+    const int nang = sw ? 1 : std::max(cols->n_gauss_angles, 1);
+    if (nang > 4) throw ArgError("lw_fluxes: n_gauss_angles must be 1..4");   // src/Rte_lw.cpp:139-151
     const bool cloud = cols->cloud != nullptr;
     if (cloud)
     {
@@ -819,7 +820,7 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
         top_at_1 = p2[0] < p2[1];
     }
 
-    const bool colres = g->colres < 0 ? g_colres : g->colres != 0;
+    const bool colres = (g->colres < 0 ? g_colres : g->colres != 0) && (sw || cols->n_gauss_angles <= 1);   // column-resident LW: one angle
     if (colres && colres_smem_bytes<Real>(nlay, h.gw, sw) > 227 * 1024)
         throw ArgError("fused fluxes: column too tall for the shared-memory resident path");
     const int cpb = FUSED_THREADS / (h.gw / 4);
@@ -905,16 +906,24 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
         }
         if (g_prof.on) { cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, s)); g_prof.ev[sw].push_back(e); }
         if (colres) launch_cols<Real>(sw, dplan<Real>(g), (const BandArgs*)g->bands_dev.p, st, a, s);
+        else if (sw)
+            for (int b = 0; b < h.nbnd; ++b) launch_sw_band<Real>(dplan<Real>(g), g->bands[b], st, a, s);
         else
-            for (int b = 0; b < h.nbnd; ++b)
+            // Gauss-Jacobi-5 quadrature (src/Rte_lw.cpp:139-151): one pass of the band kernels per angle, fluxes
+            // accumulate (the reference's GPU path has a single angle; its CPU path sums angles the same way)
+            for (int ia = 0; ia < nang; ++ia)
             {
-                if (sw) launch_sw_band<Real>(dplan<Real>(g), g->bands[b], st, a, s);
-                else launch_lw_band<Real>(dplan<Real>(g), g->bands[b], st, a, s);
+                static const double gauss_Ds[4][4] = {{1. / 0.6096748751, 0., 0., 0.}, {1. / 0.2509907356, 1. / 0.7908473988, 0., 0.},
+                    {1. / 0.1024922169, 1. / 0.4417960320, 1. / 0.8633751621, 0.}, {1. / 0.0454586727, 1. / 0.2322334416, 1. / 0.5740198775, 1. / 0.903077597}};
+                static const double gauss_wts[4][4] = {{1., 0., 0., 0.}, {0.2300253764, 0.7699746236, 0., 0.},
+                    {0.0437820218, 0.3875796738, 0.5686383044, 0.}, {0.0092068785, 0.1285704278, 0.4323381850, 0.4298845087}};
+                a.secant = (Real)gauss_Ds[nang - 1][ia]; a.weight = (Real)gauss_wts[nang - 1][ia]; a.bnd_add = ia > 0;
+                for (int b = 0; b < h.nbnd; ++b) launch_lw_band<Real>(dplan<Real>(g), g->bands[b], st, a, s);
             }
         if (g_prof.on)
         {
             cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, s)); g_prof.ev[sw].push_back(e);
-            g_prof.launches[sw] += colres ? 1 : h.nbnd;
+            g_prof.launches[sw] += colres ? 1 : h.nbnd * nang;
         }
     }
     if (out->d_flux_net) launch_net<Real>(ncv, a.flux_dn, a.flux_up, out->d_flux_net, s);

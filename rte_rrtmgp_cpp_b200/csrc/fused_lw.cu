@@ -112,7 +112,7 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
         {
 #pragma unroll
             for (int j = 0; j < 4; ++j) lev_top[j] = pf[j] * blev;
-            if (lead && a.bnd_dn) a.bnd_dn[o_top + nlev_stride * band] = 0;      // no incident diffuse flux
+            if (lead && a.bnd_dn && !a.bnd_add) a.bnd_dn[o_top + nlev_stride * band] = 0;      // no incident diffuse flux
         }
         else
         {
@@ -134,7 +134,7 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
             if (lead)
             {
                 atomicAdd(a.flux_dn + o, s);
-                if (a.bnd_dn) a.bnd_dn[o + nlev_stride * band] = s;
+                if (a.bnd_dn) { Real* b_ = a.bnd_dn + o + nlev_stride * band; *b_ = a.bnd_add ? *b_ + s : s; }
             }
         }
         if (k < nlay)
@@ -156,7 +156,7 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
         if (lead)
         {
             atomicAdd(a.flux_up + o, s);
-            if (a.bnd_up) a.bnd_up[o + nlev_stride * band] = s;
+            if (a.bnd_up) { Real* b_ = a.bnd_up + o + nlev_stride * band; *b_ = a.bnd_add ? *b_ + s : s; }
         }
     }
     // ---- up-sweep, surface -> top (F90:710-745): the parked {trans, source_up} come back LIFO through
@@ -184,7 +184,7 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
             if (lead)
             {
                 atomicAdd(a.flux_up + o, s);
-                if (a.bnd_up) a.bnd_up[o + nlev_stride * band] = s;
+                if (a.bnd_up) { Real* b_ = a.bnd_up + o + nlev_stride * band; *b_ = a.bnd_add ? *b_ + s : s; }
             }
         }
     };

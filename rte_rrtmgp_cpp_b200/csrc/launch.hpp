@@ -29,7 +29,8 @@ template<typename Real> struct FusedArgs
     int* slot_busy; int nslots;                                     // strips are claimed by resident CTAs
     Real* flux_up; Real* flux_dn; Real* flux_dir;                   // (ncol, nlay+1), accumulated
     Real* bnd_up; Real* bnd_dn; Real* bnd_dir;                      // (ncol, nlay+1, nbnd) or null
-    Real secant, weight;                                            // LW quadrature
+    Real secant, weight;                                            // LW quadrature angle of this launch
+    int bnd_add;                                                    // LW: add this angle onto the by-band outputs
 };
 constexpr int FUSED_THREADS = 128;
 template<typename Real> int lw_blocks_per_wave(int gw);

@@ -114,3 +114,21 @@ def test_errors_are_loud():
     cols.gas_concs.gas_concs_map.pop("o3")
     with pytest.raises(RuntimeError, match="o3"):
         lw.solve_gpu(cols)
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("n_ang", [2, 3, 4])
+def test_lw_fused_gauss_angles(dtype, n_ang):
+    """Gauss-Jacobi quadrature with 2..4 angles in the fused call (src/Rte_lw.cpp:139-151; the CPU reference
+    supports it, its GPU path does not): one pass of the band kernels per angle, fluxes and by-band fluxes add up."""
+    kd, lut = synthetic_kdist("lw"), synthetic_cloud_lut("lw")
+    atm = rce_atmosphere(45, 40, cloudy=True)
+    ref = oracle_lw(kd, atm, lut, n_ang=n_ang)
+    sol = api.Radiation_solver_longwave(kd, atm.vmr.keys(), lut, dtype)
+    sol.n_gauss_angles = n_ang
+    out = {}
+    for k, nd in (("flux_up", 2), ("flux_dn", 2), ("flux_net", 2), ("bnd_flux_up", 3), ("bnd_flux_dn", 3), ("bnd_flux_net", 3)):
+        out[k] = api.Array_gpu((45, 41) if nd == 2 else (45, 41, kd.nbnd), dtype)
+        out[k].t.fill_(-999.0)                       # every element must be (over)written, not accumulated onto garbage
+    sol.solve_gpu(api.DeviceColumns(atm, dtype), switch_cloud_optics=True, switch_output_bnd_fluxes=True, out=out)
+    _cmp(out, ref, ("flux_up", "flux_dn", "flux_net", "bnd_flux_up", "bnd_flux_dn", "bnd_flux_net"), TOL[dtype])
