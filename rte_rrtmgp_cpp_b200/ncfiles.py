@@ -1,0 +1,150 @@
+"""netCDF (classic, 64-bit offset) files with the reference's variable names and dimension orders.
+
+Writers for the three kinds of file the reference's executable reads and a reader for the one it
+writes, so that the command-line driver (cli/test_rte_rrtmgp.cpp) can be exercised end to end:
+  coefficients_{lw,sw}.nc        <- KDistFile      (schema: src_test/Radiation_solver.cpp:78-243)
+  cloud_coefficients_{lw,sw}.nc  <- CloudLUTFile   (schema: src_test/Radiation_solver.cpp:286-326)
+  rte_rrtmgp_input.nc            <- Atmosphere     (schema: src_test/test_rte_rrtmgp.cpp:205-330,455-478)
+  rte_rrtmgp_output.nc           -> dict of numpy arrays (schema: :300-311,394-439,559-630)
+scipy.io.netcdf_file writes CDF-1/CDF-2 only; the real rrtmgp-data files are netCDF-4 and have to be
+converted once with `nccopy -k cdf5` (no HDF5 library in this image)."""
+from __future__ import annotations
+
+from typing import Dict, Sequence
+
+import numpy as np
+from scipy.io import netcdf_file
+
+from .atmos import Atmosphere
+from .kdist import CloudLUTFile, KDistFile, STRING_LEN
+
+
+def _dims(f, **sizes):
+    for k, v in sizes.items():
+        f.createDimension(k, int(v))
+
+
+def _var(f, name: str, data, dims: Sequence[str], kind: str = "f8"):
+    v = f.createVariable(name, kind, tuple(dims))
+    a = np.asarray(data)
+    if dims:
+        v[:] = a.reshape([f.dimensions[d] for d in dims])
+    else:
+        v[...] = a.reshape(())
+    return v
+
+
+def _strings(f, name: str, names: Sequence[str], dim: str):
+    v = f.createVariable(name, "c", (dim, "string_len"))
+    block = np.array([list(s.encode("ascii")[:STRING_LEN].ljust(STRING_LEN, b" ")) for s in names], dtype=np.uint8)
+    v[:] = block.view("S1").reshape(len(names), STRING_LEN)
+
+
+def write_kdist(kd: KDistFile, path: str) -> None:
+    """rrtmgp-gas-*.nc layout: variables in file dimension order, strings as blank-padded char blocks."""
+    f = netcdf_file(path, "w", version=2)
+    nT, nPi, nE, nG = kd.kmajor.shape
+    _dims(f, temperature=nT, pressure=kd.press_ref.size, pressure_interp=nPi, absorber=len(kd.gas_names),
+          minor_absorber=len(kd.gas_minor), absorber_ext=kd.vmr_ref.shape[1], mixing_fraction=nE,
+          atmos_layer=kd.vmr_ref.shape[2], bnd=kd.nbnd, gpt=nG, pair=2,
+          minor_absorber_intervals_lower=len(kd.minor_gases_lower), minor_absorber_intervals_upper=len(kd.minor_gases_upper),
+          contributors_lower=kd.kminor_lower.shape[2], contributors_upper=kd.kminor_upper.shape[2], string_len=STRING_LEN)
+    _strings(f, "gas_names", kd.gas_names, "absorber")
+    _var(f, "key_species", kd.key_species, ("bnd", "atmos_layer", "pair"), "i4")
+    _var(f, "bnd_limits_wavenumber", kd.bnd_limits_wavenumber, ("bnd", "pair"))
+    _var(f, "bnd_limits_gpt", kd.bnd_limits_gpt, ("bnd", "pair"), "i4")
+    _var(f, "press_ref", kd.press_ref, ("pressure",))
+    _var(f, "temp_ref", kd.temp_ref, ("temperature",))
+    _var(f, "absorption_coefficient_ref_P", kd.absorption_coefficient_ref_P, ())
+    _var(f, "absorption_coefficient_ref_T", kd.absorption_coefficient_ref_T, ())
+    _var(f, "press_ref_trop", kd.press_ref_trop, ())
+    _var(f, "vmr_ref", kd.vmr_ref, ("temperature", "absorber_ext", "atmos_layer"))
+    _var(f, "kmajor", kd.kmajor, ("temperature", "pressure_interp", "mixing_fraction", "gpt"))
+    _var(f, "kminor_lower", kd.kminor_lower, ("temperature", "mixing_fraction", "contributors_lower"))
+    _var(f, "kminor_upper", kd.kminor_upper, ("temperature", "mixing_fraction", "contributors_upper"))
+    _strings(f, "gas_minor", kd.gas_minor, "minor_absorber")
+    _strings(f, "identifier_minor", kd.identifier_minor, "minor_absorber")
+    for side in ("lower", "upper"):
+        d = "minor_absorber_intervals_" + side
+        _strings(f, "minor_gases_" + side, getattr(kd, "minor_gases_" + side), d)
+        _var(f, "minor_limits_gpt_" + side, getattr(kd, "minor_limits_gpt_" + side), (d, "pair"), "i4")
+        _var(f, "minor_scales_with_density_" + side, getattr(kd, "minor_scales_with_density_" + side), (d,), "i4")
+        _var(f, "scale_by_complement_" + side, getattr(kd, "scale_by_complement_" + side), (d,), "i4")
+        _strings(f, "scaling_gas_" + side, getattr(kd, "scaling_gas_" + side), d)
+        _var(f, "kminor_start_" + side, getattr(kd, "kminor_start_" + side), (d,), "i4")
+    if kd.is_lw:
+        _dims(f, temperature_Planck=kd.totplnk.shape[1])
+        _var(f, "totplnk", kd.totplnk, ("bnd", "temperature_Planck"))
+        _var(f, "plank_fraction", kd.plank_fraction, ("temperature", "pressure_interp", "mixing_fraction", "gpt"))
+    else:
+        _var(f, "rayl_lower", kd.rayl_lower, ("temperature", "mixing_fraction", "gpt"))
+        _var(f, "rayl_upper", kd.rayl_upper, ("temperature", "mixing_fraction", "gpt"))
+        for n in ("quiet", "facular", "sunspot"):
+            _var(f, "solar_source_" + n, getattr(kd, "solar_source_" + n), ("gpt",))
+        for n in ("tsi_default", "mg_default", "sb_default"):
+            _var(f, n, getattr(kd, n), ())
+    f.close()
+
+
+def write_cloud_lut(lut: CloudLUTFile, path: str) -> None:
+    f = netcdf_file(path, "w", version=2)
+    _dims(f, nband=lut.nbnd, nrghice=lut.lut_extice.shape[0], nsize_liq=lut.lut_extliq.shape[1],
+          nsize_ice=lut.lut_extice.shape[2], pair=2)
+    _var(f, "bnd_limits_wavenumber", lut.bnd_limits_wavenumber, ("nband", "pair"))
+    for n in ("radliq_lwr", "radliq_upr", "radliq_fac", "diamice_lwr", "diamice_upr", "diamice_fac"):
+        _var(f, n, getattr(lut, n), ())
+    for n in ("lut_extliq", "lut_ssaliq", "lut_asyliq"):
+        _var(f, n, getattr(lut, n), ("nband", "nsize_liq"))
+    for n in ("lut_extice", "lut_ssaice", "lut_asyice"):
+        _var(f, n, getattr(lut, n), ("nrghice", "nband", "nsize_ice"))
+    f.close()
+
+
+def write_input(atm: Atmosphere, path: str, nx: int, ny: int, kind: str = "f8", tsi_ref: float | None = None) -> None:
+    """rte_rrtmgp_input.nc: fields as (lay|lev, y, x), surface fields as (y, x[, band]); x runs fastest
+    over the columns.  With `tsi_ref` the per-column `tsi` variable is written (tsi_scaling * tsi_ref)."""
+    assert nx * ny == atm.ncol
+    f = netcdf_file(path, "w", version=2)
+    nlay = atm.nlay
+    _dims(f, x=nx, y=ny, lay=nlay, lev=nlay + 1, band_lw=atm.emis_sfc.shape[0], band_sw=atm.sfc_alb_dir.shape[0])
+
+    def field(name, a, dim):      # (ncol, n) column-major-by-column -> (n, y, x)
+        _var(f, name, np.asarray(a).T, (dim, "y", "x"), kind)
+
+    field("p_lay", atm.play, "lay"); field("t_lay", atm.tlay, "lay")
+    field("p_lev", atm.plev, "lev"); field("t_lev", atm.tlev, "lev")
+    for gas, v in atm.vmr.items():
+        v = np.atleast_2d(np.asarray(v))
+        if v.shape == (1, 1):
+            _var(f, "vmr_" + gas, v, (), kind)
+        elif v.shape[0] == 1:
+            _var(f, "vmr_" + gas, v[0], ("lay",), kind)
+        else:
+            field("vmr_" + gas, v, "lay")
+    _var(f, "emis_sfc", atm.emis_sfc.T, ("y", "x", "band_lw"), kind)
+    _var(f, "t_sfc", atm.tsfc, ("y", "x"), kind)
+    _var(f, "mu0", atm.mu0, ("y", "x"), kind)
+    _var(f, "sfc_alb_dir", atm.sfc_alb_dir.T, ("y", "x", "band_sw"), kind)
+    _var(f, "sfc_alb_dif", atm.sfc_alb_dif.T, ("y", "x", "band_sw"), kind)
+    if tsi_ref is not None:
+        _var(f, "tsi", np.asarray(atm.tsi_scaling) * tsi_ref, ("y", "x"), kind)
+    if atm.lwp is not None:
+        for n in ("lwp", "iwp", "rel", "dei"):
+            field(n, getattr(atm, n), "lay")
+    f.close()
+
+
+def read_output(path: str) -> Dict[str, np.ndarray]:
+    """rte_rrtmgp_output.nc -> arrays in the class-API layout: (lev|lay, y, x) -> (ncol, nlev|nlay),
+    (band|gpt, lev|lay, y, x) -> (ncol, n, nband|ngpt), (gpt, y, x) -> (ncol, ngpt); band limits as stored."""
+    f = netcdf_file(path, "r", mmap=False)
+    out: Dict[str, np.ndarray] = {}
+    for name, v in f.variables.items():
+        a = np.array(v[...])
+        d = v.dimensions
+        if len(d) >= 2 and d[-2:] == ("y", "x"):
+            a = a.reshape(a.shape[:-2] + (-1,))
+            a = np.transpose(a, tuple(range(a.ndim))[::-1])
+        out[name] = a
+    f.close()
+    return out
