@@ -158,19 +158,20 @@ def test_cli_output_optical_and_tsi(tmp_path):
     """--output-optical: staged class path; tau/ssa/g/sources/toa_source written with the reference's names;
     per-column `tsi` in the input becomes the tsi scaling (src_test/test_rte_rrtmgp.cu:561-568)."""
     atm = rce_atmosphere(10, 24)
-    kl, ks, ll, ls = _stage(tmp_path, atm, 5, 2, tsi_ref=float(np.sum(synthetic_kdist("sw").solar_source_quiet) * 0 + 1.0))
+    kl, ks, ll, ls = _stage(tmp_path, atm, 5, 2)
     # the reference divides tsi by the table's own tsi: write tsi = scaling * tsi(table) using the oracle's value
-    ref_sw = oracle_sw(ks, atm, None, want_optical=True)
-    ncfiles.write_input(atm, str(tmp_path / "rte_rrtmgp_input.nc"), 5, 2, tsi_ref=ref_sw["tsi"])
+    ref_sw = oracle_sw(ks, atm, None)
+    ncfiles.write_input(atm, str(tmp_path / "rte_rrtmgp_input.nc"), 5, 2, tsi_ref=ref_sw["go"].get_tsi())
     r = subprocess.run([_exe("f64"), "--output-optical", "--timings"], capture_output=True, text=True, cwd=tmp_path)
     assert r.returncode == 0, r.stdout + r.stderr
     assert r.stdout.count("Duration longwave solver") == 11 and r.stdout.count("Duration shortwave solver") == 11
     out = ncfiles.read_output(str(tmp_path / "rte_rrtmgp_output.nc"))
-    ref_lw = oracle_lw(kl, atm, None, want_optical=True)
-    for k, ko in (("tau", "lw_tau"), ("lay_source", "lay_source"), ("lev_source", "lev_source"), ("sfc_source", "sfc_source")):
-        assert np.allclose(out[ko], ref_lw[k], rtol=1e-10, atol=1e-12), ko
-    for k, ko in (("tau", "sw_tau"), ("ssa", "ssa"), ("g", "g"), ("toa_source", "toa_source")):
-        assert np.allclose(out[ko], ref_sw[k], rtol=1e-10, atol=1e-12), ko
+    ref_lw = oracle_lw(kl, atm, None)
+    st = ref_lw["state"]
+    for a, ko in ((ref_lw["tau"], "lw_tau"), (st["lay_src"], "lay_source"), (st["lev_src"], "lev_source"), (st["sfc_src"], "sfc_source")):
+        assert out[ko].shape == a.shape and np.allclose(out[ko], a, rtol=1e-10, atol=1e-12), ko
+    for a, ko in ((ref_sw["tau"], "sw_tau"), (ref_sw["ssa"], "ssa"), (ref_sw["g"], "g"), (ref_sw["toa"], "toa_source")):
+        assert out[ko].shape == a.shape and np.allclose(out[ko], a, rtol=1e-10, atol=1e-12), ko
     assert np.array_equal(out["lw_band_lims_gpt"], kl.bnd_limits_gpt) and np.array_equal(out["sw_band_lims_gpt"], ks.bnd_limits_gpt)
     for k in ("flux_up", "flux_dn", "flux_net"):
         assert np.abs(out["lw_" + k] - ref_lw[k]).max() <= 1e-5 and np.abs(out["sw_" + k] - ref_sw[k]).max() <= 1e-5, k
