@@ -1,9 +1,9 @@
 // test_rte_rrtmgp_b200 — command-line driver with the flags and the file contract of the reference's
 // `test_rte_rrtmgp` (src_test/test_rte_rrtmgp.cu:171-818, CPU twin src_test/test_rte_rrtmgp.cpp):
-//   reads   rte_rrtmgp_input.nc, coefficients_{lw,sw}.nc, cloud_coefficients_{lw,sw}.nc   (cwd)
+//   reads   rte_rrtmgp_input.nc, coefficients_{lw,sw}.nc, cloud_coefficients_{lw,sw}.nc, aerosol_optics.nc   (cwd)
 //   writes  rte_rrtmgp_output.nc  — same variable names, dimension names and dimension orders
 //   flags   --[no-]shortwave --[no-]longwave --[no-]fluxes --[no-]cloud-optics --[no-]output-optical
-//           --[no-]output-bnd-fluxes --[no-]delta-cloud --[no-]timings   (aerosol flags are recognised and refused)
+//           --[no-]output-bnd-fluxes --[no-]delta-cloud --[no-]timings --[no-]aerosol-optics --[no-]delta-aerosol
 // Files are netCDF classic (CDF-1/2/5); see include/rrtmgp_b200/netcdf_classic.hpp.  All radiation work
 // goes through include/rrtmgp_b200/classes.hpp -> librrtmgp_b200.so; nothing is computed on the host.
 // Build: g++ -std=c++17 [-DRTE_USE_SP] -Iinclude cli/test_rte_rrtmgp.cpp -lrrtmgp_b200 -lcudart
@@ -32,12 +32,12 @@ std::vector<Option> default_options()
         {"longwave", true, "Enable computation of longwave radiation."},
         {"fluxes", true, "Enable computation of fluxes."},
         {"cloud-optics", false, "Enable cloud optics."},
-        {"aerosol-optics", false, "Enable aerosol optics (not available in this build)."},
+        {"aerosol-optics", false, "Enable aerosol optics."},
         {"output-optical", false, "Enable output of optical properties."},
         {"output-bnd-fluxes", false, "Enable output of band fluxes."},
         {"timings", false, "Repeat computation 10x for run times."},
         {"delta-cloud", true, "delta-scaling of cloud optical properties"},
-        {"delta-aerosol", false, "delta-scaling of aerosol optical properties (not available in this build)"}};
+        {"delta-aerosol", false, "delta-scaling of aerosol optical properties"}};
 }
 
 // returns true when only the help text was asked for
@@ -92,6 +92,25 @@ void read_and_set_vmr(const std::string& gas, const int nx, const int ny, const 
     else throw bad();
 }
 
+// aermr01..aermr11: (lay) or (lay, y, x) — src_test/test_rte_rrtmgp.cpp:69-100
+void read_and_set_aer(const std::string& name, const int nx, const int ny, const int nlay, const Netcdf_file& in, Aerosol_concs_gpu& concs)
+{
+    if (!in.variable_exists(name)) throw std::runtime_error("Aerosol type \"" + name + "\" not available in input file.");
+    const std::map<std::string, int> dims = in.get_variable_dimensions(name);
+    const auto bad = [&name]() { return std::runtime_error("Illegal dimensions of \"" + name + "\" in input"); };
+    if (dims.size() == 1)
+    {
+        if (!dims.count("lay") || dims.at("lay") != nlay) throw std::runtime_error("Illegal dimensions of gas \"" + name + "\" in input");
+        concs.set_vmr(name, in.get_variable<Float>(name, {nlay}), 1, nlay);
+    }
+    else if (dims.size() == 3)
+    {
+        if (!dims.count("lay") || !dims.count("x") || !dims.count("y") || dims.at("lay") != nlay || dims.at("x") != nx || dims.at("y") != ny) throw bad();
+        concs.set_vmr(name, in.get_variable<Float>(name, {nlay, ny, nx}), nx * ny, nlay);
+    }
+    else throw bad();
+}
+
 template<int N> Array_gpu<Float,N> upload(const Netcdf_file& in, const std::string& var, const std::vector<int>& file_shape, const std::array<int,N>& dims)
 { return Array_gpu<Float,N>(in.get_variable<Float>(var, file_shape), dims); }
 
@@ -133,8 +152,7 @@ static void solve_radiation(int argc, char** argv)
     const bool timings = opt(opts, "timings"), delta_cloud = opt(opts, "delta-cloud");
     say("Solver settings:");
     for (const auto& o : opts) { std::ostringstream ss; ss << std::left << std::setw(20) << o.name << " = " << std::boolalpha << o.value; say(ss.str()); }
-    if (opt(opts, "aerosol-optics") || opt(opts, "delta-aerosol"))
-        throw std::runtime_error("aerosol optics is not part of this build (SURVEY.md section 8, row f-3)");
+    const bool aerosol = opt(opts, "aerosol-optics"), delta_aerosol = opt(opts, "delta-aerosol");
 
     // ---- atmosphere: (lay|lev, y, x) in the file = (col, lay|lev) column-major in memory
     say("Reading atmospheric input data from NetCDF.");
@@ -160,6 +178,15 @@ static void solve_radiation(int argc, char** argv)
     {
         lwp = upload<2>(in, "lwp", {nlay, ny, nx}, {ncol, nlay}); iwp = upload<2>(in, "iwp", {nlay, ny, nx}, {ncol, nlay});
         rel = upload<2>(in, "rel", {nlay, ny, nx}, {ncol, nlay}); dei = upload<2>(in, "dei", {nlay, ny, nx}, {ncol, nlay});
+    }
+
+    Array_gpu<Float,2> rh;
+    Aerosol_concs_gpu aerosol_concs;
+    if (aerosol)      // src_test/test_rte_rrtmgp.cpp:274-293
+    {
+        rh = upload<2>(in, "rh", {nlay, ny, nx}, {ncol, nlay});
+        for (int i = 1; i <= 11; ++i)
+            read_and_set_aer(std::string("aermr") + (i < 10 ? "0" : "") + std::to_string(i), nx, ny, nlay, in, aerosol_concs);
     }
 
     // ---- output file
@@ -232,7 +259,9 @@ static void solve_radiation(int argc, char** argv)
         rrtmgp_b200::Kdist_tables kd("coefficients_sw.nc");
         std::unique_ptr<rrtmgp_b200::Cloud_tables> ct;
         if (cloud) ct = std::make_unique<rrtmgp_b200::Cloud_tables>("cloud_coefficients_sw.nc");
-        Radiation_solver_shortwave rad_sw(gas_concs, kd.file(), ct ? &ct->file() : nullptr);
+        std::unique_ptr<rrtmgp_b200::Aerosol_tables> at;
+        if (aerosol) at = std::make_unique<rrtmgp_b200::Aerosol_tables>("aerosol_optics.nc");
+        Radiation_solver_shortwave rad_sw(gas_concs, kd.file(), ct ? &ct->file() : nullptr, at ? &at->file() : nullptr);
         const int nbnd = rad_sw.get_n_bnd_gpu(), ngpt = rad_sw.get_n_gpt_gpu();
 
         Array_gpu<Float,1> mu0 = upload<1>(in, "mu0", {ny, nx}, {ncol});
@@ -269,8 +298,8 @@ static void solve_radiation(int argc, char** argv)
         say("Solving the shortwave radiation.");
         run_timed(timings, "shortwave", [&]()
         {
-            rad_sw.solve_gpu(fluxes, cloud, optical, bnd, delta_cloud, gas_concs, p_lay, p_lev, t_lay, t_lev, col_dry,
-                             sfc_alb_dir, sfc_alb_dif, tsi_scaling, mu0, lwp, iwp, rel, dei,
+            rad_sw.solve_gpu(fluxes, cloud, aerosol, optical, bnd, delta_cloud, delta_aerosol, gas_concs, p_lay, p_lev, t_lay, t_lev, col_dry,
+                             sfc_alb_dir, sfc_alb_dif, tsi_scaling, mu0, lwp, iwp, rel, dei, rh, aerosol_concs,
                              sw_tau, ssa, g, toa_source, sw_flux_up, sw_flux_dn, sw_flux_dn_dir, sw_flux_net,
                              sw_bnd_flux_up, sw_bnd_flux_dn, sw_bnd_flux_dn_dir, sw_bnd_flux_net);
         });

@@ -46,6 +46,7 @@ enum {
 
 typedef struct rrtmgp_b200_gas_optics rrtmgp_b200_gas_optics;     /* Gas_optics_rrtmgp_gpu  */
 typedef struct rrtmgp_b200_cloud_optics rrtmgp_b200_cloud_optics; /* Cloud_optics_gpu       */
+typedef struct rrtmgp_b200_aerosol_optics rrtmgp_b200_aerosol_optics; /* Aerosol_optics_gpu */
 
 const char* rrtmgp_b200_last_error(void);
 int rrtmgp_b200_version(void);
@@ -146,6 +147,32 @@ int rrtmgp_b200_cloud_optics_1scl(const rrtmgp_b200_cloud_optics* co, int ncol, 
                                   const void* d_lwp, const void* d_iwp, const void* d_rel,
                                   const void* d_dei, void* d_tau, void* stream);
 
+/* ---- Aerosol_optics_gpu (include/Aerosol_optics.h:48-84, src_cuda/Aerosol_optics.cu:9-279; CPU
+ * src/Aerosol_optics.cpp:10-224).  Eleven species in the reference's fixed order aermr01..aermr11
+ * (SS1,SS2,SS3,DU1,DU2,DU3,OM2(philic),OM1(phobic),BC1,BC2,SU) with its fixed table columns
+ * (src/Aerosol_optics.cpp:64-142).  Mixing ratios replace Aerosol_concs_gpu (= Gas_concs_gpu,
+ * include/Aerosol_optics.h:20): species i is a device scalar (1,1), profile (1,nlay) or field
+ * (ncol,nlay); fill_aerosols_3d's broadcast (src/Aerosol_optics.cpp:152-165) happens in the kernel.
+ * Layer mass dpg = |plev(l) - plev(l+1)| / 9.81 as in the reference's GPU twin
+ * (src_cuda/Aerosol_optics.cu:63); its CPU twin omits the abs (src/Aerosol_optics.cpp:53) and agrees
+ * for the bottom-up columns its driver uses.  The humidity class is the first i with rh <= rh_upper(i)
+ * (src/Aerosol_optics.cpp:27-38), clamped to the last class (the reference reads past the table).
+ * Output by band: tau, ssa = taussa/max(tau,eps), g = taussag/max(taussa,eps), (ncol,nlay,nband). */
+typedef struct rrtmgp_b200_aerosol_concs
+{
+    const void* d_mmr[11];     /* aermr01 .. aermr11 */
+    int mmr_ncol[11];          /* 1 or ncol */
+    int mmr_nlay[11];          /* 1 or nlay */
+} rrtmgp_b200_aerosol_concs;
+int rrtmgp_b200_aerosol_optics_create(const rrtmgp_b200_aerosol_file* lut, int dtype,
+                                      rrtmgp_b200_aerosol_optics** out);
+void rrtmgp_b200_aerosol_optics_destroy(rrtmgp_b200_aerosol_optics* ao);
+int rrtmgp_b200_aerosol_optics_nband(const rrtmgp_b200_aerosol_optics* ao);
+int rrtmgp_b200_aerosol_optics_2str(const rrtmgp_b200_aerosol_optics* ao, int ncol, int nlay,
+                                    const rrtmgp_b200_aerosol_concs* concs, const void* d_rh,
+                                    const void* d_plev, void* d_tau, void* d_ssa, void* d_g,
+                                    void* stream);
+
 /* ---- Optical_props: delta_scale / add_to (include/Optical_props.h:165-176,214-293;
  * kernels rte_delta_scale_2str_k, rte_increment_*, rte_inc_*_bybnd, include/rrtmgp_kernels.h:
  * 137-205; CUDA src_kernels_cuda/optical_props_kernels.cu:30-161).  In-place on op1. */
@@ -211,7 +238,8 @@ int rrtmgp_b200_heating_rate(int dtype, int ncol, int nlay, const void* d_flux_u
 
 /* ---- Fused column solvers: one call = Radiation_solver_{longwave,shortwave}::solve_gpu for a
  * set of columns (src_test/Radiation_solver.cu:419-657, 690-950), i.e. gas_optics ->
- * [cloud_optics -> delta_scale -> add_to] -> rte_lw / rte_sw -> Fluxes::reduce, with the
+ * [cloud_optics -> delta_scale -> add_to] -> [aerosol_optics -> delta_scale -> add_to] ->
+ * rte_lw / rte_sw -> Fluxes::reduce, with the
  * per-g-point arrays kept on chip.  All inputs as the class API takes them. */
 typedef struct rrtmgp_b200_columns
 {
@@ -234,6 +262,12 @@ typedef struct rrtmgp_b200_columns
     int delta_cloud;               /* --delta-cloud, default on in the reference (SW only) */
     const void* d_lwp; const void* d_iwp; const void* d_rel; const void* d_dei; /* (ncol,nlay) */
     int n_gauss_angles;            /* LW, 1..4 (0 -> 1): Gauss-Jacobi-5 angles of src/Rte_lw.cpp:139-151 */
+    /* aerosols, SW only (NULL handle = none): aerosol_optics -> [delta_scale] -> add_to after the
+     * clouds, src_test/Radiation_solver.cu:794-810 */
+    const rrtmgp_b200_aerosol_optics* aerosol;
+    int delta_aerosol;             /* --delta-aerosol, default off in the reference */
+    const void* d_rh;              /* (ncol,nlay) relative humidity */
+    rrtmgp_b200_aerosol_concs aerosol_concs;
 } rrtmgp_b200_columns;
 
 typedef struct rrtmgp_b200_fluxes

@@ -7,6 +7,7 @@
 //   Source_func_lw_gpu        include/Source_functions.h:70-93
 //   Gas_optics_rrtmgp_gpu     include/Gas_optics_rrtmgp.h:293-408
 //   Cloud_optics_gpu          include/Cloud_optics.h
+//   Aerosol_optics_gpu, Aerosol_concs_gpu   include/Aerosol_optics.h:20,48-84
 //   Rte_lw_gpu / Rte_sw_gpu   include/Rte_lw.h:62-77, include/Rte_sw.h:62-80
 //   Fluxes_broadband_gpu / Fluxes_byband_gpu   include/Fluxes.h:127-210
 // Precision follows the reference switch: -DRTE_USE_SP -> Float = float (include/types.h:19-25).
@@ -397,6 +398,46 @@ class Cloud_optics_gpu : public Optical_props_gpu
         rrtmgp_b200_cloud_optics* h = nullptr;
 };
 
+using Aerosol_concs_gpu = Gas_concs_gpu;       // include/Aerosol_optics.h:20
+
+namespace rrtmgp_b200 {
+// Aerosol_concs -> the C struct (aermr01..aermr11)
+inline rrtmgp_b200_aerosol_concs aerosol_view(const Aerosol_concs_gpu& a)
+{
+    rrtmgp_b200_aerosol_concs c{};
+    for (int i = 0; i < 11; ++i)
+    {
+        const std::string name = std::string("aermr") + (i < 9 ? "0" : "") + std::to_string(i + 1);
+        const auto& m = a.get_vmr(name);
+        c.d_mmr[i] = m.ptr(); c.mmr_ncol[i] = m.dim(1); c.mmr_nlay[i] = m.dim(2);
+    }
+    return c;
+}
+}  // namespace rrtmgp_b200
+
+// include/Aerosol_optics.h:48-84.  The reference constructor takes eight Arrays already reshaped to
+// (band, [humidity,] type); here the file variables arrive in one struct in file order.  Like the reference's
+// loader (src_test/Radiation_solver.cu:366-402) the band limits stay zero.
+class Aerosol_optics_gpu : public Optical_props_gpu
+{
+    public:
+        explicit Aerosol_optics_gpu(const rrtmgp_b200_aerosol_file& lut)
+            : Optical_props_gpu(std::vector<Float>(2 * (size_t)lut.n_band, Float(0.)))
+        { rrtmgp_b200::check(rrtmgp_b200_aerosol_optics_create(&lut, rrtmgp_b200::dtype, &h)); }
+        ~Aerosol_optics_gpu() { rrtmgp_b200_aerosol_optics_destroy(h); }
+        Aerosol_optics_gpu(const Aerosol_optics_gpu&) = delete;
+        void aerosol_optics(const Aerosol_concs_gpu& aerosol_concs, const Array_gpu<Float,2>& rh, const Array_gpu<Float,2>& plev,
+                            Optical_props_2str_gpu& optical_props) const
+        {
+            const rrtmgp_b200_aerosol_concs ac = rrtmgp_b200::aerosol_view(aerosol_concs);
+            rrtmgp_b200::check(rrtmgp_b200_aerosol_optics_2str(h, rh.dim(1), rh.dim(2), &ac, rh.ptr(), plev.ptr(),
+                    optical_props.get_tau().ptr(), optical_props.get_ssa().ptr(), optical_props.get_g().ptr(), rrtmgp_b200::stream()));
+        }
+        rrtmgp_b200_aerosol_optics* handle() const { return h; }
+    private:
+        rrtmgp_b200_aerosol_optics* h = nullptr;
+};
+
 class Rte_lw_gpu
 {
     public:
@@ -611,9 +652,12 @@ class Radiation_solver_shortwave
 {
     public:
         Radiation_solver_shortwave(const Gas_concs_gpu& gas_concs, const rrtmgp_b200_kdist_file& kdist,
-                                   const rrtmgp_b200_cloud_file* cloud = nullptr)
+                                   const rrtmgp_b200_cloud_file* cloud = nullptr, const rrtmgp_b200_aerosol_file* aerosol = nullptr)
             : kdist_gpu(std::make_unique<Gas_optics_rrtmgp_gpu>(gas_concs, kdist))
-        { if (cloud) cloud_optics_gpu = std::make_unique<Cloud_optics_gpu>(*cloud); }
+        {
+            if (cloud) cloud_optics_gpu = std::make_unique<Cloud_optics_gpu>(*cloud);
+            if (aerosol) aerosol_optics_gpu = std::make_unique<Aerosol_optics_gpu>(*aerosol);
+        }
 
         int get_n_gpt_gpu() const { return kdist_gpu->get_ngpt(); }
         int get_n_bnd_gpu() const { return kdist_gpu->get_nband(); }
@@ -622,6 +666,7 @@ class Radiation_solver_shortwave
         const std::vector<Float>& get_band_lims_wavenumber_gpu() const { return kdist_gpu->get_band_lims_wavenumber(); }
         Gas_optics_rrtmgp_gpu& get_kdist_gpu() { return *kdist_gpu; }
 
+        // the aerosol-free call of earlier callers
         void solve_gpu(const bool switch_fluxes, const bool switch_cloud_optics, const bool switch_output_optical,
                        const bool switch_output_bnd_fluxes, const bool switch_delta_cloud, const Gas_concs_gpu& gas_concs,
                        const Array_gpu<Float,2>& p_lay, const Array_gpu<Float,2>& p_lev,
@@ -636,9 +681,32 @@ class Radiation_solver_shortwave
                        Array_gpu<Float,3>& sw_bnd_flux_up, Array_gpu<Float,3>& sw_bnd_flux_dn,
                        Array_gpu<Float,3>& sw_bnd_flux_dn_dir, Array_gpu<Float,3>& sw_bnd_flux_net)
         {
+            solve_gpu(switch_fluxes, switch_cloud_optics, false, switch_output_optical, switch_output_bnd_fluxes, switch_delta_cloud, false,
+                      gas_concs, p_lay, p_lev, t_lay, t_lev, col_dry, sfc_alb_dir, sfc_alb_dif, tsi_scaling, mu0, lwp, iwp, rel, dei,
+                      Array_gpu<Float,2>(), Aerosol_concs_gpu(), tau, ssa, g, toa_src, sw_flux_up, sw_flux_dn, sw_flux_dn_dir, sw_flux_net,
+                      sw_bnd_flux_up, sw_bnd_flux_dn, sw_bnd_flux_dn_dir, sw_bnd_flux_net);
+        }
+        // the reference's argument list (src_test/Radiation_solver.cu:684-711)
+        void solve_gpu(const bool switch_fluxes, const bool switch_cloud_optics, const bool switch_aerosol_optics,
+                       const bool switch_output_optical, const bool switch_output_bnd_fluxes,
+                       const bool switch_delta_cloud, const bool switch_delta_aerosol, const Gas_concs_gpu& gas_concs,
+                       const Array_gpu<Float,2>& p_lay, const Array_gpu<Float,2>& p_lev,
+                       const Array_gpu<Float,2>& t_lay, const Array_gpu<Float,2>& t_lev, const Array_gpu<Float,2>& col_dry,
+                       const Array_gpu<Float,2>& sfc_alb_dir, const Array_gpu<Float,2>& sfc_alb_dif,
+                       const Array_gpu<Float,1>& tsi_scaling, const Array_gpu<Float,1>& mu0,
+                       const Array_gpu<Float,2>& lwp, const Array_gpu<Float,2>& iwp,
+                       const Array_gpu<Float,2>& rel, const Array_gpu<Float,2>& dei,
+                       const Array_gpu<Float,2>& rh, const Aerosol_concs_gpu& aerosol_concs,
+                       Array_gpu<Float,3>& tau, Array_gpu<Float,3>& ssa, Array_gpu<Float,3>& g, Array_gpu<Float,2>& toa_src,
+                       Array_gpu<Float,2>& sw_flux_up, Array_gpu<Float,2>& sw_flux_dn,
+                       Array_gpu<Float,2>& sw_flux_dn_dir, Array_gpu<Float,2>& sw_flux_net,
+                       Array_gpu<Float,3>& sw_bnd_flux_up, Array_gpu<Float,3>& sw_bnd_flux_dn,
+                       Array_gpu<Float,3>& sw_bnd_flux_dn_dir, Array_gpu<Float,3>& sw_bnd_flux_net)
+        {
             const int n_col = p_lay.dim(1), n_lay = p_lay.dim(2), n_lev = p_lev.dim(2);
             (void)t_lev;
             if (switch_cloud_optics && !cloud_optics_gpu) throw std::runtime_error("cloud optics requested without cloud tables");
+            if (switch_aerosol_optics && !aerosol_optics_gpu) throw std::runtime_error("aerosol optics requested without aerosol tables");
             if (!switch_output_optical)
             {
                 if (!switch_fluxes) return;
@@ -653,6 +721,11 @@ class Radiation_solver_shortwave
                 {
                     c.cloud = cloud_optics_gpu->handle(); c.delta_cloud = switch_delta_cloud;
                     c.d_lwp = lwp.ptr(); c.d_iwp = iwp.ptr(); c.d_rel = rel.ptr(); c.d_dei = dei.ptr();
+                }
+                if (switch_aerosol_optics)
+                {
+                    c.aerosol = aerosol_optics_gpu->handle(); c.delta_aerosol = switch_delta_aerosol;
+                    c.d_rh = rh.ptr(); c.aerosol_concs = rrtmgp_b200::aerosol_view(aerosol_concs);
                 }
                 rrtmgp_b200_fluxes f{};
                 f.d_flux_up = sw_flux_up.ptr(); f.d_flux_dn = sw_flux_dn.ptr(); f.d_flux_net = sw_flux_net.ptr();
@@ -678,6 +751,13 @@ class Radiation_solver_shortwave
                 if (switch_delta_cloud) clouds.delta_scale();
                 add_to(dynamic_cast<Optical_props_2str_gpu&>(*optical_props), clouds);
             }
+            if (switch_aerosol_optics)      // src_test/Radiation_solver.cu:794-810
+            {
+                Optical_props_2str_gpu aerosols(n_col, n_lay, *aerosol_optics_gpu);
+                aerosol_optics_gpu->aerosol_optics(aerosol_concs, rh, p_lev, aerosols);
+                if (switch_delta_aerosol) aerosols.delta_scale();
+                add_to(dynamic_cast<Optical_props_2str_gpu&>(*optical_props), aerosols);
+            }
             tau = optical_props->get_tau(); ssa = optical_props->get_ssa(); g = optical_props->get_g(); toa_src = toa;
             if (!switch_fluxes) return;
             const std::vector<Float> pl = Radiation_solver_longwave::top_probe(p_lay);
@@ -701,4 +781,5 @@ class Radiation_solver_shortwave
     private:
         std::unique_ptr<Gas_optics_rrtmgp_gpu> kdist_gpu;
         std::unique_ptr<Cloud_optics_gpu> cloud_optics_gpu;
+        std::unique_ptr<Aerosol_optics_gpu> aerosol_optics_gpu;
 };

@@ -2,7 +2,7 @@
 // netcdf_classic.hpp) into the plain-C table structs of include/rrtmgp_b200_tables.h.
 //
 // Same variables and dimension names as the reference's loaders read
-// (src_test/Radiation_solver.cpp:78-243 gas optics, :286-326 cloud optics); the arrays stay in FILE
+// (src_test/Radiation_solver.cpp:78-243 gas optics, :286-326 cloud optics, :331-367 aerosol optics); the arrays stay in FILE
 // order — the reordering the reference does on the host is part of rrtmgp_b200_gas_optics_create.
 #pragma once
 #include <deque>
@@ -123,6 +123,33 @@ class Cloud_tables
     private:
         const double* dbls(const Netcdf_file& nc, const char* n, const std::vector<int>& s) { d.push_back(nc.get_variable<double>(n, s)); return d.back().data(); }
         rrtmgp_b200_cloud_file f{};
+        std::deque<std::vector<double>> d;
+};
+
+// aerosol_optics.nc (src_test/Radiation_solver.cpp:331-367)
+class Aerosol_tables
+{
+    public:
+        explicit Aerosol_tables(const std::string& file_name)
+        {
+            Netcdf_file nc(file_name, Netcdf_mode::Read);
+            f.n_band = nc.get_dimension_size("band_sw");
+            f.n_hum = nc.get_dimension_size("relative_humidity");
+            f.n_philic = nc.get_dimension_size("hydrophilic");
+            f.n_phobic = nc.get_dimension_size("hydrophobic");
+            f.mass_ext_sw_hydrophobic = dbls(nc, "mass_ext_sw_hydrophobic", {f.n_phobic, f.n_band});
+            f.ssa_sw_hydrophobic = dbls(nc, "ssa_sw_hydrophobic", {f.n_phobic, f.n_band});
+            f.asymmetry_sw_hydrophobic = dbls(nc, "asymmetry_sw_hydrophobic", {f.n_phobic, f.n_band});
+            f.mass_ext_sw_hydrophilic = dbls(nc, "mass_ext_sw_hydrophilic", {f.n_philic, f.n_hum, f.n_band});
+            f.ssa_sw_hydrophilic = dbls(nc, "ssa_sw_hydrophilic", {f.n_philic, f.n_hum, f.n_band});
+            f.asymmetry_sw_hydrophilic = dbls(nc, "asymmetry_sw_hydrophilic", {f.n_philic, f.n_hum, f.n_band});
+            f.relative_humidity2 = dbls(nc, "relative_humidity2", {f.n_hum});
+        }
+        Aerosol_tables(const Aerosol_tables&) = delete;
+        const rrtmgp_b200_aerosol_file& file() const { return f; }
+    private:
+        const double* dbls(const Netcdf_file& nc, const char* n, const std::vector<int>& s) { d.push_back(nc.get_variable<double>(n, s)); return d.back().data(); }
+        rrtmgp_b200_aerosol_file f{};
         std::deque<std::vector<double>> d;
 };
 

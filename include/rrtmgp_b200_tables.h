@@ -95,6 +95,24 @@ typedef struct rrtmgp_b200_cloud_file
     const double* lut_asyice;
 } rrtmgp_b200_cloud_file;
 
+/* aerosol_optics.nc as read by load_and_init_aerosol_optics (src_test/Radiation_solver.cpp:331-367,
+ * src_test/Radiation_solver.cu:366-402): shortwave MERRA/IFS-style look-up tables.  Arrays are in
+ * FILE order (C order, last dimension fastest), i.e. band fastest. */
+typedef struct rrtmgp_b200_aerosol_file
+{
+    int n_band;        /* "band_sw" */
+    int n_hum;         /* "relative_humidity" */
+    int n_philic;      /* "hydrophilic" */
+    int n_phobic;      /* "hydrophobic" */
+    const double* mass_ext_sw_hydrophobic;    /* (hydrophobic, band_sw) */
+    const double* ssa_sw_hydrophobic;
+    const double* asymmetry_sw_hydrophobic;
+    const double* mass_ext_sw_hydrophilic;    /* (hydrophilic, relative_humidity, band_sw) */
+    const double* ssa_sw_hydrophilic;
+    const double* asymmetry_sw_hydrophilic;
+    const double* relative_humidity2;         /* (relative_humidity): upper bound of each class */
+} rrtmgp_b200_aerosol_file;
+
 #ifdef __cplusplus
 }
 #endif

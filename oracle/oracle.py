@@ -376,6 +376,50 @@ class CloudOptics(SpectralDisc):
 
 
 # ------------------------------------------------------------------------------------------
+# Aerosol_optics: src/Aerosol_optics.cpp (pure C++ in the reference; restated in numpy)
+# ------------------------------------------------------------------------------------------
+class AerosolOptics(SpectralDisc):
+    # (species name, "phobic" column | "philic" type (1-based), aermr index) in the summation order of
+    # list_aerosol_types, src/Aerosol_optics.cpp:51,64-142
+    SPECIES = (("SS1", -1, 1), ("SS2", -2, 2), ("SS3", -3, 3), ("DU1", 1, 4), ("DU2", 8, 5), ("DU3", 6, 6),
+               ("OM1", 10, 8), ("OM2", -4, 7), ("BC1", 11, 9), ("BC2", 11, 10), ("SU", -5, 11))
+
+    def __init__(self, lut):
+        nb = lut.mass_ext_sw_hydrophobic.shape[1]
+        super().__init__(np.zeros((2, nb)))          # the reference's loader leaves band_lims_wvn zero (:342)
+        self.phobic = [F(a) for a in (lut.mass_ext_sw_hydrophobic, lut.ssa_sw_hydrophobic, lut.asymmetry_sw_hydrophobic)]
+        self.philic = [F(a) for a in (lut.mass_ext_sw_hydrophilic, lut.ssa_sw_hydrophilic, lut.asymmetry_sw_hydrophilic)]
+        self.rh_upper = F(lut.relative_humidity2)
+
+    def aerosol_optics(self, aermr: Dict[str, np.ndarray], rh, plev, abs_dp: bool = False):
+        """Aerosol_optics::aerosol_optics, src/Aerosol_optics.cpp:167-224 -> tau, ssa, g (ncol,nlay,nbnd).
+        abs_dp=False is the CPU source (dpg signed, :53); True the GPU twin (src_cuda/Aerosol_optics.cu:63)."""
+        rh = F(rh); plev = F(plev)
+        ncol, nlay = rh.shape
+        # rh_class (:27-38): first class with rh_upper >= rh
+        ihum = np.searchsorted(self.rh_upper, rh, side="left")
+        if np.any(ihum >= self.rh_upper.size):
+            raise ValueError("relative humidity above the last class: the reference reads past the table")
+        dpg = (plev[:, :-1] - plev[:, 1:]) / 9.81
+        if abs_dp:
+            dpg = np.abs(dpg)
+        nb = self.nbnd
+        tau = np.zeros((ncol, nlay, nb)); taussa = np.zeros_like(tau); taussag = np.zeros_like(tau)
+        for _, col, iaer in self.SPECIES:
+            mmr = np.broadcast_to(F(aermr[f"aermr{iaer:02d}"]), (ncol, nlay))            # fill_aerosols_3d (:152-165)
+            if col > 0:
+                mext, ssa, g = (np.broadcast_to(t[col - 1][None, None, :], (ncol, nlay, nb)) for t in self.phobic)
+            else:
+                mext, ssa, g = (t[-col - 1][ihum, :] for t in self.philic)
+            local_od = (mmr * dpg)[..., None] * mext
+            tau = tau + local_od
+            taussa = taussa + local_od * ssa
+            taussag = taussag + local_od * ssa * g
+        eps = np.finfo(np.float64).eps
+        return F(tau), F(taussa / np.maximum(tau, eps)), F(taussag / np.maximum(taussa, eps))
+
+
+# ------------------------------------------------------------------------------------------
 # Optical_props: delta_scale / add_to — src/Optical_props.cpp:207-268
 # ------------------------------------------------------------------------------------------
 def delta_scale(tau, ssa, g):

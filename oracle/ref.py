@@ -12,7 +12,7 @@ from typing import Dict
 
 import numpy as np
 
-from rte_rrtmgp_cpp_b200.ctables import pack_kdist, pack_cloud, pack_strings, KDistFileC, CloudFileC
+from rte_rrtmgp_cpp_b200.ctables import pack_kdist, pack_cloud, pack_aerosol, pack_strings, KDistFileC, CloudFileC
 from rte_rrtmgp_cpp_b200.kdist import STRING_LEN
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -133,6 +133,21 @@ class RefGasOptics:
         _chk(lib().ref_cloud_add(self.h, C.byref(c), ncol, nlay, mode, int(do_delta), _p(lwp), _p(iwp),
                                  _p(rel), _p(dei), _p(tau), _p(ssa), _p(g), _p(ctau), _p(cssa), _p(cg)))
         return dict(tau=tau, ssa=ssa, g=g, ctau=ctau, cssa=cssa, cg=cg)
+
+    def aerosol_add(self, lut, do_delta, aermr, rh, plev, tau, ssa, g):
+        """Aerosol_optics + (delta_scale) + add_to on copies of the 2-stream gas props; returns dict."""
+        a, keep = pack_aerosol(lut)
+        rh, plev = _F(rh), _F(plev)
+        ncol, nlay = rh.shape
+        arrs = [_F(np.atleast_2d(aermr[f"aermr{i:02d}"])) for i in range(1, 12)]
+        ptrs = (c_dbl_p * 11)(*[_p(x) for x in arrs])
+        nc = (C.c_int * 11)(*[x.shape[0] for x in arrs]); nl = (C.c_int * 11)(*[x.shape[1] for x in arrs])
+        tau, ssa, g = (_F(x).copy(order="F") for x in (tau, ssa, g))
+        nb = lut.nbnd
+        atau = _z((ncol, nlay, nb)); assa = _z((ncol, nlay, nb)); ag = _z((ncol, nlay, nb))
+        _chk(lib().ref_aerosol_add(self.h, C.byref(a), ncol, nlay, int(do_delta), ptrs, nc, nl, _p(rh), _p(plev),
+                                   _p(tau), _p(ssa), _p(g), _p(atau), _p(assa), _p(ag)))
+        return dict(tau=tau, ssa=ssa, g=g, atau=atau, assa=assa, ag=ag)
 
     def fluxes_byband(self, up, dn, dr=None):
         up, dn = _F(up), _F(dn)

@@ -3,13 +3,14 @@
  *
  * Flat C entry points over the reference's OWN, UNMODIFIED C++ class layer
  * (/root/reference/src/{Gas_optics_rrtmgp,Optical_props,Rte_lw,Rte_sw,Fluxes,Source_functions,
- * Gas_concs,Cloud_optics}.cpp, compiled where they lie by oracle/Makefile into
+ * Gas_concs,Cloud_optics,Aerosol_optics}.cpp, compiled where they lie by oracle/Makefile into
  * oracle/_ref/liboracle_ref.so), linked over oracle/rrtmgp_kernels_restated.c in place of the
  * Fortran kernels that cannot be compiled here.  Construction follows what the reference's
  * driver does with the netCDF variables (src_test/Radiation_solver.cpp:70-284), using the same
  * Array dims.  Used to validate oracle/oracle.py's numpy restatement of the class layer.
  */
 #include <cstring>
+#include <cstdio>
 #include <memory>
 #include <string>
 #include <vector>
@@ -26,6 +27,7 @@
 #include "Rte_sw.h"
 #include "Fluxes.h"
 #include "Cloud_optics.h"
+#include "Aerosol_optics.h"
 
 #include "rrtmgp_b200_tables.h"
 #include "ref_kdist.hpp"
@@ -237,6 +239,51 @@ int ref_cloud_add(void* hv, const rrtmgp_b200_cloud_file* c, int ncol, int nlay,
         std::copy(gas.get_ssa().v().begin(), gas.get_ssa().v().end(), ssa);
         std::copy(gas.get_g().v().begin(), gas.get_g().v().end(), g);
     }
+    SHIM_CATCH
+}
+
+/* Aerosol_optics (src/Aerosol_optics.cpp) built like load_and_init_aerosol_optics
+ * (src_test/Radiation_solver.cpp:331-367) + optional delta_scale + add_to onto 2-stream gas props
+ * (src_test/Radiation_solver.cpp:770-786).  mmr[i] is aermr<i+1>, shape (mmr_ncol[i], mmr_nlay[i]).
+ * Returns the aerosol props (atau,assa,ag) and the incremented gas props in place. */
+int ref_aerosol_add(void* hv, const rrtmgp_b200_aerosol_file* a, int ncol, int nlay, int do_delta,
+                    const double* const* mmr, const int* mmr_ncol, const int* mmr_nlay,
+                    const double* rh, const double* plev,
+                    double* tau, double* ssa, double* g, double* atau, double* assa, double* ag)
+{
+    SHIM_TRY
+    auto* h = static_cast<Ref_gas_optics*>(hv);
+    const int ngpt = h->kdist->get_ngpt();
+    const int nb = a->n_band, nh = a->n_hum, nphil = a->n_philic, nphob = a->n_phobic;
+    const size_t n = (size_t)ncol * nlay * ngpt, nbn = (size_t)ncol * nlay * nb;
+    Array<Float,2> band_lims_wvn({2, nb});
+    Aerosol_optics ao(band_lims_wvn, arr<Float,1>(a->relative_humidity2, {nh}),
+                      arr<Float,2>(a->mass_ext_sw_hydrophobic, {nb, nphob}),
+                      arr<Float,2>(a->ssa_sw_hydrophobic, {nb, nphob}),
+                      arr<Float,2>(a->asymmetry_sw_hydrophobic, {nb, nphob}),
+                      arr<Float,3>(a->mass_ext_sw_hydrophilic, {nb, nh, nphil}),
+                      arr<Float,3>(a->ssa_sw_hydrophilic, {nb, nh, nphil}),
+                      arr<Float,3>(a->asymmetry_sw_hydrophilic, {nb, nh, nphil}));
+    Aerosol_concs ac;
+    for (int i = 0; i < 11; ++i)
+    {
+        char name[16]; snprintf(name, sizeof name, "aermr%02d", i + 1);
+        ac.set_vmr(name, arr<Float,2>(mmr[i], {mmr_ncol[i], mmr_nlay[i]}));
+    }
+    Optical_props_2str ae(ncol, nlay, ao);
+    ao.aerosol_optics(ac, arr<Float,2>(rh, {ncol, nlay}), arr<Float,2>(plev, {ncol, nlay + 1}), ae);
+    if (do_delta) ae.delta_scale();
+    std::copy(ae.get_tau().v().begin(), ae.get_tau().v().begin() + nbn, atau);
+    std::copy(ae.get_ssa().v().begin(), ae.get_ssa().v().begin() + nbn, assa);
+    std::copy(ae.get_g().v().begin(), ae.get_g().v().begin() + nbn, ag);
+    Optical_props_2str gas(ncol, nlay, *h->kdist);
+    gas.get_tau() = std::vector<Float>(tau, tau + n);
+    gas.get_ssa() = std::vector<Float>(ssa, ssa + n);
+    gas.get_g() = std::vector<Float>(g, g + n);
+    add_to(gas, ae);
+    std::copy(gas.get_tau().v().begin(), gas.get_tau().v().end(), tau);
+    std::copy(gas.get_ssa().v().begin(), gas.get_ssa().v().end(), ssa);
+    std::copy(gas.get_g().v().begin(), gas.get_g().v().end(), g);
     SHIM_CATCH
 }
 

@@ -7,6 +7,7 @@ Class and method names follow the reference's GPU twins (paths relative to the r
   Optical_props_{1scl,2str}_gpu, add_to   include/Optical_props.h:165-293
   Source_func_lw_gpu        include/Source_functions.h:70-93
   Cloud_optics_gpu          include/Cloud_optics.h
+  Aerosol_optics_gpu, Aerosol_concs_gpu   include/Aerosol_optics.h:20,48-84
   Rte_lw_gpu / Rte_sw_gpu   include/Rte_lw.h:62-77, include/Rte_sw.h:62-80
   Fluxes_broadband_gpu / Fluxes_byband_gpu  include/Fluxes.h:127-210
   Radiation_solver_{longwave,shortwave}.solve_gpu  src_test/Radiation_solver.cu:419-950 (fused)
@@ -25,8 +26,8 @@ import torch
 
 from . import capi
 from .capi import check, lib, F32, F64
-from .ctables import pack_kdist, pack_cloud, pack_strings
-from .kdist import KDistFile, CloudLUTFile, STRING_LEN
+from .ctables import pack_kdist, pack_cloud, pack_aerosol, pack_strings
+from .kdist import KDistFile, CloudLUTFile, AerosolLUTFile, STRING_LEN
 
 
 def _code(dtype: torch.dtype) -> int:
@@ -372,6 +373,48 @@ class Cloud_optics_gpu(Optical_props_gpu):
                                                       _ptr(optical_props.tau), _stream()))
 
 
+Aerosol_concs_gpu = Gas_concs_gpu          # include/Aerosol_optics.h:20
+AEROSOL_NAMES = tuple(f"aermr{i:02d}" for i in range(1, 12))
+
+
+def _pack_aerosol_concs(aerosol_concs: Gas_concs_gpu) -> capi.AerosolConcsC:
+    ac = capi.AerosolConcsC()
+    for i, name in enumerate(AEROSOL_NAMES):
+        if not aerosol_concs.exists(name):
+            raise RuntimeError(f"Aerosol_concs: {name} not set")
+        a = aerosol_concs.get_vmr(name)
+        ac.d_mmr[i], ac.mmr_ncol[i], ac.mmr_nlay[i] = a.ptr, a.dims[0], a.dims[1]
+    return ac
+
+
+class Aerosol_optics_gpu(Optical_props_gpu):
+    """include/Aerosol_optics.h:48-84; LUT aerosol optics by shortwave band (src_cuda/Aerosol_optics.cu:9-279,
+    CPU src/Aerosol_optics.cpp:10-224).  Like the reference's loader the band limits are left zero."""
+
+    def __init__(self, lut: AerosolLUTFile, dtype=torch.float64):
+        super().__init__(np.zeros((2, lut.nbnd)))
+        self.dtype = dtype
+        c, self._keep = pack_aerosol(lut)
+        self.h = C.c_void_p()
+        check(lib().rrtmgp_b200_aerosol_optics_create(C.byref(c), _code(dtype), C.byref(self.h)))
+
+    def __del__(self):
+        if getattr(self, "h", None) and self.h.value:
+            try:
+                lib().rrtmgp_b200_aerosol_optics_destroy(self.h)
+            except Exception:
+                pass
+            self.h = None
+
+    def aerosol_optics(self, aerosol_concs: Gas_concs_gpu, rh: Array_gpu, plev: Array_gpu, optical_props) -> None:
+        ncol, nlay = rh.dims
+        if optical_props.get_ngpt() != self.get_nband():
+            raise RuntimeError("aerosol_optics: optical_props must be by band")
+        ac = _pack_aerosol_concs(aerosol_concs)
+        check(lib().rrtmgp_b200_aerosol_optics_2str(self.h, ncol, nlay, C.byref(ac), _ptr(rh), _ptr(plev),
+                                                    _ptr(optical_props.tau), _ptr(optical_props.ssa), _ptr(optical_props.g), _stream()))
+
+
 class Rte_lw_gpu:
     @staticmethod
     def expand_and_transpose(ops: Optical_props_gpu, arr_in: Array_gpu) -> Array_gpu:
@@ -492,6 +535,10 @@ class DeviceColumns:
         self.emis_sfc, self.sfc_alb_dir, self.sfc_alb_dif = A(atm.emis_sfc), A(atm.sfc_alb_dir), A(atm.sfc_alb_dif)
         self.mu0, self.tsi_scaling = A(atm.mu0), A(atm.tsi_scaling)
         self.lwp, self.iwp, self.rel, self.dei = A(atm.lwp), A(atm.iwp), A(atm.rel), A(atm.dei)
+        self.rh = A(getattr(atm, "rh", None))
+        self.aerosol_concs = Aerosol_concs_gpu(dtype, device)
+        for k, v in (getattr(atm, "aermr", None) or {}).items():
+            self.aerosol_concs.set_vmr(k, v)
         self.col_dry = None
 
     def input_bytes(self) -> int:
@@ -499,7 +546,7 @@ class DeviceColumns:
         for v in vars(self).values():
             if isinstance(v, Array_gpu):
                 n += v.t.numel() * v.t.element_size()
-        for a in self.gas_concs.gas_concs_map.values():
+        for a in list(self.gas_concs.gas_concs_map.values()) + list(self.aerosol_concs.gas_concs_map.values()):
             n += a.t.numel() * a.t.element_size()
         return n
 
@@ -510,15 +557,18 @@ class _Radiation_solver:
     add_to] -> rte -> Fluxes::reduce in one C-ABI call, per-g-point arrays never leave the chip."""
     sw = False
 
-    def __init__(self, kdist: KDistFile, gas_concs, cloud_lut: Optional[CloudLUTFile] = None, dtype=torch.float64):
+    def __init__(self, kdist: KDistFile, gas_concs, cloud_lut: Optional[CloudLUTFile] = None, dtype=torch.float64,
+                 aerosol_lut: Optional[AerosolLUTFile] = None):
         self.dtype = dtype
         self.kdist = Gas_optics_rrtmgp_gpu(kdist, gas_concs, dtype)
         self.cloud = Cloud_optics_gpu(cloud_lut, dtype) if cloud_lut is not None else None
+        self.aerosol = Aerosol_optics_gpu(aerosol_lut, dtype) if aerosol_lut is not None else None
 
     def set_tile_columns(self, n: int) -> None:
         check(lib().rrtmgp_b200_set_tile_columns(self.kdist.h, int(n)))
 
-    def _pack(self, cols, out, switch_cloud_optics, switch_delta_cloud, switch_output_bnd_fluxes, heating, device):
+    def _pack(self, cols, out, switch_cloud_optics, switch_delta_cloud, switch_output_bnd_fluxes, heating, device,
+              switch_aerosol_optics=False, switch_delta_aerosol=False):
         """ColumnsC / FluxesC for `cols` (device or pinned-host resident), allocating outputs in `out`."""
         k = self.kdist
         ncol, nlay, nlev, nb = cols.ncol, cols.nlay, cols.nlay + 1, k.get_nband()
@@ -557,6 +607,15 @@ class _Radiation_solver:
             c.cloud = self.cloud.h
             c.delta_cloud = int(switch_delta_cloud)
             c.d_lwp, c.d_iwp, c.d_rel, c.d_dei = cols.lwp.ptr, cols.iwp.ptr, cols.rel.ptr, cols.dei.ptr
+        if switch_aerosol_optics:
+            if not self.sw:
+                raise RuntimeError("aerosol optics are shortwave only")
+            if self.aerosol is None or cols.rh is None:
+                raise RuntimeError("aerosol optics requested without an aerosol LUT / aerosol inputs")
+            c.aerosol = self.aerosol.h
+            c.delta_aerosol = int(switch_delta_aerosol)
+            c.d_rh = cols.rh.ptr
+            c.aerosol_concs = _pack_aerosol_concs(cols.aerosol_concs)
         c.n_gauss_angles = int(getattr(self, "n_gauss_angles", 1))
         c._keep = concs
         return c, f
@@ -566,10 +625,12 @@ class _Radiation_solver:
         check(lib().rrtmgp_b200_set_fused_path(self.kdist.h, int(path)))
 
     def solve_gpu(self, cols: DeviceColumns, switch_cloud_optics: bool = False, switch_delta_cloud: bool = True,
-                  switch_output_bnd_fluxes: bool = False, heating: bool = False, out: Optional[dict] = None) -> dict:
+                  switch_output_bnd_fluxes: bool = False, heating: bool = False, out: Optional[dict] = None,
+                  switch_aerosol_optics: bool = False, switch_delta_aerosol: bool = False) -> dict:
         if out is None:
             out = {}
-        c, f = self._pack(cols, out, switch_cloud_optics, switch_delta_cloud, switch_output_bnd_fluxes, heating, "cuda")
+        c, f = self._pack(cols, out, switch_cloud_optics, switch_delta_cloud, switch_output_bnd_fluxes, heating, "cuda",
+                          switch_aerosol_optics, switch_delta_aerosol)
         fn = lib().rrtmgp_b200_sw_fluxes if self.sw else lib().rrtmgp_b200_lw_fluxes
         check(fn(self.kdist.h, C.byref(c), C.byref(f), _stream()))
         return out
@@ -589,7 +650,7 @@ class HostColumns(DeviceColumns):
 
     def __init__(self, atm, dtype=torch.float64):
         super().__init__(atm, dtype, device="cpu")
-        for obj in (vars(self), self.gas_concs.gas_concs_map):
+        for obj in (vars(self), self.gas_concs.gas_concs_map, self.aerosol_concs.gas_concs_map):
             for v in obj.values():
                 if isinstance(v, Array_gpu):
                     v.t = v.t.pin_memory()
@@ -597,7 +658,8 @@ class HostColumns(DeviceColumns):
 
 def solve_host(lw: Optional[Radiation_solver_longwave], sw: Optional[Radiation_solver_shortwave], cols: HostColumns,
                switch_cloud_optics: bool = False, switch_delta_cloud: bool = True, switch_output_bnd_fluxes: bool = False,
-               heating: bool = False, out_lw: Optional[dict] = None, out_sw: Optional[dict] = None, chunk_columns: int = 0):
+               heating: bool = False, out_lw: Optional[dict] = None, out_sw: Optional[dict] = None, chunk_columns: int = 0,
+               switch_aerosol_optics: bool = False, switch_delta_aerosol: bool = False):
     """Host buffers in, host buffers out (rrtmgp_b200_fluxes_host): column chunks stream through
     H2D -> fused LW and SW -> D2H with the copies hidden behind the kernels.  Returns
     (out_lw, out_sw): dicts of pinned host Array_gpu objects.  Blocks until the outputs are ready."""
@@ -607,7 +669,8 @@ def solve_host(lw: Optional[Radiation_solver_longwave], sw: Optional[Radiation_s
     if lw is not None:
         cl, fl = lw._pack(cols, out_lw, switch_cloud_optics, switch_delta_cloud, switch_output_bnd_fluxes, heating, "cpu")
     if sw is not None:
-        cs, fs = sw._pack(cols, out_sw, switch_cloud_optics, switch_delta_cloud, switch_output_bnd_fluxes, heating, "cpu")
+        cs, fs = sw._pack(cols, out_sw, switch_cloud_optics, switch_delta_cloud, switch_output_bnd_fluxes, heating, "cpu",
+                          switch_aerosol_optics, switch_delta_aerosol)
     check(lib().rrtmgp_b200_fluxes_host(lw.kdist.h if lw else None, C.byref(cl) if cl else None, C.byref(fl) if fl else None,
                                         sw.kdist.h if sw else None, C.byref(cs) if cs else None, C.byref(fs) if fs else None,
                                         int(chunk_columns), _stream()))

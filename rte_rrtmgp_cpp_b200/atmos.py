@@ -34,6 +34,8 @@ class Atmosphere:
     iwp: Optional[np.ndarray] = None
     rel: Optional[np.ndarray] = None  # micron
     dei: Optional[np.ndarray] = None
+    rh: Optional[np.ndarray] = None   # (ncol, nlay) relative humidity 0..1 (aerosol optics)
+    aermr: Optional[Dict[str, np.ndarray]] = None   # "aermr01".."aermr11": (1,1), (1,nlay) or (ncol,nlay) kg/kg
 
     @property
     def ncol(self) -> int:
@@ -56,19 +58,22 @@ class Atmosphere:
             sl[axis] = slice(c0, c1)
             return np.asfortranarray(a[tuple(sl)])
         vmr = {k: (cut(v) if v.shape[0] > 1 else v) for k, v in self.vmr.items()}
+        aer = None if self.aermr is None else {k: (cut(v) if v.shape[0] > 1 else v) for k, v in self.aermr.items()}
         return Atmosphere(cut(self.play), cut(self.plev), cut(self.tlay), cut(self.tlev),
                           cut(self.tsfc), vmr, cut(self.emis_sfc, 1), cut(self.sfc_alb_dir, 1),
                           cut(self.sfc_alb_dif, 1), cut(self.mu0), cut(self.tsi_scaling),
-                          cut(self.lwp), cut(self.iwp), cut(self.rel), cut(self.dei))
+                          cut(self.lwp), cut(self.iwp), cut(self.rel), cut(self.dei), cut(self.rh), aer)
 
     def flipped(self) -> "Atmosphere":
         """Same columns with the vertical axis reversed (top_at_1 toggled)."""
         def fl(a):
             return None if a is None else np.asfortranarray(a[:, ::-1])
         vmr = {k: (np.asfortranarray(v[:, ::-1]) if v.shape[1] > 1 else v) for k, v in self.vmr.items()}
+        aer = None if self.aermr is None else {k: (np.asfortranarray(v[:, ::-1]) if v.shape[1] > 1 else v)
+                                               for k, v in self.aermr.items()}
         return Atmosphere(fl(self.play), fl(self.plev), fl(self.tlay), fl(self.tlev), self.tsfc,
                           vmr, self.emis_sfc, self.sfc_alb_dir, self.sfc_alb_dif, self.mu0,
-                          self.tsi_scaling, fl(self.lwp), fl(self.iwp), fl(self.rel), fl(self.dei))
+                          self.tsi_scaling, fl(self.lwp), fl(self.iwp), fl(self.rel), fl(self.dei), fl(self.rh), aer)
 
 
 def _rce_profile(z):
@@ -142,6 +147,29 @@ def rce_atmosphere(ncol: int, nlay: int = 128, seed: int = SEED, nbnd_lw: int = 
     if cloudy:
         _add_clouds(atm, rng)
     return atm.flipped() if top_at_1 else atm
+
+
+def add_aerosols(atm: Atmosphere, seed: int = SEED) -> Atmosphere:
+    """Relative humidity and the 11 aerosol mixing ratios (aermr01..11) for the columns of `atm`:
+    boundary-layer-weighted profiles of CAMS-like magnitude (1e-11..1e-8 kg/kg).  aermr02 is a (1,nlay)
+    profile and aermr10 a scalar so the broadcast of fill_aerosols_3d (src/Aerosol_optics.cpp:152-165) is
+    exercised; the rest are (ncol,nlay) fields."""
+    rng = np.random.default_rng(seed + 41)
+    ncol, nlay = atm.play.shape
+    sig = atm.play / np.max(atm.plev)                               # ~1 at the surface
+    shape = np.exp(-(1.0 - sig) * 6.0)
+    atm.rh = _F(np.clip(0.85 * sig ** 0.5 * rng.uniform(0.3, 1.15, (ncol, nlay)), 0.0, 0.99))
+    aer = {}
+    for i in range(1, 12):
+        amp = 10.0 ** rng.uniform(-10.5, -8.0)
+        f = amp * shape * rng.uniform(0.5, 1.5, (ncol, nlay))
+        if i == 2:
+            f = f[:1, :]
+        elif i == 10:
+            f = np.array([[amp * 0.3]])
+        aer[f"aermr{i:02d}"] = _F(f)
+    atm.aermr = aer
+    return atm
 
 
 def _add_clouds(atm: Atmosphere, rng) -> None:

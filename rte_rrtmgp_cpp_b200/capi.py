@@ -5,7 +5,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 
-from .ctables import KDistFileC, CloudFileC
+from .ctables import KDistFileC, CloudFileC, AerosolFileC
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RB200_LIB", os.path.join(_HERE, "librrtmgp_b200.so"))
@@ -26,13 +26,18 @@ class GasOpticsInfoC(C.Structure):
                 + [(n, C.c_double) for n in ("press_ref_min", "press_ref_max", "temp_ref_min", "temp_ref_max", "tsi")])
 
 
+class AerosolConcsC(C.Structure):
+    _fields_ = [("d_mmr", vp * 11), ("mmr_ncol", C.c_int * 11), ("mmr_nlay", C.c_int * 11)]
+
+
 class ColumnsC(C.Structure):
     _fields_ = [("ncol", C.c_int), ("nlay", C.c_int), ("top_at_1", C.c_int),
                 ("d_play", vp), ("d_plev", vp), ("d_tlay", vp), ("d_tlev", vp), ("d_tsfc", vp), ("d_col_dry", vp),
                 ("concs", GasConcsC),
                 ("d_sfc_emis", vp), ("d_sfc_alb_dir", vp), ("d_sfc_alb_dif", vp), ("d_mu0", vp), ("d_tsi_scaling", vp),
                 ("cloud", vp), ("delta_cloud", C.c_int),
-                ("d_lwp", vp), ("d_iwp", vp), ("d_rel", vp), ("d_dei", vp), ("n_gauss_angles", C.c_int)]
+                ("d_lwp", vp), ("d_iwp", vp), ("d_rel", vp), ("d_dei", vp), ("n_gauss_angles", C.c_int),
+                ("aerosol", vp), ("delta_aerosol", C.c_int), ("d_rh", vp), ("aerosol_concs", AerosolConcsC)]
 
 
 class FluxesC(C.Structure):
@@ -60,6 +65,10 @@ SYMBOLS = {
     "rrtmgp_b200_cloud_optics_nband": (i, [vp]),
     "rrtmgp_b200_cloud_optics_2str": (i, [vp, i, i, vp, vp, vp, vp, vp, vp, vp, vp]),
     "rrtmgp_b200_cloud_optics_1scl": (i, [vp, i, i, vp, vp, vp, vp, vp, vp]),
+    "rrtmgp_b200_aerosol_optics_create": (i, [C.POINTER(AerosolFileC), i, C.POINTER(vp)]),
+    "rrtmgp_b200_aerosol_optics_destroy": (None, [vp]),
+    "rrtmgp_b200_aerosol_optics_nband": (i, [vp]),
+    "rrtmgp_b200_aerosol_optics_2str": (i, [vp, i, i, C.POINTER(AerosolConcsC), vp, vp, vp, vp, vp, vp]),
     "rrtmgp_b200_delta_scale_2str": (i, [i, i, i, i, vp, vp, vp, vp]),
     "rrtmgp_b200_increment_1scl": (i, [i, i, i, i, vp, vp, vp]),
     "rrtmgp_b200_increment_2str": (i, [i, i, i, i, vp, vp, vp, vp, vp, vp, vp]),

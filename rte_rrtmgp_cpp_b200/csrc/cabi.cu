@@ -118,12 +118,42 @@ struct rrtmgp_b200_cloud_optics
     CloudDev<double> cd{};
 };
 
+struct rrtmgp_b200_aerosol_optics
+{
+    int dtype = 0;
+    DevBuf t[4];                    // rh_upper, mext, ssa, asy as [species][humidity class][band]
+    AerosolDev<float> af{};
+    AerosolDev<double> ad{};
+};
+
 template<typename Real> static const DevPlan<Real>& dplan(const rrtmgp_b200_gas_optics* g);
 template<> const DevPlan<float>& dplan<float>(const rrtmgp_b200_gas_optics* g) { return g->pf; }
 template<> const DevPlan<double>& dplan<double>(const rrtmgp_b200_gas_optics* g) { return g->pd; }
 template<typename Real> static const CloudDev<Real>& dcloud(const rrtmgp_b200_cloud_optics* c);
 template<> const CloudDev<float>& dcloud<float>(const rrtmgp_b200_cloud_optics* c) { return c->cf; }
 template<> const CloudDev<double>& dcloud<double>(const rrtmgp_b200_cloud_optics* c) { return c->cd; }
+template<typename Real> static const AerosolDev<Real>& daerosol(const rrtmgp_b200_aerosol_optics* a);
+template<> const AerosolDev<float>& daerosol<float>(const rrtmgp_b200_aerosol_optics* a) { return a->af; }
+template<> const AerosolDev<double>& daerosol<double>(const rrtmgp_b200_aerosol_optics* a) { return a->ad; }
+
+// aermr01..aermr11 of the caller -> the kernel's species order (summation order of src/Aerosol_optics.cpp:51:
+// SS1 SS2 SS3 DU1 DU2 DU3 OM1 OM2 BC1 BC2 SU; OM1 is aermr08 and OM2 aermr07, :131-142)
+static const int kAerosolMmrOfSpecies[AEROSOL_SPECIES] = {0, 1, 2, 3, 4, 5, 7, 6, 8, 9, 10};
+static AerosolMmr make_mmr(const rrtmgp_b200_aerosol_concs* ac, int ncol, int nlay)
+{
+    if (!ac) throw ArgError("aerosol optics: aerosol concentrations missing");
+    AerosolMmr m{};
+    for (int k = 0; k < AEROSOL_SPECIES; ++k)
+    {
+        const int i = kAerosolMmrOfSpecies[k];
+        char name[16]; snprintf(name, sizeof name, "aermr%02d", i + 1);
+        if (!ac->d_mmr[i]) throw MissingError(std::string("Aerosol_concs: ") + name + " not set");
+        if ((ac->mmr_ncol[i] != 1 && ac->mmr_ncol[i] != ncol) || (ac->mmr_nlay[i] != 1 && ac->mmr_nlay[i] != nlay))
+            throw ArgError(std::string("Aerosol_concs: ") + name + " must be a scalar, a (1,nlay) profile or an (ncol,nlay) field");
+        m.p[k] = ac->d_mmr[i]; m.ncol[k] = ac->mmr_ncol[i]; m.nlay[k] = ac->mmr_nlay[i];
+    }
+    return m;
+}
 
 template<typename Real>
 static void fill_devplan(rrtmgp_b200_gas_optics* g, DevPlan<Real>& P)
@@ -615,6 +645,59 @@ int rrtmgp_b200_cloud_optics_1scl(const rrtmgp_b200_cloud_optics* c, int ncol, i
     });
 }
 
+// ---- aerosol optics
+int rrtmgp_b200_aerosol_optics_create(const rrtmgp_b200_aerosol_file* lut, int dtype, rrtmgp_b200_aerosol_optics** out)
+{
+    if (!lut || !out) return fail(RRTMGP_B200_E_ARG, "aerosol_optics_create: null argument");
+    *out = nullptr;
+    std::unique_ptr<rrtmgp_b200_aerosol_optics> a(new rrtmgp_b200_aerosol_optics);
+    const int rc = guarded([&] {
+        if (dtype != RRTMGP_B200_F32 && dtype != RRTMGP_B200_F64) throw ArgError("bad dtype");
+        const int nb = lut->n_band, nh = lut->n_hum, nphil = lut->n_philic, nphob = lut->n_phobic;
+        // the reference addresses hydrophobic columns 1, 6, 8, 10, 11 and hydrophilic types 1..5 (src/Aerosol_optics.cpp:64-142)
+        if (nb < 1 || nh < 1 || nphil < 5 || nphob < 11) throw ArgError("aerosol LUT: bad dimensions (need >= 5 hydrophilic, >= 11 hydrophobic types)");
+        if (!lut->mass_ext_sw_hydrophobic || !lut->ssa_sw_hydrophobic || !lut->asymmetry_sw_hydrophobic || !lut->mass_ext_sw_hydrophilic ||
+            !lut->ssa_sw_hydrophilic || !lut->asymmetry_sw_hydrophilic || !lut->relative_humidity2) throw ArgError("aerosol LUT: null table");
+        a->dtype = dtype;
+        // species in kernel order; > 0: hydrophobic column (1-based), < 0: hydrophilic type (1-based)
+        static const int column[AEROSOL_SPECIES] = {-1, -2, -3, 1, 8, 6, 10, -4, 11, 11, -5};
+        const double* phob[3] = {lut->mass_ext_sw_hydrophobic, lut->ssa_sw_hydrophobic, lut->asymmetry_sw_hydrophobic};
+        const double* phil[3] = {lut->mass_ext_sw_hydrophilic, lut->ssa_sw_hydrophilic, lut->asymmetry_sw_hydrophilic};
+        std::vector<double> rh(lut->relative_humidity2, lut->relative_humidity2 + nh);
+        if (dtype == RRTMGP_B200_F32) a->t[0].upload_as<float>(rh); else a->t[0].upload_as<double>(rh);
+        for (int p = 0; p < 3; ++p)
+        {
+            std::vector<double> v((size_t)AEROSOL_SPECIES * nh * nb);
+            for (int k = 0; k < AEROSOL_SPECIES; ++k)
+                for (int ih = 0; ih < nh; ++ih)
+                    for (int b = 0; b < nb; ++b)
+                        v[((size_t)k * nh + ih) * nb + b] = column[k] > 0 ? phob[p][(size_t)(column[k] - 1) * nb + b]
+                                                                          : phil[p][((size_t)(-column[k] - 1) * nh + ih) * nb + b];
+            if (dtype == RRTMGP_B200_F32) a->t[1 + p].upload_as<float>(v); else a->t[1 + p].upload_as<double>(v);
+        }
+        a->af = AerosolDev<float>{nb, nh, (const float*)a->t[0].p, (const float*)a->t[1].p, (const float*)a->t[2].p, (const float*)a->t[3].p};
+        a->ad = AerosolDev<double>{nb, nh, (const double*)a->t[0].p, (const double*)a->t[1].p, (const double*)a->t[2].p, (const double*)a->t[3].p};
+    });
+    if (rc) return rc;
+    *out = a.release();
+    return 0;
+}
+void rrtmgp_b200_aerosol_optics_destroy(rrtmgp_b200_aerosol_optics* a) { if (a) { cudaDeviceSynchronize(); delete a; } }
+int rrtmgp_b200_aerosol_optics_nband(const rrtmgp_b200_aerosol_optics* a) { return a ? a->af.nbnd : -1; }
+
+int rrtmgp_b200_aerosol_optics_2str(const rrtmgp_b200_aerosol_optics* a, int ncol, int nlay, const rrtmgp_b200_aerosol_concs* concs,
+                                    const void* rh, const void* plev, void* tau, void* ssa, void* g, void* stream)
+{
+    return guarded([&] {
+        if (!a || !rh || !plev || !tau || !ssa || !g) throw ArgError("aerosol_optics: null argument");
+        check_dims(ncol, nlay);
+        const AerosolMmr m = make_mmr(concs, ncol, nlay);
+        DISPATCH(a->dtype,
+            launch_aerosol_optics<float>(a->af, m, false, ncol, 0, ncol, nlay, rh, plev, ncol, 0, 0, tau, ssa, g, (cudaStream_t)stream),
+            launch_aerosol_optics<double>(a->ad, m, false, ncol, 0, ncol, nlay, rh, plev, ncol, 0, 0, tau, ssa, g, (cudaStream_t)stream));
+    });
+}
+
 }  // extern "C"
 
 extern "C" {
@@ -806,6 +889,16 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
         if (cols->cloud->cf.nbnd != h.nbnd) throw ArgError("Cannot add optical properties with incompatible band - gpoint combination");
         if (!cols->d_lwp || !cols->d_iwp || !cols->d_rel || !cols->d_dei) throw ArgError("cloud inputs missing");
     }
+    const bool aerosol = cols->aerosol != nullptr;
+    AerosolMmr mmr{};
+    if (aerosol)
+    {
+        if (!sw) throw ArgError("lw_fluxes: aerosol optics are shortwave only (Radiation_solver_longwave has none)");
+        if (cols->aerosol->dtype != g->dtype) throw ArgError("aerosol optics object has a different precision");
+        if (cols->aerosol->af.nbnd != h.nbnd) throw ArgError("Cannot add optical properties with incompatible band - gpoint combination");
+        if (!cols->d_rh) throw ArgError("aerosol inputs missing: rh");
+        mmr = make_mmr(&cols->aerosol_concs, ncol, nlay);
+    }
     const bool bnd = out->d_bnd_flux_up != nullptr;
     if (bnd && !out->d_bnd_flux_dn) throw ArgError("by-band output needs both bnd_flux_up and bnd_flux_dn");
     const VmrArgs vmr = make_vmr(g, &cols->concs, ncol, nlay);
@@ -849,7 +942,7 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
     const size_t tcl = (size_t)tile * nlay, ncl = (size_t)ncol * nlay, ncv = (size_t)ncol * nlev;
     size_t need = state_bytes<Real>(h, tile, nlay) + pad256(fused_scratch_bytes<Real>(nslots, nlay, sw)) + pad256(nslots * sizeof(int)) + 4096;
     if (!cols->d_col_dry) need += pad256(ncl * sizeof(Real));
-    if (cloud) need += 3 * pad256(tcl * h.nbnd * sizeof(Real));
+    if (cloud || aerosol) need += 3 * pad256(tcl * h.nbnd * sizeof(Real));
     if (sw && !out->d_flux_dn_dir) need += pad256(ncv * sizeof(Real));
     if (sw && bnd && !out->d_bnd_flux_dn_dir) need += pad256(ncv * h.nbnd * sizeof(Real));
     g->ws.reserve(need, s);
@@ -879,7 +972,7 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
         col_dry = t;
     }
     Real *ctau = nullptr, *cssa = nullptr, *cg = nullptr;
-    if (cloud) { ctau = g->ws.take<Real>(tcl * h.nbnd); cssa = g->ws.take<Real>(tcl * h.nbnd); cg = g->ws.take<Real>(tcl * h.nbnd); }
+    if (cloud || aerosol) { ctau = g->ws.take<Real>(tcl * h.nbnd); cssa = g->ws.take<Real>(tcl * h.nbnd); cg = g->ws.take<Real>(tcl * h.nbnd); }
     if (sw && !a.flux_dir) a.flux_dir = g->ws.take<Real>(ncv);
     if (sw && bnd && !a.bnd_dir) a.bnd_dir = g->ws.take<Real>(ncv * h.nbnd);
 
@@ -902,6 +995,14 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
         {
             launch_cloud_optics<Real>(dcloud<Real>(cols->cloud), sw, ncol, c0, nc, nlay, cols->d_lwp, cols->d_iwp,
                                       cols->d_rel, cols->d_dei, nc, 0, sw && cols->delta_cloud, ctau, cssa, cg, s);
+            a.cld_tau = ctau; a.cld_ssa = cssa; a.cld_g = cg;
+        }
+        if (aerosol)
+        {
+            // the tile's by-band particulate properties = cloud (+) aerosol (increment is associative: tau, tau*ssa and
+            // tau*ssa*g add), so the band kernels still apply ONE by-band increment to the gas
+            launch_aerosol_optics<Real>(daerosol<Real>(cols->aerosol), mmr, cloud, ncol, c0, nc, nlay, cols->d_rh, cols->d_plev,
+                                        nc, 0, cols->delta_aerosol, ctau, cssa, cg, s);
             a.cld_tau = ctau; a.cld_ssa = cssa; a.cld_g = cg;
         }
         if (g_prof.on) { cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, s)); g_prof.ev[sw].push_back(e); }
@@ -1012,7 +1113,7 @@ void fluxes_host(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, co
     struct Side
     {
         rrtmgp_b200_gas_optics* g; const rrtmgp_b200_columns* c; const rrtmgp_b200_fluxes* o; bool sw;
-        int play, plev, tlay, tlev, tsfc, coldry, emis, adir, adif, mu0, tsi, lwp, iwp, rel, dei; std::vector<int> vmr;
+        int play, plev, tlay, tlev, tsfc, coldry, emis, adir, adif, mu0, tsi, lwp, iwp, rel, dei, rh, aer[11]; std::vector<int> vmr;
         std::vector<const void*> dv; std::vector<int> vnc, vnl;
     };
     std::vector<Side> sides;
@@ -1032,6 +1133,17 @@ void fluxes_host(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, co
         const bool cl = c->cloud != nullptr;
         sd.lwp = cl ? item(c->d_lwp, 0, nlay) : -1; sd.iwp = cl ? item(c->d_iwp, 0, nlay) : -1;
         sd.rel = cl ? item(c->d_rel, 0, nlay) : -1; sd.dei = cl ? item(c->d_dei, 0, nlay) : -1;
+        const bool ae = k == 1 && c->aerosol != nullptr;
+        sd.rh = ae ? item(c->d_rh, 0, nlay) : -1;
+        for (int i = 0; i < 11; ++i)
+        {
+            sd.aer[i] = -1;
+            if (!ae) continue;
+            const rrtmgp_b200_aerosol_concs& ac = c->aerosol_concs;
+            if (!ac.d_mmr[i]) throw MissingError("Aerosol_concs: aermr" + std::string(i < 9 ? "0" : "") + std::to_string(i + 1) + " not set");
+            const bool field = ac.mmr_ncol[i] == ncol && ncol > 1;
+            sd.aer[i] = item(ac.d_mmr[i], field ? 0 : 2, field ? (size_t)ac.mmr_nlay[i] : (size_t)ac.mmr_ncol[i] * ac.mmr_nlay[i]);
+        }
         const rrtmgp_b200_gas_concs& gc = c->concs;
         if (gc.ngas != g->h.ngas || !gc.d_vmr || !gc.vmr_ncol || !gc.vmr_nlay)
             throw ArgError("gas concentrations: need one entry per gas of the k-distribution object");
@@ -1101,6 +1213,13 @@ void fluxes_host(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, co
             dc.d_col_dry = D(sd.coldry); dc.d_sfc_emis = D(sd.emis); dc.d_sfc_alb_dir = D(sd.adir); dc.d_sfc_alb_dif = D(sd.adif);
             dc.d_mu0 = D(sd.mu0); dc.d_tsi_scaling = D(sd.tsi);
             dc.d_lwp = D(sd.lwp); dc.d_iwp = D(sd.iwp); dc.d_rel = D(sd.rel); dc.d_dei = D(sd.dei);
+            dc.d_rh = D(sd.rh);
+            for (int ai = 0; ai < 11; ++ai)
+                if (sd.aer[ai] >= 0)
+                {
+                    dc.aerosol_concs.d_mmr[ai] = D(sd.aer[ai]);
+                    dc.aerosol_concs.mmr_ncol[ai] = items[sd.aer[ai]].kind == 0 ? nc : sd.c->aerosol_concs.mmr_ncol[ai];
+                }
             for (size_t gi = 0; gi < sd.vmr.size(); ++gi)
             {
                 sd.dv[gi] = D(sd.vmr[gi]);

@@ -80,6 +80,86 @@ void launch_cloud_optics(const CloudDev<Real>& L, bool twostr, int ncol, int c0,
 }
 
 // ------------------------------------------------------------------------------------------
+// Aerosol optics: compute_all_from_table + combine (src/Aerosol_optics.cpp:40-224; CUDA twin
+// src_cuda/Aerosol_optics.cu:9-279).  One thread per (column, layer): the 11 mixing ratios, the
+// humidity class and the layer mass are fetched once and reused for every band (the reference's GPU
+// kernel re-reads them per band), the per-band stores are coalesced.  The look-up tables arrive as
+// one species-ordered block [species][humidity class][band] (hydrophobic rows replicated over the
+// classes), so every species is the same three loads.  MODE 0: write the aerosol properties;
+// MODE 1: increment the by-band properties already in (tau,ssa,g) (the tile's cloud properties) —
+// gas (+) cloud (+) aerosol is then one increment of the gas inside the band kernels.
+// ------------------------------------------------------------------------------------------
+template<typename Real, int MODE>
+__global__ void aerosol_optics_kernel(const AerosolDev<Real> A, const AerosolMmr mm, int ncol, int c0, int nc, int nlay,
+                                      const Real* __restrict__ rh, const Real* __restrict__ plev,
+                                      int nc_out, int c_out0, int delta,
+                                      Real* __restrict__ otau, Real* __restrict__ ossa, Real* __restrict__ og)
+{
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (size_t)nc * nlay) return;
+    const int c = (int)(idx % nc), l = (int)(idx / nc);
+    const size_t cgl = (size_t)(c0 + c);
+    const size_t i = cgl + (size_t)ncol * l;
+    // humidity class: first class whose upper bound is not below rh (src/Aerosol_optics.cpp:27-38)
+    const Real h = rh[i];
+    int ihum = 0;
+    while (ihum < A.nhum - 1 && A.rh_upper[ihum] < h) ++ihum;
+    const Real dpg = M<Real>::fabs(plev[i] - plev[i + ncol]) / (Real)9.81;
+    Real od[AEROSOL_SPECIES];
+#pragma unroll
+    for (int k = 0; k < AEROSOL_SPECIES; ++k)
+    {
+        const Real* m = (const Real*)mm.p[k];
+        const Real mmr = m[(mm.ncol[k] > 1 ? cgl : (size_t)0) + (mm.nlay[k] > 1 ? (size_t)mm.ncol[k] * l : (size_t)0)];
+        od[k] = mmr * dpg;
+    }
+    const size_t sstride = (size_t)A.nhum * A.nbnd;
+    const size_t cl_out = (size_t)nc_out * nlay;
+    size_t o = (size_t)(c_out0 + c) + (size_t)nc_out * l;
+    const Real* te = A.mext + (size_t)ihum * A.nbnd;
+    const Real* ts = A.ssa + (size_t)ihum * A.nbnd;
+    const Real* tg = A.asy + (size_t)ihum * A.nbnd;
+    for (int b = 0; b < A.nbnd; ++b, o += cl_out)
+    {
+        Real tau = 0, taussa = 0, taussag = 0;
+#pragma unroll
+        for (int k = 0; k < AEROSOL_SPECIES; ++k)
+        {
+            const Real local_od = od[k] * te[k * sstride + b];
+            const Real s = local_od * ts[k * sstride + b];
+            tau += local_od; taussa += s; taussag += s * tg[k * sstride + b];
+        }
+        Real t = tau;
+        Real w = taussa / M<Real>::max(tau, M<Real>::eps);
+        Real g = taussag / M<Real>::max(taussa, M<Real>::eps);
+        if (delta) delta_scale_cell(t, w, g);
+        if (MODE == 1)
+        {
+            Real t1 = otau[o], w1 = ossa[o], g1 = og[o];
+            increment_2str(t1, w1, g1, t, w, g);
+            t = t1; w = w1; g = g1;
+        }
+        otau[o] = t; ossa[o] = w; og[o] = g;
+    }
+}
+
+template<typename Real>
+void launch_aerosol_optics(const AerosolDev<Real>& A, const AerosolMmr& m, bool increment, int ncol, int c0, int nc, int nlay,
+                           const void* rh, const void* plev, int nc_out, int c_out0, int delta,
+                           void* tau, void* ssa, void* g, cudaStream_t s)
+{
+    const size_t n = (size_t)nc * nlay;
+    const unsigned grid = (unsigned)((n + 127) / 128);
+    if (increment)
+        aerosol_optics_kernel<Real, 1><<<grid, 128, 0, s>>>(A, m, ncol, c0, nc, nlay, (const Real*)rh, (const Real*)plev,
+                                                            nc_out, c_out0, delta, (Real*)tau, (Real*)ssa, (Real*)g);
+    else
+        aerosol_optics_kernel<Real, 0><<<grid, 128, 0, s>>>(A, m, ncol, c0, nc, nlay, (const Real*)rh, (const Real*)plev,
+                                                            nc_out, c_out0, delta, (Real*)tau, (Real*)ssa, (Real*)g);
+    count_launch();
+}
+
+// ------------------------------------------------------------------------------------------
 // Optical_props arithmetic (mo_optical_props_kernels.F90)
 // ------------------------------------------------------------------------------------------
 template<typename Real>
@@ -426,6 +506,7 @@ void launch_range_flag(size_t n, const void* x, double lo, double hi, int* d_fla
 
 #define INST(Real) \
     template void launch_cloud_optics<Real>(const CloudDev<Real>&, bool, int, int, int, int, const void*, const void*, const void*, const void*, int, int, int, void*, void*, void*, cudaStream_t); \
+    template void launch_aerosol_optics<Real>(const AerosolDev<Real>&, const AerosolMmr&, bool, int, int, int, int, const void*, const void*, int, int, int, void*, void*, void*, cudaStream_t); \
     template void launch_delta_scale<Real>(size_t, void*, void*, void*, cudaStream_t); \
     template void launch_increment<Real>(bool, size_t, int, const BandLims&, void*, void*, void*, const void*, const void*, const void*, cudaStream_t); \
     template void launch_expand<Real>(int, const BandLims&, const void*, void*, cudaStream_t); \

@@ -19,6 +19,19 @@ template<typename Real>
 void launch_cloud_optics(const CloudDev<Real>& L, bool twostr, int ncol, int c0, int nc, int nlay,
                          const void* lwp, const void* iwp, const void* rel, const void* dei,
                          int nc_out, int c_out0, int delta, void* tau, void* ssa, void* g, cudaStream_t s);
+// Aerosol look-up tables, species-ordered [species][humidity class][band]; species in the summation order of
+// src/Aerosol_optics.cpp:51 (SS1 SS2 SS3 DU1 DU2 DU3 OM1 OM2 BC1 BC2 SU)
+constexpr int AEROSOL_SPECIES = 11;
+template<typename Real> struct AerosolDev
+{
+    int nbnd, nhum;
+    const Real *rh_upper, *mext, *ssa, *asy;
+};
+struct AerosolMmr { const void* p[AEROSOL_SPECIES]; int ncol[AEROSOL_SPECIES]; int nlay[AEROSOL_SPECIES]; };   // in species order
+template<typename Real>
+void launch_aerosol_optics(const AerosolDev<Real>& A, const AerosolMmr& m, bool increment, int ncol, int c0, int nc, int nlay,
+                           const void* rh, const void* plev, int nc_out, int c_out0, int delta,
+                           void* tau, void* ssa, void* g, cudaStream_t s);
 template<typename Real> void launch_delta_scale(size_t n, void* tau, void* ssa, void* g, cudaStream_t s);
 template<typename Real>
 void launch_increment(bool twostr, size_t ncl, int ngpt, const BandLims& bl, void* tau1, void* ssa1, void* g1,

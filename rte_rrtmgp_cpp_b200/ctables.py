@@ -47,6 +47,13 @@ class CloudFileC(C.Structure):
                 ("lut_extice", c_dbl_p), ("lut_ssaice", c_dbl_p), ("lut_asyice", c_dbl_p)]
 
 
+class AerosolFileC(C.Structure):
+    _fields_ = [("n_band", C.c_int), ("n_hum", C.c_int), ("n_philic", C.c_int), ("n_phobic", C.c_int),
+                ("mass_ext_sw_hydrophobic", c_dbl_p), ("ssa_sw_hydrophobic", c_dbl_p), ("asymmetry_sw_hydrophobic", c_dbl_p),
+                ("mass_ext_sw_hydrophilic", c_dbl_p), ("ssa_sw_hydrophilic", c_dbl_p), ("asymmetry_sw_hydrophilic", c_dbl_p),
+                ("relative_humidity2", c_dbl_p)]
+
+
 def pack_strings(names: Sequence[str], length: int = STRING_LEN) -> bytes:
     """Blank-padded fixed-length block, as netCDF char arrays store strings."""
     return b"".join(s.encode("ascii")[:length].ljust(length, b" ") for s in names)
@@ -144,3 +151,14 @@ def pack_cloud(lut: CloudLUTFile):
     c.lut_asyliq = _d(lut.lut_asyliq, keep); c.lut_extice = _d(lut.lut_extice, keep)
     c.lut_ssaice = _d(lut.lut_ssaice, keep); c.lut_asyice = _d(lut.lut_asyice, keep)
     return c, keep
+
+
+def pack_aerosol(lut):
+    keep: List = []
+    a = AerosolFileC()
+    a.n_phobic, a.n_band = lut.mass_ext_sw_hydrophobic.shape
+    a.n_philic, a.n_hum, _ = lut.mass_ext_sw_hydrophilic.shape
+    for k in ("mass_ext_sw_hydrophobic", "ssa_sw_hydrophobic", "asymmetry_sw_hydrophobic", "mass_ext_sw_hydrophilic",
+              "ssa_sw_hydrophilic", "asymmetry_sw_hydrophilic", "relative_humidity2"):
+        setattr(a, k, _d(getattr(lut, k), keep))
+    return a, keep

@@ -353,3 +353,42 @@ def synthetic_cloud_lut(kind: str = "lw", seed: int = 20240607) -> CloudLUTFile:
     return CloudLUTFile(band_lims.copy(), 2.5, 21.5, 1.0, 10.0, 180.0, 1.0,
                         c(extliq), c(ssaliq), c(asyliq), c(extice), c(ssaice), c(asyice),
                         label=f"synthetic-cloud-lut-{kind}")
+
+
+@dataclass
+class AerosolLUTFile:
+    """Variables of aerosol_optics.nc in file dimension order
+    (/root/reference/src_test/Radiation_solver.cpp:331-367)."""
+    mass_ext_sw_hydrophobic: np.ndarray     # (hydrophobic, band_sw)
+    ssa_sw_hydrophobic: np.ndarray
+    asymmetry_sw_hydrophobic: np.ndarray
+    mass_ext_sw_hydrophilic: np.ndarray     # (hydrophilic, relative_humidity, band_sw)
+    ssa_sw_hydrophilic: np.ndarray
+    asymmetry_sw_hydrophilic: np.ndarray
+    relative_humidity2: np.ndarray          # (relative_humidity) upper bound of each class
+    label: str = "synthetic-aerosol-lut"
+
+    @property
+    def nbnd(self) -> int:
+        return int(self.mass_ext_sw_hydrophobic.shape[1])
+
+
+def synthetic_aerosol_lut(seed: int = 20240607, nband: int = 14) -> AerosolLUTFile:
+    """Aerosol LUT with the dimensions of the ECMWF/CAMS-style aerosol_optics.nc the reference reads
+    (14 shortwave bands, 12 humidity classes, 13 hydrophilic / 14 hydrophobic types): mass extinction in
+    m2/kg decreasing with wavelength, hydrophilic extinction growing with humidity, black carbon absorbing."""
+    rng = np.random.default_rng(seed + 29)
+    nhum, nphil, nphob = 12, 13, 14
+    rh_upper = np.array([0.1, 0.2, 0.3, 0.4, 0.5, 0.6, 0.7, 0.8, 0.85, 0.9, 0.95, 1.0])
+    wl = np.linspace(0.3, 1.0, nband)                              # relative spectral weight, band 1 = near-IR
+    mext_phob = 200.0 + 3000.0 * rng.uniform(0.2, 1.0, (nphob, 1)) * wl[None, :]
+    ssa_phob = np.clip(0.95 - 0.25 * rng.uniform(0, 1, (nphob, 1)) * (1.0 - wl[None, :]), 0.2, 0.999)
+    ssa_phob[10] = np.clip(0.15 + 0.2 * wl, 0.1, 0.5)              # black carbon (column 11)
+    asy_phob = np.clip(0.55 + 0.25 * rng.uniform(0, 1, (nphob, 1)) * wl[None, :], 0.1, 0.9)
+    growth = 1.0 + 4.0 * rh_upper ** 3
+    mext_phil = (300.0 + 4000.0 * rng.uniform(0.2, 1.0, (nphil, 1, 1)) * wl[None, None, :]) * growth[None, :, None]
+    ssa_phil = np.clip(0.90 + 0.099 * rh_upper[None, :, None] * np.ones((nphil, 1, nband))
+                       - 0.1 * rng.uniform(0, 1, (nphil, 1, 1)) * (1.0 - wl[None, None, :]), 0.5, 0.99999)
+    asy_phil = np.clip(0.6 + 0.18 * rh_upper[None, :, None] + 0.05 * rng.uniform(-1, 1, (nphil, 1, nband)), 0.1, 0.9)
+    c = np.ascontiguousarray
+    return AerosolLUTFile(c(mext_phob), c(ssa_phob), c(asy_phob), c(mext_phil), c(ssa_phil), c(asy_phil), rh_upper)

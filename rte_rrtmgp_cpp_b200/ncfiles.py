@@ -4,6 +4,7 @@ Writers for the three kinds of file the reference's executable reads and a reade
 writes, so that the command-line driver (cli/test_rte_rrtmgp.cpp) can be exercised end to end:
   coefficients_{lw,sw}.nc        <- KDistFile      (schema: src_test/Radiation_solver.cpp:78-243)
   cloud_coefficients_{lw,sw}.nc  <- CloudLUTFile   (schema: src_test/Radiation_solver.cpp:286-326)
+  aerosol_optics.nc              <- AerosolLUTFile (schema: src_test/Radiation_solver.cpp:331-367)
   rte_rrtmgp_input.nc            <- Atmosphere     (schema: src_test/test_rte_rrtmgp.cpp:205-330,455-478)
   rte_rrtmgp_output.nc           -> dict of numpy arrays (schema: :300-311,394-439,559-630)
 scipy.io.netcdf_file writes CDF-1/CDF-2 only; the real rrtmgp-data files are netCDF-4 and have to be
@@ -16,7 +17,7 @@ import numpy as np
 from scipy.io import netcdf_file
 
 from .atmos import Atmosphere
-from .kdist import CloudLUTFile, KDistFile, STRING_LEN
+from .kdist import AerosolLUTFile, CloudLUTFile, KDistFile, STRING_LEN
 
 
 def _dims(f, **sizes):
@@ -100,6 +101,19 @@ def write_cloud_lut(lut: CloudLUTFile, path: str) -> None:
     f.close()
 
 
+def write_aerosol_lut(lut: AerosolLUTFile, path: str) -> None:
+    f = netcdf_file(path, "w", version=2)
+    nphob, nb = lut.mass_ext_sw_hydrophobic.shape
+    nphil, nh, _ = lut.mass_ext_sw_hydrophilic.shape
+    _dims(f, band_sw=nb, relative_humidity=nh, hydrophilic=nphil, hydrophobic=nphob)
+    for n in ("mass_ext_sw_hydrophobic", "ssa_sw_hydrophobic", "asymmetry_sw_hydrophobic"):
+        _var(f, n, getattr(lut, n), ("hydrophobic", "band_sw"))
+    for n in ("mass_ext_sw_hydrophilic", "ssa_sw_hydrophilic", "asymmetry_sw_hydrophilic"):
+        _var(f, n, getattr(lut, n), ("hydrophilic", "relative_humidity", "band_sw"))
+    _var(f, "relative_humidity2", lut.relative_humidity2, ("relative_humidity",))
+    f.close()
+
+
 def write_input(atm: Atmosphere, path: str, nx: int, ny: int, kind: str = "f8", tsi_ref: float | None = None) -> None:
     """rte_rrtmgp_input.nc: fields as (lay|lev, y, x), surface fields as (y, x[, band]); x runs fastest
     over the columns.  With `tsi_ref` the per-column `tsi` variable is written (tsi_scaling * tsi_ref)."""
@@ -131,6 +145,14 @@ def write_input(atm: Atmosphere, path: str, nx: int, ny: int, kind: str = "f8", 
     if atm.lwp is not None:
         for n in ("lwp", "iwp", "rel", "dei"):
             field(n, getattr(atm, n), "lay")
+    if atm.rh is not None and atm.aermr is not None:      # src_test/test_rte_rrtmgp.cpp:274-293: (lay) or (lay, y, x)
+        field("rh", atm.rh, "lay")
+        for name, v in atm.aermr.items():
+            v = np.atleast_2d(np.asarray(v))
+            if v.shape[0] == 1:
+                _var(f, name, np.broadcast_to(v[0], (nlay,)), ("lay",), kind)
+            else:
+                field(name, v, "lay")
     f.close()
 
 

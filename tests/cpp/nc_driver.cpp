@@ -91,6 +91,25 @@ extern "C" int nc_cloud_equals(const char* path, const rrtmgp_b200_cloud_file* r
     catch (const std::exception& e) { g_err = e.what(); return -1; }
 }
 
+extern "C" int nc_aerosol_equals(const char* path, const rrtmgp_b200_aerosol_file* r)
+{
+    try
+    {
+        rrtmgp_b200::Aerosol_tables t(path);
+        const rrtmgp_b200_aerosol_file& f = t.file();
+        int k = 0;
+        CHECK(f.n_band == r->n_band); CHECK(f.n_hum == r->n_hum); CHECK(f.n_philic == r->n_philic); CHECK(f.n_phobic == r->n_phobic);
+        const size_t nb = (size_t)f.n_phobic * f.n_band, nl = (size_t)f.n_philic * f.n_hum * f.n_band;
+        CHECK(same(f.mass_ext_sw_hydrophobic, r->mass_ext_sw_hydrophobic, nb)); CHECK(same(f.ssa_sw_hydrophobic, r->ssa_sw_hydrophobic, nb));
+        CHECK(same(f.asymmetry_sw_hydrophobic, r->asymmetry_sw_hydrophobic, nb));
+        CHECK(same(f.mass_ext_sw_hydrophilic, r->mass_ext_sw_hydrophilic, nl)); CHECK(same(f.ssa_sw_hydrophilic, r->ssa_sw_hydrophilic, nl));
+        CHECK(same(f.asymmetry_sw_hydrophilic, r->asymmetry_sw_hydrophilic, nl));
+        CHECK(same(f.relative_humidity2, r->relative_humidity2, (size_t)f.n_hum));
+        return 0;
+    }
+    catch (const std::exception& e) { g_err = e.what(); return -1; }
+}
+
 // writer check: a file with one variable of each supported type, read back by scipy in the test
 extern "C" int nc_write_sample(const char* path, int nx, int nlev)
 {

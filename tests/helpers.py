@@ -22,7 +22,7 @@ def oracle_lw(kd, atm, cloud_lut=None, n_ang=1, col_dry=None):
     return fl
 
 
-def oracle_sw(kd, atm, cloud_lut=None, delta=True, col_dry=None):
+def oracle_sw(kd, atm, cloud_lut=None, delta=True, col_dry=None, aerosol_lut=None, delta_aerosol=False):
     go = O.GasOptics(kd, atm.vmr.keys())
     st = go.gas_optics_sw(atm.play, atm.plev, atm.tlay, atm.vmr, col_dry)
     tau, ssa, g = st["tau"], st["ssa"], st["g"]
@@ -32,6 +32,13 @@ def oracle_sw(kd, atm, cloud_lut=None, delta=True, col_dry=None):
         if delta:
             c = O.delta_scale(*c)
         tau, ssa, g = O.add_to_2str(go, tau, ssa, g, *c)
+    if aerosol_lut is not None:
+        # after the clouds, src_test/Radiation_solver.cpp:770-786; layer mass as the GPU twin takes it (|dp|),
+        # identical to the CPU source for bottom-up columns
+        a = O.AerosolOptics(aerosol_lut).aerosol_optics(atm.aermr, atm.rh, atm.plev, abs_dp=True)
+        if delta_aerosol:
+            a = O.delta_scale(*a)
+        tau, ssa, g = O.add_to_2str(go, tau, ssa, g, *a)
     toa = st["toa_src"] * np.asarray(atm.tsi_scaling)[:, None]
     up, dn, dr = O.rte_sw(go, tau, ssa, g, atm.mu0, toa, atm.sfc_alb_dir, atm.sfc_alb_dif, atm.top_at_1)
     fl = O.fluxes_byband(go, up, dn, dr)
@@ -50,7 +57,8 @@ def as_f32_valued(atm):
     a = copy.copy(atm)
     r = lambda x: None if x is None else np.asfortranarray(np.asarray(x, dtype=np.float32).astype(np.float64))
     for k in ("play", "plev", "tlay", "tlev", "tsfc", "emis_sfc", "sfc_alb_dir", "sfc_alb_dif", "mu0",
-              "tsi_scaling", "lwp", "iwp", "rel", "dei"):
+              "tsi_scaling", "lwp", "iwp", "rel", "dei", "rh"):
         setattr(a, k, r(getattr(atm, k)))
     a.vmr = {k: r(v) for k, v in atm.vmr.items()}
+    a.aermr = None if atm.aermr is None else {k: r(v) for k, v in atm.aermr.items()}
     return a

@@ -12,7 +12,8 @@ import torch
 
 from oracle import oracle as O
 from rte_rrtmgp_cpp_b200 import api, capi
-from rte_rrtmgp_cpp_b200.kdist import synthetic_kdist, synthetic_cloud_lut, REDUCED_LW_128, REDUCED_SW_112
+from rte_rrtmgp_cpp_b200.kdist import (synthetic_kdist, synthetic_cloud_lut, synthetic_aerosol_lut, REDUCED_LW_128,
+                                       REDUCED_SW_112)
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 GASES = ["h2o", "co2", "o3", "n2o", "ch4", "n2", "o2"]
@@ -89,3 +90,18 @@ def test_no_cpu_fallback_without_a_device():
     assert rc == capi.E_CUDA and b"no CPU fallback" in capi.lib().rrtmgp_b200_last_error()
     with pytest.raises(RuntimeError, match="(?i)cuda"):
         api.Cloud_optics_gpu(synthetic_cloud_lut("lw"))
+    with pytest.raises(RuntimeError, match="(?i)cuda"):
+        api.Aerosol_optics_gpu(synthetic_aerosol_lut())
+
+
+def test_aerosol_table_argument_errors_need_no_device():
+    """The reference addresses hydrophobic columns up to 11 and hydrophilic types up to 5
+    (src/Aerosol_optics.cpp:64-142): smaller tables are refused before anything touches the device."""
+    from rte_rrtmgp_cpp_b200.ctables import pack_aerosol
+    lut = synthetic_aerosol_lut()
+    lut.mass_ext_sw_hydrophobic = lut.mass_ext_sw_hydrophobic[:9]
+    a, keep = pack_aerosol(lut)
+    h = C.c_void_p()
+    rc = capi.lib().rrtmgp_b200_aerosol_optics_create(C.byref(a), capi.F64, C.byref(h))
+    assert rc == capi.E_ARG and b"hydrophobic" in capi.lib().rrtmgp_b200_last_error() and not h.value
+    assert capi.lib().rrtmgp_b200_aerosol_optics_nband(None) == -1

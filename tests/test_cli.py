@@ -16,8 +16,8 @@ import torch
 from scipy.io import netcdf_file
 
 from rte_rrtmgp_cpp_b200 import capi, ctables, ncfiles
-from rte_rrtmgp_cpp_b200.atmos import allsky_atmosphere, rce_atmosphere
-from rte_rrtmgp_cpp_b200.kdist import synthetic_cloud_lut, synthetic_kdist
+from rte_rrtmgp_cpp_b200.atmos import add_aerosols, allsky_atmosphere, rce_atmosphere
+from rte_rrtmgp_cpp_b200.kdist import synthetic_aerosol_lut, synthetic_cloud_lut, synthetic_kdist
 from helpers import oracle_lw, oracle_sw, as_f32_valued
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -57,6 +57,14 @@ def test_coefficient_files_load_identically(kind, tmp_path):
     assert rc == 0, (rc, d.nc_last_error())
     # a longwave file is not a cloud file: loud error, not garbage
     assert d.nc_cloud_equals(p.encode(), C.byref(cref)) == -1 and b"nband" in d.nc_last_error()
+    if kind == "sw":
+        alut = synthetic_aerosol_lut()
+        p3 = str(tmp_path / "aerosol_optics.nc")
+        ncfiles.write_aerosol_lut(alut, p3)
+        aref, keep3 = ctables.pack_aerosol(alut)
+        rc = d.nc_aerosol_equals(p3.encode(), C.byref(aref))
+        assert rc == 0, (rc, d.nc_last_error())
+        assert d.nc_aerosol_equals(p2.encode(), C.byref(aref)) == -1 and b"band_sw" in d.nc_last_error()
 
 
 def test_netcdf_writer_is_readable_by_scipy(tmp_path):
@@ -107,8 +115,7 @@ def test_cli_options_and_loud_failure(tmp_path):
     assert r.returncode == 1 and "EXCEPTION: frobnicate is an illegal command line option." in r.stdout
     r = subprocess.run([exe, "shortwave"], capture_output=True, text=True, cwd=tmp_path)
     assert r.returncode == 1 and "illegal command line option" in r.stdout
-    r = subprocess.run([exe, "--aerosol-optics"], capture_output=True, text=True, cwd=tmp_path)
-    assert r.returncode == 1 and "aerosol optics is not part of this build" in r.stdout
+    assert "--aerosol-optics" in subprocess.run([exe, "--help"], capture_output=True, text=True, cwd=tmp_path).stdout
     r = subprocess.run([exe], capture_output=True, text=True, cwd=tmp_path)        # no input file
     assert r.returncode == 1 and "cannot open rte_rrtmgp_input.nc" in r.stdout
     if not torch.cuda.is_available():
@@ -190,3 +197,31 @@ def test_cli_switches(tmp_path):
     assert r.returncode == 0, r.stdout
     out = ncfiles.read_output(str(tmp_path / "rte_rrtmgp_output.nc"))
     assert "lw_tau" in out and "lw_flux_up" not in out and "sw_tau" not in out
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("optical", [False, True])
+def test_cli_aerosol_optics(optical, tmp_path):
+    """--aerosol-optics [--delta-aerosol] with aerosol_optics.nc, rh and aermr01..11 in the input
+    (src_test/test_rte_rrtmgp.cpp:274-293): fused path, and with --output-optical the staged class path."""
+    atm = add_aerosols(rce_atmosphere(12, 20, cloudy=True))
+    atm.aermr["aermr10"] = np.broadcast_to(atm.aermr["aermr10"], (1, atm.nlay)).copy()   # the file contract has no scalar form
+    kl, ks, ll, ls = _stage(tmp_path, atm, 4, 3)
+    alut = synthetic_aerosol_lut()
+    ncfiles.write_aerosol_lut(alut, str(tmp_path / "aerosol_optics.nc"))
+    flags = ["--no-longwave", "--cloud-optics", "--aerosol-optics", "--delta-aerosol"] + (["--output-optical"] if optical else [])
+    r = subprocess.run([_exe("f64")] + flags, capture_output=True, text=True, cwd=tmp_path)
+    assert r.returncode == 0, r.stdout + r.stderr
+    out = ncfiles.read_output(str(tmp_path / "rte_rrtmgp_output.nc"))
+    ref = oracle_sw(ks, atm, ls, aerosol_lut=alut, delta_aerosol=True)
+    for k in ("flux_up", "flux_dn", "flux_dn_dir", "flux_net"):
+        assert np.abs(out["sw_" + k] - ref[k]).max() <= 1e-5, k
+    if optical:
+        for a, ko in ((ref["tau"], "sw_tau"), (ref["ssa"], "ssa"), (ref["g"], "g")):
+            assert np.allclose(out[ko], a, rtol=1e-10, atol=1e-12), ko
+    # a missing species is the reference's error
+    os.remove(tmp_path / "rte_rrtmgp_output.nc")
+    atm.aermr.pop("aermr05")
+    ncfiles.write_input(atm, str(tmp_path / "rte_rrtmgp_input.nc"), 4, 3)
+    r = subprocess.run([_exe("f64")] + flags, capture_output=True, text=True, cwd=tmp_path)
+    assert r.returncode == 1 and 'Aerosol type "aermr05" not available in input file.' in r.stdout

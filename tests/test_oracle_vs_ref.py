@@ -6,8 +6,9 @@ import pytest
 
 from oracle import oracle as O
 from oracle import ref as R
-from rte_rrtmgp_cpp_b200.atmos import rce_atmosphere, allsky_atmosphere
-from rte_rrtmgp_cpp_b200.kdist import synthetic_kdist, synthetic_cloud_lut, REDUCED_LW_128, REDUCED_SW_112
+from rte_rrtmgp_cpp_b200.atmos import rce_atmosphere, allsky_atmosphere, add_aerosols
+from rte_rrtmgp_cpp_b200.kdist import (synthetic_kdist, synthetic_cloud_lut, synthetic_aerosol_lut, REDUCED_LW_128,
+                                       REDUCED_SW_112)
 
 pytestmark = pytest.mark.skipif(not R.available(), reason="oracle/_ref/liboracle_ref.so not built")
 
@@ -92,6 +93,28 @@ def test_cloud_optics_delta_add_matches_reference_classes():
                     _eq(a, r[k], k)
                 for a, k in zip(t, ("tau", "ssa", "g")):
                     _eq(a, r[k], k + "+cloud")
+
+
+@pytest.mark.parametrize("top_at_1", [False, True])
+def test_aerosol_optics_delta_add_matches_reference_classes(top_at_1):
+    """Aerosol_optics::aerosol_optics (src/Aerosol_optics.cpp, compiled unmodified) -> delta_scale -> add_to.
+    top_at_1=True pins the CPU source's signed layer mass (negative optical depths, :53)."""
+    atm = add_aerosols(rce_atmosphere(11, 26, top_at_1=top_at_1))
+    kd = synthetic_kdist("sw"); lut = synthetic_aerosol_lut()
+    go = O.GasOptics(kd, atm.vmr.keys()); rf = R.RefGasOptics(kd, atm.vmr.keys())
+    ao = O.AerosolOptics(lut)
+    st = go.gas_optics_sw(atm.play, atm.plev, atm.tlay, atm.vmr)
+    for dl in (False, True):
+        a = ao.aerosol_optics(atm.aermr, atm.rh, atm.plev)
+        assert np.all(a[0] < 0) if top_at_1 else np.all(a[0] > 0)
+        if dl:
+            a = O.delta_scale(*a)
+        t = O.add_to_2str(go, st["tau"], st["ssa"], st["g"], *a)
+        r = rf.aerosol_add(lut, dl, atm.aermr, atm.rh, atm.plev, st["tau"], st["ssa"], st["g"])
+        for x, k in zip(a, ("atau", "assa", "ag")):
+            _eq(x, r[k], k)
+        for x, k in zip(t, ("tau", "ssa", "g")):
+            _eq(x, r[k], k + "+aerosol")
 
 
 def test_missing_key_gas_and_range_errors_match():
