@@ -74,6 +74,9 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     RawState<Real> nxt = load_state(st, P, B, tm, flav0, flav1, c, l, tcl);
     V2<Real> play_n = st.pl_lay[(size_t)c + (size_t)nc * l], plev_n = *plev_p;
     size_t o = o_top;
+#ifdef RB_UNROLL2
+#pragma unroll 2
+#endif
     for (int k = 0; k <= nlay; ++k)
     {
         Real pf[4] = {0, 0, 0, 0}, tau[4] = {0, 0, 0, 0};
@@ -82,15 +85,21 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
         const RawState<Real> cur = nxt;
         if (k < nlay)
         {
-            plev_p += tstep;
-            plev_n = *plev_p;
             const size_t icl = (size_t)c + (size_t)nc * l;
-            if (k + 1 < nlay)
+            auto prefetch = [&]()
             {
-                const int ln = top ? l + 1 : l - 1;
-                nxt = load_state(st, P, B, tm, flav0, flav1, c, ln, tcl);
-                play_n = st.pl_lay[(size_t)c + (size_t)nc * ln];
-            }
+                plev_p += tstep;
+                plev_n = *plev_p;
+                if (k + 1 < nlay)
+                {
+                    const int ln = top ? l + 1 : l - 1;
+                    nxt = load_state(st, P, B, tm, flav0, flav1, c, ln, tcl);
+                    play_n = st.pl_lay[(size_t)c + (size_t)nc * ln];
+                }
+            };
+#ifdef RB_PREFETCH_EARLY
+            prefetch();
+#endif
             Cell<Real> ce;
             decode_cell(cur.cell, cur.fa, cur.fb, ce);
             Real s0[4], s1[4], p0[4], p1[4];
@@ -98,6 +107,11 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
 #pragma unroll
             for (int j = 0; j < 4; ++j) { tau[j] = ce.cm0 * s0[j] + ce.cm1 * s1[j]; pf[j] = p0[j] + p1[j]; }
             add_minor_tau<G>(P, B, ce, q4, cur.sc0, cur.sc1, st.scal + icl, tcl, tau);
+#ifndef RB_PREFETCH_EARLY
+            // the next layer's state is requested AFTER the minor-gas loop: ptxas drains the scoreboard the
+            // prefetch loads share at that loop's header, so loads issued before it are waited for at once
+            prefetch();
+#endif
             if (CLOUD)
             {
                 const Real ct = a.cld_tau[icl + tcl * band];

@@ -96,16 +96,25 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     Real Ra[4] = {0, 0, 0, 0}, Sa[4] = {0, 0, 0, 0};
     RawState<Real> nxt = load_state(st, P, B, tm, flav0, flav1, c, top ? 0 : nlay - 1, tcl);
     size_t o = o_top;
+#ifdef RB_UNROLL2
+#pragma unroll 2
+#endif
     for (int k = 0; k < nlay; ++k)
     {
         const int l = top ? k : nlay - 1 - k;
         const size_t icl = (size_t)c + (size_t)nc * l;
         const RawState<Real> cur = nxt;
+#ifdef RB_PREFETCH_EARLY
         if (k + 1 < nlay) nxt = load_state(st, P, B, tm, flav0, flav1, c, top ? k + 1 : nlay - 2 - k, tcl);
+#endif
         Cell<Real> ce;
         decode_cell(cur.cell, cur.fa, cur.fb, ce);
         Real tau[4];
         gas_tau<G>(P, B, ce, kmaj, q4, cur.sc0, cur.sc1, st.scal + icl, tcl, tau);
+#ifndef RB_PREFETCH_EARLY
+        // requested after the minor-gas loop (see fused_lw.cu): the Rayleigh gather and the two-stream arithmetic cover it
+        if (k + 1 < nlay) nxt = load_state(st, P, B, tm, flav0, flav1, c, top ? k + 1 : nlay - 2 - k, tcl);
+#endif
         Real ray[4] = {0, 0, 0, 0};
         if (kray)
         {
@@ -158,6 +167,10 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     };
     V4<Real> bufA[6], bufB[6];
     ld6(bufA, nlay - 1);
+#ifndef RB_SW_RING2
+    V4<Real> bufC[6];
+    ld6(bufB, nlay - 2);
+#endif
     Real alb[4], src[4];
     {
         const Real adir = a.alb_dir[band + (size_t)P.nbnd * cg];
@@ -200,6 +213,20 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
             if (a.bnd_up) { a.bnd_up[o + nlev_stride * band] = su; a.bnd_dn[o + nlev_stride * band] = sd + a.bnd_dir[o + nlev_stride * band]; }
         }
     };
+#ifndef RB_SW_RING2
+    // three rotating buffers: two layers (192 B per thread) in flight while the third is consumed
+    for (int k0 = nlay - 1; k0 >= 0; k0 -= 3)
+    {
+        ld6(bufC, k0 - 2);
+        step(bufA);
+        if (k0 - 1 < 0) break;
+        ld6(bufA, k0 - 3);
+        step(bufB);
+        if (k0 - 2 < 0) break;
+        ld6(bufB, k0 - 4);
+        step(bufC);
+    }
+#else
     for (int k0 = nlay - 1; k0 >= 0; k0 -= 2)
     {
         ld6(bufB, k0 - 1);
@@ -208,6 +235,7 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
         ld6(bufA, k0 - 2);
         step(bufB);
     }
+#endif
     release_slot(a.slot_busy, slot);
 }
 
