@@ -68,38 +68,23 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
 
     // ---- down-sweep, top of atmosphere -> surface; layer k-1 is finalised at iteration k because
     // its lower level source needs the Planck fraction of layer k (F90:681-708).  State and
-    // Planck-table positions of the next layer are fetched one iteration ahead.
+    // Planck-table positions of the next layer are fetched one iteration ahead, INTO THE SAME VARIABLES and
+    // after their last use (the minor-gas loop): ptxas gives all these loads one scoreboard and drains it at
+    // that loop's header, and a separate current/next pair costs a register copy that waits for the loads at once.
     int l = top ? 0 : nlay - 1;                         // current layer, array order
     const V2<Real>* plev_p = st.pl_lev + (size_t)c + (size_t)nc * (top ? 0 : nlay);
-    RawState<Real> nxt = load_state(st, P, B, tm, flav0, flav1, c, l, tcl);
-    V2<Real> play_n = st.pl_lay[(size_t)c + (size_t)nc * l], plev_n = *plev_p;
+    RawState<Real> cur = load_state(st, P, B, tm, flav0, flav1, c, l, tcl);
+    V2<Real> play_c = st.pl_lay[(size_t)c + (size_t)nc * l], plev_c = *plev_p;
     size_t o = o_top;
-#ifdef RB_UNROLL2
-#pragma unroll 2
-#endif
     for (int k = 0; k <= nlay; ++k)
     {
         Real pf[4] = {0, 0, 0, 0}, tau[4] = {0, 0, 0, 0};
         Real blay = 0;
-        const V2<Real> play_c = play_n, plev_c = plev_n;
-        const RawState<Real> cur = nxt;
+        const Real blev = planck_at(plk, plev_c);
         if (k < nlay)
         {
             const size_t icl = (size_t)c + (size_t)nc * l;
-            auto prefetch = [&]()
-            {
-                plev_p += tstep;
-                plev_n = *plev_p;
-                if (k + 1 < nlay)
-                {
-                    const int ln = top ? l + 1 : l - 1;
-                    nxt = load_state(st, P, B, tm, flav0, flav1, c, ln, tcl);
-                    play_n = st.pl_lay[(size_t)c + (size_t)nc * ln];
-                }
-            };
-#ifdef RB_PREFETCH_EARLY
-            prefetch();
-#endif
+            blay = planck_at(plk, play_c);
             Cell<Real> ce;
             decode_cell(cur.cell, cur.fa, cur.fb, ce);
             Real s0[4], s1[4], p0[4], p1[4];
@@ -107,21 +92,22 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
 #pragma unroll
             for (int j = 0; j < 4; ++j) { tau[j] = ce.cm0 * s0[j] + ce.cm1 * s1[j]; pf[j] = p0[j] + p1[j]; }
             add_minor_tau<G>(P, B, ce, q4, cur.sc0, cur.sc1, st.scal + icl, tcl, tau);
-#ifndef RB_PREFETCH_EARLY
-            // the next layer's state is requested AFTER the minor-gas loop: ptxas drains the scoreboard the
-            // prefetch loads share at that loop's header, so loads issued before it are waited for at once
-            prefetch();
-#endif
+            plev_p += tstep;
+            plev_c = *plev_p;
+            if (k + 1 < nlay)
+            {
+                const int ln = top ? l + 1 : l - 1;
+                cur = load_state(st, P, B, tm, flav0, flav1, c, ln, tcl);
+                play_c = st.pl_lay[(size_t)c + (size_t)nc * ln];
+            }
             if (CLOUD)
             {
                 const Real ct = a.cld_tau[icl + tcl * band];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) tau[j] += ct;
             }
-            blay = planck_at(plk, play_c);
             l += top ? 1 : -1;
         }
-        const Real blev = planck_at(plk, plev_c);
         if (k == 0)
         {
 #pragma unroll

@@ -91,30 +91,21 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     // ---- pass 1: optics + two-stream + direct beam + adding of the stack ABOVE each level, top -> surface.
     // Ra(j) = diffuse reflectance of everything above level j seen from below, Sa(j) = downward diffuse
     // flux leaving that stack (driven by the direct-beam sources), Ra(0) = Sa(0) = 0.  The next layer's
-    // state is fetched one iteration ahead (its address does not depend on loaded data: the flavor
-    // comes from the column's tropopause bit mask).
+    // state is requested one iteration ahead (its address does not depend on loaded data: the flavor
+    // comes from the column's tropopause bit mask), into the same variable and after its last use (the
+    // minor-gas loop, see fused_lw.cu): the Rayleigh gather and the two-stream arithmetic cover the latency.
     Real Ra[4] = {0, 0, 0, 0}, Sa[4] = {0, 0, 0, 0};
-    RawState<Real> nxt = load_state(st, P, B, tm, flav0, flav1, c, top ? 0 : nlay - 1, tcl);
+    RawState<Real> cur = load_state(st, P, B, tm, flav0, flav1, c, top ? 0 : nlay - 1, tcl);
     size_t o = o_top;
-#ifdef RB_UNROLL2
-#pragma unroll 2
-#endif
     for (int k = 0; k < nlay; ++k)
     {
         const int l = top ? k : nlay - 1 - k;
         const size_t icl = (size_t)c + (size_t)nc * l;
-        const RawState<Real> cur = nxt;
-#ifdef RB_PREFETCH_EARLY
-        if (k + 1 < nlay) nxt = load_state(st, P, B, tm, flav0, flav1, c, top ? k + 1 : nlay - 2 - k, tcl);
-#endif
         Cell<Real> ce;
         decode_cell(cur.cell, cur.fa, cur.fb, ce);
         Real tau[4];
         gas_tau<G>(P, B, ce, kmaj, q4, cur.sc0, cur.sc1, st.scal + icl, tcl, tau);
-#ifndef RB_PREFETCH_EARLY
-        // requested after the minor-gas loop (see fused_lw.cu): the Rayleigh gather and the two-stream arithmetic cover it
-        if (k + 1 < nlay) nxt = load_state(st, P, B, tm, flav0, flav1, c, top ? k + 1 : nlay - 2 - k, tcl);
-#endif
+        if (k + 1 < nlay) cur = load_state(st, P, B, tm, flav0, flav1, c, top ? k + 1 : nlay - 2 - k, tcl);
         Real ray[4] = {0, 0, 0, 0};
         if (kray)
         {

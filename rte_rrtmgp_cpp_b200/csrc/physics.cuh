@@ -39,7 +39,9 @@ __device__ __forceinline__ void decode_cell(const V4<Real>& cell, const V4<Real>
     o.maj0 = r0 & 0xfffff; o.min0 = (r0 >> 20) & 0xfff;
     o.maj1 = r1 & 0xfffff; o.min1 = (r1 >> 20) & 0xfff;
     const Real fpress = cell.x, omf = (Real)1 - fpress;
-    o.wet = cell.y;
+    // cell.z is 0: the addition is exact, and it makes every lane of the 128-bit load READ here.  A lane nothing reads is
+    // handed to another value by ptxas while the load is still in flight, and that write waits for the whole prefetch.
+    o.wet = cell.y + cell.z;
     o.cm0 = fa.x; o.cm1 = fa.y;
     o.fm[0] = fa.z; o.fm[1] = fa.w; o.fm[2] = fb.x; o.fm[3] = fb.y;
     o.w[0] = omf * o.fm[0]; o.w[1] = omf * o.fm[1]; o.w[2] = fpress * o.fm[0]; o.w[3] = fpress * o.fm[1];
