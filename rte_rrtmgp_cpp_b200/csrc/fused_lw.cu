@@ -26,6 +26,12 @@ namespace rb200 {
 #ifndef RB_LW_MINB64
 #define RB_LW_MINB64 3
 #endif
+#ifndef RB_LW_PFS
+#define RB_LW_PFS 2             // down-sweep: layers beyond the register prefetch whose state lines are requested into L2 (0 = off)
+#endif
+#ifndef RB_LW_PF2
+#define RB_LW_PF2 12            // up-sweep: layers ahead of the consumed ones whose strip lines are requested into L2 (0 = off)
+#endif
 // resident CTAs per SM requested from ptxas: 5 (96 registers) for fp32, 3 (168 registers) for fp64 — measured best
 template<typename Real> struct LWMinBlocks { static constexpr int v = sizeof(Real) == 4 ? RB_LW_MINB : RB_LW_MINB64; };
 
@@ -76,6 +82,8 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     RawState<Real> cur = load_state(st, P, B, tm, flav0, flav1, c, l, tcl);
     V2<Real> play_c = st.pl_lay[(size_t)c + (size_t)nc * l], plev_c = *plev_p;
     size_t o = o_top;
+    StatePrefetch<Real, LPC, true> pfs;
+    if (RB_LW_PFS > 0) pfs.init(st, B, flav0, flav1, c, tcl);
     for (int k = 0; k <= nlay; ++k)
     {
         Real pf[4] = {0, 0, 0, 0}, tau[4] = {0, 0, 0, 0};
@@ -99,6 +107,13 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
                 const int ln = top ? l + 1 : l - 1;
                 cur = load_state(st, P, B, tm, flav0, flav1, c, ln, tcl);
                 play_c = st.pl_lay[(size_t)c + (size_t)nc * ln];
+            }
+            if (RB_LW_PFS > 0 && k + 1 + RB_LW_PFS < nlay)
+            {
+                // state of a layer further down goes to L2 now, so that the register prefetch of the next iteration
+                // is an L2 hit (the state arrays stream from DRAM once per band, ~1 us under load)
+                const int lp = top ? l + 1 + RB_LW_PFS : l - 1 - RB_LW_PFS;
+                pfs.layer(lp, layer_side(tm, lp));
             }
             if (CLOUD)
             {
@@ -189,14 +204,23 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
         }
     };
     {
+        // strip lines of the layers RB_LW_PF2 further up go to L2 while the current ones are consumed
+        auto pf4 = [&](int k0)
+        {
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (RB_LW_PF2 > 0 && k0 - u - RB_LW_PF2 >= 0) prefetch_strip_layer<Real, 2>(scr - tid, k0 - u - RB_LW_PF2);
+        };
         V4<Real> trA[4], suA[4], trB[4], suB[4];
         ld(trA, suA, nlay - 1);
         for (int k0 = nlay - 1; k0 >= 0; k0 -= 8)
         {
             ld(trB, suB, k0 - 4);
+            pf4(k0);
             sweep(trA, suA, k0);
             if (k0 - 4 < 0) break;
             ld(trA, suA, k0 - 8);
+            pf4(k0 - 4);
             sweep(trB, suB, k0 - 4);
         }
     }

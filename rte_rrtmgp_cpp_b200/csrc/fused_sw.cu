@@ -29,6 +29,13 @@ namespace rb200 {
 #ifndef RB_SW_MINB64
 #define RB_SW_MINB64 3
 #endif
+// L2 prefetch hints (see physics.cuh) measured slower in this DRAM-bound kernel (+1.4 %): off
+#ifndef RB_SW_PFS
+#define RB_SW_PFS 0
+#endif
+#ifndef RB_SW_PF2
+#define RB_SW_PF2 0
+#endif
 // resident CTAs per SM requested from ptxas: 5 (96 registers) for fp32, 3 (168 registers) for fp64 — measured best
 template<typename Real> struct SWMinBlocks { static constexpr int v = sizeof(Real) == 4 ? RB_SW_MINB : RB_SW_MINB64; };
 
@@ -97,6 +104,8 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     Real Ra[4] = {0, 0, 0, 0}, Sa[4] = {0, 0, 0, 0};
     RawState<Real> cur = load_state(st, P, B, tm, flav0, flav1, c, top ? 0 : nlay - 1, tcl);
     size_t o = o_top;
+    StatePrefetch<Real, LPC, false> pfs;
+    if (RB_SW_PFS > 0) pfs.init(st, B, flav0, flav1, c, tcl);
     for (int k = 0; k < nlay; ++k)
     {
         const int l = top ? k : nlay - 1 - k;
@@ -106,6 +115,11 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
         Real tau[4];
         gas_tau<G>(P, B, ce, kmaj, q4, cur.sc0, cur.sc1, st.scal + icl, tcl, tau);
         if (k + 1 < nlay) cur = load_state(st, P, B, tm, flav0, flav1, c, top ? k + 1 : nlay - 2 - k, tcl);
+        if (RB_SW_PFS > 0 && k + 1 + RB_SW_PFS < nlay)
+        {
+            const int lp = top ? k + 1 + RB_SW_PFS : nlay - 2 - k - RB_SW_PFS;      // to L2, see fused_lw.cu
+            pfs.layer(lp, layer_side(tm, lp));
+        }
         Real ray[4] = {0, 0, 0, 0};
         if (kray)
         {
@@ -181,8 +195,11 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
             if (a.bnd_up) { a.bnd_up[o + nlev_stride * band] = su; a.bnd_dn[o + nlev_stride * band] = sd + a.bnd_dir[o + nlev_stride * band]; }
         }
     }
+    int kpf = nlay - 1 - RB_SW_PF2;     // strip layer whose lines go to L2 while layer kpf + RB_SW_PF2 is consumed
     auto step = [&](const V4<Real> (&in)[6])
     {
+        if (RB_SW_PF2 > 0 && kpf >= 0) prefetch_strip_layer<Real, 6>(scr - tid, kpf);
+        --kpf;
         const Real* rdif = &in[0].x; const Real* tdif = &in[1].x; const Real* sup = &in[2].x; const Real* sdn = &in[3].x;
         const Real* ra = &in[4].x; const Real* sa = &in[5].x;
         Real fdn[4], fup[4];

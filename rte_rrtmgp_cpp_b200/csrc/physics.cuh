@@ -4,6 +4,7 @@
 // aligned 4-wide vector load.
 #pragma once
 #include "common.cuh"
+#include "launch.hpp"
 
 namespace rb200 {
 
@@ -79,6 +80,65 @@ __device__ __forceinline__ RawState<Real> load_state(const TileState<Real>& st, 
     r.fa = st.flvA[icl + tcl * f];
     r.fb = st.flvB[icl + tcl * f];
     return r;
+}
+
+// ---- L2 prefetch ("prefetch.global.L2": no register, no scoreboard) ------------------------------------------
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
+
+// The per-layer state of a warp's columns is one run of 32/LPC * sizeof(V4) bytes per array (a few 128-byte lines): lane i
+// of a warp requests ONE line of ONE array, so the whole warp prefetches a layer's state with a single instruction.
+// Arrays: cell, flvA, flvB, the band's first two scaling groups, and (longwave) the two Planck-position arrays.
+// Measured on B200 (1024^2 x 128): longwave (issue/latency-bound) -3 %, shortwave (DRAM-bound) +1.4 %, so it is on in the
+// longwave kernel only (RB_LW_PFS / RB_SW_PFS = layers ahead of the register prefetch, 0 = off).
+template<typename Real, int LPC, bool LW> struct StatePrefetch
+{
+    const char* base; unsigned lstep, off0, off1; bool on;           // layer step in units of 8 bytes, plane offsets in units of 16
+    __device__ __forceinline__ void init(const TileState<Real>& st, const BandArgs& B, int flav0, int flav1, int c, size_t tcl)
+    {
+        constexpr int LINES = (32 / LPC) * (int)sizeof(V4<Real>) / 128;       // lines per array per warp (V4 arrays)
+        static_assert(LINES >= 1, "a warp's state run must be at least one line");
+        constexpr int NARR = LW ? 7 : 5;
+        constexpr unsigned U4 = sizeof(V4<Real>) / 8, U2 = sizeof(V2<Real>) / 8;
+        const int lane = threadIdx.x & 31, arr = lane / LINES, sub = lane % LINES;
+        on = arr < NARR;
+        const size_t csh = (size_t)(c - (c % (32 / LPC)));                    // the warp's first column
+        lstep = (unsigned)st.nc * U4; off0 = off1 = 0;
+        const unsigned t = (unsigned)tcl * (U4 / 2);
+        if ((size_t)tcl * (U4 / 2) * (size_t)(arr < 3 ? max(flav0, flav1) : max(B.scal_off[0], B.scal_off[1]) + 1) > 0xffffffffull) on = false;
+        switch (arr)
+        {
+        case 0: base = (const char*)(st.cell + csh); break;
+        case 1: base = (const char*)(st.flvA + csh); off0 = t * flav0; off1 = t * flav1; break;
+        case 2: base = (const char*)(st.flvB + csh); off0 = t * flav0; off1 = t * flav1; break;
+        case 3: base = (const char*)(st.scal + csh); off0 = t * B.scal_off[0]; off1 = t * B.scal_off[1]; break;
+        case 4: base = (const char*)(st.scal + csh);
+                off0 = t * (B.scal_off[0] + (B.nminor[0] > 4 ? 1 : 0)); off1 = t * (B.scal_off[1] + (B.nminor[1] > 4 ? 1 : 0)); break;
+        case 5: base = (const char*)(st.pl_lay + csh); lstep = (unsigned)st.nc * U2; on = on && 2 * sub < LINES + 1; break;
+        case 6: base = (const char*)(st.pl_lev + csh); lstep = (unsigned)st.nc * U2; on = on && 2 * sub < LINES + 1; break;
+        default: base = (const char*)st.cell; break;
+        }
+        base += (size_t)sub * 128;
+    }
+    // layer l of the tile (array order); `side` = 0 lower / 1 upper atmosphere of that layer
+    __device__ __forceinline__ void layer(int l, int side) const
+    {
+        if (on) prefetch_l2(base + ((size_t)((unsigned)l * lstep) << 3) + ((size_t)(side ? off1 : off0) << 4));
+    }
+};
+
+// scratch strip of a CTA: layer k is W*T vectors = W*T*sizeof(V4)/128 lines; thread t requests lines t, t+T, ...
+template<typename Real, int W>
+__device__ __forceinline__ void prefetch_strip_layer(const V4<Real>* strip_thread0, int k)
+{
+    constexpr int T = FUSED_THREADS;
+    constexpr int LINES = W * T * (int)sizeof(V4<Real>) / 128;
+    const char* p = (const char*)(strip_thread0 + (size_t)k * W * T);
+#pragma unroll
+    for (int i = 0; i < (LINES + T - 1) / T; ++i)
+    {
+        const int line = (int)threadIdx.x + i * T;
+        if (line < LINES) prefetch_l2(p + (size_t)line * 128);
+    }
 }
 
 #define RB_FMA4(acc, s, v) { acc[0] = fma(s, v.x, acc[0]); acc[1] = fma(s, v.y, acc[1]); acc[2] = fma(s, v.z, acc[2]); acc[3] = fma(s, v.w, acc[3]); }
