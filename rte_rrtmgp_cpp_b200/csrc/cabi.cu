@@ -261,6 +261,7 @@ int rrtmgp_b200_gas_optics_create(const rrtmgp_b200_kdist_file* kd, int n_avail,
                 B.nminor[s] = (int)lst.size();
                 B.first_minor[s] = lst.empty() ? 0 : h.minor[s].desc[lst[0]].contributor;
                 B.scal_off[s] = h.minor[s].scal_off[b] / 4;
+                B.flav[s] = h.band_flavor[s + 2 * b];
                 for (size_t m = 0; m < lst.size(); ++m)
                     if (h.minor[s].desc[lst[m]].idx_minor < 0) throw ArgError("internal: minor gas index");
             }

@@ -172,6 +172,7 @@ struct BandArgs
     int nminor[2];
     int first_minor[2];      // device block index of the band's first contributor (blocks are consecutive)
     int scal_off[2];         // first group (V4 plane) of the band's contributors in TileState::scal
+    int flav[2];             // 0-based flavor of the band per side (= DevPlan::band_flavor)
 };
 
 }  // namespace rb200

@@ -37,9 +37,10 @@ template<typename Real> struct LWMinBlocks { static constexpr int v = sizeof(Rea
 
 template<typename Real, int LPC, int GWT, bool CLOUD, int NE>
 __global__ void __launch_bounds__(FUSED_THREADS, LWMinBlocks<Real>::v)
-lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const TileState<Real> st,
+lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandLaunch<Real> L, const TileState<Real> st,
                const FusedArgs<Real> a)
 {
+    const BandArgs& B = L.B;
     using G = Geo<GWT, NE, true>;      // table rows are GWT wide; LPC lanes cover this band's (<= 4*LPC) g-points
     constexpr int CPB = FUSED_THREADS / LPC;
     constexpr int T = FUSED_THREADS;
@@ -49,24 +50,23 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     const bool active = craw < a.nc;
     const int c = active ? craw : a.nc - 1;
     const int nlay = a.nlay, nc = a.nc;
-    const size_t tcl = (size_t)nc * nlay;
+    const size_t tcl = L.tcl;
     const size_t cg = (size_t)a.c0 + c;                 // column in the caller's arrays
     const int q4 = q * 4;
     const int band = B.band;
-    const size_t band_elems = (size_t)P.ntemp * (P.npres + 1) * G::neta(P) * G::RS;
-    const Real* kmaj = P.kmajor + band_elems * band + q4;
-    const Real* plk = P.totplnk + (size_t)P.nplanck * band;
-    const int flav0 = P.band_flavor[2 * band], flav1 = P.band_flavor[2 * band + 1];
+    const Real* kmaj = L.kmaj + q4;
+    const Real* plk = L.plk;
+    const int flav0 = B.flav[0], flav1 = B.flav[1];
     const unsigned* tm = st.tmask + (size_t)c * TMASK_WORDS;
     const int slot = claim_slot(a.slot_busy, a.nslots);
-    V4<Real>* const scr = a.scratch + (size_t)slot * nlay * 2 * T + tid;
+    V4<Real>* const scr = a.scratch + (size_t)slot * L.strip + tid;
     const Real piw = (Real)3.14159265358979323846 * a.weight;
     const bool lead = active && q == 0;
-    const size_t nlev_stride = (size_t)a.ncol * (nlay + 1);
+    const size_t nlev_stride = L.nlev_stride;
     const int top = a.top_at_1;
-    const long lstep = top ? (long)a.ncol : -(long)a.ncol;
+    const long lstep = L.lstep;
     const int tstep = top ? nc : -nc;                                          // same, tile arrays
-    const size_t o_top = cg + (top ? (size_t)0 : (size_t)a.ncol * nlay);       // level index * ncol
+    const size_t o_top = cg + L.o_top;                                         // level index * ncol
 
     Real radn[4] = {0, 0, 0, 0};        // incident diffuse flux = 0 (Radiation_solver.cu passes zeros)
     Real pf_prev[4] = {0, 0, 0, 0}, tau_prev[4] = {0, 0, 0, 0}, lev_top[4] = {0, 0, 0, 0};
@@ -79,7 +79,7 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     // that loop's header, and a separate current/next pair costs a register copy that waits for the loads at once.
     int l = top ? 0 : nlay - 1;                         // current layer, array order
     const V2<Real>* plev_p = st.pl_lev + (size_t)c + (size_t)nc * (top ? 0 : nlay);
-    RawState<Real> cur = load_state(st, P, B, tm, flav0, flav1, c, l, tcl);
+    RawState<Real> cur = load_state(st, L, tm, c, l);
     V2<Real> play_c = st.pl_lay[(size_t)c + (size_t)nc * l], plev_c = *plev_p;
     size_t o = o_top;
     StatePrefetch<Real, LPC, true> pfs;
@@ -99,13 +99,19 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
             interp_major_pair<G>(kmaj, P, ce, s0, s1, p0, p1);
 #pragma unroll
             for (int j = 0; j < 4; ++j) { tau[j] = ce.cm0 * s0[j] + ce.cm1 * s1[j]; pf[j] = p0[j] + p1[j]; }
-            add_minor_tau<G>(P, B, ce, q4, cur.sc0, cur.sc1, st.scal + icl, tcl, tau);
+            add_minor_tau<G>(L, ce, q4, cur.sc0, cur.sc1, st.scal + icl, tau);
+            if (CLOUD)          // before the prefetch below: a load consumed after it would wait for the prefetch too
+            {
+                const Real ct = a.cld_tau[icl + tcl * band];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) tau[j] += ct;
+            }
             plev_p += tstep;
             plev_c = *plev_p;
             if (k + 1 < nlay)
             {
                 const int ln = top ? l + 1 : l - 1;
-                cur = load_state(st, P, B, tm, flav0, flav1, c, ln, tcl);
+                cur = load_state(st, L, tm, c, ln);
                 play_c = st.pl_lay[(size_t)c + (size_t)nc * ln];
             }
             if (RB_LW_PFS > 0 && k + 1 + RB_LW_PFS < nlay)
@@ -114,12 +120,6 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
                 // is an L2 hit (the state arrays stream from DRAM once per band, ~1 us under load)
                 const int lp = top ? l + 1 + RB_LW_PFS : l - 1 - RB_LW_PFS;
                 pfs.layer(lp, layer_side(tm, lp));
-            }
-            if (CLOUD)
-            {
-                const Real ct = a.cld_tau[icl + tcl * band];
-#pragma unroll
-                for (int j = 0; j < 4; ++j) tau[j] += ct;
             }
             l += top ? 1 : -1;
         }
@@ -241,7 +241,8 @@ void launch_lw_band(const DevPlan<Real>& P, const BandArgs& B, const TileState<R
     const int lpc = (P.gw == 16 && B.ngb <= 8) ? 2 : P.gw / 4, cpb = FUSED_THREADS / lpc;
     const unsigned grid = (unsigned)((a.nc + cpb - 1) / cpb);
     const bool cloud = a.cld_tau != nullptr;
-#define RB_LAUNCH(LPC_, GW_, CL_, NE_) lw_band_kernel<Real, LPC_, GW_, CL_, NE_><<<grid, FUSED_THREADS, 0, s>>>(P, B, st, a)
+    const BandLaunch<Real> L = make_band_launch<Real>(P, B, a, B.flav[0], B.flav[1], true, 2);
+#define RB_LAUNCH(LPC_, GW_, CL_, NE_) lw_band_kernel<Real, LPC_, GW_, CL_, NE_><<<grid, FUSED_THREADS, 0, s>>>(P, L, st, a)
 #define RB_NE(LPC_, GW_, CL_) { if (P.neta == 9) RB_LAUNCH(LPC_, GW_, CL_, 9); else RB_LAUNCH(LPC_, GW_, CL_, 0); }
 #define RB_CL(LPC_, GW_) { if (cloud) RB_NE(LPC_, GW_, true) else RB_NE(LPC_, GW_, false) }
     if (P.gw == 16) { if (lpc == 4) RB_CL(4, 16) else RB_CL(2, 16) }

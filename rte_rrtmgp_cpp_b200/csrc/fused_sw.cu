@@ -49,9 +49,10 @@ template<typename Real> struct SWMinBlocks { static constexpr int v = sizeof(Rea
 
 template<typename Real, int LPC, int GWT, bool CLOUD, int NE>
 __global__ void __launch_bounds__(FUSED_THREADS, SWMinBlocks<Real>::v)
-sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const TileState<Real> st,
+sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandLaunch<Real> L, const TileState<Real> st,
                const FusedArgs<Real> a)
 {
+    const BandArgs& B = L.B;
     using G = Geo<GWT, NE, false>;      // table rows are GWT wide; LPC lanes cover this band's (<= 4*LPC) g-points
     constexpr int CPB = FUSED_THREADS / LPC;
     constexpr int T = FUSED_THREADS;
@@ -61,25 +62,21 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     const bool active = craw < a.nc;
     const int c = active ? craw : a.nc - 1;
     const int nlay = a.nlay, nc = a.nc;
-    const size_t tcl = (size_t)nc * nlay;
+    const size_t tcl = L.tcl;
     const size_t cg = (size_t)a.c0 + c;
     const int q4 = q * 4;
     const int band = B.band;
-    const size_t band_elems = (size_t)P.ntemp * (P.npres + 1) * G::neta(P) * G::RS;
-    const size_t ray_elems = (size_t)P.ntemp * G::neta(P) * G::GW;
-    const Real* kmaj = P.kmajor + band_elems * band + q4;
-    const Real* kray = P.krayl ? P.krayl + ray_elems * band + q4 : nullptr;
-    const size_t ray_side = ray_elems * P.nbnd;
-    const int flav0 = P.band_flavor[2 * band], flav1 = P.band_flavor[2 * band + 1];
+    const Real* kmaj = L.kmaj + q4;
+    const int flav0 = B.flav[0], flav1 = B.flav[1];
     const unsigned* tm = st.tmask + (size_t)c * TMASK_WORDS;
     const int slot = claim_slot(a.slot_busy, a.nslots);
-    V4<Real>* const scr = a.scratch + (size_t)slot * nlay * 6 * T + tid;
+    V4<Real>* const scr = a.scratch + (size_t)slot * L.strip + tid;
     const bool lead = active && q == 0;
-    const size_t nlev_stride = (size_t)a.ncol * (nlay + 1);
+    const size_t nlev_stride = L.nlev_stride;
     const int top = a.top_at_1;
     // level j / layer k counted from the top of the atmosphere -> array index, times ncol
-    const long lstep = top ? (long)a.ncol : -(long)a.ncol;
-    const size_t o_top = cg + (top ? (size_t)0 : (size_t)a.ncol * nlay);
+    const long lstep = L.lstep;
+    const size_t o_top = cg + L.o_top;
 
     const Real mu0 = a.mu0[cg];
     const Real mu0s = M<Real>::max(M<Real>::sqrt(M<Real>::eps), mu0);
@@ -110,7 +107,7 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
     // comes from the column's tropopause bit mask), into the same variable and after its last use (the
     // minor-gas loop, see fused_lw.cu): the Rayleigh gather and the two-stream arithmetic cover the latency.
     Real Ra[4] = {0, 0, 0, 0}, Sa[4] = {0, 0, 0, 0};
-    RawState<Real> cur = load_state(st, P, B, tm, flav0, flav1, c, top ? 0 : nlay - 1, tcl);
+    RawState<Real> cur = load_state(st, L, tm, c, top ? 0 : nlay - 1);
     size_t o = o_top;
     StatePrefetch<Real, LPC, false> pfs;
     if (RB_SW_PFS > 0) pfs.init(st, B, flav0, flav1, c, tcl);
@@ -121,30 +118,48 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandArgs B, const 
         Cell<Real> ce;
         decode_cell(cur.cell, cur.fa, cur.fb, ce);
         Real tau[4];
-        gas_tau<G>(P, B, ce, kmaj, q4, cur.sc0, cur.sc1, st.scal + icl, tcl, tau);
-        if (k + 1 < nlay) cur = load_state(st, P, B, tm, flav0, flav1, c, top ? k + 1 : nlay - 2 - k, tcl);
+        {
+            Real s0[4], s1[4];
+            interp_major<G>(kmaj, P, ce, s0, s1);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) tau[j] = ce.cm0 * s0[j] + ce.cm1 * s1[j];
+            add_minor_tau<G>(L, ce, q4, cur.sc0, cur.sc1, st.scal + icl, tau);
+        }
+        Real ray[4] = {0, 0, 0, 0};
+        if (L.kray[0])
+        {
+            interp_minor<G>(L.kray[ce.side] + q4, ce, ray);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) ray[j] *= ce.wet;
+        }
+        // optical properties of the 4 g-points: gas + Rayleigh (+ by-band cloud/aerosol increment)
+        Real tt[4], ww[4], gg[4];
+        {
+            Real ct = 0, cs = 0, cgg = 0;
+            if (CLOUD) { ct = a.cld_tau[icl + tcl * band]; cs = a.cld_ssa[icl + tcl * band]; cgg = a.cld_g[icl + tcl * band]; }
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+            {
+                gg[j] = 0;
+                combine_rayleigh(tau[j], ray[j], tt[j], ww[j]);
+                if (CLOUD) increment_2str(tt[j], ww[j], gg[j], ct, cs, cgg);
+            }
+        }
+        // The next layer's state is requested HERE: after the last load of this iteration has been consumed (every wait on
+        // the scoreboard these loads share drains all of them, so a later table or cloud load would wait for the prefetch
+        // at once) and before the two-stream arithmetic, which covers the latency.
+        if (k + 1 < nlay) cur = load_state(st, L, tm, c, top ? k + 1 : nlay - 2 - k);
         if (RB_SW_PFS > 0 && k + 1 + RB_SW_PFS < nlay)
         {
             const int lp = top ? k + 1 + RB_SW_PFS : nlay - 2 - k - RB_SW_PFS;      // to L2, see fused_lw.cu
             pfs.layer(lp, layer_side(tm, lp));
         }
-        Real ray[4] = {0, 0, 0, 0};
-        if (kray)
-        {
-            interp_minor<G>(kray + (ce.side ? ray_side : 0), ce, ray);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) ray[j] *= ce.wet;
-        }
-        Real ct = 0, cs = 0, cgg = 0;
-        if (CLOUD) { ct = a.cld_tau[icl + tcl * band]; cs = a.cld_ssa[icl + tcl * band]; cgg = a.cld_g[icl + tcl * band]; }
         V4<Real> v0, v1, v2, v3, v4, v5;
         Real* p0 = &v0.x; Real* p1 = &v1.x; Real* p2 = &v2.x; Real* p3 = &v3.x; Real* p4 = &v4.x; Real* p5 = &v5.x;
 #pragma unroll
         for (int j = 0; j < 4; ++j)
         {
-            Real t, w0, g = 0;
-            combine_rayleigh(tau[j], ray[j], t, w0);
-            if (CLOUD) increment_2str(t, w0, g, ct, cs, cgg);
+            const Real t = tt[j], w0 = ww[j], g = gg[j];
             Real Rdif, Tdif, Rdir, Tdir, Tnoscat;
             two_stream(t, w0, g, mu0s, Rdif, Tdif, Rdir, Tdir, Tnoscat);
             const Real su = sun ? Rdir * dir[j] : (Real)0;     // source_up
@@ -295,10 +310,11 @@ void launch_sw_band(const DevPlan<Real>& P, const BandArgs& B, const TileState<R
     const unsigned grid = (unsigned)((a.nc + cpb - 1) / cpb);
     const bool cloud = a.cld_tau != nullptr;
     constexpr size_t smem = sw_stage_bytes<Real>();
+    const BandLaunch<Real> L = make_band_launch<Real>(P, B, a, B.flav[0], B.flav[1], false, 6);
 #define RB_LAUNCH(LPC_, GW_, CL_, NE_) { \
         static const cudaError_t attr_ = smem > 48 * 1024 ? cudaFuncSetAttribute(sw_band_kernel<Real, LPC_, GW_, CL_, NE_>, \
                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) : cudaSuccess; (void)attr_; \
-        sw_band_kernel<Real, LPC_, GW_, CL_, NE_><<<grid, FUSED_THREADS, smem, s>>>(P, B, st, a); }
+        sw_band_kernel<Real, LPC_, GW_, CL_, NE_><<<grid, FUSED_THREADS, smem, s>>>(P, L, st, a); }
 #define RB_NE(LPC_, GW_, CL_) { if (P.neta == 9) RB_LAUNCH(LPC_, GW_, CL_, 9) else RB_LAUNCH(LPC_, GW_, CL_, 0) }
 #define RB_CL(LPC_, GW_) { if (cloud) RB_NE(LPC_, GW_, true) else RB_NE(LPC_, GW_, false) }
     if (P.gw == 16) { if (lpc == 4) RB_CL(4, 16) else RB_CL(2, 16) }

@@ -33,6 +33,48 @@ template<typename Real> struct FusedArgs
     int bnd_add;                                                    // LW: add this angle onto the by-band outputs
 };
 constexpr int FUSED_THREADS = 128;
+
+// Loop-invariant addresses and strides of one band launch, computed on the host and handed over in the constant bank:
+// at 96 registers ptxas rematerialises such values inside the layer loop, and a value that is ONE constant load costs one
+// instruction there instead of the 64-bit multiply chain it was derived with (~10 % of the longwave kernel's instructions).
+template<typename Real> struct BandLaunch
+{
+    BandArgs B;
+    const Real* kmaj;            // the band's major (+ interleaved Planck-fraction) block
+    const Real* kmin[2];         // the band's first minor contributor block, per side
+    const Real* kray[2];         // SW: the band's Rayleigh block, per side (null without Rayleigh)
+    const Real* plk;             // LW: the band's row of totplnk
+    size_t mstride;              // elements per minor contributor block
+    size_t tcl;                  // tile columns * layers
+    size_t flv[2];               // V4 offset of the band's flavor plane, per side
+    size_t scal0[2], scal1[2];   // V4 offset of the band's first / second scaling group plane, per side
+    size_t strip;                // scratch vectors per strip (nlay * words * threads)
+    size_t nlev_stride;          // ncol * (nlay + 1)
+    size_t o_top;                // ncol * (level index of the top of the atmosphere)
+    long lstep;                  // +-ncol: one level down in the caller's arrays
+};
+template<typename Real>
+inline BandLaunch<Real> make_band_launch(const DevPlan<Real>& P, const BandArgs& B, const FusedArgs<Real>& a, int flav0, int flav1,
+                                         bool lw, int words)
+{
+    BandLaunch<Real> L{};
+    L.B = B;
+    const size_t rs = (size_t)(lw ? 2 : 1) * P.gw;
+    L.kmaj = P.kmajor + (size_t)P.ntemp * (P.npres + 1) * P.neta * rs * B.band;
+    L.mstride = (size_t)P.ntemp * P.neta * P.gw;
+    for (int s = 0; s < 2; ++s) L.kmin[s] = P.kminor[s] + L.mstride * B.first_minor[s];
+    const size_t ray_elems = (size_t)P.ntemp * P.neta * P.gw;
+    for (int s = 0; s < 2; ++s) L.kray[s] = P.krayl ? P.krayl + ray_elems * ((size_t)s * P.nbnd + B.band) : nullptr;
+    L.plk = lw ? P.totplnk + (size_t)P.nplanck * B.band : nullptr;
+    L.tcl = (size_t)a.nc * a.nlay;
+    L.flv[0] = L.tcl * flav0; L.flv[1] = L.tcl * flav1;
+    for (int s = 0; s < 2; ++s) { L.scal0[s] = L.tcl * B.scal_off[s]; L.scal1[s] = L.tcl * (B.scal_off[s] + (B.nminor[s] > 4 ? 1 : 0)); }
+    L.strip = (size_t)a.nlay * words * FUSED_THREADS;
+    L.nlev_stride = (size_t)a.ncol * (a.nlay + 1);
+    L.o_top = a.top_at_1 ? 0 : (size_t)a.ncol * a.nlay;
+    L.lstep = a.top_at_1 ? (long)a.ncol : -(long)a.ncol;
+    return L;
+}
 template<typename Real> int lw_blocks_per_wave(int gw);
 template<typename Real> int sw_blocks_per_wave(int gw);
 template<typename Real> size_t fused_scratch_bytes(int nslots, int nlay, bool sw);

@@ -156,6 +156,21 @@ __device__ __forceinline__ void prefetch_strip_layer(const V4<Real>* strip_threa
     }
 }
 
+// the same with the plane offsets of the band launch precomputed on the host (BandLaunch)
+template<typename Real>
+__device__ __forceinline__ RawState<Real> load_state(const TileState<Real>& st, const BandLaunch<Real>& L, const unsigned* tm, int c, int l)
+{
+    const size_t icl = (size_t)c + (size_t)st.nc * l;
+    const int side = layer_side(tm, l);
+    RawState<Real> r;
+    r.sc0 = st.scal[icl + L.scal0[side]];
+    r.sc1 = st.scal[icl + L.scal1[side]];
+    r.cell = st.cell[icl];
+    r.fa = st.flvA[icl + L.flv[side]];
+    r.fb = st.flvB[icl + L.flv[side]];
+    return r;
+}
+
 #define RB_FMA4(acc, s, v) { acc[0] = fma(s, v.x, acc[0]); acc[1] = fma(s, v.y, acc[1]); acc[2] = fma(s, v.z, acc[2]); acc[3] = fma(s, v.w, acc[3]); }
 #define RB_MUL4(acc, s, v) { acc[0] = s * v.x; acc[1] = s * v.y; acc[2] = s * v.z; acc[3] = s * v.w; }
 
@@ -234,6 +249,34 @@ __device__ __forceinline__ void add_minor_tau(const DevPlan<Real>& P, const Band
 #pragma unroll
                 for (int j = 0; j < 4; ++j) tau[j] = fma(scp[u], s[j], tau[j]);
                 km += mstride;
+            }
+        }
+    }
+}
+
+template<typename G, typename Real>
+__device__ __forceinline__ void add_minor_tau(const BandLaunch<Real>& L, const Cell<Real>& c, int q4,
+                                              const V4<Real>& pre0, const V4<Real>& pre1,
+                                              const V4<Real>* __restrict__ scal_icl, Real (&tau)[4])
+{
+    const int side = c.side;
+    const int nm = L.B.nminor[side];
+    const Real* km = L.kmin[side] + q4;
+    for (int m0 = 0; m0 < nm; m0 += 4)
+    {
+        V4<Real> sc;
+        if (m0 == 0) sc = pre0; else if (m0 == 4) sc = pre1; else load_scal4(scal_icl, L.tcl, L.B, side, m0, sc);
+        const Real* scp = &sc.x;
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+        {
+            if (m0 + u < nm)
+            {
+                Real s[4];
+                interp_minor<G>(km, c, s);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) tau[j] = fma(scp[u], s[j], tau[j]);
+                km += L.mstride;
             }
         }
     }
