@@ -37,9 +37,10 @@ namespace rb200 {
 #ifndef RB_SW_STAGES
 #define RB_SW_STAGES 0
 #endif
-// L2 prefetch hints (see physics.cuh) measured slower in this DRAM-bound kernel (+1.4 %): off
+// L2 prefetch hints (see physics.cuh): the state two layers ahead helps a little (-1.5 %) since the prefetch was moved
+// behind the iteration's last load; strip lines ahead of pass 2 do not (this kernel is DRAM-bound: +1 % at 4 layers, +11 % at 8)
 #ifndef RB_SW_PFS
-#define RB_SW_PFS 0
+#define RB_SW_PFS 2
 #endif
 #ifndef RB_SW_PF2
 #define RB_SW_PF2 0

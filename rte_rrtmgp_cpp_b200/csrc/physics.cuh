@@ -88,8 +88,8 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 // The per-layer state of a warp's columns is one run of 32/LPC * sizeof(V4) bytes per array (a few 128-byte lines): lane i
 // of a warp requests ONE line of ONE array, so the whole warp prefetches a layer's state with a single instruction.
 // Arrays: cell, flvA, flvB, the band's first two scaling groups, and (longwave) the two Planck-position arrays.
-// Measured on B200 (1024^2 x 128): longwave (issue/latency-bound) -3 %, shortwave (DRAM-bound) +1.4 %, so it is on in the
-// longwave kernel only (RB_LW_PFS / RB_SW_PFS = layers ahead of the register prefetch, 0 = off).
+// Measured on B200 (1024^2 x 128): longwave (issue/latency-bound) -3 %, shortwave (DRAM-bound) -1.5 % for the state lines and
+// slower for the strip lines (RB_LW_PFS / RB_SW_PFS = layers ahead of the register prefetch, RB_*_PF2 = strip layers, 0 = off).
 template<typename Real, int LPC, bool LW> struct StatePrefetch
 {
     const char* base; unsigned lstep, off0, off1; bool on;           // layer step in units of 8 bytes, plane offsets in units of 16
