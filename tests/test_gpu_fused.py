@@ -132,3 +132,60 @@ def test_lw_fused_gauss_angles(dtype, n_ang):
         out[k].t.fill_(-999.0)                       # every element must be (over)written, not accumulated onto garbage
     sol.solve_gpu(api.DeviceColumns(atm, dtype), switch_cloud_optics=True, switch_output_bnd_fluxes=True, out=out)
     _cmp(out, ref, ("flux_up", "flux_dn", "flux_net", "bnd_flux_up", "bnd_flux_dn", "bnd_flux_net"), TOL[dtype])
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+def test_rfmip_block_shape(dtype):
+    """BASELINE config 1: one RFMIP block — 100 columns x 60 layers, LW 256 + SW 224 g-points — against the oracle."""
+    atm = rce_atmosphere(100, 60, night_fraction=0.1)
+    for kind, oracle, Solver, keys in (("lw", oracle_lw, api.Radiation_solver_longwave, ("flux_up", "flux_dn", "flux_net")),
+                                       ("sw", oracle_sw, api.Radiation_solver_shortwave, ("flux_up", "flux_dn", "flux_net", "flux_dn_dir"))):
+        kd = synthetic_kdist(kind)
+        assert kd.ngpt == (256 if kind == "lw" else 224)
+        out = Solver(kd, atm.vmr.keys(), dtype=dtype).solve_gpu(api.DeviceColumns(atm, dtype), heating=True)
+        ref = oracle(kd, atm)
+        _cmp(out, ref, keys, TOL[dtype])
+
+
+def replicate_columns(a, ndist, rep):
+    """Array_gpu with a column dimension of ndist -> the same with every column repeated `rep` times (column c + i*ndist
+    = column c).  Column-major: the column index is the fastest (fields) or the second (per-band surface arrays)."""
+    if a is None:
+        return None
+    t = a.t.view(*reversed(a.dims))              # torch row-major view: last index = first (fastest) dimension
+    if a.dims[0] == ndist:
+        t = t.repeat(*([1] * (t.dim() - 1)), rep)
+        dims = (ndist * rep,) + tuple(a.dims[1:])
+    elif len(a.dims) == 2 and a.dims[1] == ndist:
+        t = t.repeat(rep, 1)
+        dims = (a.dims[0], ndist * rep)
+    else:
+        return a
+    return api.Array_gpu(dims, a.t.dtype, a.t.device, t.contiguous().view(-1))
+
+
+def test_full_size_domain_replicas_are_bit_identical():
+    """BASELINE configs 3/4 at a size the oracle cannot reach: a 512 x 512 x 128 domain made of 4096 distinct columns
+    repeated 64 times.  Columns are independent, so every replica must carry exactly the bits of its source column
+    computed in a separate 4096-column call: tiles, waves and scratch-strip recycling must not leak between columns."""
+    ndist, rep, nlay = 4096, 64, 128
+    atm = rce_atmosphere(ndist, nlay, cloudy=True)
+    dt = torch.float32
+    small = api.DeviceColumns(atm, dt)
+    big = api.DeviceColumns(atm, dt)
+    for name in ("play", "plev", "tlay", "tlev", "tsfc", "mu0", "tsi_scaling", "lwp", "iwp", "rel", "dei", "emis_sfc",
+                 "sfc_alb_dir", "sfc_alb_dif"):
+        setattr(big, name, replicate_columns(getattr(small, name), ndist, rep))
+    for k, v in list(big.gas_concs.gas_concs_map.items()):
+        big.gas_concs.gas_concs_map[k] = replicate_columns(v, ndist, rep)
+    big.ncol = ndist * rep
+    for kind, Solver in (("lw", api.Radiation_solver_longwave), ("sw", api.Radiation_solver_shortwave)):
+        sol = Solver(synthetic_kdist(kind), atm.vmr.keys(), synthetic_cloud_lut(kind), dt)
+        ref = {k: v.t.clone() for k, v in sol.solve_gpu(small, switch_cloud_optics=True, heating=True).items()}
+        out = sol.solve_gpu(big, switch_cloud_optics=True, heating=True)
+        torch.cuda.synchronize()
+        for k in ("flux_up", "flux_dn", "flux_net", "heating_rate"):
+            got = out[k].t.view(-1, ndist * rep)                      # (nlev | nlay, ncol)
+            want = ref[k].view(-1, ndist).repeat(1, rep)
+            assert torch.equal(got, want), (kind, k)
+        assert torch.isfinite(out["flux_net"].t).all()
