@@ -209,6 +209,18 @@ int rrtmgp_b200_lw_solver_noscat(int dtype, int ncol, int nlay, int ngpt, int to
                                  const void* d_sfc_src, const void* d_inc_flux,
                                  void* d_flux_up, void* d_flux_dn, int do_broadband,
                                  const void* d_sfc_src_jac, void* d_flux_up_jac, void* stream);
+/* The same kernel with do_rescaling = true (include/rrtmgp_kernels.h:231-232; Fortran
+ * mo_rte_solver_kernels.F90:148-178,206-214, lw_transport_1rescl :753-844; Tang et al. 2018): d_ssa, d_g
+ * (ncol,nlay,ngpt) are the 2-stream properties; tau is scaled by 1 - ssa(1 - b), b = (1 - g)/2, and the up
+ * sweep and a second down sweep carry the scattering adjustment.  The reference C++ passes false
+ * (src/Rte_lw.cpp:178); this is the solver the Fortran front end uses for 2-stream LW properties. */
+int rrtmgp_b200_lw_solver_rescaled(int dtype, int ncol, int nlay, int ngpt, int top_at_1,
+                                   int n_gauss_angles, const void* d_tau, const void* d_ssa,
+                                   const void* d_g, const void* d_lay_src, const void* d_lev_src,
+                                   const void* d_sfc_emis_gpt, const void* d_sfc_src,
+                                   const void* d_inc_flux, void* d_flux_up, void* d_flux_dn,
+                                   int do_broadband, const void* d_sfc_src_jac, void* d_flux_up_jac,
+                                   void* stream);
 /* rte_sw_solver_2stream (include/rrtmgp_kernels.h:234-264; Fortran :503-609,985-1245).
  * mu0 (ncol); albedos, inc_flux_dir (ncol,ngpt); inc_flux_dif may be NULL. flux_dn includes
  * the direct beam on return, as in the reference. */
@@ -218,6 +230,17 @@ int rrtmgp_b200_sw_solver_2stream(int dtype, int ncol, int nlay, int ngpt, int t
                                   const void* d_sfc_alb_dif_gpt, const void* d_inc_flux_dir,
                                   const void* d_inc_flux_dif, void* d_flux_up, void* d_flux_dn,
                                   void* d_flux_dir, int do_broadband, void* stream);
+/* The kernel's own mu0 shape (ncol,nlay) (Fortran :517,1061-1065,1117-1125; src/Rte_sw.cpp:157-160 only
+ * ever broadcasts a per-column value): a height-dependent solar zenith cosine on a round earth.  The top
+ * layer's value scales the boundary condition, layers with mu0 <= 0 have no direct source, the surface
+ * layer's sign gates the surface source.  As in the Fortran, the beam crosses dark layers with the nominal
+ * mu0 = sqrt(epsilon(Real)), so the direct flux INSIDE dark layers depends on the build's precision. */
+int rrtmgp_b200_sw_solver_2stream_mu0lay(int dtype, int ncol, int nlay, int ngpt, int top_at_1,
+                                         const void* d_tau, const void* d_ssa, const void* d_g,
+                                         const void* d_mu0_lay, const void* d_sfc_alb_dir_gpt,
+                                         const void* d_sfc_alb_dif_gpt, const void* d_inc_flux_dir,
+                                         const void* d_inc_flux_dif, void* d_flux_up, void* d_flux_dn,
+                                         void* d_flux_dir, int do_broadband, void* stream);
 
 /* ---- Fluxes_broadband_gpu / Fluxes_byband_gpu ::reduce (include/Fluxes.h:127-210; kernels
  * rte_sum_broadband, rte_net_broadband_precalc, sum_byband, net_byband_precalc,

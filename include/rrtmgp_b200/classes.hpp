@@ -451,11 +451,20 @@ class Rte_lw_gpu
         static void rte_lw(const std::unique_ptr<Optical_props_arry_gpu>& optical_props, const Bool top_at_1,
                            const Source_func_lw_gpu& sources, const Array_gpu<Float,2>& sfc_emis,
                            const Array_gpu<Float,2>& inc_flux, Array_gpu<Float,3>& gpt_flux_up, Array_gpu<Float,3>& gpt_flux_dn,
-                           const int n_gauss_angles)
+                           const int n_gauss_angles, const Bool do_rescaling = false)
         {
             const int ncol = optical_props->get_ncol(), nlay = optical_props->get_nlay(), ngpt = optical_props->get_ngpt();
             Array_gpu<Float,2> emis_gpt({ncol, ngpt});
             expand_and_transpose(optical_props, sfc_emis, emis_gpt);
+            if (do_rescaling)   // false in the reference (src/Rte_lw.cpp:178); the kernel's re-scaled transport, 2-stream properties
+            {
+                rrtmgp_b200::check(rrtmgp_b200_lw_solver_rescaled(rrtmgp_b200::dtype, ncol, nlay, ngpt, top_at_1, n_gauss_angles,
+                        optical_props->get_tau().ptr(), optical_props->get_ssa().ptr(), optical_props->get_g().ptr(),
+                        sources.get_lay_source().ptr(), sources.get_lev_source().ptr(),
+                        emis_gpt.ptr(), sources.get_sfc_source().ptr(), inc_flux.size() ? inc_flux.ptr() : nullptr,
+                        gpt_flux_up.ptr(), gpt_flux_dn.ptr(), gpt_flux_up.dim(3) == 1, nullptr, nullptr, rrtmgp_b200::stream()));
+                return;
+            }
             rrtmgp_b200::check(rrtmgp_b200_lw_solver_noscat(rrtmgp_b200::dtype, ncol, nlay, ngpt, top_at_1, n_gauss_angles,
                     optical_props->get_tau().ptr(), sources.get_lay_source().ptr(), sources.get_lev_source().ptr(),
                     emis_gpt.ptr(), sources.get_sfc_source().ptr(), inc_flux.size() ? inc_flux.ptr() : nullptr,
@@ -479,6 +488,23 @@ class Rte_sw_gpu
             Rte_lw_gpu::expand_and_transpose(optical_props, sfc_alb_dif, a_dif);
             rrtmgp_b200::check(rrtmgp_b200_sw_solver_2stream(rrtmgp_b200::dtype, ncol, nlay, ngpt, top_at_1,
                     optical_props->get_tau().ptr(), optical_props->get_ssa().ptr(), optical_props->get_g().ptr(), mu0.ptr(),
+                    a_dir.ptr(), a_dif.ptr(), inc_flux_dir.ptr(), inc_flux_dif.size() ? inc_flux_dif.ptr() : nullptr,
+                    gpt_flux_up.ptr(), gpt_flux_dn.ptr(), gpt_flux_dir.ptr(), gpt_flux_up.dim(3) == 1, rrtmgp_b200::stream()));
+        }
+        // mu0 (ncol, nlay): the kernel's own shape (mo_rte_solver_kernels.F90:517), a height-dependent zenith cosine
+        static void rte_sw(const std::unique_ptr<Optical_props_arry_gpu>& optical_props, const Bool top_at_1,
+                           const Array_gpu<Float,2>& mu0_lay, const Array_gpu<Float,2>& inc_flux_dir,
+                           const Array_gpu<Float,2>& sfc_alb_dir, const Array_gpu<Float,2>& sfc_alb_dif,
+                           const Array_gpu<Float,2>& inc_flux_dif, Array_gpu<Float,3>& gpt_flux_up,
+                           Array_gpu<Float,3>& gpt_flux_dn, Array_gpu<Float,3>& gpt_flux_dir)
+        {
+            const int ncol = optical_props->get_ncol(), nlay = optical_props->get_nlay(), ngpt = optical_props->get_ngpt();
+            if (mu0_lay.dim(1) != ncol || mu0_lay.dim(2) != nlay) throw std::runtime_error("rte_sw: mu0 must be (ncol, nlay)");
+            Array_gpu<Float,2> a_dir({ncol, ngpt}), a_dif({ncol, ngpt});
+            Rte_lw_gpu::expand_and_transpose(optical_props, sfc_alb_dir, a_dir);
+            Rte_lw_gpu::expand_and_transpose(optical_props, sfc_alb_dif, a_dif);
+            rrtmgp_b200::check(rrtmgp_b200_sw_solver_2stream_mu0lay(rrtmgp_b200::dtype, ncol, nlay, ngpt, top_at_1,
+                    optical_props->get_tau().ptr(), optical_props->get_ssa().ptr(), optical_props->get_g().ptr(), mu0_lay.ptr(),
                     a_dir.ptr(), a_dif.ptr(), inc_flux_dir.ptr(), inc_flux_dif.size() ? inc_flux_dif.ptr() : nullptr,
                     gpt_flux_up.ptr(), gpt_flux_dn.ptr(), gpt_flux_dir.ptr(), gpt_flux_up.dim(3) == 1, rrtmgp_b200::stream()));
         }

@@ -481,8 +481,12 @@ def expand_and_transpose(disc: SpectralDisc, arr_in):
 
 
 def rte_lw(disc, tau, lay_src, lev_src, sfc_src, sfc_emis, top_at_1, inc_flux=None,
-           n_gauss_angles=1, broadband=False, sfc_src_jac=None):
+           n_gauss_angles=1, broadband=False, sfc_src_jac=None, ssa=None, g=None):
+    """ssa and g given: the re-scaled transport (do_rescaling, mo_rte_solver_kernels.F90:148-178,753-844) that the
+    Fortran front end uses for 2-stream optical properties; the reference C++ always passes false (src/Rte_lw.cpp:178)."""
     tau, lay_src, lev_src, sfc_src = F(tau), F(lay_src), F(lev_src), F(sfc_src)
+    rescale = ssa is not None
+    ssa_, g_ = (F(ssa), F(g)) if rescale else (tau, tau)
     ncol, nlay, ngpt = tau.shape
     sfc_emis_gpt = expand_and_transpose(disc, sfc_emis)
     n = n_gauss_angles
@@ -499,7 +503,7 @@ def rte_lw(disc, tau, lay_src, lev_src, sfc_src, sfc_emis, top_at_1, inc_flux=No
     lib().rte_lw_solver_noscat(
         _i(ncol), _i(nlay), _i(ngpt), _b(top_at_1), _i(n), _p(secants), _p(wts), _p(tau),
         _p(lay_src), _p(lev_src), _p(sfc_emis_gpt), _p(sfc_src), _p(inc), _p(up), _p(dn),
-        _b(broadband), _p(up), _p(dn), _b(do_jac), _p(jac_in), _p(jac), _b(False), _p(tau), _p(tau))
+        _b(broadband), _p(up), _p(dn), _b(do_jac), _p(jac_in), _p(jac), _b(rescale), _p(ssa_), _p(g_))
     return (up, dn, jac) if do_jac else (up, dn)
 
 
@@ -509,7 +513,8 @@ def rte_sw(disc, tau, ssa, g, mu0, inc_flux_dir, sfc_alb_dir, sfc_alb_dif, top_a
     ncol, nlay, ngpt = tau.shape
     a_dir = expand_and_transpose(disc, sfc_alb_dir)
     a_dif = expand_and_transpose(disc, sfc_alb_dif)
-    mu0_2d = F(np.tile(np.asarray(mu0)[:, None], (1, nlay)))
+    mu0 = np.asarray(mu0)                        # (ncol) as src/Rte_sw.cpp:157-160 expands it, or (ncol, nlay)
+    mu0_2d = F(mu0) if mu0.ndim == 2 else F(np.tile(mu0[:, None], (1, nlay)))
     ng_out = 1 if broadband else ngpt
     up = zeros((ncol, nlay + 1, ng_out)); dn = zeros((ncol, nlay + 1, ng_out))
     dr = zeros((ncol, nlay + 1, ng_out))

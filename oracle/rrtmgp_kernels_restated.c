@@ -771,15 +771,61 @@ static void lw_transport_noscat_up(int ncol, int nlay, int top_at_1,
     }
 }
 
-/* F90:51-240 (lw_solver_noscat_oneangle); do_rescaling is not supported by this oracle (the
- * reference C++ passes false, src/Rte_lw.cpp:178). D(ncol,ngpt). */
+/* F90:753-844 (lw_transport_1rescl): upward and second downward transport of the re-scaled solution
+ * (Tang et al. 2018).  The level whose radiance enters each adjustment is the Fortran's, per orientation. */
+static void lw_transport_1rescl(int ncol, int nlay, int top_at_1,
+                                const Float* trans, const Float* source_dn, const Float* source_up,
+                                Float* radn_up, Float* radn_dn, const Float* An, const Float* Cn,
+                                int do_Jacobians, Float* radn_up_Jac)
+{
+    if (top_at_1)
+    {
+        for (int ilev = nlay - 1; ilev >= 0; --ilev)
+            for (int icol = 0; icol < ncol; ++icol)
+            {
+                const size_t i = icol + (size_t)ncol * ilev;
+                const Float adjustmentFactor = Cn[i] * (An[i] * radn_dn[i] - trans[i] * source_dn[i] - source_up[i]);
+                radn_up[i] = trans[i] * radn_up[i + ncol] + source_up[i] + adjustmentFactor;
+                if (do_Jacobians) radn_up_Jac[i] = trans[i] * radn_up_Jac[i + ncol];
+            }
+        for (int ilev = 0; ilev < nlay; ++ilev)
+            for (int icol = 0; icol < ncol; ++icol)
+            {
+                const size_t i = icol + (size_t)ncol * ilev;
+                const Float adjustmentFactor = Cn[i] * (An[i] * radn_up[i] - trans[i] * source_up[i] - source_dn[i]);
+                radn_dn[i + ncol] = trans[i] * radn_dn[i] + source_dn[i] + adjustmentFactor;
+            }
+    }
+    else
+    {
+        for (int ilev = 0; ilev < nlay; ++ilev)
+            for (int icol = 0; icol < ncol; ++icol)
+            {
+                const size_t i = icol + (size_t)ncol * ilev;
+                const Float adjustmentFactor = Cn[i] * (An[i] * radn_dn[i + ncol] - trans[i] * source_dn[i] - source_up[i]);
+                radn_up[i + ncol] = trans[i] * radn_up[i] + source_up[i] + adjustmentFactor;
+                if (do_Jacobians) radn_up_Jac[i + ncol] = trans[i] * radn_up_Jac[i];
+            }
+        for (int ilev = nlay - 1; ilev >= 0; --ilev)
+            for (int icol = 0; icol < ncol; ++icol)
+            {
+                const size_t i = icol + (size_t)ncol * ilev;
+                const Float adjustmentFactor = Cn[i] * (An[i] * radn_up[i] - trans[i] * source_up[i] - source_dn[i]);
+                radn_dn[i] = trans[i] * radn_dn[i + ncol] + source_dn[i] + adjustmentFactor;
+            }
+    }
+}
+
+/* F90:51-240 (lw_solver_noscat_oneangle), with the re-scaling branch :148-178,206-214 (the reference C++
+ * passes do_rescaling = false, src/Rte_lw.cpp:178; the branch is restated for SURVEY 8f-4). D(ncol,ngpt). */
 static void lw_solver_noscat_oneangle(
         int ncol, int nlay, int ngpt, int top_at_1, const Float* D, Float weight,
         const Float* tau, const Float* lay_source, const Float* lev_source,
         const Float* sfc_emis, const Float* sfc_src, const Float* incident_flux,
         Float* flux_up, Float* flux_dn,
         int do_broadband, Float* broadband_up, Float* broadband_dn,
-        int do_Jacobians, const Float* sfc_srcJac, Float* flux_upJac)
+        int do_Jacobians, const Float* sfc_srcJac, Float* flux_upJac,
+        int do_rescaling, const Float* ssa, const Float* g)
 {
     const Float pi = acos(-1.0);
     const size_t ncl = (size_t)ncol * nlay, ncv = (size_t)ncol * (nlay + 1);
@@ -793,6 +839,8 @@ static void lw_solver_noscat_oneangle(
     Float* loc_flux_up = (Float*)malloc(sizeof(Float) * ncv);
     Float* loc_flux_dn = (Float*)malloc(sizeof(Float) * ncv);
     Float* gpt_flux_Jac = (Float*)malloc(sizeof(Float) * ncv);
+    Float* An = do_rescaling ? (Float*)malloc(sizeof(Float) * ncl) : NULL;
+    Float* Cn = do_rescaling ? (Float*)malloc(sizeof(Float) * ncl) : NULL;
 
     if (do_broadband)
         for (size_t i = 0; i < ncv; ++i) { broadband_up[i] = 0.0; broadband_dn[i] = 0.0; }
@@ -808,13 +856,27 @@ static void lw_solver_noscat_oneangle(
             gpt_flux_dn[icol + (size_t)ncol * top_level] =
                     incident_flux[icol + (size_t)ncol * igpt] / (pi * weight);
 
-        for (int ilay = 0; ilay < nlay; ++ilay)
-            for (int icol = 0; icol < ncol; ++icol)
-            {
-                const size_t i = icol + (size_t)ncol * ilay;
-                tau_loc[i] = tau[i + ncl * igpt] * D[icol + (size_t)ncol * igpt];
-                trans[i] = exp(-tau_loc[i]);
-            }
+        if (do_rescaling)
+            for (int ilay = 0; ilay < nlay; ++ilay)
+                for (int icol = 0; icol < ncol; ++icol)
+                {
+                    const size_t i = icol + (size_t)ncol * ilay;
+                    const Float ssal = ssa[i + ncl * igpt];
+                    const Float wb = ssal * (1.0 - g[i + ncl * igpt]) * 0.5;
+                    const Float scaleTau = (1.0 - ssal + wb);
+                    Cn[i] = 0.4 * wb / scaleTau;
+                    tau_loc[i] = tau[i + ncl * igpt] * D[icol + (size_t)ncol * igpt] * scaleTau;
+                    trans[i] = exp(-tau_loc[i]);
+                    An[i] = (1.0 - trans[i] * trans[i]);
+                }
+        else
+            for (int ilay = 0; ilay < nlay; ++ilay)
+                for (int icol = 0; icol < ncol; ++icol)
+                {
+                    const size_t i = icol + (size_t)ncol * ilay;
+                    tau_loc[i] = tau[i + ncl * igpt] * D[icol + (size_t)ncol * igpt];
+                    trans[i] = exp(-tau_loc[i]);
+                }
 
         lw_source_noscat(ncol, nlay, top_at_1, lay_source + ncl * igpt, lev_source + ncv * igpt,
                          tau_loc, trans, source_dn, source_up);
@@ -831,8 +893,12 @@ static void lw_solver_noscat_oneangle(
                 gpt_flux_Jac[icol + (size_t)ncol * sfc_level] = emis * sfc_srcJac[icol + (size_t)ncol * igpt];
         }
 
-        lw_transport_noscat_up(ncol, nlay, top_at_1, trans, source_up, gpt_flux_up,
-                               do_Jacobians, gpt_flux_Jac);
+        if (do_rescaling)
+            lw_transport_1rescl(ncol, nlay, top_at_1, trans, source_dn, source_up, gpt_flux_up, gpt_flux_dn,
+                                An, Cn, do_Jacobians, gpt_flux_Jac);
+        else
+            lw_transport_noscat_up(ncol, nlay, top_at_1, trans, source_up, gpt_flux_up,
+                                   do_Jacobians, gpt_flux_Jac);
 
         if (do_broadband)
             for (size_t i = 0; i < ncv; ++i)
@@ -861,6 +927,7 @@ static void lw_solver_noscat_oneangle(
 
     free(tau_loc); free(trans); free(source_dn); free(source_up);
     free(loc_flux_up); free(loc_flux_dn); free(gpt_flux_Jac);
+    free(An); free(Cn);
 }
 
 /* F90:248-367 (lw_solver_noscat).  Scalars arrive by reference (rrtmgp_kernels.h:207-232). */
@@ -878,12 +945,12 @@ void rte_lw_solver_noscat(
     const int top_at_1 = *top_at_1_ != 0, do_broadband = *do_broadband_ != 0;
     const int do_Jacobians = *do_Jacobians_ != 0;
     const size_t ncv = (size_t)ncol * (nlay + 1);
-    (void)do_rescaling_; (void)ssa; (void)g;
+    const int do_rescaling = *do_rescaling_ != 0;
 
     lw_solver_noscat_oneangle(ncol, nlay, ngpt, top_at_1, Ds, weights[0],
                               tau, lay_source, lev_source, sfc_emis, sfc_src, inc_flux,
                               flux_up, flux_dn, do_broadband, broadband_up, broadband_dn,
-                              do_Jacobians, sfc_srcJac, flux_upJac);
+                              do_Jacobians, sfc_srcJac, flux_upJac, do_rescaling, ssa, g);
     if (nmus > 1)
     {
         Float *this_bb_up = NULL, *this_bb_dn = NULL, *this_up = NULL, *this_dn = NULL, *this_jac = NULL;
@@ -907,7 +974,7 @@ void rte_lw_solver_noscat(
                                       Ds + (size_t)ncol * ngpt * imu, weights[imu],
                                       tau, lay_source, lev_source, sfc_emis, sfc_src, inc_flux,
                                       this_up, this_dn, do_broadband, this_bb_up, this_bb_dn,
-                                      do_Jacobians, sfc_srcJac, this_jac);
+                                      do_Jacobians, sfc_srcJac, this_jac, do_rescaling, ssa, g);
             if (do_broadband)
                 for (size_t i = 0; i < ncv; ++i)
                 {

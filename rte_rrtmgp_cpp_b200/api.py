@@ -428,12 +428,23 @@ class Rte_lw_gpu:
     @staticmethod
     def rte_lw(optical_props, top_at_1: bool, sources: Source_func_lw_gpu, sfc_emis: Array_gpu,
                inc_flux: Optional[Array_gpu], gpt_flux_up: Array_gpu, gpt_flux_dn: Array_gpu, n_gauss_angles: int,
-               sfc_src_jac: Optional[Array_gpu] = None, flux_up_jac: Optional[Array_gpu] = None) -> None:
-        """include/Rte_lw.h:62-77; broadband iff gpt_flux_up.dim(3) == 1 (src/Rte_lw.cpp:170)"""
+               sfc_src_jac: Optional[Array_gpu] = None, flux_up_jac: Optional[Array_gpu] = None,
+               do_rescaling: bool = False) -> None:
+        """include/Rte_lw.h:62-77; broadband iff gpt_flux_up.dim(3) == 1 (src/Rte_lw.cpp:170).  do_rescaling (false
+        in the reference, src/Rte_lw.cpp:178) needs 2-stream optical_props: the kernel's Tang et al. re-scaled transport."""
         ncol, nlay, ngpt = optical_props.tau.dims
         emis = Rte_lw_gpu.expand_and_transpose(optical_props, sfc_emis)
         bb = len(gpt_flux_up.dims) < 3 or gpt_flux_up.dims[2] == 1
         inc = inc_flux if (inc_flux is not None and inc_flux.size() > 0) else None
+        if do_rescaling:
+            if getattr(optical_props, "ssa", None) is None:
+                raise RuntimeError("rte_lw: do_rescaling needs 2-stream optical properties (tau, ssa, g)")
+            check(lib().rrtmgp_b200_lw_solver_rescaled(
+                _code(optical_props.dtype), ncol, nlay, ngpt, int(top_at_1), n_gauss_angles, _ptr(optical_props.tau),
+                _ptr(optical_props.ssa), _ptr(optical_props.g), _ptr(sources.lay_source), _ptr(sources.lev_source),
+                _ptr(emis), _ptr(sources.sfc_source), _ptr(inc), _ptr(gpt_flux_up), _ptr(gpt_flux_dn), int(bb),
+                _ptr(sfc_src_jac), _ptr(flux_up_jac), _stream()))
+            return
         check(lib().rrtmgp_b200_lw_solver_noscat(
             _code(optical_props.dtype), ncol, nlay, ngpt, int(top_at_1), n_gauss_angles, _ptr(optical_props.tau),
             _ptr(sources.lay_source), _ptr(sources.lev_source), _ptr(emis), _ptr(sources.sfc_source), _ptr(inc),
@@ -445,13 +456,18 @@ class Rte_sw_gpu:
     def rte_sw(optical_props, top_at_1: bool, mu0: Array_gpu, inc_flux_dir: Array_gpu, sfc_alb_dir: Array_gpu,
                sfc_alb_dif: Array_gpu, inc_flux_dif: Optional[Array_gpu], gpt_flux_up: Array_gpu,
                gpt_flux_dn: Array_gpu, gpt_flux_dir: Array_gpu) -> None:
-        """include/Rte_sw.h:62-80; has_dif_bc iff inc_flux_dif.size() > 0 (src/Rte_sw.cpp:136-184)"""
+        """include/Rte_sw.h:62-80; has_dif_bc iff inc_flux_dif.size() > 0 (src/Rte_sw.cpp:136-184).  mu0 is (ncol) as in
+        the reference, or the kernel's own (ncol, nlay): a height-dependent zenith cosine (F90:517,1061-1065)."""
         ncol, nlay, ngpt = optical_props.tau.dims
         a_dir = Rte_lw_gpu.expand_and_transpose(optical_props, sfc_alb_dir)
         a_dif = Rte_lw_gpu.expand_and_transpose(optical_props, sfc_alb_dif)
         bb = len(gpt_flux_up.dims) < 3 or gpt_flux_up.dims[2] == 1
         dif = inc_flux_dif if (inc_flux_dif is not None and inc_flux_dif.size() > 0) else None
-        check(lib().rrtmgp_b200_sw_solver_2stream(
+        by_layer = len(mu0.dims) == 2
+        if tuple(mu0.dims) not in ((ncol,), (ncol, nlay)):
+            raise RuntimeError(f"rte_sw: mu0 must be (ncol) or (ncol, nlay), got {tuple(mu0.dims)}")
+        solver = lib().rrtmgp_b200_sw_solver_2stream_mu0lay if by_layer else lib().rrtmgp_b200_sw_solver_2stream
+        check(solver(
             _code(optical_props.dtype), ncol, nlay, ngpt, int(top_at_1), _ptr(optical_props.tau), _ptr(optical_props.ssa),
             _ptr(optical_props.g), _ptr(mu0), _ptr(a_dir), _ptr(a_dif), _ptr(inc_flux_dir), _ptr(dif),
             _ptr(gpt_flux_up), _ptr(gpt_flux_dn), _ptr(gpt_flux_dir), int(bb), _stream()))

@@ -755,13 +755,16 @@ int rrtmgp_b200_expand_and_transpose(int dtype, int ncol, int nbnd, int ngpt, co
     });
 }
 
-int rrtmgp_b200_lw_solver_noscat(int dtype, int ncol, int nlay, int ngpt, int top_at_1, int nmus, const void* tau,
-                                 const void* lay_src, const void* lev_src, const void* sfc_emis, const void* sfc_src,
-                                 const void* inc_flux, void* flux_up, void* flux_dn, int do_broadband,
-                                 const void* sfc_src_jac, void* flux_up_jac, void* stream)
+// rte_lw_solver_noscat; ssa and g non-null select its do_rescaling branch
+static int lw_solver_any(int dtype, int ncol, int nlay, int ngpt, int top_at_1, int nmus, const void* tau,
+                         const void* ssa, const void* g,
+                         const void* lay_src, const void* lev_src, const void* sfc_emis, const void* sfc_src,
+                         const void* inc_flux, void* flux_up, void* flux_dn, int do_broadband,
+                         const void* sfc_src_jac, void* flux_up_jac, void* stream)
 {
     return guarded([&] {
         check_dims(ncol, nlay);
+        if ((ssa == nullptr) != (g == nullptr)) throw ArgError("lw_solver: ssa and g go together");
         if (ngpt < 1 || !tau || !lay_src || !lev_src || !sfc_emis || !sfc_src || !flux_up || !flux_dn) throw ArgError("lw_solver: null array");
         if (nmus < 1 || nmus > 4) throw ArgError("lw_solver: n_gauss_angles must be 1..4");   // src/Rte_lw.cpp:139-151
         if ((sfc_src_jac == nullptr) != (flux_up_jac == nullptr)) throw ArgError("lw_solver: Jacobian input and output go together");
@@ -770,28 +773,56 @@ int rrtmgp_b200_lw_solver_noscat(int dtype, int ncol, int nlay, int ngpt, int to
         const size_t ncv = (size_t)ncol * (nlay + 1);
         void *up = flux_up, *dn = flux_dn;
         char* tmp = nullptr;
-        if (do_broadband)
-        {
-            CK(cudaMallocAsync((void**)&tmp, 2 * ncv * ngpt * esz, s));
-            up = tmp; dn = tmp + ncv * ngpt * esz;
-        }
+        const size_t fb = ncv * ngpt * esz;                       // one (ncol, nlay+1, ngpt) array
+        const size_t nfl = do_broadband ? 2 : 0, nwk = ssa ? 2 : 0;
+        if (nfl + nwk) CK(cudaMallocAsync((void**)&tmp, (nfl + nwk) * fb, s));
+        if (do_broadband) { up = tmp; dn = tmp + fb; }
+        void* work2 = tmp + nfl * fb;
         if (flux_up_jac) CK(cudaMemsetAsync(flux_up_jac, 0, ncv * esz, s));
-        DISPATCH(dtype,
-            launch_lw_solver<float>(ncol, nlay, ngpt, top_at_1, nmus, tau, lay_src, lev_src, sfc_emis, sfc_src, inc_flux, up, dn, sfc_src_jac, flux_up_jac, s),
-            launch_lw_solver<double>(ncol, nlay, ngpt, top_at_1, nmus, tau, lay_src, lev_src, sfc_emis, sfc_src, inc_flux, up, dn, sfc_src_jac, flux_up_jac, s));
+        if (ssa)
+        {
+            DISPATCH(dtype,
+                launch_lw_solver_rescl<float>(ncol, nlay, ngpt, top_at_1, nmus, tau, ssa, g, lay_src, lev_src, sfc_emis, sfc_src, inc_flux, up, dn, sfc_src_jac, flux_up_jac, work2, s),
+                launch_lw_solver_rescl<double>(ncol, nlay, ngpt, top_at_1, nmus, tau, ssa, g, lay_src, lev_src, sfc_emis, sfc_src, inc_flux, up, dn, sfc_src_jac, flux_up_jac, work2, s));
+        }
+        else
+        {
+            DISPATCH(dtype,
+                launch_lw_solver<float>(ncol, nlay, ngpt, top_at_1, nmus, tau, lay_src, lev_src, sfc_emis, sfc_src, inc_flux, up, dn, sfc_src_jac, flux_up_jac, s),
+                launch_lw_solver<double>(ncol, nlay, ngpt, top_at_1, nmus, tau, lay_src, lev_src, sfc_emis, sfc_src, inc_flux, up, dn, sfc_src_jac, flux_up_jac, s));
+        }
         if (do_broadband)
         {
             DISPATCH(dtype, (launch_sum_broadband<float>(ncol, nlay + 1, ngpt, up, flux_up, s), launch_sum_broadband<float>(ncol, nlay + 1, ngpt, dn, flux_dn, s)),
                             (launch_sum_broadband<double>(ncol, nlay + 1, ngpt, up, flux_up, s), launch_sum_broadband<double>(ncol, nlay + 1, ngpt, dn, flux_dn, s)));
-            CK(cudaFreeAsync(tmp, s));
         }
+        if (tmp) CK(cudaFreeAsync(tmp, s));
     });
 }
 
-int rrtmgp_b200_sw_solver_2stream(int dtype, int ncol, int nlay, int ngpt, int top_at_1, const void* tau, const void* ssa,
-                                  const void* g, const void* mu0, const void* alb_dir, const void* alb_dif,
-                                  const void* inc_dir, const void* inc_dif, void* flux_up, void* flux_dn, void* flux_dir,
-                                  int do_broadband, void* stream)
+int rrtmgp_b200_lw_solver_noscat(int dtype, int ncol, int nlay, int ngpt, int top_at_1, int nmus, const void* tau,
+                                 const void* lay_src, const void* lev_src, const void* sfc_emis, const void* sfc_src,
+                                 const void* inc_flux, void* flux_up, void* flux_dn, int do_broadband,
+                                 const void* sfc_src_jac, void* flux_up_jac, void* stream)
+{
+    return lw_solver_any(dtype, ncol, nlay, ngpt, top_at_1, nmus, tau, nullptr, nullptr, lay_src, lev_src, sfc_emis, sfc_src,
+                         inc_flux, flux_up, flux_dn, do_broadband, sfc_src_jac, flux_up_jac, stream);
+}
+
+int rrtmgp_b200_lw_solver_rescaled(int dtype, int ncol, int nlay, int ngpt, int top_at_1, int nmus, const void* tau,
+                                   const void* ssa, const void* g, const void* lay_src, const void* lev_src,
+                                   const void* sfc_emis, const void* sfc_src, const void* inc_flux, void* flux_up,
+                                   void* flux_dn, int do_broadband, const void* sfc_src_jac, void* flux_up_jac, void* stream)
+{
+    if (!ssa || !g) return guarded([&] { throw ArgError("lw_solver_rescaled: ssa and g are required"); });
+    return lw_solver_any(dtype, ncol, nlay, ngpt, top_at_1, nmus, tau, ssa, g, lay_src, lev_src, sfc_emis, sfc_src,
+                         inc_flux, flux_up, flux_dn, do_broadband, sfc_src_jac, flux_up_jac, stream);
+}
+
+static int sw_solver_any(int dtype, int ncol, int nlay, int ngpt, int top_at_1, int mu0_by_layer, const void* tau, const void* ssa,
+                         const void* g, const void* mu0, const void* alb_dir, const void* alb_dif,
+                         const void* inc_dir, const void* inc_dif, void* flux_up, void* flux_dn, void* flux_dir,
+                         int do_broadband, void* stream)
 {
     return guarded([&] {
         check_dims(ncol, nlay);
@@ -806,8 +837,8 @@ int rrtmgp_b200_sw_solver_2stream(int dtype, int ncol, int nlay, int ngpt, int t
         void *up = flux_up, *dn = flux_dn, *dr = flux_dir;
         if (do_broadband) { up = tmp + wbytes; dn = tmp + wbytes + fbytes; dr = tmp + wbytes + 2 * fbytes; }
         DISPATCH(dtype,
-            launch_sw_solver<float>(ncol, nlay, ngpt, top_at_1, tau, ssa, g, mu0, alb_dir, alb_dif, inc_dir, inc_dif, up, dn, dr, tmp, s),
-            launch_sw_solver<double>(ncol, nlay, ngpt, top_at_1, tau, ssa, g, mu0, alb_dir, alb_dif, inc_dir, inc_dif, up, dn, dr, tmp, s));
+            launch_sw_solver<float>(ncol, nlay, ngpt, top_at_1, mu0_by_layer, tau, ssa, g, mu0, alb_dir, alb_dif, inc_dir, inc_dif, up, dn, dr, tmp, s),
+            launch_sw_solver<double>(ncol, nlay, ngpt, top_at_1, mu0_by_layer, tau, ssa, g, mu0, alb_dir, alb_dif, inc_dir, inc_dif, up, dn, dr, tmp, s));
         if (do_broadband)
         {
             void* src[3] = {up, dn, dr}; void* dst[3] = {flux_up, flux_dn, flux_dir};
@@ -816,6 +847,24 @@ int rrtmgp_b200_sw_solver_2stream(int dtype, int ncol, int nlay, int ngpt, int t
         }
         CK(cudaFreeAsync(tmp, s));
     });
+}
+
+int rrtmgp_b200_sw_solver_2stream(int dtype, int ncol, int nlay, int ngpt, int top_at_1, const void* tau, const void* ssa,
+                                  const void* g, const void* mu0, const void* alb_dir, const void* alb_dif,
+                                  const void* inc_dir, const void* inc_dif, void* flux_up, void* flux_dn, void* flux_dir,
+                                  int do_broadband, void* stream)
+{
+    return sw_solver_any(dtype, ncol, nlay, ngpt, top_at_1, 0, tau, ssa, g, mu0, alb_dir, alb_dif, inc_dir, inc_dif,
+                         flux_up, flux_dn, flux_dir, do_broadband, stream);
+}
+
+int rrtmgp_b200_sw_solver_2stream_mu0lay(int dtype, int ncol, int nlay, int ngpt, int top_at_1, const void* tau, const void* ssa,
+                                         const void* g, const void* mu0_lay, const void* alb_dir, const void* alb_dif,
+                                         const void* inc_dir, const void* inc_dif, void* flux_up, void* flux_dn,
+                                         void* flux_dir, int do_broadband, void* stream)
+{
+    return sw_solver_any(dtype, ncol, nlay, ngpt, top_at_1, 1, tau, ssa, g, mu0_lay, alb_dir, alb_dif, inc_dir, inc_dif,
+                         flux_up, flux_dn, flux_dir, do_broadband, stream);
 }
 
 int rrtmgp_b200_sum_broadband(int dtype, int ncol, int nlev, int ngpt, const void* gpt_flux, void* flux, void* stream)

@@ -324,12 +324,114 @@ void launch_lw_solver(int ncol, int nlay, int ngpt, int top_at_1, int nmus, cons
 }
 
 // ------------------------------------------------------------------------------------------
+// rte_lw_solver_noscat with do_rescaling (mo_rte_solver_kernels.F90:148-178, 206-214, 753-844; Tang et al. 2018):
+// the optical depth is scaled by 1 - w(1 - b), b = (1 - g)/2, and the up sweep and a SECOND down sweep carry an
+// adjustment term Cn * (An * I_opposite - ...).  The first down sweep and the up sweep must both be complete
+// before the second down sweep, so one angle's radiances live in work2 = 2 x (ncol, nlay+1, ngpt) (thread-private
+// lines: thread = (column, g-point)) and are added onto the outputs at the end of the angle.  The level whose
+// opposite-direction radiance enters each adjustment is the Fortran's, which differs between the orientations in
+// the second down sweep (top of the layer when top_at_1, bottom of the layer otherwise).
+// ------------------------------------------------------------------------------------------
+template<typename Real>
+__global__ void __launch_bounds__(128)
+lw_solver_rescl_kernel(int ncol, int nlay, int ngpt, int top_at_1, int nmus,
+                       const Real* __restrict__ tau, const Real* __restrict__ ssa, const Real* __restrict__ asy,
+                       const Real* __restrict__ lay_src, const Real* __restrict__ lev_src,
+                       const Real* __restrict__ sfc_emis, const Real* __restrict__ sfc_src,
+                       const Real* __restrict__ inc_flux, Real* __restrict__ flux_up, Real* __restrict__ flux_dn,
+                       const Real* __restrict__ sfc_src_jac, Real* __restrict__ flux_up_jac, Real* __restrict__ work2)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const int g = blockIdx.y;
+    if (c >= ncol) return;
+    const size_t ncl = (size_t)ncol * nlay, ncv = (size_t)ncol * (nlay + 1);
+    const Real* tg = tau + ncl * g + c; const Real* wg = ssa + ncl * g + c; const Real* ag = asy + ncl * g + c;
+    const Real* lay = lay_src + ncl * g + c;
+    const Real* lev = lev_src + ncv * g + c;
+    Real* up = flux_up + ncv * g + c; Real* dn = flux_dn + ncv * g + c;
+    Real* ru = work2 + ncv * g + c;   Real* rd = ru + ncv * ngpt;
+    const size_t cg = c + (size_t)ncol * g;
+    const Real emis = sfc_emis[cg], ssrc = sfc_src[cg];
+    const Real inc = inc_flux ? inc_flux[cg] : (Real)0;
+    const Real pi = (Real)3.14159265358979323846;
+    auto level = [&](int j) { return (size_t)ncol * (top_at_1 ? j : nlay - j); };
+    auto layer = [&](int k) { return (size_t)ncol * (top_at_1 ? k : nlay - 1 - k); };
+    // scaled path, transmissivity, sources, An, Cn of top-down layer k at secant D
+    auto cell = [&](int k, Real D, Real& t, Real& s_up, Real& s_dn, Real& An, Real& Cn)
+    {
+        const size_t il = layer(k);
+        const Real ssal = wg[il];
+        const Real wb = ssal * ((Real)1 - ag[il]) * (Real)0.5;
+        const Real scaleTau = (Real)1 - ssal + wb;
+        Cn = M<Real>::div((Real)0.4 * wb, scaleTau);
+        lw_layer<Real>(tg[il] * D * scaleTau, lay[il], lev[level(k)], lev[level(k + 1)], t, s_up, s_dn);
+        An = (Real)1 - t * t;
+    };
+
+    for (int imu = 0; imu < nmus; ++imu)
+    {
+        const Real D = (Real)c_gauss_Ds[nmus - 1][imu], w = (Real)c_gauss_wts[nmus - 1][imu];
+        const Real piw = pi * w;
+        Real t, s_up, s_dn, An, Cn;
+        Real radn = inc / piw;
+        rd[level(0)] = radn;
+        for (int k = 0; k < nlay; ++k)
+        {
+            cell(k, D, t, s_up, s_dn, An, Cn);
+            radn = t * radn + s_dn;
+            rd[level(k + 1)] = radn;
+        }
+        radn = radn * ((Real)1 - emis) + emis * ssrc;
+        ru[level(nlay)] = radn;
+        Real jac = sfc_src_jac ? emis * sfc_src_jac[cg] : (Real)0;
+        if (flux_up_jac) atomicAdd(flux_up_jac + c + level(nlay), piw * jac);
+        for (int k = nlay - 1; k >= 0; --k)
+        {
+            cell(k, D, t, s_up, s_dn, An, Cn);
+            const Real adj = Cn * (An * rd[level(k)] - t * s_dn - s_up);          // down-welling at the layer top
+            radn = t * radn + s_up + adj;
+            ru[level(k)] = radn;
+            if (flux_up_jac) { jac = t * jac; atomicAdd(flux_up_jac + c + level(k), piw * jac); }
+        }
+        radn = rd[level(0)];
+        for (int k = 0; k < nlay; ++k)
+        {
+            cell(k, D, t, s_up, s_dn, An, Cn);
+            const Real adj = Cn * (An * ru[level(top_at_1 ? k : k + 1)] - t * s_up - s_dn);
+            radn = t * radn + s_dn + adj;
+            rd[level(k + 1)] = radn;
+        }
+        for (int j = 0; j <= nlay; ++j)
+        {
+            const size_t lv = level(j);
+            const Real vu = piw * ru[lv], vd = piw * rd[lv];
+            up[lv] = imu == 0 ? vu : up[lv] + vu;
+            dn[lv] = imu == 0 ? vd : dn[lv] + vd;
+        }
+    }
+}
+
+template<typename Real>
+void launch_lw_solver_rescl(int ncol, int nlay, int ngpt, int top_at_1, int nmus, const void* tau, const void* ssa,
+                            const void* g, const void* lay_src, const void* lev_src, const void* sfc_emis,
+                            const void* sfc_src, const void* inc_flux, void* flux_up, void* flux_dn,
+                            const void* sfc_src_jac, void* flux_up_jac, void* work2, cudaStream_t s)
+{
+    dim3 grid((unsigned)((ncol + 127) / 128), ngpt);
+    lw_solver_rescl_kernel<Real><<<grid, 128, 0, s>>>(ncol, nlay, ngpt, top_at_1, nmus, (const Real*)tau, (const Real*)ssa,
+            (const Real*)g, (const Real*)lay_src, (const Real*)lev_src, (const Real*)sfc_emis, (const Real*)sfc_src,
+            (const Real*)inc_flux, (Real*)flux_up, (Real*)flux_dn, (const Real*)sfc_src_jac, (Real*)flux_up_jac,
+            (Real*)work2);
+    count_launch();
+}
+
+// ------------------------------------------------------------------------------------------
 // rte_sw_solver_2stream (mo_rte_solver_kernels.F90:503-609, 985-1245); work4 = 4 arrays
 // (ncol, nlay, ngpt) holding the per-layer recurrence coefficients between the passes.
 // ------------------------------------------------------------------------------------------
 template<typename Real>
 __global__ void __launch_bounds__(128)
-sw_solver_kernel(int ncol, int nlay, int ngpt, int top_at_1,
+sw_solver_kernel(int ncol, int nlay, int ngpt, int top_at_1, int mu0_by_layer,
                  const Real* __restrict__ tau, const Real* __restrict__ ssa, const Real* __restrict__ gg,
                  const Real* __restrict__ mu0_, const Real* __restrict__ alb_dir, const Real* __restrict__ alb_dif,
                  const Real* __restrict__ inc_dir, const Real* __restrict__ inc_dif,
@@ -345,17 +447,25 @@ sw_solver_kernel(int ncol, int nlay, int ngpt, int top_at_1,
     Real* w0 = work + ncl * g + c; Real* w1 = w0 + ngl; Real* w2 = w1 + ngl; Real* w3 = w2 + ngl;
     Real* up = flux_up + ncv * g + c; Real* dn = flux_dn + ncv * g + c; Real* dr = flux_dir + ncv * g + c;
     const size_t cg = c + (size_t)ncol * g;
-    const Real mu0 = mu0_[c];
-    const Real mu0s = M<Real>::max(M<Real>::sqrt(M<Real>::eps), mu0);
-    const bool sun = mu0 > (Real)0;
     auto level = [&](int j) { return (size_t)ncol * (top_at_1 ? j : nlay - j); };
     auto layer = [&](int k) { return (size_t)ncol * (top_at_1 ? k : nlay - 1 - k); };
+    // mu0 (ncol), or (ncol, nlay) on a round earth (F90:517, 1061-1065, 1117-1125): each layer's own value, the
+    // top layer's for the boundary condition, the surface layer's for the surface source
+    Real mu0 = mu0_[c + (mu0_by_layer ? layer(0) : 0)];
+    Real mu0s = M<Real>::max(M<Real>::sqrt(M<Real>::eps), mu0);
+    bool sun = mu0 > (Real)0;
 
     Real dir = inc_dir[cg] * mu0;
     dr[level(0)] = dir;
     for (int k = 0; k < nlay; ++k)
     {
         const size_t il = layer(k);
+        if (mu0_by_layer)
+        {
+            mu0 = mu0_[c + il];
+            mu0s = M<Real>::max(M<Real>::sqrt(M<Real>::eps), mu0);
+            sun = mu0 > (Real)0;
+        }
         Real Rdif, Tdif, Rdir, Tdir, Tnoscat;
         two_stream<Real>(tg[il], wg[il], ag[il], mu0s, Rdif, Tdif, Rdir, Tdir, Tnoscat);
         w0[il] = Rdif; w1[il] = Tdif;
@@ -392,12 +502,12 @@ sw_solver_kernel(int ncol, int nlay, int ngpt, int top_at_1,
 }
 
 template<typename Real>
-void launch_sw_solver(int ncol, int nlay, int ngpt, int top_at_1, const void* tau, const void* ssa, const void* g,
-                      const void* mu0, const void* alb_dir, const void* alb_dif, const void* inc_dir,
+void launch_sw_solver(int ncol, int nlay, int ngpt, int top_at_1, int mu0_by_layer, const void* tau, const void* ssa,
+                      const void* g, const void* mu0, const void* alb_dir, const void* alb_dif, const void* inc_dir,
                       const void* inc_dif, void* flux_up, void* flux_dn, void* flux_dir, void* work4, cudaStream_t s)
 {
     dim3 grid((unsigned)((ncol + 127) / 128), ngpt);
-    sw_solver_kernel<Real><<<grid, 128, 0, s>>>(ncol, nlay, ngpt, top_at_1, (const Real*)tau, (const Real*)ssa,
+    sw_solver_kernel<Real><<<grid, 128, 0, s>>>(ncol, nlay, ngpt, top_at_1, mu0_by_layer, (const Real*)tau, (const Real*)ssa,
             (const Real*)g, (const Real*)mu0, (const Real*)alb_dir, (const Real*)alb_dif, (const Real*)inc_dir,
             (const Real*)inc_dif, (Real*)flux_up, (Real*)flux_dn, (Real*)flux_dir, (Real*)work4);
     count_launch();
@@ -511,7 +621,8 @@ void launch_range_flag(size_t n, const void* x, double lo, double hi, int* d_fla
     template void launch_increment<Real>(bool, size_t, int, const BandLims&, void*, void*, void*, const void*, const void*, const void*, cudaStream_t); \
     template void launch_expand<Real>(int, const BandLims&, const void*, void*, cudaStream_t); \
     template void launch_lw_solver<Real>(int, int, int, int, int, const void*, const void*, const void*, const void*, const void*, const void*, void*, void*, const void*, void*, cudaStream_t); \
-    template void launch_sw_solver<Real>(int, int, int, int, const void*, const void*, const void*, const void*, const void*, const void*, const void*, const void*, void*, void*, void*, void*, cudaStream_t); \
+    template void launch_lw_solver_rescl<Real>(int, int, int, int, int, const void*, const void*, const void*, const void*, const void*, const void*, const void*, const void*, void*, void*, const void*, void*, void*, cudaStream_t); \
+    template void launch_sw_solver<Real>(int, int, int, int, int, const void*, const void*, const void*, const void*, const void*, const void*, const void*, const void*, void*, void*, void*, void*, cudaStream_t); \
     template void launch_sum_broadband<Real>(int, int, int, const void*, void*, cudaStream_t); \
     template void launch_sum_byband<Real>(int, int, const BandLims&, const void*, void*, cudaStream_t); \
     template void launch_net<Real>(size_t, const void*, const void*, void*, cudaStream_t); \

@@ -43,8 +43,13 @@ void launch_lw_solver(int ncol, int nlay, int ngpt, int top_at_1, int nmus, cons
                       const void* lev_src, const void* sfc_emis, const void* sfc_src, const void* inc_flux,
                       void* flux_up, void* flux_dn, const void* sfc_src_jac, void* flux_up_jac, cudaStream_t s);
 template<typename Real>
-void launch_sw_solver(int ncol, int nlay, int ngpt, int top_at_1, const void* tau, const void* ssa, const void* g,
-                      const void* mu0, const void* alb_dir, const void* alb_dif, const void* inc_dir,
+void launch_lw_solver_rescl(int ncol, int nlay, int ngpt, int top_at_1, int nmus, const void* tau, const void* ssa,
+                            const void* g, const void* lay_src, const void* lev_src, const void* sfc_emis,
+                            const void* sfc_src, const void* inc_flux, void* flux_up, void* flux_dn,
+                            const void* sfc_src_jac, void* flux_up_jac, void* work2, cudaStream_t s);
+template<typename Real>
+void launch_sw_solver(int ncol, int nlay, int ngpt, int top_at_1, int mu0_by_layer, const void* tau, const void* ssa,
+                      const void* g, const void* mu0, const void* alb_dir, const void* alb_dif, const void* inc_dir,
                       const void* inc_dif, void* flux_up, void* flux_dn, void* flux_dir, void* work4, cudaStream_t s);
 template<typename Real>
 void launch_sum_broadband(int ncol, int nlev, int ngpt, const void* gpt_flux, void* flux, cudaStream_t s);

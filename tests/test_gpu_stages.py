@@ -234,3 +234,102 @@ def test_cloud_optics_delta_scale_add_to(dtype):
             with pytest.raises(RuntimeError, match="incompatible band"):
                 bad = api.Optical_props_2str_gpu(atm.ncol, atm.nlay, api.Optical_props_gpu(lut.bnd_limits_wavenumber.T[:, :5]), dtype)
                 api.add_to(op, bad)
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("top_at_1", [False, True])
+def test_rte_lw_rescaled_stage(dtype, top_at_1):
+    """do_rescaling = true of rte_lw_solver_noscat (mo_rte_solver_kernels.F90:148-178,753-844): 2-stream
+    cloud properties in the longwave, 1 and 3 angles, g-point and broadband outputs, with the Jacobian."""
+    kd, lut = synthetic_kdist("lw"), synthetic_cloud_lut("lw")
+    atm = rce_atmosphere(33, 27, top_at_1=top_at_1, cloudy=True)
+    ref = oracle_lw(kd, atm)
+    og, st = ref["go"], ref["state"]
+    c = O.CloudOptics(lut).cloud_optics_2str(atm.lwp, atm.iwp, atm.rel, atm.dei)
+    tau, ssa, g = O.add_to_2str(og, st["tau"], np.zeros_like(st["tau"]), np.zeros_like(st["tau"]), *c)
+    assert ssa.max() > 0.3                                   # the clouds do scatter
+    go = api.Gas_optics_rrtmgp_gpu(kd, atm.vmr.keys(), dtype)
+    op = api.Optical_props_2str_gpu(atm.ncol, atm.nlay, go, dtype)
+    op.tau, op.ssa, op.g = A.from_numpy(tau, dtype), A.from_numpy(ssa, dtype), A.from_numpy(g, dtype)
+    src = api.Source_func_lw_gpu(atm.ncol, atm.nlay, go, dtype)
+    src.lay_source, src.lev_source = A.from_numpy(st["lay_src"], dtype), A.from_numpy(st["lev_src"], dtype)
+    src.sfc_source, src.sfc_source_jac = A.from_numpy(st["sfc_src"], dtype), A.from_numpy(st["sfc_src_jac"], dtype)
+    emis = A.from_numpy(atm.emis_sfc, dtype)
+    nlev, ngpt = atm.nlay + 1, go.get_ngpt()
+    tol = 1e-10 if dtype == torch.float64 else 1e-3
+    noscat_up, _ = O.rte_lw(og, tau, st["lay_src"], st["lev_src"], st["sfc_src"], atm.emis_sfc, top_at_1)
+    for n_ang in (1, 3):
+        rup, rdn, rjac = O.rte_lw(og, tau, st["lay_src"], st["lev_src"], st["sfc_src"], atm.emis_sfc, top_at_1,
+                                  n_gauss_angles=n_ang, sfc_src_jac=st["sfc_src_jac"], ssa=ssa, g=g)
+        up, dn, jac = A((atm.ncol, nlev, ngpt), dtype), A((atm.ncol, nlev, ngpt), dtype), A((atm.ncol, nlev), dtype)
+        up.t.fill_(-7.0); dn.t.fill_(-7.0)
+        api.Rte_lw_gpu.rte_lw(op, top_at_1, src, emis, None, up, dn, n_ang, src.sfc_source_jac, jac, do_rescaling=True)
+        assert np.max(np.abs(up.numpy() - rup)) < tol and np.max(np.abs(dn.numpy() - rdn)) < tol
+        assert np.max(np.abs(jac.numpy() - rjac)) < (1e-10 if dtype == torch.float64 else 1e-4)
+        bup, bdn = A((atm.ncol, nlev), dtype), A((atm.ncol, nlev), dtype)
+        api.Rte_lw_gpu.rte_lw(op, top_at_1, src, emis, None, bup, bdn, n_ang, do_rescaling=True)
+        assert np.max(np.abs(bup.numpy() - O.sum_broadband(rup))) < tol * 100
+        assert np.max(np.abs(bdn.numpy() - O.sum_broadband(rdn))) < tol * 100
+    assert np.max(np.abs(O.rte_lw(og, tau, st["lay_src"], st["lev_src"], st["sfc_src"], atm.emis_sfc, top_at_1,
+                                  ssa=ssa, g=g)[0] - noscat_up)) > 1e-3          # and the option is not a no-op
+    # without scattering the re-scaled kernel gives the noscat kernel's numbers (check_variants.F90:381-397)
+    op.ssa.t.zero_()
+    up0, dn0 = A((atm.ncol, nlev, ngpt), dtype), A((atm.ncol, nlev, ngpt), dtype)
+    api.Rte_lw_gpu.rte_lw(op, top_at_1, src, emis, None, up0, dn0, 1)
+    up1, dn1 = A((atm.ncol, nlev, ngpt), dtype), A((atm.ncol, nlev, ngpt), dtype)
+    api.Rte_lw_gpu.rte_lw(op, top_at_1, src, emis, None, up1, dn1, 1, do_rescaling=True)
+    assert np.max(np.abs(up0.numpy() - up1.numpy())) < tol and np.max(np.abs(dn0.numpy() - dn1.numpy())) < tol
+    # 1-scalar properties cannot be re-scaled
+    op1 = api.Optical_props_1scl_gpu(atm.ncol, atm.nlay, go, dtype)
+    with pytest.raises(RuntimeError, match="2-stream"):
+        api.Rte_lw_gpu.rte_lw(op1, top_at_1, src, emis, None, up0, dn0, 1, do_rescaling=True)
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("top_at_1", [False, True])
+def test_rte_sw_height_dependent_mu0(dtype, top_at_1):
+    """mu0 (ncol, nlay), the kernel's own shape (mo_rte_solver_kernels.F90:517,1061-1065,1117-1125):
+    twilight columns whose lower layers have the sun below the local horizon and, in the fp64 build, a column dark at
+    the top only.  The Fortran sends the beam through dark layers with the nominal mu0 = sqrt(epsilon(wp)), which is
+    1.5e-8 in a double build and 3.5e-4 in a single build: the direct flux INSIDE dark layers (and a beam entering
+    through a dark top, which is negative) depends on the build's precision in the reference itself, so the fp32
+    build is compared on what does not: diffuse fluxes everywhere, the direct flux outside the twilight columns."""
+    f64 = dtype == torch.float64
+    kd = synthetic_kdist("sw")
+    atm = rce_atmosphere(29, 23, top_at_1=top_at_1, night_fraction=0.1, cloudy=True)
+    ref = oracle_sw(kd, atm, synthetic_cloud_lut("sw"))
+    og = ref["go"]
+    rng = np.random.default_rng(11)
+    mu = np.tile(atm.mu0[:, None], (1, atm.nlay)) * rng.uniform(0.8, 1.2, (atm.ncol, atm.nlay))
+    mu = np.minimum(mu, 1.0)
+    low = slice(atm.nlay - 6, atm.nlay) if top_at_1 else slice(0, 6)
+    top = slice(0, 3) if top_at_1 else slice(atm.nlay - 3, atm.nlay)
+    mu[3:9, low] = -0.1
+    if f64:
+        mu[12, top] = -0.02
+    mu = np.asfortranarray(mu)
+    want = O.rte_sw(og, ref["tau"], ref["ssa"], ref["g"], mu, ref["toa"], atm.sfc_alb_dir, atm.sfc_alb_dif, top_at_1)
+    go = api.Gas_optics_rrtmgp_gpu(kd, atm.vmr.keys(), dtype)
+    op = api.Optical_props_2str_gpu(atm.ncol, atm.nlay, go, dtype)
+    op.tau, op.ssa, op.g = (A.from_numpy(ref[k], dtype) for k in ("tau", "ssa", "g"))
+    nlev, ngpt = atm.nlay + 1, go.get_ngpt()
+    up, dn, dr = (A((atm.ncol, nlev, ngpt), dtype) for _ in range(3))
+    args = (A.from_numpy(ref["toa"], dtype), A.from_numpy(atm.sfc_alb_dir, dtype), A.from_numpy(atm.sfc_alb_dif, dtype), None)
+    api.Rte_sw_gpu.rte_sw(op, top_at_1, A.from_numpy(mu, dtype), *args, up, dn, dr)
+    tol = 1e-10 if f64 else 2e-3
+    gu, gd, gr = up.numpy(), dn.numpy(), dr.numpy()
+    assert np.max(np.abs(gu - want[0])) < tol, "up"
+    assert np.max(np.abs((gd - gr) - (want[1] - want[2]))) < tol, "diffuse dn"
+    cols = slice(None) if f64 else np.r_[0:3, 9:atm.ncol]
+    assert np.max(np.abs(gr[cols] - want[2][cols])) < tol, "dir"
+    assert np.max(np.abs(gd[cols] - want[1][cols])) < tol, "dn"
+    assert np.max(np.abs(want[0] - ref["gpt_up"])) > 1e-2          # the layer values matter
+    # a constant field is the per-column call, bit for bit
+    const = np.asfortranarray(np.tile(atm.mu0[:, None], (1, atm.nlay)))
+    up2, dn2, dr2 = (A((atm.ncol, nlev, ngpt), dtype) for _ in range(3))
+    api.Rte_sw_gpu.rte_sw(op, top_at_1, A.from_numpy(const, dtype), *args, up2, dn2, dr2)
+    up1, dn1, dr1 = (A((atm.ncol, nlev, ngpt), dtype) for _ in range(3))
+    api.Rte_sw_gpu.rte_sw(op, top_at_1, A.from_numpy(atm.mu0, dtype), *args, up1, dn1, dr1)
+    assert torch.equal(up1.t, up2.t) and torch.equal(dn1.t, dn2.t) and torch.equal(dr1.t, dr2.t)
+    with pytest.raises(RuntimeError, match="mu0 must be"):
+        api.Rte_sw_gpu.rte_sw(op, top_at_1, A.from_numpy(const[:, :-1], dtype), *args, up2, dn2, dr2)
