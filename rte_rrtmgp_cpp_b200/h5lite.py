@@ -39,6 +39,7 @@ class _Dataset:
         self.symtab = None                  # old-style group: (btree, heap)
         self.link_heap = None               # dense links: (fractal heap, name index B-tree) addresses
         self.unsupported = None             # datatype class this reader does not decode
+        self.attrs: Dict[str, object] = {}  # compact attributes of decodable type (numbers, fixed-length strings)
 
 
 class File:
@@ -75,6 +76,12 @@ class File:
 
     def shape(self, name: str) -> Tuple[int, ...]:
         return self._dataset(name).shape
+
+    def attrs(self, name: str) -> Dict[str, object]:
+        """Attributes of a variable stored in its object header with a numeric or fixed-length string type."""
+        if name not in self.vars:
+            raise KeyError(f"{self.path}: no variable '{name}'")
+        return self._object(self.vars[name]).attrs
 
     def get(self, name: str) -> np.ndarray:
         """The variable in file (C) dimension order.  Fixed-length strings come back as bytes arrays ('S<n>')."""
@@ -227,6 +234,8 @@ class File:
                 if ver == 1 and ncd % 2:
                     q += 4
                 d.filters.append(fid)
+        elif mtype == 0x0C:                      # attribute (compact storage)
+            self._attribute(p, d)
         elif mtype == 0x06:                      # link
             name, addr = self._link(p)
             if addr is not None:
@@ -247,6 +256,28 @@ class File:
                 blocks.append((off + 4, ln - 8))
             else:
                 blocks.append((off, ln))
+
+    def _attribute(self, p: int, d: _Dataset) -> None:
+        b = self.b
+        ver = b[p]
+        nsz, tsz, ssz = struct.unpack_from("<HHH", b, p + 2)
+        q = p + 8 + (1 if ver == 3 else 0)
+        pad = (lambda n: (n + 7) // 8 * 8) if ver == 1 else (lambda n: n)
+        name = b[q:q + nsz].split(b"\0")[0].decode("utf-8", "replace"); q += pad(nsz)
+        dt = self._datatype(q); tq = q; q += pad(tsz)
+        sver, rank = b[q], b[q + 1]
+        sq = q + (8 if sver == 1 else 4)
+        shape = tuple(struct.unpack_from("<Q", b, sq + 8 * i)[0] for i in range(rank))
+        q += pad(ssz)
+        if dt is None:
+            return                                   # variable-length strings, references (DIMENSION_LIST ...): skipped
+        n = int(np.prod(shape)) if shape else 1
+        a = np.frombuffer(b[q:q + n * dt.itemsize], dtype=dt, count=n)
+        if dt.kind == "S":
+            v = [x.split(b"\0")[0].decode("utf-8", "replace") for x in a.tolist()]
+            d.attrs[name] = v[0] if n == 1 else v
+        else:
+            d.attrs[name] = a.reshape(shape).copy() if shape else a[0]
 
     def _datatype(self, p: int) -> Optional[np.dtype]:
         b = self.b

@@ -7,8 +7,10 @@ writes, so that the command-line driver (cli/test_rte_rrtmgp.cpp) can be exercis
   aerosol_optics.nc              <- AerosolLUTFile (schema: src_test/Radiation_solver.cpp:331-367)
   rte_rrtmgp_input.nc            <- Atmosphere     (schema: src_test/test_rte_rrtmgp.cpp:205-330,455-478)
   rte_rrtmgp_output.nc           -> dict of numpy arrays (schema: :300-311,394-439,559-630)
-scipy.io.netcdf_file writes CDF-1/CDF-2 only; the real rrtmgp-data files are netCDF-4 and have to be
-converted once with `nccopy -k cdf5` (no HDF5 library in this image)."""
+scipy.io.netcdf_file writes CDF-1/CDF-2 only.  The readers (read_kdist, read_cloud_lut, read_aerosol_lut,
+read_rfmip_input) take either format: netCDF classic through scipy, the netCDF-4/HDF5 files rrtmgp-data
+ships through h5lite (no HDF5 library in this image).  The C++ driver reads netCDF classic only and needs
+rrtmgp-data's files converted once with `nccopy -k cdf5`."""
 from __future__ import annotations
 
 from typing import Dict, Sequence
@@ -16,6 +18,7 @@ from typing import Dict, Sequence
 import numpy as np
 from scipy.io import netcdf_file
 
+from . import h5lite
 from .atmos import Atmosphere
 from .kdist import AerosolLUTFile, CloudLUTFile, KDistFile, STRING_LEN
 
@@ -170,3 +173,143 @@ def read_output(path: str) -> Dict[str, np.ndarray]:
         out[name] = a
     f.close()
     return out
+
+
+# ------------------------------------------------------------------------------------------
+# Readers, either on-disk format
+# ------------------------------------------------------------------------------------------
+class _Reader:
+    """get(name) -> array in file (C) dimension order; strings(name) -> stripped python strings."""
+
+    def __init__(self, path: str):
+        self.path = path
+        with open(path, "rb") as f:
+            magic = f.read(8)
+        if magic[:3] == b"CDF":
+            self.nc, self.h5 = netcdf_file(path, "r", mmap=False), None
+        elif magic == b"\x89HDF\r\n\x1a\n":
+            self.nc, self.h5 = None, h5lite.File(path)
+        else:
+            raise RuntimeError(f"{path}: neither netCDF classic nor netCDF-4/HDF5")
+
+    def __contains__(self, name: str) -> bool:
+        return name in (self.nc.variables if self.nc is not None else self.h5)
+
+    def get(self, name: str) -> np.ndarray:
+        if name not in self:
+            raise RuntimeError(f"{self.path}: variable '{name}' is missing")      # Netcdf_interface.h throws likewise
+        if self.nc is not None:
+            v = self.nc.variables[name]
+            return np.array(v.data if v.shape else v.getValue()).reshape(v.shape)
+        return self.h5.get(name)
+
+    def f64(self, name: str) -> np.ndarray:
+        return np.ascontiguousarray(self.get(name), dtype=np.float64)
+
+    def i32(self, name: str) -> np.ndarray:
+        return np.ascontiguousarray(self.get(name), dtype=np.int32)
+
+    def scalar(self, name: str) -> float:
+        return float(np.asarray(self.get(name)).reshape(-1)[0])
+
+    def strings(self, name: str):
+        a = self.get(name)
+        if a.dtype.kind == "S" and a.dtype.itemsize == 1:       # (n, string_len) char block
+            a = a.reshape(a.shape[0], -1)
+            rows = [b"".join(r.tolist()) for r in a]
+        elif a.dtype.kind == "S":
+            rows = a.reshape(-1).tolist()
+        else:
+            raise RuntimeError(f"{self.path}: '{name}' is not a character variable")
+        return [r.decode("ascii", "replace").replace("\0", " ").strip() for r in rows]
+
+    def attr(self, name: str, key: str):
+        if self.nc is not None:
+            v = getattr(self.nc.variables[name], key, None)
+            return v.decode() if isinstance(v, bytes) else v
+        return self.h5.attrs(name).get(key)
+
+    def close(self) -> None:
+        if self.nc is not None:
+            self.nc.close()
+
+
+def read_kdist(path: str) -> KDistFile:
+    """A gas-optics coefficient file (rrtmgp-gas-{lw,sw}-g*.nc or coefficients_{lw,sw}.nc) -> KDistFile; the variable
+    list is load_and_init_gas_optics's (src_test/Radiation_solver.cpp:78-243)."""
+    r = _Reader(path)
+    kw = dict(
+        gas_names=r.strings("gas_names"), key_species=r.i32("key_species"),
+        bnd_limits_wavenumber=r.f64("bnd_limits_wavenumber"), bnd_limits_gpt=r.i32("bnd_limits_gpt"),
+        press_ref=r.f64("press_ref"), temp_ref=r.f64("temp_ref"),
+        absorption_coefficient_ref_P=r.scalar("absorption_coefficient_ref_P"),
+        absorption_coefficient_ref_T=r.scalar("absorption_coefficient_ref_T"), press_ref_trop=r.scalar("press_ref_trop"),
+        vmr_ref=r.f64("vmr_ref"), kmajor=r.f64("kmajor"), kminor_lower=r.f64("kminor_lower"), kminor_upper=r.f64("kminor_upper"),
+        gas_minor=r.strings("gas_minor"), identifier_minor=r.strings("identifier_minor"))
+    for side in ("lower", "upper"):
+        kw["minor_gases_" + side] = r.strings("minor_gases_" + side)
+        kw["minor_limits_gpt_" + side] = r.i32("minor_limits_gpt_" + side)
+        kw["minor_scales_with_density_" + side] = r.i32("minor_scales_with_density_" + side)
+        kw["scale_by_complement_" + side] = r.i32("scale_by_complement_" + side)
+        kw["scaling_gas_" + side] = r.strings("scaling_gas_" + side)
+        kw["kminor_start_" + side] = r.i32("kminor_start_" + side)
+    if "totplnk" in r:                                                          # :189 the reference's own test
+        kw.update(totplnk=r.f64("totplnk"), plank_fraction=r.f64("plank_fraction"))
+    else:
+        kw.update(rayl_lower=r.f64("rayl_lower"), rayl_upper=r.f64("rayl_upper"),
+                  solar_source_quiet=r.f64("solar_source_quiet"), solar_source_facular=r.f64("solar_source_facular"),
+                  solar_source_sunspot=r.f64("solar_source_sunspot"), tsi_default=r.scalar("tsi_default"),
+                  mg_default=r.scalar("mg_default"), sb_default=r.scalar("sb_default"))
+    r.close()
+    return KDistFile(label=path, **kw)
+
+
+def read_cloud_lut(path: str) -> CloudLUTFile:
+    """rrtmgp-clouds-{lw,sw}.nc / cloud_coefficients_{lw,sw}.nc (src_test/Radiation_solver.cpp:286-326)."""
+    r = _Reader(path)
+    lut = CloudLUTFile(
+        bnd_limits_wavenumber=r.f64("bnd_limits_wavenumber"),
+        **{n: r.scalar(n) for n in ("radliq_lwr", "radliq_upr", "radliq_fac", "diamice_lwr", "diamice_upr", "diamice_fac")},
+        **{n: r.f64(n) for n in ("lut_extliq", "lut_ssaliq", "lut_asyliq", "lut_extice", "lut_ssaice", "lut_asyice")},
+        label=path)
+    r.close()
+    return lut
+
+
+def read_aerosol_lut(path: str) -> AerosolLUTFile:
+    """aerosol_optics.nc (src_test/Radiation_solver.cpp:331-367).  NOT rrtmgp-data's rrtmgp-aerosols-merra-*.nc: that is the
+    Fortran MERRA scheme's schema (aero_*_tbl), which the C++ reference does not read."""
+    r = _Reader(path)
+    lut = AerosolLUTFile(**{n: r.f64(n) for n in (
+        "mass_ext_sw_hydrophobic", "ssa_sw_hydrophobic", "asymmetry_sw_hydrophobic",
+        "mass_ext_sw_hydrophilic", "ssa_sw_hydrophilic", "asymmetry_sw_hydrophilic", "relative_humidity2")})
+    r.close()
+    return lut
+
+
+def read_rfmip_input(path: str, expt: int = 0):
+    """One experiment of the RFMIP clear-sky input (rrtmgp-data/examples/rfmip-clear-sky/inputs/multiple_input4MIPs_...nc)
+    as the arrays rfmip/rfmip_init.py:14-112 builds from it (site-major (100, 60|61), top first as in the file): the
+    pressure floor at the top (:34), mu0 = max(0, cos sza) (:52), tsi per site (:55), and the mole fractions of the
+    gases RFMIP_GASES lists, each multiplied by the factor in its `units` attribute as the recipe does (:82-103)."""
+    r = _Reader(path)
+
+    def unit(var):
+        return float(r.attr(var, "units"))
+
+    out = dict(play=r.f64("pres_layer"), plev=r.f64("pres_level"), tlay=r.f64("temp_layer")[expt], tlev=r.f64("temp_level")[expt],
+               tsfc=r.f64("surface_temperature")[expt], emis=r.f64("surface_emissivity"), albedo=r.f64("surface_albedo"),
+               mu0=np.maximum(0.0, np.cos(np.deg2rad(r.f64("solar_zenith_angle")))), tsi=r.f64("total_solar_irradiance"),
+               vmr={"h2o": r.f64("water_vapor")[expt] * unit("water_vapor"), "o3": r.f64("ozone")[expt] * unit("ozone")})
+    for gas, var in RFMIP_GASES:
+        out["vmr"][gas] = float(r.f64(var)[expt]) * unit(var)
+    out["plev"] = np.maximum(out["plev"], np.nextafter(1.005183574463, 1e8))
+    r.close()
+    return out
+
+
+# gas name in the k-distribution <- global-mean variable of the RFMIP file (rfmip/rfmip_init.py:82-103)
+RFMIP_GASES = (("co2", "carbon_dioxide_GM"), ("n2o", "nitrous_oxide_GM"), ("co", "carbon_monoxide_GM"), ("ch4", "methane_GM"),
+               ("o2", "oxygen_GM"), ("n2", "nitrogen_GM"), ("ccl4", "carbon_tetrachloride_GM"), ("cfc11", "cfc11_GM"),
+               ("cfc12", "cfc12_GM"), ("cfc22", "hcfc22_GM"), ("hfc143a", "hfc143a_GM"), ("hfc125", "hfc125_GM"),
+               ("hfc23", "hfc23_GM"), ("hfc32", "hfc32_GM"), ("hfc134a", "hfc134a_GM"), ("cf4", "cf4_GM"))
