@@ -1,0 +1,115 @@
+"""h5lite (netCDF-4/HDF5 reader) and the either-format readers of ncfiles: against the rrtmgp-data files of
+the reference mount where it exists (this container), against the committed fixture made from them everywhere."""
+import os
+
+import numpy as np
+import pytest
+
+import real_data as RD
+from rte_rrtmgp_cpp_b200 import h5lite, ncfiles
+from rte_rrtmgp_cpp_b200.kdist import synthetic_kdist, synthetic_cloud_lut, synthetic_aerosol_lut
+
+DATA = "/root/reference/rrtmgp-data"
+needs_mount = pytest.mark.skipif(not os.path.isdir(DATA), reason="reference mount absent (GPU box)")
+
+
+@needs_mount
+def test_reads_every_rrtmgp_data_file():
+    """superblock v0 (RFMIP input: object headers v1, dense links with holes left by renames) and v2 (LUTs, references);
+    contiguous and chunked+deflate datasets; the one variable-length string variable is refused loudly."""
+    import glob
+    files = sorted(glob.glob(DATA + "/*.nc") + glob.glob(DATA + "/examples/*/*/*.nc"))
+    assert len(files) >= 15
+    for p in files:
+        f = h5lite.File(p)
+        assert len(f.names()) >= 9
+        for n in f.names():
+            if n == "expt_label":
+                with pytest.raises(h5lite.H5Error, match="variable-length"):
+                    f.get(n)
+                continue
+            a = f.get(n)
+            assert a.shape == f.shape(n)
+            if a.dtype.kind == "f":
+                assert np.all(np.isfinite(a)), (p, n)
+    rld = h5lite.File(DATA + "/examples/rfmip-clear-sky/reference/rld_Efx_RTE-RRTMGP-181204_rad-irf_r1i1p1f1_gn.nc")
+    assert rld.shape("rld") == (18, 100, 61)           # (its attributes are variable-length strings: not decoded, skipped)
+    a = rld.get("rld")
+    assert a[0, :, 0].max() == 0.0 and 50.0 < a[0, :, -1].min() and a[0, :, -1].max() < 500.0     # TOA / surface
+    f = h5lite.File(DATA + "/examples/rfmip-clear-sky/inputs/multiple_input4MIPs_radiation_RFMIP_UColorado-RFMIP-1-2_none.nc")
+    assert len(f.names()) == 70 and f.attrs("carbon_dioxide_GM")["units"] == "1.e-6"
+    assert f.shape("pres_level") == (100, 61) and f.get("pres_level")[0, 0] == np.float32(0.01)
+
+
+@needs_mount
+def test_fixture_is_what_the_files_hold():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("mk", os.path.join(RD.HERE, "golden", "make_real_fixtures.py"))
+    mk = importlib.util.module_from_spec(spec); spec.loader.exec_module(mk)
+    z, now = RD.fixture(), mk.collect()
+    assert sorted(z.files) == sorted(now)
+    for k in z.files:
+        assert np.array_equal(z[k], now[k]) and z[k].dtype == now[k].dtype, k
+
+
+def test_fixture_contents():
+    z = RD.fixture()
+    for kind, nb in (("lw", 16), ("sw", 14)):
+        lut = RD.cloud_lut(z, kind)
+        assert lut.nbnd == nb and lut.lut_extliq.shape == (nb, 20) and lut.lut_extice.shape == (3, nb, 18)
+        assert (lut.radliq_lwr, lut.radliq_upr, lut.diamice_lwr, lut.diamice_upr) == (2.5, 21.5, 10.0, 180.0)
+        assert np.all(lut.lut_extliq > 0) and np.all((lut.lut_ssaliq > 0) & (lut.lut_ssaliq <= 1)) and np.all(np.abs(lut.lut_asyice) < 1)
+        # same dimensions as the synthetic stand-in the other tests use
+        syn = synthetic_cloud_lut(kind)
+        assert syn.lut_extliq.shape == lut.lut_extliq.shape and syn.lut_extice.shape == lut.lut_extice.shape
+    for e in (0, 3):
+        atm = RD.rfmip_atmosphere(z, e)
+        assert (atm.ncol, atm.nlay, atm.top_at_1) == (100, 60, True)
+        assert atm.plev[:, 0].min() == np.nextafter(1.005183574463, 1e8)        # rfmip_init.py:34
+        assert 0.0 <= atm.mu0.min() and atm.mu0.max() <= 1.0 and (atm.mu0 == 0).sum() > 10
+    a0, a3 = RD.rfmip_atmosphere(z, 0), RD.rfmip_atmosphere(z, 3)
+    assert abs(float(a0.vmr["co2"][0, 0]) - 397.54697e-6) < 1e-9 and float(a3.vmr["co2"][0, 0]) != float(a0.vmr["co2"][0, 0])
+
+
+def test_readers_round_trip_through_netcdf_classic(tmp_path):
+    for kind in ("lw", "sw"):
+        kd = synthetic_kdist(kind, 16)
+        ncfiles.write_kdist(kd, str(tmp_path / "k.nc"))
+        back = ncfiles.read_kdist(str(tmp_path / "k.nc"))
+        for k, v in vars(kd).items():
+            w = getattr(back, k)
+            if k == "label":
+                continue
+            if isinstance(v, np.ndarray):
+                assert v.shape == w.shape and np.array_equal(v, w), k
+            else:
+                assert v == w, k
+    lut = RD.cloud_lut(RD.fixture(), "sw")
+    ncfiles.write_cloud_lut(lut, str(tmp_path / "c.nc"))
+    back = ncfiles.read_cloud_lut(str(tmp_path / "c.nc"))
+    assert np.array_equal(back.lut_asyice, lut.lut_asyice) and back.radliq_fac == lut.radliq_fac
+    a = synthetic_aerosol_lut()
+    ncfiles.write_aerosol_lut(a, str(tmp_path / "a.nc"))
+    assert np.array_equal(ncfiles.read_aerosol_lut(str(tmp_path / "a.nc")).ssa_sw_hydrophilic, a.ssa_sw_hydrophilic)
+
+
+def test_errors_are_loud(tmp_path):
+    p = tmp_path / "x.nc"
+    p.write_bytes(b"not a netcdf file at all")
+    with pytest.raises(RuntimeError, match="neither netCDF classic nor"):
+        ncfiles.read_cloud_lut(str(p))
+    with pytest.raises(h5lite.H5Error, match="not an HDF5 file"):
+        h5lite.File(str(p))
+    ncfiles.write_aerosol_lut(synthetic_aerosol_lut(), str(p))
+    with pytest.raises(RuntimeError, match="lut_extliq|bnd_limits_wavenumber"):
+        ncfiles.read_cloud_lut(str(p))
+
+
+@needs_mount
+def test_real_cloud_lut_file_equals_fixture_through_reader():
+    z = RD.fixture()
+    for kind in ("lw", "sw"):
+        lut = ncfiles.read_cloud_lut(f"{DATA}/rrtmgp-clouds-{kind}.nc")
+        fix = RD.cloud_lut(z, kind)
+        for n in ("lut_extliq", "lut_ssaliq", "lut_asyliq", "lut_extice", "lut_ssaice", "lut_asyice", "bnd_limits_wavenumber"):
+            assert np.array_equal(getattr(lut, n), getattr(fix, n)), n

@@ -1,0 +1,84 @@
+"""Real inputs of rrtmgp-data (committed fixture tests/golden/rrtmgp_data.npz): the RFMIP clear-sky atmospheres and
+the cloud-optics LUTs the reference ships, through the numpy oracle and the reference's own compiled classes
+(oracle/_ref).  The gas-optics tables stay synthetic (rrtmgp-gas-*.nc are absent from the mount)."""
+import numpy as np
+import pytest
+
+import real_data as RD
+from helpers import oracle_lw, oracle_sw
+from oracle import oracle as O
+from oracle import ref as R
+from rte_rrtmgp_cpp_b200.atmos import allsky_atmosphere
+from rte_rrtmgp_cpp_b200.kdist import synthetic_kdist
+
+Z = RD.fixture()
+needs_ref = pytest.mark.skipif(not R.available(), reason="oracle/_ref/liboracle_ref.so not built")
+
+
+@needs_ref
+@pytest.mark.parametrize("expt", [0, 3])
+def test_rfmip_columns_oracle_matches_reference_classes_bitwise(expt):
+    atm = RD.rfmip_atmosphere(Z, expt, slice(0, 100, 9))          # 12 sites across the globe, day and night
+    for kind in ("lw", "sw"):
+        kd = synthetic_kdist(kind)
+        go, rf = O.GasOptics(kd, atm.vmr.keys()), R.RefGasOptics(kd, atm.vmr.keys())
+        col_dry = go.get_col_dry(np.broadcast_to(atm.vmr["h2o"], atm.play.shape), atm.plev)
+        assert np.array_equal(col_dry, rf.get_col_dry(atm.vmr["h2o"], atm.plev))
+        if kind == "lw":
+            a = go.gas_optics_lw(atm.play, atm.plev, atm.tlay, atm.tsfc, atm.vmr, col_dry, atm.tlev)
+            b = rf.gas_optics_lw(atm.play, atm.plev, atm.tlay, atm.tsfc, atm.vmr, col_dry, atm.tlev)
+            keys = ("tau", "lay_src", "lev_src", "sfc_src")
+        else:
+            a = go.gas_optics_sw(atm.play, atm.plev, atm.tlay, atm.vmr, col_dry)
+            b = rf.gas_optics_sw(atm.play, atm.plev, atm.tlay, atm.vmr, col_dry)
+            keys = ("tau", "ssa", "g", "toa_src")
+        for k in keys:
+            assert np.array_equal(a[k], b[k]), (kind, k)
+        if kind == "lw":
+            o = O.rte_lw(go, a["tau"], a["lay_src"], a["lev_src"], a["sfc_src"], atm.emis_sfc, atm.top_at_1)
+            r = rf.rte_lw(a["tau"], a["lay_src"], a["lev_src"], a["sfc_src"], atm.emis_sfc, atm.top_at_1, 1, False)
+        else:
+            o = O.rte_sw(go, a["tau"], a["ssa"], a["g"], atm.mu0, a["toa_src"], atm.sfc_alb_dir, atm.sfc_alb_dif, atm.top_at_1)
+            r = rf.rte_sw(a["tau"], a["ssa"], a["g"], atm.mu0, a["toa_src"], atm.sfc_alb_dir, atm.sfc_alb_dif, atm.top_at_1, False)
+        for x, y in zip(o, r):
+            assert np.array_equal(x, y), kind
+
+
+@needs_ref
+def test_real_cloud_lut_oracle_matches_reference_classes_bitwise():
+    atm = allsky_atmosphere(12, 30, random_clouds=True)
+    for kind in ("lw", "sw"):
+        kd, lut = synthetic_kdist(kind), RD.cloud_lut(Z, kind)
+        go, rf = O.GasOptics(kd, atm.vmr.keys()), R.RefGasOptics(kd, atm.vmr.keys())
+        co = O.CloudOptics(lut)
+        if kind == "lw":
+            st = go.gas_optics_lw(atm.play, atm.plev, atm.tlay, atm.tsfc, atm.vmr, tlev=atm.tlev)
+            ctau = co.cloud_optics_1scl(atm.lwp, atm.iwp, atm.rel, atm.dei)
+            r = rf.cloud_add(lut, 1, False, atm.lwp, atm.iwp, atm.rel, atm.dei, st["tau"])
+            assert ctau.max() > 1.0 and np.array_equal(ctau, r["ctau"])
+            assert np.array_equal(O.add_to_1scl(go, st["tau"], ctau), r["tau"])
+        else:
+            st = go.gas_optics_sw(atm.play, atm.plev, atm.tlay, atm.vmr)
+            for dl in (False, True):
+                c = co.cloud_optics_2str(atm.lwp, atm.iwp, atm.rel, atm.dei)
+                assert c[1].max() > 0.99                      # the real tables are near-conservative in the visible
+                if dl:
+                    c = O.delta_scale(*c)
+                t = O.add_to_2str(go, st["tau"], st["ssa"], st["g"], *c)
+                r = rf.cloud_add(lut, 2, dl, atm.lwp, atm.iwp, atm.rel, atm.dei, st["tau"], st["ssa"], st["g"])
+                for x, k in zip(c, ("ctau", "cssa", "cg")):
+                    assert np.array_equal(x, r[k]), k
+                for x, k in zip(t, ("tau", "ssa", "g")):
+                    assert np.array_equal(x, r[k]), k
+
+
+def test_rfmip_fluxes_are_physical():
+    """Synthetic tables, real columns: not the published fluxes, but energy bounds must hold for every site."""
+    atm = RD.rfmip_atmosphere(Z, 0)
+    lw = oracle_lw(synthetic_kdist("lw"), atm)
+    sw = oracle_sw(synthetic_kdist("sw"), atm)
+    sigma = 5.670374419e-8
+    assert np.all(lw["flux_dn"][:, 0] == 0.0)
+    assert np.all(lw["flux_up"][:, -1] < 1.02 * sigma * atm.tsfc ** 4) and np.all(lw["flux_up"][:, -1] > 0.5 * sigma * atm.tsfc ** 4)
+    night = atm.mu0 == 0
+    assert np.all(sw["flux_dn"][night] == 0.0) and np.all(sw["flux_up"][~night, 0] < sw["flux_dn"][~night, 0])

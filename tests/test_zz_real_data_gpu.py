@@ -1,0 +1,52 @@
+"""GPU parity on REAL inputs of rrtmgp-data (tests/golden/rrtmgp_data.npz): the 100 RFMIP clear-sky sites (60 layers,
+top first, day and night) and the cloud-optics LUTs the reference ships — the fused CUDA path through the C ABI
+against the CPU oracle (itself bit-exact against the reference's compiled classes on these inputs,
+tests/test_real_data.py).  Gas tables stay synthetic: rrtmgp-gas-*.nc are absent from the reference mount.
+Tolerances are BASELINE.json's: 1e-5 W/m2 fp64, 0.05 W/m2 fp32."""
+import numpy as np
+import pytest
+import torch
+
+import real_data as RD
+from helpers import oracle_lw, oracle_sw, as_f32_valued
+from rte_rrtmgp_cpp_b200 import api
+from rte_rrtmgp_cpp_b200.atmos import allsky_atmosphere
+from rte_rrtmgp_cpp_b200.kdist import synthetic_kdist
+
+pytestmark = pytest.mark.gpu
+Z = RD.fixture()
+TOL = {torch.float64: 1e-5, torch.float32: 0.05}
+LW_KEYS = ("flux_up", "flux_dn", "flux_net", "bnd_flux_up", "bnd_flux_dn", "bnd_flux_net")
+SW_KEYS = LW_KEYS + ("flux_dn_dir", "bnd_flux_dn_dir")
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("expt", [0, 3])
+def test_rfmip_sites_fused(expt, dtype):
+    atm = RD.rfmip_atmosphere(Z, expt)
+    if dtype == torch.float32:
+        atm = as_f32_valued(atm)
+    for kind, oracle, Solver, keys in (("lw", oracle_lw, api.Radiation_solver_longwave, LW_KEYS),
+                                       ("sw", oracle_sw, api.Radiation_solver_shortwave, SW_KEYS)):
+        kd = synthetic_kdist(kind)
+        ref = oracle(kd, atm)
+        out = Solver(kd, atm.vmr.keys(), dtype=dtype).solve_gpu(api.DeviceColumns(atm, dtype), switch_output_bnd_fluxes=True)
+        for k in keys:
+            d = np.max(np.abs(out[k].numpy() - ref[k]))
+            assert d <= TOL[dtype], f"expt {expt} {kind} {k}: max abs diff {d}"
+
+
+@pytest.mark.parametrize("delta", [True, False])
+def test_real_cloud_luts_fused(delta):
+    """fp64 build; the fp32 build's two-stream rearrangement is exercised on the synthetic LUT."""
+    atm = allsky_atmosphere(64, 72, random_clouds=True)
+    for kind, oracle, Solver, keys in (("lw", oracle_lw, api.Radiation_solver_longwave, LW_KEYS),
+                                       ("sw", oracle_sw, api.Radiation_solver_shortwave, SW_KEYS)):
+        kd, lut = synthetic_kdist(kind), RD.cloud_lut(Z, kind)
+        ref = oracle(kd, atm, lut) if kind == "lw" else oracle(kd, atm, lut, delta=delta)
+        sol = Solver(kd, atm.vmr.keys(), lut, torch.float64)
+        out = sol.solve_gpu(api.DeviceColumns(atm, torch.float64), switch_cloud_optics=True, switch_delta_cloud=delta,
+                            switch_output_bnd_fluxes=True)
+        for k in keys:
+            d = np.max(np.abs(out[k].numpy() - ref[k]))
+            assert d <= 1e-5, f"{kind} {k}: max abs diff {d}"
