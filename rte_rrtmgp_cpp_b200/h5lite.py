@@ -77,6 +77,30 @@ class File:
     def shape(self, name: str) -> Tuple[int, ...]:
         return self._dataset(name).shape
 
+    def dims(self, name: str) -> Tuple[str, ...]:
+        """netCDF dimension names of a variable, slowest first: through DIMENSION_LIST (object references to the
+        dimension scales), else _Netcdf4Coordinates / _Netcdf4Dimid; a dimension scale is its own dimension."""
+        a = self.attrs(name)
+        if a.get("CLASS") == "DIMENSION_SCALE" and len(self.shape(name)) == 1 and "DIMENSION_LIST" not in a:
+            return (name,)
+        by_addr = {addr: n for n, addr in self.vars.items()}
+        if "DIMENSION_LIST" in a:
+            return tuple(by_addr[r] for r in a["DIMENSION_LIST"])
+        if "_Netcdf4Coordinates" in a:
+            ids = {}
+            for n in self.vars:
+                an = self.attrs(n)
+                if an.get("CLASS") == "DIMENSION_SCALE" and "_Netcdf4Dimid" in an:
+                    ids[int(an["_Netcdf4Dimid"])] = n
+            return tuple(ids[int(i)] for i in np.atleast_1d(a["_Netcdf4Coordinates"]))
+        if not self.shape(name):
+            return ()
+        raise H5Error(f"'{name}': dimension names are not recorded in a form this reader decodes")
+
+    def is_pure_dimension(self, name: str) -> bool:
+        """A netCDF dimension without a coordinate variable (libnetcdf stores a placeholder dataset)."""
+        return str(self.attrs(name).get("NAME", "")).startswith("This is a netCDF dimension but not a netCDF variable")
+
     def attrs(self, name: str) -> Dict[str, object]:
         """Attributes of a variable stored in its object header with a numeric or fixed-length string type."""
         if name not in self.vars:
@@ -270,7 +294,15 @@ class File:
         shape = tuple(struct.unpack_from("<Q", b, sq + 8 * i)[0] for i in range(rank))
         q += pad(ssz)
         if dt is None:
-            return                                   # variable-length strings, references (DIMENSION_LIST ...): skipped
+            if name == "DIMENSION_LIST" and (b[tq] & 0x0F) == 9:
+                # one variable-length sequence of object references per dimension: the dimension scales' headers
+                n = int(np.prod(shape)) if shape else 1
+                refs = []
+                for i in range(n):
+                    ln, gaddr, gidx = struct.unpack_from("<IQI", b, q + 16 * i)
+                    refs.append(struct.unpack_from("<Q", self._global_heap_object(gaddr, gidx), 0)[0] if ln else None)
+                d.attrs["DIMENSION_LIST"] = refs
+            return                                   # other variable-length strings / references: skipped
         n = int(np.prod(shape)) if shape else 1
         a = np.frombuffer(b[q:q + n * dt.itemsize], dtype=dt, count=n)
         if dt.kind == "S":
@@ -278,6 +310,21 @@ class File:
             d.attrs[name] = v[0] if n == 1 else v
         else:
             d.attrs[name] = a.reshape(shape).copy() if shape else a[0]
+
+    def _global_heap_object(self, addr: int, index: int) -> bytes:
+        b = self.b
+        if b[addr:addr + 4] != b"GCOL":
+            raise H5Error("bad global heap collection")
+        size = struct.unpack_from("<Q", b, addr + 8)[0]
+        q, end = addr + 16, addr + size
+        while q + 16 <= end:
+            idx, _, _, osz = struct.unpack_from("<HHIQ", b, q)
+            if idx == 0:
+                break
+            if idx == index:
+                return b[q + 16:q + 16 + osz]
+            q += 16 + (osz + 7) // 8 * 8
+        raise H5Error("global heap object not found")
 
     def _datatype(self, p: int) -> Optional[np.dtype]:
         b = self.b

@@ -42,6 +42,19 @@ def test_reads_every_rrtmgp_data_file():
 
 
 @needs_mount
+def test_dimension_names():
+    """DIMENSION_LIST (object references through the global heap; the RFMIP file, written by an old library) and
+    _Netcdf4Coordinates / _Netcdf4Dimid (the newer LUT and all-sky files)."""
+    f = h5lite.File(DATA + "/examples/rfmip-clear-sky/inputs/multiple_input4MIPs_radiation_RFMIP_UColorado-RFMIP-1-2_none.nc")
+    assert f.dims("temp_level") == ("expt", "site", "level") and f.dims("pres_layer") == ("site", "layer")
+    assert f.dims("site") == ("site",) and f.is_pure_dimension("site") and not f.is_pure_dimension("pres_layer")
+    g = h5lite.File(DATA + "/rrtmgp-clouds-sw.nc")
+    assert g.dims("lut_extice") == ("nrghice", "nband", "nsize_ice") and g.dims("radliq_lwr") == ()
+    a = h5lite.File(DATA + "/examples/all-sky/reference/rrtmgp-allsky-sw.nc")
+    assert a.dims("sw_flux_dn") == ("lev", "col")
+
+
+@needs_mount
 def test_fixture_is_what_the_files_hold():
     import importlib.util
     spec = importlib.util.spec_from_file_location("mk", os.path.join(RD.HERE, "golden", "make_real_fixtures.py"))
