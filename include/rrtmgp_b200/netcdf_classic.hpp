@@ -5,9 +5,10 @@
 // driver makes on its Netcdf_file wrapper (include_test/Netcdf_interface.h:256-300):
 //   get_dimension_size, variable_exists, get_variable_dimensions, get_variable<T>(name[, dims]),
 //   add_dimension, add_variable<T>(name, dim names) + insert(values, start).
-// netCDF-4 files are HDF5 containers; this image has no HDF5 library, so such a file is rejected
-// with the conversion command (`nccopy -k cdf5 in.nc out.nc`).  Variable names, dimension names
-// and dimension orders are exactly the reference's, so a converted file is read unchanged.
+// netCDF-4 files are HDF5 containers: they are opened through hdf5_lite.hpp (read-only, no libhdf5) and
+// presented through the same calls, so the files the reference's python recipes write and rrtmgp-data
+// ships are read as they are.  Output is always written as netCDF classic (CDF-2), which libnetcdf and
+// netCDF4-python open transparently.
 //
 // On-disk layout (big-endian): magic "CDF" + version {1,2,5}; numrecs; dim_list; gatt_list;
 // var_list {name, dimids, vatt_list, nc_type, vsize, begin}; then the fixed-size variables and
@@ -22,6 +23,9 @@
 #include <string>
 #include <type_traits>
 #include <vector>
+#include <memory>
+#include <utility>
+#include "hdf5_lite.hpp"
 
 namespace rrtmgp_b200 { namespace nc {
 
@@ -92,6 +96,7 @@ struct Var
     uint64_t vsize = 0, begin = 0; bool record = false;
     std::vector<unsigned char> bytes;                                // create mode: big-endian payload
     uint64_t count = 0;                                              // create mode: number of elements
+    bool hdf5 = false;                                               // read through Netcdf_file::h5file
 };
 
 inline uint64_t pad4(const uint64_t n) { return (n + 3) & ~uint64_t(3); }
@@ -133,6 +138,15 @@ class Netcdf_file
         bool dimension_exists(const std::string& name) const
         { for (const auto& d : dims) if (d.name == name) return true; return false; }
         bool variable_exists(const std::string& name) const { return find(name) >= 0; }
+        std::vector<std::string> variable_names() const { std::vector<std::string> n; for (const auto& v : vars) n.push_back(v.name); return n; }
+        bool variable_is_char(const std::string& name) const { return var(name).type == nc::T_CHAR; }
+        // (dimension name, size) in file order, slowest first
+        std::vector<std::pair<std::string, int>> get_variable_dimension_list(const std::string& name) const
+        {
+            std::vector<std::pair<std::string, int>> l;
+            for (const int id : var(name).dimids) l.push_back({dims[id].name, (int)dim_len(id)});
+            return l;
+        }
         std::map<std::string, int> get_variable_dimensions(const std::string& name) const
         {
             std::map<std::string, int> m;
@@ -206,6 +220,8 @@ class Netcdf_file
         }
         uint64_t dim_len(const int id) const { return dims[id].len ? dims[id].len : numrecs; }
         void read_header();
+        void read_hdf5_header();
+        std::shared_ptr<h5::File> h5file;
         template<typename T> std::vector<T> read(const nc::Var& v) const;
 
         std::string file_name; Netcdf_mode mode; bool written = false;
@@ -256,9 +272,7 @@ inline void Netcdf_file::read_header()
     if (!in) throw std::runtime_error("netcdf: cannot open " + file_name);
     unsigned char magic[4] = {0, 0, 0, 0};
     in.read(reinterpret_cast<char*>(magic), 4);
-    if (in && magic[0] == 0x89 && magic[1] == 'H' && magic[2] == 'D' && magic[3] == 'F')
-        throw std::runtime_error("netcdf: " + file_name + " is a netCDF-4/HDF5 file; no HDF5 library is available in this build. "
-                                 "Convert it once with: nccopy -k cdf5 " + file_name + " converted.nc");
+    if (in && magic[0] == 0x89 && magic[1] == 'H' && magic[2] == 'D' && magic[3] == 'F') { in.close(); read_hdf5_header(); return; }
     if (!in || magic[0] != 'C' || magic[1] != 'D' || magic[2] != 'F' || (magic[3] != 1 && magic[3] != 2 && magic[3] != 5))
         throw std::runtime_error("netcdf: " + file_name + " is not a netCDF classic (CDF-1/2/5) file");
     version = magic[3];
@@ -308,9 +322,53 @@ inline void Netcdf_file::read_header()
     if (nrec == 1) recsize = one;
 }
 
+// netCDF-4: dimensions are the HDF5 dimension scales, variables the other datasets; a variable whose element type this
+// reader does not decode (variable-length strings) is left out, a variable whose dimension names are stored out of reach
+// (dense attribute storage) gets anonymous dimensions
+inline void Netcdf_file::read_hdf5_header()
+{
+    h5file = std::make_shared<h5::File>(file_name);
+    const std::vector<std::string> names = h5file->names();
+    for (const std::string& n : names)
+    {
+        const h5::Object& o = h5file->get(n);
+        if (o.is_dataset && o.is_scale && o.shape.size() == 1) { nc::Dim d; d.name = n; d.len = o.shape[0]; dims.push_back(d); }
+    }
+    const auto dim_id = [this](const std::string& n, const uint64_t len)
+    {
+        for (size_t i = 0; i < dims.size(); ++i) if (dims[i].name == n) return (int)i;
+        nc::Dim d; d.name = n; d.len = len; dims.push_back(d);
+        return (int)dims.size() - 1;
+    };
+    for (const std::string& n : names)
+    {
+        const h5::Object& o = h5file->get(n);
+        if (!o.is_dataset || o.pure_dimension || !o.has_type) continue;
+        nc::Var v; v.name = n; v.hdf5 = true;
+        const h5::Type& t = o.type;
+        if (t.cls == 1) v.type = t.size == 4 ? nc::T_FLOAT : nc::T_DOUBLE;
+        else if (t.cls == 0) v.type = t.size == 1 ? (t.is_signed ? nc::T_BYTE : nc::T_UBYTE) : t.size == 2 ? (t.is_signed ? nc::T_SHORT : nc::T_USHORT)
+                                    : t.size == 4 ? (t.is_signed ? nc::T_INT : nc::T_UINT) : (t.is_signed ? nc::T_INT64 : nc::T_UINT64);
+        else if (t.cls == 3 && t.size == 1) v.type = nc::T_CHAR;
+        else continue;
+        std::vector<std::string> dn;
+        try { dn = h5file->dims(n); }
+        catch (const std::runtime_error&) { dn.clear(); for (size_t i = 0; i < o.shape.size(); ++i) dn.push_back(n + "_dim" + std::to_string(i)); }
+        if (dn.size() != o.shape.size()) throw std::runtime_error("netcdf: " + file_name + ": \"" + n + "\" has " + std::to_string(o.shape.size()) +
+                                                                  " dimensions but names " + std::to_string(dn.size()));
+        v.count = 1;
+        for (size_t i = 0; i < dn.size(); ++i) { v.dimids.push_back(dim_id(dn[i], o.shape[i])); v.count *= o.shape[i]; }
+        for (size_t i = 0; i < dn.size(); ++i)
+            if (dims[v.dimids[i]].len != o.shape[i])      // an unlimited dimension: the variable's own extent counts
+                v.dimids[i] = dim_id(n + "_dim" + std::to_string(i), o.shape[i]);
+        vars.push_back(std::move(v));
+    }
+}
+
 template<typename T> inline std::vector<T> Netcdf_file::read(const nc::Var& v) const
 {
     if (mode != Netcdf_mode::Read) throw std::runtime_error("netcdf: " + file_name + " is open for writing");
+    if (v.hdf5) return h5file->read<T>(v.name);
     const size_t ts = nc::type_size(v.type);
     uint64_t per = 1;                                   // elements per record (record var) or in total
     for (size_t k = v.record ? 1 : 0; k < v.dimids.size(); ++k) per *= dims[v.dimids[k]].len;

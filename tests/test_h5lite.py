@@ -126,3 +126,51 @@ def test_real_cloud_lut_file_equals_fixture_through_reader():
         fix = RD.cloud_lut(z, kind)
         for n in ("lut_extliq", "lut_ssaliq", "lut_asyliq", "lut_extice", "lut_ssaice", "lut_asyice", "bnd_limits_wavenumber"):
             assert np.array_equal(getattr(lut, n), getattr(fix, n)), n
+
+
+@needs_mount
+def test_cpp_reader_agrees_with_python_reader_on_every_file(tmp_path):
+    """include/rrtmgp_b200/hdf5_lite.hpp behind Netcdf_file (what the command-line driver opens its files with):
+    variable list, dimension names and sizes, and order-sensitive checksums of every numeric variable."""
+    import glob
+    import shutil
+    import subprocess
+    if shutil.which("g++") is None:
+        pytest.skip("no g++")
+    root = os.path.dirname(RD.HERE)
+    exe = str(tmp_path / "h5_driver")
+    subprocess.run(["g++", "-O1", "-std=c++17", "-I" + os.path.join(root, "include"), os.path.join(RD.HERE, "cpp", "h5_driver.cpp"),
+                    "-o", exe, "-lz"], check=True)
+    files = sorted(glob.glob(DATA + "/*.nc") + glob.glob(DATA + "/examples/*/*/*.nc"))
+    checked = 0
+    for p in files:
+        out = subprocess.run([exe, p], check=True, capture_output=True, text=True).stdout.splitlines()
+        f = h5lite.File(p)
+        want = [n for n in f.names() if not f.is_pure_dimension(n) and n != "expt_label"]
+        got = {}
+        for line in out:
+            name, dims, rest = [x.strip() for x in line.split("|")]
+            got[name] = (dims, rest)
+        assert sorted(got) == sorted(want), p
+        for n in want:
+            a = f.get(n)
+            dims, rest = got[n]
+            sizes = tuple(int(x.split("=")[1]) for x in dims.split()) if dims else ()
+            assert sizes == a.shape, (p, n)
+            try:
+                names = f.dims(n)
+            except h5lite.H5Error:
+                names = None                       # attributes in dense storage: C++ names the dimensions <var>_dimN
+            if names is not None:
+                assert tuple(x.split("=")[0] for x in dims.split()) == names, (p, n)
+            if a.dtype.kind == "S":
+                assert rest == "char"
+                continue
+            v = a.astype(np.float64).reshape(-1)
+            w = (np.arange(v.size) % 97 + 1).astype(np.float64)
+            fields = dict(x.split("=") for x in rest.split())
+            assert int(fields["n"]) == v.size
+            assert abs(float(fields["sum"]) - v.sum()) <= 1e-9 * max(1.0, np.abs(v).sum()), (p, n)
+            assert abs(float(fields["wsum"]) - (v * w).sum()) <= 1e-9 * max(1.0, (np.abs(v) * w).sum()), (p, n)
+            checked += 1
+    assert checked > 200
