@@ -25,8 +25,8 @@ def build(force: bool = False) -> None:
         if not force and os.path.exists(out) and os.path.getmtime(out) >= newest:
             continue
         cmd = ["g++", "-std=c++17", "-O2", "-Wall", *defs, "-I" + inc, "-I" + os.path.join(CUDA, "include"), src, "-o", out,
-               "-L" + PKG, "-lrrtmgp_b200", "-L" + os.path.join(CUDA, "lib64"), "-lcudart",
-               "-Wl,-rpath,$ORIGIN/../rte_rrtmgp_cpp_b200"]
+               "-L" + PKG, "-lrrtmgp_b200", "-L" + os.path.join(CUDA, "lib64"), "-lcudart", "-lz",
+               "-Wl,-rpath,$ORIGIN/../rte_rrtmgp_cpp_b200"]      # zlib: deflate chunks of netCDF-4 files (hdf5_lite.hpp)
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("g++ failed for the command-line driver:\n" + r.stdout + r.stderr)

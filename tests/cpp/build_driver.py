@@ -38,12 +38,13 @@ def build_nc(force: bool = False) -> None:
     """Host-only checker of include/rrtmgp_b200/{netcdf_classic,coefficients}.hpp (no CUDA, no library)."""
     src = os.path.join(HERE, "nc_driver.cpp")
     inc = os.path.join(ROOT, "include", "rrtmgp_b200")
-    newest = max(os.path.getmtime(f) for f in (src, os.path.join(inc, "netcdf_classic.hpp"), os.path.join(inc, "coefficients.hpp"),
+    newest = max(os.path.getmtime(f) for f in (src, os.path.join(inc, "netcdf_classic.hpp"), os.path.join(inc, "hdf5_lite.hpp"),
+                                               os.path.join(inc, "coefficients.hpp"),
                                                os.path.join(ROOT, "include", "rrtmgp_b200_tables.h")))
     out = nc_path()
     if not force and os.path.exists(out) and os.path.getmtime(out) >= newest:
         return
-    r = subprocess.run(["g++", "-std=c++17", "-O1", "-fPIC", "-shared", "-Wall", "-I" + os.path.join(ROOT, "include"), src, "-o", out],
+    r = subprocess.run(["g++", "-std=c++17", "-O1", "-fPIC", "-shared", "-Wall", "-I" + os.path.join(ROOT, "include"), src, "-o", out, "-lz"],
                        capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("g++ failed for the netCDF driver:\n" + r.stdout + r.stderr)
