@@ -7,7 +7,8 @@
 // headers v1 and v2 (with continuation blocks), groups as symbol tables (B-tree v1 + local heap), compact links or
 // dense links (fractal heap + version-2 B-tree name index); datasets compact, contiguous or chunked (B-tree v1
 // index) with shuffle / deflate / fletcher32; fixed-point, IEEE float and fixed-length string element types;
-// netCDF dimension names through DIMENSION_LIST (object references in a global heap) or _Netcdf4Coordinates.
+// attributes compact or dense; netCDF dimension names through DIMENSION_LIST (object references in a global heap) or
+// _Netcdf4Coordinates.
 // Anything else throws std::runtime_error naming the feature.  Same structure as rte_rrtmgp_cpp_b200/h5lite.py,
 // which the tests check against every file of rrtmgp-data.
 #pragma once
@@ -302,6 +303,13 @@ class File
                     break;
                 }
                 case 0x0C: attribute(p, o); break;
+                case 0x15:                                                   // attributes in dense storage
+                {
+                    const int flags = b[p + 1];
+                    const size_t q = p + 2 + (flags & 1 ? 2 : 0);
+                    if (u64(q) != UNDEF) heap_objects(u64(q), u64(q + 8), 8, 0, [&](const uint64_t at) { attribute(at, o); });
+                    break;
+                }
                 case 0x06: { std::string n; uint64_t a; if (link(p, n, a)) o.links[n] = a; break; }
                 case 0x02:
                 {
@@ -397,6 +405,18 @@ class File
 
         void dense_links(const uint64_t heap, const uint64_t index, std::map<std::string, uint64_t>& out) const
         {
+            heap_objects(heap, index, 5, 4, [&](const uint64_t at)
+            {
+                std::string nm; uint64_t a;
+                if (link(at, nm, a)) out[nm] = a;
+            });
+        }
+
+        // calls `use(file address)` for every managed fractal-heap object a version-2 B-tree indexes; the heap id sits
+        // `hid_offset` bytes into each record (type 5, links: after the name hash; type 8, attributes: first)
+        void heap_objects(const uint64_t heap, const uint64_t index, const int want_type, const int hid_offset,
+                          const std::function<void(uint64_t)>& use) const
+        {
             if (!sig(heap, "FRHP")) throw err("bad fractal heap header");
             size_t p = heap + 5;
             const int idlen = u16(p), filt = u16(p + 2);
@@ -436,7 +456,7 @@ class File
             const int btype = b[index + 5]; const uint32_t node_size = u32(index + 6);
             const int rec_size = u16(index + 10), depth = u16(index + 12);
             const uint64_t root_node = u64(index + 16); const int nroot = u16(index + 24);
-            if (btype != 5 || rec_size != 4 + idlen) throw err("unexpected link name index");
+            if (btype != want_type || rec_size < hid_offset + idlen) throw err("unexpected version-2 B-tree record type");
             const int leaf_max = (int)((node_size - 10) / rec_size);
             const int nrec_bytes = (bits((uint64_t)leaf_max) + 7) / 8;
             std::function<void(uint64_t, int, int)> walk = [&](const uint64_t addr, const int n, const int level)
@@ -445,16 +465,15 @@ class File
                 if (!sig(addr, level == 0 ? "BTLF" : "BTIN")) throw err("bad version-2 B-tree node");
                 for (int i = 0; i < n; ++i)
                 {
-                    const size_t hid = addr + 6 + (size_t)i * rec_size + 4;
+                    const size_t hid = addr + 6 + (size_t)i * rec_size + hid_offset;
                     if ((b[hid] >> 4) & 3) throw err("huge / tiny fractal heap objects are not supported");
                     const uint64_t off = uN(hid + 1, off_bytes), len = uN(hid + 1 + off_bytes, len_bytes);
                     bool found = false;
                     for (const Block& k : blks)
                         if (k.off <= off && off < k.off + k.size)
                         {
-                            std::string nm; uint64_t a;
                             need(k.addr + (off - k.off), len);
-                            if (link(k.addr + (off - k.off), nm, a)) out[nm] = a;
+                            use(k.addr + (off - k.off));
                             found = true; break;
                         }
                     if (!found) throw err("fractal heap object outside every direct block");

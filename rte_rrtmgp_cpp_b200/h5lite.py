@@ -260,6 +260,13 @@ class File:
                 d.filters.append(fid)
         elif mtype == 0x0C:                      # attribute (compact storage)
             self._attribute(p, d)
+        elif mtype == 0x15:                      # attribute info: attributes in dense storage
+            flags = b[p + 1]
+            q = p + 2 + (2 if flags & 1 else 0)
+            heap, index = struct.unpack_from("<QQ", b, q)
+            if heap != UNDEF:
+                for at, _ in self._heap_objects(heap, index, 8, 0):
+                    self._attribute(at, d)
         elif mtype == 0x06:                      # link
             name, addr = self._link(p)
             if addr is not None:
@@ -369,6 +376,14 @@ class File:
     def _dense_links(self, heap: int, name_index: int):
         """Link messages of a group in "dense" storage: the version-2 B-tree `name_index` (record type 5: name hash +
         heap id) lists the managed objects of the fractal heap `heap`; each is one link message."""
+        for at, ln in self._heap_objects(heap, name_index, 5, 4):
+            name, addr = self._link(at)
+            if addr is not None:
+                yield name, addr
+
+    def _heap_objects(self, heap: int, name_index: int, want_type: int, hid_offset: int):
+        """(file address, length) of the managed fractal-heap objects a version-2 B-tree indexes; the heap id sits
+        `hid_offset` bytes into each record (type 5, links: after the hash; type 8, attributes: first)."""
         b = self.b
         if b[heap:heap + 4] != b"FRHP":
             raise H5Error("bad fractal heap header")
@@ -429,13 +444,13 @@ class File:
             raise H5Error("bad version-2 B-tree header")
         btype, node_size, rec_size, depth = struct.unpack_from("<BIHH", b, name_index + 5)
         root_node, nroot = struct.unpack_from("<QH", b, name_index + 16)
-        if btype != 5 or rec_size != 4 + idlen:
-            raise H5Error("unexpected link name index")
+        if btype != want_type or rec_size < hid_offset + idlen:
+            raise H5Error("unexpected version-2 B-tree record type")
         leaf_max = (node_size - 10) // rec_size
         nrec_bytes = (int(leaf_max).bit_length() + 7) // 8
 
         def records(addr, n):
-            return [b[addr + 6 + i * rec_size + 4: addr + 6 + (i + 1) * rec_size] for i in range(n)]
+            return [b[addr + 6 + i * rec_size + hid_offset: addr + 6 + i * rec_size + hid_offset + idlen] for i in range(n)]
 
         def walk(addr, n, level):
             if level == 0:
@@ -458,10 +473,7 @@ class File:
         if root_node == UNDEF:
             return
         for hid in walk(root_node, nroot, depth):
-            at, ln = managed(hid)
-            name, addr = self._link(at)
-            if addr is not None:
-                yield name, addr
+            yield managed(hid)
 
     def _symtab_links(self, btree: int, heap: int):
         b = self.b

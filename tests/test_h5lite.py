@@ -33,7 +33,8 @@ def test_reads_every_rrtmgp_data_file():
             if a.dtype.kind == "f":
                 assert np.all(np.isfinite(a)), (p, n)
     rld = h5lite.File(DATA + "/examples/rfmip-clear-sky/reference/rld_Efx_RTE-RRTMGP-181204_rad-irf_r1i1p1f1_gn.nc")
-    assert rld.shape("rld") == (18, 100, 61)           # (its attributes are variable-length strings: not decoded, skipped)
+    assert rld.shape("rld") == (18, 100, 61) and rld.attrs("rld")["units"] == "W m-2"      # 9 attributes: dense storage
+    assert rld.dims("rld") == ("expt", "site", "level")
     a = rld.get("rld")
     assert a[0, :, 0].max() == 0.0 and 50.0 < a[0, :, -1].min() and a[0, :, -1].max() < 500.0     # TOA / surface
     f = h5lite.File(DATA + "/examples/rfmip-clear-sky/inputs/multiple_input4MIPs_radiation_RFMIP_UColorado-RFMIP-1-2_none.nc")
@@ -157,12 +158,7 @@ def test_cpp_reader_agrees_with_python_reader_on_every_file(tmp_path):
             dims, rest = got[n]
             sizes = tuple(int(x.split("=")[1]) for x in dims.split()) if dims else ()
             assert sizes == a.shape, (p, n)
-            try:
-                names = f.dims(n)
-            except h5lite.H5Error:
-                names = None                       # attributes in dense storage: C++ names the dimensions <var>_dimN
-            if names is not None:
-                assert tuple(x.split("=")[0] for x in dims.split()) == names, (p, n)
+            assert tuple(x.split("=")[0] for x in dims.split()) == f.dims(n), (p, n)
             if a.dtype.kind == "S":
                 assert rest == "char"
                 continue
