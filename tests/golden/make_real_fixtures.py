@@ -8,6 +8,9 @@
   rfmip/...           experiment 0 (present-day) and 3 (4xCO2-like, other gas amounts) of the RFMIP clear-sky input
                       (examples/rfmip-clear-sky/inputs/multiple_input4MIPs_...nc) as rfmip/rfmip_init.py builds them
 
+  rfmip/<e>/pub_*     the PUBLISHED fluxes of those experiments (examples/rfmip-clear-sky/reference/r{ld,lu,sd,su}_Efx_...nc,
+                      float32 (site, level), level 0 = top): what the reference's own rfmip test compares with
+
 The gas-optics coefficient files (rrtmgp-gas-*.nc) are absent from the mount (.MISSING_LARGE_BLOBS), so the
 published RFMIP / all-sky reference fluxes stay out of reach; these fixtures put REAL cloud tables and REAL
 atmospheres through the oracle and the CUDA path instead of synthetic ones.
@@ -23,6 +26,7 @@ from rte_rrtmgp_cpp_b200 import ncfiles                        # noqa: E402
 
 DATA = "/root/reference/rrtmgp-data"
 RFMIP = DATA + "/examples/rfmip-clear-sky/inputs/multiple_input4MIPs_radiation_RFMIP_UColorado-RFMIP-1-2_none.nc"
+PUBLISHED = DATA + "/examples/rfmip-clear-sky/reference/{}_Efx_RTE-RRTMGP-181204_rad-irf_r1i1p1f1_gn.nc"
 LUT_VARS = ("bnd_limits_wavenumber", "radliq_lwr", "radliq_upr", "radliq_fac", "diamice_lwr", "diamice_upr", "diamice_fac",
             "lut_extliq", "lut_ssaliq", "lut_asyliq", "lut_extice", "lut_ssaice", "lut_asyice")
 EXPTS = (0, 3)
@@ -42,6 +46,12 @@ def collect():
                 out[f"rfmip/{e}/{k}"] = np.asarray(v, dtype=np.float32 if k not in ("plev",) else np.float64)
         for g, v in d["vmr"].items():
             out[f"rfmip/{e}/vmr/{g}"] = np.asarray(v, dtype=np.float32 if np.ndim(v) else np.float64)
+    for k in ("rld", "rlu", "rsd", "rsu"):
+        r = ncfiles._Reader(PUBLISHED.format(k))
+        a = r.get(k)
+        for e in EXPTS:
+            out[f"rfmip/{e}/pub_{k}"] = a[e]
+        r.close()
     return out
 
 

@@ -82,3 +82,22 @@ def test_rfmip_fluxes_are_physical():
     assert np.all(lw["flux_up"][:, -1] < 1.02 * sigma * atm.tsfc ** 4) and np.all(lw["flux_up"][:, -1] > 0.5 * sigma * atm.tsfc ** 4)
     night = atm.mu0 == 0
     assert np.all(sw["flux_dn"][night] == 0.0) and np.all(sw["flux_up"][~night, 0] < sw["flux_dn"][~night, 0])
+
+
+@pytest.mark.parametrize("expt", [0, 3])
+def test_rfmip_boundary_fluxes_match_the_published_files(expt):
+    """What the published RFMIP fluxes pin WITHOUT the gas tables: the down-welling shortwave at the top is
+    tsi * mu0 and the up-welling longwave at the surface is emissivity * Planck(t_sfc) + reflection, both independent of
+    the gas optics to first order.  Checks the whole input recipe (site order, level orientation, units, mu0, tsi
+    scaling, band-constant surface properties) against the reference's own published output."""
+    atm = RD.rfmip_atmosphere(Z, expt)
+    pub = {k: Z[f"rfmip/{expt}/pub_{k}"].astype(np.float64) for k in ("rld", "rlu", "rsd", "rsu")}
+    assert np.all(pub["rld"][:, 0] == 0.0)                                   # level 0 is the top, as in the inputs
+    sw = oracle_sw(synthetic_kdist("sw"), atm)
+    day = atm.mu0 > 0
+    assert day.sum() > 40 and np.all(pub["rsd"][~day, 0] == 0.0) and np.all(sw["flux_dn"][~day, 0] == 0.0)
+    assert np.max(np.abs(sw["flux_dn"][day, 0] / pub["rsd"][day, 0] - 1.0)) < 1e-4
+    lw = oracle_lw(synthetic_kdist("lw"), atm)
+    assert np.max(np.abs(lw["flux_up"][:, -1] / pub["rlu"][:, -1] - 1.0)) < 0.01
+    # and the synthetic tables are not the real ones: the interior differs (so the two checks above are not vacuous)
+    assert np.max(np.abs(lw["flux_dn"][:, -1] - pub["rld"][:, -1])) > 10.0
