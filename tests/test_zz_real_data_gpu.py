@@ -34,6 +34,14 @@ def test_rfmip_sites_fused(expt, dtype):
         for k in keys:
             d = np.max(np.abs(out[k].numpy() - ref[k]))
             assert d <= TOL[dtype], f"expt {expt} {kind} {k}: max abs diff {d}"
+        # the part of the PUBLISHED fluxes that does not depend on the gas tables (tests/test_real_data.py)
+        if kind == "sw":
+            day = atm.mu0 > 0
+            pub = Z[f"rfmip/{expt}/pub_rsd"].astype(np.float64)
+            assert np.max(np.abs(out["flux_dn"].numpy()[day, 0] / pub[day, 0] - 1.0)) < 1e-4
+        else:
+            pub = Z[f"rfmip/{expt}/pub_rlu"].astype(np.float64)
+            assert np.max(np.abs(out["flux_up"].numpy()[:, -1] / pub[:, -1] - 1.0)) < 0.01
 
 
 @pytest.mark.parametrize("delta", [True, False])
