@@ -11,6 +11,9 @@
   rfmip/<e>/pub_*     the PUBLISHED fluxes of those experiments (examples/rfmip-clear-sky/reference/r{ld,lu,sd,su}_Efx_...nc,
                       float32 (site, level), level 0 = top): what the reference's own rfmip test compares with
 
+  allsky/...          inputs and PUBLISHED fluxes of the all-sky example (examples/all-sky/reference/rrtmgp-allsky-{lw,sw}-no-aerosols.nc,
+                      float64 (lay|lev, col), bottom first): what allsky/allsky_init.py restates and allsky_run compares with
+
 The gas-optics coefficient files (rrtmgp-gas-*.nc) are absent from the mount (.MISSING_LARGE_BLOBS), so the
 published RFMIP / all-sky reference fluxes stay out of reach; these fixtures put REAL cloud tables and REAL
 atmospheres through the oracle and the CUDA path instead of synthetic ones.
@@ -51,6 +54,17 @@ def collect():
         a = r.get(k)
         for e in EXPTS:
             out[f"rfmip/{e}/pub_{k}"] = a[e]
+        r.close()
+    for kind in ("lw", "sw"):
+        r = ncfiles._Reader(f"{DATA}/examples/all-sky/reference/rrtmgp-allsky-{kind}-no-aerosols.nc")
+        for v in ("p_lay", "p_lev", "t_lay", "t_lev", "h2o", "o3", "lwp", "iwp", "rel", "rei"):
+            a = r.get(v)
+            if kind == "lw":
+                out[f"allsky/{v}"] = a
+            else:
+                assert np.array_equal(a, out[f"allsky/{v}"]), v             # the two files hold the same atmosphere
+        for v in (("lw_flux_up", "lw_flux_dn") if kind == "lw" else ("sw_flux_up", "sw_flux_dn", "sw_flux_dir")):
+            out[f"allsky/{v}"] = r.get(v)
         r.close()
     return out
 

@@ -101,3 +101,25 @@ def test_rfmip_boundary_fluxes_match_the_published_files(expt):
     assert np.max(np.abs(lw["flux_up"][:, -1] / pub["rlu"][:, -1] - 1.0)) < 0.01
     # and the synthetic tables are not the real ones: the interior differs (so the two checks above are not vacuous)
     assert np.max(np.abs(lw["flux_dn"][:, -1] - pub["rld"][:, -1])) > 10.0
+
+
+def test_allsky_recipe_and_boundary_fluxes_match_the_published_example():
+    """rte_rrtmgp_cpp_b200.atmos.allsky_atmosphere restates allsky/allsky_init.py; the all-sky example of rrtmgp-data
+    publishes the same atmosphere (written by the Fortran example) next to its fluxes.  Inputs agree to rounding (the
+    cloud fields exactly; only the top level pressure is floored differently by the two recipes), and the published
+    fluxes' table-independent parts are reproduced with the REAL cloud LUT over synthetic gas tables."""
+    g = lambda n: Z[f"allsky/{n}"].T                                          # (col, lay|lev), bottom first
+    atm = allsky_atmosphere(24, 72)
+    rel_err = lambda a, b: np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300))
+    assert rel_err(atm.play, g("p_lay")) < 2e-6 and rel_err(atm.plev[:, :-1], g("p_lev")[:, :-1]) < 2e-6
+    assert rel_err(atm.tlay, g("t_lay")) < 1e-7 and rel_err(atm.tlev, g("t_lev")) < 1e-7
+    assert rel_err(np.broadcast_to(atm.vmr["h2o"], (24, 72)), g("h2o")) < 1e-7
+    assert rel_err(np.broadcast_to(atm.vmr["o3"], (24, 72)), g("o3")) < 1e-5
+    for ours, name in ((atm.lwp, "lwp"), (atm.iwp, "iwp"), (atm.rel, "rel"), (atm.dei, "rei")):
+        assert np.array_equal(ours, g(name)), name
+    assert (g("lwp") > 0).sum() > 50 and (g("iwp") > 0).sum() > 50
+    sw = oracle_sw(synthetic_kdist("sw"), atm, RD.cloud_lut(Z, "sw"))
+    assert np.max(np.abs(sw["flux_dn"][:, -1] / g("sw_flux_dn")[:, -1] - 1.0)) < 1e-4          # tsi * mu0 at the top
+    assert np.max(np.abs(sw["flux_dn_dir"][:, -1] / g("sw_flux_dir")[:, -1] - 1.0)) < 1e-4
+    lw = oracle_lw(synthetic_kdist("lw"), atm, RD.cloud_lut(Z, "lw"))
+    assert np.max(np.abs(lw["flux_up"][:, 0] / g("lw_flux_up")[:, 0] - 1.0)) < 0.01            # emission at the surface
