@@ -29,14 +29,6 @@ namespace rb200 {
 #ifndef RB_SW_MINB64
 #define RB_SW_MINB64 3
 #endif
-// RB_SW_STAGES > 0: pass 2 reads the scratch strip back through a shared-memory ring filled by cp.async, that many layers
-// deep per thread (each thread copies and reads only its own 6 vectors: no block synchronisation).  cp.async completes
-// through a counting barrier, so the ring is truly N deep, while the register ring's loads share one scoreboard and every
-// wait drains all of them — yet measured SLOWER on B200 (SW pass 313 -> 319 ms at 2 stages, 332 ms at 3: the shared-memory
-// carve-out takes L1 from pass 1's table gathers).  0 = rotating register buffers (default).
-#ifndef RB_SW_STAGES
-#define RB_SW_STAGES 0
-#endif
 // L2 prefetch hints (see physics.cuh): the state two layers ahead helps a little (-1.5 %) since the prefetch was moved
 // behind the iteration's last load; strip lines ahead of pass 2 do not (this kernel is DRAM-bound: +1 % at 4 layers, +11 % at 8)
 #ifndef RB_SW_PFS
@@ -194,29 +186,9 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandLaunch<Real> L
 #pragma unroll
         for (int m = 0; m < 6; ++m) d[m] = ld_stream(w + m * T);
     };
-#if RB_SW_STAGES > 0
-    extern __shared__ __align__(128) unsigned char sw_stage_raw[];
-    V4<Real>* const stg = reinterpret_cast<V4<Real>*>(sw_stage_raw) + tid;        // [stage][word][thread]
-    auto issue = [&](int k, int d)
-    {
-        if (k >= 0)
-        {
-            const V4<Real>* w = scr + (size_t)k * 6 * T;
-#pragma unroll
-            for (int m = 0; m < 6; ++m) cp_async_v4(stg + (d * 6 + m) * T, w + m * T);
-        }
-        cp_async_commit();          // an empty group past the top keeps the pending count uniform
-    };
-#pragma unroll
-    for (int d = 0; d < RB_SW_STAGES; ++d) issue(nlay - 1 - d, d);
-#else
-    V4<Real> bufA[6], bufB[6];
+    V4<Real> bufA[6], bufB[6], bufC[6];
     ld6(bufA, nlay - 1);
-#ifndef RB_SW_RING2
-    V4<Real> bufC[6];
     ld6(bufB, nlay - 2);
-#endif
-#endif
     Real alb[4], src[4];
     {
         const Real adir = a.alb_dir[band + (size_t)P.nbnd * cg];
@@ -262,18 +234,6 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandLaunch<Real> L
             if (a.bnd_up) { a.bnd_up[o + nlev_stride * band] = su; a.bnd_dn[o + nlev_stride * band] = sd + a.bnd_dir[o + nlev_stride * band]; }
         }
     };
-#if RB_SW_STAGES > 0
-    for (int k = nlay - 1, d = 0; k >= 0; --k)
-    {
-        cp_async_wait<RB_SW_STAGES - 1>();           // the oldest group (layer k) has landed, the younger ones stay in flight
-        V4<Real> in[6];
-#pragma unroll
-        for (int m = 0; m < 6; ++m) in[m] = stg[(d * 6 + m) * T];
-        step(in);
-        issue(k - RB_SW_STAGES, d);                  // refill the stage just consumed
-        d = d + 1 == RB_SW_STAGES ? 0 : d + 1;
-    }
-#elif !defined(RB_SW_RING2)
     // three rotating buffers: two layers (192 B per thread) in flight while the third is consumed
     for (int k0 = nlay - 1; k0 >= 0; k0 -= 3)
     {
@@ -286,20 +246,8 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandLaunch<Real> L
         ld6(bufB, k0 - 4);
         step(bufC);
     }
-#else
-    for (int k0 = nlay - 1; k0 >= 0; k0 -= 2)
-    {
-        ld6(bufB, k0 - 1);
-        step(bufA);
-        if (k0 - 1 < 0) break;
-        ld6(bufA, k0 - 2);
-        step(bufB);
-    }
-#endif
     release_slot(a.slot_busy, slot);
 }
-
-template<typename Real> constexpr size_t sw_stage_bytes() { return (size_t)RB_SW_STAGES * 6 * FUSED_THREADS * sizeof(V4<Real>); }
 
 template<typename Real>
 void launch_sw_band(const DevPlan<Real>& P, const BandArgs& B, const TileState<Real>& st,
@@ -310,12 +258,8 @@ void launch_sw_band(const DevPlan<Real>& P, const BandArgs& B, const TileState<R
     const int lpc = (P.gw == 16 && B.ngb <= 8) ? 2 : P.gw / 4, cpb = FUSED_THREADS / lpc;
     const unsigned grid = (unsigned)((a.nc + cpb - 1) / cpb);
     const bool cloud = a.cld_tau != nullptr;
-    constexpr size_t smem = sw_stage_bytes<Real>();
     const BandLaunch<Real> L = make_band_launch<Real>(P, B, a, B.flav[0], B.flav[1], false, 6);
-#define RB_LAUNCH(LPC_, GW_, CL_, NE_) { \
-        static const cudaError_t attr_ = smem > 48 * 1024 ? cudaFuncSetAttribute(sw_band_kernel<Real, LPC_, GW_, CL_, NE_>, \
-                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) : cudaSuccess; (void)attr_; \
-        sw_band_kernel<Real, LPC_, GW_, CL_, NE_><<<grid, FUSED_THREADS, smem, s>>>(P, L, st, a); }
+#define RB_LAUNCH(LPC_, GW_, CL_, NE_) { sw_band_kernel<Real, LPC_, GW_, CL_, NE_><<<grid, FUSED_THREADS, 0, s>>>(P, L, st, a); }
 #define RB_NE(LPC_, GW_, CL_) { if (P.neta == 9) RB_LAUNCH(LPC_, GW_, CL_, 9) else RB_LAUNCH(LPC_, GW_, CL_, 0) }
 #define RB_CL(LPC_, GW_) { if (cloud) RB_NE(LPC_, GW_, true) else RB_NE(LPC_, GW_, false) }
     if (P.gw == 16) { if (lpc == 4) RB_CL(4, 16) else RB_CL(2, 16) }
@@ -334,13 +278,8 @@ template<typename Real> int sw_blocks_per_wave(int gw)
     int dev = 0, sms = 0, occ = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (sw_stage_bytes<Real>() > 48 * 1024)
-    {
-        cudaFuncSetAttribute(sw_band_kernel<Real, 4, 16, false, 9>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sw_stage_bytes<Real>());
-        cudaFuncSetAttribute(sw_band_kernel<Real, 2, 8, false, 9>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sw_stage_bytes<Real>());
-    }
-    if (gw == 16) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sw_band_kernel<Real, 4, 16, false, 9>, FUSED_THREADS, sw_stage_bytes<Real>());
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sw_band_kernel<Real, 2, 8, false, 9>, FUSED_THREADS, sw_stage_bytes<Real>());
+    if (gw == 16) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sw_band_kernel<Real, 4, 16, false, 9>, FUSED_THREADS, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sw_band_kernel<Real, 2, 8, false, 9>, FUSED_THREADS, 0);
     return sms * occ;
 }
 template int sw_blocks_per_wave<float>(int);

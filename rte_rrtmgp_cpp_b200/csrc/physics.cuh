@@ -126,21 +126,6 @@ template<typename Real, int LPC, bool LW> struct StatePrefetch
     }
 };
 
-// ---- cp.async (LDGSTS): 16-byte global -> shared copies completed through a counting barrier ("at most N groups
-// pending"), unlike plain loads, whose shared scoreboard makes every wait a full drain of everything in flight.
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
-{
-    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(s), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_v4(V4<float>* smem, const V4<float>* gmem) { cp_async16(smem, gmem); }
-__device__ __forceinline__ void cp_async_v4(V4<double>* smem, const V4<double>* gmem)
-{
-    cp_async16(smem, gmem); cp_async16((char*)smem + 16, (const char*)gmem + 16);
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template<int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
-
 // scratch strip of a CTA: layer k is W*T vectors = W*T*sizeof(V4)/128 lines; thread t requests lines t, t+T, ...
 template<typename Real, int W>
 __device__ __forceinline__ void prefetch_strip_layer(const V4<Real>* strip_thread0, int k)
