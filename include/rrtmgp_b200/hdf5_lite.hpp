@@ -58,17 +58,17 @@ class File
             in.read(reinterpret_cast<char*>(b.data()), n);
             static const unsigned char magic[8] = {0x89, 'H', 'D', 'F', '\r', '\n', 0x1a, '\n'};
             if (b.size() < 64 || std::memcmp(b.data(), magic, 8) != 0) throw err("not an HDF5 file");
-            const int ver = b[8];
+            const int ver = u8(8);
             uint64_t root;
             if (ver == 0 || ver == 1)
             {
-                if (b[13] != 8 || b[14] != 8) throw err("only 8-byte offsets and lengths are supported");
+                if (u8(13) != 8 || u8(14) != 8) throw err("only 8-byte offsets and lengths are supported");
                 const size_t p = 24 + (ver == 1 ? 4 : 0) + 4 * 8;
                 root = u64(p + 8);
             }
             else if (ver == 2 || ver == 3)
             {
-                if (b[9] != 8 || b[10] != 8) throw err("only 8-byte offsets and lengths are supported");
+                if (u8(9) != 8 || u8(10) != 8) throw err("only 8-byte offsets and lengths are supported");
                 root = u64(12 + 3 * 8);
             }
             else throw err("superblock version " + std::to_string(ver) + " is not supported");
@@ -128,8 +128,14 @@ class File
             if (!o.has_type) throw err("\"" + v + "\": datatype class " + std::to_string(o.unsupported_class) +
                                        " (variable-length / user-defined) is not supported");
             if (o.layout < 0) throw err("\"" + v + "\": incomplete object header");
-            uint64_t n = 1; for (const uint64_t s : o.shape) n *= s;
             const size_t isz = o.type.size;
+            uint64_t n = 1;
+            for (const uint64_t s : o.shape)
+            {
+                if (s != 0 && n > (uint64_t(1) << 40) / s) throw err("\"" + v + "\": implausible size (corrupt header?)");
+                n *= s;
+            }
+            if (isz == 0 || n > (uint64_t(1) << 40) / isz) throw err("\"" + v + "\": implausible size (corrupt header?)");
             std::vector<unsigned char> raw;
             const unsigned char* src = nullptr;
             if (o.layout == 1)
@@ -154,6 +160,7 @@ class File
 
         std::runtime_error err(const std::string& what) const { return std::runtime_error("hdf5: " + name + ": " + what); }
         void need(const uint64_t p, const uint64_t n) const { if (p > b.size() || n > b.size() - p) throw err("offset outside the file"); }
+        uint8_t u8(const size_t p) const { need(p, 1); return b[p]; }                     // every byte read is bounds-checked
         uint64_t uN(const size_t p, const int w) const { need(p, w); uint64_t v = 0; for (int i = w - 1; i >= 0; --i) v = (v << 8) | b[p + i]; return v; }
         uint64_t u64(const size_t p) const { return uN(p, 8); }
         uint32_t u32(const size_t p) const { return (uint32_t)uN(p, 4); }
@@ -186,7 +193,7 @@ class File
             std::vector<std::pair<uint64_t, uint64_t>> blocks;
             if (sig(addr, "OHDR"))
             {
-                const int flags = b[addr + 5];
+                const int flags = u8(addr + 5);
                 size_t p = addr + 6 + (flags & 0x20 ? 16 : 0) + (flags & 0x10 ? 4 : 0);
                 const int w = 1 << (flags & 3);
                 const uint64_t size = uN(p, w); p += w;
@@ -198,7 +205,7 @@ class File
                     need(q, blocks[bi].second);
                     while (q + 4 <= end)
                     {
-                        const int mtype = b[q]; const size_t msize = u16(q + 1);
+                        const int mtype = u8(q); const size_t msize = u16(q + 1);
                         q += 4 + (order ? 2 : 0);
                         if (q + msize > end) break;
                         message(mtype, q, o, blocks, true);
@@ -206,7 +213,7 @@ class File
                     }
                 }
             }
-            else if (b[addr] == 1)
+            else if (u8(addr) == 1)
             {
                 const int nmsg = u16(addr + 2); const uint32_t hsize = u32(addr + 8);
                 blocks.push_back({addr + 16, hsize});
@@ -229,7 +236,7 @@ class File
 
         bool datatype(const size_t p, Type& t) const
         {
-            t.cls = b[p] & 0x0F; t.size = u32(p + 4); t.big_endian = b[p + 1] & 1; t.is_signed = b[p + 1] & 0x08;
+            t.cls = u8(p) & 0x0F; t.size = u32(p + 4); t.big_endian = u8(p + 1) & 1; t.is_signed = u8(p + 1) & 0x08;
             if (t.cls == 0 || t.cls == 1) return t.size == 1 || t.size == 2 || t.size == 4 || t.size == 8;
             return t.cls == 3;
         }
@@ -240,7 +247,7 @@ class File
             {
                 case 0x01:
                 {
-                    const int ver = b[p], rank = b[p + 1];
+                    const int ver = u8(p), rank = u8(p + 1);
                     const size_t q = p + (ver == 1 ? 8 : 4);
                     o.shape.clear();
                     for (int i = 0; i < rank; ++i) o.shape.push_back(u64(q + 8 * i));
@@ -248,33 +255,33 @@ class File
                 }
                 case 0x03:
                     o.has_type = datatype(p, o.type);
-                    if (!o.has_type) o.unsupported_class = b[p] & 0x0F;
+                    if (!o.has_type) o.unsupported_class = u8(p) & 0x0F;
                     break;
                 case 0x05:
                 {
-                    const int ver = b[p];
-                    if ((ver == 1 || ver == 2) && (ver == 1 || b[p + 3])) { const uint32_t n = u32(p + 4); need(p + 8, n); o.fill.assign(b.begin() + p + 8, b.begin() + p + 8 + n); }
-                    else if (ver == 3 && (b[p + 1] & 0x20)) { const uint32_t n = u32(p + 2); need(p + 6, n); o.fill.assign(b.begin() + p + 6, b.begin() + p + 6 + n); }
+                    const int ver = u8(p);
+                    if ((ver == 1 || ver == 2) && (ver == 1 || u8(p + 3))) { const uint32_t n = u32(p + 4); need(p + 8, n); o.fill.assign(b.begin() + p + 8, b.begin() + p + 8 + n); }
+                    else if (ver == 3 && (u8(p + 1) & 0x20)) { const uint32_t n = u32(p + 2); need(p + 6, n); o.fill.assign(b.begin() + p + 6, b.begin() + p + 6 + n); }
                     break;
                 }
                 case 0x08:
                 {
-                    const int ver = b[p];
+                    const int ver = u8(p);
                     if (ver == 3)
                     {
-                        o.layout = b[p + 1];
+                        o.layout = u8(p + 1);
                         if (o.layout == 0) { const size_t n = u16(p + 2); need(p + 4, n); o.compact.assign(b.begin() + p + 4, b.begin() + p + 4 + n); }
                         else if (o.layout == 1) o.addr = u64(p + 2);
                         else if (o.layout == 2)
                         {
-                            const int nd = b[p + 2]; o.addr = u64(p + 3);
+                            const int nd = u8(p + 2); o.addr = u64(p + 3);
                             o.chunk.clear(); for (int i = 0; i + 1 < nd; ++i) o.chunk.push_back(u32(p + 11 + 4 * i));
                         }
                         else throw err("data layout class " + std::to_string(o.layout) + " is not supported");
                     }
                     else if (ver == 1 || ver == 2)
                     {
-                        const int nd = b[p + 1]; o.layout = b[p + 2];
+                        const int nd = u8(p + 1); o.layout = u8(p + 2);
                         size_t q = p + 8;
                         if (o.layout != 0) { o.addr = u64(q); q += 8; }
                         std::vector<uint32_t> dims; for (int i = 0; i < nd; ++i) dims.push_back(u32(q + 4 * i));
@@ -287,7 +294,7 @@ class File
                 }
                 case 0x0B:
                 {
-                    const int ver = b[p], nf = b[p + 1];
+                    const int ver = u8(p), nf = u8(p + 1);
                     size_t q = p + (ver == 1 ? 8 : 2);
                     for (int i = 0; i < nf; ++i)
                     {
@@ -305,7 +312,7 @@ class File
                 case 0x0C: attribute(p, o); break;
                 case 0x15:                                                   // attributes in dense storage
                 {
-                    const int flags = b[p + 1];
+                    const int flags = u8(p + 1);
                     const size_t q = p + 2 + (flags & 1 ? 2 : 0);
                     if (u64(q) != UNDEF) heap_objects(u64(q), u64(q + 8), 8, 0, [&](const uint64_t at) { attribute(at, o); });
                     break;
@@ -313,7 +320,7 @@ class File
                 case 0x06: { std::string n; uint64_t a; if (link(p, n, a)) o.links[n] = a; break; }
                 case 0x02:
                 {
-                    const int flags = b[p + 1];
+                    const int flags = u8(p + 1);
                     const size_t q = p + 2 + (flags & 1 ? 8 : 0);
                     if (u64(q) != UNDEF) { o.has_dense = true; o.dense_heap = u64(q); o.dense_index = u64(q + 8); }
                     break;
@@ -322,6 +329,7 @@ class File
                 case 0x10:
                 {
                     const uint64_t off = u64(p), len = u64(p + 8);
+                    if (blocks.size() > 4096 || len < 8) throw err("object header continuation chain is corrupt");
                     if (v2) { if (!sig(off, "OCHK")) throw err("bad object header continuation block"); blocks.push_back({off + 4, len - 8}); }
                     else blocks.push_back({off, len});
                     break;
@@ -332,19 +340,20 @@ class File
 
         void attribute(const size_t p, Object& o) const
         {
-            const int ver = b[p];
+            const int ver = u8(p);
             const size_t nsz = u16(p + 2), tsz = u16(p + 4), ssz = u16(p + 6);
             size_t q = p + 8 + (ver == 3 ? 1 : 0);
             const auto pad = [ver](const size_t n) { return ver == 1 ? (n + 7) / 8 * 8 : n; };
             need(q, nsz);
             std::string an(reinterpret_cast<const char*>(b.data() + q), nsz);
             an = an.substr(0, an.find('\0')); q += pad(nsz);
-            Type t; const bool ok = datatype(q, t); const int cls = b[q] & 0x0F; q += pad(tsz);
-            const int sver = b[q], rank = b[q + 1];
+            Type t; const bool ok = datatype(q, t); const int cls = u8(q) & 0x0F; q += pad(tsz);
+            const int sver = u8(q), rank = u8(q + 1);
             uint64_t n = 1; for (int i = 0; i < rank; ++i) n *= u64(q + (sver == 1 ? 8 : 4) + 8 * i);
             q += pad(ssz);
             if (an == "DIMENSION_LIST" && cls == 9)
             {
+                if (n > 64) throw err("attribute DIMENSION_LIST is implausibly long");
                 o.has_dim_refs = true; o.dim_refs.clear();
                 for (uint64_t i = 0; i < n; ++i)
                 {
@@ -363,9 +372,11 @@ class File
                 o.pure_dimension = std::string(reinterpret_cast<const char*>(b.data() + q), t.size)
                                        .compare(0, 52, "This is a netCDF dimension but not a netCDF variable") == 0;
             }
-            else if (an == "_Netcdf4Dimid" && ok && t.cls == 0) o.dimid = element<int>(b.data() + q, t);
+            else if (an == "_Netcdf4Dimid" && ok && t.cls == 0) { need(q, t.size); o.dimid = element<int>(b.data() + q, t); }
             else if (an == "_Netcdf4Coordinates" && ok && t.cls == 0)
             {
+                if (n > 64) throw err("attribute _Netcdf4Coordinates is implausibly long");
+                need(q, n * t.size);
                 o.coord_ids.clear();
                 for (uint64_t i = 0; i < n; ++i) o.coord_ids.push_back(element<int>(b.data() + q + i * t.size, t));
             }
@@ -389,9 +400,9 @@ class File
         // ---------------------------------------------------------------- groups
         bool link(const size_t p, std::string& n, uint64_t& addr) const
         {
-            const int flags = b[p + 1];
+            const int flags = u8(p + 1);
             size_t q = p + 2; int ltype = 0;
-            if (flags & 0x08) ltype = b[q++];
+            if (flags & 0x08) ltype = u8(q++);
             if (flags & 0x04) q += 8;
             if (flags & 0x10) q += 1;
             const int w = 1 << (flags & 3);
@@ -453,7 +464,7 @@ class File
                     }
             }
             if (!sig(index, "BTHD")) throw err("bad version-2 B-tree header");
-            const int btype = b[index + 5]; const uint32_t node_size = u32(index + 6);
+            const int btype = u8(index + 5); const uint32_t node_size = u32(index + 6);
             const int rec_size = u16(index + 10), depth = u16(index + 12);
             const uint64_t root_node = u64(index + 16); const int nroot = u16(index + 24);
             if (btype != want_type || rec_size < hid_offset + idlen) throw err("unexpected version-2 B-tree record type");
@@ -466,7 +477,7 @@ class File
                 for (int i = 0; i < n; ++i)
                 {
                     const size_t hid = addr + 6 + (size_t)i * rec_size + hid_offset;
-                    if ((b[hid] >> 4) & 3) throw err("huge / tiny fractal heap objects are not supported");
+                    if ((u8(hid) >> 4) & 3) throw err("huge / tiny fractal heap objects are not supported");
                     const uint64_t off = uN(hid + 1, off_bytes), len = uN(hid + 1 + off_bytes, len_bytes);
                     bool found = false;
                     for (const Block& k : blks)
@@ -494,11 +505,13 @@ class File
         {
             if (!sig(heap, "HEAP")) throw err("bad local heap");
             const uint64_t data = u64(heap + 24);
+            int visited = 0;
             std::function<void(uint64_t)> node = [&](const uint64_t addr)
             {
+                if (++visited > 100000) throw err("group B-tree does not end (corrupt file)");
                 if (sig(addr, "TREE"))
                 {
-                    if (b[addr + 4] != 0) throw err("group B-tree expected");
+                    if (u8(addr + 4) != 0) throw err("group B-tree expected");
                     const int used = u16(addr + 6);
                     for (int i = 0; i < used; ++i) node(u64(addr + 24 + 16 * (size_t)i + 8));
                 }
@@ -510,7 +523,8 @@ class File
                         const size_t q = addr + 8 + 40 * (size_t)i;
                         const uint64_t noff = u64(q), ohdr = u64(q + 8);
                         need(data + noff, 1);
-                        out[std::string(reinterpret_cast<const char*>(b.data() + data + noff))] = ohdr;
+                        const char* s0 = reinterpret_cast<const char*>(b.data() + data + noff);
+                        out[std::string(s0, strnlen(s0, b.size() - (size_t)(data + noff)))] = ohdr;
                     }
                 }
                 else throw err("bad group B-tree node");
@@ -534,11 +548,19 @@ class File
             if (o.chunk.size() != nd) throw err("chunk rank differs from the dataset's");
             std::vector<unsigned char> out = filled(o, n);
             if (o.addr == UNDEF) return out;
-            uint64_t cel = 1; for (const uint32_t c : o.chunk) cel *= c;
+            uint64_t cel = 1;
+            for (const uint32_t c : o.chunk)
+            {
+                if (c == 0 || cel > (uint64_t(1) << 32) / c) throw err("implausible chunk size (corrupt header?)");   // HDF5 caps chunks at 4 GiB
+                cel *= c;
+            }
+            if (cel * isz > (uint64_t(1) << 32)) throw err("implausible chunk size (corrupt header?)");
+            int visited = 0;
             std::function<void(uint64_t)> node = [&](const uint64_t addr)
             {
-                if (!sig(addr, "TREE") || b[addr + 4] != 1) throw err("bad chunk B-tree node");
-                const int level = b[addr + 5], used = u16(addr + 6);
+                if (++visited > 1000000) throw err("chunk B-tree does not end (corrupt file)");
+                if (!sig(addr, "TREE") || u8(addr + 4) != 1) throw err("bad chunk B-tree node");
+                const int level = u8(addr + 5), used = u16(addr + 6);
                 const size_t ksz = 8 + 8 * (nd + 1);
                 size_t q = addr + 24;
                 for (int e = 0; e < used; ++e, q += ksz + 8)
@@ -552,7 +574,7 @@ class File
                     {
                         if (mask & (1u << k)) continue;
                         const int f = o.filters[k];
-                        if (f == 3) raw.resize(raw.size() - 4);
+                        if (f == 3) { if (raw.size() < 4) throw err("short chunk"); raw.resize(raw.size() - 4); }
                         else if (f == 1)
                         {
                             std::vector<unsigned char> dec((size_t)(cel * isz));
