@@ -27,6 +27,22 @@ class H5Error(RuntimeError):
     pass
 
 
+def _guarded(fn):
+    """A corrupt file surfaces as H5Error, whatever low-level exception its bytes provoke."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapper(self, *a, **k):
+        try:
+            return fn(self, *a, **k)
+        except (H5Error, KeyError):
+            raise
+        except (struct.error, IndexError, ValueError, TypeError, OverflowError, UnicodeDecodeError, zlib.error,
+                MemoryError, RecursionError) as e:
+            raise H5Error(f"{getattr(self, 'path', '?')}: corrupt or unsupported HDF5 structure ({type(e).__name__}: {e})") from e
+    return wrapper
+
+
 class _Dataset:
     def __init__(self):
         self.shape: Tuple[int, ...] = ()
@@ -43,6 +59,7 @@ class _Dataset:
 
 
 class File:
+    @_guarded
     def __init__(self, path: str):
         with open(path, "rb") as f:
             self.b = f.read()
@@ -74,9 +91,11 @@ class File:
     def __contains__(self, name: str) -> bool:
         return name in self.vars
 
+    @_guarded
     def shape(self, name: str) -> Tuple[int, ...]:
         return self._dataset(name).shape
 
+    @_guarded
     def dims(self, name: str) -> Tuple[str, ...]:
         """netCDF dimension names of a variable, slowest first: through DIMENSION_LIST (object references to the
         dimension scales), else _Netcdf4Coordinates / _Netcdf4Dimid; a dimension scale is its own dimension."""
@@ -97,16 +116,19 @@ class File:
             return ()
         raise H5Error(f"'{name}': dimension names are not recorded in a form this reader decodes")
 
+    @_guarded
     def is_pure_dimension(self, name: str) -> bool:
         """A netCDF dimension without a coordinate variable (libnetcdf stores a placeholder dataset)."""
         return str(self.attrs(name).get("NAME", "")).startswith("This is a netCDF dimension but not a netCDF variable")
 
+    @_guarded
     def attrs(self, name: str) -> Dict[str, object]:
         """Attributes of a variable stored in its object header with a numeric or fixed-length string type."""
         if name not in self.vars:
             raise KeyError(f"{self.path}: no variable '{name}'")
         return self._object(self.vars[name]).attrs
 
+    @_guarded
     def get(self, name: str) -> np.ndarray:
         """The variable in file (C) dimension order.  Fixed-length strings come back as bytes arrays ('S<n>')."""
         d = self._dataset(name)
