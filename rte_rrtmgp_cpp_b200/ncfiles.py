@@ -159,6 +159,61 @@ def write_input(atm: Atmosphere, path: str, nx: int, ny: int, kind: str = "f8", 
     f.close()
 
 
+GAS_NAMES = ("h2o", "co2", "o3", "n2o", "co", "ch4", "o2", "n2", "ccl4", "cfc11", "cfc12", "cfc22", "hfc143a", "hfc125",
+             "hfc23", "hfc32", "hfc134a", "cf4", "no2")      # src_test/test_rte_rrtmgp.cpp:232-250
+
+
+def read_input(path: str, tsi_ref: float | None = None):
+    """rte_rrtmgp_input.nc (either format; written by the reference's rfmip_init.py / allsky_init.py / rcemip scripts or by
+    write_input) -> (Atmosphere, nx, ny), the way test_rte_rrtmgp.cpp:205-330,455-478 reads it: fields (lay|lev, y, x) ->
+    (ncol, n) with x fastest; vmr_<gas> scalar, (lay) or (lay, y, x), absent gases skipped; `tsi` (needs `tsi_ref`, the
+    k-distribution's own total solar irradiance) or `tsi_scaling` -> tsi_scaling, else 1."""
+    r = _Reader(path)
+    dims3 = r.get("p_lay").shape
+    if len(dims3) != 3:
+        raise RuntimeError(f"{path}: p_lay must be (lay, y, x)")
+    nlay, ny, nx = dims3
+    ncol = nx * ny
+    F = np.asfortranarray
+
+    def field(name):
+        a = r.f64(name)
+        return F(a.reshape(a.shape[0], ncol).T)
+
+    def surface(name):                           # (y, x, band) -> (band, ncol)
+        a = r.f64(name)
+        return F(a.reshape(ncol, -1).T)
+
+    def concentration(name):
+        a = r.f64(name)
+        if a.ndim == 0 or a.size == 1 and a.ndim <= 1 and a.shape in ((), (1,)):
+            return F(a.reshape(1, 1))
+        if a.ndim == 1 and a.shape[0] == nlay:
+            return F(a.reshape(1, nlay))
+        if a.shape == (nlay, ny, nx):
+            return F(a.reshape(nlay, ncol).T)
+        raise RuntimeError(f"Illegal dimensions of \"{name}\" in input")
+
+    vmr = {g: concentration("vmr_" + g) for g in GAS_NAMES if ("vmr_" + g) in r}
+    if "tsi" in r:
+        if tsi_ref is None:
+            raise RuntimeError(f"{path} holds `tsi`: pass tsi_ref (the k-distribution's total solar irradiance)")
+        tsi_scaling = r.f64("tsi").reshape(ncol) / tsi_ref
+    elif "tsi_scaling" in r:
+        tsi_scaling = r.f64("tsi_scaling").reshape(ncol)
+    else:
+        tsi_scaling = np.ones(ncol)
+    cloud = {n: (field(n) if n in r else None) for n in ("lwp", "iwp", "rel", "dei")}
+    aer = {n: concentration(n) for n in (f"aermr{i:02d}" for i in range(1, 12)) if n in r}
+    atm = Atmosphere(play=field("p_lay"), plev=field("p_lev"), tlay=field("t_lay"), tlev=field("t_lev"),
+                     tsfc=F(r.f64("t_sfc").reshape(ncol)), vmr=vmr, emis_sfc=surface("emis_sfc"),
+                     sfc_alb_dir=surface("sfc_alb_dir"), sfc_alb_dif=surface("sfc_alb_dif"),
+                     mu0=F(r.f64("mu0").reshape(ncol)), tsi_scaling=F(tsi_scaling),
+                     rh=field("rh") if "rh" in r else None, aermr=aer or None, **cloud)
+    r.close()
+    return atm, nx, ny
+
+
 def read_output(path: str) -> Dict[str, np.ndarray]:
     """rte_rrtmgp_output.nc -> arrays in the class-API layout: (lev|lay, y, x) -> (ncol, nlev|nlay),
     (band|gpt, lev|lay, y, x) -> (ncol, n, nband|ngpt), (gpt, y, x) -> (ncol, ngpt); band limits as stored."""

@@ -206,3 +206,24 @@ def test_cpp_reader_survives_corrupt_files(tmp_path):
         codes[r.returncode] = codes.get(r.returncode, 0) + 1
     assert set(codes) <= {0, 1}, codes
     assert codes.get(1, 0) > 10                                    # corruption is noticed
+
+
+def test_read_input_round_trip(tmp_path):
+    """ncfiles.read_input mirrors the driver's reading of rte_rrtmgp_input.nc (test_rte_rrtmgp.cpp:205-330,455-478)."""
+    from rte_rrtmgp_cpp_b200.atmos import rce_atmosphere, add_aerosols
+    for atm, nx, ny in ((rce_atmosphere(6, 5), 3, 2), (add_aerosols(rce_atmosphere(8, 7, cloudy=True, top_at_1=True)), 2, 4)):
+        p = str(tmp_path / "rte_rrtmgp_input.nc")
+        ncfiles.write_input(atm, p, nx, ny, tsi_ref=1360.0)
+        with pytest.raises(RuntimeError, match="tsi_ref"):
+            ncfiles.read_input(p)
+        back, bx, by = ncfiles.read_input(p, tsi_ref=1360.0)
+        assert (bx, by) == (nx, ny) and back.top_at_1 == atm.top_at_1
+        for k in ("play", "plev", "tlay", "tlev", "tsfc", "emis_sfc", "sfc_alb_dir", "sfc_alb_dif", "mu0", "lwp", "iwp", "rel", "dei", "rh"):
+            a, b = getattr(atm, k), getattr(back, k)
+            assert (a is None) == (b is None), k
+            if a is not None:
+                assert np.array_equal(np.asarray(a), b), k
+        assert np.allclose(back.tsi_scaling, atm.tsi_scaling, rtol=1e-15)
+        assert sorted(back.vmr) == sorted(atm.vmr)
+        for g in atm.vmr:
+            assert np.array_equal(np.atleast_2d(atm.vmr[g]), back.vmr[g]), g
