@@ -58,3 +58,26 @@ def test_real_cloud_luts_fused(delta):
         for k in keys:
             d = np.max(np.abs(out[k].numpy() - ref[k]))
             assert d <= 1e-5, f"{kind} {k}: max abs diff {d}"
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("kind", ["lw", "sw"])
+def test_rfmip_sites_interpolation_indices_bit_exact(kind, dtype):
+    """SURVEY T1 on the real RFMIP columns: jtemp, jpress, jeta, tropo bit for bit against the oracle."""
+    from oracle import oracle as O
+    A = api.Array_gpu
+    kd = synthetic_kdist(kind)
+    atm = RD.rfmip_atmosphere(Z, 0)
+    if dtype == torch.float32:
+        atm = as_f32_valued(atm)
+    go = api.Gas_optics_rrtmgp_gpu(kd, atm.vmr.keys(), dtype)
+    cols = api.DeviceColumns(atm, dtype)
+    col_dry = A((atm.ncol, atm.nlay), dtype)
+    go.get_col_dry(col_dry, cols.gas_concs.get_vmr("h2o"), cols.plev)
+    cd = col_dry.numpy().astype(np.float64)
+    out = go.interpolation(cols.play, cols.tlay, col_dry, cols.gas_concs)
+    st = O.GasOptics(kd, atm.vmr.keys())._gas_taus(O.F(atm.play), O.F(atm.plev), O.F(atm.tlay), atm.vmr, O.F(cd))
+    for k in ("jtemp", "jpress", "jeta"):
+        assert np.array_equal(out[k].numpy(), st[k]), k
+    assert np.array_equal(out["tropo"].numpy() != 0, st["tropo"] != 0)
+    assert 0.2 < (st["tropo"] != 0).mean() < 0.8                # both sides of the tropopause are exercised
