@@ -5,8 +5,8 @@ the on-disk format is read directly:
 
   superblock v0/v1 (symbol-table groups: B-tree v1 + local heap, object header v1) and v2/v3 (object header
   v2, link messages compact or "dense" in a fractal heap); datasets contiguous, compact or chunked (B-tree v1
-  chunk index) with the deflate / shuffle / fletcher32 filters; fixed-point, IEEE float and fixed-length
-  string element types.
+  chunk index) with the deflate / shuffle / fletcher32 filters; fixed-point, IEEE float, fixed-length and
+  variable-length string element types; attributes compact or dense.
 
 Only what netCDF-4 writes is handled; anything else raises H5Error naming the feature (never a silent wrong
 read).  Variables are returned in the file's (C, row-major) dimension order, like Netcdf_interface.h does
@@ -55,6 +55,7 @@ class _Dataset:
         self.symtab = None                  # old-style group: (btree, heap)
         self.link_heap = None               # dense links: (fractal heap, name index B-tree) addresses
         self.unsupported = None             # datatype class this reader does not decode
+        self.vlen_string = False            # variable-length strings: elements are global-heap references
         self.attrs: Dict[str, object] = {}  # compact attributes of decodable type (numbers, fixed-length strings)
 
 
@@ -144,6 +145,8 @@ class File:
             return self._read_chunked(d)
         if len(raw) < nbytes:
             raise H5Error(f"{name}: short read")
+        if d.vlen_string:
+            return self._vlen_strings(raw, n).reshape(d.shape)
         return np.frombuffer(raw, dtype=d.dtype, count=n).reshape(d.shape).copy()
 
     # ------------------------------------------------------------------ objects
@@ -215,7 +218,10 @@ class File:
         elif mtype == 0x03:                      # datatype
             d.dtype = self._datatype(p)
             if d.dtype is None:
-                d.unsupported = b[p] & 0x0F
+                if (b[p] & 0x0F) == 9 and (b[p + 1] & 0x0F) == 1:      # variable-length string (netCDF NC_STRING)
+                    d.vlen_string, d.dtype = True, np.dtype("V16")
+                else:
+                    d.unsupported = b[p] & 0x0F
         elif mtype == 0x05:                      # fill value
             ver = b[p]
             if ver in (1, 2):
@@ -339,6 +345,13 @@ class File:
             d.attrs[name] = v[0] if n == 1 else v
         else:
             d.attrs[name] = a.reshape(shape).copy() if shape else a[0]
+
+    def _vlen_strings(self, raw: bytes, n: int) -> np.ndarray:
+        out = np.empty(n, dtype=object)
+        for i in range(n):
+            ln, gaddr, gidx = struct.unpack_from("<IQI", raw, 16 * i)
+            out[i] = self._global_heap_object(gaddr, gidx)[:ln].decode("utf-8", "replace") if ln else ""
+        return out
 
     def _global_heap_object(self, addr: int, index: int) -> bytes:
         b = self.b

@@ -5,7 +5,7 @@
 
   cloud_{lw,sw}/...   the cloud-optics LUT variables of rrtmgp-clouds-{lw,sw}.nc the reference reads
                       (src_test/Radiation_solver.cpp:286-326), as stored (float32 / float64)
-  rfmip/...           experiment 0 (present-day) and 3 (4xCO2-like, other gas amounts) of the RFMIP clear-sky input
+  rfmip/...           experiment 0 ("Present day (PD)") and 3 ("future": other gas amounts) of the RFMIP clear-sky input
                       (examples/rfmip-clear-sky/inputs/multiple_input4MIPs_...nc) as rfmip/rfmip_init.py builds them
 
   rfmip/<e>/pub_*     the PUBLISHED fluxes of those experiments (examples/rfmip-clear-sky/reference/r{ld,lu,sd,su}_Efx_...nc,
