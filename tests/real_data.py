@@ -26,6 +26,14 @@ def cloud_lut(z, kind: str) -> CloudLUTFile:
         label=f"rrtmgp-clouds-{kind}.nc")
 
 
+def default_tsi(kd) -> float:
+    """Gas_optics_rrtmgp::get_tsi of the default solar source (src/Gas_optics_rrtmgp.cpp:745-756): what the driver
+    divides the input file's `tsi` by (test_rte_rrtmgp.cpp)."""
+    s = (kd.solar_source_quiet + (kd.mg_default - 0.1495954) * kd.solar_source_facular
+         + (kd.sb_default - 0.00066696) * kd.solar_source_sunspot)
+    return float(np.sum(s))
+
+
 def rfmip_atmosphere(z, expt: int, sites=slice(None), tsi_ref: float = 1360.85, nbnd_lw: int = 16, nbnd_sw: int = 14) -> Atmosphere:
     """The sites of one RFMIP experiment as the reference's driver sees them after rfmip_init.py: band-constant surface
     emissivity / albedo (rfmip_init.py:42-50), tsi_scaling = tsi / the k-distribution's tsi (test_rte_rrtmgp.cpp)."""

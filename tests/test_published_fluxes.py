@@ -1,0 +1,50 @@
+"""the published RFMIP clear-sky fluxes (rrtmgp-data/examples/rfmip-clear-sky/reference, in the committed
+fixture for experiments 0 and 3) within the reference's own tolerance of 5.8e-2 W/m2 — needs the REAL gas-optics
+coefficient files, which are absent from the reference mount (.MISSING_LARGE_BLOBS).  Point RRTMGP_DATA at a
+directory holding rrtmgp-gas-lw-g256.nc and rrtmgp-gas-sw-g224.nc (netCDF-4 as shipped, or classic) and these run;
+until then they are skipped, and tests/test_real_data.py pins what the published files pin without the tables."""
+import os
+
+import numpy as np
+import pytest
+
+import real_data as RD
+from helpers import oracle_lw, oracle_sw
+from rte_rrtmgp_cpp_b200 import ncfiles
+
+DIR = os.environ.get("RRTMGP_DATA", "/root/reference/rrtmgp-data")
+LW, SW = os.path.join(DIR, "rrtmgp-gas-lw-g256.nc"), os.path.join(DIR, "rrtmgp-gas-sw-g224.nc")
+needs_tables = pytest.mark.skipif(not (os.path.exists(LW) and os.path.exists(SW)),
+                                  reason="real gas-optics coefficient files not mounted (set RRTMGP_DATA)")
+TOL = 5.8e-2            # W/m2, the reference's rfmip comparison
+Z = RD.fixture()
+
+
+def _check(lw, sw, expt):
+    pub = {k: Z[f"rfmip/{expt}/pub_{k}"].astype(np.float64) for k in ("rld", "rlu", "rsd", "rsu")}
+    for got, k in ((lw["flux_dn"], "rld"), (lw["flux_up"], "rlu"), (sw["flux_dn"], "rsd"), (sw["flux_up"], "rsu")):
+        d = np.max(np.abs(np.asarray(got) - pub[k]))
+        assert d <= TOL, f"expt {expt} {k}: max abs diff {d} W/m2"
+
+
+@needs_tables
+@pytest.mark.parametrize("expt", [0, 3])
+def test_oracle_reproduces_published_rfmip_fluxes(expt):
+    kl, ks = ncfiles.read_kdist(LW), ncfiles.read_kdist(SW)
+    atm = RD.rfmip_atmosphere(Z, expt, tsi_ref=RD.default_tsi(ks), nbnd_lw=kl.nbnd, nbnd_sw=ks.nbnd)
+    _check(oracle_lw(kl, atm), oracle_sw(ks, atm), expt)
+
+
+@needs_tables
+@pytest.mark.gpu
+@pytest.mark.parametrize("expt", [0, 3])
+def test_cuda_path_reproduces_published_rfmip_fluxes(expt):
+    import torch
+    from rte_rrtmgp_cpp_b200 import api
+    kl, ks = ncfiles.read_kdist(LW), ncfiles.read_kdist(SW)
+    atm = RD.rfmip_atmosphere(Z, expt, tsi_ref=RD.default_tsi(ks), nbnd_lw=kl.nbnd, nbnd_sw=ks.nbnd)
+    for dtype in (torch.float64, torch.float32):
+        cols = api.DeviceColumns(atm, dtype)
+        lw = api.Radiation_solver_longwave(kl, atm.vmr.keys(), dtype=dtype).solve_gpu(cols)
+        sw = api.Radiation_solver_shortwave(ks, atm.vmr.keys(), dtype=dtype).solve_gpu(cols)
+        _check({k: v.numpy() for k, v in lw.items()}, {k: v.numpy() for k, v in sw.items()}, expt)
