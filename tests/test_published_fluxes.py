@@ -48,3 +48,19 @@ def test_cuda_path_reproduces_published_rfmip_fluxes(expt):
         lw = api.Radiation_solver_longwave(kl, atm.vmr.keys(), dtype=dtype).solve_gpu(cols)
         sw = api.Radiation_solver_shortwave(ks, atm.vmr.keys(), dtype=dtype).solve_gpu(cols)
         _check({k: v.numpy() for k, v in lw.items()}, {k: v.numpy() for k, v in sw.items()}, expt)
+
+
+@needs_tables
+def test_oracle_reproduces_published_allsky_fluxes():
+    """rrtmgp-allsky-{lw,sw}-no-aerosols.nc: the all-sky example (24 columns x 72 layers, liquid and ice clouds, real cloud
+    LUTs, delta scaling in the shortwave) as allsky/allsky_init.py sets it up."""
+    from rte_rrtmgp_cpp_b200.atmos import allsky_atmosphere
+    kl, ks = ncfiles.read_kdist(LW), ncfiles.read_kdist(SW)
+    atm = allsky_atmosphere(24, 72)
+    lw = oracle_lw(kl, atm, RD.cloud_lut(Z, "lw"))
+    sw = oracle_sw(ks, atm, RD.cloud_lut(Z, "sw"))
+    g = lambda n: Z[f"allsky/{n}"].T
+    for got, k in ((lw["flux_up"], "lw_flux_up"), (lw["flux_dn"], "lw_flux_dn"), (sw["flux_up"], "sw_flux_up"),
+                   (sw["flux_dn"], "sw_flux_dn"), (sw["flux_dn_dir"], "sw_flux_dir")):
+        d = np.max(np.abs(got - g(k)))
+        assert d <= TOL, f"{k}: max abs diff {d} W/m2"
