@@ -335,6 +335,14 @@ long long rrtmgp_b200_launch_count(void);
 int rrtmgp_b200_profile(int enable, double* lw_ms, long long* lw_launches, double* sw_ms,
                         long long* sw_launches);
 
+/* ---- Multi-GPU: columns are independent, so N processes (one per GPU) each run the calls
+ * above on a contiguous shard of the x-fastest flattened domain (src_test/test_rte_rrtmgp.cpp:217);
+ * the library holds no communicator and makes no collective call.  This is the partition rule
+ * (shards differ by at most one column; HOST function, no device needed): rank r of `world` owns
+ * columns [*c0, *c1).  The host model gathers the flux slabs with its own MPI / NCCL;
+ * rte_rrtmgp_cpp_b200/shard.py does it with torch.distributed for bench.py. */
+int rrtmgp_b200_shard_bounds(long long ncol, int world, int rank, long long* c0, long long* c1);
+
 #ifdef __cplusplus
 }
 #endif

@@ -227,6 +227,15 @@ int rrtmgp_b200_set_fused_path(rrtmgp_b200_gas_optics* g, int path)
 }
 long long rrtmgp_b200_launch_count(void) { return g_launches.load(); }
 
+int rrtmgp_b200_shard_bounds(long long ncol, int world, int rank, long long* c0, long long* c1)
+{
+    return guarded([&] {
+        if (ncol < 0 || world < 1 || rank < 0 || rank >= world || !c0 || !c1) throw ArgError("shard_bounds: bad ncol / world / rank");
+        *c0 = (long long)((__int128)rank * ncol / world);
+        *c1 = (long long)((__int128)(rank + 1) * ncol / world);
+    }, false);
+}
+
 int rrtmgp_b200_gas_optics_create(const rrtmgp_b200_kdist_file* kd, int n_avail, const char* names,
                                   int string_len, int dtype, rrtmgp_b200_gas_optics** out)
 {

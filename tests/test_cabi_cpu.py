@@ -105,3 +105,22 @@ def test_aerosol_table_argument_errors_need_no_device():
     rc = capi.lib().rrtmgp_b200_aerosol_optics_create(C.byref(a), capi.F64, C.byref(h))
     assert rc == capi.E_ARG and b"hydrophobic" in capi.lib().rrtmgp_b200_last_error() and not h.value
     assert capi.lib().rrtmgp_b200_aerosol_optics_nband(None) == -1
+
+
+def test_shard_bounds_is_the_python_partition():
+    """rrtmgp_b200_shard_bounds (HOST function; the partition a C/C++ host uses per rank) == shard.shard_bounds."""
+    import ctypes as C
+    from rte_rrtmgp_cpp_b200 import capi
+    from rte_rrtmgp_cpp_b200.shard import shard_bounds
+    L = capi.lib()
+    a, b = C.c_longlong(), C.c_longlong()
+    for ncol in (0, 1, 7, 100, 1048576, 3 * 10 ** 12 + 5):
+        for world in (1, 2, 3, 8):
+            prev = 0
+            for r in range(world):
+                assert L.rrtmgp_b200_shard_bounds(ncol, world, r, C.byref(a), C.byref(b)) == 0
+                assert (a.value, b.value) == shard_bounds(ncol, world, r) and a.value == prev
+                prev = b.value
+            assert prev == ncol
+    assert L.rrtmgp_b200_shard_bounds(10, 2, 2, C.byref(a), C.byref(b)) == capi.E_ARG
+    assert b"shard_bounds" in L.rrtmgp_b200_last_error()
