@@ -76,6 +76,11 @@ class File
             vars = g.links;
             if (g.has_dense) dense_links(g.dense_heap, g.dense_index, vars);
             if (g.has_symtab) symtab_links(g.symtab_btree, g.symtab_heap, vars);
+            // libnetcdf stores a variable whose name clashes with a dimension it does not span as "_nc4_non_coord_<name>"
+            static const std::string non_coord = "_nc4_non_coord_";
+            std::map<std::string, uint64_t> renamed;
+            for (const auto& kv : vars) renamed[kv.first.compare(0, non_coord.size(), non_coord) == 0 ? kv.first.substr(non_coord.size()) : kv.first] = kv.second;
+            vars.swap(renamed);
             for (const auto& kv : vars) objs[kv.first] = object(kv.second);
         }
 

@@ -21,6 +21,7 @@ from typing import Dict, List, Optional, Tuple
 import numpy as np
 
 UNDEF = 0xFFFFFFFFFFFFFFFF
+NON_COORD = "_nc4_non_coord_"
 
 
 class H5Error(RuntimeError):
@@ -83,7 +84,9 @@ class File:
         else:
             raise H5Error(f"superblock version {ver} is not supported")
         self._root = self._object(self.root)
-        self.vars: Dict[str, int] = dict(self._group_links(self._root))
+        # libnetcdf stores a variable whose name clashes with a dimension it does not span as "_nc4_non_coord_<name>"
+        self.vars: Dict[str, int] = {(n[len(NON_COORD):] if n.startswith(NON_COORD) else n): a
+                                     for n, a in self._group_links(self._root)}
 
     # ------------------------------------------------------------------ public
     def names(self) -> List[str]:
