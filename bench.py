@@ -63,6 +63,7 @@ def _cpu_worker(job):
     seed, ncols, nlay, block, cloudy = job
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ["ORACLE_REF_FAST"] = "1"          # the -O3 build of the reference classes (oracle/Makefile ref_fast): timing only
     from rte_rrtmgp_cpp_b200.atmos import rce_atmosphere
     from rte_rrtmgp_cpp_b200.kdist import synthetic_kdist
     from oracle import ref as R
@@ -88,7 +89,7 @@ def _cpu_worker(job):
             O.rte_lw(glw, st["tau"], st["lay_src"], st["lev_src"], st["sfc_src"], a.emis_sfc, a.top_at_1, broadband=True)
             ss = gsw.gas_optics_sw(a.play, a.plev, a.tlay, a.vmr)
             O.rte_sw(gsw, ss["tau"], ss["ssa"], ss["g"], a.mu0, ss["toa_src"], a.sfc_alb_dir, a.sfc_alb_dif, a.top_at_1, broadband=True)
-    return time.perf_counter() - t0, use_ref
+    return time.perf_counter() - t0, use_ref, (R.FLAGS["fast" if R.fast_selected() else "parity"] if use_ref else "gcc -O2 -ffp-contract=off (port)")
 
 
 def cpu_baseline(nlay: int, cols_per_core: int, cores: int | None = None):
@@ -106,7 +107,7 @@ def cpu_baseline(nlay: int, cols_per_core: int, cores: int | None = None):
     use_ref = all(r[1] for r in res)
     units = cores * cols_per_core * (256 + 224)
     return dict(value=units / tmax, unit="column-gpts/s", cores=cores,
-                kind="reference" if use_ref else "port",
+                kind="reference" if use_ref else "port", build_flags=res[0][2],
                 sample=f"{cores * cols_per_core} seeded S-RCE columns x {nlay} layers, LW g256 + SW g224, fp64, "
                        f"{cores} processes x {cols_per_core} columns in blocks of {block}; compute time max over "
                        f"processes {tmax:.1f} s (pool wall {wall:.1f} s)",

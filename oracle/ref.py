@@ -17,18 +17,26 @@ from rte_rrtmgp_cpp_b200.kdist import STRING_LEN
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _PATH = os.path.join(_HERE, "_ref", "liboracle_ref.so")
+# `make -C oracle ref_fast`: the same sources at the reference's release optimisation level (-O3 -march=x86-64-v3 -DNDEBUG).
+# TIMING ONLY — bench.py's CPU legs select it with ORACLE_REF_FAST=1; parity tests always use the -O2 -ffp-contract=off build.
+_PATH_FAST = os.path.join(_HERE, "_ref", "liboracle_ref_fast.so")
+FLAGS = {"parity": "g++ -O2 -ffp-contract=off", "fast": "g++ -O3 -march=x86-64-v3 -DNDEBUG"}
 _lib = None
 c_dbl_p = C.POINTER(C.c_double)
 
 
+def fast_selected() -> bool:
+    return os.environ.get("ORACLE_REF_FAST") == "1" and os.path.exists(_PATH_FAST)
+
+
 def available() -> bool:
-    return os.path.exists(_PATH)
+    return os.path.exists(_PATH_FAST if fast_selected() else _PATH)
 
 
 def lib():
     global _lib
     if _lib is None:
-        _lib = C.CDLL(_PATH)
+        _lib = C.CDLL(_PATH_FAST if fast_selected() else _PATH)
         _lib.ref_last_error.restype = C.c_char_p
     return _lib
 

@@ -62,6 +62,101 @@ def solve(atm, kd_lw, kd_sw, gases, dtype="f32", reps=3):
     return dict(lw_ms=ms_lw.value, sw_ms=ms_sw.value, lw_up=outs[0], lw_dn=outs[1], sw_up=outs[2], sw_dn=outs[3], sw_dir=outs[4])
 
 
+class RefCuda:
+    """Stage-level access to the reference's own CUDA classes and kernels (refcuda_shim.cu `refcuda_stage_*`):
+    the reference-authored implementation of rows a5-a9/a15/a17 that can run on the GPU box.  Used by
+    tests/test_oracle_vs_refcuda.py to pin the C restatement of the Fortran kernels."""
+
+    def __init__(self, kd_lw, kd_sw, gases, dtype="f64"):
+        from rte_rrtmgp_cpp_b200.ctables import pack_kdist, pack_strings
+        from rte_rrtmgp_cpp_b200.kdist import STRING_LEN
+        self._pack_strings, self._len = pack_strings, STRING_LEN
+        self.L = C.CDLL(path(dtype))
+        self.L.refcuda_last_error.restype = C.c_char_p
+        assert self.L.refcuda_float_bytes() == (4 if dtype == "f32" else 8)
+        self.kd = {0: kd_lw, 1: kd_sw}
+        self._keep = []
+        f = []
+        for kd in (kd_lw, kd_sw):
+            if kd is None:
+                f.append(None)
+            else:
+                fk, keep = pack_kdist(kd)
+                self._keep.append((fk, keep))
+                f.append(C.byref(fk))
+        names = list(gases)
+        self.h = C.c_void_p()
+        self._chk(self.L.refcuda_create(f[0], f[1], len(names), pack_strings(names), STRING_LEN, C.byref(self.h)))
+
+    def _chk(self, rc):
+        if rc:
+            raise RuntimeError(self.L.refcuda_last_error().decode())
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.refcuda_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def gas_optics(self, which, atm, nflav, ngas):
+        """which: 'lw' | 'sw'.  -> dict with the same keys and layouts as oracle.GasOptics.gas_optics_{lw,sw}.
+        nflav, ngas: flavors and retained gases of the k-distribution (oracle.GasOptics.nflav / .ngas; checked)."""
+        w = 0 if which == "lw" else 1
+        kd = self.kd[w]
+        F = lambda a: np.asfortranarray(a, dtype=np.float64)
+        P = lambda a: a.ctypes.data_as(c_dbl_p)
+        vn = list(atm.vmr.keys())
+        va = [F(np.atleast_2d(atm.vmr[n])) for n in vn]
+        ptrs = (c_dbl_p * len(vn))(*[P(a) for a in va])
+        nc = (C.c_int * len(vn))(*[a.shape[0] for a in va])
+        nl = (C.c_int * len(vn))(*[a.shape[1] for a in va])
+        ncol, nlay = atm.play.shape
+        ngpt = kd.ngpt
+        Z = lambda shape, dt=np.float64: np.zeros(shape, dtype=dt, order="F")
+        o = dict(jtemp=Z((ncol, nlay), np.int32), jpress=Z((ncol, nlay), np.int32), tropo=Z((ncol, nlay), np.int8),
+                 jeta=Z((2, ncol, nlay, nflav), np.int32), fmajor=Z((2, 2, 2, ncol, nlay, nflav)),
+                 fminor=Z((2, 2, ncol, nlay, nflav)), col_mix=Z((2, ncol, nlay, nflav)),
+                 col_gas=Z((ncol, nlay, ngas + 1)), tau=Z((ncol, nlay, ngpt)), col_dry=Z((ncol, nlay)))
+        if w == 0:
+            o.update(lay_src=Z((ncol, nlay, ngpt)), lev_src=Z((ncol, nlay + 1, ngpt)), sfc_src=Z((ncol, ngpt)),
+                     sfc_src_jac=Z((ncol, ngpt)))
+        else:
+            o.update(ssa=Z((ncol, nlay, ngpt)), g=Z((ncol, nlay, ngpt)), toa_src=Z((ncol, ngpt)))
+        ins = [F(x) for x in (atm.play, atm.plev, atm.tlay, atm.tlev, atm.tsfc)]
+        q = lambda k: P(o[k]) if k in o else c_dbl_p()
+        ip = lambda k: o[k].ctypes.data_as(C.POINTER(C.c_int))
+        nf = C.c_int()
+        self._chk(self.L.refcuda_stage_gas_optics(
+            self.h, w, ncol, nlay, len(vn), self._pack_strings(vn), self._len, ptrs, nc, nl, *[P(x) for x in ins],
+            ip("jtemp"), ip("jpress"), o["tropo"].ctypes.data_as(C.POINTER(C.c_byte)), ip("jeta"),
+            q("fmajor"), q("fminor"), q("col_mix"), q("col_gas"), q("tau"), q("ssa"), q("g"),
+            q("lay_src"), q("lev_src"), q("sfc_src"), q("sfc_src_jac"), q("toa_src"), q("col_dry"), C.byref(nf)))
+        assert nf.value == nflav, (nf.value, nflav)
+        return o
+
+    def rte_lw(self, tau, lay_src, lev_src, sfc_src, emis, top_at_1):
+        F = lambda a: np.asfortranarray(a, dtype=np.float64)
+        P = lambda a: a.ctypes.data_as(c_dbl_p)
+        tau, lay_src, lev_src, sfc_src, emis = map(F, (tau, lay_src, lev_src, sfc_src, emis))
+        ncol, nlay, ngpt = tau.shape
+        up, dn = (np.zeros((ncol, nlay + 1, ngpt), order="F") for _ in range(2))
+        self._chk(self.L.refcuda_stage_rte_lw(self.h, ncol, nlay, int(top_at_1), P(tau), P(lay_src), P(lev_src), P(sfc_src),
+                                              P(emis), P(up), P(dn)))
+        return up, dn
+
+    def rte_sw(self, tau, ssa, g, mu0, toa, alb_dir, alb_dif, top_at_1):
+        F = lambda a: np.asfortranarray(a, dtype=np.float64)
+        P = lambda a: a.ctypes.data_as(c_dbl_p)
+        tau, ssa, g, mu0, toa, alb_dir, alb_dif = map(F, (tau, ssa, g, mu0, toa, alb_dir, alb_dif))
+        ncol, nlay, ngpt = tau.shape
+        up, dn, dr = (np.zeros((ncol, nlay + 1, ngpt), order="F") for _ in range(3))
+        self._chk(self.L.refcuda_stage_rte_sw(self.h, ncol, nlay, int(top_at_1), P(tau), P(ssa), P(g), P(mu0), P(toa),
+                                              P(alb_dir), P(alb_dif), P(up), P(dn), P(dr)))
+        return up, dn, dr
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--ncol", type=int, default=65536)

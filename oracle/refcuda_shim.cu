@@ -19,11 +19,25 @@
 #include <stdexcept>
 #include <cuda_runtime.h>
 
+#include <algorithm>
+#include <array>
+#include <iostream>
+#include <fstream>
+#include <map>
+#include <utility>
+
 #include "Array.h"
 #include "Gas_concs.h"
-#include "Gas_optics_rrtmgp.h"
 #include "Optical_props.h"
 #include "Source_functions.h"
+#include "Gas_optics.h"
+// The stage entry points below (refcuda_stage_*) read the interpolation state the reference class keeps in
+// locals and private members.  Only the access specifiers of this one header are lifted, in this one test
+// translation unit; the class itself is compiled unmodified (oracle/Makefile) and its layout does not change.
+#define private public
+#include "Gas_optics_rrtmgp.h"
+#undef private
+#include "gas_optics_rrtmgp_kernels_cuda.h"
 #include "Rte_lw.h"
 #include "Rte_sw.h"
 #include "Fluxes.h"
@@ -52,6 +66,13 @@ namespace
         if (!out) return;
         Array<Float, N> h(a);
         for (size_t i = 0; i < h.v().size(); ++i) out[i] = (double)h.v()[i];
+    }
+
+    template<typename T, int N> void down_raw(const Array_gpu<T, N>& a, T* out)
+    {
+        if (!out) return;
+        Array<T, N> h(a);
+        std::copy(h.v().begin(), h.v().end(), out);
     }
 
     Gas_concs host_concs(int ngas, const char* names, int len, const double* const* vmr, const int* vnc, const int* vnl)
@@ -194,6 +215,163 @@ int refcuda_solve(void* hv, int ncol, int nlay, int ngas, const char* names, int
         down(f_up, sw_up); down(f_dn, sw_dn); down(f_dir, sw_dir);
     }
     cudaEventDestroy(e0); cudaEventDestroy(e1);
+    const cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) throw std::runtime_error(std::string("CUDA: ") + cudaGetErrorString(err));
+    SHIM_CATCH
+}
+/* ---- stage entry points: what the reference's own CUDA kernels compute at every class-API boundary of the
+ * path, on host fp64 inputs (converted to the build's Float), returned as fp64 / int32 / int8 host arrays in
+ * the reference layouts (column fastest).  tests/test_oracle_vs_refcuda.py compares them with the C
+ * restatement of the Fortran kernels (oracle/rrtmgp_kernels_restated.c) — the pin of rows a5-a9. ---- */
+
+/* which: 0 longwave, 1 shortwave.  Outputs (any may be null):
+ *   jtemp, jpress (ncol,nlay) int32; tropo (ncol,nlay) int8; jeta (2,ncol,nlay,nflav) int32;
+ *   fmajor (2,2,2,ncol,nlay,nflav); fminor (2,2,ncol,nlay,nflav); col_mix (2,ncol,nlay,nflav); col_gas (ncol,nlay,ngas+1);
+ *   tau, ssa, g (ncol,nlay,ngpt) [ssa, g shortwave only]; lay_src (ncol,nlay,ngpt), lev_src (ncol,nlay+1,ngpt),
+ *   sfc_src, sfc_src_jac (ncol,ngpt) [longwave]; toa_src (ncol,ngpt) [shortwave]; col_dry (ncol,nlay).
+ * Call sequence: get_col_dry -> public gas_optics() (src_cuda/Gas_optics_rrtmgp.cu:907-977) for the optical
+ * outputs; compute_gas_taus() (:980-1148) once more for the interpolation state it returns by reference; and the
+ * interpolation launcher (gas_optics_rrtmgp_kernels_launchers.cu:91-125) on the class's own tables for fminor /
+ * col_mix, which compute_gas_taus keeps local.  The launcher's indices must equal compute_gas_taus's (checked). */
+int refcuda_stage_gas_optics(void* hv, int which, int ncol, int nlay, int ngas, const char* names, int len,
+                             const double* const* vmr, const int* vnc, const int* vnl,
+                             const double* play, const double* plev, const double* tlay, const double* tlev, const double* tsfc,
+                             int* jtemp_o, int* jpress_o, signed char* tropo_o, int* jeta_o,
+                             double* fmajor_o, double* fminor_o, double* col_mix_o, double* col_gas_o,
+                             double* tau_o, double* ssa_o, double* g_o,
+                             double* lay_src_o, double* lev_src_o, double* sfc_src_o, double* sfc_jac_o, double* toa_o,
+                             double* col_dry_o, int* nflav_o)
+{
+    SHIM_TRY
+    auto* R = static_cast<Ref_cuda*>(hv);
+    Gas_optics_rrtmgp_gpu* K = which == 0 ? R->lw.get() : R->sw.get();
+    if (!K) throw std::runtime_error("refcuda_stage_gas_optics: k-distribution not loaded");
+    const int nlev = nlay + 1, ngpt = K->get_ngpt(), nband = K->get_nband(), nflav = K->get_nflav();
+    if (nflav_o) *nflav_o = nflav;
+    Gas_concs gc = host_concs(ngas, names, len, vmr, vnc, vnl);
+    Gas_concs_gpu gas(gc);
+    auto p_lay = up<2>(play, {ncol, nlay}); auto p_lev = up<2>(plev, {ncol, nlev}); auto t_lay = up<2>(tlay, {ncol, nlay});
+    Array_gpu<Float,2> col_dry({ncol, nlay});
+    Gas_optics_rrtmgp_gpu::get_col_dry(col_dry, gas.get_vmr("h2o"), p_lev);
+    down(col_dry, col_dry_o);
+
+    Array_gpu<int,2> jtemp({ncol, nlay}), jpress({ncol, nlay});
+    Array_gpu<Bool,2> tropo({ncol, nlay});
+    Array_gpu<Float,6> fmajor({2, 2, 2, ncol, nlay, nflav});
+    Array_gpu<int,4> jeta({2, ncol, nlay, nflav});
+    std::unique_ptr<Optical_props_arry_gpu> op;
+    if (which == 0)
+    {
+        op = std::make_unique<Optical_props_1scl_gpu>(ncol, nlay, *K);
+        Source_func_lw_gpu src(ncol, nlay, *K);
+        auto t_lev = up<2>(tlev, {ncol, nlev}); auto t_sfc = up<1>(tsfc, {ncol});
+        K->gas_optics(p_lay, p_lev, t_lay, t_sfc, gas, op, src, col_dry, t_lev);
+        down(op->get_tau(), tau_o);
+        down(src.get_lay_source(), lay_src_o); down(src.get_lev_source(), lev_src_o);
+        down(src.get_sfc_source(), sfc_src_o); down(src.get_sfc_source_jac(), sfc_jac_o);
+    }
+    else
+    {
+        op = std::make_unique<Optical_props_2str_gpu>(ncol, nlay, *K);
+        Array_gpu<Float,2> toa({ncol, ngpt});
+        K->gas_optics(p_lay, p_lev, t_lay, gas, op, toa, col_dry);
+        down(op->get_tau(), tau_o); down(op->get_ssa(), ssa_o); down(op->get_g(), g_o);
+        down(toa, toa_o);
+    }
+    // the interpolation state, as the class computes it for itself
+    K->compute_gas_taus(ncol, nlay, ngpt, nband, p_lay, p_lev, t_lay, gas, op, jtemp, jpress, jeta, tropo, fmajor, col_dry);
+    down_raw(jtemp, jtemp_o); down_raw(jpress, jpress_o); down_raw(jeta, jeta_o);
+    if (tropo_o) { Array<Bool,2> h(tropo); for (size_t i = 0; i < h.v().size(); ++i) tropo_o[i] = (signed char)(h.v()[i] ? 1 : 0); }
+    down(fmajor, fmajor_o);
+
+    // fminor / col_mix: the reference's interpolation launcher on the class's own device tables; col_gas as
+    // fill_gases_kernel builds it (src_cuda/Gas_optics_rrtmgp.cu:392-422: slot 0 = col_dry, slot i = vmr_i * col_dry,
+    // one exactly-rounded product per element, so the host product in Float is the same number)
+    {
+        const int ng = K->get_ngas();
+        Array<Float,2> cd_h(col_dry);
+        Array<Float,3> cg_h({ncol, nlay, ng + 1});
+        for (int il = 0; il < nlay; ++il) for (int ic = 0; ic < ncol; ++ic) cg_h.v()[ic + (size_t)ncol * il] = cd_h.v()[ic + (size_t)ncol * il];
+        for (int ig = 1; ig <= ng; ++ig)
+        {
+            const Array<Float,2>& v = gc.get_vmr(K->gas_names({ig}));
+            const int vc = v.dim(1), vl = v.dim(2);
+            for (int il = 0; il < nlay; ++il) for (int ic = 0; ic < ncol; ++ic)
+            {
+                const Float x = v.v()[(vc > 1 ? ic : 0) + (size_t)vc * (vl > 1 ? il : 0)];
+                cg_h.v()[ic + (size_t)ncol * (il + (size_t)nlay * ig)] = x * cd_h.v()[ic + (size_t)ncol * il];
+            }
+        }
+        Array_gpu<Float,3> col_gas(cg_h);
+        Array_gpu<Float,4> col_mix({2, ncol, nlay, nflav});
+        Array_gpu<Float,5> fminor({2, 2, ncol, nlay, nflav});
+        Array_gpu<int,2> jtemp2({ncol, nlay}), jpress2({ncol, nlay});
+        Array_gpu<Bool,2> tropo2({ncol, nlay});
+        Array_gpu<Float,6> fmajor2({2, 2, 2, ncol, nlay, nflav});
+        Array_gpu<int,4> jeta2({2, ncol, nlay, nflav});
+        Gas_optics_rrtmgp_kernels_cuda::interpolation(
+                ncol, nlay, ng, nflav, K->get_neta(), K->get_npres(), K->get_ntemp(),
+                K->flavor_gpu.ptr(), K->press_ref_log_gpu.ptr(), K->temp_ref_gpu.ptr(),
+                K->press_ref_log_delta, K->temp_ref_min, K->temp_ref_delta, K->press_ref_trop_log,
+                K->vmr_ref_gpu.ptr(), p_lay.ptr(), t_lay.ptr(), col_gas.ptr(),
+                jtemp2.ptr(), fmajor2.ptr(), fminor.ptr(), col_mix.ptr(), tropo2.ptr(), jeta2.ptr(), jpress2.ptr());
+        cudaDeviceSynchronize();
+        Array<int,2> a(jtemp), b(jtemp2); Array<int,4> c(jeta), d(jeta2); Array<Float,6> e(fmajor), f(fmajor2);
+        if (a.v() != b.v() || c.v() != d.v() || e.v() != f.v())
+            throw std::runtime_error("refcuda_stage_gas_optics: the launcher call and compute_gas_taus disagree (col_gas restatement?)");
+        down(fminor, fminor_o); down(col_mix, col_mix_o); down(col_gas, col_gas_o);
+    }
+    const cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) throw std::runtime_error(std::string("CUDA: ") + cudaGetErrorString(err));
+    SHIM_CATCH
+}
+
+/* Rte_lw_gpu::rte_lw (src_cuda/Rte_lw.cu:60-159; kernels rte_solver_kernels.cu:35-193), one Gauss angle (the
+ * reference GPU launcher throws for more), no incident flux: per-g-point fluxes (ncol,nlay+1,ngpt). */
+int refcuda_stage_rte_lw(void* hv, int ncol, int nlay, int top_at_1, const double* tau, const double* lay_src,
+                         const double* lev_src, const double* sfc_src, const double* emis, double* gpt_up, double* gpt_dn)
+{
+    SHIM_TRY
+    auto* R = static_cast<Ref_cuda*>(hv);
+    if (!R->lw) throw std::runtime_error("refcuda_stage_rte_lw: longwave k-distribution not loaded");
+    const int nlev = nlay + 1, ngpt = R->lw->get_ngpt(), nbnd = R->lw->get_nband();
+    std::unique_ptr<Optical_props_arry_gpu> op = std::make_unique<Optical_props_1scl_gpu>(ncol, nlay, *R->lw);
+    op->get_tau() = up<3>(tau, {ncol, nlay, ngpt});
+    Source_func_lw_gpu src(ncol, nlay, *R->lw);
+    src.get_lay_source() = up<3>(lay_src, {ncol, nlay, ngpt});
+    src.get_lev_source() = up<3>(lev_src, {ncol, nlev, ngpt});
+    src.get_sfc_source() = up<2>(sfc_src, {ncol, ngpt});
+    src.get_sfc_source_jac().fill(Float(0.));
+    auto em = up<2>(emis, {nbnd, ncol});
+    Array_gpu<Float,3> g_up({ncol, nlev, ngpt}), g_dn({ncol, nlev, ngpt});
+    R->rte_lw.rte_lw(op, (Bool)top_at_1, src, em, Array_gpu<Float,2>(), g_up, g_dn, 1);
+    cudaDeviceSynchronize();
+    down(g_up, gpt_up); down(g_dn, gpt_dn);
+    const cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) throw std::runtime_error(std::string("CUDA: ") + cudaGetErrorString(err));
+    SHIM_CATCH
+}
+
+/* Rte_sw_gpu::rte_sw (src_cuda/Rte_sw.cu:116-185; kernels rte_solver_kernels.cu:196-286,543-655), no incident
+ * diffuse flux: per-g-point up / down / direct fluxes (ncol,nlay+1,ngpt). */
+int refcuda_stage_rte_sw(void* hv, int ncol, int nlay, int top_at_1, const double* tau, const double* ssa, const double* g,
+                         const double* mu0, const double* toa, const double* alb_dir, const double* alb_dif,
+                         double* gpt_up, double* gpt_dn, double* gpt_dir)
+{
+    SHIM_TRY
+    auto* R = static_cast<Ref_cuda*>(hv);
+    if (!R->sw) throw std::runtime_error("refcuda_stage_rte_sw: shortwave k-distribution not loaded");
+    const int nlev = nlay + 1, ngpt = R->sw->get_ngpt(), nbnd = R->sw->get_nband();
+    std::unique_ptr<Optical_props_arry_gpu> op = std::make_unique<Optical_props_2str_gpu>(ncol, nlay, *R->sw);
+    op->get_tau() = up<3>(tau, {ncol, nlay, ngpt});
+    op->get_ssa() = up<3>(ssa, {ncol, nlay, ngpt});
+    op->get_g() = up<3>(g, {ncol, nlay, ngpt});
+    auto m0 = up<1>(mu0, {ncol}); auto t = up<2>(toa, {ncol, ngpt});
+    auto ad = up<2>(alb_dir, {nbnd, ncol}); auto af = up<2>(alb_dif, {nbnd, ncol});
+    Array_gpu<Float,3> g_up({ncol, nlev, ngpt}), g_dn({ncol, nlev, ngpt}), g_dir({ncol, nlev, ngpt});
+    R->rte_sw.rte_sw(op, (Bool)top_at_1, m0, t, ad, af, Array_gpu<Float,2>(), g_up, g_dn, g_dir);
+    cudaDeviceSynchronize();
+    down(g_up, gpt_up); down(g_dn, gpt_dn); down(g_dir, gpt_dir);
     const cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess) throw std::runtime_error(std::string("CUDA: ") + cudaGetErrorString(err));
     SHIM_CATCH
