@@ -230,10 +230,10 @@ static void solve_radiation(int argc, char** argv)
 
         say("Storing the longwave output.");
         out.add_dimension("gpt_lw", ngpt); out.add_dimension("band_lw", nbnd);
-        out.add_variable<Float>("lw_band_lims_wvn", {"band_lw", "pair"}).insert(rad_lw.get_band_lims_wavenumber_gpu(), {0, 0});
+        out.add_variable<Float>("lw_band_lims_wvn", {"band_lw", "pair"}).insert(rad_lw.get_band_lims_wavenumber_gpu().v(), {0, 0});
         if (optical)
         {
-            out.add_variable<int>("lw_band_lims_gpt", {"band_lw", "pair"}).insert(rad_lw.get_band_lims_gpoint_gpu(), {0, 0});
+            out.add_variable<int>("lw_band_lims_gpt", {"band_lw", "pair"}).insert(rad_lw.get_band_lims_gpoint_gpu().v(), {0, 0});
             write<3>(out, "lw_tau", {"gpt_lw", "lay", "y", "x"}, lw_tau);
             write<3>(out, "lay_source", {"gpt_lw", "lay", "y", "x"}, lay_source);
             write<3>(out, "lev_source", {"gpt_lw", "lev", "y", "x"}, lev_source);
@@ -306,10 +306,10 @@ static void solve_radiation(int argc, char** argv)
 
         say("Storing the shortwave output.");
         out.add_dimension("gpt_sw", ngpt); out.add_dimension("band_sw", nbnd);
-        out.add_variable<Float>("sw_band_lims_wvn", {"band_sw", "pair"}).insert(rad_sw.get_band_lims_wavenumber_gpu(), {0, 0});
+        out.add_variable<Float>("sw_band_lims_wvn", {"band_sw", "pair"}).insert(rad_sw.get_band_lims_wavenumber_gpu().v(), {0, 0});
         if (optical)
         {
-            out.add_variable<int>("sw_band_lims_gpt", {"band_sw", "pair"}).insert(rad_sw.get_band_lims_gpoint_gpu(), {0, 0});
+            out.add_variable<int>("sw_band_lims_gpt", {"band_sw", "pair"}).insert(rad_sw.get_band_lims_gpoint_gpu().v(), {0, 0});
             write<3>(out, "sw_tau", {"gpt_sw", "lay", "y", "x"}, sw_tau);
             write<3>(out, "ssa", {"gpt_sw", "lay", "y", "x"}, ssa);
             write<3>(out, "g", {"gpt_sw", "lay", "y", "x"}, g);

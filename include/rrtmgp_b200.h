@@ -76,6 +76,11 @@ int rrtmgp_b200_gas_optics_get_tables(const rrtmgp_b200_gas_optics* go, int* ban
                                       int* gpoint_flavor, char* gas_names, int string_len,
                                       double* solar_source);
 
+/* 64-bit hash over every prepared table of the handle (coefficients in device layout, index tables, reference grids,
+ * retained gas names): equal hashes = built from bit-identical coefficient arrays and available-gas lists, whichever
+ * constructor packed them.  HOST function. */
+int rrtmgp_b200_gas_optics_table_hash(const rrtmgp_b200_gas_optics* go, unsigned long long* hash);
+
 /* reduced minor-contributor descriptors of side 0 (lower) / 1 (upper): arrays of n_minor_* ints;
  * idx_minor / idx_minor_scaling as create_idx_minor[_scaling] (src/Gas_optics_rrtmgp.cpp:164-196),
  * kminor_start and limits(2,n) as reduce_minor_arrays (:54-162).  Any pointer may be NULL. */
@@ -255,6 +260,16 @@ int rrtmgp_b200_net_flux(int dtype, size_t n, const void* d_dn, const void* d_up
 /* x(icol, j) *= scale(icol), j < n2: the TSI scaling of the top-of-atmosphere source
  * (scaling_to_subset, src_test/Radiation_solver.cu:42-70). */
 int rrtmgp_b200_scale_columns(int dtype, int ncol, int n2, void* d_x, const void* d_scale, void* stream);
+/* Array_gpu<T,N>::fill and ::subset (include/Array.h:311-350 kernels, :515-524 and :579-622 members), type-erased:
+ * elem_bytes = sizeof(T) in {1, 2, 4, 8, 16}.  fill: a[i] = *value (HOST pointer to one element), i < n.
+ * subset: both arrays column-major; src has extents src_dims and index offsets src_offsets (NULL = zeros; element
+ * (i1..iN) is at sum (i_k - offset_k - 1) * stride_k like the reference's calc_index); sub(j1..jN) = src(first + j - 1);
+ * a source dimension of extent 1 is broadcast.  Ranges outside the source return E_ARG (the reference reads out of
+ * bounds).  One stream-ordered kernel each, no synchronisation. */
+int rrtmgp_b200_array_fill(int elem_bytes, long long n, void* d_a, const void* value /*HOST*/, void* stream);
+int rrtmgp_b200_array_subset(int elem_bytes, int ndim, const int* src_dims /*HOST*/, const int* src_offsets /*HOST*/,
+                             const int* first /*HOST, 1-based + offset*/, const int* sub_dims /*HOST*/,
+                             const void* d_src, void* d_sub, void* stream);
 /* heating rate (not in the C++ reference; rte-rrtmgp/extensions/mo_heating_rates.F90:44-73) */
 int rrtmgp_b200_heating_rate(int dtype, int ncol, int nlay, const void* d_flux_up,
                              const void* d_flux_dn, const void* d_plev, void* d_hr, void* stream);

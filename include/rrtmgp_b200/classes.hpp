@@ -16,6 +16,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <array>
+#include <deque>
 #include <map>
 #include <memory>
 #include <stdexcept>
@@ -30,139 +31,155 @@ using Float = double;
 #endif
 using Bool = signed char;
 
+#include "array.hpp"       // Array<T,N>, Array_gpu<T,N>, rrtmgp_b200::stream() / check()
+
 namespace rrtmgp_b200 {
-inline cudaStream_t& stream() { static cudaStream_t s = nullptr; return s; }
 constexpr int dtype = sizeof(Float) == 4 ? RRTMGP_B200_F32 : RRTMGP_B200_F64;
-inline void check(int rc)
-{
-    if (rc == RRTMGP_B200_OK) return;
-    const std::string msg = rrtmgp_b200_last_error();
-    if (rc == RRTMGP_B200_E_RANGE) throw std::range_error(msg);      // src/Gas_optics_rrtmgp.cpp:812-827
-    throw std::runtime_error(msg);
-}
-inline void cuda_check(cudaError_t e) { if (e != cudaSuccess) throw std::runtime_error(cudaGetErrorString(e)); }
+// OR-ed into dtype when a k-distribution object is constructed.  RRTMGP_B200_HOST_ONLY builds the host tables only,
+// so constructor logic can be checked on a machine without a GPU (compute calls on such an object fail).
+inline int& create_flags() { static int f = 0; return f; }
 }  // namespace rrtmgp_b200
 
-template<typename T, int N>
-class Array_gpu
+// include/Gas_concs.h:40-70, src/Gas_concs.cpp:28-117 (host volume mixing ratios: scalar (1,1), profile (1,nlay), field (ncol,nlay))
+class Gas_concs
 {
     public:
-        Array_gpu() = default;
-        explicit Array_gpu(const std::array<int, N>& dims) { set_dims(dims); }
-        Array_gpu(T* ptr, const std::array<int, N>& dims) : dims_(dims), n_(count(dims)), p_(ptr), own_(false) {}   // view
-        Array_gpu(const std::vector<T>& host, const std::array<int, N>& dims) { set_dims(dims); copy_from(host); }
-        Array_gpu(const Array_gpu& o) { *this = o; }
-        Array_gpu(Array_gpu&& o) noexcept { *this = std::move(o); }
-        ~Array_gpu() { release(); }
-        Array_gpu& operator=(const Array_gpu& o)
+        Gas_concs() = default;
+        Gas_concs(const Gas_concs& gas_concs_ref, const int start, const int size)
         {
-            if (this == &o) return *this;
-            set_dims(o.dims_);
-            if (n_) rrtmgp_b200::cuda_check(cudaMemcpyAsync(p_, o.p_, n_ * sizeof(T), cudaMemcpyDeviceToDevice, rrtmgp_b200::stream()));
-            return *this;
+            for (auto& g : gas_concs_ref.gas_concs_map)
+                gas_concs_map[g.first] = g.second.dim(1) == 1 ? g.second
+                                       : g.second.subset({{ {start, start + size - 1}, {1, g.second.dim(2)} }});
         }
-        Array_gpu& operator=(Array_gpu&& o) noexcept
+        void set_vmr(const std::string& name, const Float data)
         {
-            if (this == &o) return *this;
-            release();
-            dims_ = o.dims_; n_ = o.n_; p_ = o.p_; own_ = o.own_;
-            o.p_ = nullptr; o.n_ = 0; o.own_ = false;
-            return *this;
+            if (data < Float(0.) || data > Float(1.)) throw std::range_error("Gas concentration " + name + " is out of range");
+            gas_concs_map[name] = Array<Float,2>(std::vector<Float>{data}, {1, 1});
         }
-        void set_dims(const std::array<int, N>& dims)
+        void set_vmr(const std::string& name, const Array<Float,1>& data)
         {
-            release();
-            dims_ = dims; n_ = count(dims); own_ = true;
-            if (n_) rrtmgp_b200::cuda_check(cudaMalloc((void**)&p_, n_ * sizeof(T)));
+            if (any_vals_outside(data, Float(0.), Float(1.))) throw std::range_error("Gas concentration " + name + " is out of range");
+            gas_concs_map[name] = Array<Float,2>(data.v(), {1, data.dim(1)});
         }
-        void fill(const T v)
+        void set_vmr(const std::string& name, const Array<Float,2>& data)
         {
-            std::vector<T> h(n_, v);
-            copy_from(h);
+            if (any_vals_outside(data, Float(0.), Float(1.))) throw std::range_error("Gas concentration " + name + " is out of range");
+            gas_concs_map[name] = data;
         }
-        void copy_from(const std::vector<T>& h)
-        {
-            if (h.size() != n_) throw std::runtime_error("Array_gpu: size mismatch");
-            if (n_) rrtmgp_b200::cuda_check(cudaMemcpy(p_, h.data(), n_ * sizeof(T), cudaMemcpyHostToDevice));
-        }
-        std::vector<T> to_host() const
-        {
-            std::vector<T> h(n_);
-            rrtmgp_b200::cuda_check(cudaStreamSynchronize(rrtmgp_b200::stream()));
-            if (n_) rrtmgp_b200::cuda_check(cudaMemcpy(h.data(), p_, n_ * sizeof(T), cudaMemcpyDeviceToHost));
-            return h;
-        }
-        T* ptr() { return p_; }
-        const T* ptr() const { return p_; }
-        int dim(const int i) const { return dims_[i - 1]; }      // 1-based like the reference
-        size_t size() const { return n_; }
-        const std::array<int, N>& get_dims() const { return dims_; }
+        const Array<Float,2>& get_vmr(const std::string& name) const { return gas_concs_map.at(name); }
+        Bool exists(const std::string& name) const { return gas_concs_map.count(name) != 0; }
     private:
-        static size_t count(const std::array<int, N>& d) { size_t n = 1; for (int v : d) n *= (size_t)v; return n; }
-        void release() { if (own_ && p_) cudaFree(p_); p_ = nullptr; n_ = 0; }
-        std::array<int, N> dims_{};
-        size_t n_ = 0;
-        T* p_ = nullptr;
-        bool own_ = false;
+        std::map<std::string, Array<Float,2>> gas_concs_map;
+        friend class Gas_concs_gpu;
 };
 
+// include/Gas_concs.h:73-91, src_cuda/Gas_concs.cu:29-80
 class Gas_concs_gpu
 {
     public:
+        Gas_concs_gpu() = default;
+        Gas_concs_gpu(const Gas_concs& gas_concs_ref)
+        {
+            for (auto& g : gas_concs_ref.gas_concs_map) gas_concs_map.emplace(g.first, Array_gpu<Float,2>(g.second));
+        }
+        // columns [start, start+size-1] (1-based) of every field; scalars and profiles are shared
+        Gas_concs_gpu(const Gas_concs_gpu& gas_concs_ref, const int start, const int size)
+        {
+            for (auto& g : gas_concs_ref.gas_concs_map)
+            {
+                if (g.second.dim(1) == 1) gas_concs_map.emplace(g.first, g.second);
+                else gas_concs_map.emplace(g.first, g.second.subset({{ {start, start + size - 1}, {1, g.second.dim(2)} }}));
+            }
+        }
+        void set_vmr(const std::string& name, const Array<Float,2>& data)
+        {
+            if (any_vals_outside(data, Float(0.), Float(1.))) throw std::range_error("Gas concentration " + name + " is out of range");
+            gas_concs_map.erase(name);
+            gas_concs_map.emplace(name, Array_gpu<Float,2>(data));
+        }
+        void set_vmr(const std::string& name, const Array_gpu<Float,2>& data) { gas_concs_map.erase(name); gas_concs_map.emplace(name, data); }   // caller validated
+        // extensions (not in the reference): scalar and flat-vector setters
         void set_vmr(const std::string& name, const Float data)
         {
-            if (data < Float(0.) || data > Float(1.)) throw std::range_error("Gas concentration values should be between 0 and 1");
-            gas_concs_map[name] = Array_gpu<Float,2>(std::vector<Float>{data}, {1, 1});
+            if (data < Float(0.) || data > Float(1.)) throw std::range_error("Gas concentration " + name + " is out of range");
+            set_vmr(name, Array_gpu<Float,2>(std::vector<Float>{data}, {1, 1}));
         }
         void set_vmr(const std::string& name, const std::vector<Float>& data, const int ncol, const int nlay)
         {
             for (const Float v : data)
-                if (v < Float(0.) || v > Float(1.)) throw std::range_error("Gas concentration values should be between 0 and 1");
-            gas_concs_map[name] = Array_gpu<Float,2>(data, {ncol, nlay});
+                if (v < Float(0.) || v > Float(1.)) throw std::range_error("Gas concentration " + name + " is out of range");
+            set_vmr(name, Array_gpu<Float,2>(data, {ncol, nlay}));
         }
-        void set_vmr(const std::string& name, const Array_gpu<Float,2>& data) { gas_concs_map[name] = data; }   // caller validated
         const Array_gpu<Float,2>& get_vmr(const std::string& name) const
         {
             auto it = gas_concs_map.find(name);
             if (it == gas_concs_map.end()) throw std::runtime_error("Gas_concs: gas " + name + " not set");
             return it->second;
         }
-        bool exists(const std::string& name) const { return gas_concs_map.count(name) != 0; }
+        Bool exists(const std::string& name) const { return gas_concs_map.count(name) != 0; }
         std::vector<std::string> names() const { std::vector<std::string> n; for (auto& kv : gas_concs_map) n.push_back(kv.first); return n; }
     private:
         std::map<std::string, Array_gpu<Float,2>> gas_concs_map;
 };
 
-// band <-> g-point bookkeeping (src/Optical_props.cpp:31-72); limits are (2, nbnd), 1-based
+// band <-> g-point bookkeeping (include/Optical_props.h:178-210, src/Optical_props.cpp:31-72); limits are (2, nbnd), 1-based
 class Optical_props_gpu
 {
     public:
         Optical_props_gpu() = default;
-        Optical_props_gpu(const std::vector<Float>& band_lims_wvn, const std::vector<int>& band_lims_gpt)
-            : band_lims_wvn(band_lims_wvn), band2gpt(band_lims_gpt) { init(); }
-        explicit Optical_props_gpu(const std::vector<Float>& band_lims_wvn) : band_lims_wvn(band_lims_wvn)
+        Optical_props_gpu(const Array<Float,2>& band_lims_wvn, const Array<int,2>& band_lims_gpt)
+            : band2gpt(band_lims_gpt), band_lims_wvn(band_lims_wvn) { init(); }
+        // one g-point per band
+        Optical_props_gpu(const Array<Float,2>& band_lims_wvn) : band2gpt({2, band_lims_wvn.dim(2)}), band_lims_wvn(band_lims_wvn)
         {
-            for (int b = 1; b <= (int)band_lims_wvn.size() / 2; ++b) { band2gpt.push_back(b); band2gpt.push_back(b); }
+            for (int b = 1; b <= band_lims_wvn.dim(2); ++b) { band2gpt({1, b}) = b; band2gpt({2, b}) = b; }
             init();
         }
         virtual ~Optical_props_gpu() = default;
-        int get_nband() const { return (int)band2gpt.size() / 2; }
-        int get_ngpt() const { return ngpt; }
-        const std::vector<int>& get_band_lims_gpoint() const { return band2gpt; }
-        const std::vector<Float>& get_band_lims_wavenumber() const { return band_lims_wvn; }
-        const std::vector<int>& get_gpoint_bands() const { return gpt2band; }
+        Optical_props_gpu(const Optical_props_gpu& o) : band2gpt(o.band2gpt), gpt2band(o.gpt2band), band_lims_wvn(o.band_lims_wvn) {}
+        Optical_props_gpu& operator=(const Optical_props_gpu& o)
+        {
+            band2gpt = o.band2gpt; gpt2band = o.gpt2band; band_lims_wvn = o.band_lims_wvn;
+            band2gpt_gpu.reset(); gpt2band_gpu.reset();
+            return *this;
+        }
+        int get_nband() const { return band2gpt.dim(2); }
+        int get_ngpt() const { return band2gpt.is_empty() ? 0 : band2gpt.max(); }
+        Array<int,1> get_gpoint_bands() const { return gpt2band; }
+        const Array<int,2>& get_band_lims_gpoint() const { return band2gpt; }
+        const Array<Float,2>& get_band_lims_wavenumber() const { return band_lims_wvn; }
+        // device copies, uploaded on first use
+        const Array_gpu<int,1>& get_gpoint_bands_gpu() const
+        {
+            if (!gpt2band_gpu) gpt2band_gpu = std::make_shared<Array_gpu<int,1>>(gpt2band);
+            return *gpt2band_gpu;
+        }
+        const Array_gpu<int,2>& get_band_lims_gpoint_gpu() const
+        {
+            if (!band2gpt_gpu) band2gpt_gpu = std::make_shared<Array_gpu<int,2>>(band2gpt);
+            return *band2gpt_gpu;
+        }
     protected:
         void init()
         {
-            ngpt = 0;
-            for (size_t i = 1; i < band2gpt.size(); i += 2) ngpt = std::max(ngpt, band2gpt[i]);
-            gpt2band.assign(ngpt, 0);
-            for (int b = 0; b < get_nband(); ++b)
-                for (int g = band2gpt[2 * b]; g <= band2gpt[2 * b + 1]; ++g) gpt2band[g - 1] = b + 1;
+            const int ngpt = get_ngpt();
+            gpt2band = Array<int,1>({ngpt});
+            for (int b = 1; b <= get_nband(); ++b)
+                for (int g = band2gpt({1, b}); g <= band2gpt({2, b}); ++g) gpt2band({g}) = b;
+            band2gpt_gpu.reset(); gpt2band_gpu.reset();
         }
-        std::vector<Float> band_lims_wvn;
-        std::vector<int> band2gpt, gpt2band;
-        int ngpt = 0;
+        void set_spectral(const std::vector<double>& wvn, const std::vector<int>& lims)       // from the C ABI's flat tables
+        {
+            const int nb = (int)lims.size() / 2;
+            band2gpt = Array<int,2>(lims, {2, nb});
+            band_lims_wvn = Array<Float,2>(std::vector<Float>(wvn.begin(), wvn.end()), {2, nb});
+            init();
+        }
+        Array<int,2> band2gpt;
+        Array<int,1> gpt2band;
+        Array<Float,2> band_lims_wvn;
+        mutable std::shared_ptr<Array_gpu<int,2>> band2gpt_gpu;
+        mutable std::shared_ptr<Array_gpu<int,1>> gpt2band_gpu;
 };
 
 class Optical_props_arry_gpu : public Optical_props_gpu
@@ -232,7 +249,7 @@ inline void add_to(Optical_props_1scl_gpu& op_inout, const Optical_props_1scl_gp
         if (op_in.get_ngpt() != op_inout.get_nband())
             throw std::runtime_error("Cannot add optical properties with incompatible band - gpoint combination");
         rrtmgp_b200::check(rrtmgp_b200_increment_1scl_bybnd(rrtmgp_b200::dtype, ncol, nlay, ngpt, op_inout.get_tau().ptr(),
-                op_in.get_tau().ptr(), op_inout.get_nband(), op_inout.get_band_lims_gpoint().data(), rrtmgp_b200::stream()));
+                op_in.get_tau().ptr(), op_inout.get_nband(), op_inout.get_band_lims_gpoint().ptr(), rrtmgp_b200::stream()));
     }
 }
 inline void add_to(Optical_props_2str_gpu& op_inout, const Optical_props_2str_gpu& op_in)
@@ -248,7 +265,7 @@ inline void add_to(Optical_props_2str_gpu& op_inout, const Optical_props_2str_gp
             throw std::runtime_error("Cannot add optical properties with incompatible band - gpoint combination");
         rrtmgp_b200::check(rrtmgp_b200_increment_2str_bybnd(rrtmgp_b200::dtype, ncol, nlay, ngpt, op_inout.get_tau().ptr(),
                 op_inout.get_ssa().ptr(), op_inout.get_g().ptr(), op_in.get_tau().ptr(), op_in.get_ssa().ptr(),
-                op_in.get_g().ptr(), op_inout.get_nband(), op_inout.get_band_lims_gpoint().data(), rrtmgp_b200::stream()));
+                op_in.get_g().ptr(), op_inout.get_nband(), op_inout.get_band_lims_gpoint().ptr(), rrtmgp_b200::stream()));
     }
 }
 
@@ -290,34 +307,140 @@ inline std::string pad_names(const std::vector<std::string>& names, int len)
 }
 }  // namespace rrtmgp_b200
 
+namespace rrtmgp_b200 {
+// Helpers of the positional constructors: the reference hands its constructors Array objects whose memory order IS
+// the coefficient file's (column-major dims reversed, src_test/Radiation_solver.cu:125-243), so packing them into the
+// C ABI's file-order structs is a pointer hand-over (plus a widening copy when Float is float).
+struct Table_pack
+{
+    std::deque<std::vector<double>> dbl; std::deque<std::vector<int>> ints; std::deque<std::string> strs;   // deque: element addresses are stable
+    template<int N> const double* d(const Array<Float,N>& a)
+    {
+        if (a.size() == 0) return nullptr;
+        dbl.emplace_back(a.v().begin(), a.v().end());
+        return dbl.back().data();
+    }
+    const int* b(const Array<Bool,1>& a)
+    {
+        ints.emplace_back(a.v().begin(), a.v().end());
+        return ints.back().data();
+    }
+    const char* s(const Array<std::string,1>& a, int len)
+    {
+        strs.push_back(pad_names(a.v(), len));
+        return strs.back().c_str();
+    }
+};
+constexpr int kNameLen = 32;
+}  // namespace rrtmgp_b200
+
 class Gas_optics_rrtmgp_gpu : public Optical_props_gpu
 {
     public:
-        // The reference constructor takes the ~32 file variables as Array objects
-        // (include/Gas_optics_rrtmgp.h:293-364); here they arrive in one struct with the same
-        // names and file dimension orders (include/rrtmgp_b200_tables.h).
-        Gas_optics_rrtmgp_gpu(const Gas_concs_gpu& available_gases, const rrtmgp_b200_kdist_file& kdist)
+        // Longwave constructor, the reference's 32 positional arguments (include/Gas_optics_rrtmgp.h:293-325)
+        Gas_optics_rrtmgp_gpu(
+                const Gas_concs_gpu& available_gases,
+                const Array<std::string,1>& gas_names,
+                const Array<int,3>& key_species,
+                const Array<int,2>& band2gpt,
+                const Array<Float,2>& band_lims_wavenum,
+                const Array<Float,1>& press_ref,
+                const Float press_ref_trop,
+                const Array<Float,1>& temp_ref,
+                const Float temp_ref_p,
+                const Float temp_ref_t,
+                const Array<Float,3>& vmr_ref,
+                const Array<Float,4>& kmajor,
+                const Array<Float,3>& kminor_lower,
+                const Array<Float,3>& kminor_upper,
+                const Array<std::string,1>& gas_minor,
+                const Array<std::string,1>& identifier_minor,
+                const Array<std::string,1>& minor_gases_lower,
+                const Array<std::string,1>& minor_gases_upper,
+                const Array<int,2>& minor_limits_gpt_lower,
+                const Array<int,2>& minor_limits_gpt_upper,
+                const Array<Bool,1>& minor_scales_with_density_lower,
+                const Array<Bool,1>& minor_scales_with_density_upper,
+                const Array<std::string,1>& scaling_gas_lower,
+                const Array<std::string,1>& scaling_gas_upper,
+                const Array<Bool,1>& scale_by_complement_lower,
+                const Array<Bool,1>& scale_by_complement_upper,
+                const Array<int,1>& kminor_start_lower,
+                const Array<int,1>& kminor_start_upper,
+                const Array<Float,2>& totplnk,
+                const Array<Float,4>& planck_frac,
+                const Array<Float,3>& rayl_lower,
+                const Array<Float,3>& rayl_upper)
         {
-            const auto names = available_gases.names();
-            const std::string blk = rrtmgp_b200::pad_names(names, 32);
-            rrtmgp_b200::check(rrtmgp_b200_gas_optics_create(&kdist, (int)names.size(), blk.c_str(), 32, rrtmgp_b200::dtype, &h));
-            rrtmgp_b200::check(rrtmgp_b200_gas_optics_get_info(h, &info));
-            band2gpt.resize(2 * info.nbnd); gpt2band.resize(info.ngpt);
-            std::vector<double> wvn(2 * info.nbnd), sol(info.ngpt);
-            std::vector<char> gn((size_t)info.ngas * 32);
-            rrtmgp_b200::check(rrtmgp_b200_gas_optics_get_tables(h, band2gpt.data(), wvn.data(), gpt2band.data(), nullptr,
-                                                                 nullptr, gn.data(), 32, sol.data()));
-            band_lims_wvn.assign(wvn.begin(), wvn.end());
-            init();
-            for (int i = 0; i < info.ngas; ++i)
-            {
-                std::string s(gn.data() + (size_t)i * 32, 32);
-                gas_names.push_back(s.substr(0, s.find_last_not_of(' ') + 1));
-            }
+            rrtmgp_b200::Table_pack t;
+            rrtmgp_b200_kdist_file f = pack_common(t, gas_names, key_species, band2gpt, band_lims_wavenum, press_ref, press_ref_trop,
+                    temp_ref, temp_ref_p, temp_ref_t, vmr_ref, kmajor, kminor_lower, kminor_upper, gas_minor, identifier_minor,
+                    minor_gases_lower, minor_gases_upper, minor_limits_gpt_lower, minor_limits_gpt_upper,
+                    minor_scales_with_density_lower, minor_scales_with_density_upper, scaling_gas_lower, scaling_gas_upper,
+                    scale_by_complement_lower, scale_by_complement_upper, kminor_start_lower, kminor_start_upper, rayl_lower, rayl_upper);
+            f.n_planck_temps = totplnk.dim(1);
+            f.totplnk = t.d(totplnk); f.plank_fraction = t.d(planck_frac);
+            create(available_gases, f);
         }
-        ~Gas_optics_rrtmgp_gpu() { rrtmgp_b200_gas_optics_destroy(h); }
+        // Shortwave constructor, 35 positional arguments (include/Gas_optics_rrtmgp.h:328-364)
+        Gas_optics_rrtmgp_gpu(
+                const Gas_concs_gpu& available_gases,
+                const Array<std::string,1>& gas_names,
+                const Array<int,3>& key_species,
+                const Array<int,2>& band2gpt,
+                const Array<Float,2>& band_lims_wavenum,
+                const Array<Float,1>& press_ref,
+                const Float press_ref_trop,
+                const Array<Float,1>& temp_ref,
+                const Float temp_ref_p,
+                const Float temp_ref_t,
+                const Array<Float,3>& vmr_ref,
+                const Array<Float,4>& kmajor,
+                const Array<Float,3>& kminor_lower,
+                const Array<Float,3>& kminor_upper,
+                const Array<std::string,1>& gas_minor,
+                const Array<std::string,1>& identifier_minor,
+                const Array<std::string,1>& minor_gases_lower,
+                const Array<std::string,1>& minor_gases_upper,
+                const Array<int,2>& minor_limits_gpt_lower,
+                const Array<int,2>& minor_limits_gpt_upper,
+                const Array<Bool,1>& minor_scales_with_density_lower,
+                const Array<Bool,1>& minor_scales_with_density_upper,
+                const Array<std::string,1>& scaling_gas_lower,
+                const Array<std::string,1>& scaling_gas_upper,
+                const Array<Bool,1>& scale_by_complement_lower,
+                const Array<Bool,1>& scale_by_complement_upper,
+                const Array<int,1>& kminor_start_lower,
+                const Array<int,1>& kminor_start_upper,
+                const Array<Float,1>& solar_src_quiet,
+                const Array<Float,1>& solar_src_facular,
+                const Array<Float,1>& solar_src_sunspot,
+                const Float tsi_default,
+                const Float mg_default,
+                const Float sb_default,
+                const Array<Float,3>& rayl_lower,
+                const Array<Float,3>& rayl_upper)
+        {
+            rrtmgp_b200::Table_pack t;
+            rrtmgp_b200_kdist_file f = pack_common(t, gas_names, key_species, band2gpt, band_lims_wavenum, press_ref, press_ref_trop,
+                    temp_ref, temp_ref_p, temp_ref_t, vmr_ref, kmajor, kminor_lower, kminor_upper, gas_minor, identifier_minor,
+                    minor_gases_lower, minor_gases_upper, minor_limits_gpt_lower, minor_limits_gpt_upper,
+                    minor_scales_with_density_lower, minor_scales_with_density_upper, scaling_gas_lower, scaling_gas_upper,
+                    scale_by_complement_lower, scale_by_complement_upper, kminor_start_lower, kminor_start_upper, rayl_lower, rayl_upper);
+            f.solar_source_quiet = t.d(solar_src_quiet); f.solar_source_facular = t.d(solar_src_facular);
+            f.solar_source_sunspot = t.d(solar_src_sunspot);
+            f.tsi_default = tsi_default; f.mg_default = mg_default; f.sb_default = sb_default;
+            create(available_gases, f);
+        }
+        // The same variables as one struct in file order (include/rrtmgp_b200_tables.h): what this repository's own
+        // loaders (include/rrtmgp_b200/coefficients.hpp) produce.
+        Gas_optics_rrtmgp_gpu(const Gas_concs_gpu& available_gases, const rrtmgp_b200_kdist_file& kdist) { create(available_gases, kdist); }
+        ~Gas_optics_rrtmgp_gpu() { if (h) rrtmgp_b200_gas_optics_destroy(h); }
         Gas_optics_rrtmgp_gpu(const Gas_optics_rrtmgp_gpu&) = delete;
         Gas_optics_rrtmgp_gpu& operator=(const Gas_optics_rrtmgp_gpu&) = delete;
+        // returned by value by load_and_init_gas_optics (src_test/Radiation_solver.cu:243, :428)
+        Gas_optics_rrtmgp_gpu(Gas_optics_rrtmgp_gpu&& o) noexcept
+            : Optical_props_gpu(o), h(o.h), info(o.info), gas_names(std::move(o.gas_names)) { o.h = nullptr; }
 
         static void get_col_dry(Array_gpu<Float,2>& col_dry, const Array_gpu<Float,2>& vmr_h2o, const Array_gpu<Float,2>& plev)
         {
@@ -367,6 +490,65 @@ class Gas_optics_rrtmgp_gpu : public Optical_props_gpu
             const double lo = pressure ? info.press_ref_min : info.temp_ref_min, hi = pressure ? info.press_ref_max : info.temp_ref_max;
             rrtmgp_b200::check(rrtmgp_b200_check_range(rrtmgp_b200::dtype, a.size(), a.ptr(), lo, hi, name, rrtmgp_b200::stream()));
         }
+        void create(const Gas_concs_gpu& available_gases, const rrtmgp_b200_kdist_file& kdist)
+        {
+            const auto names = available_gases.names();
+            const std::string blk = rrtmgp_b200::pad_names(names, rrtmgp_b200::kNameLen);
+            rrtmgp_b200::check(rrtmgp_b200_gas_optics_create(&kdist, (int)names.size(), blk.c_str(), rrtmgp_b200::kNameLen,
+                                                             rrtmgp_b200::dtype | rrtmgp_b200::create_flags(), &h));
+            rrtmgp_b200::check(rrtmgp_b200_gas_optics_get_info(h, &info));
+            std::vector<int> lims(2 * (size_t)info.nbnd), g2b((size_t)info.ngpt);
+            std::vector<double> wvn(2 * (size_t)info.nbnd), sol((size_t)info.ngpt);
+            std::vector<char> gn((size_t)info.ngas * rrtmgp_b200::kNameLen);
+            rrtmgp_b200::check(rrtmgp_b200_gas_optics_get_tables(h, lims.data(), wvn.data(), g2b.data(), nullptr,
+                                                                 nullptr, gn.data(), rrtmgp_b200::kNameLen, sol.data()));
+            set_spectral(wvn, lims);
+            for (int i = 0; i < info.ngas; ++i)
+            {
+                std::string s(gn.data() + (size_t)i * rrtmgp_b200::kNameLen, rrtmgp_b200::kNameLen);
+                gas_names.push_back(s.substr(0, s.find_last_not_of(' ') + 1));
+            }
+        }
+        // the 28 arguments the two constructors share -> the file struct (dimension names: rrtmgp_b200_tables.h)
+        static rrtmgp_b200_kdist_file pack_common(rrtmgp_b200::Table_pack& t,
+                const Array<std::string,1>& gas_names, const Array<int,3>& key_species, const Array<int,2>& band2gpt,
+                const Array<Float,2>& band_lims_wavenum, const Array<Float,1>& press_ref, const Float press_ref_trop,
+                const Array<Float,1>& temp_ref, const Float temp_ref_p, const Float temp_ref_t, const Array<Float,3>& vmr_ref,
+                const Array<Float,4>& kmajor, const Array<Float,3>& kminor_lower, const Array<Float,3>& kminor_upper,
+                const Array<std::string,1>& gas_minor, const Array<std::string,1>& identifier_minor,
+                const Array<std::string,1>& minor_gases_lower, const Array<std::string,1>& minor_gases_upper,
+                const Array<int,2>& minor_limits_gpt_lower, const Array<int,2>& minor_limits_gpt_upper,
+                const Array<Bool,1>& dens_lower, const Array<Bool,1>& dens_upper,
+                const Array<std::string,1>& scaling_gas_lower, const Array<std::string,1>& scaling_gas_upper,
+                const Array<Bool,1>& comp_lower, const Array<Bool,1>& comp_upper,
+                const Array<int,1>& kminor_start_lower, const Array<int,1>& kminor_start_upper,
+                const Array<Float,3>& rayl_lower, const Array<Float,3>& rayl_upper)
+        {
+            const int L = rrtmgp_b200::kNameLen;
+            rrtmgp_b200_kdist_file f{};
+            f.n_temps = temp_ref.dim(1); f.n_press = press_ref.dim(1); f.n_absorbers = gas_names.dim(1);
+            f.n_minorabsorbers = gas_minor.dim(1); f.n_extabsorbers = vmr_ref.dim(2); f.n_mixingfracs = kmajor.dim(2);
+            f.n_layers = vmr_ref.dim(1); f.n_bnds = band2gpt.dim(2); f.n_gpts = kmajor.dim(1); f.n_pairs = 2;
+            f.n_minor_lower = minor_limits_gpt_lower.dim(2); f.n_minor_upper = minor_limits_gpt_upper.dim(2);
+            f.n_contrib_lower = kminor_lower.dim(1); f.n_contrib_upper = kminor_upper.dim(1);
+            f.n_planck_temps = 0; f.string_len = L;
+            if (kmajor.dim(3) != f.n_press + 1 || kmajor.dim(4) != f.n_temps || key_species.dim(1) != 2 || key_species.dim(3) != f.n_bnds)
+                throw std::runtime_error("Gas_optics_rrtmgp_gpu: inconsistent table dimensions");
+            f.gas_names = t.s(gas_names, L); f.key_species = key_species.ptr();
+            f.bnd_limits_wavenumber = t.d(band_lims_wavenum); f.bnd_limits_gpt = band2gpt.ptr();
+            f.press_ref = t.d(press_ref); f.temp_ref = t.d(temp_ref);
+            f.absorption_coefficient_ref_P = temp_ref_p; f.absorption_coefficient_ref_T = temp_ref_t; f.press_ref_trop = press_ref_trop;
+            f.vmr_ref = t.d(vmr_ref); f.kmajor = t.d(kmajor); f.kminor_lower = t.d(kminor_lower); f.kminor_upper = t.d(kminor_upper);
+            f.gas_minor = t.s(gas_minor, L); f.identifier_minor = t.s(identifier_minor, L);
+            f.minor_gases_lower = t.s(minor_gases_lower, L); f.minor_gases_upper = t.s(minor_gases_upper, L);
+            f.minor_limits_gpt_lower = minor_limits_gpt_lower.ptr(); f.minor_limits_gpt_upper = minor_limits_gpt_upper.ptr();
+            f.minor_scales_with_density_lower = t.b(dens_lower); f.minor_scales_with_density_upper = t.b(dens_upper);
+            f.scale_by_complement_lower = t.b(comp_lower); f.scale_by_complement_upper = t.b(comp_upper);
+            f.scaling_gas_lower = t.s(scaling_gas_lower, L); f.scaling_gas_upper = t.s(scaling_gas_upper, L);
+            f.kminor_start_lower = kminor_start_lower.ptr(); f.kminor_start_upper = kminor_start_upper.ptr();
+            f.rayl_lower = t.d(rayl_lower); f.rayl_upper = t.d(rayl_upper);
+            return f;
+        }
         rrtmgp_b200_gas_optics* h = nullptr;
         rrtmgp_b200_gas_optics_info info{};
         std::vector<std::string> gas_names;
@@ -375,11 +557,34 @@ class Gas_optics_rrtmgp_gpu : public Optical_props_gpu
 class Cloud_optics_gpu : public Optical_props_gpu
 {
     public:
+        // the reference's positional constructor (include/Cloud_optics.h:84-89; arrays as load_and_init_cloud_optics
+        // builds them, src_test/Radiation_solver.cu:327-364: band_lims_wvn (2, nband), lut_*liq (nsize_liq, nband),
+        // lut_*ice (nsize_ice, nband, nrghice))
+        Cloud_optics_gpu(
+                const Array<Float,2>& band_lims_wvn,
+                const Float radliq_lwr, const Float radliq_upr, const Float radliq_fac,
+                const Float diamice_lwr, const Float diamice_upr, const Float diamice_fac,
+                const Array<Float,2>& lut_extliq, const Array<Float,2>& lut_ssaliq, const Array<Float,2>& lut_asyliq,
+                const Array<Float,3>& lut_extice, const Array<Float,3>& lut_ssaice, const Array<Float,3>& lut_asyice)
+            : Optical_props_gpu(band_lims_wvn)
+        {
+            rrtmgp_b200::Table_pack t;
+            rrtmgp_b200_cloud_file f{};
+            f.n_band = band_lims_wvn.dim(2); f.n_rghice = lut_extice.dim(3); f.n_size_liq = lut_extliq.dim(1); f.n_size_ice = lut_extice.dim(1);
+            if (lut_extliq.dim(2) != f.n_band || lut_extice.dim(2) != f.n_band) throw std::runtime_error("Cloud_optics_gpu: inconsistent table dimensions");
+            f.bnd_limits_wavenumber = t.d(band_lims_wvn);
+            f.radliq_lwr = radliq_lwr; f.radliq_upr = radliq_upr; f.radliq_fac = radliq_fac;
+            f.diamice_lwr = diamice_lwr; f.diamice_upr = diamice_upr; f.diamice_fac = diamice_fac;
+            f.lut_extliq = t.d(lut_extliq); f.lut_ssaliq = t.d(lut_ssaliq); f.lut_asyliq = t.d(lut_asyliq);
+            f.lut_extice = t.d(lut_extice); f.lut_ssaice = t.d(lut_ssaice); f.lut_asyice = t.d(lut_asyice);
+            rrtmgp_b200::check(rrtmgp_b200_cloud_optics_create(&f, rrtmgp_b200::dtype, &h));
+        }
         explicit Cloud_optics_gpu(const rrtmgp_b200_cloud_file& lut)
-            : Optical_props_gpu(std::vector<Float>(lut.bnd_limits_wavenumber, lut.bnd_limits_wavenumber + 2 * lut.n_band))
+            : Optical_props_gpu(Array<Float,2>(std::vector<Float>(lut.bnd_limits_wavenumber, lut.bnd_limits_wavenumber + 2 * lut.n_band), {2, lut.n_band}))
         { rrtmgp_b200::check(rrtmgp_b200_cloud_optics_create(&lut, rrtmgp_b200::dtype, &h)); }
-        ~Cloud_optics_gpu() { rrtmgp_b200_cloud_optics_destroy(h); }
+        ~Cloud_optics_gpu() { if (h) rrtmgp_b200_cloud_optics_destroy(h); }
         Cloud_optics_gpu(const Cloud_optics_gpu&) = delete;
+        Cloud_optics_gpu(Cloud_optics_gpu&& o) noexcept : Optical_props_gpu(o), h(o.h) { o.h = nullptr; }
         void cloud_optics(const Array_gpu<Float,2>& clwp, const Array_gpu<Float,2>& ciwp, const Array_gpu<Float,2>& reliq,
                           const Array_gpu<Float,2>& deice, Optical_props_2str_gpu& optical_props)
         {
@@ -415,17 +620,35 @@ inline rrtmgp_b200_aerosol_concs aerosol_view(const Aerosol_concs_gpu& a)
 }
 }  // namespace rrtmgp_b200
 
-// include/Aerosol_optics.h:48-84.  The reference constructor takes eight Arrays already reshaped to
-// (band, [humidity,] type); here the file variables arrive in one struct in file order.  Like the reference's
-// loader (src_test/Radiation_solver.cu:366-402) the band limits stay zero.
+// include/Aerosol_optics.h:48-84.  Like the reference's loader (src_test/Radiation_solver.cu:366-402) the band
+// limits of the struct constructor stay zero.
 class Aerosol_optics_gpu : public Optical_props_gpu
 {
     public:
+        // the reference's positional constructor (include/Aerosol_optics.h:53-56; arrays as load_and_init_aerosol_optics
+        // builds them, src_test/Radiation_solver.cu:366-402: m*_phobic (band, hydrophobic), m*_philic (band, humidity, hydrophilic))
+        Aerosol_optics_gpu(
+                const Array<Float,2>& band_lims_wvn, const Array<Float,1>& rh_upper,
+                const Array<Float,2>& mext_phobic, const Array<Float,2>& ssa_phobic, const Array<Float,2>& g_phobic,
+                const Array<Float,3>& mext_philic, const Array<Float,3>& ssa_philic, const Array<Float,3>& g_philic)
+            : Optical_props_gpu(band_lims_wvn)
+        {
+            rrtmgp_b200::Table_pack t;
+            rrtmgp_b200_aerosol_file f{};
+            f.n_band = band_lims_wvn.dim(2); f.n_hum = rh_upper.dim(1); f.n_philic = mext_philic.dim(3); f.n_phobic = mext_phobic.dim(2);
+            if (mext_phobic.dim(1) != f.n_band || mext_philic.dim(1) != f.n_band || mext_philic.dim(2) != f.n_hum)
+                throw std::runtime_error("Aerosol_optics_gpu: inconsistent table dimensions");
+            f.mass_ext_sw_hydrophobic = t.d(mext_phobic); f.ssa_sw_hydrophobic = t.d(ssa_phobic); f.asymmetry_sw_hydrophobic = t.d(g_phobic);
+            f.mass_ext_sw_hydrophilic = t.d(mext_philic); f.ssa_sw_hydrophilic = t.d(ssa_philic); f.asymmetry_sw_hydrophilic = t.d(g_philic);
+            f.relative_humidity2 = t.d(rh_upper);
+            rrtmgp_b200::check(rrtmgp_b200_aerosol_optics_create(&f, rrtmgp_b200::dtype, &h));
+        }
         explicit Aerosol_optics_gpu(const rrtmgp_b200_aerosol_file& lut)
-            : Optical_props_gpu(std::vector<Float>(2 * (size_t)lut.n_band, Float(0.)))
+            : Optical_props_gpu(Array<Float,2>({2, lut.n_band}))
         { rrtmgp_b200::check(rrtmgp_b200_aerosol_optics_create(&lut, rrtmgp_b200::dtype, &h)); }
-        ~Aerosol_optics_gpu() { rrtmgp_b200_aerosol_optics_destroy(h); }
+        ~Aerosol_optics_gpu() { if (h) rrtmgp_b200_aerosol_optics_destroy(h); }
         Aerosol_optics_gpu(const Aerosol_optics_gpu&) = delete;
+        Aerosol_optics_gpu(Aerosol_optics_gpu&& o) noexcept : Optical_props_gpu(o), h(o.h) { o.h = nullptr; }
         void aerosol_optics(const Aerosol_concs_gpu& aerosol_concs, const Array_gpu<Float,2>& rh, const Array_gpu<Float,2>& plev,
                             Optical_props_2str_gpu& optical_props) const
         {
@@ -445,7 +668,7 @@ class Rte_lw_gpu
                                          Array_gpu<Float,2>& arr_out)
         {
             rrtmgp_b200::check(rrtmgp_b200_expand_and_transpose(rrtmgp_b200::dtype, arr_in.dim(2), arr_in.dim(1), ops->get_ngpt(),
-                    ops->get_band_lims_gpoint().data(), arr_in.ptr(), arr_out.ptr(), rrtmgp_b200::stream()));
+                    ops->get_band_lims_gpoint().ptr(), arr_in.ptr(), arr_out.ptr(), rrtmgp_b200::stream()));
         }
         // include/Rte_lw.h:62-77; broadband iff gpt_flux_up.dim(3) == 1 (src/Rte_lw.cpp:170)
         static void rte_lw(const std::unique_ptr<Optical_props_arry_gpu>& optical_props, const Bool top_at_1,
@@ -537,6 +760,11 @@ class Fluxes_broadband_gpu
         Array_gpu<Float,2>& get_flux_dn() { return flux_dn; }
         Array_gpu<Float,2>& get_flux_dn_dir() { return flux_dn_dir; }
         Array_gpu<Float,2>& get_flux_net() { return flux_net; }
+        // include/Fluxes.h:169-172
+        virtual Array_gpu<Float,3>& get_bnd_flux_up() { throw std::runtime_error("Band fluxes are not available"); }
+        virtual Array_gpu<Float,3>& get_bnd_flux_dn() { throw std::runtime_error("Band fluxes are not available"); }
+        virtual Array_gpu<Float,3>& get_bnd_flux_dn_dir() { throw std::runtime_error("Band fluxes are not available"); }
+        virtual Array_gpu<Float,3>& get_bnd_flux_net() { throw std::runtime_error("Band fluxes are not available"); }
     protected:
         static void sum(const Array_gpu<Float,3>& g, Array_gpu<Float,2>& f)
         {
@@ -567,15 +795,15 @@ class Fluxes_byband_gpu : public Fluxes_broadband_gpu
             reduce(gpt_flux_up, gpt_flux_dn, spectral_disc, top_at_1);
             sum(gpt_flux_dn_dir, flux_dn_dir); sumb(gpt_flux_dn_dir, bnd_flux_dn_dir, spectral_disc);
         }
-        Array_gpu<Float,3>& get_bnd_flux_up() { return bnd_flux_up; }
-        Array_gpu<Float,3>& get_bnd_flux_dn() { return bnd_flux_dn; }
-        Array_gpu<Float,3>& get_bnd_flux_dn_dir() { return bnd_flux_dn_dir; }
-        Array_gpu<Float,3>& get_bnd_flux_net() { return bnd_flux_net; }
+        Array_gpu<Float,3>& get_bnd_flux_up() override { return bnd_flux_up; }
+        Array_gpu<Float,3>& get_bnd_flux_dn() override { return bnd_flux_dn; }
+        Array_gpu<Float,3>& get_bnd_flux_dn_dir() override { return bnd_flux_dn_dir; }
+        Array_gpu<Float,3>& get_bnd_flux_net() override { return bnd_flux_net; }
     private:
         static void sumb(const Array_gpu<Float,3>& g, Array_gpu<Float,3>& f, const std::unique_ptr<Optical_props_arry_gpu>& d)
         {
             rrtmgp_b200::check(rrtmgp_b200_sum_byband(rrtmgp_b200::dtype, g.dim(1), g.dim(2), g.dim(3), d->get_nband(),
-                    d->get_band_lims_gpoint().data(), g.ptr(), f.ptr(), rrtmgp_b200::stream()));
+                    d->get_band_lims_gpoint().ptr(), g.ptr(), f.ptr(), rrtmgp_b200::stream()));
         }
         Array_gpu<Float,3> bnd_flux_up, bnd_flux_dn, bnd_flux_dn_dir, bnd_flux_net;
 };
@@ -591,11 +819,18 @@ class Radiation_solver_longwave
                                   const rrtmgp_b200_cloud_file* cloud = nullptr)
             : kdist_gpu(std::make_unique<Gas_optics_rrtmgp_gpu>(gas_concs, kdist))
         { if (cloud) cloud_optics_gpu = std::make_unique<Cloud_optics_gpu>(*cloud); }
+        // from objects a caller built itself with the reference's positional constructors (what the reference's own
+        // constructor does with load_and_init_gas_optics / load_and_init_cloud_optics, src_test/Radiation_solver.cu:404-416)
+        explicit Radiation_solver_longwave(Gas_optics_rrtmgp_gpu&& kdist)
+            : kdist_gpu(std::make_unique<Gas_optics_rrtmgp_gpu>(std::move(kdist))) {}
+        Radiation_solver_longwave(Gas_optics_rrtmgp_gpu&& kdist, Cloud_optics_gpu&& cloud)
+            : kdist_gpu(std::make_unique<Gas_optics_rrtmgp_gpu>(std::move(kdist))),
+              cloud_optics_gpu(std::make_unique<Cloud_optics_gpu>(std::move(cloud))) {}
 
         int get_n_gpt_gpu() const { return kdist_gpu->get_ngpt(); }
         int get_n_bnd_gpu() const { return kdist_gpu->get_nband(); }
-        const std::vector<int>& get_band_lims_gpoint_gpu() const { return kdist_gpu->get_band_lims_gpoint(); }
-        const std::vector<Float>& get_band_lims_wavenumber_gpu() const { return kdist_gpu->get_band_lims_wavenumber(); }
+        const Array<int,2>& get_band_lims_gpoint_gpu() const { return kdist_gpu->get_band_lims_gpoint(); }
+        const Array<Float,2>& get_band_lims_wavenumber_gpu() const { return kdist_gpu->get_band_lims_wavenumber(); }
         Gas_optics_rrtmgp_gpu& get_kdist_gpu() { return *kdist_gpu; }
         void set_n_gauss_angles(const int n) { n_gauss_angles = n; }
 
@@ -684,12 +919,21 @@ class Radiation_solver_shortwave
             if (cloud) cloud_optics_gpu = std::make_unique<Cloud_optics_gpu>(*cloud);
             if (aerosol) aerosol_optics_gpu = std::make_unique<Aerosol_optics_gpu>(*aerosol);
         }
+        explicit Radiation_solver_shortwave(Gas_optics_rrtmgp_gpu&& kdist)
+            : kdist_gpu(std::make_unique<Gas_optics_rrtmgp_gpu>(std::move(kdist))) {}
+        Radiation_solver_shortwave(Gas_optics_rrtmgp_gpu&& kdist, Cloud_optics_gpu&& cloud)
+            : kdist_gpu(std::make_unique<Gas_optics_rrtmgp_gpu>(std::move(kdist))),
+              cloud_optics_gpu(std::make_unique<Cloud_optics_gpu>(std::move(cloud))) {}
+        Radiation_solver_shortwave(Gas_optics_rrtmgp_gpu&& kdist, Cloud_optics_gpu&& cloud, Aerosol_optics_gpu&& aerosol)
+            : kdist_gpu(std::make_unique<Gas_optics_rrtmgp_gpu>(std::move(kdist))),
+              cloud_optics_gpu(std::make_unique<Cloud_optics_gpu>(std::move(cloud))),
+              aerosol_optics_gpu(std::make_unique<Aerosol_optics_gpu>(std::move(aerosol))) {}
 
         int get_n_gpt_gpu() const { return kdist_gpu->get_ngpt(); }
         int get_n_bnd_gpu() const { return kdist_gpu->get_nband(); }
         Float get_tsi_gpu() const { return kdist_gpu->get_tsi(); }
-        const std::vector<int>& get_band_lims_gpoint_gpu() const { return kdist_gpu->get_band_lims_gpoint(); }
-        const std::vector<Float>& get_band_lims_wavenumber_gpu() const { return kdist_gpu->get_band_lims_wavenumber(); }
+        const Array<int,2>& get_band_lims_gpoint_gpu() const { return kdist_gpu->get_band_lims_gpoint(); }
+        const Array<Float,2>& get_band_lims_wavenumber_gpu() const { return kdist_gpu->get_band_lims_wavenumber(); }
         Gas_optics_rrtmgp_gpu& get_kdist_gpu() { return *kdist_gpu; }
 
         // the aerosol-free call of earlier callers

@@ -127,13 +127,13 @@ class RefCuda:
         ins = [F(x) for x in (atm.play, atm.plev, atm.tlay, atm.tlev, atm.tsfc)]
         q = lambda k: P(o[k]) if k in o else c_dbl_p()
         ip = lambda k: o[k].ctypes.data_as(C.POINTER(C.c_int))
-        nf = C.c_int()
+        nf, ng = C.c_int(nflav), C.c_int(ngas)          # in: what the buffers are sized for; the shim refuses a mismatch
         self._chk(self.L.refcuda_stage_gas_optics(
             self.h, w, ncol, nlay, len(vn), self._pack_strings(vn), self._len, ptrs, nc, nl, *[P(x) for x in ins],
             ip("jtemp"), ip("jpress"), o["tropo"].ctypes.data_as(C.POINTER(C.c_byte)), ip("jeta"),
             q("fmajor"), q("fminor"), q("col_mix"), q("col_gas"), q("tau"), q("ssa"), q("g"),
-            q("lay_src"), q("lev_src"), q("sfc_src"), q("sfc_src_jac"), q("toa_src"), q("col_dry"), C.byref(nf)))
-        assert nf.value == nflav, (nf.value, nflav)
+            q("lay_src"), q("lev_src"), q("sfc_src"), q("sfc_src_jac"), q("toa_src"), q("col_dry"), C.byref(nf), C.byref(ng)))
+        assert (nf.value, ng.value) == (nflav, ngas), ("flavors / gases of the reference class differ from the caller's", nf.value, ng.value, nflav, ngas)
         return o
 
     def rte_lw(self, tau, lay_src, lev_src, sfc_src, emis, top_at_1):

@@ -240,14 +240,19 @@ int refcuda_stage_gas_optics(void* hv, int which, int ncol, int nlay, int ngas, 
                              double* fmajor_o, double* fminor_o, double* col_mix_o, double* col_gas_o,
                              double* tau_o, double* ssa_o, double* g_o,
                              double* lay_src_o, double* lev_src_o, double* sfc_src_o, double* sfc_jac_o, double* toa_o,
-                             double* col_dry_o, int* nflav_o)
+                             double* col_dry_o, int* nflav_o, int* ngas_o)
 {
     SHIM_TRY
     auto* R = static_cast<Ref_cuda*>(hv);
     Gas_optics_rrtmgp_gpu* K = which == 0 ? R->lw.get() : R->sw.get();
     if (!K) throw std::runtime_error("refcuda_stage_gas_optics: k-distribution not loaded");
     const int nlev = nlay + 1, ngpt = K->get_ngpt(), nband = K->get_nband(), nflav = K->get_nflav();
+    // in: the sizes the caller allocated for (negative = unknown); out: the class's own.  A mismatch stops before any write.
+    const int nflav_in = nflav_o ? *nflav_o : -1, ngas_in = ngas_o ? *ngas_o : -1;
     if (nflav_o) *nflav_o = nflav;
+    if (ngas_o) *ngas_o = K->get_ngas();
+    if ((nflav_in >= 0 && nflav_in != nflav) || (ngas_in >= 0 && ngas_in != K->get_ngas()))
+        throw std::runtime_error("refcuda_stage_gas_optics: caller's nflav / ngas differ from the reference class's (different available gases?)");
     Gas_concs gc = host_concs(ngas, names, len, vmr, vnc, vnl);
     Gas_concs_gpu gas(gc);
     auto p_lay = up<2>(play, {ncol, nlay}); auto p_lev = up<2>(plev, {ncol, nlev}); auto t_lay = up<2>(tlay, {ncol, nlay});

@@ -54,6 +54,7 @@ SYMBOLS = {
     "rrtmgp_b200_gas_optics_destroy": (None, [vp]),
     "rrtmgp_b200_gas_optics_get_info": (i, [vp, C.POINTER(GasOpticsInfoC)]),
     "rrtmgp_b200_gas_optics_get_tables": (i, [vp, ip, C.POINTER(d), ip, ip, ip, C.c_char_p, i, C.POINTER(d)]),
+    "rrtmgp_b200_gas_optics_table_hash": (i, [vp, C.POINTER(C.c_ulonglong)]),
     "rrtmgp_b200_gas_optics_get_minor": (i, [vp, i, ip, ip, ip, ip, ip, ip]),
     "rrtmgp_b200_get_col_dry": (i, [i, i, i, vp, vp, vp, vp]),
     "rrtmgp_b200_interpolation": (i, [vp, i, i, vp, vp, vp, C.POINTER(GasConcsC), vp, vp, vp, vp, vp, vp, vp, vp, vp]),
@@ -84,6 +85,8 @@ SYMBOLS = {
     "rrtmgp_b200_net_flux": (i, [i, sz, vp, vp, vp, vp]),
     "rrtmgp_b200_scale_columns": (i, [i, i, i, vp, vp, vp]),
     "rrtmgp_b200_heating_rate": (i, [i, i, i, vp, vp, vp, vp, vp]),
+    "rrtmgp_b200_array_fill": (i, [i, C.c_longlong, vp, vp, vp]),
+    "rrtmgp_b200_array_subset": (i, [i, i, ip, ip, ip, ip, vp, vp, vp]),
     "rrtmgp_b200_lw_fluxes": (i, [vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp]),
     "rrtmgp_b200_sw_fluxes": (i, [vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp]),
     "rrtmgp_b200_fluxes_host": (i, [vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), i, vp]),

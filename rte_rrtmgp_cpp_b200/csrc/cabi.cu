@@ -334,6 +334,37 @@ int rrtmgp_b200_gas_optics_get_tables(const rrtmgp_b200_gas_optics* g, int* band
     return 0;
 }
 
+/* 64-bit FNV-1a over every prepared table of the handle (device-layout kmajor / planck_frac, Rayleigh, both minor
+ * sides, Planck, solar source, reference grids and all index tables): two handles with equal hashes were built from
+ * bit-identical coefficients and available-gas lists.  HOST function. */
+int rrtmgp_b200_gas_optics_table_hash(const rrtmgp_b200_gas_optics* g, unsigned long long* out)
+{
+    if (!g || !out) return fail(RRTMGP_B200_E_ARG, "table_hash: null argument");
+    unsigned long long hsh = 1469598103934665603ull;
+    auto mix = [&](const void* p, size_t n) { const unsigned char* b = (const unsigned char*)p; for (size_t i = 0; i < n; ++i) { hsh ^= b[i]; hsh *= 1099511628211ull; } };
+    auto vd = [&](const std::vector<double>& v) { const size_t n = v.size(); mix(&n, sizeof n); if (n) mix(v.data(), n * sizeof(double)); };
+    auto vi = [&](const std::vector<int>& v) { const size_t n = v.size(); mix(&n, sizeof n); if (n) mix(v.data(), n * sizeof(int)); };
+    const HostPlan& h = g->h;
+    const int dims[] = {h.is_lw, h.ntemp, h.npres, h.neta, h.nbnd, h.ngpt, h.nflav, h.ngas, h.gw, h.nplanck, h.idx_h2o, h.row_stride, h.nscal, h.nuniq};
+    mix(dims, sizeof dims);
+    for (auto& s : h.gas_names) mix(s.data(), s.size() + 1);
+    vi(h.band_lims_gpt); vd(h.band_lims_wvn); vi(h.gpoint_bands); vi(h.flavor); vi(h.gpoint_flavor); vi(h.band_flavor);
+    vd(h.vmr_ref); vd(h.press_ref); vd(h.press_ref_log); vd(h.temp_ref);
+    const double sc[] = {h.press_ref_log_delta, h.temp_ref_min, h.temp_ref_max, h.temp_ref_delta, h.press_ref_min, h.press_ref_max,
+                         h.press_ref_trop_log, h.totplnk_delta, h.tsi};
+    mix(sc, sizeof sc);
+    vd(h.kmajor); vd(h.krayl); vd(h.totplnk); vd(h.solar_source);
+    for (int s = 0; s < 2; ++s)
+    {
+        const MinorSide& m = h.minor[s];
+        mix(&m.n, sizeof m.n); mix(&m.nk, sizeof m.nk);
+        vi(m.limits); vi(m.kstart); vd(m.kminor_ref); vd(m.table); vi(m.uid); vi(m.uniq_rep); vi(m.scal_off); vi(m.slot_desc);
+        if (!m.desc.empty()) mix(m.desc.data(), m.desc.size() * sizeof(m.desc[0]));
+    }
+    *out = hsh;
+    return 0;
+}
+
 int rrtmgp_b200_profile(int enable, double* lw_ms, long long* lw_launches, double* sw_ms, long long* sw_launches)
 {
     // collect: synchronises the device, folds the recorded event pairs into milliseconds
@@ -907,6 +938,36 @@ int rrtmgp_b200_scale_columns(int dtype, int ncol, int n2, void* x, const void* 
         if (ncol < 1 || n2 < 1 || !x || !scale) throw ArgError("scale_columns: bad argument");
         DISPATCH(dtype, launch_scale_columns<float>(ncol, n2, x, scale, (cudaStream_t)stream),
                         launch_scale_columns<double>(ncol, n2, x, scale, (cudaStream_t)stream));
+    });
+}
+/* Array_gpu::fill / Array_gpu::subset (include/Array.h:311-350, 515-524, 579-622) */
+int rrtmgp_b200_array_fill(int elem_bytes, long long n, void* d_a, const void* value, void* stream)
+{
+    return guarded([&] {
+        if (n < 0 || (n > 0 && !d_a) || !value) throw ArgError("array_fill: bad argument");
+        if (n == 0) return;
+        if (!launch_array_fill(elem_bytes, d_a, value, (size_t)n, (cudaStream_t)stream)) throw ArgError("array_fill: element size must be 1, 2, 4, 8 or 16 bytes");
+    });
+}
+int rrtmgp_b200_array_subset(int elem_bytes, int ndim, const int* src_dims, const int* src_offsets, const int* first,
+                             const int* sub_dims, const void* d_src, void* d_sub, void* stream)
+{
+    return guarded([&] {
+        if (ndim < 1 || ndim > SubsetGeom::MAXD || !src_dims || !first || !sub_dims || !d_src || !d_sub) throw ArgError("array_subset: bad argument");
+        SubsetGeom g{};
+        g.ndim = ndim;
+        size_t n = 1, stride = 1;
+        for (int k = 0; k < ndim; ++k)
+        {
+            const int off = src_offsets ? src_offsets[k] : 0;
+            g.extent[k] = sub_dims[k]; g.spread[k] = src_dims[k] == 1; g.stride[k] = stride;
+            g.start0[k] = first[k] - off - 1;
+            if (sub_dims[k] < 1 || src_dims[k] < 1) throw ArgError("array_subset: empty dimension");
+            if (!g.spread[k] && (g.start0[k] < 0 || g.start0[k] + sub_dims[k] > src_dims[k])) throw ArgError("array_subset: range outside the array");
+            if (g.spread[k]) g.start0[k] = -off;          // index 1 of a broadcast dimension (include/Array.h:329)
+            n *= (size_t)sub_dims[k]; stride *= (size_t)src_dims[k];
+        }
+        if (!launch_array_subset(elem_bytes, d_sub, d_src, g, n, (cudaStream_t)stream)) throw ArgError("array_subset: element size must be 1, 2, 4, 8 or 16 bytes");
     });
 }
 int rrtmgp_b200_heating_rate(int dtype, int ncol, int nlay, const void* up, const void* dn, const void* plev, void* hr, void* stream)

@@ -62,6 +62,19 @@ void launch_heating_rate(int ncol, int nlay, const void* up, const void* dn, con
 template<typename Real>
 void launch_range_flag(size_t n, const void* x, double lo, double hi, int* d_flag, cudaStream_t s);
 
+// arrays.cu : Array_gpu::fill / Array_gpu::subset, type-erased by element size (false = unsupported size)
+struct SubsetGeom
+{
+    static constexpr int MAXD = 8;
+    int ndim;
+    int extent[MAXD];          // extents of the window (= the output array)
+    int start0[MAXD];          // 0-based first source index of the window per dimension
+    size_t stride[MAXD];       // column-major strides of the source
+    bool spread[MAXD];         // source extent 1: broadcast
+};
+bool launch_array_fill(int elem_bytes, void* a, const void* value, size_t n, cudaStream_t s);
+bool launch_array_subset(int elem_bytes, void* out, const void* in, const SubsetGeom& g, size_t n, cudaStream_t s);
+
 // gasopt.cu : materialised gas optics of one band from a TileState (c0 = 0, nc = ncol)
 template<typename Real> struct GasOut
 {

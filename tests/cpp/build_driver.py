@@ -14,9 +14,19 @@ def path(tag: str) -> str:
     return os.path.join(HERE, f"libclasses_driver_{tag}.so")
 
 
+def ctor_path(tag: str) -> str:
+    return os.path.join(HERE, f"libctor_driver_{tag}.so")
+
+
 def build(force: bool = False) -> None:
-    src = os.path.join(HERE, "classes_driver.cpp")
-    hdrs = [os.path.join(ROOT, "include", "rrtmgp_b200", "classes.hpp"), os.path.join(ROOT, "include", "rrtmgp_b200.h"), src]
+    _build("classes_driver.cpp", path, force)
+    _build("ctor_driver.cpp", ctor_path, force)
+
+
+def _build(source: str, path, force: bool) -> None:
+    src = os.path.join(HERE, source)
+    hdrs = [os.path.join(ROOT, "include", "rrtmgp_b200", "classes.hpp"), os.path.join(ROOT, "include", "rrtmgp_b200", "array.hpp"),
+            os.path.join(ROOT, "include", "rrtmgp_b200.h"), src]
     newest = max(os.path.getmtime(h) for h in hdrs)
     for tag, defs in (("f64", []), ("f32", ["-DRTE_USE_SP"])):
         out = path(tag)

@@ -150,3 +150,91 @@ def test_clear_sky_no_bands_and_range_error():
     bad.tlay[3, 5] = 1000.0
     rc, msg, _ = run_lw("f64", kd, bad, mode=1)
     assert rc == 2 and "out of range" in msg
+
+
+# ---- set-up half of the boundary: host Array / Array_gpu and the reference's positional constructors -----------------
+def _ctor(tag):
+    capi.lib()
+    build_driver.build()
+    d = C.CDLL(build_driver.ctor_path(tag))
+    d.ctor_last_message.restype = C.c_char_p
+    assert d.ctor_float_bytes() == (8 if tag == "f64" else 4)
+    return d
+
+
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+def test_host_array_has_the_reference_semantics(tag):
+    """include/Array.h:94-297: column-major, 1-based operator(), offsets, subset with broadcast, move leaves the source
+    empty, set_dims / expand_dims errors; Gas_concs scalar / profile / field and column subset (no device needed)."""
+    d = _ctor(tag)
+    assert d.ctor_array_host_selftest() == 0, d.ctor_last_message().decode()
+
+
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+@pytest.mark.parametrize("kind", ["lw", "sw"])
+def test_positional_constructor_builds_identical_tables(kind, tag):
+    """Gas_optics_rrtmgp_gpu through the reference's 32 / 35 positional Array arguments (include/Gas_optics_rrtmgp.h:
+    293-364), fed like load_and_init_gas_optics feeds them, against the struct constructor: every prepared table
+    (hash over coefficients in device layout, index tables, grids, retained gases) bit-identical.  Host-only handles."""
+    d = _ctor(tag)
+    kd = synthetic_kdist(kind)
+    if tag == "f32":
+        # an RTE_USE_SP caller holds the file variables as float Arrays: compare on float-representable coefficients
+        import copy
+        kd = copy.copy(kd)
+        for k, v in vars(kd).items():
+            if isinstance(v, np.ndarray) and v.dtype == np.float64:
+                setattr(kd, k, v.astype(np.float32).astype(np.float64))
+            elif isinstance(v, float):
+                setattr(kd, k, float(np.float32(v)))
+    kc, keep = ctables.pack_kdist(kd)
+    for gases in (["h2o", "co2", "o3", "n2o", "ch4", "n2", "o2"], ["h2o", "co2", "o3", "n2o", "ch4", "n2", "o2", "co", "cfc11", "no2"]):
+        rc = d.ctor_tables_equal(C.byref(kc), len(gases), ctables.pack_strings(gases, 32), 32, 1)
+        assert rc == 0, d.ctor_last_message().decode()
+    # a missing key gas is refused with the reference's message through either constructor
+    rc = d.ctor_tables_equal(C.byref(kc), 2, ctables.pack_strings(["h2o", "o3"], 32), 32, 1)
+    assert rc == 1 and "missing" in d.ctor_last_message().decode()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+def test_array_gpu_has_the_reference_semantics(tag):
+    """include/Array.h:355-650 on the device: Array <-> Array_gpu conversions, views, deep copies, moves, the subset kernel
+    against the host subset (with a broadcast dimension and a 1-byte type), fill, insert, operator(), Gas_concs_gpu subset."""
+    d = _ctor(tag)
+    assert d.ctor_array_gpu_selftest() == 0, d.ctor_last_message().decode()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+def test_positional_constructors_solve_identically(tag):
+    """All-sky LW + SW (clouds, aerosols) with every optics object built through the reference's positional constructors
+    (Gas_optics_rrtmgp_gpu, Cloud_optics_gpu, Aerosol_optics_gpu) against the struct-constructed solvers: fluxes bit-identical,
+    and within tolerance of the oracle."""
+    from rte_rrtmgp_cpp_b200.atmos import add_aerosols
+    from rte_rrtmgp_cpp_b200.kdist import synthetic_aerosol_lut
+    d = _ctor(tag)
+    kd_lw, kd_sw = synthetic_kdist("lw"), synthetic_kdist("sw")
+    lut_lw, lut_sw, alut = synthetic_cloud_lut("lw"), synthetic_cloud_lut("sw"), synthetic_aerosol_lut()
+    atm = add_aerosols(allsky_atmosphere(24, 72))
+    klw, k1 = ctables.pack_kdist(kd_lw); ksw, k2 = ctables.pack_kdist(kd_sw)
+    clw, k3 = ctables.pack_cloud(lut_lw); csw, k4 = ctables.pack_cloud(lut_sw); aer, k5 = ctables.pack_aerosol(alut)
+    ng, names, ptrs, nc, nl, arrs = _concs(atm)
+    ncol, nlay = atm.ncol, atm.nlay
+    ins = [_F(x) for x in (atm.play, atm.plev, atm.tlay, atm.tlev, atm.tsfc, atm.emis_sfc, atm.sfc_alb_dir, atm.sfc_alb_dif, atm.mu0,
+                           atm.lwp, atm.iwp, atm.rel, atm.dei, atm.rh)]
+    am = [_F(np.broadcast_to(atm.aermr[f"aermr{i:02d}"], (ncol, nlay))) for i in range(1, 12)]
+    amp = (dp * 11)(*[_p(x) for x in am])
+    res = {}
+    for positional in (0, 1):
+        o = [_out(ncol, nlay + 1) for _ in range(5)]
+        rc = d.ctor_solve(C.byref(klw), C.byref(ksw), C.byref(clw), C.byref(csw), C.byref(aer), positional, ncol, nlay, ng, names, ptrs, nc, nl,
+                          *[_p(x) for x in ins], amp, *[_p(x) for x in o])
+        assert rc == 0, d.ctor_last_message().decode()
+        res[positional] = o
+    for a, b in zip(res[0], res[1]):
+        assert a.any() and np.array_equal(a, b)
+    ref_lw = oracle_lw(kd_lw, atm, lut_lw)
+    ref_sw = oracle_sw(kd_sw, atm, lut_sw, delta=True, aerosol_lut=alut, delta_aerosol=False)
+    for got, want in zip(res[1], (ref_lw["flux_up"], ref_lw["flux_dn"], ref_sw["flux_up"], ref_sw["flux_dn"], ref_sw["flux_dn_dir"])):
+        assert np.max(np.abs(got - want)) <= TOL[tag]
