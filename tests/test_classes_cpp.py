@@ -162,6 +162,19 @@ def _ctor(tag):
     return d
 
 
+def _f32_tables(t):
+    """An RTE_USE_SP caller holds the file variables as float Arrays: the same coefficients rounded to fp32 (kept as fp64),
+    so the struct constructor and the positional constructor are handed identical values."""
+    import copy
+    t = copy.copy(t)
+    for k, v in vars(t).items():
+        if isinstance(v, np.ndarray) and v.dtype == np.float64:
+            setattr(t, k, v.astype(np.float32).astype(np.float64))
+        elif isinstance(v, float):
+            setattr(t, k, float(np.float32(v)))
+    return t
+
+
 @pytest.mark.parametrize("tag", ["f64", "f32"])
 def test_host_array_has_the_reference_semantics(tag):
     """include/Array.h:94-297: column-major, 1-based operator(), offsets, subset with broadcast, move leaves the source
@@ -177,16 +190,7 @@ def test_positional_constructor_builds_identical_tables(kind, tag):
     293-364), fed like load_and_init_gas_optics feeds them, against the struct constructor: every prepared table
     (hash over coefficients in device layout, index tables, grids, retained gases) bit-identical.  Host-only handles."""
     d = _ctor(tag)
-    kd = synthetic_kdist(kind)
-    if tag == "f32":
-        # an RTE_USE_SP caller holds the file variables as float Arrays: compare on float-representable coefficients
-        import copy
-        kd = copy.copy(kd)
-        for k, v in vars(kd).items():
-            if isinstance(v, np.ndarray) and v.dtype == np.float64:
-                setattr(kd, k, v.astype(np.float32).astype(np.float64))
-            elif isinstance(v, float):
-                setattr(kd, k, float(np.float32(v)))
+    kd = _f32_tables(synthetic_kdist(kind)) if tag == "f32" else synthetic_kdist(kind)
     kc, keep = ctables.pack_kdist(kd)
     for gases in (["h2o", "co2", "o3", "n2o", "ch4", "n2", "o2"], ["h2o", "co2", "o3", "n2o", "ch4", "n2", "o2", "co", "cfc11", "no2"]):
         rc = d.ctor_tables_equal(C.byref(kc), len(gases), ctables.pack_strings(gases, 32), 32, 1)
@@ -216,6 +220,8 @@ def test_positional_constructors_solve_identically(tag):
     d = _ctor(tag)
     kd_lw, kd_sw = synthetic_kdist("lw"), synthetic_kdist("sw")
     lut_lw, lut_sw, alut = synthetic_cloud_lut("lw"), synthetic_cloud_lut("sw"), synthetic_aerosol_lut()
+    if tag == "f32":
+        kd_lw, kd_sw, lut_lw, lut_sw, alut = (_f32_tables(t) for t in (kd_lw, kd_sw, lut_lw, lut_sw, alut))
     atm = add_aerosols(allsky_atmosphere(24, 72))
     klw, k1 = ctables.pack_kdist(kd_lw); ksw, k2 = ctables.pack_kdist(kd_sw)
     clw, k3 = ctables.pack_cloud(lut_lw); csw, k4 = ctables.pack_cloud(lut_sw); aer, k5 = ctables.pack_aerosol(alut)
