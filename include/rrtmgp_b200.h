@@ -350,6 +350,25 @@ long long rrtmgp_b200_launch_count(void);
 int rrtmgp_b200_profile(int enable, double* lw_ms, long long* lw_launches, double* sw_ms,
                         long long* sw_launches);
 
+/* ---- Allocation-free variant.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that may not allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  The same computation and arguments as rrtmgp_b200_sw_solver_2stream with per-g-point
+ * outputs (ncol,nlay+1,ngpt) and mu0 (ncol); the solver's four recurrence arrays live in a static device array of
+ * RRTMGP_B200_NOALLOC_SCRATCH_BYTES inside the library (held by every GPU that loads it until the process exits)
+ * instead of a stream-ordered allocation.  Calls no cudaMalloc / cudaFree and no allocating library routine.
+ * Limit: ncol*nlay*ngpt <= RRTMGP_B200_NOALLOC_SCRATCH_BYTES / (4 * sizeof(Real)) = 2 097 152 cells (fp32) /
+ * 1 048 576 (fp64); larger calls return E_ARG with the limit in the message.  Every call on a device shares the
+ * array: calls that overlap on the GPU (different streams or threads) race — serialise them.  The array keeps the
+ * previous call's contents; the kernel writes each scratch cell before reading it, so nothing needs clearing.  The
+ * first call on a device resolves the array's device address (cudaGetSymbolAddress, not capturable): make one call
+ * per device outside graph capture first. */
+#define RRTMGP_B200_NOALLOC_SCRATCH_BYTES (32u * 1024u * 1024u)
+int rrtmgp_b200_sw_solver_2stream_noalloc(int dtype, int ncol, int nlay, int ngpt, int top_at_1,
+                                          const void* d_tau, const void* d_ssa, const void* d_g, const void* d_mu0,
+                                          const void* d_sfc_alb_dir_gpt, const void* d_sfc_alb_dif_gpt,
+                                          const void* d_inc_flux_dir, const void* d_inc_flux_dif /*may be NULL*/,
+                                          void* d_gpt_flux_up, void* d_gpt_flux_dn, void* d_gpt_flux_dir, void* stream);
+
 /* ---- Multi-GPU: columns are independent, so N processes (one per GPU) each run the calls
  * above on a contiguous shard of the x-fastest flattened domain (src_test/test_rte_rrtmgp.cpp:217);
  * the library holds no communicator and makes no collective call.  This is the partition rule

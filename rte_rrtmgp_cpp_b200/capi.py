@@ -80,6 +80,7 @@ SYMBOLS = {
     "rrtmgp_b200_lw_solver_rescaled": (i, [i, i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, vp, vp, vp]),
     "rrtmgp_b200_sw_solver_2stream": (i, [i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, vp]),
     "rrtmgp_b200_sw_solver_2stream_mu0lay": (i, [i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, vp]),
+    "rrtmgp_b200_sw_solver_2stream_noalloc": (i, [i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "rrtmgp_b200_sum_broadband": (i, [i, i, i, i, vp, vp, vp]),
     "rrtmgp_b200_sum_byband": (i, [i, i, i, i, i, ip, vp, vp, vp]),
     "rrtmgp_b200_net_flux": (i, [i, sz, vp, vp, vp, vp]),

@@ -1396,3 +1396,65 @@ int rrtmgp_b200_sw_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* 
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free shortwave solver (no counterpart in the reference).
+// For callers that may not allocate: code under CUDA graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc.  Same kernel as rrtmgp_b200_sw_solver_2stream (sw_solver_kernel, stages.cu); its four recurrence
+// arrays (ncol, nlay, ngpt) live in this file-scope device array instead of a cudaMallocAsync block.
+//   * 32 MiB per GPU that loads the library, held until the process exits;
+//   * every call on a device shares it: calls that overlap on the GPU (two streams, two host threads) RACE;
+//   * it keeps the previous call's contents.  Nothing has to start at zero: each thread writes every scratch cell
+//     of its (column, g-point) before it reads it back, so no clearing is needed;
+//   * in host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the address the kernel gets
+//     comes from cudaGetSymbolAddress, looked up once per device with that device current, below.
+// ---------------------------------------------------------------------------------------------
+namespace {
+constexpr size_t kNoAllocScratchBytes = RRTMGP_B200_NOALLOC_SCRATCH_BYTES;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+constexpr int kNoAllocMaxDevices = 64;
+std::atomic<void*> g_noalloc_addr[kNoAllocMaxDevices];      // zero-initialised: not looked up yet
+
+// device address of the scratch array on the CURRENT device (first call per device: one cudaGetSymbolAddress)
+void* noalloc_scratch_address()
+{
+    int dev = -1;
+    CK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kNoAllocMaxDevices) throw ArgError("sw_solver_2stream_noalloc: device ordinal beyond 63");
+    void* p = g_noalloc_addr[dev].load(std::memory_order_acquire);
+    if (!p)
+    {
+        CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p) throw CudaError("cudaGetSymbolAddress returned a null address for the static scratch array");
+        g_noalloc_addr[dev].store(p, std::memory_order_release);      // racing first calls store the same address
+    }
+    return p;
+}
+}  // namespace
+
+extern "C" int rrtmgp_b200_sw_solver_2stream_noalloc(int dtype, int ncol, int nlay, int ngpt, int top_at_1, const void* tau,
+                                                     const void* ssa, const void* g, const void* mu0, const void* alb_dir,
+                                                     const void* alb_dif, const void* inc_dir, const void* inc_dif,
+                                                     void* gpt_flux_up, void* gpt_flux_dn, void* gpt_flux_dir, void* stream)
+{
+    return guarded([&] {
+        check_dims(ncol, nlay);
+        if (dtype != RRTMGP_B200_F32 && dtype != RRTMGP_B200_F64) throw ArgError("bad dtype");
+        if (ngpt < 1 || !tau || !ssa || !g || !mu0 || !alb_dir || !alb_dif || !inc_dir || !gpt_flux_up || !gpt_flux_dn || !gpt_flux_dir)
+            throw ArgError("sw_solver_2stream_noalloc: null array");
+        const size_t esz = dtype == RRTMGP_B200_F32 ? 4 : 8;
+        const size_t cells = (size_t)ncol * (size_t)nlay * (size_t)ngpt;
+        const size_t max_cells = kNoAllocScratchBytes / (4 * esz);
+        if (cells > max_cells)
+            throw ArgError("sw_solver_2stream_noalloc: ncol*nlay*ngpt = " + std::to_string(cells) + " exceeds the static scratch ("
+                           + std::to_string(max_cells) + " cells for this dtype, " + std::to_string(kNoAllocScratchBytes)
+                           + " bytes); split the columns or use rrtmgp_b200_sw_solver_2stream");
+        void* work4 = noalloc_scratch_address();
+        DISPATCH(dtype,
+            launch_sw_solver<float>(ncol, nlay, ngpt, top_at_1, 0, tau, ssa, g, mu0, alb_dir, alb_dif, inc_dir, inc_dif,
+                                    gpt_flux_up, gpt_flux_dn, gpt_flux_dir, work4, (cudaStream_t)stream),
+            launch_sw_solver<double>(ncol, nlay, ngpt, top_at_1, 0, tau, ssa, g, mu0, alb_dir, alb_dif, inc_dir, inc_dif,
+                                     gpt_flux_up, gpt_flux_dn, gpt_flux_dir, work4, (cudaStream_t)stream));
+    });
+}
