@@ -110,6 +110,92 @@ template<> struct M<double>
     static __device__ __forceinline__ double from_int(int a) { return __longlong_as_double((long long)a); }
 };
 
+// ---- Pr<Real>: two adjacent g-points of a thread's quad --------------------------------------------------------------
+// fp32: one 64-bit register pair driven by sm_100's packed fp32 instructions (FFMA2 / FMUL2 / FADD2: two lanes per issue
+// slot, scalar operands broadcast for free as `R.F32`); the band kernels are issue-bound on the FMA pipe, so every
+// multiply-add written on a pair costs half an instruction per g-point.  fp64: two scalars, same interface, so the
+// kernels are written once.  SFU functions (ex2, rcp, sqrt) and min/max/select stay per lane.
+template<typename Real> struct Pr;
+template<> struct Pr<float>
+{
+    float2 v;
+    __device__ __forceinline__ Pr() {}
+    __device__ __forceinline__ Pr(float a, float b) : v(make_float2(a, b)) {}
+    __device__ __forceinline__ explicit Pr(float s) : v(make_float2(s, s)) {}
+    __device__ __forceinline__ explicit Pr(float2 f) : v(f) {}
+    __device__ __forceinline__ float lo() const { return v.x; }
+    __device__ __forceinline__ float hi() const { return v.y; }
+};
+template<> struct Pr<double>
+{
+    double x, y;
+    __device__ __forceinline__ Pr() {}
+    __device__ __forceinline__ Pr(double a, double b) : x(a), y(b) {}
+    __device__ __forceinline__ explicit Pr(double s) : x(s), y(s) {}
+    __device__ __forceinline__ double lo() const { return x; }
+    __device__ __forceinline__ double hi() const { return y; }
+};
+using PrF = Pr<float>;
+using PrD = Pr<double>;
+__device__ __forceinline__ PrF operator-(PrF a) { return PrF(-a.v.x, -a.v.y); }                 // folded into operand modifiers
+__device__ __forceinline__ PrF operator+(PrF a, PrF b) { return PrF(__fadd2_rn(a.v, b.v)); }
+__device__ __forceinline__ PrF operator-(PrF a, PrF b) { return PrF(__fadd2_rn(a.v, (-b).v)); }
+__device__ __forceinline__ PrF operator*(PrF a, PrF b) { return PrF(__fmul2_rn(a.v, b.v)); }
+__device__ __forceinline__ PrF operator+(PrF a, float s) { return a + PrF(s); }
+__device__ __forceinline__ PrF operator+(float s, PrF a) { return a + PrF(s); }
+__device__ __forceinline__ PrF operator-(PrF a, float s) { return a + PrF(-s); }
+__device__ __forceinline__ PrF operator-(float s, PrF a) { return PrF(s) - a; }
+__device__ __forceinline__ PrF operator*(PrF a, float s) { return a * PrF(s); }
+__device__ __forceinline__ PrF operator*(float s, PrF a) { return a * PrF(s); }
+__device__ __forceinline__ PrF pfma(PrF a, PrF b, PrF c) { return PrF(__ffma2_rn(a.v, b.v, c.v)); }   // a*b + c
+__device__ __forceinline__ PrF pfma(float a, PrF b, PrF c) { return pfma(PrF(a), b, c); }
+__device__ __forceinline__ PrF pfma(PrF a, float b, PrF c) { return pfma(a, PrF(b), c); }
+__device__ __forceinline__ PrF pfma(PrF a, PrF b, float c) { return pfma(a, b, PrF(c)); }
+__device__ __forceinline__ PrF pfma(float a, PrF b, float c) { return pfma(PrF(a), b, PrF(c)); }
+__device__ __forceinline__ PrF pfma(PrF a, float b, float c) { return pfma(a, PrF(b), PrF(c)); }
+__device__ __forceinline__ PrD operator-(PrD a) { return PrD(-a.x, -a.y); }
+__device__ __forceinline__ PrD operator+(PrD a, PrD b) { return PrD(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ PrD operator-(PrD a, PrD b) { return PrD(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ PrD operator*(PrD a, PrD b) { return PrD(a.x * b.x, a.y * b.y); }
+__device__ __forceinline__ PrD operator+(PrD a, double s) { return PrD(a.x + s, a.y + s); }
+__device__ __forceinline__ PrD operator+(double s, PrD a) { return PrD(a.x + s, a.y + s); }
+__device__ __forceinline__ PrD operator-(PrD a, double s) { return PrD(a.x - s, a.y - s); }
+__device__ __forceinline__ PrD operator-(double s, PrD a) { return PrD(s - a.x, s - a.y); }
+__device__ __forceinline__ PrD operator*(PrD a, double s) { return PrD(a.x * s, a.y * s); }
+__device__ __forceinline__ PrD operator*(double s, PrD a) { return PrD(a.x * s, a.y * s); }
+__device__ __forceinline__ PrD pfma(PrD a, PrD b, PrD c) { return PrD(fma(a.x, b.x, c.x), fma(a.y, b.y, c.y)); }
+__device__ __forceinline__ PrD pfma(double a, PrD b, PrD c) { return PrD(fma(a, b.x, c.x), fma(a, b.y, c.y)); }
+__device__ __forceinline__ PrD pfma(PrD a, double b, PrD c) { return PrD(fma(a.x, b, c.x), fma(a.y, b, c.y)); }
+__device__ __forceinline__ PrD pfma(PrD a, PrD b, double c) { return PrD(fma(a.x, b.x, c), fma(a.y, b.y, c)); }
+__device__ __forceinline__ PrD pfma(double a, PrD b, double c) { return PrD(fma(a, b.x, c), fma(a, b.y, c)); }
+__device__ __forceinline__ PrD pfma(PrD a, double b, double c) { return PrD(fma(a.x, b, c), fma(a.y, b, c)); }
+// per-lane functions
+template<typename Real> __device__ __forceinline__ Pr<Real> prcp(Pr<Real> a) { return Pr<Real>(M<Real>::rcp(a.lo()), M<Real>::rcp(a.hi())); }
+template<typename Real> __device__ __forceinline__ Pr<Real> psqrt(Pr<Real> a) { return Pr<Real>(M<Real>::sqrt(a.lo()), M<Real>::sqrt(a.hi())); }
+template<typename Real> __device__ __forceinline__ Pr<Real> pmax(Pr<Real> a, Real s) { return Pr<Real>(M<Real>::max(a.lo(), s), M<Real>::max(a.hi(), s)); }
+template<typename Real> __device__ __forceinline__ Pr<Real> pmin(Pr<Real> a, Pr<Real> b) { return Pr<Real>(M<Real>::min(a.lo(), b.lo()), M<Real>::min(a.hi(), b.hi())); }
+template<typename Real> __device__ __forceinline__ Pr<Real> pmax(Pr<Real> a, Pr<Real> b) { return Pr<Real>(M<Real>::max(a.lo(), b.lo()), M<Real>::max(a.hi(), b.hi())); }
+// exp(x): fp32 = one packed multiply by log2(e) + two MUFU.EX2; fp64 = the library exp
+__device__ __forceinline__ PrF pexp(PrF x)
+{
+#ifdef RB_F32_PRECISE
+    return PrF(expf(x.lo()), expf(x.hi()));
+#else
+    const PrF t = x * 1.4426950408889634f;
+    float a, b;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(a) : "f"(t.lo()));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(b) : "f"(t.hi()));
+    return PrF(a, b);
+#endif
+}
+__device__ __forceinline__ PrD pexp(PrD x) { return PrD(::exp(x.x), ::exp(x.y)); }
+// halves of a 4-vector / of a thread's 4-element register array
+template<typename Real> __device__ __forceinline__ Pr<Real> plo(const V4<Real>& v) { return Pr<Real>(v.x, v.y); }
+template<typename Real> __device__ __forceinline__ Pr<Real> phi(const V4<Real>& v) { return Pr<Real>(v.z, v.w); }
+template<typename Real> __device__ __forceinline__ Pr<Real> pget(const Real (&a)[4], int h) { return Pr<Real>(a[2 * h], a[2 * h + 1]); }
+template<typename Real> __device__ __forceinline__ void pput(Real (&a)[4], int h, Pr<Real> p) { a[2 * h] = p.lo(); a[2 * h + 1] = p.hi(); }
+template<typename Real> __device__ __forceinline__ V4<Real> v4_of(Pr<Real> lo, Pr<Real> hi) { return V4<Real>{lo.lo(), lo.hi(), hi.lo(), hi.hi()}; }
+
 // ---- device view of the k-distribution (tables in Real, index grids in double) -------------
 template<typename Real> struct DevPlan
 {

@@ -98,13 +98,17 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandLaunch<Real> L
             Real s0[4], s1[4], p0[4], p1[4];
             interp_major_pair<G>(kmaj, P, ce, s0, s1, p0, p1);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) { tau[j] = ce.cm0 * s0[j] + ce.cm1 * s1[j]; pf[j] = p0[j] + p1[j]; }
+            for (int h = 0; h < 2; ++h)
+            {
+                pput(tau, h, pfma(ce.cm1, pget(s1, h), ce.cm0 * pget(s0, h)));
+                pput(pf, h, pget(p0, h) + pget(p1, h));
+            }
             add_minor_tau<G>(L, ce, q4, cur.sc0, cur.sc1, st.scal + icl, tau);
             if (CLOUD)          // before the prefetch below: a load consumed after it would wait for the prefetch too
             {
                 const Real ct = a.cld_tau[icl + tcl * band];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) tau[j] += ct;
+                for (int h = 0; h < 2; ++h) pput(tau, h, pget(tau, h) + ct);
             }
             plev_p += tstep;
             plev_c = *plev_p;
@@ -126,25 +130,24 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandLaunch<Real> L
         if (k == 0)
         {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) lev_top[j] = pf[j] * blev;
+            for (int h = 0; h < 2; ++h) pput(lev_top, h, pget(pf, h) * blev);
             if (lead && a.bnd_dn && !a.bnd_add) a.bnd_dn[o_top + nlev_stride * band] = 0;      // no incident diffuse flux
         }
         else
         {
-            V4<Real> tr, su;
-            Real* trp = &tr.x; Real* sup = &su.x;
+            Pr<Real> t2[2], su2[2];
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
+            for (int h = 0; h < 2; ++h)
             {
-                const Real lev_bot = (k < nlay) ? M<Real>::sqrt(pf_prev[j] * pf[j]) * blev : pf_prev[j] * blev;
-                Real t, s_up, s_dn;
-                lw_layer(tau_prev[j] * a.secant, pf_prev[j] * blay_prev, lev_top[j], lev_bot, t, s_up, s_dn);
-                radn[j] = fma(t, radn[j], s_dn);
-                trp[j] = t; sup[j] = s_up;
-                lev_top[j] = lev_bot;
+                const Pr<Real> pfp = pget(pf_prev, h);
+                const Pr<Real> lev_bot = ((k < nlay) ? psqrt(pfp * pget(pf, h)) : pfp) * blev;
+                Pr<Real> s_dn;
+                lw_layer2(pget(tau_prev, h) * a.secant, pfp * blay_prev, pget(lev_top, h), lev_bot, t2[h], su2[h], s_dn);
+                pput(radn, h, pfma(t2[h], pget(radn, h), s_dn));
+                pput(lev_top, h, lev_bot);
             }
             V4<Real>* w = scr + (size_t)(k - 1) * 2 * T;
-            st_stream(w, tr); st_stream(w + T, su);
+            st_stream(w, v4_of(t2[0], t2[1])); st_stream(w + T, v4_of(su2[0], su2[1]));
             const Real s = quad_sum<Real, LPC>(radn) * piw;
             if (lead)
             {
@@ -165,8 +168,9 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandLaunch<Real> L
     {
         const Real bsfc = planck_band(plk, P.nplanck, P.planck_tmin, P.planck_delta, a.tsfc[cg]);
         const Real emis = a.sfc_emis[band + (size_t)P.nbnd * cg];
+        const Real refl = (Real)1 - emis, eb = emis * bsfc;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) radn[j] = radn[j] * ((Real)1 - emis) + emis * (pf_prev[j] * bsfc);
+        for (int h = 0; h < 2; ++h) pput(radn, h, pfma(eb, pget(pf_prev, h), pget(radn, h) * refl));
         const Real s = quad_sum<Real, LPC>(radn) * piw;
         if (lead)
         {
@@ -192,8 +196,8 @@ lw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandLaunch<Real> L
         for (int u = 0; u < 4; ++u)
         {
             if (k0 - u < 0) break;
-            radn[0] = fma(tr[u].x, radn[0], su[u].x); radn[1] = fma(tr[u].y, radn[1], su[u].y);
-            radn[2] = fma(tr[u].z, radn[2], su[u].z); radn[3] = fma(tr[u].w, radn[3], su[u].w);
+            pput(radn, 0, pfma(plo(tr[u]), pget(radn, 0), plo(su[u])));
+            pput(radn, 1, pfma(phi(tr[u]), pget(radn, 1), phi(su[u])));
             const Real s = quad_sum<Real, LPC>(radn) * piw;
             o -= lstep;
             if (lead)

@@ -115,7 +115,7 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandLaunch<Real> L
             Real s0[4], s1[4];
             interp_major<G>(kmaj, P, ce, s0, s1);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) tau[j] = ce.cm0 * s0[j] + ce.cm1 * s1[j];
+            for (int h = 0; h < 2; ++h) pput(tau, h, pfma(ce.cm1, pget(s1, h), ce.cm0 * pget(s0, h)));
             add_minor_tau<G>(L, ce, q4, cur.sc0, cur.sc1, st.scal + icl, tau);
         }
         Real ray[4] = {0, 0, 0, 0};
@@ -123,19 +123,19 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandLaunch<Real> L
         {
             interp_minor<G>(L.kray[ce.side] + q4, ce, ray);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) ray[j] *= ce.wet;
+            for (int h = 0; h < 2; ++h) pput(ray, h, pget(ray, h) * ce.wet);
         }
         // optical properties of the 4 g-points: gas + Rayleigh (+ by-band cloud/aerosol increment)
-        Real tt[4], ww[4], gg[4];
+        Pr<Real> tt[2], ww[2], gg[2];
         {
             Real ct = 0, cs = 0, cgg = 0;
             if (CLOUD) { ct = a.cld_tau[icl + tcl * band]; cs = a.cld_ssa[icl + tcl * band]; cgg = a.cld_g[icl + tcl * band]; }
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
+            for (int h = 0; h < 2; ++h)
             {
-                gg[j] = 0;
-                combine_rayleigh(tau[j], ray[j], tt[j], ww[j]);
-                if (CLOUD) increment_2str(tt[j], ww[j], gg[j], ct, cs, cgg);
+                gg[h] = Pr<Real>((Real)0);
+                combine_rayleigh2(pget(tau, h), pget(ray, h), tt[h], ww[h]);
+                if (CLOUD) increment_2str2(tt[h], ww[h], gg[h], ct, cs, cgg);
             }
         }
         // The next layer's state is requested HERE: after the last load of this iteration has been consumed (every wait on
@@ -147,25 +147,26 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandLaunch<Real> L
             const int lp = top ? k + 1 + RB_SW_PFS : nlay - 2 - k - RB_SW_PFS;      // to L2, see fused_lw.cu
             pfs.layer(lp, layer_side(tm, lp));
         }
-        V4<Real> v0, v1, v2, v3, v4, v5;
-        Real* p0 = &v0.x; Real* p1 = &v1.x; Real* p2 = &v2.x; Real* p3 = &v3.x; Real* p4 = &v4.x; Real* p5 = &v5.x;
+        // two g-points at a time: packed fp32 arithmetic (FFMA2 / FMUL2 / FADD2), exp / rcp / sqrt per lane
+        Pr<Real> Rdif[2], Tdif[2], su[2], sd[2], Ra0[2], Sa0[2];
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
+        for (int h = 0; h < 2; ++h)
         {
-            const Real t = tt[j], w0 = ww[j], g = gg[j];
-            Real Rdif, Tdif, Rdir, Tdir, Tnoscat;
-            two_stream(t, w0, g, mu0s, Rdif, Tdif, Rdir, Tdir, Tnoscat);
-            const Real su = sun ? Rdir * dir[j] : (Real)0;     // source_up
-            const Real sd = sun ? Tdir * dir[j] : (Real)0;     // source_dn
-            dir[j] = Tnoscat * dir[j];
-            p0[j] = Rdif; p1[j] = Tdif; p2[j] = su; p3[j] = sd; p4[j] = Ra[j]; p5[j] = Sa[j];
+            Pr<Real> Rdir, Tdir, Tnoscat;
+            two_stream2<Real>(tt[h], ww[h], gg[h], mu0s, Rdif[h], Tdif[h], Rdir, Tdir, Tnoscat);
+            const Pr<Real> dirh = pget(dir, h), Rah = pget(Ra, h), Sah = pget(Sa, h);
+            su[h] = sun ? Rdir * dirh : Pr<Real>((Real)0);     // source_up
+            sd[h] = sun ? Tdir * dirh : Pr<Real>((Real)0);     // source_dn
+            pput(dir, h, Tnoscat * dirh);
+            Ra0[h] = Rah; Sa0[h] = Sah;
             // add layer k below the stack: multiple reflections between Ra (above) and Rdif (the layer)
-            const Real td = Tdif * M<Real>::rcp((Real)1 - Ra[j] * Rdif);
-            Sa[j] = sd + td * (Sa[j] + Ra[j] * su);
-            Ra[j] = Rdif + Tdif * td * Ra[j];
+            const Pr<Real> td = Tdif[h] * prcp(pfma(-Rah, Rdif[h], (Real)1));
+            pput(Sa, h, pfma(td, pfma(Rah, su[h], Sah), sd[h]));
+            pput(Ra, h, pfma(Tdif[h] * td, Rah, Rdif[h]));
         }
         V4<Real>* w = scr + (size_t)k * 6 * T;
-        st_stream(w, v0); st_stream(w + T, v1); st_stream(w + 2 * T, v2); st_stream(w + 3 * T, v3); st_stream(w + 4 * T, v4); st_stream(w + 5 * T, v5);
+        st_stream(w, v4_of(Rdif[0], Rdif[1])); st_stream(w + T, v4_of(Tdif[0], Tdif[1])); st_stream(w + 2 * T, v4_of(su[0], su[1]));
+        st_stream(w + 3 * T, v4_of(sd[0], sd[1])); st_stream(w + 4 * T, v4_of(Ra0[0], Ra0[1])); st_stream(w + 5 * T, v4_of(Sa0[0], Sa0[1]));
         const Real s = quad_sum<Real, LPC>(dir);
         o += lstep;
         if (lead)
@@ -195,11 +196,12 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandLaunch<Real> L
         const Real adif = a.alb_dif[band + (size_t)P.nbnd * cg];
         Real fdn[4], fup[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
+        for (int h = 0; h < 2; ++h)
         {
-            alb[j] = adif; src[j] = sun ? dir[j] * adir : (Real)0;
-            fdn[j] = (Sa[j] + Ra[j] * src[j]) * M<Real>::rcp((Real)1 - Ra[j] * alb[j]);
-            fup[j] = alb[j] * fdn[j] + src[j];
+            const Pr<Real> albh(adif), srch = sun ? pget(dir, h) * adir : Pr<Real>((Real)0), Rah = pget(Ra, h);
+            const Pr<Real> fd = pfma(Rah, srch, pget(Sa, h)) * prcp(pfma(-Rah, albh, (Real)1));
+            pput(alb, h, albh); pput(src, h, srch);
+            pput(fdn, h, fd); pput(fup, h, pfma(albh, fd, srch));
         }
         const Real su = quad_sum<Real, LPC>(fup), sd = quad_sum<Real, LPC>(fdn);
         if (lead)
@@ -213,18 +215,19 @@ sw_band_kernel(const DevPlan<Real> P, const __grid_constant__ BandLaunch<Real> L
     {
         if (RB_SW_PF2 > 0 && kpf >= 0) prefetch_strip_layer<Real, 6>(scr - tid, kpf);
         --kpf;
-        const Real* rdif = &in[0].x; const Real* tdif = &in[1].x; const Real* sup = &in[2].x; const Real* sdn = &in[3].x;
-        const Real* ra = &in[4].x; const Real* sa = &in[5].x;
         Real fdn[4], fup[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
+        for (int h = 0; h < 2; ++h)
         {
-            const Real td = tdif[j] * M<Real>::rcp((Real)1 - rdif[j] * alb[j]);
-            const Real nsrc = sup[j] + td * (src[j] + alb[j] * sdn[j]);
-            alb[j] = rdif[j] + tdif[j] * td * alb[j];
-            src[j] = nsrc;
-            fdn[j] = (sa[j] + ra[j] * src[j]) * M<Real>::rcp((Real)1 - ra[j] * alb[j]);
-            fup[j] = alb[j] * fdn[j] + src[j];
+            const Pr<Real> rdif = h ? phi(in[0]) : plo(in[0]), tdif = h ? phi(in[1]) : plo(in[1]), sup = h ? phi(in[2]) : plo(in[2]);
+            const Pr<Real> sdn = h ? phi(in[3]) : plo(in[3]), ra = h ? phi(in[4]) : plo(in[4]), sa = h ? phi(in[5]) : plo(in[5]);
+            const Pr<Real> albh = pget(alb, h), srch = pget(src, h);
+            const Pr<Real> td = tdif * prcp(pfma(-rdif, albh, (Real)1));
+            const Pr<Real> nsrc = pfma(td, pfma(albh, sdn, srch), sup);
+            const Pr<Real> nalb = pfma(tdif * td, albh, rdif);
+            const Pr<Real> fd = pfma(ra, nsrc, sa) * prcp(pfma(-ra, nalb, (Real)1));
+            pput(alb, h, nalb); pput(src, h, nsrc);
+            pput(fdn, h, fd); pput(fup, h, pfma(nalb, fd, nsrc));
         }
         const Real su = quad_sum<Real, LPC>(fup), sd = quad_sum<Real, LPC>(fdn);
         o -= lstep;

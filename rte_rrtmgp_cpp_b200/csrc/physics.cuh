@@ -45,8 +45,10 @@ __device__ __forceinline__ void decode_cell(const V4<Real>& cell, const V4<Real>
     o.wet = cell.y + cell.z;
     o.cm0 = fa.x; o.cm1 = fa.y;
     o.fm[0] = fa.z; o.fm[1] = fa.w; o.fm[2] = fb.x; o.fm[3] = fb.y;
-    o.w[0] = omf * o.fm[0]; o.w[1] = omf * o.fm[1]; o.w[2] = fpress * o.fm[0]; o.w[3] = fpress * o.fm[1];
-    o.w[4] = omf * o.fm[2]; o.w[5] = omf * o.fm[3]; o.w[6] = fpress * o.fm[2]; o.w[7] = fpress * o.fm[3];
+    const Pr<Real> f01(o.fm[0], o.fm[1]), f23(o.fm[2], o.fm[3]);
+    const Pr<Real> w01 = omf * f01, w23 = fpress * f01, w45 = omf * f23, w67 = fpress * f23;
+    o.w[0] = w01.lo(); o.w[1] = w01.hi(); o.w[2] = w23.lo(); o.w[3] = w23.hi();
+    o.w[4] = w45.lo(); o.w[5] = w45.hi(); o.w[6] = w67.lo(); o.w[7] = w67.hi();
 }
 
 // raw per-(column, layer) state of one band: what the prologue kernel left in HBM
@@ -156,8 +158,21 @@ __device__ __forceinline__ RawState<Real> load_state(const TileState<Real>& st, 
     return r;
 }
 
-#define RB_FMA4(acc, s, v) { acc[0] = fma(s, v.x, acc[0]); acc[1] = fma(s, v.y, acc[1]); acc[2] = fma(s, v.z, acc[2]); acc[3] = fma(s, v.w, acc[3]); }
-#define RB_MUL4(acc, s, v) { acc[0] = s * v.x; acc[1] = s * v.y; acc[2] = s * v.z; acc[3] = s * v.w; }
+// acc (+)= s * v on a thread's quad: two packed instructions in fp32 (the scalar weight is a broadcast operand)
+template<typename Real> __device__ __forceinline__ void q_fma(Real (&acc)[4], Real s, const V4<Real>& v)
+{
+    pput(acc, 0, pfma(s, plo(v), pget(acc, 0))); pput(acc, 1, pfma(s, phi(v), pget(acc, 1)));
+}
+template<typename Real> __device__ __forceinline__ void q_mul(Real (&acc)[4], Real s, const V4<Real>& v)
+{
+    pput(acc, 0, s * plo(v)); pput(acc, 1, s * phi(v));
+}
+template<typename Real> __device__ __forceinline__ void q_fma(Real (&acc)[4], Real s, const Real (&v)[4])
+{
+    pput(acc, 0, pfma(s, pget(v, 0), pget(acc, 0))); pput(acc, 1, pfma(s, pget(v, 1), pget(acc, 1)));
+}
+#define RB_FMA4(acc, s, v) q_fma(acc, s, v);
+#define RB_MUL4(acc, s, v) q_mul(acc, s, v);
 
 // interpolate3D_byflav (mo_gas_optics_rrtmgp_kernels.F90:760-789): partial sums per temperature.
 // `tab` points at the band block (+ slot and quad offset); with G::NE > 0 the 4 corners of a
@@ -231,8 +246,7 @@ __device__ __forceinline__ void add_minor_tau(const DevPlan<Real>& P, const Band
             {
                 Real s[4];
                 interp_minor<G>(km, c, s);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) tau[j] = fma(scp[u], s[j], tau[j]);
+                q_fma(tau, scp[u], s);
                 km += mstride;
             }
         }
@@ -259,8 +273,7 @@ __device__ __forceinline__ void add_minor_tau(const BandLaunch<Real>& L, const C
             {
                 Real s[4];
                 interp_minor<G>(km, c, s);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) tau[j] = fma(scp[u], s[j], tau[j]);
+                q_fma(tau, scp[u], s);
                 km += L.mstride;
             }
         }
@@ -277,7 +290,7 @@ __device__ __forceinline__ void gas_tau(const DevPlan<Real>& P, const BandArgs& 
     Real s0[4], s1[4];
     interp_major<G>(kmaj_quad, P, c, s0, s1);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) tau[j] = c.cm0 * s0[j] + c.cm1 * s1[j];
+    for (int h = 0; h < 2; ++h) pput(tau, h, pfma(c.cm1, pget(s1, h), c.cm0 * pget(s0, h)));
     add_minor_tau<G>(P, B, c, q4, pre0, pre1, scal_icl, tcl, tau);
 }
 
@@ -325,7 +338,8 @@ __device__ __forceinline__ void release_slot(int* busy, int slot)
 template<typename Real, int LPC>
 __device__ __forceinline__ Real quad_sum(const Real (&v)[4])
 {
-    Real s = (v[0] + v[1]) + (v[2] + v[3]);
+    const Pr<Real> h = pget(v, 0) + pget(v, 1);          // (v0 + v2, v1 + v3): one packed add
+    Real s = h.lo() + h.hi();
     if (LPC >= 2) s += __shfl_xor_sync(0xffffffffu, s, 1);
     if (LPC >= 4) s += __shfl_xor_sync(0xffffffffu, s, 2);
     return s;
@@ -345,6 +359,22 @@ __device__ __forceinline__ void lw_layer(Real tau_loc, Real lay_src, Real lev_ab
     const Real fact = tau_loc > tau_thresh ? f_big : f_small;
     src_dn = omt * lev_below + (Real)2 * fact * (lay_src - lev_below);
     src_up = omt * lev_above + (Real)2 * fact * (lay_src - lev_above);
+}
+
+// the same for a pair of g-points (packed arithmetic in fp32; exp / rcp / select per lane)
+template<typename Real>
+__device__ __forceinline__ void lw_layer2(Pr<Real> tau_loc, Pr<Real> lay_src, Pr<Real> lev_above, Pr<Real> lev_below,
+                                          Pr<Real>& trans, Pr<Real>& src_up, Pr<Real>& src_dn)
+{
+    const Real tau_thresh = sizeof(Real) == 4 ? (Real)1.857e-2 : (Real)1.220703125e-4;
+    trans = pexp(-tau_loc);
+    const Pr<Real> omt = (Real)1 - trans;
+    const Pr<Real> f_big = omt * prcp(pmax(tau_loc, tau_thresh)) - trans;
+    const Pr<Real> f_small = tau_loc * pfma(tau_loc, pfma(tau_loc, (Real)0.125, (Real)(-1.0 / 3.0)), (Real)0.5);
+    const Pr<Real> fact(tau_loc.lo() > tau_thresh ? f_big.lo() : f_small.lo(), tau_loc.hi() > tau_thresh ? f_big.hi() : f_small.hi());
+    const Pr<Real> fact2 = fact + fact;
+    src_dn = pfma(fact2, lay_src - lev_below, omt * lev_below);
+    src_up = pfma(fact2, lay_src - lev_above, omt * lev_above);
 }
 
 }  // namespace rb200
@@ -500,6 +530,104 @@ __device__ __forceinline__ void two_stream<float>(float tau, float w0, float g, 
                                                   float& Rdif, float& Tdif, float& Rdir, float& Tdir, float& Tnoscat)
 {
     two_stream_f32(tau, w0, g, mu0s, Rdif, Tdif, Rdir, Tdir, Tnoscat);
+}
+#endif
+
+// ---- the same per-cell functions for a pair of g-points ---------------------------------------------------------------
+template<typename Real>
+__device__ __forceinline__ void combine_rayleigh2(Pr<Real> tau_abs, Pr<Real> tau_ray, Pr<Real>& tau, Pr<Real>& ssa)
+{
+    tau = tau_abs + tau_ray;
+    const Real thr = sizeof(Real) == 4 ? (Real)2 * M<Real>::tiny : (Real)2 * M<Real>::eps;
+    const Pr<Real> q = sizeof(Real) == 4 ? tau_ray * prcp(tau) : Pr<Real>(M<Real>::div(tau_ray.lo(), tau.lo()), M<Real>::div(tau_ray.hi(), tau.hi()));
+    ssa = Pr<Real>(tau.lo() > thr ? q.lo() : (Real)0, tau.hi() > thr ? q.hi() : (Real)0);
+}
+
+template<typename Real>
+__device__ __forceinline__ void increment_2str2(Pr<Real>& tau, Pr<Real>& ssa, Pr<Real>& g, Real t2, Real s2, Real g2)
+{
+    const Real eps3 = (Real)3 * M<Real>::tiny;
+    const Real ts2 = t2 * s2;
+    const Pr<Real> tau12 = tau + t2;
+    const Pr<Real> ts1 = tau * ssa;
+    const Pr<Real> tauscat12 = ts1 + ts2;
+    const Pr<Real> num = pfma(ts1, g, ts2 * g2);
+    const Pr<Real> d1 = pmax(tauscat12, eps3), d2 = pmax(tau12, eps3);
+    g = Pr<Real>(M<Real>::div(num.lo(), d1.lo()), M<Real>::div(num.hi(), d1.hi()));
+    ssa = Pr<Real>(M<Real>::div(tauscat12.lo(), d2.lo()), M<Real>::div(tauscat12.hi(), d2.hi()));
+    tau = tau12;
+}
+
+// generic (fp64): the reference expressions per lane
+template<typename Real>
+__device__ __forceinline__ void two_stream2(Pr<Real> tau, Pr<Real> w0, Pr<Real> g, Real mu0s,
+                                            Pr<Real>& Rdif, Pr<Real>& Tdif, Pr<Real>& Rdir, Pr<Real>& Tdir, Pr<Real>& Tnoscat)
+{
+    Real a0, a1, a2, a3, a4, b0, b1, b2, b3, b4;
+    two_stream<Real>(tau.lo(), w0.lo(), g.lo(), mu0s, a0, a1, a2, a3, a4);
+    two_stream<Real>(tau.hi(), w0.hi(), g.hi(), mu0s, b0, b1, b2, b3, b4);
+    Rdif = Pr<Real>(a0, b0); Tdif = Pr<Real>(a1, b1); Rdir = Pr<Real>(a2, b2); Tdir = Pr<Real>(a3, b3); Tnoscat = Pr<Real>(a4, b4);
+}
+
+#ifndef RB_F32_REFERENCE_TWOSTREAM
+// (1 - exp(-x)) / x for a pair, e = exp(-x)
+__device__ __forceinline__ PrF omexp_over_x2(PrF x, PrF e)
+{
+    const PrF ser = pfma(x * -0.5f, pfma(x * -(1.f / 3.f), pfma(x, -0.25f, 1.f), 1.f), 1.f);
+    const PrF dir = (1.f - e) * prcp(pmax(x, 1e-30f));
+    return PrF(x.lo() < 0.03f ? ser.lo() : dir.lo(), x.hi() < 0.03f ? ser.hi() : dir.hi());
+}
+// one lane of the removable singularity |1 - k^2 mu^2| < band (two_stream_f32): rare, scalar
+__device__ __forceinline__ void two_stream_nudge(float k, float tau, float& d, float& mu, float& T0, float& omT)
+{
+    const float band = 1.e-3f;
+    d = d >= 0.f ? band : -band;
+    mu = M<float>::div(M<float>::sqrt(1.f - d), k);
+    const float xe = M<float>::div(tau, mu);
+    T0 = M<float>::exp(-xe);
+    omT = xe * omexp_over_x(xe, T0);
+}
+// fp32: two_stream_f32 on two g-points with packed arithmetic (same expressions, same order)
+template<>
+__device__ __forceinline__ void two_stream2<float>(PrF tau, PrF w0, PrF g, float mu0s,
+                                                   PrF& Rdif, PrF& Tdif, PrF& Rdir, PrF& Tdir, PrF& Tnoscat)
+{
+    const PrF g3 = g * 3.f;
+    const PrF gamma1 = pfma(w0 * -0.25f, g3 + 5.f, 2.f);                       // (8 - w0 (5 + 3g)) / 4
+    const PrF gamma2 = (w0 * 0.75f) * (1.f - g);
+    const PrF k2 = pmax((2.f * (1.f - w0)) * pfma(w0 * -0.5f, g3 + 1.f, 2.f), 0.f);
+    const PrF k = psqrt(k2);
+    const PrF a = k * tau;
+    const PrF e1 = pexp(-a), e2 = e1 * e1;
+    const PrF ga = omexp_over_x2(a, e1);
+    const PrF om1 = a * ga;
+    const PrF P = (tau * ga) * (1.f + e1);
+    const PrF rD = prcp(pfma(gamma1, P, 1.f + e2));
+    Rdif = (gamma2 * P) * rD;
+    Tdif = (e1 + e1) * rD;
+
+    const PrF x = tau * M<float>::rcp(mu0s);
+    Tnoscat = pexp(-x);
+    const PrF omT_true = x * omexp_over_x2(x, Tnoscat);
+    const PrF kmu = k * mu0s;
+    const PrF d0 = pfma(-kmu, kmu, 1.f);
+    float dl = d0.lo(), dh = d0.hi(), mul = mu0s, muh = mu0s, T0l = Tnoscat.lo(), T0h = Tnoscat.hi(), oml = omT_true.lo(), omh = omT_true.hi();
+    if (fabsf(dl) < 1.e-3f) two_stream_nudge(k.lo(), tau.lo(), dl, mul, T0l, oml);
+    if (fabsf(dh) < 1.e-3f) two_stream_nudge(k.hi(), tau.hi(), dh, muh, T0h, omh);
+    const PrF d(dl, dh), mu(mul, muh), T0(T0l, T0h), omT(oml, omh);
+    const PrF gamma3 = pfma(mu * -0.75f, g, 0.5f);                              // (2 - 3 mu g) / 4
+    const PrF gamma4 = 1.f - gamma3;
+    const PrF alpha1 = pfma(gamma1, gamma4, gamma2 * gamma3);
+    const PrF alpha2 = pfma(gamma1, gamma3, gamma2 * gamma4);
+    const PrF om1sq = om1 * om1, e1omT2 = (e1 + e1) * omT;
+    const PrF Q = om1sq + e1omT2;
+    const PrF Qp = pfma(T0, om1sq, -e1omT2);
+    const PrF k2muP = (k2 * mu) * P;
+    const PrF NR = pfma(pfma(-mu, alpha2, gamma3), Q, pfma(alpha2, P, -(k2muP * gamma3)));
+    const PrF NT = pfma(pfma(mu, alpha1, gamma4), Qp, T0 * pfma(alpha1, P, k2muP * gamma4));
+    const PrF f = (w0 * rD) * prcp(d);
+    Rdir = pmax(pmin(f * NR, omT_true), 0.f);
+    Tdir = pmax(pmin(-(f * NT), omT_true - Rdir), 0.f);
 }
 #endif
 
