@@ -46,6 +46,7 @@ def parse():
     ap.add_argument("--reduced", action="store_true", help="reduced g-point sets LW 128 / SW 112 (BASELINE config 5)")
     ap.add_argument("--tile", type=int, default=0, help="columns per tile of the fused path (0 = auto)")
     ap.add_argument("--chunk", type=int, default=0, help="columns per chunk of the host-buffer pipeline (0 = auto)")
+    ap.add_argument("--no-pair", action="store_true", help="longwave and shortwave as two calls instead of the paired call (rrtmgp_b200_lwsw_fluxes)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true", help="skip timing the reference's own CUDA path (oracle/_ref/librefcuda_*.so)")
@@ -251,8 +252,11 @@ def run_b200(args):
     gather_buf = None
 
     def step():
-        lw.solve_gpu(cols, switch_cloud_optics=args.cloudy, out=out_lw)
-        sw.solve_gpu(cols, switch_cloud_optics=args.cloudy, out=out_sw)
+        if args.no_pair:
+            lw.solve_gpu(cols, switch_cloud_optics=args.cloudy, out=out_lw)
+            sw.solve_gpu(cols, switch_cloud_optics=args.cloudy, out=out_sw)
+        else:       # one call: longwave and shortwave CTAs co-resident, band pair by band pair
+            api.solve_pair(lw, sw, cols, switch_cloud_optics=args.cloudy, out_lw=out_lw, out_sw=out_sw)
         if world > 1:
             # final flux gather to rank 0 over NCCL: (rank, field, level, column-in-shard)
             nonlocal gather_buf
@@ -284,6 +288,8 @@ def run_b200(args):
     launches = L.rrtmgp_b200_launch_count() - launches0
     lw_ms, sw_ms = C.c_double(), C.c_double(); lw_n, sw_n = C.c_longlong(), C.c_longlong()
     L.rrtmgp_b200_profile(0, C.byref(lw_ms), C.byref(lw_n), C.byref(sw_ms), C.byref(sw_n))
+    pair_ms, pair_n = C.c_double(), C.c_longlong()
+    L.rrtmgp_b200_profile_pair(C.byref(pair_ms), C.byref(pair_n))
     clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
     if world > 1:
         t = torch.tensor([ms], device="cuda", dtype=torch.float64)
@@ -349,10 +355,17 @@ def run_b200(args):
     # ---- roofline of the dominant kernel (SURVEY 8d byte model; launches = one band of one tile)
     L_, V_ = nlay, nlev
     b_lw, b_sw = (4 * L_ + 6 * V_) * esz, (6 * L_ + 6 * V_) * esz
-    dom = "sw_band_kernel" if sw_ms.value >= lw_ms.value else "lw_band_kernel"
-    k_ms, k_n, k_b, k_g = (sw_ms.value, sw_n.value, b_sw, sw.kdist.get_ngpt()) if dom == "sw_band_kernel" else \
-                          (lw_ms.value, lw_n.value, b_lw, lw.kdist.get_ngpt())
-    alg_bytes_total = ncol * k_g * k_b * args.steps           # this rank, all launches of that kernel
+    paired = pair_ms.value > 0
+    if paired:
+        # one launch = one longwave band + one shortwave band of a tile (plus the few unpaired single-role launches of the
+        # same loops): algorithmic bytes of both
+        dom, k_ms, k_n = "lwsw_band_kernel", pair_ms.value, pair_n.value
+        alg_bytes_total = ncol * (g_lw * b_lw + g_sw * b_sw) * args.steps
+    else:
+        dom = "sw_band_kernel" if sw_ms.value >= lw_ms.value else "lw_band_kernel"
+        k_ms, k_n, k_b, k_g = (sw_ms.value, sw_n.value, b_sw, sw.kdist.get_ngpt()) if dom == "sw_band_kernel" else \
+                              (lw_ms.value, lw_n.value, b_lw, lw.kdist.get_ngpt())
+        alg_bytes_total = ncol * k_g * k_b * args.steps           # this rank, all launches of that kernel
     achieved = alg_bytes_total / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
     peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     try:
@@ -387,7 +400,7 @@ def run_b200(args):
                                         "Radiation_solver::solve_gpu; its fluxes are NOT the parity target (SURVEY 2.1 quirks)")
         except Exception as ex:      # noqa: BLE001 - a baseline failure must not lose the measurement
             ref_cuda = {"unavailable": str(ex)[:200]}
-    whole = (ncol * (g_lw * b_lw + g_sw * b_sw) * args.steps) / ((lw_ms.value + sw_ms.value) * 1e-3) / 1e9
+    whole = (ncol * (g_lw * b_lw + g_sw * b_sw) * args.steps) / ((lw_ms.value + sw_ms.value + pair_ms.value) * 1e-3) / 1e9
     line = {
         "metric": "LW+SW column-gpts/s", "value": value, "unit": "column-gpts/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
@@ -405,7 +418,7 @@ def run_b200(args):
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_column_gpt": {"lw": b_lw, "sw": b_sw},
                      "avg_launch_ms": k_ms / max(k_n, 1), "launches_timed": int(k_n),
-                     "lw_band_ms_total": lw_ms.value, "sw_band_ms_total": sw_ms.value,
+                     "lw_band_ms_total": lw_ms.value, "sw_band_ms_total": sw_ms.value, "paired_band_ms_total": pair_ms.value,
                      "lw_plus_sw_effective_GBs": whole, "lw_plus_sw_frac": whole / peak,
                      "note": "effective bandwidth on the materialised-API byte model; the fused kernels move far fewer DRAM bytes"},
         "cpu_baseline": cpu, "e2e": e2e, "reference_cuda": ref_cuda,

@@ -350,6 +350,19 @@ long long rrtmgp_b200_launch_count(void);
 int rrtmgp_b200_profile(int enable, double* lw_ms, long long* lw_launches, double* sw_ms,
                         long long* sw_launches);
 
+/* Longwave AND shortwave fluxes of the same columns in one call: Radiation_solver_longwave::solve_gpu followed by
+ * Radiation_solver_shortwave::solve_gpu (src_test/Radiation_solver.cu:419-657, 690-950; the reference driver calls them back to
+ * back, src_test/test_rte_rrtmgp.cu:560-900) with the two advanced together tile by tile: band i of both k-distributions
+ * runs in ONE launch whose CTAs alternate between the longwave and the shortwave role, so the L1-bound longwave work and the
+ * DRAM-bound shortwave work share every SM.  Arguments as rrtmgp_b200_lw_fluxes / rrtmgp_b200_sw_fluxes; ncol and nlay must
+ * agree; results are bit-identical to the two separate calls.  Bands the paired kernel does not cover (narrow bands of reduced
+ * g-point sets, extra Gauss angles) and handles set to the column-resident path fall back to the single-role launches. */
+int rrtmgp_b200_lwsw_fluxes(rrtmgp_b200_gas_optics* go_lw, const rrtmgp_b200_columns* cols_lw, const rrtmgp_b200_fluxes* out_lw,
+                            rrtmgp_b200_gas_optics* go_sw, const rrtmgp_b200_columns* cols_sw, const rrtmgp_b200_fluxes* out_sw,
+                            void* stream);
+/* time and launches of the paired band loops collected by the last rrtmgp_b200_profile call */
+int rrtmgp_b200_profile_pair(double* pair_ms, long long* pair_launches);
+
 /* ---- Allocation-free variant.  NO COUNTERPART IN THE REFERENCE: added for
  * callers that may not allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that
  * forbid cudaMalloc).  The same computation and arguments as rrtmgp_b200_sw_solver_2stream with per-g-point

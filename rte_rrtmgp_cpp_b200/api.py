@@ -672,6 +672,22 @@ class HostColumns(DeviceColumns):
                     v.t = v.t.pin_memory()
 
 
+def solve_pair(lw: Radiation_solver_longwave, sw: Radiation_solver_shortwave, cols: DeviceColumns,
+               switch_cloud_optics: bool = False, switch_delta_cloud: bool = True, switch_output_bnd_fluxes: bool = False,
+               heating: bool = False, out_lw: Optional[dict] = None, out_sw: Optional[dict] = None,
+               switch_aerosol_optics: bool = False, switch_delta_aerosol: bool = False):
+    """Longwave and shortwave solve_gpu of the same device-resident columns in one call (rrtmgp_b200_lwsw_fluxes): band i of
+    both k-distributions in one launch with longwave and shortwave CTAs co-resident on every SM.  Bit-identical to
+    lw.solve_gpu(...) + sw.solve_gpu(...).  Returns (out_lw, out_sw)."""
+    out_lw = {} if out_lw is None else out_lw
+    out_sw = {} if out_sw is None else out_sw
+    cl, fl = lw._pack(cols, out_lw, switch_cloud_optics, switch_delta_cloud, switch_output_bnd_fluxes, heating, "cuda")
+    cs, fs = sw._pack(cols, out_sw, switch_cloud_optics, switch_delta_cloud, switch_output_bnd_fluxes, heating, "cuda",
+                      switch_aerosol_optics, switch_delta_aerosol)
+    check(lib().rrtmgp_b200_lwsw_fluxes(lw.kdist.h, C.byref(cl), C.byref(fl), sw.kdist.h, C.byref(cs), C.byref(fs), _stream()))
+    return out_lw, out_sw
+
+
 def solve_host(lw: Optional[Radiation_solver_longwave], sw: Optional[Radiation_solver_shortwave], cols: HostColumns,
                switch_cloud_optics: bool = False, switch_delta_cloud: bool = True, switch_output_bnd_fluxes: bool = False,
                heating: bool = False, out_lw: Optional[dict] = None, out_sw: Optional[dict] = None, chunk_columns: int = 0,

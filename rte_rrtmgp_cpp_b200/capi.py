@@ -90,6 +90,8 @@ SYMBOLS = {
     "rrtmgp_b200_array_subset": (i, [i, i, ip, ip, ip, ip, vp, vp, vp]),
     "rrtmgp_b200_lw_fluxes": (i, [vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp]),
     "rrtmgp_b200_sw_fluxes": (i, [vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp]),
+    "rrtmgp_b200_lwsw_fluxes": (i, [vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp]),
+    "rrtmgp_b200_profile_pair": (i, [C.POINTER(d), C.POINTER(C.c_longlong)]),
     "rrtmgp_b200_fluxes_host": (i, [vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), i, vp]),
     "rrtmgp_b200_set_tile_columns": (i, [vp, i]),
     "rrtmgp_b200_set_fused_path": (i, [vp, i]),

@@ -19,7 +19,7 @@ static std::atomic<long long> g_launches{0};
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 // optional device-side timing of the fused band kernels (bench.py's roofline leg)
-struct Profile { bool on = false; std::vector<cudaEvent_t> ev[2]; double ms[2] = {0, 0}; long long launches[2] = {0, 0}; };
+struct Profile { bool on = false; std::vector<cudaEvent_t> ev[3]; double ms[3] = {0, 0, 0}; long long launches[3] = {0, 0, 0}; };   // 0 LW, 1 SW, 2 paired LW+SW
 static Profile g_prof;
 // host-buffer entry: run the LW and the SW band kernels of a chunk on two streams (RB200_HOST_CONCURRENT=0 disables)
 // RB200_PATH=colres selects the column-resident kernels (recurrences in shared memory) instead of the
@@ -365,11 +365,12 @@ int rrtmgp_b200_gas_optics_table_hash(const rrtmgp_b200_gas_optics* g, unsigned 
     return 0;
 }
 
+static double g_pair_ms = 0; static long long g_pair_launches = 0;
 int rrtmgp_b200_profile(int enable, double* lw_ms, long long* lw_launches, double* sw_ms, long long* sw_launches)
 {
     // collect: synchronises the device, folds the recorded event pairs into milliseconds
     cudaDeviceSynchronize();
-    for (int k = 0; k < 2; ++k)
+    for (int k = 0; k < 3; ++k)
     {
         for (size_t i = 0; i + 1 < g_prof.ev[k].size(); i += 2)
         {
@@ -382,8 +383,15 @@ int rrtmgp_b200_profile(int enable, double* lw_ms, long long* lw_launches, doubl
     if (lw_launches) *lw_launches = g_prof.launches[0];
     if (sw_ms) *sw_ms = g_prof.ms[1];
     if (sw_launches) *sw_launches = g_prof.launches[1];
-    g_prof.ms[0] = g_prof.ms[1] = 0; g_prof.launches[0] = g_prof.launches[1] = 0;
+    g_pair_ms = g_prof.ms[2]; g_pair_launches = g_prof.launches[2];
+    for (int k = 0; k < 3; ++k) { g_prof.ms[k] = 0; g_prof.launches[k] = 0; }
     g_prof.on = enable != 0;
+    return 0;
+}
+int rrtmgp_b200_profile_pair(double* pair_ms, long long* pair_launches)
+{
+    if (pair_ms) *pair_ms = g_pair_ms;
+    if (pair_launches) *pair_launches = g_pair_launches;
     return 0;
 }
 
@@ -987,124 +995,142 @@ int rrtmgp_b200_heating_rate(int dtype, int ncol, int nlay, const void* up, cons
 // ---------------------------------------------------------------------------------------------
 namespace {
 
+// One fused call (= one solve_gpu of the reference driver) as an object, so that the longwave and the shortwave call of a
+// step can also be advanced tile by tile TOGETHER (fused_pair below).  setup() = validation, workspace, zeroing;
+// prologue(c0) = the tile's interpolation state and by-band particulate optics; bands() = the band launches of the tile;
+// finish() = net flux and heating rate.
 template<typename Real>
-void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, const rrtmgp_b200_fluxes* out,
-                  cudaStream_t s, bool sw)
+struct FusedJob
 {
-    if (!g || !cols || !out) throw ArgError("fused fluxes: null argument");
-    const HostPlan& h = g->h;
-    if (h.is_lw == sw) throw ArgError(sw ? "sw_fluxes needs a shortwave k-distribution" : "lw_fluxes needs a longwave k-distribution");
-    const int ncol = cols->ncol, nlay = cols->nlay, nlev = nlay + 1;
-    check_dims(ncol, nlay);
-    if (!cols->d_play || !cols->d_plev || !cols->d_tlay || !out->d_flux_up || !out->d_flux_dn) throw ArgError("fused fluxes: null array");
-    if (!sw && (!cols->d_tlev || !cols->d_tsfc || !cols->d_sfc_emis)) throw ArgError("lw_fluxes: tlev, tsfc and sfc_emis are required");
-    if (sw && (!cols->d_mu0 || !cols->d_sfc_alb_dir || !cols->d_sfc_alb_dif)) throw ArgError("sw_fluxes: mu0 and surface albedos are required");
-    if (nlay > 32 * TMASK_WORDS) throw ArgError("fused fluxes: at most 256 layers (use the stage calls for taller columns)");
-    const int nang = sw ? 1 : std::max(cols->n_gauss_angles, 1);
-    if (nang > 4) throw ArgError("lw_fluxes: n_gauss_angles must be 1..4");   // src/Rte_lw.cpp:139-151
-    const bool cloud = cols->cloud != nullptr;
-    if (cloud)
-    {
-        if (cols->cloud->dtype != g->dtype) throw ArgError("cloud optics object has a different precision");
-        if (cols->cloud->cf.nbnd != h.nbnd) throw ArgError("Cannot add optical properties with incompatible band - gpoint combination");
-        if (!cols->d_lwp || !cols->d_iwp || !cols->d_rel || !cols->d_dei) throw ArgError("cloud inputs missing");
-    }
-    const bool aerosol = cols->aerosol != nullptr;
-    AerosolMmr mmr{};
-    if (aerosol)
-    {
-        if (!sw) throw ArgError("lw_fluxes: aerosol optics are shortwave only (Radiation_solver_longwave has none)");
-        if (cols->aerosol->dtype != g->dtype) throw ArgError("aerosol optics object has a different precision");
-        if (cols->aerosol->af.nbnd != h.nbnd) throw ArgError("Cannot add optical properties with incompatible band - gpoint combination");
-        if (!cols->d_rh) throw ArgError("aerosol inputs missing: rh");
-        mmr = make_mmr(&cols->aerosol_concs, ncol, nlay);
-    }
-    const bool bnd = out->d_bnd_flux_up != nullptr;
-    if (bnd && !out->d_bnd_flux_dn) throw ArgError("by-band output needs both bnd_flux_up and bnd_flux_dn");
-    const VmrArgs vmr = make_vmr(g, &cols->concs, ncol, nlay);
+    rrtmgp_b200_gas_optics* g = nullptr; const rrtmgp_b200_columns* cols = nullptr; const rrtmgp_b200_fluxes* out = nullptr;
+    bool sw = false, cloud = false, aerosol = false, bnd = false, colres = false;
+    int ncol = 0, nlay = 0, nlev = 0, nang = 1, top_at_1 = 0, cpb = 32, wave = 1, nslots = 0, tile = 0;
+    AerosolMmr mmr{}; VmrArgs vmr{};
+    TileState<Real> st{}; FusedArgs<Real> a{};
+    const Real* col_dry = nullptr; Real *ctau = nullptr, *cssa = nullptr, *cg = nullptr;
+    size_t ncv = 0;
 
-    int top_at_1 = cols->top_at_1;
-    if (top_at_1 < 0)
+    // everything before the tile loop.  forced_tile > 0: use that tile size (the paired driver gives both calls the same)
+    void setup(rrtmgp_b200_gas_optics* g_, const rrtmgp_b200_columns* cols_, const rrtmgp_b200_fluxes* out_, cudaStream_t s, bool sw_,
+               int forced_tile = 0, int forced_wave = 0)
     {
-        Real p2[2];
-        CK(cudaMemcpyAsync(&p2[0], cols->d_play, sizeof(Real), cudaMemcpyDeviceToHost, s));
-        CK(cudaMemcpyAsync(&p2[1], (const Real*)cols->d_play + (size_t)ncol * (nlay - 1), sizeof(Real), cudaMemcpyDeviceToHost, s));
-        CK(cudaStreamSynchronize(s));
-        top_at_1 = p2[0] < p2[1];
+        g = g_; cols = cols_; out = out_; sw = sw_;
+        if (!g || !cols || !out) throw ArgError("fused fluxes: null argument");
+        const HostPlan& h = g->h;
+        if (h.is_lw == sw) throw ArgError(sw ? "sw_fluxes needs a shortwave k-distribution" : "lw_fluxes needs a longwave k-distribution");
+        ncol = cols->ncol; nlay = cols->nlay; nlev = nlay + 1;
+        check_dims(ncol, nlay);
+        if (!cols->d_play || !cols->d_plev || !cols->d_tlay || !out->d_flux_up || !out->d_flux_dn) throw ArgError("fused fluxes: null array");
+        if (!sw && (!cols->d_tlev || !cols->d_tsfc || !cols->d_sfc_emis)) throw ArgError("lw_fluxes: tlev, tsfc and sfc_emis are required");
+        if (sw && (!cols->d_mu0 || !cols->d_sfc_alb_dir || !cols->d_sfc_alb_dif)) throw ArgError("sw_fluxes: mu0 and surface albedos are required");
+        if (nlay > 32 * TMASK_WORDS) throw ArgError("fused fluxes: at most 256 layers (use the stage calls for taller columns)");
+        nang = sw ? 1 : std::max(cols->n_gauss_angles, 1);
+        if (nang > 4) throw ArgError("lw_fluxes: n_gauss_angles must be 1..4");   // src/Rte_lw.cpp:139-151
+        cloud = cols->cloud != nullptr;
+        if (cloud)
+        {
+            if (cols->cloud->dtype != g->dtype) throw ArgError("cloud optics object has a different precision");
+            if (cols->cloud->cf.nbnd != h.nbnd) throw ArgError("Cannot add optical properties with incompatible band - gpoint combination");
+            if (!cols->d_lwp || !cols->d_iwp || !cols->d_rel || !cols->d_dei) throw ArgError("cloud inputs missing");
+        }
+        aerosol = cols->aerosol != nullptr;
+        if (aerosol)
+        {
+            if (!sw) throw ArgError("lw_fluxes: aerosol optics are shortwave only (Radiation_solver_longwave has none)");
+            if (cols->aerosol->dtype != g->dtype) throw ArgError("aerosol optics object has a different precision");
+            if (cols->aerosol->af.nbnd != h.nbnd) throw ArgError("Cannot add optical properties with incompatible band - gpoint combination");
+            if (!cols->d_rh) throw ArgError("aerosol inputs missing: rh");
+            mmr = make_mmr(&cols->aerosol_concs, ncol, nlay);
+        }
+        bnd = out->d_bnd_flux_up != nullptr;
+        if (bnd && !out->d_bnd_flux_dn) throw ArgError("by-band output needs both bnd_flux_up and bnd_flux_dn");
+        vmr = make_vmr(g, &cols->concs, ncol, nlay);
+
+        top_at_1 = cols->top_at_1;
+        if (top_at_1 < 0)
+        {
+            Real p2[2];
+            CK(cudaMemcpyAsync(&p2[0], cols->d_play, sizeof(Real), cudaMemcpyDeviceToHost, s));
+            CK(cudaMemcpyAsync(&p2[1], (const Real*)cols->d_play + (size_t)ncol * (nlay - 1), sizeof(Real), cudaMemcpyDeviceToHost, s));
+            CK(cudaStreamSynchronize(s));
+            top_at_1 = p2[0] < p2[1];
+        }
+
+        colres = (g->colres < 0 ? g_colres : g->colres != 0) && (sw || cols->n_gauss_angles <= 1);   // column-resident LW: one angle
+        if (colres && colres_smem_bytes<Real>(nlay, h.gw, sw) > 227 * 1024)
+            throw ArgError("fused fluxes: column too tall for the shared-memory resident path");
+        cpb = FUSED_THREADS / (h.gw / 4);
+        // strips path: a tile is several waves of CTAs (CTAs retire and start continuously, so compute-heavy
+        // and memory-heavy passes of different CTAs overlap); scratch strips are per resident CTA.
+        // column-resident path: a tile only bounds the interpolation state (one CTA per 16/gw columns).
+        wave = forced_wave > 0 ? forced_wave : std::max(sw ? sw_blocks_per_wave<Real>(h.gw) : lw_blocks_per_wave<Real>(h.gw), 1);
+        nslots = colres ? 0 : 2 * wave;
+        tile = forced_tile > 0 ? forced_tile : auto_tile(g, ncol, nlay, wave, cpb);
+        const size_t tcl = (size_t)tile * nlay, ncl = (size_t)ncol * nlay;
+        ncv = (size_t)ncol * nlev;
+        size_t need = state_bytes<Real>(h, tile, nlay) + pad256(fused_scratch_bytes<Real>(nslots, nlay, sw)) + pad256(nslots * sizeof(int)) + 4096;
+        if (!cols->d_col_dry) need += pad256(ncl * sizeof(Real));
+        if (cloud || aerosol) need += 3 * pad256(tcl * h.nbnd * sizeof(Real));
+        if (sw && !out->d_flux_dn_dir) need += pad256(ncv * sizeof(Real));
+        if (sw && bnd && !out->d_bnd_flux_dn_dir) need += pad256(ncv * h.nbnd * sizeof(Real));
+        g->ws.reserve(need, s);
+        st = carve_state<Real>(g->ws, h, tile, nlay);
+
+        a = FusedArgs<Real>{};
+        a.ncol = ncol; a.nlay = nlay; a.top_at_1 = top_at_1;
+        a.tlay = (const Real*)cols->d_tlay; a.tlev = (const Real*)cols->d_tlev; a.tsfc = (const Real*)cols->d_tsfc;
+        a.sfc_emis = (const Real*)cols->d_sfc_emis; a.mu0 = (const Real*)cols->d_mu0;
+        a.alb_dir = (const Real*)cols->d_sfc_alb_dir; a.alb_dif = (const Real*)cols->d_sfc_alb_dif;
+        a.tsi_scaling = (const Real*)cols->d_tsi_scaling;
+        a.scratch = (V4<Real>*)g->ws.take<char>(fused_scratch_bytes<Real>(nslots, nlay, sw));
+        a.slot_busy = g->ws.take<int>(nslots); a.nslots = nslots;
+        if (nslots) CK(cudaMemsetAsync(a.slot_busy, 0, nslots * sizeof(int), s));
+        a.flux_up = (Real*)out->d_flux_up; a.flux_dn = (Real*)out->d_flux_dn;
+        a.flux_dir = (Real*)out->d_flux_dn_dir;
+        a.bnd_up = (Real*)out->d_bnd_flux_up; a.bnd_dn = (Real*)out->d_bnd_flux_dn; a.bnd_dir = (Real*)out->d_bnd_flux_dn_dir;
+        a.secant = (Real)(1. / 0.6096748751); a.weight = (Real)1;      // src/Rte_lw.cpp:139-151, n = 1
+        col_dry = (const Real*)cols->d_col_dry;
+        if (!col_dry)
+        {
+            const int ih = h.idx_h2o - 1;
+            if (!(cols->concs.vmr_ncol[ih] == ncol && cols->concs.vmr_nlay[ih] == nlay))
+                throw ArgError("fused fluxes: computing col_dry needs an (ncol,nlay) h2o field");
+            Real* t = g->ws.take<Real>(ncl);
+            launch_col_dry<Real>(ncol, nlay, cols->concs.d_vmr[ih], cols->d_plev, t, s);
+            col_dry = t;
+        }
+        if (cloud || aerosol) { ctau = g->ws.take<Real>(tcl * h.nbnd); cssa = g->ws.take<Real>(tcl * h.nbnd); cg = g->ws.take<Real>(tcl * h.nbnd); }
+        if (sw && !a.flux_dir) a.flux_dir = g->ws.take<Real>(ncv);
+        if (sw && bnd && !a.bnd_dir) a.bnd_dir = g->ws.take<Real>(ncv * h.nbnd);
+
+        if (!colres)        // the strips kernels accumulate band by band; the column-resident ones store once
+        {
+            CK(cudaMemsetAsync(a.flux_up, 0, ncv * sizeof(Real), s));
+            CK(cudaMemsetAsync(a.flux_dn, 0, ncv * sizeof(Real), s));
+            if (sw) CK(cudaMemsetAsync(a.flux_dir, 0, ncv * sizeof(Real), s));
+        }
     }
 
-    const bool colres = (g->colres < 0 ? g_colres : g->colres != 0) && (sw || cols->n_gauss_angles <= 1);   // column-resident LW: one angle
-    if (colres && colres_smem_bytes<Real>(nlay, h.gw, sw) > 227 * 1024)
-        throw ArgError("fused fluxes: column too tall for the shared-memory resident path");
-    const int cpb = FUSED_THREADS / (h.gw / 4);
-    // strips path: a tile is several waves of CTAs (CTAs retire and start continuously, so compute-heavy
-    // and memory-heavy passes of different CTAs overlap); scratch strips are per resident CTA.
-    // column-resident path: a tile only bounds the interpolation state (one CTA per 16/gw columns).
-    const int wave = std::max(sw ? sw_blocks_per_wave<Real>(h.gw) : lw_blocks_per_wave<Real>(h.gw), 1);
-    const int nslots = colres ? 0 : 2 * wave;
-    int tile = g->tile_cols;
-    if (tile <= 0)
+    static int auto_tile(rrtmgp_b200_gas_optics* g, int ncol, int nlay, int wave, int cpb)
     {
-        // 8 waves per tile; 16 when the interpolation state of such a tile takes under a quarter of the
-        // free device memory (longer launches: fewer tails, fewer prologue launches)
-        tile = 8 * wave * cpb;
-        size_t free_b = 0, total_b = 0;
-        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess &&
-            state_bytes<Real>(h, 2 * tile, nlay) < (free_b + g->ws.cap) / 4) tile *= 2;
-    }
-    tile = std::min(tile, ncol);
-    {
+        int tile = g->tile_cols;
+        if (tile <= 0)
+        {
+            // 8 waves per tile; 16 when the interpolation state of such a tile takes under a quarter of the
+            // free device memory (longer launches: fewer tails, fewer prologue launches)
+            tile = 8 * wave * cpb;
+            size_t free_b = 0, total_b = 0;
+            if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess &&
+                state_bytes<Real>(g->h, 2 * tile, nlay) < (free_b + g->ws.cap) / 4) tile *= 2;
+        }
+        tile = std::min(tile, ncol);
         // equal tiles (rounded up to whole CTAs) instead of full tiles plus a remainder
         const int ntiles = (ncol + tile - 1) / tile;
         tile = (((ncol + ntiles - 1) / ntiles + cpb - 1) / cpb) * cpb;
-        tile = std::min(tile, ncol);
-    }
-    const size_t tcl = (size_t)tile * nlay, ncl = (size_t)ncol * nlay, ncv = (size_t)ncol * nlev;
-    size_t need = state_bytes<Real>(h, tile, nlay) + pad256(fused_scratch_bytes<Real>(nslots, nlay, sw)) + pad256(nslots * sizeof(int)) + 4096;
-    if (!cols->d_col_dry) need += pad256(ncl * sizeof(Real));
-    if (cloud || aerosol) need += 3 * pad256(tcl * h.nbnd * sizeof(Real));
-    if (sw && !out->d_flux_dn_dir) need += pad256(ncv * sizeof(Real));
-    if (sw && bnd && !out->d_bnd_flux_dn_dir) need += pad256(ncv * h.nbnd * sizeof(Real));
-    g->ws.reserve(need, s);
-    TileState<Real> st = carve_state<Real>(g->ws, h, tile, nlay);
-
-    FusedArgs<Real> a{};
-    a.ncol = ncol; a.nlay = nlay; a.top_at_1 = top_at_1;
-    a.tlay = (const Real*)cols->d_tlay; a.tlev = (const Real*)cols->d_tlev; a.tsfc = (const Real*)cols->d_tsfc;
-    a.sfc_emis = (const Real*)cols->d_sfc_emis; a.mu0 = (const Real*)cols->d_mu0;
-    a.alb_dir = (const Real*)cols->d_sfc_alb_dir; a.alb_dif = (const Real*)cols->d_sfc_alb_dif;
-    a.tsi_scaling = (const Real*)cols->d_tsi_scaling;
-    a.scratch = (V4<Real>*)g->ws.take<char>(fused_scratch_bytes<Real>(nslots, nlay, sw));
-    a.slot_busy = g->ws.take<int>(nslots); a.nslots = nslots;
-    if (nslots) CK(cudaMemsetAsync(a.slot_busy, 0, nslots * sizeof(int), s));
-    a.flux_up = (Real*)out->d_flux_up; a.flux_dn = (Real*)out->d_flux_dn;
-    a.flux_dir = (Real*)out->d_flux_dn_dir;
-    a.bnd_up = (Real*)out->d_bnd_flux_up; a.bnd_dn = (Real*)out->d_bnd_flux_dn; a.bnd_dir = (Real*)out->d_bnd_flux_dn_dir;
-    a.secant = (Real)(1. / 0.6096748751); a.weight = (Real)1;      // src/Rte_lw.cpp:139-151, n = 1
-    const Real* col_dry = (const Real*)cols->d_col_dry;
-    if (!col_dry)
-    {
-        const int ih = h.idx_h2o - 1;
-        if (!(cols->concs.vmr_ncol[ih] == ncol && cols->concs.vmr_nlay[ih] == nlay))
-            throw ArgError("fused fluxes: computing col_dry needs an (ncol,nlay) h2o field");
-        Real* t = g->ws.take<Real>(ncl);
-        launch_col_dry<Real>(ncol, nlay, cols->concs.d_vmr[ih], cols->d_plev, t, s);
-        col_dry = t;
-    }
-    Real *ctau = nullptr, *cssa = nullptr, *cg = nullptr;
-    if (cloud || aerosol) { ctau = g->ws.take<Real>(tcl * h.nbnd); cssa = g->ws.take<Real>(tcl * h.nbnd); cg = g->ws.take<Real>(tcl * h.nbnd); }
-    if (sw && !a.flux_dir) a.flux_dir = g->ws.take<Real>(ncv);
-    if (sw && bnd && !a.bnd_dir) a.bnd_dir = g->ws.take<Real>(ncv * h.nbnd);
-
-    if (!colres)        // the strips kernels accumulate band by band; the column-resident ones store once
-    {
-        CK(cudaMemsetAsync(a.flux_up, 0, ncv * sizeof(Real), s));
-        CK(cudaMemsetAsync(a.flux_dn, 0, ncv * sizeof(Real), s));
-        if (sw) CK(cudaMemsetAsync(a.flux_dir, 0, ncv * sizeof(Real), s));
+        return std::min(tile, ncol);
     }
 
-    L2Pin pin(s, g->kmajor.p, g->kmajor.bytes);
-    for (int c0 = 0; c0 < ncol; c0 += tile)
+    void prologue(int c0, cudaStream_t s)
     {
         const int nc = std::min(tile, ncol - c0);
         st.nc = nc; a.c0 = c0; a.nc = nc;
@@ -1125,20 +1151,31 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
                                         nc, 0, cols->delta_aerosol, ctau, cssa, cg, s);
             a.cld_tau = ctau; a.cld_ssa = cssa; a.cld_g = cg;
         }
+    }
+
+    // Gauss-Jacobi-5 quadrature (src/Rte_lw.cpp:139-151): secant and weight of angle ia of nang
+    void set_angle(int ia)
+    {
+        static const double gauss_Ds[4][4] = {{1. / 0.6096748751, 0., 0., 0.}, {1. / 0.2509907356, 1. / 0.7908473988, 0., 0.},
+            {1. / 0.1024922169, 1. / 0.4417960320, 1. / 0.8633751621, 0.}, {1. / 0.0454586727, 1. / 0.2322334416, 1. / 0.5740198775, 1. / 0.903077597}};
+        static const double gauss_wts[4][4] = {{1., 0., 0., 0.}, {0.2300253764, 0.7699746236, 0., 0.},
+            {0.0437820218, 0.3875796738, 0.5686383044, 0.}, {0.0092068785, 0.1285704278, 0.4323381850, 0.4298845087}};
+        a.secant = (Real)gauss_Ds[nang - 1][ia]; a.weight = (Real)gauss_wts[nang - 1][ia]; a.bnd_add = ia > 0;
+    }
+
+    void bands(cudaStream_t s)
+    {
+        const HostPlan& h = g->h;
         if (g_prof.on) { cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, s)); g_prof.ev[sw].push_back(e); }
         if (colres) launch_cols<Real>(sw, dplan<Real>(g), (const BandArgs*)g->bands_dev.p, st, a, s);
         else if (sw)
             for (int b = 0; b < h.nbnd; ++b) launch_sw_band<Real>(dplan<Real>(g), g->bands[b], st, a, s);
         else
-            // Gauss-Jacobi-5 quadrature (src/Rte_lw.cpp:139-151): one pass of the band kernels per angle, fluxes
-            // accumulate (the reference's GPU path has a single angle; its CPU path sums angles the same way)
+            // one pass of the band kernels per angle, fluxes accumulate (the reference's GPU path has a single angle; its CPU
+            // path sums angles the same way)
             for (int ia = 0; ia < nang; ++ia)
             {
-                static const double gauss_Ds[4][4] = {{1. / 0.6096748751, 0., 0., 0.}, {1. / 0.2509907356, 1. / 0.7908473988, 0., 0.},
-                    {1. / 0.1024922169, 1. / 0.4417960320, 1. / 0.8633751621, 0.}, {1. / 0.0454586727, 1. / 0.2322334416, 1. / 0.5740198775, 1. / 0.903077597}};
-                static const double gauss_wts[4][4] = {{1., 0., 0., 0.}, {0.2300253764, 0.7699746236, 0., 0.},
-                    {0.0437820218, 0.3875796738, 0.5686383044, 0.}, {0.0092068785, 0.1285704278, 0.4323381850, 0.4298845087}};
-                a.secant = (Real)gauss_Ds[nang - 1][ia]; a.weight = (Real)gauss_wts[nang - 1][ia]; a.bnd_add = ia > 0;
+                set_angle(ia);
                 for (int b = 0; b < h.nbnd; ++b) launch_lw_band<Real>(dplan<Real>(g), g->bands[b], st, a, s);
             }
         if (g_prof.on)
@@ -1147,9 +1184,96 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
             g_prof.launches[sw] += colres ? 1 : h.nbnd * nang;
         }
     }
-    if (out->d_flux_net) launch_net<Real>(ncv, a.flux_dn, a.flux_up, out->d_flux_net, s);
-    if (bnd && out->d_bnd_flux_net) launch_net<Real>(ncv * h.nbnd, a.bnd_dn, a.bnd_up, out->d_bnd_flux_net, s);
-    if (out->d_heating_rate) launch_heating_rate<Real>(ncol, nlay, a.flux_up, a.flux_dn, cols->d_plev, out->d_heating_rate, s);
+
+    void finish(cudaStream_t s)
+    {
+        const HostPlan& h = g->h;
+        if (out->d_flux_net) launch_net<Real>(ncv, a.flux_dn, a.flux_up, out->d_flux_net, s);
+        if (bnd && out->d_bnd_flux_net) launch_net<Real>(ncv * h.nbnd, a.bnd_dn, a.bnd_up, out->d_bnd_flux_net, s);
+        if (out->d_heating_rate) launch_heating_rate<Real>(ncol, nlay, a.flux_up, a.flux_dn, cols->d_plev, out->d_heating_rate, s);
+    }
+};
+
+template<typename Real>
+void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, const rrtmgp_b200_fluxes* out,
+                  cudaStream_t s, bool sw)
+{
+    FusedJob<Real> j;
+    j.setup(g, cols, out, s, sw);
+    L2Pin pin(s, g->kmajor.p, g->kmajor.bytes);
+    for (int c0 = 0; c0 < j.ncol; c0 += j.tile)
+    {
+        j.prologue(c0, s);
+        j.bands(s);
+    }
+    j.finish(s);
+}
+
+// Longwave and shortwave of the same columns in ONE call: per tile both prologues, then band i of the longwave and band i of
+// the shortwave k-distribution in one launch whose CTAs alternate between the two roles (fused_pair.cu), so the L1-bound
+// longwave CTAs and the DRAM-bound shortwave CTAs share every SM; bands without a partner, and every band the paired
+// kernel does not cover (narrow bands of the reduced g-point sets, extra Gauss angles, the column-resident path), run through
+// the single-role launches.  Results are bit-identical to rrtmgp_b200_lw_fluxes + rrtmgp_b200_sw_fluxes.
+template<typename Real>
+void fused_pair(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, const rrtmgp_b200_fluxes* olw,
+                rrtmgp_b200_gas_optics* gsw, const rrtmgp_b200_columns* csw, const rrtmgp_b200_fluxes* osw, cudaStream_t s)
+{
+    if (!glw || !gsw || !clw || !csw || !olw || !osw) throw ArgError("lwsw_fluxes: null argument");
+    if (glw == gsw) throw ArgError("lwsw_fluxes: the longwave and the shortwave call need their own k-distribution objects");
+    if (clw->ncol != csw->ncol || clw->nlay != csw->nlay) throw ArgError("lwsw_fluxes: the two calls must cover the same columns");
+    const int wave = std::max(pair_blocks_per_wave<Real>(), 1);
+    // one tile size for both: the smaller of the two automatic choices
+    const int cpb = FUSED_THREADS / 4;
+    const int tile = std::min(FusedJob<Real>::auto_tile(glw, clw->ncol, clw->nlay, wave, cpb), FusedJob<Real>::auto_tile(gsw, csw->ncol, csw->nlay, wave, cpb));
+    FusedJob<Real> L, S;
+    L.setup(glw, clw, olw, s, false, tile, wave);
+    S.setup(gsw, csw, osw, s, true, tile, wave);
+    // paired launches need both roles with the same particulate flag (one kernel instantiation per flag); the fp64 build
+    // measured slower paired (pair_supported refuses it)
+    const bool pairable = sizeof(Real) == 4 && !L.colres && !S.colres && glw->h.gw == 16 && gsw->h.gw == 16 &&
+                          ((L.cloud || L.aerosol) == (S.cloud || S.aerosol));
+    if (!pairable)
+    {
+        // nothing to pair: the two calls one after the other (each with its own tiling)
+        fused_fluxes<Real>(glw, clw, olw, s, false);
+        fused_fluxes<Real>(gsw, csw, osw, s, true);
+        return;
+    }
+    L2Pin pin(s, gsw->kmajor.p, gsw->kmajor.bytes);
+    const int nbl = glw->h.nbnd, nbs = gsw->h.nbnd;
+    for (int c0 = 0; c0 < L.ncol; c0 += tile)
+    {
+        L.prologue(c0, s);
+        S.prologue(c0, s);
+        if (g_prof.on) { cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, s)); g_prof.ev[2].push_back(e); }
+        L.set_angle(0);
+        int il = 0, is = 0, npair = 0, nsingle = 0;
+        while (il < nbl || is < nbs)
+        {
+            if (il < nbl && is < nbs && pair_supported<Real>(dplan<Real>(glw), glw->bands[il], dplan<Real>(gsw), gsw->bands[is]))
+            {
+                launch_lwsw_band<Real>(dplan<Real>(glw), glw->bands[il], L.st, L.a, dplan<Real>(gsw), gsw->bands[is], S.st, S.a, s);
+                ++il; ++is; ++npair;
+            }
+            // no pair: the band the paired kernel does not cover (or the only kind left) goes through its own kernel
+            else if (il < nbl && (is >= nbs || glw->bands[il].ngb <= 8))
+            { launch_lw_band<Real>(dplan<Real>(glw), glw->bands[il], L.st, L.a, s); ++il; ++nsingle; }
+            else
+            { launch_sw_band<Real>(dplan<Real>(gsw), gsw->bands[is], S.st, S.a, s); ++is; ++nsingle; }
+        }
+        for (int ia = 1; ia < L.nang; ++ia)      // further Gauss angles of the longwave call
+        {
+            L.set_angle(ia);
+            for (int b = 0; b < nbl; ++b) { launch_lw_band<Real>(dplan<Real>(glw), glw->bands[b], L.st, L.a, s); ++nsingle; }
+        }
+        if (g_prof.on)
+        {
+            cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, s)); g_prof.ev[2].push_back(e);
+            g_prof.launches[2] += npair + nsingle;
+        }
+    }
+    L.finish(s);
+    S.finish(s);
 }
 
 
@@ -1384,6 +1508,16 @@ int rrtmgp_b200_fluxes_host(rrtmgp_b200_gas_optics* go_lw, const rrtmgp_b200_col
         if (!g0) throw ArgError("fluxes_host: null handles");
         if (g0->dtype == RRTMGP_B200_F32) fluxes_host<float>(go_lw, cols_lw, out_lw, go_sw, cols_sw, out_sw, chunk_cols, (cudaStream_t)stream);
         else fluxes_host<double>(go_lw, cols_lw, out_lw, go_sw, cols_sw, out_sw, chunk_cols, (cudaStream_t)stream);
+    });
+}
+int rrtmgp_b200_lwsw_fluxes(rrtmgp_b200_gas_optics* go_lw, const rrtmgp_b200_columns* cols_lw, const rrtmgp_b200_fluxes* out_lw,
+                            rrtmgp_b200_gas_optics* go_sw, const rrtmgp_b200_columns* cols_sw, const rrtmgp_b200_fluxes* out_sw, void* stream)
+{
+    return guarded([&] {
+        if (!go_lw || !go_sw) throw ArgError("lwsw_fluxes: null handle");
+        if (go_lw->dtype != go_sw->dtype) throw ArgError("lwsw_fluxes: the two k-distribution objects have different precisions");
+        if (go_lw->dtype == RRTMGP_B200_F32) fused_pair<float>(go_lw, cols_lw, out_lw, go_sw, cols_sw, out_sw, (cudaStream_t)stream);
+        else fused_pair<double>(go_lw, cols_lw, out_lw, go_sw, cols_sw, out_sw, (cudaStream_t)stream);
     });
 }
 int rrtmgp_b200_sw_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, const rrtmgp_b200_fluxes* out, void* stream)

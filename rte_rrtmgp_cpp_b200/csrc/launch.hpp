@@ -83,6 +83,15 @@ template<typename Real> void launch_lw_band(const DevPlan<Real>& P, const BandAr
 template<typename Real> void launch_sw_band(const DevPlan<Real>& P, const BandArgs& B, const TileState<Real>& st,
                                             const FusedArgs<Real>& a, cudaStream_t s);
 
+// ---- fused_pair.cu : one launch = one longwave band + one shortwave band of the same tile, CTAs of both kinds co-resident
+template<typename Real> bool pair_supported(const DevPlan<Real>& Plw, const BandArgs& Blw, const DevPlan<Real>& Psw, const BandArgs& Bsw);
+template<typename Real> void launch_lwsw_band(const DevPlan<Real>& Plw, const BandArgs& Blw, const TileState<Real>& stlw, const FusedArgs<Real>& alw,
+                                              const DevPlan<Real>& Psw, const BandArgs& Bsw, const TileState<Real>& stsw, const FusedArgs<Real>& asw,
+                                              cudaStream_t s);
+template<typename Real> void launch_role_band(bool shortwave, const DevPlan<Real>& P, const BandArgs& B, const TileState<Real>& st,
+                                              const FusedArgs<Real>& a, cudaStream_t s);
+template<typename Real> int pair_blocks_per_wave();
+
 // ---- colres.cu : one launch = all bands of one column tile, recurrences resident in shared memory
 template<typename Real> size_t colres_smem_bytes(int nlay, int gw, bool sw);
 template<typename Real> void launch_cols(bool sw, const DevPlan<Real>& P, const BandArgs* bands_dev, const TileState<Real>& st,

@@ -171,6 +171,57 @@ template<typename Real> __device__ __forceinline__ void q_fma(Real (&acc)[4], Re
 {
     pput(acc, 0, pfma(s, pget(v, 0), pget(acc, 0))); pput(acc, 1, pfma(s, pget(v, 1), pget(acc, 1)));
 }
+// ---- L1 prefetch of the NEXT layer's table rows ("prefetch.global.L1": no register, no scoreboard) ---------------------
+// MEASURED SLOWER, off by default (-DRB_TAB_PF=1 enables it): step 569 -> 934 ms on B200.  The band kernels are bound by
+// the L1TEX LSU data pipe (ncu: l1tex__data_pipe_lsu_wavefronts 75 % of peak in the longwave kernel), not by the latency
+// of the gathers, and these uncoalesced requests (one line per lane) add as many L1 wavefronts as the gathers themselves.
+// Mechanism kept for the record: the packed row numbers of the layer AFTER next arrive together with the next layer's
+// state (same scoreboard wait); at the top of a layer step the lanes of a column request the lines the NEXT step gathers.
+#ifndef RB_TAB_PF
+#define RB_TAB_PF 0
+#endif
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
+
+// {rows(itemp 1), rows(itemp 2)} of layer l for the band's flavor on that layer's side: the .z/.w half of flvB
+template<typename Real>
+__device__ __forceinline__ V2<Real> load_rows(const TileState<Real>& st, const BandLaunch<Real>& L, const unsigned* tm, int c, int l)
+{
+    const size_t icl = (size_t)c + (size_t)st.nc * l;
+    return reinterpret_cast<const V2<Real>*>(st.flvB + icl + L.flv[layer_side(tm, l)])[1];
+}
+
+// lane q of the LPC lanes of a column requests its share of the lines; `side` is the side of the layer the rows belong to
+template<typename G, int LPC, bool RAYLEIGH, typename Real>
+__device__ __forceinline__ void prefetch_tables(const BandLaunch<Real>& L, const DevPlan<Real>& P, const V2<Real>& rows, int side, int q)
+{
+    const int r0 = M<Real>::as_int(rows.x), r1 = M<Real>::as_int(rows.y);
+    const int dp = G::neta(P);
+    // major block: 8 corner rows (itemp, ipress, ieta); a row is RS elements (k, and the Planck fraction behind it in LW)
+#pragma unroll
+    for (int j = 0; j < 8 / LPC; ++j)
+    {
+        const int i = q + j * LPC;
+        const int row = ((i & 4) ? (r1 & 0xfffff) : (r0 & 0xfffff)) + ((i >> 1) & 1) * dp + (i & 1);
+        const char* p = (const char*)(L.kmaj + (size_t)((unsigned)row * (unsigned)G::RS));
+        prefetch_l1(p);
+        if (G::RS * sizeof(Real) > 128) prefetch_l1(p + 128);
+    }
+    // minor contributors of this side: per contributor two row pairs (itemp 1 / 2), the two eta rows of a pair adjacent
+    const int m0 = (r0 >> 20) & 0xfff, m1 = (r1 >> 20) & 0xfff;
+    const int npairs = 2 * L.B.nminor[side];
+    const Real* km = L.kmin[side];
+    for (int p2 = q; p2 < npairs; p2 += LPC)
+    {
+        const Real* t = km + (size_t)(p2 >> 1) * L.mstride + ((p2 & 1) ? m1 : m0) * G::GW;
+        prefetch_l1(t); prefetch_l1(t + G::GW);
+    }
+    if (RAYLEIGH && L.kray[0] && q < 2)
+    {
+        const Real* t = L.kray[side] + (q ? m1 : m0) * G::GW;
+        prefetch_l1(t); prefetch_l1(t + G::GW);
+    }
+}
+
 #define RB_FMA4(acc, s, v) q_fma(acc, s, v);
 #define RB_MUL4(acc, s, v) q_mul(acc, s, v);
 
@@ -316,12 +367,12 @@ __device__ __forceinline__ Real planck_at(const Real* __restrict__ tab, const V2
 
 // A resident CTA claims one scratch strip for its lifetime (grids are larger than one wave, so
 // strips are recycled as CTAs retire; which strip a CTA gets does not affect any result).
-__device__ __forceinline__ int claim_slot(int* busy, int nslots)
+__device__ __forceinline__ int claim_slot(int* busy, int nslots, int bid)
 {
     __shared__ int s_slot;
     if (threadIdx.x == 0)
     {
-        int s = (int)((blockIdx.x * 2654435761u) % (unsigned)nslots);
+        int s = (int)(((unsigned)bid * 2654435761u) % (unsigned)nslots);
         while (atomicCAS(&busy[s], 0, 1) != 0) s = (s + 1 == nslots) ? 0 : s + 1;
         s_slot = s;
     }

@@ -189,3 +189,51 @@ def test_full_size_domain_replicas_are_bit_identical():
             want = ref[k].view(-1, ndist).repeat(1, rep)
             assert torch.equal(got, want), (kind, k)
         assert torch.isfinite(out["flux_net"].t).all()
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("case", ["clear", "allsky-aerosol-3angles", "aerosol-only", "reduced", "ragged-tiles"])
+def test_paired_lw_sw_call_is_bit_identical_to_the_two_calls(case, dtype):
+    """rrtmgp_b200_lwsw_fluxes: longwave and shortwave CTAs co-resident in one launch per band pair (fused_pair.cu).  Separate
+    strips and flux slabs, the same per-CTA code: every output must equal lw.solve_gpu + sw.solve_gpu bit for bit — full-width
+    bands (paired kernel), the reduced g-point sets (narrow bands fall back to the single-role kernels mid-sequence), several
+    tiles with a ragged last one, clouds + aerosols, and extra longwave Gauss angles."""
+    from rte_rrtmgp_cpp_b200.atmos import add_aerosols
+    from rte_rrtmgp_cpp_b200.kdist import synthetic_aerosol_lut, REDUCED_LW_128, REDUCED_SW_112
+    kw = {}
+    if case == "clear":
+        atm = rce_atmosphere(150, 40)
+        kd_lw, kd_sw, lut_lw, lut_sw, alut = synthetic_kdist("lw"), synthetic_kdist("sw"), None, None, None
+    elif case == "allsky-aerosol-3angles":
+        atm = add_aerosols(allsky_atmosphere(70, 48, random_clouds=True))
+        kd_lw, kd_sw = synthetic_kdist("lw"), synthetic_kdist("sw")
+        lut_lw, lut_sw, alut = synthetic_cloud_lut("lw"), synthetic_cloud_lut("sw"), synthetic_aerosol_lut()
+        kw = dict(switch_cloud_optics=True, switch_output_bnd_fluxes=True, heating=True)
+    elif case == "aerosol-only":        # shortwave with, longwave without a particulate increment: not paired, same results
+        atm = add_aerosols(rce_atmosphere(60, 30))
+        kd_lw, kd_sw, lut_lw, lut_sw, alut = synthetic_kdist("lw"), synthetic_kdist("sw"), None, None, synthetic_aerosol_lut()
+    elif case == "reduced":
+        atm = rce_atmosphere(100, 33, top_at_1=True)
+        kd_lw, kd_sw, lut_lw, lut_sw, alut = synthetic_kdist("lw", REDUCED_LW_128), synthetic_kdist("sw", REDUCED_SW_112), None, None, None
+    else:
+        atm = rce_atmosphere(333, 17)
+        kd_lw, kd_sw, lut_lw, lut_sw, alut = synthetic_kdist("lw"), synthetic_kdist("sw"), None, None, None
+    lw = api.Radiation_solver_longwave(kd_lw, atm.vmr.keys(), lut_lw, dtype)
+    sw = api.Radiation_solver_shortwave(kd_sw, atm.vmr.keys(), lut_sw, dtype, aerosol_lut=alut) if alut is not None else \
+        api.Radiation_solver_shortwave(kd_sw, atm.vmr.keys(), lut_sw, dtype)
+    if case == "ragged-tiles":
+        lw.set_tile_columns(128); sw.set_tile_columns(96)
+    if case == "allsky-aerosol-3angles":
+        lw.n_gauss_angles = 3
+    cols = api.DeviceColumns(atm, dtype)
+    kw_sw = dict(kw, switch_aerosol_optics=True) if alut is not None else kw
+    ref_lw = {k: v.numpy().copy() for k, v in lw.solve_gpu(cols, **kw).items()}
+    ref_sw = {k: v.numpy().copy() for k, v in sw.solve_gpu(cols, **kw_sw).items()}
+    out_lw, out_sw = api.solve_pair(lw, sw, cols, **kw_sw)
+    torch.cuda.synchronize()
+    assert set(out_lw) == set(ref_lw) and set(out_sw) == set(ref_sw)
+    for k in ref_lw:
+        assert np.array_equal(out_lw[k].numpy(), ref_lw[k]), ("lw", k)
+    for k in ref_sw:
+        assert np.array_equal(out_sw[k].numpy(), ref_sw[k]), ("sw", k)
+    assert np.abs(ref_lw["flux_up"]).max() > 10 and np.abs(ref_sw["flux_dn"]).max() > 10
