@@ -338,10 +338,11 @@ int rrtmgp_b200_fluxes_host(rrtmgp_b200_gas_optics* go_lw, const rrtmgp_b200_col
 /* tuning / introspection of the fused path: columns per tile (0 = default), and the number of
  * kernels the last fused call launched (for bench.py's gpu_launches). */
 int rrtmgp_b200_set_tile_columns(rrtmgp_b200_gas_optics* go, int ncol_tile);
-/* which fused kernels a handle uses: 0 = per-band kernels with recurrence scratch strips in HBM
- * (default: measured faster), 1 = column-resident (recurrences in shared memory, one launch per
- * tile, ~30x less DRAM traffic), -1 = default (environment RB200_PATH=colres selects 1).
- * Both give the same fluxes to rounding. */
+/* which fused kernels a handle uses: 0 = per-band kernels with recurrence scratch strips in HBM (measured faster
+ * on large domains), 1 = column-resident (recurrences in shared memory, every band of a tile in one launch, no atomics,
+ * ~30x less DRAM traffic; measured 3.8x faster on 100-column calls), 2 = chosen per call by size (column-resident up to
+ * 6144 columns), -1 = default: environment RB200_PATH=strips|colres when set, else by size.  All give the same fluxes to
+ * rounding (each is compared with the oracle). */
 int rrtmgp_b200_set_fused_path(rrtmgp_b200_gas_optics* go, int path);
 long long rrtmgp_b200_launch_count(void);
 /* Device-side timing of the fused band kernels: each call first returns (and resets) the time
@@ -389,6 +390,30 @@ int rrtmgp_b200_sw_solver_2stream_noalloc(int dtype, int ncol, int nlay, int ngp
  * columns [*c0, *c1).  The host model gathers the flux slabs with its own MPI / NCCL;
  * rte_rrtmgp_cpp_b200/shard.py does it with torch.distributed for bench.py. */
 int rrtmgp_b200_shard_bounds(long long ncol, int world, int rank, long long* c0, long long* c1);
+
+/* Shard plan + flux gather over NCCL (SURVEY 8b "shard_plan_create(ncol, ngpu, ncclComm_t)", "gather_fluxes"; the reference
+ * itself is single-GPU).  One plan per process (= per GPU).  The communicator is either the host model's own ncclComm_t
+ * (nccl_comm, borrowed) or created here from the 128-byte NCCL unique id that rank 0 obtains with
+ * rrtmgp_b200_nccl_unique_id and hands to every rank by whatever means it has (MPI_Bcast, torch.distributed, a file).
+ * NCCL is resolved with dlopen("libnccl.so.2") on first use (RB200_NCCL_LIB overrides); world == 1 needs no NCCL at all. */
+typedef struct rrtmgp_b200_shard_plan rrtmgp_b200_shard_plan;
+int rrtmgp_b200_nccl_unique_id(void* id128 /*HOST, 128 bytes out*/);
+int rrtmgp_b200_shard_plan_create(long long ncol, int world, int rank, const void* id128 /*HOST or NULL*/,
+                                  void* nccl_comm /*ncclComm_t or NULL*/, rrtmgp_b200_shard_plan** out);
+void rrtmgp_b200_shard_plan_destroy(rrtmgp_b200_shard_plan* plan);
+/* columns [*c0, *c1) of `rank` (rank < 0: this process) — the rule of rrtmgp_b200_shard_bounds */
+int rrtmgp_b200_shard_plan_bounds(const rrtmgp_b200_shard_plan* plan, int rank, long long* c0, long long* c1);
+/* Gather flux slabs to `root` in the reference layout.  Every rank calls it with the same (nlev, nfields, part, nparts, root).
+ * A rank's shard may be processed in `nparts` column blocks (the rule of rrtmgp_b200_shard_bounds applied to the shard):
+ * d_part_fields[f] is this rank's (count_of_part, nlev) column-major slab of field f for block `part`; on the root
+ * d_full_fields[f] is the whole-domain (ncol, nlev) array (ignored elsewhere, may be NULL).  Each level of a slab is one
+ * contiguous run on both sides, so it is received straight into its place: grouped ncclSend / ncclRecv on `stream`, no
+ * staging buffer, no reordering pass; the root's own columns are one strided device copy per field.  Stream-ordered,
+ * returns without synchronising.  Calling it per block on a side stream overlaps the gather with the next block's kernels. */
+int rrtmgp_b200_gather_fluxes(rrtmgp_b200_shard_plan* plan, int dtype, int nlev, int nfields,
+                              const void* const* d_part_fields /*HOST array of device pointers*/,
+                              void* const* d_full_fields /*HOST array of device pointers, root only*/,
+                              int part, int nparts, int root, void* stream);
 
 #ifdef __cplusplus
 }

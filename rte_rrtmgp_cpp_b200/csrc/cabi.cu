@@ -5,6 +5,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <memory>
+#include <mutex>
+#include <cstring>
 #include <string>
 #include <vector>
 #include "../../include/rrtmgp_b200.h"
@@ -24,7 +26,12 @@ static Profile g_prof;
 // host-buffer entry: run the LW and the SW band kernels of a chunk on two streams (RB200_HOST_CONCURRENT=0 disables)
 // RB200_PATH=colres selects the column-resident kernels (recurrences in shared memory) instead of the
 // per-band kernels with recurrence scratch strips in HBM, which measure faster (kernels)
-static const bool g_colres = [] { const char* e = getenv("RB200_PATH"); return e && e[0] == 'c'; }();
+// unset: chosen per call by size (small calls are column-resident); "strips" / "colres" force one
+static const int g_colres = [] { const char* e = getenv("RB200_PATH"); return !e || !*e ? -1 : (e[0] == 'c' ? 1 : 0); }();
+// Calls of at most this many columns take the column-resident kernels when the path is not forced.  Measured on B200 (fp32):
+// 100 columns x 60 layers 1.6 ms (strips, paired) vs 0.42 ms; 16384 x 72 8.0 ms vs 10.0 ms; the strips launches cost a
+// fixed ~0.23 ms per band pair until they fill a wave (23680 columns), the column-resident kernel ~0.56 us per column.
+constexpr int kColresAutoMaxCols = 6144;
 static const bool g_host_concurrent = [] { const char* e = getenv("RB200_HOST_CONCURRENT"); return !(e && e[0] == '0'); }();
 
 struct CudaError : std::runtime_error { using std::runtime_error::runtime_error; };
@@ -218,10 +225,10 @@ extern "C" {
 
 const char* rrtmgp_b200_last_error(void) { return g_err.c_str(); }
 int rrtmgp_b200_version(void) { return 100; }
-int rrtmgp_b200_set_fused_path(rrtmgp_b200_gas_optics* g, int path)
+int rrtmgp_b200_set_fused_path(rrtmgp_b200_gas_optics* g, int path)   /* -1 default (RB200_PATH, else by size), 0, 1, 2 = by size */
 {
     return guarded([&] {
-        if (!g || path < -1 || path > 1) throw ArgError("set_fused_path: handle and path in {-1, 0, 1}");
+        if (!g || path < -1 || path > 2) throw ArgError("set_fused_path: handle and path in {-1, 0, 1, 2}");
         g->colres = path;
     }, false);
 }
@@ -1056,9 +1063,12 @@ struct FusedJob
             top_at_1 = p2[0] < p2[1];
         }
 
-        colres = (g->colres < 0 ? g_colres : g->colres != 0) && (sw || cols->n_gauss_angles <= 1);   // column-resident LW: one angle
-        if (colres && colres_smem_bytes<Real>(nlay, h.gw, sw) > 227 * 1024)
+        // path: the handle's setting (0 strips, 1 column-resident, 2 by size), else RB200_PATH, else by size
+        const int want = g->colres >= 0 ? (g->colres == 2 ? -1 : g->colres) : g_colres;
+        const bool colres_ok = (sw || cols->n_gauss_angles <= 1) && colres_smem_bytes<Real>(nlay, h.gw, sw) <= 227 * 1024;   // column-resident LW: one angle
+        if (want == 1 && (sw || cols->n_gauss_angles <= 1) && !colres_ok)
             throw ArgError("fused fluxes: column too tall for the shared-memory resident path");
+        colres = want == 1 ? colres_ok : (want < 0 && colres_ok && ncol <= kColresAutoMaxCols);
         cpb = FUSED_THREADS / (h.gw / 4);
         // strips path: a tile is several waves of CTAs (CTAs retire and start continuously, so compute-heavy
         // and memory-heavy passes of different CTAs overlap); scratch strips are per resident CTA.
@@ -1120,7 +1130,8 @@ struct FusedJob
             // free device memory (longer launches: fewer tails, fewer prologue launches)
             tile = 8 * wave * cpb;
             size_t free_b = 0, total_b = 0;
-            if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess &&
+            if (ncol > tile &&          // a call that fits one tile needs no memory query (it costs ~50 us per call)
+                cudaMemGetInfo(&free_b, &total_b) == cudaSuccess &&
                 state_bytes<Real>(g->h, 2 * tile, nlay) < (free_b + g->ws.cap) / 4) tile *= 2;
         }
         tile = std::min(tile, ncol);
@@ -1592,3 +1603,191 @@ extern "C" int rrtmgp_b200_sw_solver_2stream_noalloc(int dtype, int ncol, int nl
                                      gpt_flux_up, gpt_flux_dn, gpt_flux_dir, work4, (cudaStream_t)stream));
     });
 }
+
+// ---------------------------------------------------------------------------------------------
+// Multi-GPU: column-shard plan + flux gather over NCCL.  The library has no link-time dependency on NCCL:
+// libnccl.so.2 is resolved with dlopen on first use (the copy already in the process when the host model or PyTorch loaded
+// one; RB200_NCCL_LIB overrides the name), and only the eight entry points below are used.
+// ---------------------------------------------------------------------------------------------
+#include <dlfcn.h>
+namespace {
+struct NcclUniqueId { char internal[128]; };                    // nccl.h: NCCL_UNIQUE_ID_BYTES
+struct NcclApi
+{
+    void* lib = nullptr;
+    int (*GetUniqueId)(NcclUniqueId*) = nullptr;
+    int (*CommInitRank)(void**, int, NcclUniqueId, int) = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    int (*CommCount)(void*, int*) = nullptr;
+    int (*CommUserRank)(void*, int*) = nullptr;
+    int (*Send)(const void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+NcclApi& nccl()
+{
+    static NcclApi api;
+    static std::once_flag once;
+    static std::string err;
+    std::call_once(once, [] {
+        const char* names[] = {getenv("RB200_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+        for (const char* n : names)
+        {
+            if (!n || !*n) continue;
+            api.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+            if (api.lib) break;
+            err = dlerror();
+        }
+        if (!api.lib) return;
+        auto sym = [&](const char* s) { void* p = dlsym(api.lib, s); if (!p) err = std::string("missing symbol ") + s; return p; };
+        api.GetUniqueId = (int (*)(NcclUniqueId*))sym("ncclGetUniqueId");
+        api.CommInitRank = (int (*)(void**, int, NcclUniqueId, int))sym("ncclCommInitRank");
+        api.CommDestroy = (int (*)(void*))sym("ncclCommDestroy");
+        api.CommCount = (int (*)(void*, int*))sym("ncclCommCount");
+        api.CommUserRank = (int (*)(void*, int*))sym("ncclCommUserRank");
+        api.Send = (int (*)(const void*, size_t, int, int, void*, cudaStream_t))sym("ncclSend");
+        api.Recv = (int (*)(void*, size_t, int, int, void*, cudaStream_t))sym("ncclRecv");
+        api.GroupStart = (int (*)())sym("ncclGroupStart");
+        api.GroupEnd = (int (*)())sym("ncclGroupEnd");
+        api.GetErrorString = (const char* (*)(int))sym("ncclGetErrorString");
+    });
+    if (!api.lib || !api.GetUniqueId || !api.CommInitRank || !api.CommDestroy || !api.Send || !api.Recv || !api.GroupStart || !api.GroupEnd)
+        throw CudaError("NCCL is not available (dlopen libnccl.so.2: " + (err.empty() ? std::string("unknown error") : err) + "); set RB200_NCCL_LIB");
+    return api;
+}
+void nccl_ck(int rc, const char* what)
+{
+    if (rc == 0) return;
+    NcclApi& n = nccl();
+    throw CudaError(std::string(what) + ": " + (n.GetErrorString ? n.GetErrorString(rc) : "NCCL error") + " (" + std::to_string(rc) + ")");
+}
+// the partition rule of rrtmgp_b200_shard_bounds
+void shard_range(long long n, int parts, int i, long long& a, long long& b)
+{
+    a = (long long)((__int128)i * n / parts); b = (long long)((__int128)(i + 1) * n / parts);
+}
+}  // namespace
+
+struct rrtmgp_b200_shard_plan
+{
+    long long ncol = 0; int world = 1, rank = 0;
+    void* comm = nullptr; bool owns_comm = false;
+};
+
+extern "C" {
+
+int rrtmgp_b200_nccl_unique_id(void* id128)
+{
+    return guarded([&] {
+        if (!id128) throw ArgError("nccl_unique_id: null buffer");
+        NcclUniqueId id;
+        nccl_ck(nccl().GetUniqueId(&id), "ncclGetUniqueId");
+        std::memcpy(id128, id.internal, sizeof id.internal);
+    }, false);
+}
+
+int rrtmgp_b200_shard_plan_create(long long ncol, int world, int rank, const void* id128, void* nccl_comm, rrtmgp_b200_shard_plan** out)
+{
+    return guarded([&] {
+        if (!out) throw ArgError("shard_plan_create: null output");
+        *out = nullptr;
+        if (ncol < 0 || world < 1 || rank < 0 || rank >= world) throw ArgError("shard_plan_create: need ncol >= 0 and 0 <= rank < world");
+        std::unique_ptr<rrtmgp_b200_shard_plan> p(new rrtmgp_b200_shard_plan);
+        p->ncol = ncol; p->world = world; p->rank = rank;
+        if (nccl_comm)
+        {
+            // the host model's communicator (ncclComm_t): checked against world / rank, never destroyed here
+            NcclApi& n = nccl();
+            int cw = world, cr = rank;
+            if (n.CommCount && n.CommUserRank) { nccl_ck(n.CommCount(nccl_comm, &cw), "ncclCommCount"); nccl_ck(n.CommUserRank(nccl_comm, &cr), "ncclCommUserRank"); }
+            if (cw != world || cr != rank) throw ArgError("shard_plan_create: communicator size / rank differ from world / rank");
+            p->comm = nccl_comm;
+        }
+        else if (world > 1)
+        {
+            if (!id128) throw ArgError("shard_plan_create: world > 1 needs a communicator or the 128-byte unique id of rank 0");
+            NcclUniqueId id;
+            std::memcpy(id.internal, id128, sizeof id.internal);
+            nccl_ck(nccl().CommInitRank(&p->comm, world, id, rank), "ncclCommInitRank");
+            p->owns_comm = true;
+        }
+        *out = p.release();
+    }, false);
+}
+
+void rrtmgp_b200_shard_plan_destroy(rrtmgp_b200_shard_plan* p)
+{
+    if (!p) return;
+    if (p->owns_comm && p->comm) { try { nccl().CommDestroy(p->comm); } catch (...) {} }
+    delete p;
+}
+
+int rrtmgp_b200_shard_plan_bounds(const rrtmgp_b200_shard_plan* p, int rank, long long* c0, long long* c1)
+{
+    if (!p || !c0 || !c1) return fail(RRTMGP_B200_E_ARG, "shard_plan_bounds: null argument");
+    if (rank < 0) rank = p->rank;
+    if (rank >= p->world) return fail(RRTMGP_B200_E_ARG, "shard_plan_bounds: rank outside the plan");
+    shard_range(p->ncol, p->world, rank, *c0, *c1);
+    return 0;
+}
+
+int rrtmgp_b200_gather_fluxes(rrtmgp_b200_shard_plan* p, int dtype, int nlev, int nfields, const void* const* d_part_fields,
+                              void* const* d_full_fields, int part, int nparts, int root, void* stream)
+{
+    return guarded([&] {
+        if (!p) throw ArgError("gather_fluxes: null plan");
+        if (dtype != RRTMGP_B200_F32 && dtype != RRTMGP_B200_F64) throw ArgError("bad dtype");
+        if (nlev < 1 || nfields < 1 || nparts < 1 || part < 0 || part >= nparts || root < 0 || root >= p->world) throw ArgError("gather_fluxes: bad argument");
+        if (!d_part_fields) throw ArgError("gather_fluxes: null field list");
+        const bool is_root = p->rank == root;
+        if (is_root && !d_full_fields) throw ArgError("gather_fluxes: the root needs the full-domain arrays");
+        const size_t esz = dtype == RRTMGP_B200_F32 ? 4 : 8;
+        const int dt = dtype == RRTMGP_B200_F32 ? 7 : 8;             // ncclFloat32 / ncclFloat64
+        cudaStream_t s = (cudaStream_t)stream;
+        // columns of part `part` of rank r's shard, in domain coordinates
+        auto span = [&](int r, long long& first, long long& count) {
+            long long a, b, pa, pb;
+            shard_range(p->ncol, p->world, r, a, b);
+            shard_range(b - a, nparts, part, pa, pb);
+            first = a + pa; count = pb - pa;
+        };
+        long long my_first, my_count;
+        span(p->rank, my_first, my_count);
+        for (int f = 0; f < nfields; ++f)
+            if ((my_count > 0 && !d_part_fields[f]) || (is_root && !d_full_fields[f])) throw ArgError("gather_fluxes: null field");
+        if (is_root && my_count > 0)        // the root's own columns: one strided device copy per field
+            for (int f = 0; f < nfields; ++f)
+                CK(cudaMemcpy2DAsync((char*)d_full_fields[f] + (size_t)my_first * esz, (size_t)p->ncol * esz, d_part_fields[f],
+                                     (size_t)my_count * esz, (size_t)my_count * esz, (size_t)nlev, cudaMemcpyDeviceToDevice, s));
+        if (p->world == 1) return;
+        if (!p->comm) throw ArgError("gather_fluxes: the plan has no communicator");
+        NcclApi& n = nccl();
+        // every level of a part is one contiguous run of `count` columns on both sides: it goes straight into the
+        // reference-layout (ncol, nlev) array of the root, no staging buffer and no reordering pass
+        nccl_ck(n.GroupStart(), "ncclGroupStart");
+        if (is_root)
+        {
+            for (int r = 0; r < p->world; ++r)
+            {
+                if (r == root) continue;
+                long long first, count;
+                span(r, first, count);
+                if (count == 0) continue;
+                for (int f = 0; f < nfields; ++f)
+                    for (int l = 0; l < nlev; ++l)
+                        nccl_ck(n.Recv((char*)d_full_fields[f] + ((size_t)l * p->ncol + (size_t)first) * esz, (size_t)count, dt, r, p->comm, s), "ncclRecv");
+            }
+        }
+        else if (my_count > 0)
+        {
+            for (int f = 0; f < nfields; ++f)
+                for (int l = 0; l < nlev; ++l)
+                    nccl_ck(n.Send((const char*)d_part_fields[f] + (size_t)l * my_count * esz, (size_t)my_count, dt, root, p->comm, s), "ncclSend");
+        }
+        nccl_ck(n.GroupEnd(), "ncclGroupEnd");
+    });
+}
+
+}  // extern "C"

@@ -86,8 +86,11 @@ template<typename Real> int pair_blocks_per_wave()
 {
     int dev = 0, sms = 0, occ = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    static int cache[64] = {};                            // per device
+    if (dev >= 0 && dev < 64 && cache[dev] > 0) return cache[dev];
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, lwsw_band_kernel<Real, false>, FUSED_THREADS, 0);
+    if (dev >= 0 && dev < 64) cache[dev] = sms * occ;
     return sms * occ;
 }
 

@@ -34,10 +34,14 @@ template<typename Real> int sw_blocks_per_wave(int gw)
 {
     int dev = 0, sms = 0, occ = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    static int cache[64][2] = {};                       // per device, per table width: asked on every call of the C ABI
+    int* slot = dev >= 0 && dev < 64 ? &cache[dev][gw == 16] : nullptr;
+    if (slot && *slot > 0) return *slot;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (gw == 16 && sizeof(Real) == 4) return pair_blocks_per_wave<Real>();
     if (gw == 16) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sw_band_kernel<Real, 4, 16, false, 9>, FUSED_THREADS, 0);
     else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sw_band_kernel<Real, 2, 8, false, 9>, FUSED_THREADS, 0);
+    if (slot) *slot = sms * occ;
     return sms * occ;
 }
 template int sw_blocks_per_wave<float>(int);

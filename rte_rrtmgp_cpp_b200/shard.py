@@ -65,3 +65,64 @@ def domain_mean(profile_sum: torch.Tensor, ncol: int) -> torch.Tensor:
     """All-reduce of per-rank column sums (nlev,) -> domain-mean profile on every rank."""
     dist.all_reduce(profile_sum, op=dist.ReduceOp.SUM)
     return profile_sum / ncol
+
+
+class ShardPlan:
+    """rrtmgp_b200_shard_plan (C ABI): this process's column shard of an `ncol`-column domain plus the NCCL communicator the
+    flux gather runs on.  The communicator is created inside the library from a unique id that rank 0 obtains
+    (rrtmgp_b200_nccl_unique_id) and torch.distributed only carries to the other ranks; world == 1 needs neither."""
+
+    def __init__(self, ncol: int, world: int = 1, rank: int = 0, device: Optional[torch.device] = None):
+        import ctypes as C
+        from . import capi
+        self._C, self._capi, self.L = C, capi, capi.lib()
+        self.ncol, self.world, self.rank = int(ncol), int(world), int(rank)
+        idbuf = None
+        if world > 1:
+            # the library resolves NCCL with dlopen: point it at the copy PyTorch ships unless the caller chose one
+            import os
+            if "RB200_NCCL_LIB" not in os.environ:
+                try:
+                    import nvidia.nccl
+                    cand = os.path.join(list(nvidia.nccl.__path__)[0], "lib", "libnccl.so.2")
+                    if os.path.exists(cand):
+                        os.environ["RB200_NCCL_LIB"] = cand
+                except Exception:
+                    pass
+            raw = (C.c_ubyte * 128)()
+            if rank == 0:
+                capi.check(self.L.rrtmgp_b200_nccl_unique_id(raw))
+            t = torch.tensor(list(raw), dtype=torch.uint8, device=device if device is not None else "cuda")
+            dist.broadcast(t, src=0)
+            idbuf = (C.c_ubyte * 128)(*t.cpu().tolist())
+        self.h = C.c_void_p()
+        capi.check(self.L.rrtmgp_b200_shard_plan_create(self.ncol, self.world, self.rank, idbuf, None, C.byref(self.h)))
+
+    def bounds(self, rank: int = -1) -> Tuple[int, int]:
+        C = self._C
+        a, b = C.c_longlong(), C.c_longlong()
+        self._capi.check(self.L.rrtmgp_b200_shard_plan_bounds(self.h, int(rank), C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def gather(self, part_fields: Sequence[torch.Tensor], full_fields: Optional[Sequence[torch.Tensor]], nlev: int,
+               part: int = 0, nparts: int = 1, root: int = 0, stream=None) -> None:
+        """part_fields[f]: this rank's (count, nlev) column-major slab of field f; full_fields[f] on the root: (ncol, nlev)."""
+        C = self._C
+        n = len(part_fields)
+        dt = part_fields[0].dtype
+        src = (C.c_void_p * n)(*[f.data_ptr() for f in part_fields])
+        dst = (C.c_void_p * n)(*[f.data_ptr() for f in full_fields]) if full_fields is not None else None
+        s = stream if stream is not None else torch.cuda.current_stream()
+        self._capi.check(self.L.rrtmgp_b200_gather_fluxes(self.h, self._capi.F32 if dt == torch.float32 else self._capi.F64, int(nlev), n,
+                                                          src, dst, int(part), int(nparts), int(root), C.c_void_p(s.cuda_stream)))
+
+    def close(self) -> None:
+        if getattr(self, "h", None) is not None and self.h.value:
+            self.L.rrtmgp_b200_shard_plan_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -124,3 +124,21 @@ def test_shard_bounds_is_the_python_partition():
             assert prev == ncol
     assert L.rrtmgp_b200_shard_bounds(10, 2, 2, C.byref(a), C.byref(b)) == capi.E_ARG
     assert b"shard_bounds" in L.rrtmgp_b200_last_error()
+
+
+def test_shard_plan_host_logic_needs_no_device_and_no_nccl():
+    """rrtmgp_b200_shard_plan_*: a single-process plan is pure host state; its bounds are rrtmgp_b200_shard_bounds; a
+    multi-process plan without a communicator or unique id is refused (no NCCL call is made for any of this)."""
+    L = capi.lib()
+    h = C.c_void_p()
+    assert L.rrtmgp_b200_shard_plan_create(1000003, 1, 0, None, None, C.byref(h)) == 0 and h.value
+    a, b = C.c_longlong(), C.c_longlong()
+    assert L.rrtmgp_b200_shard_plan_bounds(h, -1, C.byref(a), C.byref(b)) == 0 and (a.value, b.value) == (0, 1000003)
+    assert L.rrtmgp_b200_shard_plan_bounds(h, 1, C.byref(a), C.byref(b)) == capi.E_ARG
+    L.rrtmgp_b200_shard_plan_destroy(h)
+    h = C.c_void_p()
+    rc = L.rrtmgp_b200_shard_plan_create(100, 4, 1, None, None, C.byref(h))
+    assert rc == capi.E_ARG and not h.value and b"unique id" in L.rrtmgp_b200_last_error()
+    assert L.rrtmgp_b200_shard_plan_create(100, 4, 4, None, None, C.byref(h)) == capi.E_ARG
+    assert L.rrtmgp_b200_gather_fluxes(None, capi.F32, 3, 1, None, None, 0, 1, 0, None) == capi.E_ARG
+    L.rrtmgp_b200_shard_plan_destroy(None)

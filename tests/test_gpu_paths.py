@@ -58,3 +58,26 @@ def test_paths_agree(dtype, kind, ncol, nlay, top_at_1, cloudy, reduced):
     for k in KEYS[kind]:
         scale = max(1.0, float(np.max(np.abs(res[0][k]))))
         assert np.max(np.abs(res[1][k] - res[0][k])) <= rt * scale, k
+
+
+def test_path_is_chosen_by_call_size():
+    """set_fused_path(2): calls of up to 6144 columns run the column-resident kernels (one launch for all bands), larger ones
+    the per-band kernels; both within tolerance of each other.  Counted through the library's launch counter."""
+    from rte_rrtmgp_cpp_b200 import capi
+    L = capi.lib()
+    kd = synthetic_kdist("lw")
+    launches = {}
+    for ncol in (64, 6144, 6145):
+        atm = rce_atmosphere(ncol, 12)
+        sol = api.Radiation_solver_longwave(kd, atm.vmr.keys(), None, torch.float32)
+        sol.set_fused_path(2)
+        cols = api.DeviceColumns(atm, torch.float32)
+        n0 = L.rrtmgp_b200_launch_count()
+        out = sol.solve_gpu(cols)
+        torch.cuda.synchronize()
+        launches[ncol] = L.rrtmgp_b200_launch_count() - n0
+        sol.set_fused_path(0)
+        ref = sol.solve_gpu(cols, out={})
+        assert np.max(np.abs(out["flux_up"].numpy() - ref["flux_up"].numpy())) < 1e-2
+    assert launches[64] == launches[6144] < kd.nbnd          # prologue + one kernel for all bands (+ col_dry, net)
+    assert launches[6145] >= kd.nbnd + 1                      # prologue + one launch per band
