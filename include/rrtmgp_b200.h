@@ -338,6 +338,13 @@ int rrtmgp_b200_fluxes_host(rrtmgp_b200_gas_optics* go_lw, const rrtmgp_b200_col
 /* tuning / introspection of the fused path: columns per tile (0 = default), and the number of
  * kernels the last fused call launched (for bench.py's gpu_launches). */
 int rrtmgp_b200_set_tile_columns(rrtmgp_b200_gas_optics* go, int ncol_tile);
+/* Debug aid standing in for compute-sanitizer (closed on this GPU pool).  flags = 1: before every fused call of this handle
+ * the whole workspace (tile state, scratch strips, strip flags, temporaries) is filled with 0xFF bytes — NaN as float or
+ * double — so a value read before it is written poisons the fluxes, and every carved piece is followed by a 256-byte canary
+ * block; after the call the stream is synchronised and an overwritten canary fails the call with E_CUDA naming the piece.
+ * Results must be bit-identical with and without it (tests/test_gpu_debug_arena.py).  flags = 3 additionally corrupts one
+ * canary byte on purpose (self-test of the check: the call must fail).  flags = 0 switches it off. */
+int rrtmgp_b200_set_debug(rrtmgp_b200_gas_optics* go, int flags);
 /* which fused kernels a handle uses: 0 = per-band kernels with recurrence scratch strips in HBM (measured faster
  * on large domains), 1 = column-resident (recurrences in shared memory, every band of a tile in one launch, no atomics,
  * ~30x less DRAM traffic; measured 3.8x faster on 100-column calls), 2 = chosen per call by size (column-resident up to
@@ -406,10 +413,12 @@ int rrtmgp_b200_shard_plan_bounds(const rrtmgp_b200_shard_plan* plan, int rank, 
 /* Gather flux slabs to `root` in the reference layout.  Every rank calls it with the same (nlev, nfields, part, nparts, root).
  * A rank's shard may be processed in `nparts` column blocks (the rule of rrtmgp_b200_shard_bounds applied to the shard):
  * d_part_fields[f] is this rank's (count_of_part, nlev) column-major slab of field f for block `part`; on the root
- * d_full_fields[f] is the whole-domain (ncol, nlev) array (ignored elsewhere, may be NULL).  Each level of a slab is one
- * contiguous run on both sides, so it is received straight into its place: grouped ncclSend / ncclRecv on `stream`, no
- * staging buffer, no reordering pass; the root's own columns are one strided device copy per field.  Stream-ordered,
- * returns without synchronising.  Calling it per block on a side stream overlaps the gather with the next block's kernels. */
+ * d_full_fields[f] is the whole-domain (ncol, nlev) array (ignored elsewhere, may be NULL).  Default: one ncclSend / ncclRecv
+ * per field and peer (grouped) into a staging buffer the plan keeps on the root, then one strided device copy per (peer, field)
+ * into the reference layout; RB200_GATHER=direct receives every level straight into its place instead (no staging copy, but
+ * nlev x nfields small messages per peer: measured 3x slower).  The root's own columns are one strided device copy per field.
+ * Stream-ordered, returns without synchronising (the staging buffer grows, synchronising, only while sizes still increase).
+ * Calling it per block on a side stream overlaps the gather with the next block's kernels. */
 int rrtmgp_b200_gather_fluxes(rrtmgp_b200_shard_plan* plan, int dtype, int nlev, int nfields,
                               const void* const* d_part_fields /*HOST array of device pointers*/,
                               void* const* d_full_fields /*HOST array of device pointers, root only*/,

@@ -636,6 +636,10 @@ class _Radiation_solver:
         c._keep = concs
         return c, f
 
+    def set_debug(self, flags: int) -> None:
+        """1: NaN-poison the workspace before and check canary blocks after every fused call (rrtmgp_b200_set_debug)."""
+        check(lib().rrtmgp_b200_set_debug(self.kdist.h, int(flags)))
+
     def set_fused_path(self, path: int) -> None:
         """0 per-band kernels with HBM scratch strips (default), 1 column-resident kernels."""
         check(lib().rrtmgp_b200_set_fused_path(self.kdist.h, int(path)))

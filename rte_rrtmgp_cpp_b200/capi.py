@@ -94,6 +94,7 @@ SYMBOLS = {
     "rrtmgp_b200_profile_pair": (i, [C.POINTER(d), C.POINTER(C.c_longlong)]),
     "rrtmgp_b200_fluxes_host": (i, [vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), i, vp]),
     "rrtmgp_b200_set_tile_columns": (i, [vp, i]),
+    "rrtmgp_b200_set_debug": (i, [vp, i]),
     "rrtmgp_b200_set_fused_path": (i, [vp, i]),
     "rrtmgp_b200_launch_count": (C.c_longlong, []),
     "rrtmgp_b200_shard_bounds": (i, [C.c_longlong, i, i, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),

@@ -75,23 +75,61 @@ struct DevBuf
 struct Arena
 {
     char* base = nullptr; size_t cap = 0, off = 0;
+    // debug mode (rrtmgp_b200_set_debug; the pool's compute-sanitizer is closed): reserve() fills the whole arena with 0xFF
+    // bytes (NaN as float / double, -1 as int) so that anything read before it is written shows up in the fluxes, and every
+    // piece is followed by a 256-byte canary block that check() expects untouched after the call.
+    bool debug = false, selftest = false;      // selftest: arm() corrupts the first canary on purpose (the check must then fail)
+    static constexpr size_t kCanary = 256;
+    static constexpr unsigned char kCanaryByte = 0xA5;
+    std::vector<size_t> canaries;       // offsets of the canary blocks carved since the last reserve()
     ~Arena() { if (base) cudaFree(base); }
     void reserve(size_t n, cudaStream_t s)
     {
+        if (debug) n += 64 * (kCanary + 256);
         if (n > cap)
         {
             if (base) { CK(cudaStreamSynchronize(s)); cudaFree(base); base = nullptr; }
             CK(cudaMalloc((void**)&base, n)); cap = n;
         }
         off = 0;
+        canaries.clear();
+        if (debug && cap) CK(cudaMemsetAsync(base, 0xFF, cap, s));
     }
     template<typename T> T* take(size_t count)
     {
         off = (off + 255) & ~(size_t)255;
         T* r = reinterpret_cast<T*>(base + off);
         off += count * sizeof(T);
+        if (debug)
+        {
+            off = (off + 255) & ~(size_t)255;
+            canaries.push_back(off);
+            off += kCanary;
+        }
         if (off > cap) throw ArgError("internal: workspace overflow");
         return r;
+    }
+    // after the last take(): write the canary blocks (stream-ordered, before the kernels of the call)
+    void arm(cudaStream_t s)
+    {
+        if (!debug) return;
+        for (size_t o : canaries) CK(cudaMemsetAsync(base + o, kCanaryByte, kCanary, s));
+        if (selftest && !canaries.empty()) CK(cudaMemsetAsync(base + canaries[0] + 7, 0, 1, s));
+    }
+    // after the call: synchronises; throws when a kernel wrote past the end of a piece
+    void check(cudaStream_t s, const char* what)
+    {
+        if (!debug) return;
+        CK(cudaStreamSynchronize(s));
+        std::vector<unsigned char> h(kCanary);
+        for (size_t i = 0; i < canaries.size(); ++i)
+        {
+            CK(cudaMemcpy(h.data(), base + canaries[i], kCanary, cudaMemcpyDeviceToHost));
+            for (unsigned char b : h)
+                if (b != kCanaryByte)
+                    throw CudaError(std::string(what) + ": workspace canary " + std::to_string(i) + " of " + std::to_string(canaries.size()) +
+                                    " overwritten (a kernel wrote past the end of a workspace piece)");
+        }
     }
 };
 static size_t pad256(size_t n) { return (n + 255) & ~(size_t)255; }
@@ -399,6 +437,13 @@ int rrtmgp_b200_profile_pair(double* pair_ms, long long* pair_launches)
 {
     if (pair_ms) *pair_ms = g_pair_ms;
     if (pair_launches) *pair_launches = g_pair_launches;
+    return 0;
+}
+
+int rrtmgp_b200_set_debug(rrtmgp_b200_gas_optics* g, int flags)
+{
+    if (!g || flags < 0 || flags > 3) return fail(RRTMGP_B200_E_ARG, "set_debug: handle and flags in 0..3");
+    g->ws.debug = (flags & 1) != 0; g->ws.selftest = (flags & 3) == 3;
     return 0;
 }
 
@@ -1119,6 +1164,7 @@ struct FusedJob
             CK(cudaMemsetAsync(a.flux_dn, 0, ncv * sizeof(Real), s));
             if (sw) CK(cudaMemsetAsync(a.flux_dir, 0, ncv * sizeof(Real), s));
         }
+        g->ws.arm(s);
     }
 
     static int auto_tile(rrtmgp_b200_gas_optics* g, int ncol, int nlay, int wave, int cpb)
@@ -1202,6 +1248,7 @@ struct FusedJob
         if (out->d_flux_net) launch_net<Real>(ncv, a.flux_dn, a.flux_up, out->d_flux_net, s);
         if (bnd && out->d_bnd_flux_net) launch_net<Real>(ncv * h.nbnd, a.bnd_dn, a.bnd_up, out->d_bnd_flux_net, s);
         if (out->d_heating_rate) launch_heating_rate<Real>(ncol, nlay, a.flux_up, a.flux_dn, cols->d_plev, out->d_heating_rate, s);
+        g->ws.check(s, sw ? "sw_fluxes" : "lw_fluxes");
     }
 };
 
@@ -1438,7 +1485,10 @@ void fluxes_host(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, co
         if (it.kind == 2)
             for (int b = 0; b < 2; ++b) CK(cudaMemcpyAsync(it.d[b], it.h, it.n2 * sizeof(Real), cudaMemcpyHostToDevice, P.h2d));
 
-    const bool concurrent = sides.size() == 2 && g_host_concurrent;
+    // both sides present, fp32: each chunk runs through the paired driver (longwave and shortwave CTAs co-resident, one
+    // stream); otherwise longwave on the caller's stream and shortwave on a side stream
+    const bool paired = sides.size() == 2 && sizeof(Real) == 4 && g_host_concurrent;
+    const bool concurrent = sides.size() == 2 && g_host_concurrent && !paired;
     int i = 0;
     for (int c0 = 0; c0 < ncol; c0 += chunk, ++i)
     {
@@ -1457,6 +1507,7 @@ void fluxes_host(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, co
         CK(cudaStreamWaitEvent(s, P.e_h2d[b], 0));
         if (i >= 2) CK(cudaStreamWaitEvent(s, P.e_d2h[b], 0));
         if (concurrent) { CK(cudaEventRecord(P.e_side[0], s)); CK(cudaStreamWaitEvent(P.side, P.e_side[0], 0)); }
+        rrtmgp_b200_columns dcs[2]; rrtmgp_b200_fluxes dfs[2];
         for (size_t k = 0; k < sides.size(); ++k)
         {
             Side& sd = sides[k];
@@ -1485,8 +1536,10 @@ void fluxes_host(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, co
             df.d_flux_up = O(so[k].up); df.d_flux_dn = O(so[k].dn); df.d_flux_net = O(so[k].net); df.d_flux_dn_dir = O(so[k].dir);
             df.d_bnd_flux_up = O(so[k].bup); df.d_bnd_flux_dn = O(so[k].bdn); df.d_bnd_flux_net = O(so[k].bnet);
             df.d_bnd_flux_dn_dir = O(so[k].bdir); df.d_heating_rate = O(so[k].hr);
-            fused_fluxes<Real>(sd.g, &dc, &df, (concurrent && k == 1) ? P.side : s, sd.sw);
+            dcs[k] = dc; dfs[k] = df;
+            if (!paired) fused_fluxes<Real>(sd.g, &dc, &df, (concurrent && k == 1) ? P.side : s, sd.sw);
         }
+        if (paired) fused_pair<Real>(sides[0].g, &dcs[0], &dfs[0], sides[1].g, &dcs[1], &dfs[1], s);
         if (concurrent) { CK(cudaEventRecord(P.e_side[1], P.side)); CK(cudaStreamWaitEvent(s, P.e_side[1], 0)); }
         CK(cudaEventRecord(P.e_comp[b], s));
         CK(cudaStreamWaitEvent(P.d2h, P.e_comp[b], 0));
@@ -1674,7 +1727,12 @@ struct rrtmgp_b200_shard_plan
 {
     long long ncol = 0; int world = 1, rank = 0;
     void* comm = nullptr; bool owns_comm = false;
+    Arena stage;                    // root: landing area of the peers' slabs (grow-only, allocated at the first gather)
 };
+// RB200_GATHER=direct: every level of a slab received straight into its place (no staging copy, but nlev x nfields small
+// messages per peer: measured 11.9 ms for 1.35 GB at N=2, 113 GB/s).  Default "staged": one message per field and peer into a
+// staging buffer on the root, then one strided device copy per (peer, field) into the reference layout.
+static const bool g_gather_direct = [] { const char* e = getenv("RB200_GATHER"); return e && e[0] == 'd'; }();
 
 extern "C" {
 
@@ -1764,7 +1822,52 @@ int rrtmgp_b200_gather_fluxes(rrtmgp_b200_shard_plan* p, int dtype, int nlev, in
         if (p->world == 1) return;
         if (!p->comm) throw ArgError("gather_fluxes: the plan has no communicator");
         NcclApi& n = nccl();
-        // every level of a part is one contiguous run of `count` columns on both sides: it goes straight into the
+        if (!g_gather_direct)
+        {
+            // staged: a peer's (count, nlev) slab of a field is ONE message; the root lays it out with a strided copy
+            char* base = nullptr;
+            std::vector<size_t> off((size_t)p->world * nfields, 0);
+            if (is_root)
+            {
+                size_t total = 0;
+                for (int r = 0; r < p->world; ++r)
+                {
+                    if (r == root) continue;
+                    long long first, count; span(r, first, count);
+                    for (int f = 0; f < nfields; ++f) { off[(size_t)r * nfields + f] = total; total += pad256((size_t)count * nlev * esz); }
+                }
+                p->stage.reserve(total + 256, s);       // grows (synchronising) only while the sizes still increase
+                base = p->stage.take<char>(total);
+            }
+            nccl_ck(n.GroupStart(), "ncclGroupStart");
+            if (is_root)
+            {
+                for (int r = 0; r < p->world; ++r)
+                {
+                    if (r == root) continue;
+                    long long first, count; span(r, first, count);
+                    if (count == 0) continue;
+                    for (int f = 0; f < nfields; ++f)
+                        nccl_ck(n.Recv(base + off[(size_t)r * nfields + f], (size_t)count * nlev, dt, r, p->comm, s), "ncclRecv");
+                }
+            }
+            else if (my_count > 0)
+                for (int f = 0; f < nfields; ++f)
+                    nccl_ck(n.Send(d_part_fields[f], (size_t)my_count * nlev, dt, root, p->comm, s), "ncclSend");
+            nccl_ck(n.GroupEnd(), "ncclGroupEnd");
+            if (is_root)
+                for (int r = 0; r < p->world; ++r)
+                {
+                    if (r == root) continue;
+                    long long first, count; span(r, first, count);
+                    if (count == 0) continue;
+                    for (int f = 0; f < nfields; ++f)
+                        CK(cudaMemcpy2DAsync((char*)d_full_fields[f] + (size_t)first * esz, (size_t)p->ncol * esz, base + off[(size_t)r * nfields + f],
+                                             (size_t)count * esz, (size_t)count * esz, (size_t)nlev, cudaMemcpyDeviceToDevice, s));
+                }
+            return;
+        }
+        // direct: every level of a part is one contiguous run of `count` columns on both sides: it goes straight into the
         // reference-layout (ncol, nlev) array of the root, no staging buffer and no reordering pass
         nccl_ck(n.GroupStart(), "ncclGroupStart");
         if (is_root)
