@@ -134,6 +134,16 @@ struct Arena
 };
 static size_t pad256(size_t n) { return (n + 255) & ~(size_t)255; }
 
+// stream-ordered temporary of a stage call, released on every exit path (an exception included)
+struct AsyncTemp
+{
+    char* p = nullptr; cudaStream_t s = nullptr;
+    explicit AsyncTemp(cudaStream_t s_) : s(s_) {}
+    AsyncTemp(const AsyncTemp&) = delete; AsyncTemp& operator=(const AsyncTemp&) = delete;
+    void alloc(size_t n) { if (n) CK(cudaMallocAsync((void**)&p, n, s)); }
+    ~AsyncTemp() { if (p) cudaFreeAsync(p, s); }
+};
+
 }  // namespace rb200
 
 using namespace rb200;
@@ -868,35 +878,40 @@ static int lw_solver_any(int dtype, int ncol, int nlay, int ngpt, int top_at_1, 
         if (ngpt < 1 || !tau || !lay_src || !lev_src || !sfc_emis || !sfc_src || !flux_up || !flux_dn) throw ArgError("lw_solver: null array");
         if (nmus < 1 || nmus > 4) throw ArgError("lw_solver: n_gauss_angles must be 1..4");   // src/Rte_lw.cpp:139-151
         if ((sfc_src_jac == nullptr) != (flux_up_jac == nullptr)) throw ArgError("lw_solver: Jacobian input and output go together");
+        if (dtype != RRTMGP_B200_F32 && dtype != RRTMGP_B200_F64) throw ArgError("bad dtype");      // before anything is allocated
         cudaStream_t s = (cudaStream_t)stream;
         const size_t esz = dtype == RRTMGP_B200_F32 ? 4 : 8;
         const size_t ncv = (size_t)ncol * (nlay + 1);
         void *up = flux_up, *dn = flux_dn;
-        char* tmp = nullptr;
+        AsyncTemp temp(s);
         const size_t fb = ncv * ngpt * esz;                       // one (ncol, nlay+1, ngpt) array
-        const size_t nfl = do_broadband ? 2 : 0, nwk = ssa ? 2 : 0;
-        if (nfl + nwk) CK(cudaMallocAsync((void**)&tmp, (nfl + nwk) * fb, s));
+        // the surface-temperature Jacobian is computed per g-point and summed in g-point order afterwards (deterministic; it
+        // used to be accumulated with atomicAdd across g-point blocks)
+        const size_t nfl = do_broadband ? 2 : 0, nwk = ssa ? 2 : 0, njac = flux_up_jac ? 1 : 0;
+        temp.alloc((nfl + nwk + njac) * fb);
+        char* const tmp = temp.p;
+        void* const jac_gpt = njac ? tmp + (nfl + nwk) * fb : nullptr;
         if (do_broadband) { up = tmp; dn = tmp + fb; }
         void* work2 = tmp + nfl * fb;
-        if (flux_up_jac) CK(cudaMemsetAsync(flux_up_jac, 0, ncv * esz, s));
         if (ssa)
         {
             DISPATCH(dtype,
-                launch_lw_solver_rescl<float>(ncol, nlay, ngpt, top_at_1, nmus, tau, ssa, g, lay_src, lev_src, sfc_emis, sfc_src, inc_flux, up, dn, sfc_src_jac, flux_up_jac, work2, s),
-                launch_lw_solver_rescl<double>(ncol, nlay, ngpt, top_at_1, nmus, tau, ssa, g, lay_src, lev_src, sfc_emis, sfc_src, inc_flux, up, dn, sfc_src_jac, flux_up_jac, work2, s));
+                launch_lw_solver_rescl<float>(ncol, nlay, ngpt, top_at_1, nmus, tau, ssa, g, lay_src, lev_src, sfc_emis, sfc_src, inc_flux, up, dn, sfc_src_jac, jac_gpt, work2, s),
+                launch_lw_solver_rescl<double>(ncol, nlay, ngpt, top_at_1, nmus, tau, ssa, g, lay_src, lev_src, sfc_emis, sfc_src, inc_flux, up, dn, sfc_src_jac, jac_gpt, work2, s));
         }
         else
         {
             DISPATCH(dtype,
-                launch_lw_solver<float>(ncol, nlay, ngpt, top_at_1, nmus, tau, lay_src, lev_src, sfc_emis, sfc_src, inc_flux, up, dn, sfc_src_jac, flux_up_jac, s),
-                launch_lw_solver<double>(ncol, nlay, ngpt, top_at_1, nmus, tau, lay_src, lev_src, sfc_emis, sfc_src, inc_flux, up, dn, sfc_src_jac, flux_up_jac, s));
+                launch_lw_solver<float>(ncol, nlay, ngpt, top_at_1, nmus, tau, lay_src, lev_src, sfc_emis, sfc_src, inc_flux, up, dn, sfc_src_jac, jac_gpt, s),
+                launch_lw_solver<double>(ncol, nlay, ngpt, top_at_1, nmus, tau, lay_src, lev_src, sfc_emis, sfc_src, inc_flux, up, dn, sfc_src_jac, jac_gpt, s));
         }
+        if (flux_up_jac)
+        { DISPATCH(dtype, launch_sum_broadband<float>(ncol, nlay + 1, ngpt, jac_gpt, flux_up_jac, s), launch_sum_broadband<double>(ncol, nlay + 1, ngpt, jac_gpt, flux_up_jac, s)); }
         if (do_broadband)
         {
             DISPATCH(dtype, (launch_sum_broadband<float>(ncol, nlay + 1, ngpt, up, flux_up, s), launch_sum_broadband<float>(ncol, nlay + 1, ngpt, dn, flux_dn, s)),
                             (launch_sum_broadband<double>(ncol, nlay + 1, ngpt, up, flux_up, s), launch_sum_broadband<double>(ncol, nlay + 1, ngpt, dn, flux_dn, s)));
         }
-        if (tmp) CK(cudaFreeAsync(tmp, s));
     });
 }
 
@@ -928,12 +943,14 @@ static int sw_solver_any(int dtype, int ncol, int nlay, int ngpt, int top_at_1, 
         check_dims(ncol, nlay);
         if (ngpt < 1 || !tau || !ssa || !g || !mu0 || !alb_dir || !alb_dif || !inc_dir || !flux_up || !flux_dn || !flux_dir)
             throw ArgError("sw_solver: null array");
+        if (dtype != RRTMGP_B200_F32 && dtype != RRTMGP_B200_F64) throw ArgError("bad dtype");      // before anything is allocated
         cudaStream_t s = (cudaStream_t)stream;
         const size_t esz = dtype == RRTMGP_B200_F32 ? 4 : 8;
         const size_t ncv = (size_t)ncol * (nlay + 1), ncl = (size_t)ncol * nlay;
-        char* tmp = nullptr;
+        AsyncTemp temp(s);
         const size_t wbytes = 4 * ncl * ngpt * esz, fbytes = ncv * ngpt * esz;
-        CK(cudaMallocAsync((void**)&tmp, wbytes + (do_broadband ? 3 * fbytes : 0), s));
+        temp.alloc(wbytes + (do_broadband ? 3 * fbytes : 0));
+        char* const tmp = temp.p;
         void *up = flux_up, *dn = flux_dn, *dr = flux_dir;
         if (do_broadband) { up = tmp + wbytes; dn = tmp + wbytes + fbytes; dr = tmp + wbytes + 2 * fbytes; }
         DISPATCH(dtype,
@@ -945,7 +962,6 @@ static int sw_solver_any(int dtype, int ncol, int nlay, int ngpt, int top_at_1, 
             for (int k = 0; k < 3; ++k)
             { DISPATCH(dtype, launch_sum_broadband<float>(ncol, nlay + 1, ngpt, src[k], dst[k], s), launch_sum_broadband<double>(ncol, nlay + 1, ngpt, src[k], dst[k], s)); }
         }
-        CK(cudaFreeAsync(tmp, s));
     });
 }
 

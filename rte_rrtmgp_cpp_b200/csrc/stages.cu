@@ -19,7 +19,10 @@ __device__ __forceinline__ void cloud_from_table(Real cwp, Real re, int nsteps, 
     if (cwp > (Real)0)
     {
         const Real x = (re - offset) / step;
-        const int index = min((int)x + 1, nsteps - 1);
+        // the reference clamps from above only (src/Cloud_optics.cpp:86): a particle size below the table's lower bound
+        // (x < 0: rel < radliq_lwr, or dei = 0 in partly specified cells) would read ext[-1...]: clamp from below too.
+        // In-range sizes (x >= 0) give index >= 1 anyway, so results inside the table are unchanged.
+        const int index = max(1, min((int)x + 1, nsteps - 1));
         const Real fint = x - (Real)(index - 1);
         tau = cwp * (ext[index - 1] + fint * (ext[index] - ext[index - 1]));
         taussa = tau * (ssa[index - 1] + fint * (ssa[index] - ssa[index - 1]));
@@ -298,7 +301,7 @@ lw_solver_kernel(int ncol, int nlay, int ngpt, int top_at_1, int nmus,
         radn = radn * ((Real)1 - emis) + emis * ssrc;
         Real jac = sfc_src_jac ? emis * sfc_src_jac[cg] : (Real)0;
         { const Real v = piw * radn; Real* o = up + level(nlay); *o = imu == 0 ? v : *o + v; }
-        if (flux_up_jac) atomicAdd(flux_up_jac + c + level(nlay), piw * jac);
+        if (flux_up_jac) { const Real v = piw * jac; Real* o = flux_up_jac + ncv * g + c + level(nlay); *o = imu == 0 ? v : *o + v; }
         for (int k = nlay - 1; k >= 0; --k)
         {
             const size_t il = layer(k);
@@ -306,7 +309,7 @@ lw_solver_kernel(int ncol, int nlay, int ngpt, int top_at_1, int nmus,
             lw_layer<Real>(tg[il] * D, lay[il], lev[level(k)], lev[level(k + 1)], t, s_up, s_dn);
             radn = t * radn + s_up;
             const Real v = piw * radn; Real* o = up + level(k); *o = imu == 0 ? v : *o + v;
-            if (flux_up_jac) { jac = t * jac; atomicAdd(flux_up_jac + c + level(k), piw * jac); }
+            if (flux_up_jac) { jac = t * jac; const Real v = piw * jac; Real* o = flux_up_jac + ncv * g + c + level(k); *o = imu == 0 ? v : *o + v; }
         }
     }
 }
@@ -384,14 +387,14 @@ lw_solver_rescl_kernel(int ncol, int nlay, int ngpt, int top_at_1, int nmus,
         radn = radn * ((Real)1 - emis) + emis * ssrc;
         ru[level(nlay)] = radn;
         Real jac = sfc_src_jac ? emis * sfc_src_jac[cg] : (Real)0;
-        if (flux_up_jac) atomicAdd(flux_up_jac + c + level(nlay), piw * jac);
+        if (flux_up_jac) { const Real v = piw * jac; Real* o = flux_up_jac + ncv * g + c + level(nlay); *o = imu == 0 ? v : *o + v; }
         for (int k = nlay - 1; k >= 0; --k)
         {
             cell(k, D, t, s_up, s_dn, An, Cn);
             const Real adj = Cn * (An * rd[level(k)] - t * s_dn - s_up);          // down-welling at the layer top
             radn = t * radn + s_up + adj;
             ru[level(k)] = radn;
-            if (flux_up_jac) { jac = t * jac; atomicAdd(flux_up_jac + c + level(k), piw * jac); }
+            if (flux_up_jac) { jac = t * jac; const Real v = piw * jac; Real* o = flux_up_jac + ncv * g + c + level(k); *o = imu == 0 ? v : *o + v; }
         }
         radn = rd[level(0)];
         for (int k = 0; k < nlay; ++k)

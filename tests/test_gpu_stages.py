@@ -333,3 +333,33 @@ def test_rte_sw_height_dependent_mu0(dtype, top_at_1):
     assert torch.equal(up1.t, up2.t) and torch.equal(dn1.t, dn2.t) and torch.equal(dr1.t, dr2.t)
     with pytest.raises(RuntimeError, match="mu0 must be"):
         api.Rte_sw_gpu.rte_sw(op, top_at_1, A.from_numpy(const[:, :-1], dtype), *args, up2, dn2, dr2)
+
+
+def test_cloud_particle_size_below_the_table_does_not_read_before_it():
+    """Liquid radius below radliq_lwr / ice diameter 0 in a cloudy cell: the reference clamps the LUT index from above only
+    (src/Cloud_optics.cpp:86) and would read before the table; here the index is clamped to the first interval, i.e. the
+    value is the linear extrapolation of the first two table entries (and equals the oracle for every in-range cell)."""
+    dtype = torch.float64
+    lut = synthetic_cloud_lut("lw")
+    atm = allsky_atmosphere(6, 10, random_clouds=True)
+    atm.lwp[:] = 20.0; atm.iwp[:] = 0.0
+    atm.rel[:] = lut.radliq_lwr + 3.3                      # in range everywhere ...
+    step0 = (lut.radliq_upr - lut.radliq_lwr) / (lut.lut_extliq.shape[1] - 1)
+    atm.rel[2, 4] = lut.radliq_lwr - 2.5 * step0           # ... except one cell 2.5 table steps below it (index -1 unclamped)
+    atm.dei[:] = 0.0                                       # no ice water: the ice branch must not matter
+    cols = api.DeviceColumns(atm, dtype)
+    co = api.Cloud_optics_gpu(lut, dtype)
+    cl = api.Optical_props_1scl_gpu(atm.ncol, atm.nlay, co, dtype)
+    co.cloud_optics(cols.lwp, cols.iwp, cols.rel, cols.dei, cl)
+    got = cl.tau.numpy()
+    assert np.isfinite(got).all()
+    want = O.CloudOptics(lut).cloud_optics_1scl(atm.lwp, atm.iwp, atm.rel, atm.dei)
+    mask = np.ones(got.shape[:2], bool); mask[2, 4] = False
+    assert np.max(np.abs(got[mask] - want[mask])) < 1e-12 * max(1.0, want[mask].max())
+    nl = lut.lut_extliq.shape[1]
+    step = (lut.radliq_upr - lut.radliq_lwr) / (nl - 1)
+    x = (atm.rel[2, 4] - lut.radliq_lwr) / step            # negative
+    for b in range(lut.nbnd):
+        ext = lut.lut_extliq[b, 0] + x * (lut.lut_extliq[b, 1] - lut.lut_extliq[b, 0])
+        ssa = lut.lut_ssaliq[b, 0] + x * (lut.lut_ssaliq[b, 1] - lut.lut_ssaliq[b, 0])
+        assert abs(got[2, 4, b] - 20.0 * ext * (1.0 - ssa)) < 1e-10 * max(1.0, abs(got[2, 4, b]))
