@@ -61,6 +61,7 @@ def parse():
     ap.add_argument("--cloudy", action="store_true", help="all-sky: cloud optics LUT + delta scaling")
     ap.add_argument("--reduced", action="store_true", help="reduced g-point sets LW 128 / SW 112 (BASELINE config 5)")
     ap.add_argument("--parts", type=int, default=1, help="N > 1: process the shard in this many column blocks, each gathered on a side stream")
+    ap.add_argument("--nccl-gather", action="store_true", help="N > 1: rrtmgp_b200_gather_fluxes without the peer-memory registration")
     ap.add_argument("--torch-gather", action="store_true", help="N > 1: gather with torch.distributed.gather instead of rrtmgp_b200_gather_fluxes")
     ap.add_argument("--tile", type=int, default=0, help="columns per tile of the fused path (0 = auto)")
     ap.add_argument("--chunk", type=int, default=0, help="columns per chunk of the host-buffer pipeline (0 = auto)")
@@ -329,6 +330,7 @@ def run_b200(args):
     # what rank 0 assembles at N > 1: up / down (/ direct) travel, the two net fluxes are formed on the root (dn - up)
     sent = [("lw", "flux_up"), ("lw", "flux_dn"), ("sw", "flux_up"), ("sw", "flux_dn"), ("sw", "flux_dn_dir")]
     plan = full = net = None
+    gather_mode = None
     gather_buf = None
     side = torch.cuda.Stream() if world > 1 else None
     ev_g = []
@@ -337,6 +339,11 @@ def run_b200(args):
         if rank == 0:
             full = [torch.empty(nlev * args.ncol, device="cuda", dtype=dtype) for _ in sent]
             net = [torch.empty(nlev * args.ncol, device="cuda", dtype=dtype) for _ in range(2)]
+        # peer-memory mode: every rank writes its slabs straight into rank 0's arrays over NVLink (CUDA IPC); falls back to the
+        # NCCL path when the arrays cannot be mapped
+        gather_mode = "nccl (one message per field and peer, layout copies on the root)"
+        if not args.nccl_gather and plan.register(full, len(sent)) == len(sent):
+            gather_mode = "peer-memory writes over NVLink (CUDA IPC) + one-element completion messages"
     L = capi.lib()
     code = capi.F32 if args.dtype == "f32" else capi.F64
 
@@ -529,7 +536,7 @@ def run_b200(args):
                                f"{'all-sky (cloud LUT + delta scaling)' if args.cloudy else 'clear-sky'}, fused path"
                                + (", longwave + shortwave CTAs co-resident (rrtmgp_b200_lwsw_fluxes)" if paired else "")
                                + (f", column-sharded over {world} GPUs, flux gather to rank 0 "
-                                  + ("(torch.distributed.gather)" if args.torch_gather else "(rrtmgp_b200_gather_fluxes: grouped ncclSend/Recv)") if world > 1 else ""),
+                                  + ("(torch.distributed.gather)" if args.torch_gather else f"(rrtmgp_b200_gather_fluxes: {gather_mode})") if world > 1 else ""),
                    "name": args.config, "ncol": args.ncol, "nlay": nlay, "ngpt_lw": g_lw, "ngpt_sw": g_sw, "calls_per_step": len(calls),
                    "distinct_columns": min(NBASE, ncol), "l2_policy": "inputs and scratch larger than L2 (GBs per step)" if args.ncol >= 65536 else
                                        "inputs smaller than L2 (a small-call workload by definition; nothing is flushed between calls)",

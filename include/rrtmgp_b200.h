@@ -423,6 +423,17 @@ int rrtmgp_b200_shard_plan_bounds(const rrtmgp_b200_shard_plan* plan, int rank, 
  * nlev x nfields small messages per peer: measured 3x slower).  The root's own columns are one strided device copy per field.
  * Stream-ordered, returns without synchronising (the staging buffer grows, synchronising, only while sizes still increase).
  * Calling it per block on a side stream overlaps the gather with the next block's kernels. */
+/* Peer-memory mode of the gather (optional, collective, blocking; call once at set-up from every rank with the same nfields and
+ * root).  The root hands the CUDA-IPC handles of its whole-domain arrays to the other processes, which map them; from then
+ * on rrtmgp_b200_gather_fluxes with the same root / nfields / arrays makes every rank WRITE its slab straight into the root's
+ * reference-layout arrays over NVLink (one strided peer-to-peer copy per field, all ranks at once) and signal completion with a
+ * one-element message: no staging buffer and no layout copy on the root.  All or nothing: when any rank cannot map the arrays
+ * (no peer access, memory not from cudaMalloc) nothing is registered and the gather keeps the NCCL path; returns OK either
+ * way — rrtmgp_b200_shard_plan_registered tells (number of registered fields, 0 = none).  d_full_fields is read on the root
+ * only; the arrays must stay allocated while registered; registering again replaces the registration. */
+int rrtmgp_b200_shard_plan_register(rrtmgp_b200_shard_plan* plan, int nfields, void* const* d_full_fields /*HOST array, root only*/,
+                                    int root, void* stream);
+int rrtmgp_b200_shard_plan_registered(const rrtmgp_b200_shard_plan* plan);
 int rrtmgp_b200_gather_fluxes(rrtmgp_b200_shard_plan* plan, int dtype, int nlev, int nfields,
                               const void* const* d_part_fields /*HOST array of device pointers*/,
                               void* const* d_full_fields /*HOST array of device pointers, root only*/,

@@ -102,6 +102,8 @@ SYMBOLS = {
     "rrtmgp_b200_shard_plan_create": (i, [C.c_longlong, i, i, vp, vp, C.POINTER(vp)]),
     "rrtmgp_b200_shard_plan_destroy": (None, [vp]),
     "rrtmgp_b200_shard_plan_bounds": (i, [vp, i, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),
+    "rrtmgp_b200_shard_plan_register": (i, [vp, i, C.POINTER(vp), i, vp]),
+    "rrtmgp_b200_shard_plan_registered": (i, [vp]),
     "rrtmgp_b200_gather_fluxes": (i, [vp, i, i, i, C.POINTER(vp), C.POINTER(vp), i, i, i, vp]),
     "rrtmgp_b200_profile": (i, [i, C.POINTER(d), C.POINTER(C.c_longlong), C.POINTER(d), C.POINTER(C.c_longlong)]),
 }

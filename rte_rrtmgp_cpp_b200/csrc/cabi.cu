@@ -1744,6 +1744,11 @@ struct rrtmgp_b200_shard_plan
     long long ncol = 0; int world = 1, rank = 0;
     void* comm = nullptr; bool owns_comm = false;
     Arena stage;                    // root: landing area of the peers' slabs (grow-only, allocated at the first gather)
+    // peer-memory mode (rrtmgp_b200_shard_plan_register): the root's whole-domain arrays mapped into this process
+    int reg_root = -1; int reg_nfields = 0;
+    std::vector<void*> reg_full;    // root: the registered arrays; peers: their addresses in THIS process (CUDA IPC mappings)
+    std::vector<void*> ipc_opened;  // peers: mappings to close
+    void* signal = nullptr;         // one device word for the completion messages
 };
 // RB200_GATHER=direct: every level of a slab received straight into its place (no staging copy, but nlev x nfields small
 // messages per peer: measured 11.9 ms for 1.35 GB at N=2, 113 GB/s).  Default "staged": one message per field and peer into a
@@ -1794,6 +1799,8 @@ int rrtmgp_b200_shard_plan_create(long long ncol, int world, int rank, const voi
 void rrtmgp_b200_shard_plan_destroy(rrtmgp_b200_shard_plan* p)
 {
     if (!p) return;
+    for (void* m : p->ipc_opened) cudaIpcCloseMemHandle(m);
+    if (p->signal) cudaFree(p->signal);
     if (p->owns_comm && p->comm) { try { nccl().CommDestroy(p->comm); } catch (...) {} }
     delete p;
 }
@@ -1806,6 +1813,116 @@ int rrtmgp_b200_shard_plan_bounds(const rrtmgp_b200_shard_plan* p, int rank, lon
     shard_range(p->ncol, p->world, rank, *c0, *c1);
     return 0;
 }
+
+// base address and size of the allocation a device pointer lies in (driver entry point resolved at run time: the library
+// does not link libcuda)
+static bool allocation_base(const void* ptr, char** base)
+{
+    typedef int (*Fn)(unsigned long long*, size_t*, unsigned long long);
+    static Fn fn = [] { void* h = dlopen("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL); return h ? (Fn)dlsym(h, "cuMemGetAddressRange_v2") : (Fn) nullptr; }();
+    unsigned long long b = 0; size_t n = 0;
+    if (!fn || fn(&b, &n, (unsigned long long)(uintptr_t)ptr) != 0) return false;
+    *base = (char*)(uintptr_t)b;
+    return true;
+}
+
+int rrtmgp_b200_shard_plan_register(rrtmgp_b200_shard_plan* p, int nfields, void* const* d_full_fields, int root, void* stream)
+{
+    return guarded([&] {
+        if (!p || nfields < 1 || nfields > 64 || root < 0 || root >= p->world) throw ArgError("shard_plan_register: bad argument");
+        const bool is_root = p->rank == root;
+        if (is_root && !d_full_fields) throw ArgError("shard_plan_register: the root needs the whole-domain arrays");
+        for (void* m : p->ipc_opened) cudaIpcCloseMemHandle(m);
+        p->ipc_opened.clear(); p->reg_full.clear(); p->reg_root = -1; p->reg_nfields = 0;
+        if (p->world == 1) return;
+        if (!p->comm) throw ArgError("shard_plan_register: the plan has no communicator");
+        NcclApi& n = nccl();
+        cudaStream_t s = (cudaStream_t)stream;
+        struct Entry { cudaIpcMemHandle_t h; unsigned long long offset; int ok; int pad; };
+        std::vector<Entry> host((size_t)nfields);
+        Entry* dev = nullptr;
+        CK(cudaMalloc((void**)&dev, sizeof(Entry) * nfields));
+        int* dflag = nullptr;
+        CK(cudaMalloc((void**)&dflag, sizeof(int) * (size_t)(p->world + 1)));
+        if (!p->signal) CK(cudaMalloc(&p->signal, 256));
+        auto cleanup = [&] { cudaFree(dev); cudaFree(dflag); };
+        try
+        {
+            int ok = 1;
+            if (is_root)
+            {
+                for (int f = 0; f < nfields; ++f)
+                {
+                    char* base = nullptr;
+                    host[f].ok = d_full_fields[f] && allocation_base(d_full_fields[f], &base) &&
+                                 cudaIpcGetMemHandle(&host[f].h, base) == cudaSuccess;
+                    host[f].offset = host[f].ok ? (unsigned long long)((char*)d_full_fields[f] - base) : 0;
+                    if (!host[f].ok) { ok = 0; cudaGetLastError(); }
+                }
+                CK(cudaMemcpyAsync(dev, host.data(), sizeof(Entry) * nfields, cudaMemcpyHostToDevice, s));
+            }
+            // 1. handles root -> peers
+            nccl_ck(n.GroupStart(), "ncclGroupStart");
+            if (is_root) { for (int r = 0; r < p->world; ++r) if (r != root) nccl_ck(n.Send(dev, sizeof(Entry) * nfields, 1 /*ncclUint8*/, r, p->comm, s), "ncclSend"); }
+            else nccl_ck(n.Recv(dev, sizeof(Entry) * nfields, 1, root, p->comm, s), "ncclRecv");
+            nccl_ck(n.GroupEnd(), "ncclGroupEnd");
+            CK(cudaStreamSynchronize(s));
+            std::vector<void*> mapped((size_t)nfields, nullptr);
+            if (!is_root)
+            {
+                CK(cudaMemcpy(host.data(), dev, sizeof(Entry) * nfields, cudaMemcpyDeviceToHost));
+                std::vector<std::pair<cudaIpcMemHandle_t, void*>> seen;        // arrays may share an allocation: open it once
+                for (int f = 0; f < nfields && ok; ++f)
+                {
+                    if (!host[f].ok) { ok = 0; break; }
+                    void* m = nullptr;
+                    for (auto& sv : seen) if (std::memcmp(&sv.first, &host[f].h, sizeof(cudaIpcMemHandle_t)) == 0) m = sv.second;
+                    if (!m)
+                    {
+                        if (cudaIpcOpenMemHandle(&m, host[f].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = 0; break; }
+                        seen.push_back({host[f].h, m}); p->ipc_opened.push_back(m);
+                    }
+                    mapped[f] = (char*)m + host[f].offset;
+                }
+            }
+            // 2. every rank's verdict -> root; 3. the decision root -> peers (all or nothing)
+            CK(cudaMemcpyAsync(dflag + p->rank, &ok, sizeof(int), cudaMemcpyHostToDevice, s));
+            nccl_ck(n.GroupStart(), "ncclGroupStart");
+            if (is_root) { for (int r = 0; r < p->world; ++r) if (r != root) nccl_ck(n.Recv(dflag + r, 1, 2 /*ncclInt32*/, r, p->comm, s), "ncclRecv"); }
+            else nccl_ck(n.Send(dflag + p->rank, 1, 2, root, p->comm, s), "ncclSend");
+            nccl_ck(n.GroupEnd(), "ncclGroupEnd");
+            CK(cudaStreamSynchronize(s));
+            int all = ok;
+            if (is_root)
+            {
+                std::vector<int> flags((size_t)p->world);
+                CK(cudaMemcpy(flags.data(), dflag, sizeof(int) * p->world, cudaMemcpyDeviceToHost));
+                for (int r = 0; r < p->world; ++r) if (r != root && !flags[r]) all = 0;
+                CK(cudaMemcpyAsync(dflag + p->world, &all, sizeof(int), cudaMemcpyHostToDevice, s));
+            }
+            nccl_ck(n.GroupStart(), "ncclGroupStart");
+            if (is_root) { for (int r = 0; r < p->world; ++r) if (r != root) nccl_ck(n.Send(dflag + p->world, 1, 2, r, p->comm, s), "ncclSend"); }
+            else nccl_ck(n.Recv(dflag + p->world, 1, 2, root, p->comm, s), "ncclRecv");
+            nccl_ck(n.GroupEnd(), "ncclGroupEnd");
+            CK(cudaStreamSynchronize(s));
+            if (!is_root) CK(cudaMemcpy(&all, dflag + p->world, sizeof(int), cudaMemcpyDeviceToHost));
+            if (all)
+            {
+                p->reg_root = root; p->reg_nfields = nfields;
+                if (is_root) p->reg_full.assign(d_full_fields, d_full_fields + nfields); else p->reg_full = mapped;
+            }
+            else
+            {
+                for (void* m : p->ipc_opened) cudaIpcCloseMemHandle(m);
+                p->ipc_opened.clear();
+            }
+        }
+        catch (...) { cleanup(); throw; }
+        cleanup();
+    });
+}
+
+int rrtmgp_b200_shard_plan_registered(const rrtmgp_b200_shard_plan* p) { return p && p->reg_root >= 0 ? p->reg_nfields : 0; }
 
 int rrtmgp_b200_gather_fluxes(rrtmgp_b200_shard_plan* p, int dtype, int nlev, int nfields, const void* const* d_part_fields,
                               void* const* d_full_fields, int part, int nparts, int root, void* stream)
@@ -1838,6 +1955,30 @@ int rrtmgp_b200_gather_fluxes(rrtmgp_b200_shard_plan* p, int dtype, int nlev, in
         if (p->world == 1) return;
         if (!p->comm) throw ArgError("gather_fluxes: the plan has no communicator");
         NcclApi& n = nccl();
+        if (p->reg_root == root && p->reg_nfields == nfields)
+        {
+            // peer-memory mode: every rank WRITES its slab into the root's arrays over NVLink (one strided peer copy per
+            // field, straight into the reference layout: no staging buffer, no layout copy on the root, all peers at once),
+            // then tells the root with a one-element message that its columns have landed
+            if (is_root)
+                for (int f = 0; f < nfields; ++f)
+                    if (d_full_fields[f] != p->reg_full[f]) throw ArgError("gather_fluxes: the whole-domain arrays differ from the registered ones");
+            // "clear to write": the root's stream has reached this gather, i.e. everything it enqueued before (the consumers
+            // of the previous result) is ordered ahead; a peer's copies wait for it
+            nccl_ck(n.GroupStart(), "ncclGroupStart");
+            if (is_root) { for (int r = 0; r < p->world; ++r) if (r != root) nccl_ck(n.Send(p->signal, 1, 2, r, p->comm, s), "ncclSend"); }
+            else nccl_ck(n.Recv((int*)p->signal + 40, 1, 2, root, p->comm, s), "ncclRecv");
+            nccl_ck(n.GroupEnd(), "ncclGroupEnd");
+            if (!is_root && my_count > 0)
+                for (int f = 0; f < nfields; ++f)
+                    CK(cudaMemcpy2DAsync((char*)p->reg_full[f] + (size_t)my_first * esz, (size_t)p->ncol * esz, d_part_fields[f],
+                                         (size_t)my_count * esz, (size_t)my_count * esz, (size_t)nlev, cudaMemcpyDeviceToDevice, s));
+            nccl_ck(n.GroupStart(), "ncclGroupStart");
+            if (is_root) { for (int r = 0; r < p->world; ++r) if (r != root) nccl_ck(n.Recv((int*)p->signal + 1 + (r % 32), 1, 2, r, p->comm, s), "ncclRecv"); }
+            else nccl_ck(n.Send(p->signal, 1, 2 /*ncclInt32*/, root, p->comm, s), "ncclSend");
+            nccl_ck(n.GroupEnd(), "ncclGroupEnd");
+            return;
+        }
         if (!g_gather_direct)
         {
             // staged: a peer's (count, nlev) slab of a field is ONE message; the root lays it out with a strided copy

@@ -104,6 +104,15 @@ class ShardPlan:
         self._capi.check(self.L.rrtmgp_b200_shard_plan_bounds(self.h, int(rank), C.byref(a), C.byref(b)))
         return a.value, b.value
 
+    def register(self, full_fields: Optional[Sequence[torch.Tensor]], nfields: int, root: int = 0) -> int:
+        """Collective: peer-memory mode of gather() for these whole-domain arrays of the root (rrtmgp_b200_shard_plan_register).
+        Returns the number of registered fields (0: peer mapping unavailable, gather() keeps the NCCL path)."""
+        C = self._C
+        dst = (C.c_void_p * nfields)(*[f.data_ptr() for f in full_fields]) if full_fields is not None else None
+        s = torch.cuda.current_stream()
+        self._capi.check(self.L.rrtmgp_b200_shard_plan_register(self.h, int(nfields), dst, int(root), C.c_void_p(s.cuda_stream)))
+        return int(self.L.rrtmgp_b200_shard_plan_registered(self.h))
+
     def gather(self, part_fields: Sequence[torch.Tensor], full_fields: Optional[Sequence[torch.Tensor]], nlev: int,
                part: int = 0, nparts: int = 1, root: int = 0, stream=None) -> None:
         """part_fields[f]: this rank's (count, nlev) column-major slab of field f; full_fields[f] on the root: (ncol, nlev)."""

@@ -32,6 +32,10 @@ def main():
     full = [torch.full((nlev * ncol,), float("nan"), device="cuda", dtype=dtype) for _ in names] if rank == 0 else None
     side = torch.cuda.Stream()
     keep = []
+    mode = os.environ.get("RB200_TEST_GATHER", "nccl")
+    if mode == "p2p":       # peer-memory mode: every rank writes into rank 0's arrays over NVLink
+        nreg = plan.register(full, len(names))
+        assert nreg == len(names), f"peer-memory registration failed on rank {rank}: {nreg}"
     for part in range(nparts):
         p0, p1 = shard_bounds(c1 - c0, nparts, part)
         o_lw, o_sw = api.solve_pair(lw, sw, api.DeviceColumns(atm.subset(c0 + p0, c0 + p1), dtype))
