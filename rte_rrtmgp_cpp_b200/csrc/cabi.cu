@@ -1414,10 +1414,36 @@ void fluxes_host(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, co
                 chunk = std::max(chunk, g->tile_cols > 0 ? g->tile_cols : 4 * wave * cpb);   // finer than a tile: shorter pipeline ramps
             }
     chunk = std::min(chunk, ncol);
-    if (chunk_cols <= 0)
+    // The schedule of chunks.  Explicit chunk_cols: equal chunks of that size.  Automatic: a ramp.  The pipeline's exposed time
+    // is the upload of the FIRST chunk and the download of the LAST one (the rest hides behind the kernels as long as a chunk's
+    // copies are shorter than its neighbour's kernels), and every band launch of a chunk ends in a partly empty wave, so
+    // chunks should be large.  Hence 1, 2, 4 waves of CTAs per role at both ends and equal chunks of up to 8 waves between
+    // (copies of a chunk take ~0.3 of its kernels' time, so a chunk twice its neighbour still hides).  Measured: two equal
+    // chunks exposed 18 ms of an 87 ms step at 8 GPUs (131072 columns per rank); equal 4-wave chunks cost 6 % in tails at 1 GPU.
+    std::vector<std::pair<int, int>> sched;      // (first column, columns)
     {
-        const int nchunks = (ncol + chunk - 1) / chunk;          // equal chunks, whole CTAs
-        chunk = std::min((((ncol + nchunks - 1) / nchunks + 31) / 32) * 32, ncol);
+        std::vector<int> left, right;
+        int remaining = ncol;
+        const bool ramp = chunk_cols <= 0 && !(glw && glw->tile_cols > 0) && !(gsw && gsw->tile_cols > 0);   // a set tile size is the chunk size
+        if (ramp)
+        {
+            rrtmgp_b200_gas_optics* g = glw ? glw : gsw;
+            const int cpb = FUSED_THREADS / (g->h.gw / 4);
+            const int wave = std::max(g->h.is_lw ? lw_blocks_per_wave<Real>(g->h.gw) : sw_blocks_per_wave<Real>(g->h.gw), 1);
+            const int W = wave * cpb;
+            chunk = 8 * W;
+            for (int size = W; size < chunk && remaining > 3 * size; size *= 2) { left.push_back(size); right.push_back(size); remaining -= 2 * size; }
+        }
+        const int nmid = std::max((remaining + chunk - 1) / chunk, 1);
+        const int mid = std::min((((remaining + nmid - 1) / nmid + 31) / 32) * 32, remaining);   // equal chunks, whole CTAs
+        int c0 = 0;
+        for (int n : left) { sched.push_back({c0, n}); c0 += n; }
+        for (int end = c0 + remaining; c0 < end; c0 += mid) sched.push_back({c0, std::min(mid, end - c0)});
+        c0 = ncol;
+        for (int n : right) c0 -= n;
+        for (auto it = right.rbegin(); it != right.rend(); ++it) { sched.push_back({c0, *it}); c0 += *it; }
+        chunk = mid;
+        for (auto& sc : sched) chunk = std::max(chunk, sc.second);
     }
 
     // inputs, de-duplicated by host address (LW and SW normally share play/plev/tlay/vmr/col_dry)
@@ -1505,10 +1531,9 @@ void fluxes_host(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, co
     // stream); otherwise longwave on the caller's stream and shortwave on a side stream
     const bool paired = sides.size() == 2 && sizeof(Real) == 4 && g_host_concurrent;
     const bool concurrent = sides.size() == 2 && g_host_concurrent && !paired;
-    int i = 0;
-    for (int c0 = 0; c0 < ncol; c0 += chunk, ++i)
+    for (int i = 0; i < (int)sched.size(); ++i)
     {
-        const int nc = std::min(chunk, ncol - c0), b = i & 1;
+        const int c0 = sched[i].first, nc = sched[i].second, b = i & 1;
         // H2D of chunk i once the kernels of chunk i-2 have drained this buffer
         if (i >= 2) CK(cudaStreamWaitEvent(P.h2d, P.e_comp[b], 0));
         for (auto& it : items)
