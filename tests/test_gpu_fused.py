@@ -237,3 +237,51 @@ def test_paired_lw_sw_call_is_bit_identical_to_the_two_calls(case, dtype):
     for k in ref_sw:
         assert np.array_equal(out_sw[k].numpy(), ref_sw[k]), ("sw", k)
     assert np.abs(ref_lw["flux_up"]).max() > 10 and np.abs(ref_sw["flux_dn"]).max() > 10
+
+
+def test_many_waves_recycle_strips_and_keep_columns_independent():
+    """A domain of many waves of CTAs (more CTAs per band launch than scratch strips: strips are claimed, released and claimed
+    again by later CTAs) built from a small set of distinct columns repeated periodically.  Size-independent properties: every
+    period is bit-identical to the first, and the first equals the same columns computed alone — whatever strip a CTA got,
+    whichever wave it ran in, whichever tile it fell into.  Both the paired call and the two single calls."""
+    dtype = torch.float32
+    nbase, reps, nlay = 2048, 49, 20                     # 100 352 columns = 3136 CTAs per role; 1480 strips per role
+    base = rce_atmosphere(nbase, nlay, cloudy=True)
+    kd_lw, kd_sw = synthetic_kdist("lw"), synthetic_kdist("sw")
+    lw = api.Radiation_solver_longwave(kd_lw, base.vmr.keys(), synthetic_cloud_lut("lw"), dtype)
+    sw = api.Radiation_solver_shortwave(kd_sw, base.vmr.keys(), synthetic_cloud_lut("sw"), dtype)
+    small = api.DeviceColumns(base, dtype)
+    ref_lw, ref_sw = api.solve_pair(lw, sw, small, switch_cloud_optics=True)
+    ref = {("lw", k): v.t.clone() for k, v in ref_lw.items()} | {("sw", k): v.t.clone() for k, v in ref_sw.items()}
+
+    def rep2(a):          # (nbase, n2) column-major -> (nbase*reps, n2)
+        n2 = a.dims[1]
+        return api.Array_gpu((nbase * reps, n2), a.t.dtype, data=a.t.view(n2, nbase).repeat(1, reps).contiguous().view(-1))
+
+    def repb(a):          # (nbnd, nbase) -> (nbnd, nbase*reps)
+        n1 = a.dims[0]
+        return api.Array_gpu((n1, nbase * reps), a.t.dtype, data=a.t.view(nbase, n1).repeat(reps, 1).contiguous().view(-1))
+
+    big = api.DeviceColumns(base, dtype)
+    for k in ("play", "plev", "tlay", "tlev", "lwp", "iwp", "rel", "dei"):
+        setattr(big, k, rep2(getattr(big, k)))
+    for k in ("emis_sfc", "sfc_alb_dir", "sfc_alb_dif"):
+        setattr(big, k, repb(getattr(big, k)))
+    for k in ("tsfc", "mu0", "tsi_scaling"):
+        a = getattr(big, k)
+        setattr(big, k, api.Array_gpu((nbase * reps,), a.t.dtype, data=a.t.repeat(reps).contiguous()))
+    for name, a in list(big.gas_concs.gas_concs_map.items()):
+        if a.dims[0] > 1:
+            big.gas_concs.gas_concs_map[name] = rep2(a)
+    big.ncol = nbase * reps
+    lw.set_tile_columns(40000); sw.set_tile_columns(40000)            # three ragged tiles, not a multiple of the period
+    nlev = nlay + 1
+    for mode in ("pair", "single"):
+        if mode == "pair":
+            o_lw, o_sw = api.solve_pair(lw, sw, big, switch_cloud_optics=True)
+        else:
+            o_lw, o_sw = lw.solve_gpu(big, switch_cloud_optics=True), sw.solve_gpu(big, switch_cloud_optics=True)
+        torch.cuda.synchronize()
+        for (w, k), want in ref.items():
+            got = (o_lw if w == "lw" else o_sw)[k].t.view(nlev, reps, nbase)
+            assert torch.equal(got, want.view(nlev, 1, nbase).expand(nlev, reps, nbase)), (mode, w, k)
