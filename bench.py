@@ -542,9 +542,11 @@ def run_b200(args):
                                        "inputs smaller than L2 (a small-call workload by definition; nothing is flushed between calls)",
                    "tile_columns": args.tile or "auto: equal tiles of at most 16 waves of CTAs (8 when the tile state would exceed a quarter of free memory)"},
         "breakdown_ms_per_step": {"band_kernels": (lw_ms.value + sw_ms.value + pair_ms.value) / args.steps, "gather": gather_ms,
-                                  "other": ms_per_step - (lw_ms.value + sw_ms.value + pair_ms.value) / args.steps - (gather_ms if len(calls) == 1 else 0.0),
+                                  "other": max(0.0, ms_per_step - (lw_ms.value + sw_ms.value + pair_ms.value) / args.steps - (gather_ms if len(calls) == 1 else 0.0)),
                                   "note": "rank 0; other = tile prologues (interpolation state), zeroing, net flux; with several blocks the gather of "
-                                          "block i overlaps the kernels of block i+1"},
+                                          "block i overlaps the kernels of block i+1"
+                                          + ("; small calls: the longwave and the shortwave call of a pair run on two streams, so band_kernels "
+                                             "(each kernel timed on its own stream) overlaps itself and can exceed the wall time" if args.ncol // len(calls) <= 6144 else "")},
         "clocks": clocks, "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_source": "static: profiles/traffic.json (ncu capture of this kernel, not measured in this run)" if traffic else None,

@@ -1124,12 +1124,7 @@ struct FusedJob
             top_at_1 = p2[0] < p2[1];
         }
 
-        // path: the handle's setting (0 strips, 1 column-resident, 2 by size), else RB200_PATH, else by size
-        const int want = g->colres >= 0 ? (g->colres == 2 ? -1 : g->colres) : g_colres;
-        const bool colres_ok = (sw || cols->n_gauss_angles <= 1) && colres_smem_bytes<Real>(nlay, h.gw, sw) <= 227 * 1024;   // column-resident LW: one angle
-        if (want == 1 && (sw || cols->n_gauss_angles <= 1) && !colres_ok)
-            throw ArgError("fused fluxes: column too tall for the shared-memory resident path");
-        colres = want == 1 ? colres_ok : (want < 0 && colres_ok && ncol <= kColresAutoMaxCols);
+        colres = wants_colres(g, cols, sw);
         cpb = FUSED_THREADS / (h.gw / 4);
         // strips path: a tile is several waves of CTAs (CTAs retire and start continuously, so compute-heavy
         // and memory-heavy passes of different CTAs overlap); scratch strips are per resident CTA.
@@ -1144,6 +1139,9 @@ struct FusedJob
         if (cloud || aerosol) need += 3 * pad256(tcl * h.nbnd * sizeof(Real));
         if (sw && !out->d_flux_dn_dir) need += pad256(ncv * sizeof(Real));
         if (sw && bnd && !out->d_bnd_flux_dn_dir) need += pad256(ncv * h.nbnd * sizeof(Real));
+        // a small column-resident call spreads its bands over CTAs: per-band partial sums, added in band order afterwards
+        const int nsplit = colres ? colres_band_split(tile, h.gw, h.nbnd) : 1;
+        if (nsplit > 1) need += pad256((size_t)nsplit * 3 * ncv * sizeof(Real));
         g->ws.reserve(need, s);
         st = carve_state<Real>(g->ws, h, tile, nlay);
 
@@ -1173,6 +1171,7 @@ struct FusedJob
         if (cloud || aerosol) { ctau = g->ws.take<Real>(tcl * h.nbnd); cssa = g->ws.take<Real>(tcl * h.nbnd); cg = g->ws.take<Real>(tcl * h.nbnd); }
         if (sw && !a.flux_dir) a.flux_dir = g->ws.take<Real>(ncv);
         if (sw && bnd && !a.bnd_dir) a.bnd_dir = g->ws.take<Real>(ncv * h.nbnd);
+        if (nsplit > 1) { a.part = g->ws.take<Real>((size_t)nsplit * 3 * ncv); a.nsplit = nsplit; }
 
         if (!colres)        // the strips kernels accumulate band by band; the column-resident ones store once
         {
@@ -1181,6 +1180,16 @@ struct FusedJob
             if (sw) CK(cudaMemsetAsync(a.flux_dir, 0, ncv * sizeof(Real), s));
         }
         g->ws.arm(s);
+    }
+
+    // path: the handle's setting (0 strips, 1 column-resident, 2 by size), else RB200_PATH, else by size
+    static bool wants_colres(const rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, bool sw)
+    {
+        const int want = g->colres >= 0 ? (g->colres == 2 ? -1 : g->colres) : g_colres;
+        const bool one_angle = sw || cols->n_gauss_angles <= 1;          // column-resident LW: one angle
+        const bool colres_ok = one_angle && cols->nlay <= 256 && colres_smem_bytes<Real>(cols->nlay, g->h.gw, sw) <= 227 * 1024;
+        if (want == 1 && one_angle && !colres_ok) throw ArgError("fused fluxes: column too tall for the shared-memory resident path");
+        return want == 1 ? colres_ok : (want < 0 && colres_ok && cols->ncol <= kColresAutoMaxCols);
     }
 
     static int auto_tile(rrtmgp_b200_gas_optics* g, int ncol, int nlay, int wave, int cpb)
@@ -1283,6 +1292,35 @@ void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, co
     j.finish(s);
 }
 
+// ---- host-buffer entry: chunks of columns stream H2D -> fused LW/SW -> D2H, double-buffered on
+// three streams so the PCIe copies hide behind the band kernels of the neighbouring chunks.
+struct HostPipe
+{
+    Arena in[2], out[2];
+    cudaStream_t h2d = nullptr, d2h = nullptr, side = nullptr;
+    cudaEvent_t e_h2d[2]{}, e_comp[2]{}, e_d2h[2]{}, e_side[2]{};
+    HostPipe()
+    {
+        CK(cudaStreamCreateWithFlags(&h2d, cudaStreamNonBlocking)); CK(cudaStreamCreateWithFlags(&d2h, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i)
+        {
+            CK(cudaEventCreateWithFlags(&e_h2d[i], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&e_comp[i], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&e_d2h[i], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&e_side[i], cudaEventDisableTiming));
+        }
+    }
+    ~HostPipe()
+    {
+        for (int i = 0; i < 2; ++i) { cudaEventDestroy(e_h2d[i]); cudaEventDestroy(e_comp[i]); cudaEventDestroy(e_d2h[i]); cudaEventDestroy(e_side[i]); }
+        cudaStreamDestroy(h2d); cudaStreamDestroy(d2h); cudaStreamDestroy(side);
+    }
+};
+HostPipe& host_pipe(rrtmgp_b200_gas_optics* g)
+{
+    if (!g->pipe) g->pipe = std::make_shared<HostPipe>();
+    return *static_cast<HostPipe*>(g->pipe.get());
+}
+
 // Longwave and shortwave of the same columns in ONE call: per tile both prologues, then band i of the longwave and band i of
 // the shortwave k-distribution in one launch whose CTAs alternate between the two roles (fused_pair.cu), so the L1-bound
 // longwave CTAs and the DRAM-bound shortwave CTAs share every SM; bands without a partner, and every band the paired
@@ -1295,6 +1333,17 @@ void fused_pair(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, con
     if (!glw || !gsw || !clw || !csw || !olw || !osw) throw ArgError("lwsw_fluxes: null argument");
     if (glw == gsw) throw ArgError("lwsw_fluxes: the longwave and the shortwave call need their own k-distribution objects");
     if (clw->ncol != csw->ncol || clw->nlay != csw->nlay) throw ArgError("lwsw_fluxes: the two calls must cover the same columns");
+    if (FusedJob<Real>::wants_colres(glw, clw, false) && FusedJob<Real>::wants_colres(gsw, csw, true))
+    {
+        // two small calls (column-resident kernels): neither fills the SMs, so the shortwave one runs on a side stream beside
+        // the longwave one, forked from and joined back into the caller's stream
+        HostPipe& pp = host_pipe(gsw);
+        CK(cudaEventRecord(pp.e_side[0], s)); CK(cudaStreamWaitEvent(pp.side, pp.e_side[0], 0));
+        fused_fluxes<Real>(gsw, csw, osw, pp.side, true);
+        fused_fluxes<Real>(glw, clw, olw, s, false);
+        CK(cudaEventRecord(pp.e_side[1], pp.side)); CK(cudaStreamWaitEvent(s, pp.e_side[1], 0));
+        return;
+    }
     const int wave = std::max(pair_blocks_per_wave<Real>(), 1);
     // one tile size for both: the smaller of the two automatic choices
     const int cpb = FUSED_THREADS / 4;
@@ -1350,35 +1399,6 @@ void fused_pair(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, con
     S.finish(s);
 }
 
-
-// ---- host-buffer entry: chunks of columns stream H2D -> fused LW/SW -> D2H, double-buffered on
-// three streams so the PCIe copies hide behind the band kernels of the neighbouring chunks.
-struct HostPipe
-{
-    Arena in[2], out[2];
-    cudaStream_t h2d = nullptr, d2h = nullptr, side = nullptr;
-    cudaEvent_t e_h2d[2]{}, e_comp[2]{}, e_d2h[2]{}, e_side[2]{};
-    HostPipe()
-    {
-        CK(cudaStreamCreateWithFlags(&h2d, cudaStreamNonBlocking)); CK(cudaStreamCreateWithFlags(&d2h, cudaStreamNonBlocking));
-        CK(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
-        for (int i = 0; i < 2; ++i)
-        {
-            CK(cudaEventCreateWithFlags(&e_h2d[i], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&e_comp[i], cudaEventDisableTiming));
-            CK(cudaEventCreateWithFlags(&e_d2h[i], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&e_side[i], cudaEventDisableTiming));
-        }
-    }
-    ~HostPipe()
-    {
-        for (int i = 0; i < 2; ++i) { cudaEventDestroy(e_h2d[i]); cudaEventDestroy(e_comp[i]); cudaEventDestroy(e_d2h[i]); cudaEventDestroy(e_side[i]); }
-        cudaStreamDestroy(h2d); cudaStreamDestroy(d2h); cudaStreamDestroy(side);
-    }
-};
-HostPipe& host_pipe(rrtmgp_b200_gas_optics* g)
-{
-    if (!g->pipe) g->pipe = std::make_shared<HostPipe>();
-    return *static_cast<HostPipe*>(g->pipe.get());
-}
 
 // one host array of the column set. kind 0: (ncol, n2) column-major, chunked by rows of the first index;
 // kind 1: (n2, ncol) band-major, a chunk is contiguous; kind 2: not column-dependent, uploaded whole

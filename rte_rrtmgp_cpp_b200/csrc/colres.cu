@@ -18,6 +18,8 @@
 // physics.cuh); see those files for the Fortran line references.
 #include "physics.cuh"
 #include "launch.hpp"
+#include <algorithm>
+#include <atomic>
 
 namespace rb200 {
 
@@ -73,9 +75,15 @@ sw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
     const int cs = min(blockIdx.x * NCB + cbs, nc - 1);
     const size_t cgs = (size_t)a.c0 + cs;
 
+    // one CTA per column group: the broadband sums are stored once.  Bands split over gridDim.y: every y stores its own
+    // partial sums (part[y][field][ncol * nlev]) and sum_parts_kernel adds them in band order (no atomics: reproducible)
+    const bool split = gridDim.y > 1;
+    Real* const o_up = split ? a.part + ((size_t)blockIdx.y * 3 + 0) * nlev_stride : a.flux_up;
+    Real* const o_dn = split ? a.part + ((size_t)blockIdx.y * 3 + 1) * nlev_stride : a.flux_dn;
+    Real* const o_dir = split ? a.part + ((size_t)blockIdx.y * 3 + 2) * nlev_stride : a.flux_dir;
     for (int i = tid; i < NCB * 3 * nlev; i += CR_T) acc[i] = (Real)0;
 
-    for (int ib = 0; ib < P.nbnd; ++ib)
+    for (int ib = blockIdx.y; ib < P.nbnd; ib += gridDim.y)     // gridDim.y > 1: the bands of a small call spread over CTAs
     {
         if (tid == 0) sB = bands[ib];
         __syncthreads();                 // also orders the previous band's phase 3 before this phase 1
@@ -253,8 +261,8 @@ sw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
         {
             const size_t o = (size_t)a.c0 + cc + (size_t)a.ncol * (top ? j : nlay - j);
             const Real* ac = acc + (size_t)cbi * 3 * nlev;
-            a.flux_up[o] = ac[j]; a.flux_dn[o] = ac[nlev + j];
-            if (a.flux_dir) a.flux_dir[o] = ac[2 * nlev + j];
+            o_up[o] = ac[j]; o_dn[o] = ac[nlev + j];
+            if (o_dir) o_dir[o] = ac[2 * nlev + j];
         }
     }
 }
@@ -297,9 +305,12 @@ lw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
     const int cs = min(blockIdx.x * NCB + cbs, nc - 1);
     const size_t cgs = (size_t)a.c0 + cs;
 
+    const bool split = gridDim.y > 1;
+    Real* const o_up = split ? a.part + ((size_t)blockIdx.y * 3 + 0) * nlev_stride : a.flux_up;
+    Real* const o_dn = split ? a.part + ((size_t)blockIdx.y * 3 + 1) * nlev_stride : a.flux_dn;
     for (int i = tid; i < NCB * 2 * nlev; i += CR_T) acc[i] = (Real)0;
 
-    for (int ib = 0; ib < P.nbnd; ++ib)
+    for (int ib = blockIdx.y; ib < P.nbnd; ib += gridDim.y)     // gridDim.y > 1: the bands of a small call spread over CTAs
     {
         if (tid == 0) sB = bands[ib];
         __syncthreads();
@@ -445,7 +456,7 @@ lw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
         {
             const size_t o = (size_t)a.c0 + cc + (size_t)a.ncol * (top ? j : nlay - j);
             const Real* ac = acc + (size_t)cbi * 2 * nlev;
-            a.flux_up[o] = ac[j]; a.flux_dn[o] = ac[nlev + j];
+            o_up[o] = ac[j]; o_dn[o] = ac[nlev + j];
         }
     }
 }
@@ -457,12 +468,47 @@ template<typename Real> size_t colres_smem_bytes(int nlay, int gw, bool sw)
     return (size_t)(nlev * CR_RS + (sw ? 3 : 2) * ncb * nlev) * sizeof(Real);
 }
 
-template<typename K> static void cr_launch(K kern, unsigned grid, size_t smem, cudaStream_t s,
+// flux(c, j) = sum over y of part[y][field](c, j), y ascending (= band order), for the nc columns of the tile
+template<typename Real>
+__global__ void __launch_bounds__(256)
+sum_parts_kernel(const Real* __restrict__ part, const int nsplit, const int nfield, const int ncol, const int c0, const int nc,
+                 const int nlev, Real* __restrict__ up, Real* __restrict__ dn, Real* __restrict__ dir)
+{
+    const size_t n = (size_t)nc * nlev, plane = (size_t)ncol * nlev;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n * nfield; i += (size_t)gridDim.x * blockDim.x)
+    {
+        const int f = (int)(i / n);
+        const size_t r = i - (size_t)f * n;
+        const size_t o = (size_t)c0 + r % nc + (size_t)ncol * (r / nc);
+        Real acc = 0;
+        for (int y = 0; y < nsplit; ++y) acc += part[((size_t)y * 3 + f) * plane + o];
+        Real* dst = f == 0 ? up : (f == 1 ? dn : dir);
+        if (dst) dst[o] = acc;
+    }
+}
+
+template<typename K> static void cr_launch(K kern, dim3 grid, size_t smem, cudaStream_t s,
                                            const void* P, const void* bands, const void* st, const void* a)
 {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     void* args[4] = {const_cast<void*>(P), const_cast<void*>(bands), const_cast<void*>(st), const_cast<void*>(a)};
-    cudaLaunchKernel((const void*)kern, dim3(grid), dim3(CR_T), args, smem, s);
+    cudaLaunchKernel((const void*)kern, grid, dim3(CR_T), args, smem, s);
+}
+
+// A call of fewer column groups than this leaves SMs idle with one CTA per group looping over every band (100 RFMIP columns:
+// 100 CTAs, 16 bands in series each); its bands are spread over the grid's y dimension instead.
+int colres_band_split(int ncol, int gw, int nbnd)
+{
+    static std::atomic<int> sms{0};
+    int n = sms.load();
+    if (!n)
+    {
+        int dev = 0; cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        sms.store(n);
+    }
+    const int ncb = CR_CH / gw, groups = (ncol + ncb - 1) / ncb;
+    return groups < 4 * n ? nbnd : 1;
 }
 
 template<typename Real>
@@ -470,7 +516,8 @@ void launch_cols(bool sw, const DevPlan<Real>& P, const BandArgs* bands, const T
                  const FusedArgs<Real>& a, cudaStream_t s)
 {
     const int lpc = P.gw / 4, ncb = CR_CH / P.gw;
-    const unsigned grid = (unsigned)((a.nc + ncb - 1) / ncb);
+    const int nsplit = a.part ? a.nsplit : 1;
+    const dim3 grid((unsigned)((a.nc + ncb - 1) / ncb), (unsigned)nsplit);
     const size_t smem = colres_smem_bytes<Real>(a.nlay, P.gw, sw);
     const bool cloud = a.cld_tau != nullptr;
     const void* pb = &bands;
@@ -483,6 +530,15 @@ void launch_cols(bool sw, const DevPlan<Real>& P, const BandArgs* bands, const T
 #undef RB_NE
 #undef RB_GO
     count_launch();
+    if (nsplit > 1)
+    {
+        const int nlev = a.nlay + 1, nfield = sw ? 3 : 2;
+        const size_t n = (size_t)a.nc * nlev * nfield;
+        const unsigned blocks = (unsigned)std::min<size_t>((n + 255) / 256, 4096);
+        sum_parts_kernel<Real><<<blocks, 256, 0, s>>>(a.part, nsplit, nfield, a.ncol, a.c0, a.nc, nlev, a.flux_up, a.flux_dn,
+                                                      sw ? a.flux_dir : nullptr);
+        count_launch();
+    }
 }
 
 template size_t colres_smem_bytes<float>(int, int, bool);

@@ -31,6 +31,7 @@ template<typename Real> struct FusedArgs
     Real* bnd_up; Real* bnd_dn; Real* bnd_dir;                      // (ncol, nlay+1, nbnd) or null
     Real secant, weight;                                            // LW quadrature angle of this launch
     int bnd_add;                                                    // LW: add this angle onto the by-band outputs
+    Real* part; int nsplit;                                         // column-resident kernels, bands split over CTAs: partial sums
 };
 constexpr int FUSED_THREADS = 128;
 
@@ -94,6 +95,7 @@ template<typename Real> int pair_blocks_per_wave();
 
 // ---- colres.cu : one launch = all bands of one column tile, recurrences resident in shared memory
 template<typename Real> size_t colres_smem_bytes(int nlay, int gw, bool sw);
+int colres_band_split(int ncol, int gw, int nbnd);       // nbnd when a call of ncol columns should spread its bands over CTAs, else 1
 template<typename Real> void launch_cols(bool sw, const DevPlan<Real>& P, const BandArgs* bands_dev, const TileState<Real>& st,
                                          const FusedArgs<Real>& a, cudaStream_t s);
 

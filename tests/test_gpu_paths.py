@@ -79,5 +79,7 @@ def test_path_is_chosen_by_call_size():
         sol.set_fused_path(0)
         ref = sol.solve_gpu(cols, out={})
         assert np.max(np.abs(out["flux_up"].numpy() - ref["flux_up"].numpy())) < 1e-2
-    assert launches[64] == launches[6144] < kd.nbnd          # prologue + one kernel for all bands (+ col_dry, net)
+    # prologue + one kernel for all bands (+ col_dry, net); a call too small to fill the SMs spreads its bands over the grid of
+    # that one launch and adds the per-band partial sums in a second, tiny one
+    assert launches[64] == launches[6144] + 1 < kd.nbnd
     assert launches[6145] >= kd.nbnd + 1                      # prologue + one launch per band
