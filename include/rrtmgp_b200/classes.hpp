@@ -808,6 +808,28 @@ class Fluxes_byband_gpu : public Fluxes_broadband_gpu
         Array_gpu<Float,3> bnd_flux_up, bnd_flux_dn, bnd_flux_dn_dir, bnd_flux_net;
 };
 
+// One prepared fused call: the C-ABI arguments of a solver's solve_gpu(switch_fluxes = true, switch_output_optical = false),
+// not launched yet.  Radiation_solver_{longwave,shortwave}::prepare_gpu fill it; solve_gpu launches its own straight away;
+// rrtmgp_b200::solve_gpu_pair launches a longwave and a shortwave one of the same columns together (no counterpart in the
+// reference, whose driver calls the two solvers one after the other, src_test/test_rte_rrtmgp.cu).  The arrays it points to
+// must stay alive until the launch.
+namespace rrtmgp_b200 {
+struct Fused_call
+{
+    rrtmgp_b200_gas_optics* handle = nullptr;
+    rrtmgp_b200_columns c{};
+    rrtmgp_b200_fluxes f{};
+    std::unique_ptr<Concs_view> concs;       // owns the per-gas pointer lists c.concs points into
+};
+// Longwave and shortwave of the same columns in one library call: on large domains band i of both runs in one launch with
+// longwave and shortwave CTAs co-resident on every SM; small calls run side by side on two streams.  Fluxes are bit-identical
+// to lw.solve_gpu(...) followed by sw.solve_gpu(...).
+inline void solve_gpu_pair(const Fused_call& lw, const Fused_call& sw)
+{
+    check(rrtmgp_b200_lwsw_fluxes(lw.handle, &lw.c, &lw.f, sw.handle, &sw.c, &sw.f, stream()));
+}
+}  // namespace rrtmgp_b200
+
 // ---- Radiation_solver_{longwave,shortwave}::solve_gpu (include_test/Radiation_solver.h:73-88,176-199;
 // src_test/Radiation_solver.cu:419-657,690-950).  Same switches and argument order (aerosols are out of
 // scope).  With switch_output_optical=false the whole chain runs in the fused band
@@ -834,6 +856,34 @@ class Radiation_solver_longwave
         Gas_optics_rrtmgp_gpu& get_kdist_gpu() { return *kdist_gpu; }
         void set_n_gauss_angles(const int n) { n_gauss_angles = n; }
 
+        // the fused call of solve_gpu(true, switch_cloud_optics, false, switch_output_bnd_fluxes, ...), prepared but not launched
+        rrtmgp_b200::Fused_call prepare_gpu(const bool switch_cloud_optics, const bool switch_output_bnd_fluxes, const Gas_concs_gpu& gas_concs,
+                       const Array_gpu<Float,2>& p_lay, const Array_gpu<Float,2>& p_lev,
+                       const Array_gpu<Float,2>& t_lay, const Array_gpu<Float,2>& t_lev,
+                       const Array_gpu<Float,2>& col_dry, const Array_gpu<Float,1>& t_sfc, const Array_gpu<Float,2>& emis_sfc,
+                       const Array_gpu<Float,2>& lwp, const Array_gpu<Float,2>& iwp,
+                       const Array_gpu<Float,2>& rel, const Array_gpu<Float,2>& dei,
+                       Array_gpu<Float,2>& lw_flux_up, Array_gpu<Float,2>& lw_flux_dn, Array_gpu<Float,2>& lw_flux_net,
+                       Array_gpu<Float,3>& lw_bnd_flux_up, Array_gpu<Float,3>& lw_bnd_flux_dn, Array_gpu<Float,3>& lw_bnd_flux_net) const
+        {
+            if (switch_cloud_optics && !cloud_optics_gpu) throw std::runtime_error("cloud optics requested without cloud tables");
+            rrtmgp_b200::Fused_call fc;
+            fc.handle = kdist_gpu->handle();
+            fc.concs = std::make_unique<rrtmgp_b200::Concs_view>(gas_concs, kdist_gpu->get_gas_names());
+            rrtmgp_b200_columns& c = fc.c;
+            c.ncol = p_lay.dim(1); c.nlay = p_lay.dim(2); c.top_at_1 = -1;
+            c.d_play = p_lay.ptr(); c.d_plev = p_lev.ptr(); c.d_tlay = t_lay.ptr(); c.d_tlev = t_lev.ptr();
+            c.d_tsfc = t_sfc.ptr(); c.d_col_dry = col_dry.size() ? col_dry.ptr() : nullptr; c.concs = fc.concs->c;
+            c.d_sfc_emis = emis_sfc.ptr(); c.n_gauss_angles = n_gauss_angles;
+            if (switch_cloud_optics)
+            { c.cloud = cloud_optics_gpu->handle(); c.d_lwp = lwp.ptr(); c.d_iwp = iwp.ptr(); c.d_rel = rel.ptr(); c.d_dei = dei.ptr(); }
+            rrtmgp_b200_fluxes& f = fc.f;
+            f.d_flux_up = lw_flux_up.ptr(); f.d_flux_dn = lw_flux_dn.ptr(); f.d_flux_net = lw_flux_net.ptr();
+            if (switch_output_bnd_fluxes)
+            { f.d_bnd_flux_up = lw_bnd_flux_up.ptr(); f.d_bnd_flux_dn = lw_bnd_flux_dn.ptr(); f.d_bnd_flux_net = lw_bnd_flux_net.ptr(); }
+            return fc;
+        }
+
         void solve_gpu(const bool switch_fluxes, const bool switch_cloud_optics, const bool switch_output_optical,
                        const bool switch_output_bnd_fluxes, const Gas_concs_gpu& gas_concs,
                        const Array_gpu<Float,2>& p_lay, const Array_gpu<Float,2>& p_lev,
@@ -851,19 +901,9 @@ class Radiation_solver_longwave
             if (!switch_output_optical)
             {
                 if (!switch_fluxes) return;
-                rrtmgp_b200::Concs_view cv(gas_concs, kdist_gpu->get_gas_names());
-                rrtmgp_b200_columns c{};
-                c.ncol = n_col; c.nlay = n_lay; c.top_at_1 = -1;
-                c.d_play = p_lay.ptr(); c.d_plev = p_lev.ptr(); c.d_tlay = t_lay.ptr(); c.d_tlev = t_lev.ptr();
-                c.d_tsfc = t_sfc.ptr(); c.d_col_dry = col_dry.size() ? col_dry.ptr() : nullptr; c.concs = cv.c;
-                c.d_sfc_emis = emis_sfc.ptr(); c.n_gauss_angles = n_gauss_angles;
-                if (switch_cloud_optics)
-                { c.cloud = cloud_optics_gpu->handle(); c.d_lwp = lwp.ptr(); c.d_iwp = iwp.ptr(); c.d_rel = rel.ptr(); c.d_dei = dei.ptr(); }
-                rrtmgp_b200_fluxes f{};
-                f.d_flux_up = lw_flux_up.ptr(); f.d_flux_dn = lw_flux_dn.ptr(); f.d_flux_net = lw_flux_net.ptr();
-                if (switch_output_bnd_fluxes)
-                { f.d_bnd_flux_up = lw_bnd_flux_up.ptr(); f.d_bnd_flux_dn = lw_bnd_flux_dn.ptr(); f.d_bnd_flux_net = lw_bnd_flux_net.ptr(); }
-                rrtmgp_b200::check(rrtmgp_b200_lw_fluxes(kdist_gpu->handle(), &c, &f, rrtmgp_b200::stream()));
+                const rrtmgp_b200::Fused_call fc = prepare_gpu(switch_cloud_optics, switch_output_bnd_fluxes, gas_concs, p_lay, p_lev, t_lay, t_lev,
+                        col_dry, t_sfc, emis_sfc, lwp, iwp, rel, dei, lw_flux_up, lw_flux_dn, lw_flux_net, lw_bnd_flux_up, lw_bnd_flux_dn, lw_bnd_flux_net);
+                rrtmgp_b200::check(rrtmgp_b200_lw_fluxes(fc.handle, &fc.c, &fc.f, rrtmgp_b200::stream()));
                 return;
             }
             // staged path: gas_optics -> [cloud_optics -> add_to] -> rte_lw -> reduce
@@ -936,6 +976,54 @@ class Radiation_solver_shortwave
         const Array<Float,2>& get_band_lims_wavenumber_gpu() const { return kdist_gpu->get_band_lims_wavenumber(); }
         Gas_optics_rrtmgp_gpu& get_kdist_gpu() { return *kdist_gpu; }
 
+        // the fused call of solve_gpu(true, ..., switch_output_optical = false, ...), prepared but not launched
+        rrtmgp_b200::Fused_call prepare_gpu(const bool switch_cloud_optics, const bool switch_aerosol_optics, const bool switch_output_bnd_fluxes,
+                       const bool switch_delta_cloud, const bool switch_delta_aerosol, const Gas_concs_gpu& gas_concs,
+                       const Array_gpu<Float,2>& p_lay, const Array_gpu<Float,2>& p_lev,
+                       const Array_gpu<Float,2>& t_lay, const Array_gpu<Float,2>& t_lev, const Array_gpu<Float,2>& col_dry,
+                       const Array_gpu<Float,2>& sfc_alb_dir, const Array_gpu<Float,2>& sfc_alb_dif,
+                       const Array_gpu<Float,1>& tsi_scaling, const Array_gpu<Float,1>& mu0,
+                       const Array_gpu<Float,2>& lwp, const Array_gpu<Float,2>& iwp,
+                       const Array_gpu<Float,2>& rel, const Array_gpu<Float,2>& dei,
+                       const Array_gpu<Float,2>& rh, const Aerosol_concs_gpu& aerosol_concs,
+                       Array_gpu<Float,2>& sw_flux_up, Array_gpu<Float,2>& sw_flux_dn,
+                       Array_gpu<Float,2>& sw_flux_dn_dir, Array_gpu<Float,2>& sw_flux_net,
+                       Array_gpu<Float,3>& sw_bnd_flux_up, Array_gpu<Float,3>& sw_bnd_flux_dn,
+                       Array_gpu<Float,3>& sw_bnd_flux_dn_dir, Array_gpu<Float,3>& sw_bnd_flux_net) const
+        {
+            (void)t_lev;
+            if (switch_cloud_optics && !cloud_optics_gpu) throw std::runtime_error("cloud optics requested without cloud tables");
+            if (switch_aerosol_optics && !aerosol_optics_gpu) throw std::runtime_error("aerosol optics requested without aerosol tables");
+            rrtmgp_b200::Fused_call fc;
+            fc.handle = kdist_gpu->handle();
+            fc.concs = std::make_unique<rrtmgp_b200::Concs_view>(gas_concs, kdist_gpu->get_gas_names());
+            rrtmgp_b200_columns& c = fc.c;
+            c.ncol = p_lay.dim(1); c.nlay = p_lay.dim(2); c.top_at_1 = -1;
+            c.d_play = p_lay.ptr(); c.d_plev = p_lev.ptr(); c.d_tlay = t_lay.ptr();
+            c.d_col_dry = col_dry.size() ? col_dry.ptr() : nullptr; c.concs = fc.concs->c;
+            c.d_sfc_alb_dir = sfc_alb_dir.ptr(); c.d_sfc_alb_dif = sfc_alb_dif.ptr(); c.d_mu0 = mu0.ptr();
+            c.d_tsi_scaling = tsi_scaling.size() ? tsi_scaling.ptr() : nullptr;
+            if (switch_cloud_optics)
+            {
+                c.cloud = cloud_optics_gpu->handle(); c.delta_cloud = switch_delta_cloud;
+                c.d_lwp = lwp.ptr(); c.d_iwp = iwp.ptr(); c.d_rel = rel.ptr(); c.d_dei = dei.ptr();
+            }
+            if (switch_aerosol_optics)
+            {
+                c.aerosol = aerosol_optics_gpu->handle(); c.delta_aerosol = switch_delta_aerosol;
+                c.d_rh = rh.ptr(); c.aerosol_concs = rrtmgp_b200::aerosol_view(aerosol_concs);
+            }
+            rrtmgp_b200_fluxes& f = fc.f;
+            f.d_flux_up = sw_flux_up.ptr(); f.d_flux_dn = sw_flux_dn.ptr(); f.d_flux_net = sw_flux_net.ptr();
+            f.d_flux_dn_dir = sw_flux_dn_dir.ptr();
+            if (switch_output_bnd_fluxes)
+            {
+                f.d_bnd_flux_up = sw_bnd_flux_up.ptr(); f.d_bnd_flux_dn = sw_bnd_flux_dn.ptr();
+                f.d_bnd_flux_net = sw_bnd_flux_net.ptr(); f.d_bnd_flux_dn_dir = sw_bnd_flux_dn_dir.ptr();
+            }
+            return fc;
+        }
+
         // the aerosol-free call of earlier callers
         void solve_gpu(const bool switch_fluxes, const bool switch_cloud_optics, const bool switch_output_optical,
                        const bool switch_output_bnd_fluxes, const bool switch_delta_cloud, const Gas_concs_gpu& gas_concs,
@@ -980,32 +1068,10 @@ class Radiation_solver_shortwave
             if (!switch_output_optical)
             {
                 if (!switch_fluxes) return;
-                rrtmgp_b200::Concs_view cv(gas_concs, kdist_gpu->get_gas_names());
-                rrtmgp_b200_columns c{};
-                c.ncol = n_col; c.nlay = n_lay; c.top_at_1 = -1;
-                c.d_play = p_lay.ptr(); c.d_plev = p_lev.ptr(); c.d_tlay = t_lay.ptr();
-                c.d_col_dry = col_dry.size() ? col_dry.ptr() : nullptr; c.concs = cv.c;
-                c.d_sfc_alb_dir = sfc_alb_dir.ptr(); c.d_sfc_alb_dif = sfc_alb_dif.ptr(); c.d_mu0 = mu0.ptr();
-                c.d_tsi_scaling = tsi_scaling.size() ? tsi_scaling.ptr() : nullptr;
-                if (switch_cloud_optics)
-                {
-                    c.cloud = cloud_optics_gpu->handle(); c.delta_cloud = switch_delta_cloud;
-                    c.d_lwp = lwp.ptr(); c.d_iwp = iwp.ptr(); c.d_rel = rel.ptr(); c.d_dei = dei.ptr();
-                }
-                if (switch_aerosol_optics)
-                {
-                    c.aerosol = aerosol_optics_gpu->handle(); c.delta_aerosol = switch_delta_aerosol;
-                    c.d_rh = rh.ptr(); c.aerosol_concs = rrtmgp_b200::aerosol_view(aerosol_concs);
-                }
-                rrtmgp_b200_fluxes f{};
-                f.d_flux_up = sw_flux_up.ptr(); f.d_flux_dn = sw_flux_dn.ptr(); f.d_flux_net = sw_flux_net.ptr();
-                f.d_flux_dn_dir = sw_flux_dn_dir.ptr();
-                if (switch_output_bnd_fluxes)
-                {
-                    f.d_bnd_flux_up = sw_bnd_flux_up.ptr(); f.d_bnd_flux_dn = sw_bnd_flux_dn.ptr();
-                    f.d_bnd_flux_net = sw_bnd_flux_net.ptr(); f.d_bnd_flux_dn_dir = sw_bnd_flux_dn_dir.ptr();
-                }
-                rrtmgp_b200::check(rrtmgp_b200_sw_fluxes(kdist_gpu->handle(), &c, &f, rrtmgp_b200::stream()));
+                const rrtmgp_b200::Fused_call fc = prepare_gpu(switch_cloud_optics, switch_aerosol_optics, switch_output_bnd_fluxes, switch_delta_cloud,
+                        switch_delta_aerosol, gas_concs, p_lay, p_lev, t_lay, t_lev, col_dry, sfc_alb_dir, sfc_alb_dif, tsi_scaling, mu0, lwp, iwp, rel, dei,
+                        rh, aerosol_concs, sw_flux_up, sw_flux_dn, sw_flux_dn_dir, sw_flux_net, sw_bnd_flux_up, sw_bnd_flux_dn, sw_bnd_flux_dn_dir, sw_bnd_flux_net);
+                rrtmgp_b200::check(rrtmgp_b200_sw_fluxes(fc.handle, &fc.c, &fc.f, rrtmgp_b200::stream()));
                 return;
             }
             std::unique_ptr<Optical_props_arry_gpu> optical_props = std::make_unique<Optical_props_2str_gpu>(n_col, n_lay, *kdist_gpu);

@@ -340,6 +340,25 @@ extern "C" int ctor_solve(const rrtmgp_b200_kdist_file* kd_lw, const rrtmgp_b200
                           Array_gpu<Float,1>(), a_mu0, a_lwp, a_iwp, a_rel, a_dei, a_rh, aer, o3a, o3b, o3c, o2a,
                           f_up, f_dn, f_dir, f_net, b0, b1, b2, b3);
         down(f_up, sw_up); down(f_dn, sw_dn); down(f_dir, sw_dir);
+        // the same two calls prepared and launched together (rrtmgp_b200::solve_gpu_pair): bit-identical fluxes
+        {
+            Array_gpu<Float,2> l_up({ncol, nlev}), l_dn({ncol, nlev}), l_net({ncol, nlev});
+            Array_gpu<Float,2> s_up({ncol, nlev}), s_dn({ncol, nlev}), s_dir({ncol, nlev}), s_net({ncol, nlev});
+            const rrtmgp_b200::Fused_call clw = rad_lw->prepare_gpu(true, false, gas_concs, p_lay, p_lev, t_lay, t_lev, col_dry, t_sfc, emis_sfc,
+                    a_lwp, a_iwp, a_rel, a_dei, l_up, l_dn, l_net, b0, b1, b2);
+            const rrtmgp_b200::Fused_call csw = rad_sw->prepare_gpu(true, true, false, true, false, gas_concs, p_lay, p_lev, t_lay, t_lev, col_dry,
+                    a_dir, a_dif, Array_gpu<Float,1>(), a_mu0, a_lwp, a_iwp, a_rel, a_dei, a_rh, aer, s_up, s_dn, s_dir, s_net, b0, b1, b2, b3);
+            rrtmgp_b200::solve_gpu_pair(clw, csw);
+            const size_t n = (size_t)ncol * nlev;
+            std::vector<double> h(n);
+            const std::pair<const Array_gpu<Float,2>*, const double*> chk[5] = {{&l_up, lw_up}, {&l_dn, lw_dn}, {&s_up, sw_up}, {&s_dn, sw_dn}, {&s_dir, sw_dir}};
+            for (int k = 0; k < 5; ++k)
+            {
+                down(*chk[k].first, h.data());
+                for (size_t i = 0; i < n; ++i)
+                    if (h[i] != chk[k].second[i]) return fail("solve_gpu_pair differs from the two solve_gpu calls (field " + std::to_string(k) + ")");
+            }
+        }
         return 0;
     }
     catch (const std::exception& ex) { return fail(std::string("exception: ") + ex.what()); }
