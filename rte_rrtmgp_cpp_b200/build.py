@@ -14,7 +14,7 @@ EXTRA = os.environ.get("RB200_DEFS", "").split()
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 # k1_interp.cu carries the index arithmetic: no FMA contraction there (bit-exact indices)
-SOURCES = {"cabi.cu": [], "k1_interp.cu": ["--fmad=false"], "fused_lw.cu": [], "fused_sw.cu": [], "fused_pair.cu": [], "colres.cu": [],
+SOURCES = {"cabi.cu": [], "k1_interp.cu": ["--fmad=false"], "fused_lw.cu": [], "fused_lw_ma.cu": [], "fused_sw.cu": [], "fused_pair.cu": [], "colres.cu": [],
            "stages.cu": [], "gasopt.cu": [], "arrays.cu": []}
 
 

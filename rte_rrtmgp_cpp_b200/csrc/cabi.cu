@@ -27,6 +27,9 @@ static Profile g_prof;
 // RB200_PATH=colres selects the column-resident kernels (recurrences in shared memory) instead of the
 // per-band kernels with recurrence scratch strips in HBM, which measure faster (kernels)
 // unset: chosen per call by size (small calls are column-resident); "strips" / "colres" force one
+// RB200_ANGLES=launches: longwave calls with several Gauss angles run one pass of the single-angle kernels per angle (the
+// round-1 path, kept for A/B timing) instead of the kernels with the angles inside the layer loop
+static const bool g_angle_launches = [] { const char* e = getenv("RB200_ANGLES"); return e && e[0] == 'l'; }();
 static const int g_colres = [] { const char* e = getenv("RB200_PATH"); return !e || !*e ? -1 : (e[0] == 'c' ? 1 : 0); }();
 // Calls of at most this many columns take the column-resident kernels when the path is not forced.  Measured on B200 (fp32):
 // 100 columns x 60 layers 1.6 ms (strips, paired) vs 0.42 ms; 16384 x 72 8.0 ms vs 10.0 ms; the strips launches cost a
@@ -1134,7 +1137,9 @@ struct FusedJob
         tile = forced_tile > 0 ? forced_tile : auto_tile(g, ncol, nlay, wave, cpb);
         const size_t tcl = (size_t)tile * nlay, ncl = (size_t)ncol * nlay;
         ncv = (size_t)ncol * nlev;
-        size_t need = state_bytes<Real>(h, tile, nlay) + pad256(fused_scratch_bytes<Real>(nslots, nlay, sw)) + pad256(nslots * sizeof(int)) + 4096;
+        // longwave with several Gauss angles: the strip holds {trans, source_up} per angle (fused_lw_ma.cu)
+        const int words = sw ? 6 : 2 * (nang > 1 && !g_angle_launches && h.gw == 16 && h.neta == 9 ? nang : 1);
+        size_t need = state_bytes<Real>(h, tile, nlay) + pad256(fused_scratch_bytes<Real>(nslots, nlay, words)) + pad256(nslots * sizeof(int)) + 4096;
         if (!cols->d_col_dry) need += pad256(ncl * sizeof(Real));
         if (cloud || aerosol) need += 3 * pad256(tcl * h.nbnd * sizeof(Real));
         if (sw && !out->d_flux_dn_dir) need += pad256(ncv * sizeof(Real));
@@ -1151,7 +1156,7 @@ struct FusedJob
         a.sfc_emis = (const Real*)cols->d_sfc_emis; a.mu0 = (const Real*)cols->d_mu0;
         a.alb_dir = (const Real*)cols->d_sfc_alb_dir; a.alb_dif = (const Real*)cols->d_sfc_alb_dif;
         a.tsi_scaling = (const Real*)cols->d_tsi_scaling;
-        a.scratch = (V4<Real>*)g->ws.take<char>(fused_scratch_bytes<Real>(nslots, nlay, sw));
+        a.scratch = (V4<Real>*)g->ws.take<char>(fused_scratch_bytes<Real>(nslots, nlay, words));
         a.slot_busy = g->ws.take<int>(nslots); a.nslots = nslots;
         if (nslots) CK(cudaMemsetAsync(a.slot_busy, 0, nslots * sizeof(int), s));
         a.flux_up = (Real*)out->d_flux_up; a.flux_dn = (Real*)out->d_flux_dn;
@@ -1243,27 +1248,41 @@ struct FusedJob
         static const double gauss_wts[4][4] = {{1., 0., 0., 0.}, {0.2300253764, 0.7699746236, 0., 0.},
             {0.0437820218, 0.3875796738, 0.5686383044, 0.}, {0.0092068785, 0.1285704278, 0.4323381850, 0.4298845087}};
         a.secant = (Real)gauss_Ds[nang - 1][ia]; a.weight = (Real)gauss_wts[nang - 1][ia]; a.bnd_add = ia > 0;
+        for (int k = 0; k < 4; ++k) { a.secants[k] = (Real)gauss_Ds[nang - 1][k]; a.weights[k] = (Real)gauss_wts[nang - 1][k]; }
     }
 
     void bands(cudaStream_t s)
     {
         const HostPlan& h = g->h;
+        int nlaunch = 0;
         if (g_prof.on) { cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, s)); g_prof.ev[sw].push_back(e); }
         if (colres) launch_cols<Real>(sw, dplan<Real>(g), (const BandArgs*)g->bands_dev.p, st, a, s);
         else if (sw)
             for (int b = 0; b < h.nbnd; ++b) launch_sw_band<Real>(dplan<Real>(g), g->bands[b], st, a, s);
         else
-            // one pass of the band kernels per angle, fluxes accumulate (the reference's GPU path has a single angle; its CPU
-            // path sums angles the same way)
-            for (int ia = 0; ia < nang; ++ia)
+            // several Gauss angles (the reference's GPU path has a single one; its CPU path sums them, src/Rte_lw.cpp:139-151):
+            // one launch per band with the angles inside the layer loop where that kernel exists, else one pass of the
+            // single-angle kernel per angle; fluxes accumulate either way
+            for (int b = 0; b < h.nbnd; ++b)
             {
-                set_angle(ia);
-                for (int b = 0; b < h.nbnd; ++b) launch_lw_band<Real>(dplan<Real>(g), g->bands[b], st, a, s);
+                if (nang > 1 && !g_angle_launches && lw_multi_angle_supported<Real>(dplan<Real>(g), g->bands[b]))
+                {
+                    set_angle(0);
+                    launch_lw_band_angles<Real>(dplan<Real>(g), g->bands[b], st, a, nang, s);
+                    ++nlaunch;
+                    continue;
+                }
+                for (int ia = 0; ia < nang; ++ia)
+                {
+                    set_angle(ia);
+                    launch_lw_band<Real>(dplan<Real>(g), g->bands[b], st, a, s);
+                    ++nlaunch;
+                }
             }
         if (g_prof.on)
         {
             cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, s)); g_prof.ev[sw].push_back(e);
-            g_prof.launches[sw] += colres ? 1 : h.nbnd * nang;
+            g_prof.launches[sw] += colres ? 1 : (sw ? h.nbnd : nlaunch);
         }
     }
 
@@ -1324,7 +1343,7 @@ HostPipe& host_pipe(rrtmgp_b200_gas_optics* g)
 // Longwave and shortwave of the same columns in ONE call: per tile both prologues, then band i of the longwave and band i of
 // the shortwave k-distribution in one launch whose CTAs alternate between the two roles (fused_pair.cu), so the L1-bound
 // longwave CTAs and the DRAM-bound shortwave CTAs share every SM; bands without a partner, and every band the paired
-// kernel does not cover (narrow bands of the reduced g-point sets, extra Gauss angles, the column-resident path), run through
+// kernel does not cover (narrow bands of the reduced g-point sets, the column-resident path), run through
 // the single-role launches.  Results are bit-identical to rrtmgp_b200_lw_fluxes + rrtmgp_b200_sw_fluxes.
 template<typename Real>
 void fused_pair(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, const rrtmgp_b200_fluxes* olw,
@@ -1353,7 +1372,7 @@ void fused_pair(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, con
     S.setup(gsw, csw, osw, s, true, tile, wave);
     // paired launches need both roles with the same particulate flag (one kernel instantiation per flag); the fp64 build
     // measured slower paired (pair_supported refuses it)
-    const bool pairable = sizeof(Real) == 4 && !L.colres && !S.colres && glw->h.gw == 16 && gsw->h.gw == 16 &&
+    const bool pairable = sizeof(Real) == 4 && !L.colres && !S.colres && glw->h.gw == 16 && gsw->h.gw == 16 && L.nang == 1 &&
                           ((L.cloud || L.aerosol) == (S.cloud || S.aerosol));
     if (!pairable)
     {
@@ -1383,11 +1402,6 @@ void fused_pair(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, con
             { launch_lw_band<Real>(dplan<Real>(glw), glw->bands[il], L.st, L.a, s); ++il; ++nsingle; }
             else
             { launch_sw_band<Real>(dplan<Real>(gsw), gsw->bands[is], S.st, S.a, s); ++is; ++nsingle; }
-        }
-        for (int ia = 1; ia < L.nang; ++ia)      // further Gauss angles of the longwave call
-        {
-            L.set_angle(ia);
-            for (int b = 0; b < nbl; ++b) { launch_lw_band<Real>(dplan<Real>(glw), glw->bands[b], L.st, L.a, s); ++nsingle; }
         }
         if (g_prof.on)
         {

@@ -3,9 +3,9 @@
 
 namespace rb200 {
 
-template<typename Real> size_t fused_scratch_bytes(int nslots, int nlay, bool sw)
+template<typename Real> size_t fused_scratch_bytes(int nslots, int nlay, int words)
 {
-    return (size_t)nslots * nlay * (sw ? 6 : 2) * FUSED_THREADS * sizeof(V4<Real>);
+    return (size_t)nslots * nlay * words * FUSED_THREADS * sizeof(V4<Real>);
 }
 
 template<typename Real>
@@ -32,8 +32,8 @@ void launch_lw_band(const DevPlan<Real>& P, const BandArgs& B, const TileState<R
     count_launch();
 }
 
-template size_t fused_scratch_bytes<float>(int, int, bool);
-template size_t fused_scratch_bytes<double>(int, int, bool);
+template size_t fused_scratch_bytes<float>(int, int, int);
+template size_t fused_scratch_bytes<double>(int, int, int);
 template void launch_lw_band<float>(const DevPlan<float>&, const BandArgs&, const TileState<float>&, const FusedArgs<float>&, cudaStream_t);
 template void launch_lw_band<double>(const DevPlan<double>&, const BandArgs&, const TileState<double>&, const FusedArgs<double>&, cudaStream_t);
 

@@ -38,7 +38,10 @@ template<typename Real> struct LWMinBlocks { static constexpr int v = sizeof(Rea
 
 // The whole band computation of one CTA; `bid` is the CTA's index among the launch's LW CTAs (blockIdx.x in the
 // single-role kernel below, a role-local index in the paired longwave + shortwave kernel of fused_pair.cu).
-template<typename Real, int LPC, int GWT, bool CLOUD, int NE>
+// NANG > 1: the Gauss angles of the quadrature (src/Rte_lw.cpp:139-151) inside the layer loop — optical depths and Planck
+// sources are computed once per layer, only exp(-tau * secant), the layer sources and the transport are per angle; the strip
+// holds {trans, source_up} per (layer, angle).
+template<typename Real, int LPC, int GWT, bool CLOUD, int NE, int NANG = 1>
 __device__ __forceinline__ void lw_band_body(const DevPlan<Real>& P, const BandLaunch<Real>& L, const TileState<Real>& st,
                                              const FusedArgs<Real>& a, const int bid)
 {
@@ -62,7 +65,21 @@ __device__ __forceinline__ void lw_band_body(const DevPlan<Real>& P, const BandL
     const unsigned* tm = st.tmask + (size_t)c * TMASK_WORDS;
     const int slot = claim_slot(a.slot_busy, a.nslots, bid);
     V4<Real>* const scr = a.scratch + (size_t)slot * L.strip + tid;
-    const Real piw = (Real)3.14159265358979323846 * a.weight;
+    const Real pi = (Real)3.14159265358979323846;
+    const Real piw = pi * a.weight;
+    auto secant = [&](int ia) -> Real { return NANG == 1 ? a.secant : a.secants[ia]; };
+    auto weight = [&](int ia) -> Real { return NANG == 1 ? a.weight : a.weights[ia]; };
+    // pi * sum over angles of weight * radiance, summed over the band's g-points (one angle: the launch's weight)
+    auto band_flux = [&](const Real (&r)[NANG][4]) -> Real
+    {
+        if (NANG == 1) return quad_sum<Real, LPC>(r[0]) * piw;
+        Real ws[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int ia = 0; ia < NANG; ++ia)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) ws[j] += weight(ia) * r[ia][j];
+        return quad_sum<Real, LPC>(ws) * pi;
+    };
     const bool lead = active && q == 0;
     const size_t nlev_stride = L.nlev_stride;
     const int top = a.top_at_1;
@@ -70,7 +87,7 @@ __device__ __forceinline__ void lw_band_body(const DevPlan<Real>& P, const BandL
     const int tstep = top ? nc : -nc;                                          // same, tile arrays
     const size_t o_top = cg + L.o_top;                                         // level index * ncol
 
-    Real radn[4] = {0, 0, 0, 0};        // incident diffuse flux = 0 (Radiation_solver.cu passes zeros)
+    Real radn[NANG][4] = {};            // incident diffuse flux = 0 (Radiation_solver.cu passes zeros)
     Real pf_prev[4] = {0, 0, 0, 0}, tau_prev[4] = {0, 0, 0, 0}, lev_top[4] = {0, 0, 0, 0};
     Real blay_prev = 0;
 
@@ -141,20 +158,30 @@ __device__ __forceinline__ void lw_band_body(const DevPlan<Real>& P, const BandL
         }
         else
         {
-            Pr<Real> t2[2], su2[2];
+            Pr<Real> lev_bot[2];
 #pragma unroll
             for (int h = 0; h < 2; ++h)
             {
                 const Pr<Real> pfp = pget(pf_prev, h);
-                const Pr<Real> lev_bot = ((k < nlay) ? psqrt(pfp * pget(pf, h)) : pfp) * blev;
-                Pr<Real> s_dn;
-                lw_layer2(pget(tau_prev, h) * a.secant, pfp * blay_prev, pget(lev_top, h), lev_bot, t2[h], su2[h], s_dn);
-                pput(radn, h, pfma(t2[h], pget(radn, h), s_dn));
-                pput(lev_top, h, lev_bot);
+                lev_bot[h] = ((k < nlay) ? psqrt(pfp * pget(pf, h)) : pfp) * blev;
             }
-            V4<Real>* w = scr + (size_t)(k - 1) * 2 * T;
-            st_stream(w, v4_of(t2[0], t2[1])); st_stream(w + T, v4_of(su2[0], su2[1]));
-            const Real s = quad_sum<Real, LPC>(radn) * piw;
+#pragma unroll
+            for (int ia = 0; ia < NANG; ++ia)
+            {
+                Pr<Real> t2[2], su2[2];
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+                {
+                    Pr<Real> s_dn;
+                    lw_layer2(pget(tau_prev, h) * secant(ia), pget(pf_prev, h) * blay_prev, pget(lev_top, h), lev_bot[h], t2[h], su2[h], s_dn);
+                    pput(radn[ia], h, pfma(t2[h], pget(radn[ia], h), s_dn));
+                }
+                V4<Real>* w = scr + ((size_t)(k - 1) * NANG + ia) * 2 * T;
+                st_stream(w, v4_of(t2[0], t2[1])); st_stream(w + T, v4_of(su2[0], su2[1]));
+            }
+#pragma unroll
+            for (int h = 0; h < 2; ++h) pput(lev_top, h, lev_bot[h]);
+            const Real s = band_flux(radn);
             if (lead)
             {
                 atomicAdd(a.flux_dn + o, s);
@@ -176,8 +203,10 @@ __device__ __forceinline__ void lw_band_body(const DevPlan<Real>& P, const BandL
         const Real emis = a.sfc_emis[band + (size_t)P.nbnd * cg];
         const Real refl = (Real)1 - emis, eb = emis * bsfc;
 #pragma unroll
-        for (int h = 0; h < 2; ++h) pput(radn, h, pfma(eb, pget(pf_prev, h), pget(radn, h) * refl));
-        const Real s = quad_sum<Real, LPC>(radn) * piw;
+        for (int ia = 0; ia < NANG; ++ia)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) pput(radn[ia], h, pfma(eb, pget(pf_prev, h), pget(radn[ia], h) * refl));
+        const Real s = band_flux(radn);
         if (lead)
         {
             atomicAdd(a.flux_up + o, s);
@@ -187,39 +216,46 @@ __device__ __forceinline__ void lw_band_body(const DevPlan<Real>& P, const BandL
     // ---- up-sweep, surface -> top (F90:710-745): the parked {trans, source_up} come back LIFO through
     // two register buffers of 4 layers; the loads of the next 4 layers are issued before the
     // arithmetic of the current 4.
-    auto ld = [&](V4<Real> (&tr)[4], V4<Real> (&su)[4], int k0)
-    {
+    const size_t o_sfc = o;
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
-        {
-            const V4<Real>* w = scr + (size_t)max(k0 - u, 0) * 2 * T;
-            tr[u] = ld_stream(w); su[u] = ld_stream(w + T);
-        }
-    };
-    auto sweep = [&](const V4<Real> (&tr)[4], const V4<Real> (&su)[4], int k0)
+    for (int ia = 0; ia < NANG; ++ia)
     {
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
+        Real (&rad)[4] = radn[ia];
+        const Real pw = NANG == 1 ? piw : pi * weight(ia);
+        const bool add = a.bnd_add || ia > 0;           // by-band outputs: the first angle stores, the others add
+        o = o_sfc;
+        auto ld = [&](V4<Real> (&tr)[4], V4<Real> (&su)[4], int k0)
         {
-            if (k0 - u < 0) break;
-            pput(radn, 0, pfma(plo(tr[u]), pget(radn, 0), plo(su[u])));
-            pput(radn, 1, pfma(phi(tr[u]), pget(radn, 1), phi(su[u])));
-            const Real s = quad_sum<Real, LPC>(radn) * piw;
-            o -= lstep;
-            if (lead)
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
             {
-                atomicAdd(a.flux_up + o, s);
-                if (a.bnd_up) { Real* b_ = a.bnd_up + o + nlev_stride * band; *b_ = a.bnd_add ? *b_ + s : s; }
+                const V4<Real>* w = scr + ((size_t)max(k0 - u, 0) * NANG + ia) * 2 * T;
+                tr[u] = ld_stream(w); su[u] = ld_stream(w + T);
             }
-        }
-    };
-    {
+        };
+        auto sweep = [&](const V4<Real> (&tr)[4], const V4<Real> (&su)[4], int k0)
+        {
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+            {
+                if (k0 - u < 0) break;
+                pput(rad, 0, pfma(plo(tr[u]), pget(rad, 0), plo(su[u])));
+                pput(rad, 1, pfma(phi(tr[u]), pget(rad, 1), phi(su[u])));
+                const Real s = quad_sum<Real, LPC>(rad) * pw;
+                o -= lstep;
+                if (lead)
+                {
+                    atomicAdd(a.flux_up + o, s);
+                    if (a.bnd_up) { Real* b_ = a.bnd_up + o + nlev_stride * band; *b_ = add ? *b_ + s : s; }
+                }
+            }
+        };
         // strip lines of the layers RB_LW_PF2 further up go to L2 while the current ones are consumed
         auto pf4 = [&](int k0)
         {
 #pragma unroll
             for (int u = 0; u < 4; ++u)
-                if (RB_LW_PF2 > 0 && k0 - u - RB_LW_PF2 >= 0) prefetch_strip_layer<Real, 2>(scr - tid, k0 - u - RB_LW_PF2);
+                if (RB_LW_PF2 > 0 && k0 - u - RB_LW_PF2 >= 0) prefetch_strip_layer<Real, 2>(scr - tid, (k0 - u - RB_LW_PF2) * NANG + ia);
         };
         V4<Real> trA[4], suA[4], trB[4], suB[4];
         ld(trA, suA, nlay - 1);

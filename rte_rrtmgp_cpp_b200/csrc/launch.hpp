@@ -32,6 +32,7 @@ template<typename Real> struct FusedArgs
     Real secant, weight;                                            // LW quadrature angle of this launch
     int bnd_add;                                                    // LW: add this angle onto the by-band outputs
     Real* part; int nsplit;                                         // column-resident kernels, bands split over CTAs: partial sums
+    Real secants[4], weights[4];                                    // LW, all angles in one launch (fused_lw_ma.cu)
 };
 constexpr int FUSED_THREADS = 128;
 
@@ -78,11 +79,16 @@ inline BandLaunch<Real> make_band_launch(const DevPlan<Real>& P, const BandArgs&
 }
 template<typename Real> int lw_blocks_per_wave(int gw);
 template<typename Real> int sw_blocks_per_wave(int gw);
-template<typename Real> size_t fused_scratch_bytes(int nslots, int nlay, bool sw);
+template<typename Real> size_t fused_scratch_bytes(int nslots, int nlay, int words);     // words per layer: 6 SW, 2 per angle LW
 template<typename Real> void launch_lw_band(const DevPlan<Real>& P, const BandArgs& B, const TileState<Real>& st,
                                             const FusedArgs<Real>& a, cudaStream_t s);
 template<typename Real> void launch_sw_band(const DevPlan<Real>& P, const BandArgs& B, const TileState<Real>& st,
                                             const FusedArgs<Real>& a, cudaStream_t s);
+
+// ---- fused_lw_ma.cu : longwave band launch with the 2..4 Gauss angles inside the layer loop (16-wide bands, 9 mixing fractions)
+template<typename Real> bool lw_multi_angle_supported(const DevPlan<Real>& P, const BandArgs& B);
+template<typename Real> void launch_lw_band_angles(const DevPlan<Real>& P, const BandArgs& B, const TileState<Real>& st,
+                                                   const FusedArgs<Real>& a, int nang, cudaStream_t s);
 
 // ---- fused_pair.cu : one launch = one longwave band + one shortwave band of the same tile, CTAs of both kinds co-resident
 template<typename Real> bool pair_supported(const DevPlan<Real>& Plw, const BandArgs& Blw, const DevPlan<Real>& Psw, const BandArgs& Bsw);

@@ -117,11 +117,14 @@ def test_errors_are_loud():
 
 
 @pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
-@pytest.mark.parametrize("n_ang", [2, 3, 4])
-def test_lw_fused_gauss_angles(dtype, n_ang):
+@pytest.mark.parametrize("n_ang,reduced", [(2, False), (3, False), (4, False), (3, True)])
+def test_lw_fused_gauss_angles(dtype, n_ang, reduced):
     """Gauss-Jacobi quadrature with 2..4 angles in the fused call (src/Rte_lw.cpp:139-151; the CPU reference
-    supports it, its GPU path does not): one pass of the band kernels per angle, fluxes and by-band fluxes add up."""
-    kd, lut = synthetic_kdist("lw"), synthetic_cloud_lut("lw")
+    supports it, its GPU path does not).  Bands of the common shape run ONE launch with the angles inside the layer loop
+    (fused_lw_ma.cu: optical depths and Planck sources once per layer); the narrow bands of the reduced g-point set run one
+    pass of the single-angle kernel per angle.  Either way fluxes and by-band fluxes add up over the angles."""
+    kd = synthetic_kdist("lw", REDUCED_LW_128) if reduced else synthetic_kdist("lw")
+    lut = synthetic_cloud_lut("lw")
     atm = rce_atmosphere(45, 40, cloudy=True)
     ref = oracle_lw(kd, atm, lut, n_ang=n_ang)
     sol = api.Radiation_solver_longwave(kd, atm.vmr.keys(), lut, dtype)
