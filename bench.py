@@ -67,6 +67,7 @@ def parse():
     ap.add_argument("--chunk", type=int, default=0, help="columns per chunk of the host-buffer pipeline (0 = auto)")
     ap.add_argument("--no-pair", action="store_true", help="longwave and shortwave as two calls instead of the paired call (rrtmgp_b200_lwsw_fluxes)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-affinity", action="store_true", help="multi-GPU runs: do not bind a rank's host threads to its GPU's NUMA node")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true", help="skip timing the reference's own CUDA path (oracle/_ref/librefcuda_*.so)")
     ap.add_argument("--ref-cuda-cols", type=int, default=65536)
@@ -283,6 +284,26 @@ def build_columns(args, api, dtype, ncol, rank):
     return out
 
 
+def bind_to_gpu_numa_node(local: int):
+    """Several ranks on one node: run this rank's host threads on the CPUs NVML reports as local to its GPU, so the pinned host
+    buffers of the e2e leg are first-touched on that NUMA node and the PCIe copies do not cross sockets (what `numactl` in a
+    launch script does).  Returns the number of CPUs bound, or None when NVML has no answer."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return None
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -299,6 +320,7 @@ def run_b200(args):
         cpu = cpu_baseline(args, args.cpu_cols_per_core)       # before any CUDA state exists
     assert torch.cuda.is_available(), "bench.py needs a CUDA device: there is no CPU fallback"
     torch.cuda.set_device(local)
+    affinity = bind_to_gpu_numa_node(local) if world > 1 and not args.no_affinity else None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dtype = torch.float32 if args.dtype == "f32" else torch.float64
@@ -547,7 +569,7 @@ def run_b200(args):
                                           "block i overlaps the kernels of block i+1"
                                           + ("; small calls: the longwave and the shortwave call of a pair run on two streams, so band_kernels "
                                              "(each kernel timed on its own stream) overlaps itself and can exceed the wall time" if args.ncol // len(calls) <= 6144 else "")},
-        "clocks": clocks, "gpu_launches": int(launches),
+        "clocks": clocks, "gpu_launches": int(launches), "host_cpus_bound_to_gpu_node": affinity,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_source": "static: profiles/traffic.json (ncu capture of this kernel, not measured in this run)" if traffic else None,
                      "peak_source": peak_src,

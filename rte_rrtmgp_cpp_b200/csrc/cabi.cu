@@ -1467,6 +1467,9 @@ void fluxes_host(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, co
             const int W = wave * cpb;
             chunk = 8 * W;
             for (int size = W; size < chunk && remaining > 3 * size; size *= 2) { left.push_back(size); right.push_back(size); remaining -= 2 * size; }
+            // a shard of 1.5 to 3 waves (65 536 columns per rank at 8 GPUs) still gets a one-wave first chunk: one chunk would
+            // expose its whole upload and download (17 of 84 ms), two hide the larger one's upload and the smaller one's download
+            if (left.empty() && 2 * remaining > 3 * W) { left.push_back(W); remaining -= W; }
         }
         const int nmid = std::max((remaining + chunk - 1) / chunk, 1);
         const int mid = std::min((((remaining + nmid - 1) / nmid + 31) / 32) * 32, remaining);   // equal chunks, whole CTAs
