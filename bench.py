@@ -572,6 +572,10 @@ def run_b200(args):
         "clocks": clocks, "gpu_launches": int(launches), "host_cpus_bound_to_gpu_node": affinity,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_source": "static: profiles/traffic.json (ncu capture of this kernel, not measured in this run)" if traffic else None,
+                     # the DRAM bytes the kernel really moves (ncu) over this run's launch time: how busy the memory system is, next to
+                     # `frac`, which counts the bytes of the materialised pipeline the kernel replaces
+                     "dram_achieved": traffic / (k_ms / max(k_n, 1) * 1e-3) / 1e9 if traffic and k_ms > 0 else None,
+                     "dram_frac": traffic / (k_ms / max(k_n, 1) * 1e-3) / 1e9 / peak if traffic and k_ms > 0 else None,
                      "peak_source": peak_src,
                      "algorithmic_bytes_per_column_gpt": {"lw": b_lw, "sw": b_sw},
                      "avg_launch_ms": k_ms / max(k_n, 1), "launches_timed": int(k_n),

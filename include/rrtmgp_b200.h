@@ -44,10 +44,11 @@ enum {
     RRTMGP_B200_E_CUDA = 4      /* CUDA runtime failure (reference: printf + throw 1)        */
 };
 
-/* Concurrency: a handle owns ONE workspace that every compute call re-carves and that is ordered only by the stream of that call:
- * ONE call in flight per handle.  Calls on the same handle from different streams or host threads must be serialised by
- * the caller (or use one handle per stream: handles are independent, tables are a few tens of MB).  Calls on different handles
- * may overlap freely; rrtmgp_b200_profile's counters are process-wide and not thread-safe. */
+/* Concurrency: a handle owns ONE workspace that every compute call re-carves, so the calls on one handle SERIALISE: the library
+ * holds a per-handle mutex for the duration of a call (host threads) and makes the call's stream wait for an event recorded
+ * after the previous call's last launch (different streams).  That is safe, not concurrent: for overlapping calls use one handle
+ * per stream (handles are independent, tables are a few tens of MB).  Calls on different handles overlap freely;
+ * rrtmgp_b200_profile's counters and rrtmgp_b200_last_error's message are process-wide and not thread-safe. */
 typedef struct rrtmgp_b200_gas_optics rrtmgp_b200_gas_optics;     /* Gas_optics_rrtmgp_gpu  */
 typedef struct rrtmgp_b200_cloud_optics rrtmgp_b200_cloud_optics; /* Cloud_optics_gpu       */
 typedef struct rrtmgp_b200_aerosol_optics rrtmgp_b200_aerosol_optics; /* Aerosol_optics_gpu */

@@ -166,6 +166,33 @@ struct rrtmgp_b200_gas_optics
     int tile_cols = 0;
     int colres = -1;                // fused path: 1 column-resident, 0 strips, -1 default (RB200_PATH)
     std::shared_ptr<void> pipe;     // HostPipe of the host-buffer entry, created on first use
+    std::recursive_mutex mu;        // HandleCall: one call at a time carves the workspace ...
+    cudaEvent_t last_done = nullptr; // ... and its device work is ordered behind the previous call's, whatever their streams
+    ~rrtmgp_b200_gas_optics() { if (last_done) cudaEventDestroy(last_done); }
+};
+
+// Every call that carves a handle's workspace (fused fluxes, materialised gas optics, the host pipeline) holds one of these: the
+// arena is re-carved from offset 0 by each call, so two calls on one handle from different host threads or CUDA streams would
+// otherwise overwrite each other's tile state and scratch strips.  Host side: the handle's mutex for the duration of the call
+// (recursive: the host pipeline calls the fused entries).  Device side: the call's stream first waits for the event the
+// previous call on this handle recorded after its last launch.  Calls on one handle therefore serialise; calls on different
+// handles stay independent.
+struct HandleCall
+{
+    rrtmgp_b200_gas_optics* g; cudaStream_t s;
+    HandleCall(rrtmgp_b200_gas_optics* g_, cudaStream_t s_) : g(g_), s(s_)
+    {
+        g->mu.lock();
+        if (!g->last_done) { if (cudaEventCreateWithFlags(&g->last_done, cudaEventDisableTiming) != cudaSuccess) { g->last_done = nullptr; cudaGetLastError(); } }
+        else cudaStreamWaitEvent(s, g->last_done, 0);
+    }
+    ~HandleCall()
+    {
+        if (g->last_done) cudaEventRecord(g->last_done, s);
+        g->mu.unlock();
+    }
+    HandleCall(const HandleCall&) = delete;
+    HandleCall& operator=(const HandleCall&) = delete;
 };
 
 struct rrtmgp_b200_cloud_optics
@@ -563,6 +590,7 @@ void gas_optics_materialised(rrtmgp_b200_gas_optics* g, int ncol, int nlay, cons
     check_dims(ncol, nlay);
     const HostPlan& h = g->h;
     if (!play || !tlay || !o.tau) throw ArgError("gas_optics: null array");
+    HandleCall hc(g, s);
     const VmrArgs vmr = make_vmr(g, concs, ncol, nlay);
     const size_t tcl = (size_t)ncol * nlay;
     g->ws.reserve(state_bytes<Real>(h, ncol, nlay) + pad256(tcl * sizeof(Real)) + 2 * sizeof(Real) + 512, s);
@@ -1300,6 +1328,8 @@ template<typename Real>
 void fused_fluxes(rrtmgp_b200_gas_optics* g, const rrtmgp_b200_columns* cols, const rrtmgp_b200_fluxes* out,
                   cudaStream_t s, bool sw)
 {
+    if (!g) throw ArgError("fused fluxes: null handle");
+    HandleCall hc(g, s);
     FusedJob<Real> j;
     j.setup(g, cols, out, s, sw);
     L2Pin pin(s, g->kmajor.p, g->kmajor.bytes);
@@ -1352,6 +1382,7 @@ void fused_pair(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, con
     if (!glw || !gsw || !clw || !csw || !olw || !osw) throw ArgError("lwsw_fluxes: null argument");
     if (glw == gsw) throw ArgError("lwsw_fluxes: the longwave and the shortwave call need their own k-distribution objects");
     if (clw->ncol != csw->ncol || clw->nlay != csw->nlay) throw ArgError("lwsw_fluxes: the two calls must cover the same columns");
+    HandleCall hl(glw, s), hs(gsw, s);
     if (FusedJob<Real>::wants_colres(glw, clw, false) && FusedJob<Real>::wants_colres(gsw, csw, true))
     {
         // two small calls (column-resident kernels): neither fills the SMs, so the shortwave one runs on a side stream beside
@@ -1433,6 +1464,7 @@ void fluxes_host(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, co
     const int ncol = c0p->ncol, nlay = c0p->nlay, nlev = nlay + 1;
     check_dims(ncol, nlay);
     if (!c0p->d_play) throw ArgError("fluxes_host: play missing");
+    HandleCall hp(g0, s);            // the pipeline's buffers live in g0's HostPipe; the fused calls below guard their own handles
     HostPipe& P = host_pipe(g0);
     int top_at_1 = c0p->top_at_1;
     if (top_at_1 < 0) { const Real* pl = (const Real*)c0p->d_play; top_at_1 = pl[0] < pl[(size_t)ncol * (nlay - 1)]; }
