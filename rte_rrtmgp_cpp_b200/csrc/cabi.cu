@@ -528,14 +528,15 @@ TileState<Real> carve_state(Arena& ws, const HostPlan& h, int nc, int nlay)
     st.scal = ws.take<V4<Real>>(tcl * (h.nscal / 4));
     st.pl_lay = nullptr; st.pl_lev = nullptr;
     if (h.is_lw) { st.pl_lay = ws.take<V2<Real>>(tcl); st.pl_lev = ws.take<V2<Real>>(tcl + nc); }
-    st.tmask = ws.take<unsigned>((size_t)nc * TMASK_WORDS);
+    st.tmw = tmask_words(nlay);
+    st.tmask = ws.take<unsigned>((size_t)nc * st.tmw);
     return st;
 }
 template<typename Real> size_t state_bytes(const HostPlan& h, int nc, int nlay)
 {
     const size_t tcl = (size_t)nc * nlay;
     return pad256(tcl * sizeof(V4<Real>)) + 2 * pad256(tcl * h.nflav * sizeof(V4<Real>))
-         + pad256(tcl * h.nscal * sizeof(Real)) + pad256((size_t)nc * TMASK_WORDS * sizeof(unsigned))
+         + pad256(tcl * h.nscal * sizeof(Real)) + pad256((size_t)nc * tmask_words(nlay) * sizeof(unsigned))
          + 2 * pad256((tcl + nc) * sizeof(V2<Real>)) + 1024;
 }
 
@@ -1122,7 +1123,6 @@ struct FusedJob
         if (!cols->d_play || !cols->d_plev || !cols->d_tlay || !out->d_flux_up || !out->d_flux_dn) throw ArgError("fused fluxes: null array");
         if (!sw && (!cols->d_tlev || !cols->d_tsfc || !cols->d_sfc_emis)) throw ArgError("lw_fluxes: tlev, tsfc and sfc_emis are required");
         if (sw && (!cols->d_mu0 || !cols->d_sfc_alb_dir || !cols->d_sfc_alb_dif)) throw ArgError("sw_fluxes: mu0 and surface albedos are required");
-        if (nlay > 32 * TMASK_WORDS) throw ArgError("fused fluxes: at most 256 layers (use the stage calls for taller columns)");
         nang = sw ? 1 : std::max(cols->n_gauss_angles, 1);
         if (nang > 4) throw ArgError("lw_fluxes: n_gauss_angles must be 1..4");   // src/Rte_lw.cpp:139-151
         cloud = cols->cloud != nullptr;
@@ -1220,7 +1220,7 @@ struct FusedJob
     {
         const int want = g->colres >= 0 ? (g->colres == 2 ? -1 : g->colres) : g_colres;
         const bool one_angle = sw || cols->n_gauss_angles <= 1;          // column-resident LW: one angle
-        const bool colres_ok = one_angle && cols->nlay <= 256 && colres_smem_bytes<Real>(cols->nlay, g->h.gw, sw) <= 227 * 1024;
+        const bool colres_ok = one_angle && colres_smem_bytes<Real>(cols->nlay, g->h.gw, sw) <= 227 * 1024;
         if (want == 1 && one_angle && !colres_ok) throw ArgError("fused fluxes: column too tall for the shared-memory resident path");
         return want == 1 ? colres_ok : (want < 0 && colres_ok && cols->ncol <= kColresAutoMaxCols);
     }
@@ -1249,7 +1249,7 @@ struct FusedJob
     {
         const int nc = std::min(tile, ncol - c0);
         st.nc = nc; a.c0 = c0; a.nc = nc;
-        CK(cudaMemsetAsync(st.tmask, 0, (size_t)nc * TMASK_WORDS * sizeof(unsigned), s));
+        CK(cudaMemsetAsync(st.tmask, 0, (size_t)nc * st.tmw * sizeof(unsigned), s));
         launch_interp<Real>(dplan<Real>(g), vmr, ncol, c0, nc, nlay, cols->d_play, cols->d_tlay, col_dry, cols->d_tlev, st,
                             nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, s);
         if (cloud)

@@ -64,7 +64,7 @@ sw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
     const int c = active ? craw : nc - 1;
     const size_t tcl = (size_t)nc * nlay;
     const size_t cg = (size_t)a.c0 + c;
-    const unsigned* tm = st.tmask + (size_t)c * TMASK_WORDS;
+    const unsigned* tm = st.tmask + (size_t)c * st.tmw;
     const int top = a.top_at_1;
     const size_t nlev_stride = (size_t)a.ncol * nlev;
     const Real mu0 = a.mu0[cg];
@@ -295,7 +295,7 @@ lw_col_kernel(const DevPlan<Real> P, const BandArgs* __restrict__ bands, const T
     const int c = active ? craw : nc - 1;
     const size_t tcl = (size_t)nc * nlay;
     const size_t cg = (size_t)a.c0 + c;
-    const unsigned* tm = st.tmask + (size_t)c * TMASK_WORDS;
+    const unsigned* tm = st.tmask + (size_t)c * st.tmw;
     const int top = a.top_at_1;
     const size_t nlev_stride = (size_t)a.ncol * nlev;
     const Real piw = (Real)3.14159265358979323846 * a.weight;

@@ -246,9 +246,11 @@ template<typename Real> struct TileState
                              //   rows = major row | minor row << 20 (row = offset / row stride)
     V2<Real>* pl_lay;        // LW: Planck table position of tlay {frac, lower index}  (nc, nlay)
     V2<Real>* pl_lev;        // LW: idem for tlev                                      (nc, nlay+1)
-    unsigned* tmask;         // [c][TMASK_WORDS]: bit l of a column = tropo(c, l)  (fused path only)
+    unsigned* tmask;         // [c][tmw]: bit l of a column = tropo(c, l)  (fused path only)
+    int tmw;                 // mask words per column: tmask_words(nlay)
 };
-constexpr int TMASK_WORDS = 8;   // the fused path handles up to 256 layers
+constexpr int TMASK_WORDS = 8;   // at least 8 words (256 layers) per column, more for taller columns
+inline int tmask_words(int nlay) { const int w = (nlay + 31) / 32; return w > TMASK_WORDS ? w : TMASK_WORDS; }
 
 struct MinorDev { int idx_minor, idx_scaling, flags, contributor; };   // flags: 1 density, 2 complement
 

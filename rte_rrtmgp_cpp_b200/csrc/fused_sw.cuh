@@ -63,7 +63,7 @@ __device__ __forceinline__ void sw_band_body(const DevPlan<Real>& P, const BandL
     const int band = B.band;
     const Real* kmaj = L.kmaj + q4;
     const int flav0 = B.flav[0], flav1 = B.flav[1];
-    const unsigned* tm = st.tmask + (size_t)c * TMASK_WORDS;
+    const unsigned* tm = st.tmask + (size_t)c * st.tmw;
     const int slot = claim_slot(a.slot_busy, a.nslots, bid);
     V4<Real>* const scr = a.scratch + (size_t)slot * L.strip + tid;
     const bool lead = active && q == 0;

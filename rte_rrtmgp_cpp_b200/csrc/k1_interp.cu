@@ -132,7 +132,7 @@ interp_kernel(const DevPlan<Real> P, const VmrArgs vmr, int ncol, int c0, int nc
             st.pl_lev[it] = pos(tlev[i]);
             if (l == nlay - 1) st.pl_lev[it + nc] = pos(tlev[i + ncol]);
         }
-        if (st.tmask && tropo) atomicOr(&st.tmask[(size_t)c * TMASK_WORDS + (l >> 5)], 1u << (l & 31));
+        if (st.tmask && tropo) atomicOr(&st.tmask[(size_t)c * st.tmw + (l >> 5)], 1u << (l & 31));
     }
 
     // F90:127-169

@@ -41,8 +41,10 @@ def _same(a, b, what):
     (333, 17, 96, 1),       # column-resident kernels
     (45, 1, 0, 0),          # a single layer
     (45, 2, 0, 0),
-    (9, 255, 0, 0),         # odd, and the maximum layer count of the fused path
+    (9, 255, 0, 0),         # odd, and the last layer count of one block of tropopause-mask words
     (9, 256, 0, 0),
+    (9, 257, 0, 0),         # one layer into the second block of tropopause-mask words
+    (6, 400, 0, 2),         # by size: column-resident in fp32; in fp64 400 layers exceed its shared memory, so the strips kernels
     (70, 40, 64, 2),        # path chosen by size
 ])
 def test_poisoned_workspace_and_canaries(dtype, ncol, nlay, tile, path):

@@ -35,7 +35,8 @@ def _poisoned(sol, cols, nb, sw):
 @pytest.mark.parametrize("kind", ["lw", "sw"])
 @pytest.mark.parametrize("ncol,nlay,top_at_1,cloudy,reduced", [
     (70, 48, False, False, False), (33, 37, True, True, False), (1, 128, False, True, False),
-    (37, 30, False, True, True), (64, 129, True, False, True)])
+    (37, 30, False, True, True), (64, 129, True, False, True),
+    (5, 300, False, True, False)])          # taller than the 256 layers one tropopause-mask block covers
 def test_paths_agree(dtype, kind, ncol, nlay, top_at_1, cloudy, reduced):
     sizes = (REDUCED_LW_128 if kind == "lw" else REDUCED_SW_112) if reduced else None
     kd = synthetic_kdist(kind, sizes) if reduced else synthetic_kdist(kind)
