@@ -534,7 +534,7 @@ def run_b200(args):
             if refcuda.available(args.dtype):
                 torch.cuda.empty_cache()
                 r = subprocess.run([sys.executable, "-m", "oracle.refcuda", "--ncol", str(min(args.ref_cuda_cols, args.ncol)),
-                                    "--nlay", str(nlay), "--dtype", args.dtype, "--reps", "3"], cwd=ROOT,
+                                    "--nlay", str(nlay), "--dtype", args.dtype, "--reps", "3", "--check"], cwd=ROOT,
                                    capture_output=True, text=True, timeout=600)
                 for ln in r.stdout.splitlines():
                     if ln.startswith("{"):
@@ -543,7 +543,9 @@ def run_b200(args):
                     ref_cuda = {"unavailable": (r.stderr or r.stdout).strip().splitlines()[-1][:200] if (r.stderr or r.stdout).strip() else "no output"}
                 else:
                     ref_cuda["note"] = ("unmodified reference src_cuda + src_kernels_cuda built for sm_100a, driven like "
-                                        "Radiation_solver::solve_gpu; its fluxes are NOT the parity target (SURVEY 2.1 quirks)")
+                                        "Radiation_solver::solve_gpu; its fluxes are NOT the parity target (SURVEY 2.1 quirks: "
+                                        "max_abs_diff_vs_cpu_oracle_Wm2 is its distance from the CPU oracle on 256 of these columns; "
+                                        "stage by stage the two are compared in tests/test_oracle_vs_refcuda.py)")
         except Exception as ex:      # noqa: BLE001 - a baseline failure must not lose the measurement
             ref_cuda = {"unavailable": str(ex)[:200]}
     whole = (ncol * (g_lw * b_lw + g_sw * b_sw) * args.steps) / ((lw_ms.value + sw_ms.value + pair_ms.value) * 1e-3) / 1e9

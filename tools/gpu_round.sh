@@ -18,7 +18,10 @@ python bench.py --config rfmip --ncol 1801 --steps 5 --warmup 3 --no-ref-cuda --
 for C in big rce512; do
   python bench.py --config $C --dtype f64 --steps 3 --warmup 3 --no-cpu > $O/bench_${C}_f64_$TAG.json 2> $O/bench_${C}_f64_$TAG.err; echo -n "$C f64: "; python tools/benchline.py $O/bench_${C}_f64_$TAG.json
 done
+python tools/time_angles.py > $O/angles_$TAG.txt 2>&1; RB200_ANGLES=launches python tools/time_angles.py >> $O/angles_$TAG.txt 2>&1; cat $O/angles_$TAG.txt
 [ -n "$QUICK" ] && exit 0
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches_rfmip_$TAG.csv python bench.py --config rfmip --steps 1 --warmup 3 --no-cpu --no-e2e --no-ref-cuda > $O/ncu_list_rfmip_$TAG.log 2>&1
+python tools/launch_summary.py $O/launches_rfmip_$TAG.csv > $O/launches_rfmip_${TAG}_summary.txt 2>&1
 B="python bench.py --steps 1 --warmup 3 --no-cpu --no-e2e --no-ref-cuda"
 ncu --metrics gpu__time_duration.sum --clock-control none -c 300 --csv --log-file $O/launches_$TAG.csv $B > $O/ncu_list_$TAG.log 2>&1
 python tools/launch_summary.py $O/launches_$TAG.csv > $O/launches_${TAG}_summary.txt 2>&1
