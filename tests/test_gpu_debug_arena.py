@@ -86,6 +86,24 @@ def test_host_pipeline_with_ragged_chunks_under_debug_mode():
     _same(ref[0], _snapshot(o_lw), "host lw"); _same(ref[1], _snapshot(o_sw), "host sw")
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+@pytest.mark.parametrize("n_ang,reduced", [(2, False), (4, False), (3, True)])
+def test_gauss_angles_under_debug_mode(dtype, n_ang, reduced):
+    """Several Gauss angles: the strips hold {trans, source_up} per angle (fused_lw_ma.cu), so a strip is n_ang times longer;
+    the reduced g-point set mixes those launches with one pass per angle for its narrow bands."""
+    lw, _ = _solvers(dtype, cloudy=True, reduced=reduced)
+    lw.set_fused_path(0)
+    lw.set_tile_columns(64)
+    lw.n_gauss_angles = n_ang
+    cols = api.DeviceColumns(rce_atmosphere(150, 33, cloudy=True), dtype)
+    kw = dict(switch_cloud_optics=True, switch_output_bnd_fluxes=True)
+    ref = _snapshot(lw.solve_gpu(cols, **kw))
+    lw.set_debug(1)
+    for rep in range(2):
+        _same(ref, _snapshot(lw.solve_gpu(cols, **kw)), f"lw {n_ang} angles")
+    lw.set_debug(0)
+
+
 def test_an_overwritten_canary_fails_the_call():
     """flags = 3: the library corrupts one canary byte after arming them; the call must fail and name the canary."""
     lw, sw = _solvers(torch.float32)
