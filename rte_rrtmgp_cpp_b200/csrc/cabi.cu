@@ -1394,17 +1394,12 @@ void fused_pair(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, con
         CK(cudaEventRecord(pp.e_side[1], pp.side)); CK(cudaStreamWaitEvent(s, pp.e_side[1], 0));
         return;
     }
-    const int wave = std::max(pair_blocks_per_wave<Real>(), 1);
-    // one tile size for both: the smaller of the two automatic choices
-    const int cpb = FUSED_THREADS / 4;
-    const int tile = std::min(FusedJob<Real>::auto_tile(glw, clw->ncol, clw->nlay, wave, cpb), FusedJob<Real>::auto_tile(gsw, csw->ncol, csw->nlay, wave, cpb));
-    FusedJob<Real> L, S;
-    L.setup(glw, clw, olw, s, false, tile, wave);
-    S.setup(gsw, csw, osw, s, true, tile, wave);
-    // paired launches need both roles with the same particulate flag (one kernel instantiation per flag); the fp64 build
-    // measured slower paired (pair_supported refuses it)
-    const bool pairable = sizeof(Real) == 4 && !L.colres && !S.colres && glw->h.gw == 16 && gsw->h.gw == 16 && L.nang == 1 &&
-                          ((L.cloud || L.aerosol) == (S.cloud || S.aerosol));
+    // paired launches need both roles with the same particulate flag (one kernel instantiation per flag), one longwave angle
+    // (several run in their own kernels, fused_lw_ma.cu) and the per-band path on both sides; the fp64 build measured slower
+    // paired (pair_supported refuses it).  Decided before any set-up work.
+    const bool pairable = sizeof(Real) == 4 && !FusedJob<Real>::wants_colres(glw, clw, false) && !FusedJob<Real>::wants_colres(gsw, csw, true) &&
+                          glw->h.gw == 16 && gsw->h.gw == 16 && clw->n_gauss_angles <= 1 &&
+                          ((clw->cloud != nullptr) == (csw->cloud != nullptr || csw->aerosol != nullptr));
     if (!pairable)
     {
         // nothing to pair: the two calls one after the other (each with its own tiling)
@@ -1412,6 +1407,13 @@ void fused_pair(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, con
         fused_fluxes<Real>(gsw, csw, osw, s, true);
         return;
     }
+    const int wave = std::max(pair_blocks_per_wave<Real>(), 1);
+    // one tile size for both: the smaller of the two automatic choices
+    const int cpb = FUSED_THREADS / 4;
+    const int tile = std::min(FusedJob<Real>::auto_tile(glw, clw->ncol, clw->nlay, wave, cpb), FusedJob<Real>::auto_tile(gsw, csw->ncol, csw->nlay, wave, cpb));
+    FusedJob<Real> L, S;
+    L.setup(glw, clw, olw, s, false, tile, wave);
+    S.setup(gsw, csw, osw, s, true, tile, wave);
     L2Pin pin(s, gsw->kmajor.p, gsw->kmajor.bytes);
     const int nbl = glw->h.nbnd, nbs = gsw->h.nbnd;
     for (int c0 = 0; c0 < L.ncol; c0 += tile)
