@@ -368,12 +368,15 @@ int rrtmgp_b200_profile(int enable, double* lw_ms, long long* lw_launches, doubl
  * back, src_test/test_rte_rrtmgp.cu:560-900) with the two advanced together tile by tile: band i of both k-distributions
  * runs in ONE launch whose CTAs alternate between the longwave and the shortwave role, so the L1-bound longwave work and the
  * DRAM-bound shortwave work share every SM.  Arguments as rrtmgp_b200_lw_fluxes / rrtmgp_b200_sw_fluxes; ncol and nlay must
- * agree; results are bit-identical to the two separate calls.  Bands the paired kernel does not cover (narrow bands of reduced
- * g-point sets, extra Gauss angles) and handles set to the column-resident path fall back to the single-role launches. */
+ * agree; results are bit-identical to the two separate calls.  Single bands the paired kernel does not cover run through the
+ * single-role launches; whole calls it does not cover (fp64, reduced g-point sets, several Gauss angles, different particulate
+ * flags, small calls on the column-resident path) run as the two calls side by side: the shortwave one on an internal side stream
+ * forked from and joined back into `stream`, so the caller still sees one stream-ordered call. */
 int rrtmgp_b200_lwsw_fluxes(rrtmgp_b200_gas_optics* go_lw, const rrtmgp_b200_columns* cols_lw, const rrtmgp_b200_fluxes* out_lw,
                             rrtmgp_b200_gas_optics* go_sw, const rrtmgp_b200_columns* cols_sw, const rrtmgp_b200_fluxes* out_sw,
                             void* stream);
-/* time and launches of the paired band loops collected by the last rrtmgp_b200_profile call */
+/* time and launches of the paired band loops collected by the last rrtmgp_b200_profile call (large calls run as two calls on two
+ * streams: the wall time from fork to join, one count per call pair) */
 int rrtmgp_b200_profile_pair(double* pair_ms, long long* pair_launches);
 
 /* ---- Allocation-free variant.  NO COUNTERPART IN THE REFERENCE: added for

@@ -1383,15 +1383,23 @@ void fused_pair(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, con
     if (glw == gsw) throw ArgError("lwsw_fluxes: the longwave and the shortwave call need their own k-distribution objects");
     if (clw->ncol != csw->ncol || clw->nlay != csw->nlay) throw ArgError("lwsw_fluxes: the two calls must cover the same columns");
     HandleCall hl(glw, s), hs(gsw, s);
-    if (FusedJob<Real>::wants_colres(glw, clw, false) && FusedJob<Real>::wants_colres(gsw, csw, true))
+    // the two calls side by side: the shortwave one on a side stream, forked from and joined back into the caller's stream
+    auto two_streams = [&](bool prof)
     {
-        // two small calls (column-resident kernels): neither fills the SMs, so the shortwave one runs on a side stream beside
-        // the longwave one, forked from and joined back into the caller's stream
         HostPipe& pp = host_pipe(gsw);
+        // profile (large calls only: two more events would show in a 40 us call): the band times of the two calls overlap, so
+        // the wall time from fork to join goes to the third counter
+        prof = prof && g_prof.on;
+        if (prof) { cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, s)); g_prof.ev[2].push_back(e); }
         CK(cudaEventRecord(pp.e_side[0], s)); CK(cudaStreamWaitEvent(pp.side, pp.e_side[0], 0));
         fused_fluxes<Real>(gsw, csw, osw, pp.side, true);
         fused_fluxes<Real>(glw, clw, olw, s, false);
         CK(cudaEventRecord(pp.e_side[1], pp.side)); CK(cudaStreamWaitEvent(s, pp.e_side[1], 0));
+        if (prof) { cudaEvent_t e; CK(cudaEventCreate(&e)); CK(cudaEventRecord(e, s)); g_prof.ev[2].push_back(e); g_prof.launches[2] += 1; }
+    };
+    if (FusedJob<Real>::wants_colres(glw, clw, false) && FusedJob<Real>::wants_colres(gsw, csw, true))
+    {
+        two_streams(false);     // two small calls (column-resident kernels): neither fills the SMs
         return;
     }
     // paired launches need both roles with the same particulate flag (one kernel instantiation per flag), one longwave angle
@@ -1402,9 +1410,14 @@ void fused_pair(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, con
                           ((clw->cloud != nullptr) == (csw->cloud != nullptr || csw->aerosol != nullptr));
     if (!pairable)
     {
-        // nothing to pair: the two calls one after the other (each with its own tiling)
-        fused_fluxes<Real>(glw, clw, olw, s, false);
-        fused_fluxes<Real>(gsw, csw, osw, s, true);
+        // nothing to pair (each call with its own tiling): on two streams the launches of one fill the tails of the other's
+        // (what the host pipeline has always done for the fp64 build: +5 %); RB200_HOST_CONCURRENT=0: one after the other
+        if (g_host_concurrent) two_streams(true);
+        else
+        {
+            fused_fluxes<Real>(glw, clw, olw, s, false);
+            fused_fluxes<Real>(gsw, csw, osw, s, true);
+        }
         return;
     }
     const int wave = std::max(pair_blocks_per_wave<Real>(), 1);
