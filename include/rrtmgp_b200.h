@@ -340,6 +340,12 @@ int rrtmgp_b200_fluxes_host(rrtmgp_b200_gas_optics* go_lw, const rrtmgp_b200_col
                             const rrtmgp_b200_fluxes* out_lw, rrtmgp_b200_gas_optics* go_sw,
                             const rrtmgp_b200_columns* cols_sw, const rrtmgp_b200_fluxes* out_sw,
                             int chunk_cols, void* stream);
+/* The column chunks rrtmgp_b200_fluxes_host cuts a call of ncol columns into (no GPU needed; for tests and for hosts that size
+ * their pinned buffers): wave_columns > 0 = the automatic ramp for a GPU whose resident wave of CTAs covers that many columns
+ * (1, 2, 4 waves at both ends, equal chunks of at most 8 waves between); wave_columns = 0 = equal chunks of chunk_columns.
+ * Writes up to max_chunks (first column, columns) pairs and the number of chunks. */
+int rrtmgp_b200_host_chunk_schedule(int ncol, int wave_columns, int chunk_columns, int max_chunks, int* first, int* count,
+                                    int* nchunks);
 /* tuning / introspection of the fused path: columns per tile (0 = default), and the number of
  * kernels the last fused call launched (for bench.py's gpu_launches). */
 int rrtmgp_b200_set_tile_columns(rrtmgp_b200_gas_optics* go, int ncol_tile);

@@ -92,6 +92,7 @@ SYMBOLS = {
     "rrtmgp_b200_sw_fluxes": (i, [vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp]),
     "rrtmgp_b200_lwsw_fluxes": (i, [vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp]),
     "rrtmgp_b200_profile_pair": (i, [C.POINTER(d), C.POINTER(C.c_longlong)]),
+    "rrtmgp_b200_host_chunk_schedule": (i, [i, i, i, i, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "rrtmgp_b200_fluxes_host": (i, [vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), vp, C.POINTER(ColumnsC), C.POINTER(FluxesC), i, vp]),
     "rrtmgp_b200_set_tile_columns": (i, [vp, i]),
     "rrtmgp_b200_set_debug": (i, [vp, i]),

@@ -1460,6 +1460,39 @@ void fused_pair(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, con
 }
 
 
+// The schedule of column chunks of the host pipeline: (first column, columns), contiguous, covering [0, ncol).
+// wave_cols == 0: equal chunks of `chunk` columns (an explicit chunk or tile size).  wave_cols = W > 0: a ramp.  The pipeline's
+// exposed time is the upload of the FIRST chunk and the download of the LAST one (the rest hides behind the kernels as long as a
+// chunk's copies are shorter than its neighbour's kernels), and every band launch of a chunk ends in a partly empty wave, so
+// chunks should be large.  Hence 1, 2, 4 waves of CTAs per role at both ends and equal chunks of up to 8 waves between (copies of
+// a chunk take ~0.3 of its kernels' time, so a chunk twice its neighbour still hides).  Measured: two equal chunks exposed 18 ms
+// of an 87 ms step at 8 GPUs (131 072 columns per rank); equal 4-wave chunks cost 6 % in tails at 1 GPU.
+static std::vector<std::pair<int, int>> chunk_schedule(int ncol, int wave_cols, int chunk)
+{
+    std::vector<std::pair<int, int>> sched;
+    std::vector<int> left, right;
+    int remaining = ncol;
+    if (wave_cols > 0)
+    {
+        const int W = wave_cols;
+        chunk = 8 * W;
+        for (int size = W; size < chunk && remaining > 3 * size; size *= 2) { left.push_back(size); right.push_back(size); remaining -= 2 * size; }
+        // a call of 1.5 to 3 waves still gets a one-wave first chunk: one chunk would expose its whole upload and download, two
+        // hide the larger one's upload and the smaller one's download
+        if (left.empty() && 2 * remaining > 3 * W) { left.push_back(W); remaining -= W; }
+    }
+    chunk = std::max(std::min(chunk, remaining), 1);
+    const int nmid = std::max((remaining + chunk - 1) / chunk, 1);
+    const int mid = std::min((((remaining + nmid - 1) / nmid + 31) / 32) * 32, remaining);   // equal chunks, whole CTAs
+    int c0 = 0;
+    for (int n : left) { sched.push_back({c0, n}); c0 += n; }
+    const int end = c0 + remaining;
+    for (; c0 < end; c0 += mid) sched.push_back({c0, std::min(mid, end - c0)});
+    c0 = end;                      // the last equal chunk may be short: the loop variable overshoots
+    for (auto it = right.rbegin(); it != right.rend(); ++it) { sched.push_back({c0, *it}); c0 += *it; }
+    return sched;
+}
+
 // one host array of the column set. kind 0: (ncol, n2) column-major, chunked by rows of the first index;
 // kind 1: (n2, ncol) band-major, a chunk is contiguous; kind 2: not column-dependent, uploaded whole
 struct HostItem { const void* h; int kind; size_t n2; void* d[2]; };
@@ -1495,40 +1528,17 @@ void fluxes_host(rrtmgp_b200_gas_optics* glw, const rrtmgp_b200_columns* clw, co
                 chunk = std::max(chunk, g->tile_cols > 0 ? g->tile_cols : 4 * wave * cpb);   // finer than a tile: shorter pipeline ramps
             }
     chunk = std::min(chunk, ncol);
-    // The schedule of chunks.  Explicit chunk_cols: equal chunks of that size.  Automatic: a ramp.  The pipeline's exposed time
-    // is the upload of the FIRST chunk and the download of the LAST one (the rest hides behind the kernels as long as a chunk's
-    // copies are shorter than its neighbour's kernels), and every band launch of a chunk ends in a partly empty wave, so
-    // chunks should be large.  Hence 1, 2, 4 waves of CTAs per role at both ends and equal chunks of up to 8 waves between
-    // (copies of a chunk take ~0.3 of its kernels' time, so a chunk twice its neighbour still hides).  Measured: two equal
-    // chunks exposed 18 ms of an 87 ms step at 8 GPUs (131072 columns per rank); equal 4-wave chunks cost 6 % in tails at 1 GPU.
-    std::vector<std::pair<int, int>> sched;      // (first column, columns)
+    const bool ramp = chunk_cols <= 0 && !(glw && glw->tile_cols > 0) && !(gsw && gsw->tile_cols > 0);   // a set tile size is the chunk size
+    int W = 0;
+    if (ramp)
     {
-        std::vector<int> left, right;
-        int remaining = ncol;
-        const bool ramp = chunk_cols <= 0 && !(glw && glw->tile_cols > 0) && !(gsw && gsw->tile_cols > 0);   // a set tile size is the chunk size
-        if (ramp)
-        {
-            rrtmgp_b200_gas_optics* g = glw ? glw : gsw;
-            const int cpb = FUSED_THREADS / (g->h.gw / 4);
-            const int wave = std::max(g->h.is_lw ? lw_blocks_per_wave<Real>(g->h.gw) : sw_blocks_per_wave<Real>(g->h.gw), 1);
-            const int W = wave * cpb;
-            chunk = 8 * W;
-            for (int size = W; size < chunk && remaining > 3 * size; size *= 2) { left.push_back(size); right.push_back(size); remaining -= 2 * size; }
-            // a shard of 1.5 to 3 waves (65 536 columns per rank at 8 GPUs) still gets a one-wave first chunk: one chunk would
-            // expose its whole upload and download (17 of 84 ms), two hide the larger one's upload and the smaller one's download
-            if (left.empty() && 2 * remaining > 3 * W) { left.push_back(W); remaining -= W; }
-        }
-        const int nmid = std::max((remaining + chunk - 1) / chunk, 1);
-        const int mid = std::min((((remaining + nmid - 1) / nmid + 31) / 32) * 32, remaining);   // equal chunks, whole CTAs
-        int c0 = 0;
-        for (int n : left) { sched.push_back({c0, n}); c0 += n; }
-        for (int end = c0 + remaining; c0 < end; c0 += mid) sched.push_back({c0, std::min(mid, end - c0)});
-        c0 = ncol;
-        for (int n : right) c0 -= n;
-        for (auto it = right.rbegin(); it != right.rend(); ++it) { sched.push_back({c0, *it}); c0 += *it; }
-        chunk = mid;
-        for (auto& sc : sched) chunk = std::max(chunk, sc.second);
+        rrtmgp_b200_gas_optics* g = glw ? glw : gsw;
+        const int cpb = FUSED_THREADS / (g->h.gw / 4);
+        W = std::max(g->h.is_lw ? lw_blocks_per_wave<Real>(g->h.gw) : sw_blocks_per_wave<Real>(g->h.gw), 1) * cpb;
     }
+    const std::vector<std::pair<int, int>> sched = chunk_schedule(ncol, ramp ? W : 0, chunk);      // (first column, columns)
+    chunk = 0;
+    for (auto& sc : sched) chunk = std::max(chunk, sc.second);
 
     // inputs, de-duplicated by host address (LW and SW normally share play/plev/tlay/vmr/col_dry)
     std::vector<HostItem> items;
@@ -1698,6 +1708,19 @@ int rrtmgp_b200_fluxes_host(rrtmgp_b200_gas_optics* go_lw, const rrtmgp_b200_col
         if (g0->dtype == RRTMGP_B200_F32) fluxes_host<float>(go_lw, cols_lw, out_lw, go_sw, cols_sw, out_sw, chunk_cols, (cudaStream_t)stream);
         else fluxes_host<double>(go_lw, cols_lw, out_lw, go_sw, cols_sw, out_sw, chunk_cols, (cudaStream_t)stream);
     });
+}
+int rrtmgp_b200_host_chunk_schedule(int ncol, int wave_columns, int chunk_columns, int max_chunks, int* first, int* count, int* nchunks)
+{
+    return guarded([&] {
+        if (ncol < 1 || wave_columns < 0 || (wave_columns == 0 && chunk_columns < 1) || !nchunks) throw ArgError("host_chunk_schedule: bad argument");
+        const auto sched = chunk_schedule(ncol, wave_columns, std::min(chunk_columns, ncol));
+        *nchunks = (int)sched.size();
+        for (int i = 0; i < (int)sched.size() && i < max_chunks; ++i)
+        {
+            if (first) first[i] = sched[i].first;
+            if (count) count[i] = sched[i].second;
+        }
+    }, false);
 }
 int rrtmgp_b200_lwsw_fluxes(rrtmgp_b200_gas_optics* go_lw, const rrtmgp_b200_columns* cols_lw, const rrtmgp_b200_fluxes* out_lw,
                             rrtmgp_b200_gas_optics* go_sw, const rrtmgp_b200_columns* cols_sw, const rrtmgp_b200_fluxes* out_sw, void* stream)

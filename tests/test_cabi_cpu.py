@@ -142,3 +142,34 @@ def test_shard_plan_host_logic_needs_no_device_and_no_nccl():
     assert L.rrtmgp_b200_shard_plan_create(100, 4, 4, None, None, C.byref(h)) == capi.E_ARG
     assert L.rrtmgp_b200_gather_fluxes(None, capi.F32, 3, 1, None, None, 0, 1, 0, None) == capi.E_ARG
     L.rrtmgp_b200_shard_plan_destroy(None)
+
+
+def test_host_pipeline_chunk_schedule():
+    """rrtmgp_b200_host_chunk_schedule: the chunks of the host pipeline are contiguous, cover every column once, are whole CTAs
+    (multiples of 32 columns) except the last of the equal run, ramp up 1-2-4 waves from both ends and never exceed 8 waves."""
+    import ctypes as C
+    L = capi.lib()
+    W = 23680                                    # one resident wave of the fp32 paired kernel on a B200: 148 SMs x 5 CTAs x 32 columns
+
+    def sched(ncol, wave, chunk=0):
+        first, count, n = (C.c_int * 256)(), (C.c_int * 256)(), C.c_int()
+        capi.check(L.rrtmgp_b200_host_chunk_schedule(ncol, wave, chunk, 256, first, count, C.byref(n)))
+        return [(first[i], count[i]) for i in range(n.value)]
+
+    for ncol in (1, 31, 100, W - 1, W, W + 1, 40000, 65536, 131072, 262144, 1048576, 1048577):
+        s = sched(ncol, W)
+        assert s[0][0] == 0 and sum(c for _, c in s) == ncol
+        assert all(s[i][0] + s[i][1] == s[i + 1][0] for i in range(len(s) - 1))
+        assert all(c > 0 and c <= 8 * W for _, c in s)
+    assert sched(20000, W) == [(0, 20000)]                               # under 1.5 waves: one chunk
+    assert sched(65536, W) == [(0, W), (W, 65536 - W)]                   # 1.5 .. 3 waves: a one-wave first chunk
+    s = sched(131072, W)                                                 # a rank's shard of the 1024 x 1024 domain at 8 GPUs
+    assert [c for _, c in s] == [W, 131072 - 2 * W, W]
+    s = [c for _, c in sched(1048576, W)]                                # the whole domain on one GPU
+    assert s[:3] == [W, 2 * W, 4 * W] and s[-3:] == [4 * W, 2 * W, W]
+    mid = s[3:-3]
+    assert len(set(mid[:-1])) == 1 and mid[0] % 32 == 0 and mid[0] <= 8 * W and sum(s) == 1048576
+    # explicit chunk size: equal chunks of whole CTAs, no ramp
+    s = sched(301, 0, 128)
+    assert [c for _, c in s] == [128, 128, 45]
+    assert L.rrtmgp_b200_host_chunk_schedule(0, W, 0, 0, None, None, None) == capi.E_ARG
