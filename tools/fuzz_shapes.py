@@ -51,7 +51,11 @@ for case in range(ncases):
     lw.n_gauss_angles = n_ang
     cols = api.DeviceColumns(atm, dtype)
     kw = dict(switch_cloud_optics=cloudy, switch_output_bnd_fluxes=bnd)
-    if pair:
+    host = bool(rng.integers(4) == 0)
+    if host:                                       # the host-buffer pipeline with a chunk size that does not divide the columns
+        chunk = int(rng.choice([0, 32, 50, 96]))
+        o_lw, o_sw = api.solve_host(lw, sw, api.HostColumns(atm, dtype), chunk_columns=chunk, switch_aerosol_optics=aero, **kw)
+    elif pair:
         o_lw, o_sw = api.solve_pair(lw, sw, cols, switch_aerosol_optics=aero, **kw)
     else:
         o_lw, o_sw = lw.solve_gpu(cols, **kw), sw.solve_gpu(cols, switch_aerosol_optics=aero, **kw)
@@ -65,7 +69,7 @@ for case in range(ncases):
             d = max(d, float(np.max(np.abs(v - ref[k]))))
     worst[dtype] = max(worst[dtype], d)
     desc = (f"case {case:3d} ncol {ncol:3d} nlay {nlay:3d} top {int(top)} cloud {int(cloudy)} aero {int(aero)} reduced {int(reduced)} "
-            f"{str(dtype)[6:]:7s} angles {n_ang} path {path} pair {int(pair)} tile {tile:2d} bnd {int(bnd)}  max|d| {d:.2e}")
+            f"{str(dtype)[6:]:7s} angles {n_ang} path {path} pair {int(pair)} host {int(host)} tile {tile:2d} bnd {int(bnd)}  max|d| {d:.2e}")
     print(desc, flush=True)
     if d > TOL[dtype]:
         print("MISS", desc)
