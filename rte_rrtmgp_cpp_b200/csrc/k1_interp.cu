@@ -10,6 +10,7 @@
 // bit-identical to the fp64 CPU path on the same input values.
 #include "common.cuh"
 #include "launch.hpp"
+#include <algorithm>
 
 namespace rb200 {
 
@@ -72,12 +73,22 @@ interp_kernel(const DevPlan<Real> P, const VmrArgs vmr, int ncol, int c0, int nc
 
     auto cgas = [&](int ig) -> double { return ig == 0 ? cd : vmr_at<Real>(vmr, ig - 1, i, l) * cd; };
 
-    if (ro.jtemp) ro.jtemp[i] = jt;
-    if (ro.jpress) ro.jpress[i] = jp;
-    if (ro.tropo) ro.tropo[i] = (signed char)tropo;
-    if (ro.col_gas)
-        for (int ig = 0; ig <= P.ngas; ++ig) ro.col_gas[i + ncl * ig] = (Real)cgas(ig);
-    if (st.cell)
+    // gridDim.y > 1 (small calls, too few cells to fill the SMs with one thread per cell): the work of a cell is spread over
+    // y — y = 0 writes the cell record, the minor-gas scalings, the Planck positions and the tropopause bit, y = 1.. take the
+    // flavors round-robin.  Every thread repeats the few operations above; what each stores is computed exactly as before.
+    const int ny = (int)gridDim.y, ry = (int)blockIdx.y;
+    const bool do_cell = ry == 0;
+    const int f_first = ny == 1 ? 0 : ry - 1, f_step = ny == 1 ? 1 : ny - 1;
+
+    if (do_cell)
+    {
+        if (ro.jtemp) ro.jtemp[i] = jt;
+        if (ro.jpress) ro.jpress[i] = jp;
+        if (ro.tropo) ro.tropo[i] = (signed char)tropo;
+        if (ro.col_gas)
+            for (int ig = 0; ig <= P.ngas; ++ig) ro.col_gas[i + ncl * ig] = (Real)cgas(ig);
+    }
+    if (st.cell && do_cell)
     {
         V4<Real> rec;
         rec.x = (Real)fpress;
@@ -136,7 +147,8 @@ interp_kernel(const DevPlan<Real> P, const VmrArgs vmr, int ncol, int c0, int nc
     }
 
     // F90:127-169
-    for (int f = 0; f < P.nflav; ++f)
+    if (ny > 1 && ry == 0) return;
+    for (int f = f_first; f < P.nflav; f += f_step)
     {
         const int ig1 = P.flavor[2 * f], ig2 = P.flavor[2 * f + 1];
         const double cg1 = cgas(ig1), cg2 = cgas(ig2);
@@ -203,7 +215,10 @@ void launch_interp(const DevPlan<Real>& P, const VmrArgs& vmr, int ncol, int c0,
 {
     RefInterpOut<Real> ro{jtemp, jpress, tropo, jeta, (Real*)col_mix, (Real*)fminor, (Real*)fmajor, (Real*)col_gas};
     const size_t n = (size_t)nc * nlay;
-    interp_kernel<Real><<<(unsigned)((n + 127) / 128), 128, 0, s>>>(
+    // a small call (under 65 536 cells; 100 RFMIP sites x 60 layers = 47 CTAs of one thread per cell): spread each cell's flavors
+    // over the grid's y dimension, the kernel is a 20 us latency chain per thread otherwise
+    const unsigned ny = n < 65536 ? (unsigned)std::min(P.nflav + 1, 16) : 1u;
+    interp_kernel<Real><<<dim3((unsigned)((n + 127) / 128), ny), 128, 0, s>>>(
             P, vmr, ncol, c0, nc, nlay, (const Real*)play, (const Real*)tlay, (const Real*)col_dry,
             (const Real*)tlev, st, ro);
     count_launch();
